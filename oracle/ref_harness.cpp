@@ -1,0 +1,285 @@
+// oracle/ref_harness.cpp -- TEST INFRASTRUCTURE (never linked into, loaded by, or timed as the product).
+//
+// Harness around the UNMODIFIED reference sources, compiled where they lie under /root/reference/src
+// (see oracle/Makefile).  It reaches the reference's file-static MapPhotons() and globals by
+// #including src/photonmap.cpp with `main` renamed, and exposes seeded, batched entry points whose
+// binary outputs become the golden fixtures under tests/golden/ and the "reference" CPU baseline:
+//
+//   ref_harness dump_scene <in.scn> <out.txt> [-real]
+//   ref_harness camrays    <in.scn> <W> <H> <rays.bin>
+//   ref_harness isect      <in.scn> <rays.bin> <hits.bin> [threads]      (R3Scene::Intersects, R3Scene.cpp:471)
+//   ref_harness photons    <in.scn> <out_prefix> <seed> [photonmap flags] (MapPhotons, photonmap.cpp:260)
+//   ref_harness gather     <photons.bin> <queries.bin> <out.bin> <k> <r> <filter 0|1|2> [threads]
+//                                                     (EstimateRadiance, photon_utils.cpp:72)
+//   ref_harness shade      <in.scn> <rays.bin> <out.bin> <seed> [photonmap flags + -load_global f -load_caustic f]
+//                                                     (Intersects + RayTrace, render.cpp:119-124)
+// With -DGI_REF_MAIN the same translation unit is just the reference program (`photonmap_ref`).
+//
+// The only deviation from the reference text: `offsetof` is redefined to yield an int, because
+// `new R3Kdtree<Photon*>(array, offsetof(...))` (photonmap.cpp:365,372) is ambiguous under g++
+// (int offset vs function-pointer overload, R3Kdtree.h:35-36).  Same value, same overload the
+// author's compiler picked.
+
+#include <cstddef>
+#include <cstdio>
+#include <cstdlib>
+#include <cstring>
+#include <cstdint>
+#include <cmath>
+#include <map>
+#include <vector>
+#include <string>
+#include <thread>
+#include <algorithm>
+#include <chrono>
+#include "R3Graphics/R3Graphics.h"
+#undef offsetof
+#define offsetof(t, m) ((int)__builtin_offsetof(t, m))
+#define main ref_main
+#include "photonmap.cpp"
+#undef main
+#include "raytracer.h"
+
+#ifdef GI_REF_MAIN
+int main(int argc, char **argv) { return ref_main(argc, argv); }
+#else
+
+// ---------------------------------------------------------------- file formats (shared with tests/)
+static const uint32_t RAYS_MAGIC = 0x59415247;  // "GRAY": u32 magic, u32 n, n x {f64 o[3], f64 d[3]}
+static const uint32_t HITS_MAGIC = 0x54494847;  // "GHIT": u32 magic, u32 n, n x HitRec
+static const uint32_t PMAP_MAGIC = 0x4d504947;  // "GIPM": u32 magic, u32 version, u64 n, n x 32-byte Photon
+struct HitRec { int32_t hit; int32_t shape_id; double t; double p[3]; double n[3]; };
+static_assert(sizeof(HitRec) == 64, "HitRec layout");
+static_assert(sizeof(Photon) == 32, "reference Photon layout (render.h:17-21)");
+struct QueryRec { double p[3], n[3], bounce[3], cos_theta, kd[3], ks[3], shininess; };  // 17 doubles
+static_assert(sizeof(QueryRec) == 136, "QueryRec layout");
+
+static void die(const char *msg) { fprintf(stderr, "ref_harness: %s\n", msg); exit(2); }
+
+static std::vector<double> read_rays(const char *path, uint32_t &n) {
+  FILE *f = fopen(path, "rb"); if (!f) die("cannot open rays file");
+  uint32_t hdr[2]; if (fread(hdr, 4, 2, f) != 2 || hdr[0] != RAYS_MAGIC) die("bad rays file");
+  n = hdr[1]; std::vector<double> r((size_t)n * 6);
+  if (fread(r.data(), 48, n, f) != n) die("short rays file");
+  fclose(f); return r;
+}
+
+// ---------------------------------------------------------------- scene walk (reference DFS order)
+// Order = order in which R3SceneNode::Intersects visits shapes: a node's elements (insertion order),
+// each element's shapes (insertion order), then the node's children (R3SceneNode.cpp:461-490).
+struct Walk {
+  std::map<const R3Shape *, int> shape_id;
+  std::vector<const R3Shape *> shapes;
+  std::vector<int> shape_node, shape_elem;
+  std::vector<const R3SceneNode *> nodes;
+  std::vector<int> node_parent;
+  std::vector<const R3SceneElement *> elems;
+  void visit(const R3SceneNode *node, int parent) {
+    int me = (int)nodes.size(); nodes.push_back(node); node_parent.push_back(parent);
+    for (int i = 0; i < node->NElements(); i++) {
+      const R3SceneElement *e = node->Element(i);
+      int eid = (int)elems.size(); elems.push_back(e);
+      for (int j = 0; j < e->NShapes(); j++) {
+        const R3Shape *s = e->Shape(j);
+        shape_id[s] = (int)shapes.size(); shapes.push_back(s); shape_node.push_back(me); shape_elem.push_back(eid);
+      }
+    }
+    for (int i = 0; i < node->NChildren(); i++) visit(node->Child(i), me);
+  }
+};
+
+static R3Scene *load_scene(const char *path, bool real) {
+  R3Scene *s = ReadScene((char *)path, real);
+  if (!s) die("cannot read scene");
+  SCENE = s;
+  SCENE_RADIUS = s->BBox().DiagonalRadius();
+  SCENE_AMBIENT = s->Ambient();
+  SCENE_NLIGHTS = s->NLights();
+  return s;
+}
+
+// ---------------------------------------------------------------- dump_scene
+static void p3(FILE *f, const double *v) { fprintf(f, " %.17g %.17g %.17g", v[0], v[1], v[2]); }
+static void prgb(FILE *f, const RNRgb &c) { fprintf(f, " %.17g %.17g %.17g", c.R(), c.G(), c.B()); }
+static void ppt(FILE *f, const R3Point &p) { fprintf(f, " %.17g %.17g %.17g", p.X(), p.Y(), p.Z()); }
+static void pvec(FILE *f, const R3Vector &p) { fprintf(f, " %.17g %.17g %.17g", p.X(), p.Y(), p.Z()); }
+
+static int cmd_dump_scene(int argc, char **argv) {
+  if (argc < 4) die("usage: dump_scene in.scn out.txt [-real]");
+  bool real = (argc > 4 && !strcmp(argv[4], "-real"));
+  R3Scene *scene = load_scene(argv[2], real);
+  Walk w; w.visit(scene->Root(), -1);
+  FILE *f = fopen(argv[3], "w"); if (!f) die("cannot open output");
+  // materials are identified by their brdf values per element (pointer identity is not portable)
+  fprintf(f, "nodes %d\n", (int)w.nodes.size());
+  for (size_t i = 0; i < w.nodes.size(); i++) {
+    const R4Matrix &m = w.nodes[i]->Transformation().Matrix();
+    const R4Matrix &mi = w.nodes[i]->Transformation().InverseMatrix();
+    fprintf(f, "node %d parent %d\n m", (int)i, w.node_parent[i]);
+    for (int r = 0; r < 4; r++) for (int c = 0; c < 4; c++) fprintf(f, " %.17g", m[r][c]);
+    fprintf(f, "\n minv");
+    for (int r = 0; r < 4; r++) for (int c = 0; c < 4; c++) fprintf(f, " %.17g", mi[r][c]);
+    fprintf(f, "\n");
+  }
+  fprintf(f, "elements %d\n", (int)w.elems.size());
+  for (size_t i = 0; i < w.elems.size(); i++) {
+    const R3Material *mat = w.elems[i]->Material();
+    const R3Brdf *b = mat ? mat->Brdf() : &R3default_brdf;
+    if (!b) b = &R3default_brdf;
+    fprintf(f, "element %d\n ka", (int)i); prgb(f, b->Ambient());
+    fprintf(f, "\n kd"); prgb(f, b->Diffuse());
+    fprintf(f, "\n ks"); prgb(f, b->Specular());
+    fprintf(f, "\n kt"); prgb(f, b->Transmission());
+    fprintf(f, "\n ke"); prgb(f, b->Emission());
+    fprintf(f, "\n n %.17g ir %.17g\n", b->Shininess(), b->IndexOfRefraction());
+  }
+  fprintf(f, "shapes %d\n", (int)w.shapes.size());
+  for (size_t i = 0; i < w.shapes.size(); i++) {
+    const R3Shape *s = w.shapes[i];
+    fprintf(f, "shape %d node %d element %d ", (int)i, w.shape_node[i], w.shape_elem[i]);
+    if (s->ClassID() == R3Sphere::CLASS_ID()) {
+      const R3Sphere *q = (const R3Sphere *)s;
+      fprintf(f, "sphere"); ppt(f, q->Center()); fprintf(f, " %.17g\n", q->Radius());
+    } else if (s->ClassID() == R3Box::CLASS_ID()) {
+      const R3Box *q = (const R3Box *)s;
+      fprintf(f, "box"); ppt(f, q->Min()); ppt(f, q->Max()); fprintf(f, "\n");
+    } else if (s->ClassID() == R3Cylinder::CLASS_ID()) {
+      const R3Cylinder *q = (const R3Cylinder *)s;
+      fprintf(f, "cylinder"); ppt(f, q->Axis().Start()); ppt(f, q->Axis().End()); fprintf(f, " %.17g\n", q->Radius());
+    } else if (s->ClassID() == R3Cone::CLASS_ID()) {
+      const R3Cone *q = (const R3Cone *)s;
+      fprintf(f, "cone"); ppt(f, q->Axis().Start()); ppt(f, q->Axis().End()); fprintf(f, " %.17g\n", q->Radius());
+    } else if (s->ClassID() == R3Circle::CLASS_ID()) {
+      const R3Circle *q = (const R3Circle *)s;
+      fprintf(f, "circle"); ppt(f, q->Center()); pvec(f, q->Normal()); fprintf(f, " %.17g\n", q->Radius());
+    } else if (s->ClassID() == R3Triangle::CLASS_ID()) {
+      const R3Triangle *q = (const R3Triangle *)s;
+      fprintf(f, "tri");
+      for (int k = 0; k < 3; k++) ppt(f, q->Vertex(k)->Position());
+      fprintf(f, "\n");
+    } else if (s->ClassID() == R3TriangleArray::CLASS_ID()) {
+      const R3TriangleArray *q = (const R3TriangleArray *)s;
+      fprintf(f, "mesh %d\n", q->NTriangles());
+      for (int t = 0; t < q->NTriangles(); t++) {
+        fprintf(f, " t");
+        for (int k = 0; k < 3; k++) ppt(f, q->Triangle(t)->Vertex(k)->Position());
+        fprintf(f, "\n");
+      }
+    } else {
+      fprintf(f, "unknown %d\n", (int)s->ClassID());
+    }
+  }
+  fprintf(f, "lights %d\n", scene->NLights());
+  for (int i = 0; i < scene->NLights(); i++) {
+    R3Light *l = scene->Light(i);
+    fprintf(f, "light %d ", i);
+    if (l->ClassID() == R3DirectionalLight::CLASS_ID()) {
+      R3DirectionalLight *q = (R3DirectionalLight *)l;
+      fprintf(f, "dir"); prgb(f, q->Color()); fprintf(f, " %.17g", q->Intensity()); pvec(f, q->Direction());
+    } else if (l->ClassID() == R3PointLight::CLASS_ID()) {
+      R3PointLight *q = (R3PointLight *)l;
+      fprintf(f, "point"); prgb(f, q->Color()); fprintf(f, " %.17g", q->Intensity()); ppt(f, q->Position());
+      fprintf(f, " %.17g %.17g %.17g", q->ConstantAttenuation(), q->LinearAttenuation(), q->QuadraticAttenuation());
+    } else if (l->ClassID() == R3SpotLight::CLASS_ID()) {
+      R3SpotLight *q = (R3SpotLight *)l;
+      fprintf(f, "spot"); prgb(f, q->Color()); fprintf(f, " %.17g", q->Intensity()); ppt(f, q->Position());
+      pvec(f, q->Direction());
+      fprintf(f, " %.17g %.17g %.17g", q->ConstantAttenuation(), q->LinearAttenuation(), q->QuadraticAttenuation());
+      fprintf(f, " %.17g %.17g", q->DropOffRate(), q->CutOffAngle());
+    } else if (l->ClassID() == R3AreaLight::CLASS_ID()) {
+      R3AreaLight *q = (R3AreaLight *)l;
+      fprintf(f, "area"); prgb(f, q->Color()); fprintf(f, " %.17g", q->Intensity()); ppt(f, q->Position());
+      pvec(f, q->Direction()); fprintf(f, " %.17g", q->Radius());
+      fprintf(f, " %.17g %.17g %.17g", q->ConstantAttenuation(), q->LinearAttenuation(), q->QuadraticAttenuation());
+    } else if (l->ClassID() == R3RectLight::CLASS_ID()) {
+      R3RectLight *q = (R3RectLight *)l;
+      fprintf(f, "rect"); prgb(f, q->Color()); fprintf(f, " %.17g", q->Intensity()); ppt(f, q->Position());
+      pvec(f, q->Direction()); pvec(f, q->PrimaryAxis()); pvec(f, q->SecondaryAxis());
+      fprintf(f, " %.17g %.17g", q->PrimaryLength(), q->SecondaryLength());
+      fprintf(f, " %.17g %.17g %.17g", q->ConstantAttenuation(), q->LinearAttenuation(), q->QuadraticAttenuation());
+    } else fprintf(f, "unknown");
+    fprintf(f, "\n");
+  }
+  const R3Camera &c = scene->Camera();
+  fprintf(f, "camera"); ppt(f, c.Origin()); pvec(f, c.Towards()); pvec(f, c.Up()); pvec(f, c.Right());
+  fprintf(f, " %.17g %.17g %.17g %.17g\n", c.XFOV(), c.YFOV(), c.Near(), c.Far());
+  fprintf(f, "ambient"); prgb(f, scene->Ambient()); fprintf(f, "\nbackground"); prgb(f, scene->Background());
+  fprintf(f, "\nbbox"); ppt(f, scene->BBox().Min()); ppt(f, scene->BBox().Max());
+  fprintf(f, "\ncentroid"); ppt(f, scene->Centroid());
+  fprintf(f, "\nradius %.17g\n", SCENE_RADIUS);
+  fclose(f);
+  return 0;
+}
+
+// ---------------------------------------------------------------- camrays (render.cpp:64-117, no DOF)
+static int cmd_camrays(int argc, char **argv) {
+  if (argc < 6) die("usage: camrays in.scn W H rays.bin");
+  R3Scene *scene = load_scene(argv[2], false);
+  int W = atoi(argv[3]), H = atoi(argv[4]);
+  scene->SetViewport(R2Viewport(0, 0, W, H));
+  R3Camera camera = scene->Camera();
+  R2Viewport viewport = scene->Viewport();
+  R3Point far_org = camera.Origin() + camera.Towards() * FOCUS_DEPTH;
+  R3Vector far_right = camera.Right() * tan(camera.XFOV()) * FOCUS_DEPTH;
+  R3Vector far_up = camera.Up() * tan(camera.YFOV()) * FOCUS_DEPTH;
+  FILE *f = fopen(argv[5], "wb"); if (!f) die("cannot open output");
+  uint32_t hdr[2] = {RAYS_MAGIC, (uint32_t)(W * H)};
+  fwrite(hdr, 4, 2, f);
+  for (int i = 0; i < W; i++) for (int j = 0; j < H; j++) {   // column-major like image_buffer[i][j]
+    RNScalar dx = (RNScalar)(2 * (i - viewport.XCenter())) / (RNScalar)viewport.Width();
+    RNScalar dy = (RNScalar)(2 * (j - viewport.YCenter())) / (RNScalar)viewport.Height();
+    R3Point far_point = far_org + (far_right * dx) + (far_up * dy);
+    R3Ray ray(camera.Origin(), far_point);
+    double r[6] = {ray.Start().X(), ray.Start().Y(), ray.Start().Z(), ray.Vector().X(), ray.Vector().Y(), ray.Vector().Z()};
+    fwrite(r, 8, 6, f);
+  }
+  fclose(f);
+  return 0;
+}
+
+// ---------------------------------------------------------------- isect
+static int cmd_isect(int argc, char **argv) {
+  if (argc < 5) die("usage: isect in.scn rays.bin hits.bin [threads]");
+  R3Scene *scene = load_scene(argv[2], false);
+  Walk w; w.visit(scene->Root(), -1);
+  uint32_t n; std::vector<double> rays = read_rays(argv[3], n);
+  int threads = argc > 5 ? atoi(argv[5]) : 1; if (threads < 1) threads = 1;
+  std::vector<HitRec> hits(n);
+  auto t0 = std::chrono::steady_clock::now();
+  auto work = [&](int id) {
+    for (uint32_t i = id; i < n; i += threads) {
+      const double *r = &rays[(size_t)i * 6];
+      R3Ray ray(R3Point(r[0], r[1], r[2]), R3Vector(r[3], r[4], r[5]), TRUE);
+      R3SceneNode *node; R3SceneElement *element; R3Shape *shape; R3Point point; R3Vector normal; RNScalar t;
+      HitRec h; memset(&h, 0, sizeof(h)); h.shape_id = -1;
+      if (scene->Intersects(ray, &node, &element, &shape, &point, &normal, &t)) {
+        h.hit = 1; h.shape_id = w.shape_id[shape]; h.t = t;
+        h.p[0] = point.X(); h.p[1] = point.Y(); h.p[2] = point.Z();
+        h.n[0] = normal.X(); h.n[1] = normal.Y(); h.n[2] = normal.Z();
+      }
+      hits[i] = h;
+    }
+  };
+  std::vector<std::thread> th;
+  for (int i = 1; i < threads; i++) th.emplace_back(work, i);
+  work(0);
+  for (auto &x : th) x.join();
+  double sec = std::chrono::duration<double>(std::chrono::steady_clock::now() - t0).count();
+  FILE *f = fopen(argv[4], "wb"); if (!f) die("cannot open output");
+  uint32_t hdr[2] = {HITS_MAGIC, n};
+  fwrite(hdr, 4, 2, f); fwrite(hits.data(), sizeof(HitRec), n, f); fclose(f);
+  printf("{\"cmd\": \"isect\", \"rays\": %u, \"threads\": %d, \"seconds\": %.6f, \"mrays_per_s\": %.6f}\n",
+         n, threads, sec, n / sec / 1e6);
+  return 0;
+}
+
+int main(int argc, char **argv) {
+  if (argc < 2) die("usage: ref_harness <dump_scene|camrays|isect|photons|gather|shade> ...");
+  std::string c = argv[1];
+  if (c == "dump_scene") return cmd_dump_scene(argc, argv);
+  if (c == "camrays") return cmd_camrays(argc, argv);
+  if (c == "isect") return cmd_isect(argc, argv);
+  die("unknown command");
+  return 2;
+}
+#endif
