@@ -1,0 +1,238 @@
+/* gi_b200.h -- C ABI of the B200-native hot path of the photon-mapping renderer.
+ *
+ * Drop-in boundary.  The reference (ReillyBova/Global-Illumination) has no FFI: its "boundary" is two
+ * C++ calls inside main() -- MapPhotons() (src/photonmap.cpp:461) and RenderImage(aa, W, H)
+ * (src/photonmap.cpp:471) -- which talk through ~60 mutable globals (src/render.h:27-110) and the
+ * R3Scene object graph.  This header replaces exactly those two call sites with a plain-C ABI:
+ * plain pointers and sizes, POD structs, no C++/torch types.  Each entry point cites the reference
+ * interface it stands in for.  Host code (our `photonmap` CLI, tests, bench) stays C++/Python above
+ * this line; everything below it is hand-written sm_100a CUDA.
+ *
+ * Conventions
+ *   - every function returns 0 on success, non-zero on failure; gi_last_error() gives the message.
+ *     The library never calls exit() (the reference prints to stderr and exit(-1)s; main() maps our
+ *     status to the same text/exit code).
+ *   - the caller owns every host buffer passed in or out; the library owns all device memory behind
+ *     the opaque GiContext.
+ *   - there is NO CPU fallback: without a CUDA device gi_create fails.
+ *   - all geometry is double precision like the reference (RNScalar = double, RNCompat.h:82-88).
+ */
+#ifndef GI_B200_H
+#define GI_B200_H
+
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+#define GI_ABI_VERSION 1
+
+/* ------------------------------------------------------------------------------------------------
+ * Scene description (flattened R3Scene; src/R3Graphics/R3Scene.h).  Order is the order in which
+ * R3SceneNode::Intersects (R3SceneNode.cpp:420-510) visits things: a node's elements in insertion
+ * order, each element's shapes in insertion order, then the node's children, depth first.
+ * ---------------------------------------------------------------------------------------------- */
+
+typedef struct GiMaterial {          /* R3Brdf (R3Brdf.h:50-58) */
+  double ka[3], kd[3], ks[3], kt[3], ke[3];
+  double shininess;
+  double ir;
+} GiMaterial;
+
+typedef struct GiNode {              /* R3SceneNode: transformation to the parent's coordinates */
+  int32_t parent;                    /* -1 for the root */
+  int32_t reserved;
+  double m[16];                      /* row-major 4x4, R3Affine::Matrix() */
+  double minv[16];                   /* R3Affine::InverseMatrix() (R4Matrix::Invert, R4Matrix.cpp:252) */
+} GiNode;
+
+typedef struct GiElement {           /* R3SceneElement: (node, material) bucket of shapes */
+  int32_t node;
+  int32_t material;                  /* index into GiScene.materials */
+} GiElement;
+
+enum GiShapeType {
+  GI_SHAPE_TRIANGLE = 0,             /* d = v0 v1 v2                                (R3Triangle)      */
+  GI_SHAPE_SPHERE   = 1,             /* d = centre(3) radius                        (R3Sphere)        */
+  GI_SHAPE_BOX      = 2,             /* d = min(3) max(3)                           (R3Box)           */
+  GI_SHAPE_CYLINDER = 3,             /* d = axis start(3) axis end(3) radius        (R3Cylinder)      */
+  GI_SHAPE_CONE     = 4,             /* d = axis start(3) axis end(3) radius        (R3Cone)          */
+  GI_SHAPE_CIRCLE   = 5              /* d = centre(3) unit normal(3) radius         (R3Circle)        */
+};
+
+typedef struct GiPrim {              /* one intersectable primitive; a mesh is a run of triangles */
+  int32_t type;                      /* GiShapeType */
+  int32_t element;                   /* index into GiScene.elements (gives node + material) */
+  int32_t shape;                     /* reference shape id (DFS order); all triangles of one       */
+                                     /* R3TriangleArray share it                                   */
+  int32_t index_in_shape;            /* triangle index inside its mesh, 0 otherwise                */
+  double d[9];
+} GiPrim;
+
+enum GiLightType { GI_LIGHT_DIR = 0, GI_LIGHT_POINT = 1, GI_LIGHT_SPOT = 2, GI_LIGHT_AREA = 3, GI_LIGHT_RECT = 4 };
+
+typedef struct GiLight {             /* R3{Directional,Point,Spot,Area,Rect}Light */
+  int32_t type;
+  int32_t active;
+  double color[3];
+  double intensity;
+  double position[3];
+  double direction[3];               /* unit; area/rect: emitting normal */
+  double axis1[3], axis2[3];         /* rect light unit axes */
+  double len1, len2;                 /* rect light side lengths */
+  double radius;                     /* area light */
+  double ca, la, qa;                 /* constant / linear / quadratic attenuation */
+  double dropoff, cutoff;            /* spot light */
+} GiLight;
+
+typedef struct GiCamera {            /* R3Camera */
+  double eye[3], towards[3], up[3], right[3];
+  double xfov, yfov, neardist, fardist;
+} GiCamera;
+
+typedef struct GiScene {
+  int32_t n_nodes, n_elements, n_materials, n_prims, n_lights, n_shapes;
+  const GiNode *nodes;
+  const GiElement *elements;
+  const GiMaterial *materials;
+  const GiPrim *prims;
+  const GiLight *lights;
+  GiCamera camera;
+  double ambient[3];
+  double background[3];
+  double bbox_min[3], bbox_max[3];   /* R3Scene::BBox() */
+  double centroid[3];                /* R3Scene::Centroid() */
+  double radius;                     /* SCENE_RADIUS = BBox().DiagonalRadius() (photonmap.cpp:455) */
+} GiScene;
+
+/* ------------------------------------------------------------------------------------------------
+ * Batched ray queries: R3Scene::Intersects(ray, &node,&element,&shape,&point,&normal,&t)
+ * (R3Scene.cpp:471-479) with min_t = 0, max_t = RN_INFINITY = 1e6 (R3Scene.h:73-76).
+ * ---------------------------------------------------------------------------------------------- */
+
+typedef struct GiRay { double o[3]; double d[3]; } GiRay;   /* d must be unit (R3Ray(p, v, TRUE)) */
+
+typedef struct GiHit {
+  int32_t hit;                       /* 0 = miss (all other fields zero, prim/shape = -1) */
+  int32_t shape;                     /* reference shape id */
+  int32_t prim;                      /* index into GiScene.prims */
+  int32_t element;
+  double t;
+  double p[3];                       /* world hit point */
+  double n[3];                       /* world geometric normal as the reference returns it */
+} GiHit;
+
+/* ------------------------------------------------------------------------------------------------
+ * Photon maps: struct Photon (src/render.h:17-21), 32 bytes.
+ * ---------------------------------------------------------------------------------------------- */
+
+typedef struct GiPhoton {
+  double position[3];
+  uint8_t rgbe[4];                   /* Ward RGBE (graphics_utils.cpp:50-77) */
+  uint16_t direction;                /* phi*256 + theta (photon_utils.cpp:56-60) */
+  uint16_t pad;
+} GiPhoton;
+
+enum GiMap { GI_MAP_GLOBAL = 0, GI_MAP_CAUSTIC = 1 };
+enum GiFilter { GI_FILTER_DISK = 0, GI_FILTER_CONE = 1, GI_FILTER_GAUSS = 2 };   /* Filter_Type, render.h:63 */
+
+typedef struct GiGatherQuery {       /* arguments of EstimateRadiance (photon_utils.cpp:72-75) */
+  double p[3];                       /* point */
+  double n[3];                       /* normal */
+  double bounce[3];                  /* exact_bounce */
+  double cos_theta;
+  double kd[3], ks[3];               /* brdf->Diffuse(), brdf->Specular() */
+  double shininess;
+} GiGatherQuery;
+
+/* ------------------------------------------------------------------------------------------------
+ * Parameters: one field per reference global (src/render.h:27-110, defaults src/photonmap.cpp:41-106)
+ * ---------------------------------------------------------------------------------------------- */
+
+typedef struct GiParams {
+  int32_t verbose, threads, fresnel;
+  double ir_air;
+  int32_t ambient, direct_illum, transmissive_illum, specular_illum, indirect_illum, caustic_illum;
+  int32_t direct_photon_illum, fast_global, irradiance_cache;
+  int32_t shadows, soft_shadows, light_test, shadow_test;
+  int32_t monte_carlo, max_monte_depth;
+  double prob_absorb;
+  int32_t recursive_shadows, distrib_transmissive, transmissive_test, distrib_specular, specular_test;
+  int32_t depth_of_field, dof_test;
+  double focus_depth, aperture_radius;
+  int32_t global_photon_count, caustic_photon_count, max_photon_depth;
+  int32_t indirect_test, global_estimate_size;
+  double global_estimate_dist;
+  int32_t global_filter, caustic_estimate_size;
+  double caustic_estimate_dist;
+  int32_t caustic_filter;
+  double filter_const_a, filter_const_b, filter_const_k;
+  uint64_t seed;                     /* new: counter-based RNG seed (reference is unseeded) */
+  int32_t rank, world_size;          /* new: photon / tile sharding across GPUs */
+} GiParams;
+
+typedef struct GiPhotonStats {       /* side effects of MapPhotons (photonmap.cpp:339-361) */
+  uint64_t global_stored, caustic_stored;
+  uint64_t global_emitted, caustic_emitted;
+  int32_t indirect_illum, caustic_illum, direct_photon_illum;   /* flags after the pass */
+  int32_t rounds;
+  double trace_ms, build_ms;
+} GiPhotonStats;
+
+typedef struct GiRenderStats {       /* the -v block of RenderImage (render.cpp:224-255) */
+  uint64_t screen_rays, shadow_rays, monte_rays, transmissive_samples, specular_samples,
+           indirect_samples, caustic_samples;
+  double render_ms;
+} GiRenderStats;
+
+typedef struct GiContext GiContext;
+
+/* library / device */
+int gi_abi_version(void);
+const char *gi_last_error(void);
+int gi_create(int device, GiContext **out);                       /* fails if no CUDA device */
+void gi_destroy(GiContext *ctx);
+void gi_default_params(GiParams *p);                              /* photonmap.cpp:41-106 */
+
+/* replaces the pointer-chasing R3Scene graph: flatten + upload + GPU BVH build */
+int gi_upload_scene(GiContext *ctx, const GiScene *scene);
+
+/* R3Scene::Intersects over a batch.  Host buffers; copies are part of the call. */
+int gi_intersect_batch(GiContext *ctx, const GiRay *rays, uint64_t n, GiHit *hits_out);
+/* same with device-resident buffers on `stream` (a cudaStream_t, NULL = default stream) */
+int gi_intersect_batch_device(GiContext *ctx, const GiRay *d_rays, uint64_t n, GiHit *d_hits, void *stream);
+
+/* photon maps: GLOBAL_PHOTONS / CAUSTIC_PHOTONS + R3Kdtree build (photonmap.cpp:364-377) */
+int gi_load_photons(GiContext *ctx, int map, const GiPhoton *photons, uint64_t n);
+int gi_load_photons_file(GiContext *ctx, int map, const char *path);
+int gi_dump_photons_file(GiContext *ctx, int map, const char *path);
+int gi_photon_count(GiContext *ctx, int map, uint64_t *n_out);
+int gi_get_photons(GiContext *ctx, int map, GiPhoton *out, uint64_t capacity);   /* map order */
+int gi_build_maps(GiContext *ctx, const GiParams *params);
+
+/* EstimateRadiance over a batch (photon_utils.cpp:72-162): kNN index sets + radiance.
+ * idx_out: n*k int32, ascending photon indices of the k nearest within r (ties broken by lower index),
+ * padded with -1; rgb_out: n*3 doubles (the estimate that the reference adds into `color`);
+ * count_out: n int32.  Any output pointer may be NULL. */
+int gi_gather_batch(GiContext *ctx, int map, const GiGatherQuery *queries, uint64_t n, int k, double r,
+                    int filter, const GiParams *params, int32_t *idx_out, int32_t *count_out, double *rgb_out);
+int gi_gather_batch_device(GiContext *ctx, int map, const GiGatherQuery *d_queries, uint64_t n, int k, double r,
+                           int filter, const GiParams *params, int32_t *d_idx, int32_t *d_count, double *d_rgb,
+                           void *stream);
+
+/* MapPhotons() (photonmap.cpp:260-436): emission + tracing + power scaling; maps stay on the device */
+int gi_trace_photons(GiContext *ctx, const GiParams *params, GiPhotonStats *stats);
+
+/* RenderImage(aa, W, H) (render.cpp:155-259).  rgb_out: W*H*3 bytes, row 0 = bottom row like R2Image. */
+int gi_render(GiContext *ctx, const GiParams *params, int width, int height, int aa, uint8_t *rgb_out,
+              GiRenderStats *stats);
+/* same, but returns the un-quantised, un-clamped supersampled buffer (W*2^aa x H*2^aa x 3 doubles,
+ * column-major like image_buffer[i][j]) for parity tests */
+int gi_render_float(GiContext *ctx, const GiParams *params, int width, int height, int aa, double *rgb_out,
+                    GiRenderStats *stats);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* GI_B200_H */
