@@ -1,0 +1,32 @@
+# Top-level build: libgi_b200.so (CUDA, sm_100a) + host tools.  `python -c "import __graft_entry__ as g; g.build()"`
+# drives the same targets.
+PKG    := global-illumination_b200
+NVCC   ?= /usr/local/cuda/bin/nvcc
+CXX    ?= g++
+ARCH   := -gencode arch=compute_100a,code=sm_100a
+# -fmad=false: parity with the reference's x86-64 build needs un-fused FP64 multiply/add
+NVFLAGS := -O3 -std=c++17 $(ARCH) -lineinfo -Xcompiler -fPIC -Iinclude -I$(PKG)/host -I$(PKG)/csrc
+CXXFLAGS := -O2 -std=c++17 -fPIC -Wall -Iinclude -I$(PKG)/host
+
+HOST_SRCS := $(PKG)/host/scene_loader.cpp $(PKG)/host/scene_io.cpp
+CU_SRCS   := $(wildcard $(PKG)/csrc/*.cu)
+CU_HDRS   := $(wildcard $(PKG)/csrc/*.cuh) $(wildcard $(PKG)/csrc/*.h) include/gi_b200.h $(PKG)/host/scene.h
+
+.PHONY: all lib tools oracle clean
+all: lib tools oracle
+
+tools: $(PKG)/bin/gi_scene_tool
+$(PKG)/bin/gi_scene_tool: $(PKG)/host/scene_tool.cpp $(HOST_SRCS) $(PKG)/host/scene.h include/gi_b200.h
+	@mkdir -p $(PKG)/bin
+	$(CXX) $(CXXFLAGS) $< $(HOST_SRCS) -o $@
+
+lib: $(PKG)/libgi_b200.so
+$(PKG)/libgi_b200.so: $(CU_SRCS) $(CU_HDRS) $(HOST_SRCS) $(PKG)/host/capi_host.cpp
+	$(NVCC) $(NVFLAGS) -shared $(CU_SRCS) $(HOST_SRCS) $(PKG)/host/capi_host.cpp -o $@ -lcudart
+
+oracle:
+	$(MAKE) -C oracle all
+
+clean:
+	rm -rf $(PKG)/bin $(PKG)/libgi_b200.so
+	$(MAKE) -C oracle clean

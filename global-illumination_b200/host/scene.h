@@ -15,6 +15,7 @@ struct SceneData {
   std::vector<GiElement> elements;
   std::vector<GiMaterial> materials;
   std::vector<GiPrim> prims;
+  std::vector<GiShape> shapes;
   std::vector<GiLight> lights;
   int n_shapes = 0;
   std::vector<uint8_t> shape_is_mesh;  // per reference shape id: came from a `mesh` command
@@ -32,6 +33,10 @@ struct SceneData {
 // Reads a Princeton .scn file (and the .off meshes / included .scn files it names).  On failure
 // returns false and sets `err` to the message the reference would print to stderr.
 bool load_scene(const std::string &path, bool real_material, SceneData &out, std::string &err);
+
+// Binary (GISC) serialisation of the flattened scene, see scene_io.cpp.
+bool save_scene_binary(const SceneData &s, const std::string &path);
+bool load_scene_binary(const std::string &path, SceneData &out, std::string &err);
 
 // Text dump in the format of `oracle/_ref/ref_harness dump_scene` (loader parity tests diff the two).
 bool dump_scene(const SceneData &s, const std::string &path);

@@ -486,14 +486,27 @@ void flatten(const Builder &b, int n, int parent_flat, SceneData &out) {
   g.parent = parent_flat;
   memcpy(g.m, node.m, sizeof(g.m));
   invert4(node.m, g.minv);
+  Box nb = node_bbox(b, n);
+  for (int i = 0; i < 3; i++) { g.bbox[i] = nb.lo[i]; g.bbox[3 + i] = nb.hi[i]; }
   int me = (int)out.nodes.size();
   out.nodes.push_back(g);
   for (const TmpElement &e : node.elements) {
     int eid = (int)out.elements.size();
-    out.elements.push_back(GiElement{me, e.material});
+    GiElement ge; memset(&ge, 0, sizeof(ge));
+    ge.node = me; ge.material = e.material;
+    Box eb;
+    for (const TmpShape &s : e.shapes) eb.add(shape_bbox(s));
+    for (int i = 0; i < 3; i++) { ge.bbox[i] = eb.lo[i]; ge.bbox[3 + i] = eb.hi[i]; }
+    out.elements.push_back(ge);
     for (const TmpShape &s : e.shapes) {
       int sid = out.n_shapes++;
       out.shape_is_mesh.push_back(s.type == -1 ? 1 : 0);
+      GiShape gs; memset(&gs, 0, sizeof(gs));
+      gs.is_mesh = s.type == -1 ? 1 : 0; gs.element = eid; gs.first_prim = (int)out.prims.size();
+      gs.n_prims = s.type == -1 ? (int)(s.tris.size() / 9) : 1;
+      Box sb = shape_bbox(s);
+      for (int i = 0; i < 3; i++) { gs.bbox[i] = sb.lo[i]; gs.bbox[3 + i] = sb.hi[i]; }
+      out.shapes.push_back(gs);
       if (s.type == -1) {
         for (size_t t = 0; t * 9 < s.tris.size(); t++) {
           GiPrim p; p.type = GI_SHAPE_TRIANGLE; p.element = eid; p.shape = sid; p.index_in_shape = (int)t;
@@ -517,7 +530,7 @@ GiScene SceneData::view() const {
   s.n_nodes = (int)nodes.size(); s.n_elements = (int)elements.size(); s.n_materials = (int)materials.size();
   s.n_prims = (int)prims.size(); s.n_lights = (int)lights.size(); s.n_shapes = n_shapes;
   s.nodes = nodes.data(); s.elements = elements.data(); s.materials = materials.data();
-  s.prims = prims.data(); s.lights = lights.data();
+  s.prims = prims.data(); s.shapes = shapes.data(); s.lights = lights.data();
   s.camera = camera;
   for (int i = 0; i < 3; i++) {
     s.ambient[i] = ambient[i]; s.background[i] = background[i];

@@ -45,12 +45,22 @@ typedef struct GiNode {              /* R3SceneNode: transformation to the paren
   int32_t reserved;
   double m[16];                      /* row-major 4x4, R3Affine::Matrix() */
   double minv[16];                   /* R3Affine::InverseMatrix() (R4Matrix::Invert, R4Matrix.cpp:252) */
+  double bbox[6];                    /* min(3) max(3) in the PARENT's coordinates (R3SceneNode::UpdateBBox,  */
+                                     /* R3SceneNode.cpp:539-560); min > max = empty                          */
 } GiNode;
 
 typedef struct GiElement {           /* R3SceneElement: (node, material) bucket of shapes */
   int32_t node;
   int32_t material;                  /* index into GiScene.materials */
+  double bbox[6];                    /* node-local union of the shapes' boxes (R3SceneElement.cpp:294-302) */
 } GiElement;
+
+typedef struct GiShape {             /* one R3Shape of the reference, in DFS visiting order */
+  int32_t is_mesh;                   /* 1: R3TriangleArray (brute-force loop, R3Isect.cpp:800-833) */
+  int32_t element;
+  int32_t first_prim, n_prims;       /* run inside GiScene.prims */
+  double bbox[6];                    /* node-local; a mesh's box covers ALL its vertices (R3TriangleArray.cpp:385-393) */
+} GiShape;
 
 enum GiShapeType {
   GI_SHAPE_TRIANGLE = 0,             /* d = v0 v1 v2                                (R3Triangle)      */
@@ -97,6 +107,7 @@ typedef struct GiScene {
   const GiElement *elements;
   const GiMaterial *materials;
   const GiPrim *prims;
+  const GiShape *shapes;
   const GiLight *lights;
   GiCamera camera;
   double ambient[3];
