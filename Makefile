@@ -5,15 +5,15 @@ NVCC   ?= /usr/local/cuda/bin/nvcc
 CXX    ?= g++
 ARCH   := -gencode arch=compute_100a,code=sm_100a
 # -fmad=false: parity with the reference's x86-64 build needs un-fused FP64 multiply/add
-NVFLAGS := -O3 -std=c++17 $(ARCH) -lineinfo -Xcompiler -fPIC -Iinclude -I$(PKG)/host -I$(PKG)/csrc
+NVFLAGS := -O3 -std=c++17 $(ARCH) -lineinfo -fmad=false -Xcompiler -fPIC,-ffp-contract=off -Iinclude -I$(PKG)/host -I$(PKG)/csrc
 CXXFLAGS := -O2 -std=c++17 -fPIC -Wall -Iinclude -I$(PKG)/host
 
 HOST_SRCS := $(PKG)/host/scene_loader.cpp $(PKG)/host/scene_io.cpp
 CU_SRCS   := $(wildcard $(PKG)/csrc/*.cu)
 CU_HDRS   := $(wildcard $(PKG)/csrc/*.cuh) $(wildcard $(PKG)/csrc/*.h) include/gi_b200.h $(PKG)/host/scene.h
 
-.PHONY: all lib tools oracle clean
-all: lib tools oracle
+.PHONY: all lib tools oracle host_sim clean
+all: lib tools oracle host_sim
 
 tools: $(PKG)/bin/gi_scene_tool
 $(PKG)/bin/gi_scene_tool: $(PKG)/host/scene_tool.cpp $(HOST_SRCS) $(PKG)/host/scene.h include/gi_b200.h
@@ -23,6 +23,10 @@ $(PKG)/bin/gi_scene_tool: $(PKG)/host/scene_tool.cpp $(HOST_SRCS) $(PKG)/host/sc
 lib: $(PKG)/libgi_b200.so
 $(PKG)/libgi_b200.so: $(CU_SRCS) $(CU_HDRS) $(HOST_SRCS) $(PKG)/host/capi_host.cpp
 	$(NVCC) $(NVFLAGS) -shared $(CU_SRCS) $(HOST_SRCS) $(PKG)/host/capi_host.cpp -o $@ -lcudart
+
+host_sim: tests/host_sim/libisect_sim.so
+tests/host_sim/libisect_sim.so: tests/host_sim/isect_sim.cpp $(CU_HDRS) $(HOST_SRCS)
+	$(CXX) -O2 -std=c++17 -fPIC -shared -ffp-contract=off -w -Iinclude -I$(PKG)/host -I$(PKG)/csrc $< $(HOST_SRCS) -o $@ -lpthread
 
 oracle:
 	$(MAKE) -C oracle all

@@ -1,0 +1,190 @@
+// csrc/capi_photon.cu -- photon-map entry points of include/gi_b200.h: load / dump / build / gather.
+//
+// gi_load_photons + gi_build_maps stand in for GLOBAL_PHOTONS / CAUSTIC_PHOTONS and the two
+// `new R3Kdtree<Photon*>` of MapPhotons (src/photonmap.cpp:364-377); gi_gather_batch stands in for a loop of
+// EstimateRadiance calls (src/utils/photon_utils.cpp:72-162).  The photon file format ("GIPM": u32 magic,
+// u32 version, u64 n, n x 32-byte Photon) is new -- the reference never writes its maps -- and is shared with
+// oracle/ref_harness so that both sides can be fed the same map.
+#include <cuda_runtime.h>
+#include <cmath>
+#include <cstdio>
+#include <cstring>
+#include <vector>
+#include "context.h"
+#include "gather.h"
+#include "gi_math.cuh"
+#include "kdtree_build.h"
+
+namespace gi {
+
+static const uint32_t PMAP_MAGIC = 0x4d504947u;   // "GIPM"
+
+void free_map(PhotonMapStore &m) {
+  cudaFree((void *)m.dev.px); cudaFree((void *)m.dev.py); cudaFree((void *)m.dev.pz);
+  cudaFree((void *)m.dev.node); cudaFree((void *)m.dev.shade); cudaFree((void *)m.dev.orig);
+  cudaFree(m.raw);
+  m = PhotonMapStore();
+}
+
+// BuildDirectionLookupTable (src/utils/photon_utils.cpp:253-272), built on the host with the same libm calls and
+// kept in HBM (1.5 MB, L2-resident): entry [phi * 256 + theta] = normalised (x, y, z)
+static double *g_lut[64] = {nullptr};
+static const double *direction_lut(GiContext *ctx) {
+  if (ctx->device < 64 && g_lut[ctx->device]) return g_lut[ctx->device];
+  std::vector<double> h(65536 * 3);
+  const double PI = 3.14159265358979323846, TWO_PI = 6.28318530717958647692;   // RN_PI / RN_TWO_PI (RNScalar.h)
+  for (int phi = 0; phi < 256; phi++)
+    for (int theta = 0; theta < 256; theta++) {
+      const double tp = (phi * TWO_PI / 255.0) - PI, tt = (theta * PI / 255.0);
+      D3 v = normalized(mk3(sin(tt) * cos(tp), sin(tt) * sin(tp), cos(tt)));
+      double *o = &h[3 * (size_t)(256 * phi + theta)];
+      o[0] = v.x; o[1] = v.y; o[2] = v.z;
+    }
+  double *d = nullptr;
+  if (!cuda_ok(cudaMalloc(&d, h.size() * 8), "cudaMalloc(lut)")) return nullptr;
+  if (!cuda_ok(cudaMemcpy(d, h.data(), h.size() * 8, cudaMemcpyHostToDevice), "cudaMemcpy(lut)")) { cudaFree(d); return nullptr; }
+  if (ctx->device < 64) g_lut[ctx->device] = d;
+  return d;
+}
+
+static int pow2ceil(int v) { int p = 1; while (p < v) p <<= 1; return p; }
+
+}  // namespace gi
+
+using namespace gi;
+
+extern "C" {
+
+int gi_load_photons(GiContext *ctx, int map, const GiPhoton *photons, uint64_t n) {
+  if (!ctx || map < 0 || map > 1) { set_error("gi_load_photons: bad argument"); return 1; }
+  if (n > 0 && !photons) { set_error("gi_load_photons: null photon buffer"); return 1; }
+  if (n >= ((uint64_t)1 << 31)) { set_error("gi_load_photons: at most 2^31 - 1 photons per map"); return 1; }
+  GI_CUDA(cudaSetDevice(ctx->device));
+  PhotonMapStore &m = ctx->maps[map];
+  free_map(m);
+  m.dev.n = n;
+  if (n == 0) return 0;
+  GI_CUDA(cudaMalloc(&m.raw, sizeof(GiPhoton) * n));
+  GI_CUDA(cudaMemcpyAsync(m.raw, photons, sizeof(GiPhoton) * n, cudaMemcpyHostToDevice, ctx->stream));
+  GI_CUDA(cudaStreamSynchronize(ctx->stream));
+  return 0;
+}
+
+// device-resident variant used by the multi-GPU path (photons all-gathered by NCCL into d_photons)
+int gi_load_photons_device(GiContext *ctx, int map, const GiPhoton *d_photons, uint64_t n) {
+  if (!ctx || map < 0 || map > 1) { set_error("gi_load_photons_device: bad argument"); return 1; }
+  if (n >= ((uint64_t)1 << 31)) { set_error("gi_load_photons_device: at most 2^31 - 1 photons per map"); return 1; }
+  GI_CUDA(cudaSetDevice(ctx->device));
+  PhotonMapStore &m = ctx->maps[map];
+  free_map(m);
+  m.dev.n = n;
+  if (n == 0) return 0;
+  GI_CUDA(cudaMalloc(&m.raw, sizeof(GiPhoton) * n));
+  GI_CUDA(cudaMemcpyAsync(m.raw, d_photons, sizeof(GiPhoton) * n, cudaMemcpyDeviceToDevice, ctx->stream));
+  GI_CUDA(cudaStreamSynchronize(ctx->stream));
+  return 0;
+}
+
+int gi_photon_count(GiContext *ctx, int map, uint64_t *n_out) {
+  if (!ctx || map < 0 || map > 1 || !n_out) { set_error("gi_photon_count: bad argument"); return 1; }
+  *n_out = ctx->maps[map].dev.n;
+  return 0;
+}
+
+int gi_get_photons(GiContext *ctx, int map, GiPhoton *out, uint64_t capacity) {
+  if (!ctx || map < 0 || map > 1) { set_error("gi_get_photons: bad argument"); return 1; }
+  PhotonMapStore &m = ctx->maps[map];
+  if (capacity < m.dev.n) { set_error("gi_get_photons: buffer too small"); return 1; }
+  if (m.dev.n == 0) return 0;
+  GI_CUDA(cudaSetDevice(ctx->device));
+  GI_CUDA(cudaMemcpy(out, m.raw, sizeof(GiPhoton) * m.dev.n, cudaMemcpyDeviceToHost));
+  return 0;
+}
+
+int gi_load_photons_file(GiContext *ctx, int map, const char *path) {
+  FILE *f = path ? fopen(path, "rb") : nullptr;
+  if (!f) { set_error(std::string("Unable to open photon file ") + (path ? path : "(null)")); return 1; }
+  uint32_t hdr[2]; uint64_t n = 0;
+  if (fread(hdr, 4, 2, f) != 2 || hdr[0] != PMAP_MAGIC || fread(&n, 8, 1, f) != 1) {
+    fclose(f); set_error(std::string("Bad photon file ") + path); return 1;
+  }
+  std::vector<GiPhoton> ph(n);
+  if (n && fread(ph.data(), sizeof(GiPhoton), n, f) != n) { fclose(f); set_error(std::string("Truncated photon file ") + path); return 1; }
+  fclose(f);
+  return gi_load_photons(ctx, map, ph.data(), n);
+}
+
+int gi_dump_photons_file(GiContext *ctx, int map, const char *path) {
+  if (!ctx || map < 0 || map > 1 || !path) { set_error("gi_dump_photons_file: bad argument"); return 1; }
+  const uint64_t n = ctx->maps[map].dev.n;
+  std::vector<GiPhoton> ph(n);
+  if (gi_get_photons(ctx, map, ph.data(), n)) return 1;
+  FILE *f = fopen(path, "wb");
+  if (!f) { set_error(std::string("Unable to open photon file ") + path); return 1; }
+  uint32_t hdr[2] = {PMAP_MAGIC, 1};
+  bool ok = fwrite(hdr, 4, 2, f) == 2 && fwrite(&n, 8, 1, f) == 1 && (n == 0 || fwrite(ph.data(), sizeof(GiPhoton), n, f) == n);
+  fclose(f);
+  if (!ok) { set_error(std::string("Unable to write photon file ") + path); return 1; }
+  return 0;
+}
+
+int gi_build_maps(GiContext *ctx, const GiParams *params) {
+  (void)params;
+  if (!ctx) { set_error("gi_build_maps: null context"); return 1; }
+  GI_CUDA(cudaSetDevice(ctx->device));
+  for (int k = 0; k < 2; k++) {
+    PhotonMapStore &m = ctx->maps[k];
+    if (m.built || m.dev.n == 0) continue;
+    GI_CUDA(build_photon_map(ctx, m, m.dev.n));
+  }
+  return 0;
+}
+
+int gi_gather_batch_device(GiContext *ctx, int map, const GiGatherQuery *d_queries, uint64_t n, int k, double r,
+                           int filter, const GiParams *params, int32_t *d_idx, int32_t *d_count, double *d_rgb,
+                           void *stream) {
+  if (!ctx || map < 0 || map > 1) { set_error("gi_gather_batch: bad argument"); return 1; }
+  if (k < 1 || k > GI_MAX_K) { set_error("gi_gather_batch: estimate size must be in [1, 512]"); return 1; }
+  if (filter < 0 || filter > 2) { set_error("gi_gather_batch: unknown filter"); return 1; }
+  PhotonMapStore &m = ctx->maps[map];
+  if (m.dev.n > 0 && !m.built) { set_error("gi_gather_batch: photon map not built (call gi_build_maps)"); return 1; }
+  if (n == 0) return 0;
+  GI_CUDA(cudaSetDevice(ctx->device));
+  const double *lut = direction_lut(ctx);
+  if (!lut) return 1;
+  GatherArgs ga;
+  ga.k = k; ga.cap = pow2ceil(2 * k) < 256 ? 256 : pow2ceil(2 * k); ga.filter = filter; ga.r2 = r * r;
+  ga.fa = params ? params->filter_const_a : 0.918; ga.fb = params ? params->filter_const_b : 1.953;
+  ga.fk = params ? params->filter_const_k : 1.0;
+  cudaStream_t st = stream ? (cudaStream_t)stream : ctx->stream;
+  GI_CUDA(launch_gather(ctx, m.dev, lut, d_queries, n, ga, d_idx, d_count, d_rgb, st));
+  return 0;
+}
+
+int gi_gather_batch(GiContext *ctx, int map, const GiGatherQuery *queries, uint64_t n, int k, double r, int filter,
+                    const GiParams *params, int32_t *idx_out, int32_t *count_out, double *rgb_out) {
+  if (!ctx) { set_error("gi_gather_batch: null context"); return 1; }
+  if (n == 0) return 0;
+  if (!queries) { set_error("gi_gather_batch: null query buffer"); return 1; }
+  if (k < 1 || k > GI_MAX_K) { set_error("gi_gather_batch: estimate size must be in [1, 512]"); return 1; }
+  GI_CUDA(cudaSetDevice(ctx->device));
+  GiGatherQuery *d_q = nullptr; int32_t *d_idx = nullptr, *d_cnt = nullptr; double *d_rgb = nullptr;
+  int rc = 1;
+  do {
+    if (!cuda_ok(cudaMalloc(&d_q, sizeof(GiGatherQuery) * n), "cudaMalloc(queries)")) break;
+    if (idx_out && !cuda_ok(cudaMalloc(&d_idx, sizeof(int32_t) * n * k), "cudaMalloc(idx)")) break;
+    if (count_out && !cuda_ok(cudaMalloc(&d_cnt, sizeof(int32_t) * n), "cudaMalloc(count)")) break;
+    if (rgb_out && !cuda_ok(cudaMalloc(&d_rgb, sizeof(double) * 3 * n), "cudaMalloc(rgb)")) break;
+    if (!cuda_ok(cudaMemcpyAsync(d_q, queries, sizeof(GiGatherQuery) * n, cudaMemcpyHostToDevice, ctx->stream), "H2D queries")) break;
+    if (gi_gather_batch_device(ctx, map, d_q, n, k, r, filter, params, d_idx, d_cnt, d_rgb, ctx->stream)) break;
+    if (idx_out && !cuda_ok(cudaMemcpyAsync(idx_out, d_idx, sizeof(int32_t) * n * k, cudaMemcpyDeviceToHost, ctx->stream), "D2H idx")) break;
+    if (count_out && !cuda_ok(cudaMemcpyAsync(count_out, d_cnt, sizeof(int32_t) * n, cudaMemcpyDeviceToHost, ctx->stream), "D2H count")) break;
+    if (rgb_out && !cuda_ok(cudaMemcpyAsync(rgb_out, d_rgb, sizeof(double) * 3 * n, cudaMemcpyDeviceToHost, ctx->stream), "D2H rgb")) break;
+    if (!cuda_ok(cudaStreamSynchronize(ctx->stream), "gather sync")) break;
+    rc = 0;
+  } while (0);
+  cudaFree(d_q); cudaFree(d_idx); cudaFree(d_cnt); cudaFree(d_rgb);
+  return rc;
+}
+
+}  // extern "C"

@@ -1,0 +1,176 @@
+// csrc/capi_scene.cu -- context, scene upload and the batched closest-hit entry points of include/gi_b200.h.
+//
+// gi_upload_scene stands in for building the R3Scene graph the reference traverses (R3Scene::ReadFile leaves
+// the graph in host memory, R3Scene.cpp:514-587); gi_intersect_batch stands in for a loop of
+// R3Scene::Intersects calls (R3Scene.cpp:471-479), e.g. the pixel loop of render.cpp:90-125.
+#include <cuda_runtime.h>
+#include <cstdio>
+#include <cstring>
+#include <mutex>
+#include "bvh_build.h"
+#include "context.h"
+#include "isect.cuh"
+#include "scene_prep.h"
+
+namespace gi {
+
+static thread_local std::string g_error;
+void set_error(const std::string &msg) { g_error = msg; }
+bool cuda_ok(cudaError_t e, const char *what) {
+  if (e == cudaSuccess) return true;
+  set_error(std::string("CUDA error: ") + cudaGetErrorString(e) + " in " + what);
+  return false;
+}
+
+void free_scene(GiContext *ctx) {
+  for (void *p : ctx->scene_allocs) cudaFree(p);
+  ctx->scene_allocs.clear();
+  ctx->has_scene = false;
+  memset(&ctx->scene, 0, sizeof(ctx->scene));
+}
+
+template <class T> static bool upload(GiContext *ctx, const std::vector<T> &h, const T **d) {
+  *d = nullptr;
+  size_t bytes = sizeof(T) * (h.empty() ? 1 : h.size());
+  void *p = nullptr;
+  if (!cuda_ok(cudaMalloc(&p, bytes), "cudaMalloc(scene)")) return false;
+  ctx->scene_allocs.push_back(p);
+  if (!h.empty() && !cuda_ok(cudaMemcpyAsync(p, h.data(), sizeof(T) * h.size(), cudaMemcpyHostToDevice, ctx->stream),
+                             "cudaMemcpy(scene)"))
+    return false;
+  *d = (const T *)p;
+  return true;
+}
+
+// one thread per ray; rays and hits are the AoS records of the C ABI (48 B in, 72 B out)
+__global__ void __launch_bounds__(128) intersect_kernel(DevScene sc, const GiRay *__restrict__ rays, uint64_t n,
+                                                        GiHit *__restrict__ hits) {
+  for (uint64_t i = (uint64_t)blockIdx.x * blockDim.x + threadIdx.x; i < n; i += (uint64_t)gridDim.x * blockDim.x) {
+    const double2 *rp = (const double2 *)(rays + i);        // 48-byte records are 16-byte aligned
+    const double2 r0 = rp[0], r1 = rp[1], r2 = rp[2];
+    RayD ray; ray.o = mk3(r0.x, r0.y, r1.x); ray.d = mk3(r1.y, r2.x, r2.y);
+    HitRec h;
+    closest_hit(sc, ray, h);
+    GiHit g;
+    g.hit = h.prim >= 0 ? 1 : 0; g.shape = h.shape; g.prim = h.prim; g.element = h.element; g.t = h.t;
+    g.p[0] = h.p.x; g.p[1] = h.p.y; g.p[2] = h.p.z; g.n[0] = h.n.x; g.n[1] = h.n.y; g.n[2] = h.n.z;
+    hits[i] = g;
+  }
+}
+
+}  // namespace gi
+
+using namespace gi;
+
+extern "C" {
+
+int gi_abi_version(void) { return GI_ABI_VERSION; }
+const char *gi_last_error(void) { return g_error.c_str(); }
+
+int gi_create(int device, GiContext **out) {
+  if (!out) { set_error("gi_create: null output pointer"); return 1; }
+  *out = nullptr;
+  int count = 0;
+  cudaError_t e = cudaGetDeviceCount(&count);
+  if (e != cudaSuccess || count <= 0) {
+    set_error(std::string("gi_create: no CUDA device (") + cudaGetErrorString(e) + "); this library has no CPU path");
+    return 1;
+  }
+  if (device < 0 || device >= count) { set_error("gi_create: device index out of range"); return 1; }
+  GI_CUDA(cudaSetDevice(device));
+  cudaDeviceProp prop;
+  GI_CUDA(cudaGetDeviceProperties(&prop, device));
+  if (prop.major < 10) { set_error("gi_create: this library is built for sm_100a (B200) only"); return 1; }
+  GiContext *ctx = new GiContext();
+  ctx->device = device; ctx->sm_count = prop.multiProcessorCount;
+  if (!cuda_ok(cudaStreamCreateWithFlags(&ctx->stream, cudaStreamNonBlocking), "cudaStreamCreate")) { delete ctx; return 1; }
+  *out = ctx;
+  return 0;
+}
+
+void gi_destroy(GiContext *ctx) {
+  if (!ctx) return;
+  cudaSetDevice(ctx->device);
+  free_scene(ctx);
+  free_map(ctx->maps[0]); free_map(ctx->maps[1]);
+  if (ctx->stream) cudaStreamDestroy(ctx->stream);
+  delete ctx;
+}
+
+int gi_upload_scene(GiContext *ctx, const GiScene *scene) {
+  if (!ctx || !scene) { set_error("gi_upload_scene: null argument"); return 1; }
+  GI_CUDA(cudaSetDevice(ctx->device));
+  free_scene(ctx);
+  PreparedScene ps; std::string err;
+  if (!prepare_scene(*scene, ps, err)) { set_error("gi_upload_scene: " + err); return 1; }
+  DevScene d; memset(&d, 0, sizeof(d));
+  const float *d_boxes = nullptr;
+  bool ok = upload(ctx, ps.nodes, &d.nodes) && upload(ctx, ps.elements, &d.elements) && upload(ctx, ps.shapes, &d.shapes) &&
+            upload(ctx, ps.materials, &d.materials) && upload(ctx, ps.prim_a, &d.prim_a) &&
+            upload(ctx, ps.prim_b, &d.prim_b) && upload(ctx, ps.prim_meta, &d.prim_meta) &&
+            upload(ctx, ps.prim_boxes, &d_boxes);
+  if (!ok) { free_scene(ctx); return 1; }
+  d.n_prims = scene->n_prims; d.n_shapes = scene->n_shapes; d.n_elements = scene->n_elements;
+  d.n_nodes = scene->n_nodes; d.n_materials = scene->n_materials; d.has_mesh = ps.has_mesh; d.abs_max = ps.abs_max;
+  d.n_bvh_nodes = scene->n_prims > 1 ? scene->n_prims - 1 : 1;
+  float4 *bvh = nullptr;
+  if (!cuda_ok(cudaMalloc(&bvh, sizeof(float4) * 4 * (size_t)d.n_bvh_nodes), "cudaMalloc(bvh)")) { free_scene(ctx); return 1; }
+  ctx->scene_allocs.push_back(bvh);
+  if (!cuda_ok(cudaMemsetAsync(bvh, 0, sizeof(float4) * 4 * (size_t)d.n_bvh_nodes, ctx->stream), "memset(bvh)") ||
+      !cuda_ok(build_bvh(d_boxes, scene->n_prims, ps.lo, ps.hi, bvh, ctx->stream), "build_bvh") ||
+      !cuda_ok(cudaStreamSynchronize(ctx->stream), "upload sync")) { free_scene(ctx); return 1; }
+  ctx->launches += scene->n_prims > 1 ? 6 : 1;
+  d.bvh = bvh;
+  ctx->scene = d;
+  ctx->lights.assign(scene->lights, scene->lights + scene->n_lights);
+  ctx->materials.assign(scene->materials, scene->materials + scene->n_materials);
+  ctx->camera = scene->camera;
+  for (int k = 0; k < 3; k++) {
+    ctx->ambient[k] = scene->ambient[k]; ctx->background[k] = scene->background[k];
+    ctx->bbox_min[k] = scene->bbox_min[k]; ctx->bbox_max[k] = scene->bbox_max[k]; ctx->centroid[k] = scene->centroid[k];
+  }
+  ctx->radius = scene->radius;
+  ctx->has_scene = true;
+  return 0;
+}
+
+int gi_intersect_batch_device(GiContext *ctx, const GiRay *d_rays, uint64_t n, GiHit *d_hits, void *stream) {
+  if (!ctx || !ctx->has_scene) { set_error("gi_intersect_batch: no scene uploaded"); return 1; }
+  if (n == 0) return 0;
+  GI_CUDA(cudaSetDevice(ctx->device));
+  cudaStream_t st = stream ? (cudaStream_t)stream : ctx->stream;
+  const int block = 128;
+  uint64_t want = (n + block - 1) / block;
+  uint64_t cap = (uint64_t)ctx->sm_count * 64;         // grid-stride beyond 64 CTAs per SM
+  int grid = (int)(want < cap ? want : cap);
+  intersect_kernel<<<grid, block, 0, st>>>(ctx->scene, d_rays, n, d_hits);
+  ctx->launches++;
+  GI_CUDA(cudaGetLastError());
+  return 0;
+}
+
+int gi_intersect_batch(GiContext *ctx, const GiRay *rays, uint64_t n, GiHit *hits_out) {
+  if (!ctx || !ctx->has_scene) { set_error("gi_intersect_batch: no scene uploaded"); return 1; }
+  if (n == 0) return 0;
+  if (!rays || !hits_out) { set_error("gi_intersect_batch: null buffer"); return 1; }
+  GI_CUDA(cudaSetDevice(ctx->device));
+  GiRay *d_rays = nullptr; GiHit *d_hits = nullptr;
+  GI_CUDA(cudaMalloc(&d_rays, sizeof(GiRay) * n));
+  if (!cuda_ok(cudaMalloc(&d_hits, sizeof(GiHit) * n), "cudaMalloc(hits)")) { cudaFree(d_rays); return 1; }
+  int rc = 1;
+  if (cuda_ok(cudaMemcpyAsync(d_rays, rays, sizeof(GiRay) * n, cudaMemcpyHostToDevice, ctx->stream), "H2D rays") &&
+      gi_intersect_batch_device(ctx, d_rays, n, d_hits, ctx->stream) == 0 &&
+      cuda_ok(cudaMemcpyAsync(hits_out, d_hits, sizeof(GiHit) * n, cudaMemcpyDeviceToHost, ctx->stream), "D2H hits") &&
+      cuda_ok(cudaStreamSynchronize(ctx->stream), "intersect sync"))
+    rc = 0;
+  cudaFree(d_rays); cudaFree(d_hits);
+  return rc;
+}
+
+int gi_launch_count(GiContext *ctx, uint64_t *out) {
+  if (!ctx || !out) { set_error("gi_launch_count: null argument"); return 1; }
+  *out = ctx->launches;
+  return 0;
+}
+
+}  // extern "C"

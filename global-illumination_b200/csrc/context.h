@@ -1,0 +1,36 @@
+// csrc/context.h -- the opaque GiContext behind include/gi_b200.h: one CUDA device, one stream, and every
+// device allocation of the uploaded scene and photon maps.  The library owns all device memory; callers own
+// every host buffer they pass in (see the ownership rules in gi_b200.h).
+#pragma once
+#include <cuda_runtime.h>
+#include <string>
+#include <vector>
+#include "gi_b200.h"
+#include "scene_dev.h"
+#include "photon_dev.h"
+
+struct GiContext {
+  int device = 0;
+  cudaStream_t stream = nullptr;
+  int sm_count = 0;
+  bool has_scene = false;
+  gi::DevScene scene{};                       // device pointers, passed to kernels by value
+  std::vector<void *> scene_allocs;
+  // host copy of the flattened scene (lights, camera, materials are needed by the render stages)
+  std::vector<GiLight> lights;
+  std::vector<GiMaterial> materials;
+  GiCamera camera{};
+  double ambient[3] = {0, 0, 0}, background[3] = {0, 0, 0}, bbox_min[3] = {0, 0, 0}, bbox_max[3] = {0, 0, 0};
+  double centroid[3] = {0, 0, 0}, radius = 0;
+  gi::PhotonMapStore maps[2];                 // GI_MAP_GLOBAL, GI_MAP_CAUSTIC
+  uint64_t launches = 0;                      // kernels launched by this context (bench.py: gpu_launches)
+};
+
+namespace gi {
+void set_error(const std::string &msg);
+bool cuda_ok(cudaError_t e, const char *what);
+void free_scene(GiContext *ctx);
+void free_map(PhotonMapStore &m);
+}  // namespace gi
+
+#define GI_CUDA(call) do { if (!gi::cuda_ok((call), #call)) return 1; } while (0)

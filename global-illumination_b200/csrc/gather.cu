@@ -1,0 +1,300 @@
+// csrc/gather.cu -- photon k-nearest-neighbour gather + radiance estimate (K6), the bandwidth-bound hot kernel.
+//
+// Replaces EstimateRadiance (src/utils/photon_utils.cpp:72-162) and the search it calls,
+// R3Kdtree::FindClosestQuick (src/R3Shapes/R3Kdtree.cpp:688-848): a recursive descent with a std:: max-heap in
+// a std::vector per query.  Semantics kept: the k photons nearest to the query point with d^2 <= r^2 (both
+// inclusive, :756-757), distances in FP64 with the reference's formula (R3SquaredDistance, R3Dist.cpp:41-46);
+// estimate radius^2 = r^2 if fewer than k were found, else max(d^2, 1e-6) (photon_utils.cpp:85-96); side test,
+// Phong weight, disk / cone / Gauss filters as photon_utils.cpp:109-158.  Documented tightening: exact d^2 ties at
+// the k-th place go to the photon with the lower index (the reference's choice depends on its randomised tree).
+//
+// Design: one warp per query.
+//   * Upper levels of the left-balanced tree are walked by the whole warp (uniform control flow, near child first,
+//     far child pushed with its plane distance; float32 split planes are widened by one ulp so pruning is
+//     conservative w.r.t. the FP64 coordinates).
+//   * The bottom GI_TILE_LEVELS levels below a node are a "tile": in heap layout they are <= 6 contiguous runs, read
+//     by the 32 lanes in two coalesced rounds of FP64 distance tests.
+//   * Candidates (d^2, slot, photon index) are appended to a per-warp buffer in shared memory with ballot/popc.
+//     When the buffer runs full it is cut back with a 256-bin histogram of d^2 / bound (photons on a surface are
+//     uniform in d^2, so the boundary bin holds ~cap/256 candidates): everything up to the bin that contains the
+//     k-th candidate is kept and the search bound shrinks to the largest kept d^2.  Only the last cut is exact.
+#include <cuda_runtime.h>
+#include <math.h>
+#include <stdint.h>
+#include "context.h"
+#include "gather.h"
+
+namespace gi {
+
+#define FULL 0xffffffffu
+
+struct WarpBuf {
+  double *d2; uint32_t *slot; uint32_t *orig; uint32_t *hist; int cap;
+};
+
+__device__ __forceinline__ bool lex_less(double da, uint32_t oa, double db, uint32_t ob) {
+  return da < db || (da == db && oa < ob);
+}
+
+// warp-cooperative bitonic sort of buf[0..cap) ascending by (d2, orig); cap is a power of two
+__device__ void bitonic_sort(WarpBuf &b, int lane) {
+  for (int k2 = 2; k2 <= b.cap; k2 <<= 1)
+    for (int j = k2 >> 1; j > 0; j >>= 1) {
+      for (int i = lane; i < b.cap; i += 32) {
+        const int x = i ^ j;
+        if (x > i) {
+          const double di = b.d2[i], dx = b.d2[x];
+          const uint32_t oi = b.orig[i], ox = b.orig[x];
+          const bool up = (i & k2) == 0;
+          const bool sw = up ? lex_less(dx, ox, di, oi) : lex_less(di, oi, dx, ox);
+          if (sw) {
+            b.d2[i] = dx; b.d2[x] = di; b.orig[i] = ox; b.orig[x] = oi;
+            const uint32_t s = b.slot[i]; b.slot[i] = b.slot[x]; b.slot[x] = s;
+          }
+        }
+      }
+      __syncwarp();
+    }
+}
+
+// exact: keep the k smallest by (d2, orig); once k are held the bound becomes the largest kept d2
+__device__ void exact_select(WarpBuf &b, int &count, double &bound, int k, int lane) {
+  if (count < k) return;
+  if (count - k <= 16) {
+    while (count > k) {                                   // drop the lexicographic maximum
+      double md = -1.0; uint32_t mo = 0; int mi = -1;
+      for (int i = lane; i < count; i += 32) {
+        const double d = b.d2[i]; const uint32_t o = b.orig[i];
+        if (mi < 0 || lex_less(md, mo, d, o)) { md = d; mo = o; mi = i; }
+      }
+      for (int s = 16; s > 0; s >>= 1) {
+        const double od = __shfl_xor_sync(FULL, md, s); const uint32_t oo = __shfl_xor_sync(FULL, mo, s);
+        const int oi = __shfl_xor_sync(FULL, mi, s);
+        if (oi >= 0 && (mi < 0 || lex_less(md, mo, od, oo))) { md = od; mo = oo; mi = oi; }
+      }
+      if (lane == 0) { b.d2[mi] = b.d2[count - 1]; b.slot[mi] = b.slot[count - 1]; b.orig[mi] = b.orig[count - 1]; }
+      count--;
+      __syncwarp();
+    }
+  } else {
+    for (int i = count + lane; i < b.cap; i += 32) { b.d2[i] = INFINITY; b.orig[i] = 0xffffffffu; b.slot[i] = 0; }
+    __syncwarp();
+    bitonic_sort(b, lane);
+    count = k;
+  }
+  double mx = 0.0;
+  for (int i = lane; i < count; i += 32) mx = fmax(mx, b.d2[i]);
+  for (int s = 16; s > 0; s >>= 1) mx = fmax(mx, __shfl_xor_sync(FULL, mx, s));
+  bound = fmin(bound, mx);
+}
+
+// approximate cut (see file header); falls back to exact_select when the histogram cannot make enough room
+__device__ void compact(WarpBuf &b, int &count, double &bound, int k, int lane) {
+  if (!(bound > 0.0)) { exact_select(b, count, bound, k, lane); return; }
+  for (int i = lane; i < 256; i += 32) b.hist[i] = 0;
+  __syncwarp();
+  const double scale = 256.0 / bound;
+  for (int i = lane; i < count; i += 32) {
+    int bin = (int)(b.d2[i] * scale); bin = bin > 255 ? 255 : bin;
+    atomicAdd(&b.hist[bin], 1u);
+  }
+  __syncwarp();
+  uint32_t h[8]; uint32_t s = 0;
+  for (int j = 0; j < 8; j++) { h[j] = b.hist[lane * 8 + j]; s += h[j]; }
+  uint32_t incl = s;
+  for (int o = 1; o < 32; o <<= 1) { const uint32_t v = __shfl_up_sync(FULL, incl, o); if (lane >= o) incl += v; }
+  const uint32_t excl = incl - s;
+  const unsigned crossing = __ballot_sync(FULL, incl >= (uint32_t)k);
+  const int owner = __ffs(crossing) - 1;                  // count > k  =>  some lane crosses
+  int B = 255;
+  if (lane == owner) { uint32_t c = excl; for (int j = 0; j < 8; j++) { c += h[j]; if (c >= (uint32_t)k) { B = lane * 8 + j; break; } } }
+  B = __shfl_sync(FULL, B, owner);
+  int newcount = 0; double mx = 0.0;
+  for (int base = 0; base < count; base += 32) {
+    const int i = base + lane;
+    double d = 0.0; uint32_t sl = 0, og = 0; bool keep = false;
+    if (i < count) {
+      d = b.d2[i]; sl = b.slot[i]; og = b.orig[i];
+      int bin = (int)(d * scale); bin = bin > 255 ? 255 : bin;
+      keep = bin <= B;
+    }
+    const unsigned m = __ballot_sync(FULL, keep);
+    const int pos = newcount + __popc(m & ((1u << lane) - 1u));
+    __syncwarp();
+    if (keep) { b.d2[pos] = d; b.slot[pos] = sl; b.orig[pos] = og; mx = fmax(mx, d); }
+    newcount += __popc(m);
+    __syncwarp();
+  }
+  for (int o = 16; o > 0; o >>= 1) mx = fmax(mx, __shfl_xor_sync(FULL, mx, o));
+  count = newcount; bound = fmin(bound, mx);
+  if (count > b.cap - 64) exact_select(b, count, bound, k, lane);
+}
+
+__device__ __forceinline__ void append(WarpBuf &b, const PhotonMapDev &m, int &count, double &bound, int k, int lane,
+                                       bool pred, double d2, uint32_t slot) {
+  const unsigned mask = __ballot_sync(FULL, pred);
+  if (mask == 0) return;
+  const int pos = count + __popc(mask & ((1u << lane) - 1u));
+  if (pred) { b.d2[pos] = d2; b.slot[pos] = slot; b.orig[pos] = m.orig[slot]; }
+  count += __popc(mask);
+  __syncwarp();
+  if (count > b.cap - 32) compact(b, count, bound, k, lane);
+}
+
+__device__ __forceinline__ double dist2(const PhotonMapDev &m, uint64_t slot, double qx, double qy, double qz) {
+  const double dx = qx - m.px[slot], dy = qy - m.py[slot], dz = qz - m.pz[slot];   // v = query - photon; v.Dot(v)
+  return (dx * dx) + (dy * dy) + (dz * dz);
+}
+
+__global__ void __launch_bounds__(GI_GATHER_WARPS * 32)
+gather_kernel(PhotonMapDev m, const double *__restrict__ lut, const GiGatherQuery *__restrict__ queries, uint64_t nq,
+              GatherArgs ga, int32_t *idx_out, int32_t *count_out, double *rgb_out) {
+  extern __shared__ double smem[];
+  const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+  WarpBuf b; b.cap = ga.cap;
+  {
+    char *base = (char *)smem + (size_t)warp * ((size_t)ga.cap * 16 + 1024);
+    b.d2 = (double *)base; b.slot = (uint32_t *)(base + (size_t)ga.cap * 8);
+    b.orig = b.slot + ga.cap; b.hist = b.orig + ga.cap;
+  }
+  const int k = ga.k;
+  const uint64_t n = m.n;
+  const int tile_level = m.levels - GI_TILE_LEVELS;        // nodes at this level or deeper are handled as tiles
+  const uint64_t warps_total = (uint64_t)gridDim.x * GI_GATHER_WARPS;
+  for (uint64_t qi = (uint64_t)blockIdx.x * GI_GATHER_WARPS + warp; qi < nq; qi += warps_total) {
+    // ---- query record: 17 doubles, one per lane, broadcast by shuffle
+    const double *qp = (const double *)(queries + qi);
+    const double mine = lane < 17 ? qp[lane] : 0.0;
+    const double qx = __shfl_sync(FULL, mine, 0), qy = __shfl_sync(FULL, mine, 1), qz = __shfl_sync(FULL, mine, 2);
+    int count = 0;
+    double bound = ga.r2;
+    if (n > 0) {
+      uint32_t st_node[40]; double st_d[40]; int sp = 0;
+      st_node[0] = 0; st_d[0] = 0.0; sp = 1;
+      while (sp > 0) {
+        --sp;
+        uint64_t s = st_node[sp];
+        if (st_d[sp] > bound) continue;
+        while (true) {
+          const int lvl = 63 - __clzll((long long)(s + 1));
+          if (lvl >= tile_level) {
+            // ---- tile: subtree of s, relative depth j occupies slots (s << j) + e, e in [2^j - 1, 2^(j+1) - 1)
+            const int h = m.levels - lvl;
+            const int total = (1 << h) - 1;
+            for (int e = lane; e < total + lane; e += 32) {            // uniform trip count for the ballots
+              bool pred = false; double d2 = 0.0; uint64_t slot = 0;
+              if (e < total) {
+                const int j = 31 - __clz(e + 1);
+                slot = (s << j) + (uint64_t)e;
+                if (slot < n) { d2 = dist2(m, slot, qx, qy, qz); pred = d2 <= bound; }
+              }
+              append(b, m, count, bound, k, lane, pred, d2, (uint32_t)slot);
+            }
+            break;
+          }
+          // ---- interior node: its own photon, then near child first
+          const double d2 = dist2(m, s, qx, qy, qz);
+          append(b, m, count, bound, k, lane, lane == 0 && d2 <= bound, d2, (uint32_t)s);
+          const uint2 nd = m.node[s];
+          const float sf = __uint_as_float(nd.x);
+          const double qa = nd.y == 0 ? qx : (nd.y == 1 ? qy : qz);
+          uint64_t near, far; double fd;
+          if (qa < (double)sf) { near = 2 * s + 1; far = 2 * s + 2; fd = (double)nextafterf(sf, -INFINITY) - qa; }
+          else { near = 2 * s + 2; far = 2 * s + 1; fd = qa - (double)nextafterf(sf, INFINITY); }
+          fd = fd > 0.0 ? fd : 0.0;
+          const double fd2 = fd * fd;
+          if (far < n && fd2 <= bound) { st_node[sp] = (uint32_t)far; st_d[sp] = fd2; sp++; }
+          if (near < n) s = near; else break;
+        }
+      }
+      exact_select(b, count, bound, k, lane);
+    }
+    // ---- radiance estimate, photon_utils.cpp:80-161
+    const int found = count;
+    double est[3] = {0.0, 0.0, 0.0};
+    if (found > 0 && rgb_out) {
+      const double nx = __shfl_sync(FULL, mine, 3), ny = __shfl_sync(FULL, mine, 4), nz = __shfl_sync(FULL, mine, 5);
+      const double bx = __shfl_sync(FULL, mine, 6), by = __shfl_sync(FULL, mine, 7), bz = __shfl_sync(FULL, mine, 8);
+      const double cos_theta = __shfl_sync(FULL, mine, 9);
+      double kd[3], ks[3];
+      for (int c = 0; c < 3; c++) { kd[c] = __shfl_sync(FULL, mine, 10 + c); ks[c] = __shfl_sync(FULL, mine, 13 + c); }
+      const double shin = __shfl_sync(FULL, mine, 16);
+      const bool has_spec = ks[0] != 0.0 || ks[1] != 0.0 || ks[2] != 0.0;
+      double max_d2 = 1.0e-6;                                                   // RN_EPSILON
+      if (found < k) max_d2 = ga.r2;
+      else max_d2 = fmax(max_d2, bound);                                        // bound == max kept d^2 after exact_select
+      double c1 = 1.0, c2 = 1.0, total_w = 0.0;
+      if (ga.filter == GI_FILTER_CONE) c1 = 1.0 / (ga.fk * sqrt(max_d2));
+      else if (ga.filter == GI_FILTER_GAUSS) { c1 = exp(-ga.fb); c2 = 1.0 / (2.0 * max_d2); }
+      for (int i = lane; i < found; i += 32) {
+        const uint2 sh = m.shade[b.slot[i]];
+        const double *dir = lut + 3 * (size_t)(sh.y & 0xffffu);
+        const double ix = dir[0], iy = dir[1], iz = dir[2];
+        const double perp = (nx * ix) + (ny * iy) + (nz * iz);
+        if ((cos_theta < 0 && perp < 0) || (cos_theta > 0 && perp > 0)) continue;
+        const uint32_t e = sh.x >> 24;
+        if (e == 0) { if (ga.filter == GI_FILTER_GAUSS) {
+            total_w += 1.0 - (1.0 - pow(c1, c2 * b.d2[i])) / (1.0 - c1); } continue; }
+        const double inv = __longlong_as_double((long long)(e - 136 + 1023) << 52);   // ldexp(1.0, e - 128 - 8)
+        double rgb[3] = {(double)(sh.x & 0xff) * inv, (double)((sh.x >> 8) & 0xff) * inv, (double)((sh.x >> 16) & 0xff) * inv};
+        double cos_alpha = (bx * -ix) + (by * -iy) + (bz * -iz);
+        if (cos_alpha < 0) cos_alpha = 0;
+        const double pw = has_spec ? pow(cos_alpha, shin) : 0.0;
+        const double ap = fabs(perp);
+        for (int c = 0; c < 3; c++) rgb[c] *= ap * kd[c] + pw * ks[c];
+        if (ga.filter == GI_FILTER_CONE) {
+          const double w = 1.0 - c1 * sqrt(b.d2[i]);
+          for (int c = 0; c < 3; c++) rgb[c] *= w;
+        } else if (ga.filter == GI_FILTER_GAUSS) {
+          const double w = 1.0 - (1.0 - pow(c1, c2 * b.d2[i])) / (1.0 - c1);
+          for (int c = 0; c < 3; c++) rgb[c] *= w;
+          total_w += w;
+        }
+        for (int c = 0; c < 3; c++) est[c] += rgb[c];
+      }
+      for (int o = 16; o > 0; o >>= 1) {
+        for (int c = 0; c < 3; c++) est[c] += __shfl_xor_sync(FULL, est[c], o);
+        total_w += __shfl_xor_sync(FULL, total_w, o);
+      }
+      const double PI = 3.14159265358979323846;
+      if (ga.filter == GI_FILTER_DISK && max_d2 > 0) { for (int c = 0; c < 3; c++) est[c] /= PI * max_d2; }
+      else if (ga.filter == GI_FILTER_CONE && max_d2 > 0) { for (int c = 0; c < 3; c++) est[c] /= (1.0 - 2.0 / 3.0 / ga.fk) * PI * max_d2; }
+      else if (ga.filter == GI_FILTER_GAUSS && total_w > 0 && max_d2 > 0) {
+        for (int c = 0; c < 3; c++) est[c] *= ga.fa * (found / total_w) / (PI * max_d2);
+      } else { est[0] = est[1] = est[2] = 0.0; }
+    }
+    if (rgb_out && lane == 0) { rgb_out[3 * qi] = est[0]; rgb_out[3 * qi + 1] = est[1]; rgb_out[3 * qi + 2] = est[2]; }
+    if (count_out && lane == 0) count_out[qi] = found;
+    if (idx_out) {
+      // ascending photon indices: sort the index column alone (d2 = 0 makes (d2, orig) order == orig order)
+      for (int i = lane; i < b.cap; i += 32) { b.d2[i] = 0.0; if (i >= found) b.orig[i] = 0xffffffffu; }
+      __syncwarp();
+      bitonic_sort(b, lane);
+      for (int i = lane; i < k; i += 32) idx_out[qi * (uint64_t)k + i] = i < found ? (int32_t)b.orig[i] : -1;
+    }
+    __syncwarp();
+  }
+}
+
+cudaError_t launch_gather(GiContext *ctx, const PhotonMapDev &m, const double *d_lut, const GiGatherQuery *d_q,
+                          uint64_t nq, const GatherArgs &ga, int32_t *d_idx, int32_t *d_count, double *d_rgb,
+                          cudaStream_t st) {
+  const size_t smem = (size_t)GI_GATHER_WARPS * ((size_t)ga.cap * 16 + 1024);
+  static size_t configured = 0;
+  if (smem > configured) {
+    cudaError_t e = cudaFuncSetAttribute(gather_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
+    if (e != cudaSuccess) return e;
+    configured = smem;
+  }
+  int per_sm = 1;
+  cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, gather_kernel, GI_GATHER_WARPS * 32, smem);
+  if (per_sm < 1) per_sm = 1;
+  uint64_t want = (nq + GI_GATHER_WARPS - 1) / GI_GATHER_WARPS;
+  uint64_t cap = (uint64_t)ctx->sm_count * per_sm;         // persistent: one resident wave, warps stride over queries
+  unsigned grid = (unsigned)(want < cap ? want : cap);
+  gather_kernel<<<grid, GI_GATHER_WARPS * 32, smem, st>>>(m, d_lut, d_q, nq, ga, d_idx, d_count, d_rgb);
+  ctx->launches++;
+  return cudaGetLastError();
+}
+
+}  // namespace gi

@@ -1,0 +1,217 @@
+// csrc/kdtree_build.cu -- GPU construction of a photon map: left-balanced kd-tree in heap layout (K5).
+//
+// Replaces `new R3Kdtree<Photon*>(photons, offset)` (src/photonmap.cpp:365,372), i.e. R3Kdtree::InsertPoints /
+// PartitionPoints (src/R3Shapes/R3Kdtree.cpp:1624-1671, 1552-1620): a single-threaded recursive build with
+// randomised quickselect and 31-photon leaf buckets (15 s for 1e7 photons on the CPU).
+//
+// Here: level-synchronous, sort-based construction of Jensen's left-balanced tree.  Every photon carries the id
+// ("tag") of the subtree it currently belongs to.  For level l = 0..L-1:
+//   1. key = (tag, float32 coordinate on the subtree's split axis); radix sort (key, photon id) -- after the sort
+//      the photons of subtree s are contiguous and start at a closed-form offset (left-balanced => every subtree
+//      size is known from n alone);
+//   2. the photon at offset `size of the left child subtree` inside its segment becomes node s; photons before it
+//      move to subtree 2s+1, after it to 2s+2;
+//   3. child boxes = parent box cut at the split; the split axis of a node is the longest axis of its box, as in
+//      the reference (R3Kdtree.cpp:1640, R3Box::LongestAxis R3Box.cpp:258-274).
+// Splits are float32 (monotone rounding of the FP64 coordinate); the search widens them by one ulp, distances stay
+// FP64, so the k-nearest SET is exact (see gather.cu).  Only photons not yet placed take part in a level's sort.
+#include <cub/device/device_radix_sort.cuh>
+#include <cuda_runtime.h>
+#include <float.h>
+#include <stdint.h>
+#include "context.h"
+#include "kdtree_build.h"
+
+namespace gi {
+
+__host__ __device__ __forceinline__ int level_of(uint64_t s) {
+#ifdef __CUDA_ARCH__
+  return 63 - __clzll((long long)(s + 1));
+#else
+  int l = 0; while (((s + 1) >> (l + 1)) != 0) l++; return l;
+#endif
+}
+
+// number of nodes in the subtree rooted at heap slot s of a left-balanced tree with n nodes and L levels
+__host__ __device__ __forceinline__ uint64_t subtree_size(uint64_t s, uint64_t n, int L) {
+  if (s >= n) return 0;
+  const int h = L - 1 - level_of(s);
+  const uint64_t inner = ((uint64_t)1 << h) - 1;
+  const uint64_t first_last = ((s + 1) << h) - 1;
+  uint64_t last = 0;
+  if (n > first_last) { last = n - first_last; if (last > ((uint64_t)1 << h)) last = (uint64_t)1 << h; }
+  return inner + last;
+}
+
+// array position where subtree s starts once the array is sorted by (tag) at the level of s
+__host__ __device__ __forceinline__ uint64_t segment_begin(uint64_t s, uint64_t n, int L) {
+  const int l = level_of(s);
+  const int h = L - 1 - l;
+  const uint64_t above = ((uint64_t)1 << l) - 1;
+  const uint64_t k = s - above;
+  const uint64_t full_above_last = ((uint64_t)1 << (L - 1)) - 1;
+  const uint64_t total_last = n > full_above_last ? n - full_above_last : 0;
+  uint64_t last = k << h; if (last > total_last) last = total_last;
+  return above + k * (((uint64_t)1 << h) - 1) + last;
+}
+
+__device__ __forceinline__ uint32_t float_to_ordered(float f) {
+  uint32_t u = __float_as_uint(f);
+  return (u & 0x80000000u) ? ~u : (u | 0x80000000u);
+}
+__device__ __forceinline__ float ordered_to_float(uint32_t o) {
+  return __uint_as_float((o & 0x80000000u) ? (o & 0x7fffffffu) : ~o);
+}
+
+__device__ __forceinline__ int longest_axis(const float *b) {          // R3Box::LongestAxis, R3Box.cpp:258-274
+  const float dx = b[3] - b[0], dy = b[4] - b[1], dz = b[5] - b[2];
+  if (dx > dy) return dx > dz ? 0 : 2;
+  return dy > dz ? 1 : 2;
+}
+
+__global__ void bbox_kernel(const GiPhoton *__restrict__ ph, uint64_t n, uint32_t *obox /* 6 ordered floats */) {
+  float lo[3] = {FLT_MAX, FLT_MAX, FLT_MAX}, hi[3] = {-FLT_MAX, -FLT_MAX, -FLT_MAX};
+  for (uint64_t i = (uint64_t)blockIdx.x * blockDim.x + threadIdx.x; i < n; i += (uint64_t)gridDim.x * blockDim.x)
+    for (int k = 0; k < 3; k++) {
+      const float c = (float)ph[i].position[k];
+      lo[k] = fminf(lo[k], c); hi[k] = fmaxf(hi[k], c);
+    }
+  for (int k = 0; k < 3; k++) {
+    for (int o = 16; o > 0; o >>= 1) {
+      lo[k] = fminf(lo[k], __shfl_xor_sync(0xffffffffu, lo[k], o));
+      hi[k] = fmaxf(hi[k], __shfl_xor_sync(0xffffffffu, hi[k], o));
+    }
+    if ((threadIdx.x & 31) == 0) {
+      atomicMin(&obox[k], float_to_ordered(lo[k]));
+      atomicMax(&obox[3 + k], float_to_ordered(hi[k]));
+    }
+  }
+}
+
+__global__ void init_kernel(uint64_t n, const uint32_t *__restrict__ obox, float *boxes, uint8_t *axis, uint64_t *keys,
+                            uint32_t *vals) {
+  const uint64_t i = (uint64_t)blockIdx.x * blockDim.x + threadIdx.x;
+  if (i == 0) {
+    float b[6];
+    for (int k = 0; k < 6; k++) { b[k] = ordered_to_float(obox[k]); boxes[k] = b[k]; }
+    axis[0] = (uint8_t)longest_axis(b);
+  }
+  if (i < n) { keys[i] = 0; vals[i] = (uint32_t)i; }
+}
+
+// key = tag << 32 | ordered float coordinate on the split axis of subtree `tag`
+__global__ void make_keys_kernel(const GiPhoton *__restrict__ ph, uint64_t first, uint64_t n, int level,
+                                 const uint8_t *__restrict__ axis, uint64_t *keys, const uint32_t *__restrict__ vals) {
+  const uint64_t p = first + (uint64_t)blockIdx.x * blockDim.x + threadIdx.x;
+  if (p >= n) return;
+  const uint64_t tag = keys[p] >> 32;
+  if (level_of(tag) < level) { keys[p] = tag << 32; return; }          // placed on the previous level
+  const float c = (float)ph[vals[p]].position[axis[tag]];
+  keys[p] = (tag << 32) | float_to_ordered(c);
+}
+
+__global__ void assign_kernel(uint64_t first, uint64_t n, int L, int level, uint64_t *keys,
+                              const uint32_t *__restrict__ vals, uint32_t *heap_photon, float *split) {
+  const uint64_t p = first + (uint64_t)blockIdx.x * blockDim.x + threadIdx.x;
+  if (p >= n) return;
+  const uint64_t key = keys[p];
+  const uint64_t s = key >> 32;
+  if (level_of(s) < level) return;
+  const uint64_t pivot = segment_begin(s, n, L) + subtree_size(2 * s + 1, n, L);
+  if (p < pivot) keys[p] = (2 * s + 1) << 32;
+  else if (p > pivot) keys[p] = (2 * s + 2) << 32;
+  else { heap_photon[s] = vals[p]; split[s] = ordered_to_float((uint32_t)key); }
+}
+
+__global__ void child_box_kernel(uint64_t n, int level, const float *__restrict__ split, float *boxes, uint8_t *axis) {
+  const uint64_t s = (((uint64_t)1 << level) - 1) + (uint64_t)blockIdx.x * blockDim.x + threadIdx.x;
+  if (s >= n || s >= ((uint64_t)2 << level) - 1) return;
+  float b[6];
+  for (int k = 0; k < 6; k++) b[k] = boxes[6 * s + k];
+  const int ax = axis[s];
+  const float sp = split[s];
+  for (int c = 0; c < 2; c++) {
+    const uint64_t ch = 2 * s + 1 + c;
+    if (ch >= n) break;
+    float cb[6];
+    for (int k = 0; k < 6; k++) cb[k] = b[k];
+    if (c == 0) cb[3 + ax] = sp; else cb[ax] = sp;
+    for (int k = 0; k < 6; k++) boxes[6 * ch + k] = cb[k];
+    axis[ch] = (uint8_t)longest_axis(cb);
+  }
+}
+
+__global__ void finalize_kernel(const GiPhoton *__restrict__ ph, uint64_t n, const uint32_t *__restrict__ heap_photon,
+                                const float *__restrict__ split, const uint8_t *__restrict__ axis, double *px, double *py,
+                                double *pz, uint2 *node, uint2 *shade, uint32_t *orig) {
+  const uint64_t i = (uint64_t)blockIdx.x * blockDim.x + threadIdx.x;
+  if (i >= n) return;
+  const uint32_t src = heap_photon[i];
+  const uint4 *raw = (const uint4 *)(ph + src);                        // 32-byte record: 2 x LDG.128
+  const uint4 a = raw[0], b = raw[1];
+  px[i] = __hiloint2double(a.y, a.x); py[i] = __hiloint2double(a.w, a.z); pz[i] = __hiloint2double(b.y, b.x);
+  shade[i] = make_uint2(b.z, b.w & 0xffffu);
+  orig[i] = src;
+  node[i] = make_uint2(__float_as_uint(split[i]), axis[i]);
+}
+
+#define CKB(x) do { cudaError_t e_ = (x); if (e_ != cudaSuccess) { err = e_; goto done; } } while (0)
+
+cudaError_t build_photon_map(GiContext *ctx, PhotonMapStore &m, uint64_t n) {
+  cudaError_t err = cudaSuccess;
+  cudaStream_t st = ctx->stream;
+  const GiPhoton *ph = (const GiPhoton *)m.raw;
+  int L = 0; while (((uint64_t)1 << L) <= n) L++;                       // floor(log2 n) + 1
+  uint64_t *keys[2] = {nullptr, nullptr}; uint32_t *vals[2] = {nullptr, nullptr};
+  uint32_t *heap_photon = nullptr, *obox = nullptr; float *split = nullptr, *boxes = nullptr; uint8_t *axis = nullptr;
+  void *tmp = nullptr; size_t tmp_bytes = 0;
+  double *px = nullptr, *py = nullptr, *pz = nullptr; uint2 *node = nullptr, *shade = nullptr; uint32_t *orig = nullptr;
+  const int B = 256;
+  const unsigned G = (unsigned)((n + B - 1) / B);
+  int cur = 0;
+  for (int k = 0; k < 2; k++) { CKB(cudaMalloc(&keys[k], 8 * n)); CKB(cudaMalloc(&vals[k], 4 * n)); }
+  CKB(cudaMalloc(&heap_photon, 4 * n)); CKB(cudaMalloc(&split, 4 * n)); CKB(cudaMalloc(&boxes, 24 * n));
+  CKB(cudaMalloc(&axis, n)); CKB(cudaMalloc(&obox, 24));
+  CKB(cub::DeviceRadixSort::SortPairs(nullptr, tmp_bytes, keys[0], keys[1], vals[0], vals[1], (int)n, 0, 64, st));
+  CKB(cudaMalloc(&tmp, tmp_bytes));
+  {
+    const uint32_t init[6] = {0xffffffffu, 0xffffffffu, 0xffffffffu, 0u, 0u, 0u};
+    CKB(cudaMemcpyAsync(obox, init, 24, cudaMemcpyHostToDevice, st));
+    unsigned gb = G < 1184u ? G : 1184u;
+    bbox_kernel<<<gb, B, 0, st>>>(ph, n, obox);
+    init_kernel<<<G, B, 0, st>>>(n, obox, boxes, axis, keys[0], vals[0]);
+    ctx->launches += 2;
+  }
+  for (int level = 0; level < L; level++) {
+    const uint64_t first = level == 0 ? 0 : ((uint64_t)1 << (level - 1)) - 1;    // placed two levels up: final
+    const uint64_t cnt = n - first;
+    const unsigned g = (unsigned)((cnt + B - 1) / B);
+    make_keys_kernel<<<g, B, 0, st>>>(ph, first, n, level, axis, keys[cur], vals[cur]);
+    int end_bit = 33 + level; if (end_bit > 64) end_bit = 64;
+    CKB(cub::DeviceRadixSort::SortPairs(tmp, tmp_bytes, keys[cur] + first, keys[cur ^ 1] + first, vals[cur] + first,
+                                        vals[cur ^ 1] + first, (int)cnt, 0, end_bit, st));
+    cur ^= 1;
+    assign_kernel<<<g, B, 0, st>>>(first, n, L, level, keys[cur], vals[cur], heap_photon, split);
+    const uint64_t level_nodes = (uint64_t)1 << level;
+    child_box_kernel<<<(unsigned)((level_nodes + B - 1) / B), B, 0, st>>>(n, level, split, boxes, axis);
+    ctx->launches += 4;
+    CKB(cudaGetLastError());
+  }
+  CKB(cudaMalloc(&px, 8 * n)); CKB(cudaMalloc(&py, 8 * n)); CKB(cudaMalloc(&pz, 8 * n));
+  CKB(cudaMalloc(&node, 8 * n)); CKB(cudaMalloc(&shade, 8 * n)); CKB(cudaMalloc(&orig, 4 * n));
+  finalize_kernel<<<G, B, 0, st>>>(ph, n, heap_photon, split, axis, px, py, pz, node, shade, orig);
+  ctx->launches++;
+  CKB(cudaGetLastError());
+  CKB(cudaStreamSynchronize(st));
+  m.dev.n = n; m.dev.levels = L; m.dev.px = px; m.dev.py = py; m.dev.pz = pz; m.dev.node = node; m.dev.shade = shade;
+  m.dev.orig = orig;
+  m.built = true;
+  px = py = pz = nullptr; node = shade = nullptr; orig = nullptr;
+done:
+  for (int k = 0; k < 2; k++) { cudaFree(keys[k]); cudaFree(vals[k]); }
+  cudaFree(heap_photon); cudaFree(split); cudaFree(boxes); cudaFree(axis); cudaFree(obox); cudaFree(tmp);
+  cudaFree(px); cudaFree(py); cudaFree(pz); cudaFree(node); cudaFree(shade); cudaFree(orig);
+  return err;
+}
+
+}  // namespace gi

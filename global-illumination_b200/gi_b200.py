@@ -1,0 +1,243 @@
+"""ctypes binding of libgi_b200.so (include/gi_b200.h) -- the thin Python host side used by tests and bench.py.
+
+The product is the C-ABI library; this module only marshals numpy buffers into it.  There is NO CPU path: if the
+shared library is missing, or no CUDA device is present, everything here raises.
+Structure layouts mirror include/gi_b200.h one to one.
+"""
+import ctypes
+import os
+import numpy as np
+
+_HERE = os.path.dirname(os.path.abspath(__file__))
+LIB_PATH = os.path.join(_HERE, "libgi_b200.so")
+
+GI_MAP_GLOBAL, GI_MAP_CAUSTIC = 0, 1
+GI_FILTER_DISK, GI_FILTER_CONE, GI_FILTER_GAUSS = 0, 1, 2
+
+RAY = np.dtype([("o", "<f8", 3), ("d", "<f8", 3)])
+HIT = np.dtype([("hit", "<i4"), ("shape", "<i4"), ("prim", "<i4"), ("element", "<i4"), ("t", "<f8"),
+                ("p", "<f8", 3), ("n", "<f8", 3)])
+PHOTON = np.dtype([("position", "<f8", 3), ("rgbe", "u1", 4), ("direction", "<u2"), ("pad", "<u2")])
+QUERY = np.dtype([("p", "<f8", 3), ("n", "<f8", 3), ("bounce", "<f8", 3), ("cos_theta", "<f8"), ("kd", "<f8", 3),
+                  ("ks", "<f8", 3), ("shininess", "<f8")])
+
+
+class GiCamera(ctypes.Structure):
+    _fields_ = [("eye", ctypes.c_double * 3), ("towards", ctypes.c_double * 3), ("up", ctypes.c_double * 3),
+                ("right", ctypes.c_double * 3), ("xfov", ctypes.c_double), ("yfov", ctypes.c_double),
+                ("neardist", ctypes.c_double), ("fardist", ctypes.c_double)]
+
+
+class GiScene(ctypes.Structure):
+    _fields_ = [("n_nodes", ctypes.c_int32), ("n_elements", ctypes.c_int32), ("n_materials", ctypes.c_int32),
+                ("n_prims", ctypes.c_int32), ("n_lights", ctypes.c_int32), ("n_shapes", ctypes.c_int32),
+                ("nodes", ctypes.c_void_p), ("elements", ctypes.c_void_p), ("materials", ctypes.c_void_p),
+                ("prims", ctypes.c_void_p), ("shapes", ctypes.c_void_p), ("lights", ctypes.c_void_p),
+                ("camera", GiCamera), ("ambient", ctypes.c_double * 3), ("background", ctypes.c_double * 3),
+                ("bbox_min", ctypes.c_double * 3), ("bbox_max", ctypes.c_double * 3), ("centroid", ctypes.c_double * 3),
+                ("radius", ctypes.c_double)]
+
+
+class GiParams(ctypes.Structure):
+    _fields_ = [("verbose", ctypes.c_int32), ("threads", ctypes.c_int32), ("fresnel", ctypes.c_int32),
+                ("ir_air", ctypes.c_double),
+                ("ambient", ctypes.c_int32), ("direct_illum", ctypes.c_int32), ("transmissive_illum", ctypes.c_int32),
+                ("specular_illum", ctypes.c_int32), ("indirect_illum", ctypes.c_int32), ("caustic_illum", ctypes.c_int32),
+                ("direct_photon_illum", ctypes.c_int32), ("fast_global", ctypes.c_int32), ("irradiance_cache", ctypes.c_int32),
+                ("shadows", ctypes.c_int32), ("soft_shadows", ctypes.c_int32), ("light_test", ctypes.c_int32),
+                ("shadow_test", ctypes.c_int32),
+                ("monte_carlo", ctypes.c_int32), ("max_monte_depth", ctypes.c_int32),
+                ("prob_absorb", ctypes.c_double),
+                ("recursive_shadows", ctypes.c_int32), ("distrib_transmissive", ctypes.c_int32),
+                ("transmissive_test", ctypes.c_int32), ("distrib_specular", ctypes.c_int32), ("specular_test", ctypes.c_int32),
+                ("depth_of_field", ctypes.c_int32), ("dof_test", ctypes.c_int32),
+                ("focus_depth", ctypes.c_double), ("aperture_radius", ctypes.c_double),
+                ("global_photon_count", ctypes.c_int32), ("caustic_photon_count", ctypes.c_int32),
+                ("max_photon_depth", ctypes.c_int32),
+                ("indirect_test", ctypes.c_int32), ("global_estimate_size", ctypes.c_int32),
+                ("global_estimate_dist", ctypes.c_double),
+                ("global_filter", ctypes.c_int32), ("caustic_estimate_size", ctypes.c_int32),
+                ("caustic_estimate_dist", ctypes.c_double),
+                ("caustic_filter", ctypes.c_int32),
+                ("filter_const_a", ctypes.c_double), ("filter_const_b", ctypes.c_double), ("filter_const_k", ctypes.c_double),
+                ("seed", ctypes.c_uint64), ("rank", ctypes.c_int32), ("world_size", ctypes.c_int32)]
+
+
+class GiPhotonStats(ctypes.Structure):
+    _fields_ = [("global_stored", ctypes.c_uint64), ("caustic_stored", ctypes.c_uint64),
+                ("global_emitted", ctypes.c_uint64), ("caustic_emitted", ctypes.c_uint64),
+                ("indirect_illum", ctypes.c_int32), ("caustic_illum", ctypes.c_int32),
+                ("direct_photon_illum", ctypes.c_int32), ("rounds", ctypes.c_int32),
+                ("trace_ms", ctypes.c_double), ("build_ms", ctypes.c_double)]
+
+
+class GiRenderStats(ctypes.Structure):
+    _fields_ = [("screen_rays", ctypes.c_uint64), ("shadow_rays", ctypes.c_uint64), ("monte_rays", ctypes.c_uint64),
+                ("transmissive_samples", ctypes.c_uint64), ("specular_samples", ctypes.c_uint64),
+                ("indirect_samples", ctypes.c_uint64), ("caustic_samples", ctypes.c_uint64),
+                ("render_ms", ctypes.c_double)]
+
+
+# every symbol include/gi_b200.h declares (tests check the built library exports all of them)
+EXPORTS = ["gi_abi_version", "gi_last_error", "gi_create", "gi_destroy", "gi_default_params", "gi_launch_count",
+           "gi_host_scene_load", "gi_host_scene_view", "gi_host_scene_save", "gi_host_scene_free",
+           "gi_upload_scene", "gi_intersect_batch", "gi_intersect_batch_device",
+           "gi_load_photons", "gi_load_photons_device", "gi_load_photons_file", "gi_dump_photons_file",
+           "gi_photon_count", "gi_get_photons", "gi_build_maps", "gi_gather_batch", "gi_gather_batch_device",
+           "gi_trace_photons", "gi_render", "gi_render_float"]
+
+_lib = None
+
+
+def lib():
+    """Load libgi_b200.so; raises if it has not been built (no fallback)."""
+    global _lib
+    if _lib is None:
+        if not os.path.exists(LIB_PATH):
+            raise RuntimeError("libgi_b200.so is not built (run `make lib` or __graft_entry__.build()); "
+                               "gi_b200 has no CPU fallback")
+        L = ctypes.CDLL(LIB_PATH)
+        L.gi_last_error.restype = ctypes.c_char_p
+        vp, u64, i32, dbl = ctypes.c_void_p, ctypes.c_uint64, ctypes.c_int, ctypes.c_double
+        L.gi_create.argtypes = [i32, ctypes.POINTER(vp)]
+        L.gi_destroy.argtypes = [vp]; L.gi_destroy.restype = None
+        L.gi_default_params.argtypes = [ctypes.POINTER(GiParams)]; L.gi_default_params.restype = None
+        L.gi_launch_count.argtypes = [vp, ctypes.POINTER(u64)]
+        L.gi_host_scene_load.argtypes = [ctypes.c_char_p, i32, ctypes.POINTER(vp)]
+        L.gi_host_scene_view.argtypes = [vp, ctypes.POINTER(GiScene)]
+        L.gi_host_scene_save.argtypes = [vp, ctypes.c_char_p]
+        L.gi_host_scene_free.argtypes = [vp]; L.gi_host_scene_free.restype = None
+        L.gi_upload_scene.argtypes = [vp, ctypes.POINTER(GiScene)]
+        L.gi_intersect_batch.argtypes = [vp, vp, u64, vp]
+        L.gi_intersect_batch_device.argtypes = [vp, vp, u64, vp, vp]
+        L.gi_load_photons.argtypes = [vp, i32, vp, u64]
+        L.gi_load_photons_device.argtypes = [vp, i32, vp, u64]
+        L.gi_load_photons_file.argtypes = [vp, i32, ctypes.c_char_p]
+        L.gi_dump_photons_file.argtypes = [vp, i32, ctypes.c_char_p]
+        L.gi_photon_count.argtypes = [vp, i32, ctypes.POINTER(u64)]
+        L.gi_get_photons.argtypes = [vp, i32, vp, u64]
+        L.gi_build_maps.argtypes = [vp, ctypes.POINTER(GiParams)]
+        L.gi_gather_batch.argtypes = [vp, i32, vp, u64, i32, dbl, i32, ctypes.POINTER(GiParams), vp, vp, vp]
+        L.gi_gather_batch_device.argtypes = [vp, i32, vp, u64, i32, dbl, i32, ctypes.POINTER(GiParams), vp, vp, vp, vp]
+        L.gi_trace_photons.argtypes = [vp, ctypes.POINTER(GiParams), ctypes.POINTER(GiPhotonStats)]
+        L.gi_render.argtypes = [vp, ctypes.POINTER(GiParams), i32, i32, i32, vp, ctypes.POINTER(GiRenderStats)]
+        L.gi_render_float.argtypes = [vp, ctypes.POINTER(GiParams), i32, i32, i32, vp, ctypes.POINTER(GiRenderStats)]
+        _lib = L
+    return _lib
+
+
+class GiError(RuntimeError):
+    pass
+
+
+def _check(rc):
+    if rc != 0:
+        raise GiError(lib().gi_last_error().decode(errors="replace"))
+
+
+def default_params():
+    p = GiParams()
+    lib().gi_default_params(ctypes.byref(p))
+    return p
+
+
+class HostScene:
+    """Flattened scene on the host: the .scn/.off loader of the reference's CLI, or a saved .gisc file."""
+
+    def __init__(self, path, real_material=False):
+        self.handle = ctypes.c_void_p()
+        _check(lib().gi_host_scene_load(path.encode(), int(real_material), ctypes.byref(self.handle)))
+        self.view = GiScene()
+        _check(lib().gi_host_scene_view(self.handle, ctypes.byref(self.view)))
+
+    def save(self, gisc_path):
+        _check(lib().gi_host_scene_save(self.handle, gisc_path.encode()))
+
+    def close(self):
+        if self.handle:
+            lib().gi_host_scene_free(self.handle)
+            self.handle = ctypes.c_void_p()
+
+    def __del__(self):
+        try:
+            self.close()
+        except Exception:
+            pass
+
+
+class Context:
+    """One GPU.  Mirrors the gi_* entry points; host numpy buffers in, host numpy buffers out."""
+
+    def __init__(self, device=0):
+        self.handle = ctypes.c_void_p()
+        _check(lib().gi_create(device, ctypes.byref(self.handle)))
+
+    def close(self):
+        if self.handle:
+            lib().gi_destroy(self.handle)
+            self.handle = ctypes.c_void_p()
+
+    def __del__(self):
+        try:
+            self.close()
+        except Exception:
+            pass
+
+    def launch_count(self):
+        n = ctypes.c_uint64()
+        _check(lib().gi_launch_count(self.handle, ctypes.byref(n)))
+        return n.value
+
+    def upload_scene(self, scene):
+        _check(lib().gi_upload_scene(self.handle, ctypes.byref(scene.view)))
+
+    def intersect(self, rays):
+        rays = np.ascontiguousarray(rays, dtype=np.float64).reshape(-1, 6)
+        hits = np.zeros(len(rays), dtype=HIT)
+        _check(lib().gi_intersect_batch(self.handle, rays.ctypes.data, len(rays), hits.ctypes.data))
+        return hits
+
+    def intersect_device(self, d_rays, n, d_hits, stream=None):
+        _check(lib().gi_intersect_batch_device(self.handle, d_rays, n, d_hits, stream))
+
+    def load_photons(self, which, photons):
+        photons = np.ascontiguousarray(photons, dtype=PHOTON)
+        _check(lib().gi_load_photons(self.handle, which, photons.ctypes.data, len(photons)))
+
+    def load_photons_device(self, which, d_ptr, n):
+        _check(lib().gi_load_photons_device(self.handle, which, d_ptr, n))
+
+    def load_photons_file(self, which, path):
+        _check(lib().gi_load_photons_file(self.handle, which, path.encode()))
+
+    def dump_photons_file(self, which, path):
+        _check(lib().gi_dump_photons_file(self.handle, which, path.encode()))
+
+    def photon_count(self, which):
+        n = ctypes.c_uint64()
+        _check(lib().gi_photon_count(self.handle, which, ctypes.byref(n)))
+        return n.value
+
+    def get_photons(self, which):
+        out = np.zeros(self.photon_count(which), dtype=PHOTON)
+        _check(lib().gi_get_photons(self.handle, which, out.ctypes.data, len(out)))
+        return out
+
+    def build_maps(self, params=None):
+        p = params or default_params()
+        _check(lib().gi_build_maps(self.handle, ctypes.byref(p)))
+
+    def gather(self, which, queries, k, r, filter=GI_FILTER_DISK, params=None, want_idx=True):
+        queries = np.ascontiguousarray(queries, dtype=QUERY)
+        n = len(queries)
+        idx = np.full((n, k), -1, dtype=np.int32) if want_idx else None
+        cnt = np.zeros(n, dtype=np.int32)
+        rgb = np.zeros((n, 3), dtype=np.float64)
+        p = params or default_params()
+        _check(lib().gi_gather_batch(self.handle, which, queries.ctypes.data, n, k, float(r), filter, ctypes.byref(p),
+                                     idx.ctypes.data if want_idx else None, cnt.ctypes.data, rgb.ctypes.data))
+        return idx, cnt, rgb
+
+    def gather_device(self, which, d_queries, n, k, r, filter, params, d_idx, d_count, d_rgb, stream=None):
+        _check(lib().gi_gather_batch_device(self.handle, which, d_queries, n, k, float(r), filter, ctypes.byref(params),
+                                            d_idx, d_count, d_rgb, stream))

@@ -206,6 +206,17 @@ int gi_create(int device, GiContext **out);                       /* fails if no
 void gi_destroy(GiContext *ctx);
 void gi_default_params(GiParams *p);                              /* photonmap.cpp:41-106 */
 
+int gi_launch_count(GiContext *ctx, uint64_t *out);                /* kernels launched so far by this context */
+
+/* host-side .scn/.off loader (no device needed): ReadScene (src/utils/io_utils.cpp:219-250) ->
+ * R3Scene::ReadFile (R3Scene.cpp:514-587) -> ReadPrinceton (:1463-1953) / R3Mesh::ReadOffFile
+ * (R3Mesh.cpp:4075-4215).  `path` ending in .gisc reads a flattened scene saved by gi_host_scene_save. */
+typedef struct GiHostScene GiHostScene;
+int gi_host_scene_load(const char *path, int real_material, GiHostScene **out);
+int gi_host_scene_view(const GiHostScene *h, GiScene *out);       /* pointers stay owned by `h` */
+int gi_host_scene_save(const GiHostScene *h, const char *gisc_path);
+void gi_host_scene_free(GiHostScene *h);
+
 /* replaces the pointer-chasing R3Scene graph: flatten + upload + GPU BVH build */
 int gi_upload_scene(GiContext *ctx, const GiScene *scene);
 
@@ -216,6 +227,7 @@ int gi_intersect_batch_device(GiContext *ctx, const GiRay *d_rays, uint64_t n, G
 
 /* photon maps: GLOBAL_PHOTONS / CAUSTIC_PHOTONS + R3Kdtree build (photonmap.cpp:364-377) */
 int gi_load_photons(GiContext *ctx, int map, const GiPhoton *photons, uint64_t n);
+int gi_load_photons_device(GiContext *ctx, int map, const GiPhoton *d_photons, uint64_t n);   /* device buffer */
 int gi_load_photons_file(GiContext *ctx, int map, const char *path);
 int gi_dump_photons_file(GiContext *ctx, int map, const char *path);
 int gi_photon_count(GiContext *ctx, int map, uint64_t *n_out);

@@ -273,12 +273,191 @@ static int cmd_isect(int argc, char **argv) {
   return 0;
 }
 
+// ---------------------------------------------------------------- photon files
+static std::vector<Photon> read_photons(const char *path) {
+  FILE *f = fopen(path, "rb"); if (!f) die("cannot open photon file");
+  uint32_t hdr[2]; uint64_t n;
+  if (fread(hdr, 4, 2, f) != 2 || hdr[0] != PMAP_MAGIC || fread(&n, 8, 1, f) != 1) die("bad photon file");
+  std::vector<Photon> ph(n);
+  if (n && fread(ph.data(), sizeof(Photon), n, f) != n) die("short photon file");
+  fclose(f); return ph;
+}
+static void write_photons(const std::string &path, RNArray<Photon *> &arr) {
+  FILE *f = fopen(path.c_str(), "wb"); if (!f) die("cannot open photon output");
+  uint32_t hdr[2] = {PMAP_MAGIC, 1}; uint64_t n = arr.NEntries();
+  fwrite(hdr, 4, 2, f); fwrite(&n, 8, 1, f);
+  for (uint64_t i = 0; i < n; i++) {
+    Photon p; memset(&p, 0, sizeof(p)); p.position = arr[i]->position; memcpy(p.rgbe, arr[i]->rgbe, 4);
+    p.direction = arr[i]->direction;
+    fwrite(&p, sizeof(Photon), 1, f);
+  }
+  fclose(f);
+}
+
+// ---------------------------------------------------------------- photons (MapPhotons, photonmap.cpp:260-436)
+static int cmd_photons(int argc, char **argv) {
+  if (argc < 4) die("usage: photons in.scn out_prefix [-global N] [-caustic N] [-threads N] [-pd N]");
+  for (int i = 4; i + 1 < argc; i += 2) {
+    if (!strcmp(argv[i], "-global")) GLOBAL_PHOTON_COUNT = atoi(argv[i + 1]);
+    else if (!strcmp(argv[i], "-caustic")) CAUSTIC_PHOTON_COUNT = atoi(argv[i + 1]);
+    else if (!strcmp(argv[i], "-threads")) THREADS = atoi(argv[i + 1]);
+    else if (!strcmp(argv[i], "-pd")) MAX_PHOTON_DEPTH = atoi(argv[i + 1]);
+    else die("unknown photons flag");
+  }
+  load_scene(argv[2], false);
+  auto t0 = std::chrono::steady_clock::now();
+  MapPhotons();
+  double sec = std::chrono::duration<double>(std::chrono::steady_clock::now() - t0).count();
+  write_photons(std::string(argv[3]) + ".global.gipm", GLOBAL_PHOTONS);
+  write_photons(std::string(argv[3]) + ".caustic.gipm", CAUSTIC_PHOTONS);
+  printf("{\"cmd\": \"photons\", \"global\": %d, \"caustic\": %d, \"threads\": %d, \"seconds\": %.6f}\n",
+         GLOBAL_PHOTONS.NEntries(), CAUSTIC_PHOTONS.NEntries(), THREADS, sec);
+  return 0;
+}
+
+// ---------------------------------------------------------------- gather (EstimateRadiance, photon_utils.cpp:72-162)
+// queries.bin: u32 magic "GQRY", u32 n, n x QueryRec.  out.bin: u32 magic "GGAT", u32 n, u32 k, u32 0,
+// then n x {i32 count, f64 rgb[3] (packed: 4 + 24 = 28 -> stored as i32 count, i32 pad, 3 f64)}, then n*k i32 ascending
+// photon indices (padded with -1) from FindClosestQuick (R3Kdtree.cpp:829-848) on the same tree.
+static int cmd_gather(int argc, char **argv) {
+  if (argc < 8) die("usage: gather photons.gipm queries.bin out.bin k r filter [threads]");
+  std::vector<Photon> ph = read_photons(argv[2]);
+  FILE *f = fopen(argv[3], "rb"); if (!f) die("cannot open queries");
+  uint32_t hdr[2]; if (fread(hdr, 4, 2, f) != 2 || hdr[0] != 0x59525147) die("bad queries file");
+  uint32_t n = hdr[1]; std::vector<QueryRec> q(n);
+  if (n && fread(q.data(), sizeof(QueryRec), n, f) != n) die("short queries file");
+  fclose(f);
+  int k = atoi(argv[5]); double r = atof(argv[6]); int filter = atoi(argv[7]);
+  int threads = argc > 8 ? atoi(argv[8]) : 1; if (threads < 1) threads = 1;
+  RNArray<Photon *> arr;
+  for (size_t i = 0; i < ph.size(); i++) arr.Insert(&ph[i]);
+  auto tb = std::chrono::steady_clock::now();
+  R3Kdtree<Photon *> *tree = ph.empty() ? NULL : new R3Kdtree<Photon *>(arr, offsetof(struct Photon, position));
+  double build_sec = std::chrono::duration<double>(std::chrono::steady_clock::now() - tb).count();
+  BuildDirectionLookupTable();
+  struct Out { int32_t count, pad; double rgb[3]; };
+  std::vector<Out> out(n); std::vector<int32_t> idx((size_t)n * k, -1);
+  auto t0 = std::chrono::steady_clock::now();
+  auto work = [&](int id) {
+    for (uint32_t i = id; i < n; i += threads) {
+      const QueryRec &qq = q[i];
+      R3Point point(qq.p[0], qq.p[1], qq.p[2]); R3Vector normal(qq.n[0], qq.n[1], qq.n[2]);
+      R3Vector bounce(qq.bounce[0], qq.bounce[1], qq.bounce[2]);
+      R3Brdf brdf(RNblack_rgb, RNRgb(qq.kd[0], qq.kd[1], qq.kd[2]), RNRgb(qq.ks[0], qq.ks[1], qq.ks[2]), RNblack_rgb,
+                  RNblack_rgb, qq.shininess, 1.0);
+      RNRgb color = RNblack_rgb;
+      Out o; memset(&o, 0, sizeof(o));
+      if (tree) {
+        EstimateRadiance(point, normal, color, &brdf, bounce, qq.cos_theta, tree, k, r, (Filter_Type)filter);
+        std::vector<PointAndDistanceSqd<Photon *> > near;
+        tree->FindClosestQuick(point, 0, r, k, near);
+        o.count = (int32_t)near.size();
+        std::vector<int32_t> ids;
+        for (auto &e : near) ids.push_back((int32_t)(e.point - ph.data()));
+        std::sort(ids.begin(), ids.end());
+        for (size_t j = 0; j < ids.size(); j++) idx[(size_t)i * k + j] = ids[j];
+      }
+      o.rgb[0] = color.R(); o.rgb[1] = color.G(); o.rgb[2] = color.B();
+      out[i] = o;
+    }
+  };
+  std::vector<std::thread> th;
+  for (int i = 1; i < threads; i++) th.emplace_back(work, i);
+  work(0);
+  for (auto &x : th) x.join();
+  double sec = std::chrono::duration<double>(std::chrono::steady_clock::now() - t0).count();
+  f = fopen(argv[4], "wb"); if (!f) die("cannot open output");
+  uint32_t oh[4] = {0x54414747, n, (uint32_t)k, 0};
+  fwrite(oh, 4, 4, f); fwrite(out.data(), sizeof(Out), n, f); fwrite(idx.data(), 4, idx.size(), f); fclose(f);
+  printf("{\"cmd\": \"gather\", \"photons\": %zu, \"queries\": %u, \"k\": %d, \"threads\": %d, \"build_seconds\": %.6f, "
+         "\"seconds\": %.6f, \"gathers_per_s\": %.3f}\n", ph.size(), n, k, threads, build_sec, sec, 2.0 * n / sec);
+  return 0;
+}
+
+// ---------------------------------------------------------------- bench: the hot path on all host threads
+// One "step" = R3Scene::Intersects over every ray of rays.bin + EstimateRadiance over every query of queries.bin
+// (kd-tree built once, outside the timed steps).  Prints one JSON line with the per-step seconds.
+static int cmd_bench(int argc, char **argv) {
+  if (argc < 12) die("usage: bench in.scn rays.bin photons.gipm queries.bin k r filter threads steps warmup");
+  R3Scene *scene = load_scene(argv[2], false);
+  uint32_t nr; std::vector<double> rays = read_rays(argv[3], nr);
+  std::vector<Photon> ph = read_photons(argv[4]);
+  FILE *f = fopen(argv[5], "rb"); if (!f) die("cannot open queries");
+  uint32_t hdr[2]; if (fread(hdr, 4, 2, f) != 2 || hdr[0] != 0x59525147) die("bad queries file");
+  uint32_t nq = hdr[1]; std::vector<QueryRec> q(nq);
+  if (nq && fread(q.data(), sizeof(QueryRec), nq, f) != nq) die("short queries file");
+  fclose(f);
+  int k = atoi(argv[6]); double r = atof(argv[7]); int filter = atoi(argv[8]);
+  int threads = atoi(argv[9]), steps = atoi(argv[10]), warmup = atoi(argv[11]); if (threads < 1) threads = 1;
+  RNArray<Photon *> arr;
+  for (size_t i = 0; i < ph.size(); i++) arr.Insert(&ph[i]);
+  auto tb = std::chrono::steady_clock::now();
+  R3Kdtree<Photon *> *tree = ph.empty() ? NULL : new R3Kdtree<Photon *>(arr, offsetof(struct Photon, position));
+  double build_sec = std::chrono::duration<double>(std::chrono::steady_clock::now() - tb).count();
+  BuildDirectionLookupTable();
+  std::vector<double> sink(threads, 0.0), isect_s, gather_s;
+  for (int step = 0; step < warmup + steps; step++) {
+    auto t0 = std::chrono::steady_clock::now();
+    {
+      auto work = [&](int id) {
+        double acc = 0;
+        for (uint32_t i = id; i < nr; i += threads) {
+          const double *rr = &rays[(size_t)i * 6];
+          R3Ray ray(R3Point(rr[0], rr[1], rr[2]), R3Vector(rr[3], rr[4], rr[5]), TRUE);
+          R3SceneNode *node; R3SceneElement *element; R3Shape *shape; R3Point point; R3Vector normal; RNScalar t;
+          if (scene->Intersects(ray, &node, &element, &shape, &point, &normal, &t)) acc += t;
+        }
+        sink[id] += acc;
+      };
+      std::vector<std::thread> th;
+      for (int i = 1; i < threads; i++) th.emplace_back(work, i);
+      work(0);
+      for (auto &x : th) x.join();
+    }
+    auto t1 = std::chrono::steady_clock::now();
+    if (tree) {
+      auto work = [&](int id) {
+        double acc = 0;
+        for (uint32_t i = id; i < nq; i += threads) {
+          const QueryRec &qq = q[i];
+          R3Point point(qq.p[0], qq.p[1], qq.p[2]); R3Vector normal(qq.n[0], qq.n[1], qq.n[2]);
+          R3Vector bounce(qq.bounce[0], qq.bounce[1], qq.bounce[2]);
+          R3Brdf brdf(RNblack_rgb, RNRgb(qq.kd[0], qq.kd[1], qq.kd[2]), RNRgb(qq.ks[0], qq.ks[1], qq.ks[2]), RNblack_rgb,
+                      RNblack_rgb, qq.shininess, 1.0);
+          RNRgb color = RNblack_rgb;
+          EstimateRadiance(point, normal, color, &brdf, bounce, qq.cos_theta, tree, k, r, (Filter_Type)filter);
+          acc += color.R();
+        }
+        sink[id] += acc;
+      };
+      std::vector<std::thread> th;
+      for (int i = 1; i < threads; i++) th.emplace_back(work, i);
+      work(0);
+      for (auto &x : th) x.join();
+    }
+    auto t2 = std::chrono::steady_clock::now();
+    if (step >= warmup) {
+      isect_s.push_back(std::chrono::duration<double>(t1 - t0).count());
+      gather_s.push_back(std::chrono::duration<double>(t2 - t1).count());
+    }
+  }
+  double si = 0, sg = 0; for (double v : isect_s) si += v; for (double v : gather_s) sg += v;
+  double chk = 0; for (double v : sink) chk += v;
+  printf("{\"cmd\": \"bench\", \"rays\": %u, \"queries\": %u, \"photons\": %zu, \"k\": %d, \"threads\": %d, \"steps\": %d, "
+         "\"kd_build_seconds\": %.6f, \"isect_seconds_per_step\": %.6f, \"gather_seconds_per_step\": %.6f, \"checksum\": %.6g}\n",
+         nr, nq, ph.size(), k, threads, steps, build_sec, si / steps, sg / steps, chk);
+  return 0;
+}
+
 int main(int argc, char **argv) {
   if (argc < 2) die("usage: ref_harness <dump_scene|camrays|isect|photons|gather|shade> ...");
   std::string c = argv[1];
   if (c == "dump_scene") return cmd_dump_scene(argc, argv);
   if (c == "camrays") return cmd_camrays(argc, argv);
   if (c == "isect") return cmd_isect(argc, argv);
+  if (c == "photons") return cmd_photons(argc, argv);
+  if (c == "gather") return cmd_gather(argc, argv);
+  if (c == "bench") return cmd_bench(argc, argv);
   die("unknown command");
   return 2;
 }

@@ -98,3 +98,93 @@ class Oracle:
         rc = self.lib.oracle_intersect(scene, rays.ctypes.data, len(rays), hits.ctypes.data, threads)
         assert rc == 0
         return hits
+
+
+# ---------------------------------------------------------------------------------------------- photon maps
+GI_PHOTON = np.dtype([("position", "<f8", 3), ("rgbe", "u1", 4), ("direction", "<u2"), ("pad", "<u2")])
+GI_QUERY = np.dtype([("p", "<f8", 3), ("n", "<f8", 3), ("bounce", "<f8", 3), ("cos_theta", "<f8"), ("kd", "<f8", 3),
+                     ("ks", "<f8", 3), ("shininess", "<f8")])
+assert GI_PHOTON.itemsize == 32 and GI_QUERY.itemsize == 136
+PMAP_MAGIC = 0x4D504947
+QRY_MAGIC = 0x59525147
+
+
+def read_photons(path):
+    with open(path, "rb") as f:
+        hdr = np.frombuffer(f.read(8), dtype="<u4")
+        assert hdr[0] == PMAP_MAGIC
+        n = int(np.frombuffer(f.read(8), dtype="<u8")[0])
+        return np.frombuffer(f.read(32 * n), dtype=GI_PHOTON).copy()
+
+
+def write_photons(path, ph):
+    ph = np.ascontiguousarray(ph, dtype=GI_PHOTON)
+    with open(path, "wb") as f:
+        f.write(np.array([PMAP_MAGIC, 1], dtype="<u4").tobytes())
+        f.write(np.array([len(ph)], dtype="<u8").tobytes())
+        f.write(ph.tobytes())
+
+
+def write_queries(path, q):
+    q = np.ascontiguousarray(q, dtype=GI_QUERY)
+    with open(path, "wb") as f:
+        f.write(np.array([QRY_MAGIC, len(q)], dtype="<u4").tobytes())
+        f.write(q.tobytes())
+
+
+def read_ref_gather(path):
+    """output of `ref_harness gather`: (count[n], rgb[n,3], idx[n,k])"""
+    with open(path, "rb") as f:
+        hdr = np.frombuffer(f.read(16), dtype="<u4")
+        assert hdr[0] == 0x54414747
+        n, k = int(hdr[1]), int(hdr[2])
+        rec = np.frombuffer(f.read(32 * n), dtype=np.dtype([("count", "<i4"), ("pad", "<i4"), ("rgb", "<f8", 3)]))
+        idx = np.frombuffer(f.read(4 * n * k), dtype="<i4").reshape(n, k)
+        return rec["count"].copy(), rec["rgb"].copy(), idx.copy()
+
+
+def queries_from_hits(rays, hits, kd=(0.5, 0.6, 0.7), ks=(0.2, 0.1, 0.3), shininess=10.0):
+    """gather queries at hit points, set up as RayTrace / CausticIllumination do (raytracer.cpp:138-149,174-190):
+    view = ray direction, cos_theta = n . (-view), exact_bounce = mirror direction of the view ray"""
+    m = hits["hit"] == 1
+    d = rays[m, 3:6]; n = hits["n"][m]
+    cos_theta = -(n * d).sum(1)
+    q = np.zeros(m.sum(), dtype=GI_QUERY)
+    q["p"] = hits["p"][m]; q["n"] = n
+    q["bounce"] = d + 2.0 * cos_theta[:, None] * n
+    q["cos_theta"] = cos_theta
+    q["kd"] = kd; q["ks"] = ks; q["shininess"] = shininess
+    return q
+
+
+def synthetic_photons(n, seed, lo=(-1, -1, -1), hi=(1, 1, 1)):
+    """photons uniform on the six faces of a box, random power / direction codes"""
+    rng = np.random.default_rng(seed)
+    lo = np.asarray(lo, dtype=np.float64); hi = np.asarray(hi, dtype=np.float64)
+    p = lo + rng.random((n, 3)) * (hi - lo)
+    face = rng.integers(0, 6, n)
+    ax = face % 3
+    p[np.arange(n), ax] = np.where(face < 3, lo[ax], hi[ax])
+    ph = np.zeros(n, dtype=GI_PHOTON)
+    ph["position"] = p
+    ph["rgbe"][:, :3] = rng.integers(0, 256, (n, 3)); ph["rgbe"][:, 3] = rng.integers(110, 130, n)
+    ph["direction"] = rng.integers(0, 65536, n)
+    return ph
+
+
+def _oracle_gather(self, photons, queries, k, r, filter=0, fa=0.918, fb=1.953, fk=1.0, threads=8, want_idx=True):
+    photons = np.ascontiguousarray(photons, dtype=GI_PHOTON); queries = np.ascontiguousarray(queries, dtype=GI_QUERY)
+    nq = len(queries)
+    idx = np.full((nq, k), -1, dtype=np.int32) if want_idx else None
+    cnt = np.zeros(nq, dtype=np.int32); rgb = np.zeros((nq, 3), dtype=np.float64)
+    f = self.lib.oracle_gather
+    f.argtypes = [ctypes.c_void_p, ctypes.c_uint64, ctypes.c_void_p, ctypes.c_uint64, ctypes.c_int, ctypes.c_double,
+                  ctypes.c_int, ctypes.c_double, ctypes.c_double, ctypes.c_double, ctypes.c_void_p, ctypes.c_void_p,
+                  ctypes.c_void_p, ctypes.c_int]
+    rc = f(photons.ctypes.data, len(photons), queries.ctypes.data, nq, k, r, filter, fa, fb, fk,
+           idx.ctypes.data if want_idx else None, cnt.ctypes.data, rgb.ctypes.data, threads)
+    assert rc == 0
+    return idx, cnt, rgb
+
+
+Oracle.gather = _oracle_gather

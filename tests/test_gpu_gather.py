@@ -1,0 +1,119 @@
+"""GPU suite (pytest -m gpu): gi_build_maps + gi_gather_batch through the C ABI against (1) the reference's own
+R3Kdtree / EstimateRadiance outputs on reference-traced cornell maps (golden fixture), (2) the brute-force oracle on
+synthetic maps, plus size-independent properties at large sizes.  Bar (BASELINE.json): bit-exact kNN index sets (ties
+by lower index); radiance within 1e-4 relative (we assert 1e-9: only the summation order differs)."""
+import os
+
+import numpy as np
+import pytest
+
+import gi_b200
+from gi_testlib import ROOT, read_photons, synthetic_photons, GI_QUERY
+
+pytestmark = pytest.mark.gpu
+GOLDEN = os.path.join(ROOT, "tests", "golden")
+
+
+def surface_queries(n, seed, kd=(0.5, 0.6, 0.7), ks=(0.2, 0.1, 0.3), shin=10.0):
+    rng = np.random.default_rng(seed)
+    ph = synthetic_photons(n, seed + 1000)
+    q = np.zeros(n, dtype=GI_QUERY)
+    q["p"] = ph["position"] + rng.normal(scale=1e-3, size=(n, 3))
+    nn = rng.normal(size=(n, 3)); nn /= np.linalg.norm(nn, axis=1)[:, None]
+    b = rng.normal(size=(n, 3)); b /= np.linalg.norm(b, axis=1)[:, None]
+    q["n"] = nn; q["bounce"] = b; q["cos_theta"] = rng.uniform(-1, 1, n)
+    q["kd"] = kd; q["ks"] = ks; q["shininess"] = shin
+    return q
+
+
+def check(ref, got, rtol=1e-9):
+    ridx, rcnt, rrgb = ref; idx, cnt, rgb = got
+    assert np.array_equal(rcnt, cnt)
+    bad = np.nonzero((ridx != idx).any(1))[0]
+    assert len(bad) == 0, f"kNN sets differ for queries {bad[:5]}"
+    scale = np.abs(rrgb).max(axis=1, keepdims=True)
+    assert (np.abs(rgb - rrgb) <= rtol * scale + 1e-300).all()
+
+
+@pytest.mark.parametrize("mp,k", [("caustic", 225), ("global", 50), ("caustic", 40)])
+@pytest.mark.parametrize("filt", [0, 1, 2])
+def test_cuda_gather_matches_reference_fixture(gpu_ctx, mp, k, filt):
+    fx = np.load(os.path.join(GOLDEN, "cornell.gather.npz"))
+    which = gi_b200.GI_MAP_CAUSTIC if mp == "caustic" else gi_b200.GI_MAP_GLOBAL
+    gpu_ctx.load_photons_file(which, os.path.join(GOLDEN, f"cornell.{mp}.gipm"))
+    gpu_ctx.build_maps()
+    key = f"{mp}_{k}_{filt}"
+    got = gpu_ctx.gather(which, fx["queries"], k, float(fx[key + "_r"][0]), filt)
+    check((fx[f"{mp}_{k}_idx"], fx[key + "_count"], fx[key + "_rgb"]), got)
+
+
+@pytest.mark.parametrize("n,k,r", [(1, 1, 0.5), (2, 5, 3.0), (63, 10, 0.8), (64, 64, 4.0), (1000, 50, 0.3), (4097, 225, 0.4),
+                                   (100000, 225, 0.05), (100000, 512, 0.2), (300000, 50, 0.02), (50000, 1, 0.1)])
+def test_cuda_gather_matches_oracle_on_synthetic_maps(gpu_ctx, oracle, n, k, r):
+    ph = synthetic_photons(n, seed=n + k)
+    q = surface_queries(600, seed=k)
+    gpu_ctx.load_photons(gi_b200.GI_MAP_CAUSTIC, ph)
+    gpu_ctx.build_maps()
+    for filt in (0, 1, 2):
+        check(oracle.gather(ph, q, k, r, filt, threads=os.cpu_count() or 8), gpu_ctx.gather(gi_b200.GI_MAP_CAUSTIC, q, k, r, filt))
+
+
+def test_ties_duplicates_and_empty_map(gpu_ctx, oracle):
+    q = surface_queries(200, seed=3)
+    # empty map: nothing found, zero radiance
+    gpu_ctx.load_photons(gi_b200.GI_MAP_GLOBAL, synthetic_photons(0, 1))
+    gpu_ctx.build_maps()
+    idx, cnt, rgb = gpu_ctx.gather(gi_b200.GI_MAP_GLOBAL, q, 20, 1.0)
+    assert (cnt == 0).all() and (idx == -1).all() and (rgb == 0).all()
+    # every photon four times (exact distance ties everywhere) + a cluster of identical positions
+    base = synthetic_photons(3000, 5)
+    ph = np.concatenate([base, base, base, base])
+    ph["position"][100:400] = ph["position"][100]
+    gpu_ctx.load_photons(gi_b200.GI_MAP_GLOBAL, ph)
+    gpu_ctx.build_maps()
+    for k in (1, 7, 50, 300):
+        check(oracle.gather(ph, q, k, 0.5, 0), gpu_ctx.gather(gi_b200.GI_MAP_GLOBAL, q, k, 0.5, 0))
+    # query exactly on photons (d^2 = 0) and far outside
+    q2 = q.copy(); q2["p"][:100] = ph["position"][:100]; q2["p"][100:] += 50.0
+    check(oracle.gather(ph, q2, 30, 0.3, 0), gpu_ctx.gather(gi_b200.GI_MAP_GLOBAL, q2, 30, 0.3, 0))
+
+
+def test_photon_roundtrip_and_errors(gpu_ctx, tmp_path):
+    ph = synthetic_photons(5000, 8)
+    gpu_ctx.load_photons(gi_b200.GI_MAP_CAUSTIC, ph)
+    assert gpu_ctx.photon_count(gi_b200.GI_MAP_CAUSTIC) == 5000
+    assert gpu_ctx.get_photons(gi_b200.GI_MAP_CAUSTIC).tobytes() == ph.tobytes()
+    p = str(tmp_path / "m.gipm")
+    gpu_ctx.dump_photons_file(gi_b200.GI_MAP_CAUSTIC, p)
+    assert read_photons(p).tobytes() == ph.tobytes()
+    with pytest.raises(gi_b200.GiError, match="not built"):
+        gpu_ctx.gather(gi_b200.GI_MAP_CAUSTIC, surface_queries(4, 1), 5, 0.1)
+    gpu_ctx.build_maps()
+    with pytest.raises(gi_b200.GiError, match="estimate size"):
+        gpu_ctx.gather(gi_b200.GI_MAP_CAUSTIC, surface_queries(4, 1), 513, 0.1)
+
+
+def test_full_size_properties(gpu_ctx):
+    """10^7 photons (BASELINE default caustic map size), k = 225: too big for the brute-force oracle, so check
+    size-independent properties: counts, sortedness, and that every reported photon lies within r and no unreported
+    photon of a random sample is closer than the reported k-th."""
+    n = 10_000_000
+    ph = synthetic_photons(n, seed=77)
+    gpu_ctx.load_photons(gi_b200.GI_MAP_CAUSTIC, ph)
+    gpu_ctx.build_maps()
+    q = surface_queries(2000, seed=12)
+    k, r = 225, 0.02
+    idx, cnt, rgb = gpu_ctx.gather(gi_b200.GI_MAP_CAUSTIC, q, k, r, 0)
+    assert (cnt == k).sum() > 1500
+    rng = np.random.default_rng(0)
+    for qi in rng.choice(len(q), 40, replace=False):
+        ids = idx[qi][:cnt[qi]]
+        assert (np.diff(ids) > 0).all()
+        d2 = ((ph["position"] - q["p"][qi]) ** 2)
+        d2 = (d2[:, 0] + d2[:, 1]) + d2[:, 2]
+        inside = np.nonzero(d2 <= r * r)[0]
+        if len(inside) <= k:
+            assert np.array_equal(np.sort(inside), ids)
+        else:
+            order = inside[np.lexsort((inside, d2[inside]))][:k]
+            assert np.array_equal(np.sort(order), ids)
