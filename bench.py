@@ -311,7 +311,9 @@ def run_ours(args):
     ctx = gi_b200.Context(local_rank)
     scene = gi_b200.HostScene(os.path.join(GOLDEN, SCENE + ".gisc"))
     ctx.upload_scene(scene)
-    stream = torch.cuda.current_stream().cuda_stream
+    work_stream = torch.cuda.Stream(device=dev)          # a real (non-default) stream: kernels and events both go here
+    torch.cuda.set_stream(work_stream)
+    stream = work_stream.cuda_stream
     W, H = args.width << args.aa, args.height << args.aa
     n_rays = W * H
     # weak scaling: every rank renders its own full frame (sub-pixel offset per rank so the inputs differ)

@@ -156,7 +156,7 @@ int gi_gather_batch_device(GiContext *ctx, int map, const GiGatherQuery *d_queri
   ga.k = k; ga.cap = pow2ceil(2 * k) < 256 ? 256 : pow2ceil(2 * k); ga.filter = filter; ga.r2 = r * r;
   ga.fa = params ? params->filter_const_a : 0.918; ga.fb = params ? params->filter_const_b : 1.953;
   ga.fk = params ? params->filter_const_k : 1.0;
-  cudaStream_t st = stream ? (cudaStream_t)stream : ctx->stream;
+  cudaStream_t st = (cudaStream_t)stream;      // NULL = the CUDA default stream, as documented
   GI_CUDA(launch_gather(ctx, m.dev, lut, d_queries, n, ga, d_idx, d_count, d_rgb, st));
   return 0;
 }

@@ -138,7 +138,7 @@ int gi_intersect_batch_device(GiContext *ctx, const GiRay *d_rays, uint64_t n, G
   if (!ctx || !ctx->has_scene) { set_error("gi_intersect_batch: no scene uploaded"); return 1; }
   if (n == 0) return 0;
   GI_CUDA(cudaSetDevice(ctx->device));
-  cudaStream_t st = stream ? (cudaStream_t)stream : ctx->stream;
+  cudaStream_t st = (cudaStream_t)stream;      // NULL = the CUDA default stream, as documented
   const int block = 128;
   uint64_t want = (n + block - 1) / block;
   uint64_t cap = (uint64_t)ctx->sm_count * 64;         // grid-stride beyond 64 CTAs per SM

@@ -17,7 +17,8 @@
 //   * Candidates (d^2, slot, photon index) are appended to a per-warp buffer in shared memory with ballot/popc.
 //     When the buffer runs full it is cut back with a 256-bin histogram of d^2 / bound (photons on a surface are
 //     uniform in d^2, so the boundary bin holds ~cap/256 candidates): everything up to the bin that contains the
-//     k-th candidate is kept and the search bound shrinks to the largest kept d^2.  Only the last cut is exact.
+//     k-th candidate is kept whole, the few candidates inside that bin are ranked by shuffles, and the search bound
+//     shrinks to the exact k-th smallest d^2.
 #include <cuda_runtime.h>
 #include <math.h>
 #include <stdint.h>
@@ -57,40 +58,22 @@ __device__ void bitonic_sort(WarpBuf &b, int lane) {
     }
 }
 
-// exact: keep the k smallest by (d2, orig); once k are held the bound becomes the largest kept d2
-__device__ void exact_select(WarpBuf &b, int &count, double &bound, int k, int lane) {
-  if (count < k) return;
-  if (count - k <= 16) {
-    while (count > k) {                                   // drop the lexicographic maximum
-      double md = -1.0; uint32_t mo = 0; int mi = -1;
-      for (int i = lane; i < count; i += 32) {
-        const double d = b.d2[i]; const uint32_t o = b.orig[i];
-        if (mi < 0 || lex_less(md, mo, d, o)) { md = d; mo = o; mi = i; }
-      }
-      for (int s = 16; s > 0; s >>= 1) {
-        const double od = __shfl_xor_sync(FULL, md, s); const uint32_t oo = __shfl_xor_sync(FULL, mo, s);
-        const int oi = __shfl_xor_sync(FULL, mi, s);
-        if (oi >= 0 && (mi < 0 || lex_less(md, mo, od, oo))) { md = od; mo = oo; mi = oi; }
-      }
-      if (lane == 0) { b.d2[mi] = b.d2[count - 1]; b.slot[mi] = b.slot[count - 1]; b.orig[mi] = b.orig[count - 1]; }
-      count--;
-      __syncwarp();
-    }
-  } else {
-    for (int i = count + lane; i < b.cap; i += 32) { b.d2[i] = INFINITY; b.orig[i] = 0xffffffffu; b.slot[i] = 0; }
-    __syncwarp();
-    bitonic_sort(b, lane);
-    count = k;
-  }
-  double mx = 0.0;
-  for (int i = lane; i < count; i += 32) mx = fmax(mx, b.d2[i]);
-  for (int s = 16; s > 0; s >>= 1) mx = fmax(mx, __shfl_xor_sync(FULL, mx, s));
-  bound = fmin(bound, mx);
+// slow exact path (heavy ties only): full sort, keep the first k
+__device__ void sort_select(WarpBuf &b, int &count, double &bound, int k, int lane) {
+  for (int i = count + lane; i < b.cap; i += 32) { b.d2[i] = INFINITY; b.orig[i] = 0xffffffffu; b.slot[i] = 0; }
+  __syncwarp();
+  bitonic_sort(b, lane);
+  count = k;
+  bound = fmin(bound, b.d2[k - 1]);
+  __syncwarp();
 }
 
-// approximate cut (see file header); falls back to exact_select when the histogram cannot make enough room
-__device__ void compact(WarpBuf &b, int &count, double &bound, int k, int lane) {
-  if (!(bound > 0.0)) { exact_select(b, count, bound, k, lane); return; }
+// Exact cut of the candidate buffer to the k smallest by (d2, orig).  Requires count > k.
+// A 256-bin histogram of d2 / bound locates the bin B that holds the k-th candidate; bins below B are kept whole,
+// and inside B (a handful of candidates, since surface photons are uniform in d2) each lane ranks one candidate
+// against the others by shuffles.  The bound becomes the largest kept d2.
+__device__ void cut(WarpBuf &b, int &count, double &bound, int k, int lane) {
+  if (!(bound > 0.0)) { sort_select(b, count, bound, k, lane); return; }
   for (int i = lane; i < 256; i += 32) b.hist[i] = 0;
   __syncwarp();
   const double scale = 256.0 / bound;
@@ -106,9 +89,36 @@ __device__ void compact(WarpBuf &b, int &count, double &bound, int k, int lane) 
   const uint32_t excl = incl - s;
   const unsigned crossing = __ballot_sync(FULL, incl >= (uint32_t)k);
   const int owner = __ffs(crossing) - 1;                  // count > k  =>  some lane crosses
-  int B = 255;
-  if (lane == owner) { uint32_t c = excl; for (int j = 0; j < 8; j++) { c += h[j]; if (c >= (uint32_t)k) { B = lane * 8 + j; break; } } }
-  B = __shfl_sync(FULL, B, owner);
+  int B = 255, below = 0, m = 0;
+  if (lane == owner) {
+    uint32_t c = excl;
+    for (int j = 0; j < 8; j++) { if (c + h[j] >= (uint32_t)k) { B = lane * 8 + j; below = (int)c; m = (int)h[j]; break; } c += h[j]; }
+  }
+  B = __shfl_sync(FULL, B, owner); below = __shfl_sync(FULL, below, owner); m = __shfl_sync(FULL, m, owner);
+  const int need = k - below;                             // candidates to keep from bin B, 1 <= need <= m
+  __syncwarp();
+  if (need < m) {
+    if (m > 32) { sort_select(b, count, bound, k, lane); return; }
+    int c = 0;                                            // list the members of bin B in hist[0..m)
+    for (int base = 0; base < count; base += 32) {
+      const int i = base + lane;
+      bool inb = false;
+      if (i < count) { int bin = (int)(b.d2[i] * scale); bin = bin > 255 ? 255 : bin; inb = bin == B; }
+      const unsigned mk = __ballot_sync(FULL, inb);
+      if (inb) b.hist[c + __popc(mk & ((1u << lane) - 1u))] = (uint32_t)i;
+      c += __popc(mk);
+    }
+    __syncwarp();
+    double md = INFINITY; uint32_t mo = 0xffffffffu; int mi = -1;
+    if (lane < m) { mi = (int)b.hist[lane]; md = b.d2[mi]; mo = b.orig[mi]; }
+    int rank = 0;
+    for (int l = 0; l < m; l++) {
+      const double od = __shfl_sync(FULL, md, l); const uint32_t oo = __shfl_sync(FULL, mo, l);
+      rank += lex_less(od, oo, md, mo) ? 1 : 0;
+    }
+    if (lane < m && rank >= need) b.d2[mi] = -1.0;        // dropped
+    __syncwarp();
+  }
   int newcount = 0; double mx = 0.0;
   for (int base = 0; base < count; base += 32) {
     const int i = base + lane;
@@ -116,18 +126,27 @@ __device__ void compact(WarpBuf &b, int &count, double &bound, int k, int lane) 
     if (i < count) {
       d = b.d2[i]; sl = b.slot[i]; og = b.orig[i];
       int bin = (int)(d * scale); bin = bin > 255 ? 255 : bin;
-      keep = bin <= B;
+      keep = d >= 0.0 && bin <= B;
     }
-    const unsigned m = __ballot_sync(FULL, keep);
-    const int pos = newcount + __popc(m & ((1u << lane) - 1u));
+    const unsigned mk = __ballot_sync(FULL, keep);
+    const int pos = newcount + __popc(mk & ((1u << lane) - 1u));
     __syncwarp();
     if (keep) { b.d2[pos] = d; b.slot[pos] = sl; b.orig[pos] = og; mx = fmax(mx, d); }
-    newcount += __popc(m);
+    newcount += __popc(mk);
     __syncwarp();
   }
   for (int o = 16; o > 0; o >>= 1) mx = fmax(mx, __shfl_xor_sync(FULL, mx, o));
   count = newcount; bound = fmin(bound, mx);
-  if (count > b.cap - 64) exact_select(b, count, bound, k, lane);
+}
+
+// after the traversal: exactly the k nearest (or everything found, if fewer); bound = largest kept d2 when k are held
+__device__ void finish(WarpBuf &b, int &count, double &bound, int k, int lane) {
+  if (count > k) { cut(b, count, bound, k, lane); return; }
+  if (count < k) return;
+  double mx = 0.0;
+  for (int i = lane; i < count; i += 32) mx = fmax(mx, b.d2[i]);
+  for (int s = 16; s > 0; s >>= 1) mx = fmax(mx, __shfl_xor_sync(FULL, mx, s));
+  bound = fmin(bound, mx);
 }
 
 __device__ __forceinline__ void append(WarpBuf &b, const PhotonMapDev &m, int &count, double &bound, int k, int lane,
@@ -138,7 +157,7 @@ __device__ __forceinline__ void append(WarpBuf &b, const PhotonMapDev &m, int &c
   if (pred) { b.d2[pos] = d2; b.slot[pos] = slot; b.orig[pos] = m.orig[slot]; }
   count += __popc(mask);
   __syncwarp();
-  if (count > b.cap - 32) compact(b, count, bound, k, lane);
+  if (count > b.cap - 32) cut(b, count, bound, k, lane);
 }
 
 __device__ __forceinline__ double dist2(const PhotonMapDev &m, uint64_t slot, double qx, double qy, double qz) {
@@ -146,7 +165,7 @@ __device__ __forceinline__ double dist2(const PhotonMapDev &m, uint64_t slot, do
   return (dx * dx) + (dy * dy) + (dz * dz);
 }
 
-__global__ void __launch_bounds__(GI_GATHER_WARPS * 32)
+__global__ void __launch_bounds__(GI_GATHER_WARPS * 32, 3)
 gather_kernel(PhotonMapDev m, const double *__restrict__ lut, const GiGatherQuery *__restrict__ queries, uint64_t nq,
               GatherArgs ga, int32_t *idx_out, int32_t *count_out, double *rgb_out) {
   extern __shared__ double smem[];
@@ -161,7 +180,12 @@ gather_kernel(PhotonMapDev m, const double *__restrict__ lut, const GiGatherQuer
   const uint64_t n = m.n;
   const int tile_level = m.levels - GI_TILE_LEVELS;        // nodes at this level or deeper are handled as tiles
   const uint64_t warps_total = (uint64_t)gridDim.x * GI_GATHER_WARPS;
-  for (uint64_t qi = (uint64_t)blockIdx.x * GI_GATHER_WARPS + warp; qi < nq; qi += warps_total) {
+  const uint64_t nchunks = (nq + GI_GATHER_CHUNK - 1) / GI_GATHER_CHUNK;
+  // Search radius carried from one query to the next: consecutive queries of a chunk are neighbouring pixels, so the
+  // previous k-th distance (x2 in area) is tried first and the full radius only if fewer than k photons are inside.
+  double guess = ga.r2;
+  for (uint64_t chunk = (uint64_t)blockIdx.x * GI_GATHER_WARPS + warp; chunk < nchunks; chunk += warps_total)
+  for (uint64_t qi = chunk * GI_GATHER_CHUNK; qi < nq && qi < (chunk + 1) * GI_GATHER_CHUNK; qi++) {
     // ---- query record: 17 doubles, one per lane, broadcast by shuffle
     const double *qp = (const double *)(queries + qi);
     const double mine = lane < 17 ? qp[lane] : 0.0;
@@ -169,13 +193,24 @@ gather_kernel(PhotonMapDev m, const double *__restrict__ lut, const GiGatherQuer
     int count = 0;
     double bound = ga.r2;
     if (n > 0) {
-      uint32_t st_node[40]; double st_d[40]; int sp = 0;
-      st_node[0] = 0; st_d[0] = 0.0; sp = 1;
-      while (sp > 0) {
-        --sp;
-        uint64_t s = st_node[sp];
-        if (st_d[sp] > bound) continue;
+      double init = fmin(ga.r2, guess);
+      while (true) {
+        count = 0; bound = init;
+        // traversal stack spread over the lanes (entry i lives in lane i): node, squared distance from the query to
+        // the node's cell, and the per-axis offsets it is made of (Arya & Mount incremental distance)
+        uint32_t sk_node = 0; double sk_rd = 0.0, sk_ox = 0.0, sk_oy = 0.0, sk_oz = 0.0;
+        int sp = 0;
+        uint64_t s = 0; double rd = 0.0, ox = 0.0, oy = 0.0, oz = 0.0;
+        bool have = true;
         while (true) {
+          if (!have) {
+            if (sp == 0) break;
+            --sp;
+            s = __shfl_sync(FULL, sk_node, sp); rd = __shfl_sync(FULL, sk_rd, sp);
+            ox = __shfl_sync(FULL, sk_ox, sp); oy = __shfl_sync(FULL, sk_oy, sp); oz = __shfl_sync(FULL, sk_oz, sp);
+            if (rd > bound) continue;
+          }
+          have = false;
           const int lvl = 63 - __clzll((long long)(s + 1));
           if (lvl >= tile_level) {
             // ---- tile: subtree of s, relative depth j occupies slots (s << j) + e, e in [2^j - 1, 2^(j+1) - 1)
@@ -190,24 +225,41 @@ gather_kernel(PhotonMapDev m, const double *__restrict__ lut, const GiGatherQuer
               }
               append(b, m, count, bound, k, lane, pred, d2, (uint32_t)slot);
             }
-            break;
+            continue;
           }
-          // ---- interior node: its own photon, then near child first
+          // ---- interior node: its own photon (same value in every lane: uniform branch), then near child first
           const double d2 = dist2(m, s, qx, qy, qz);
-          append(b, m, count, bound, k, lane, lane == 0 && d2 <= bound, d2, (uint32_t)s);
+          if (d2 <= bound) {
+            if (lane == 0) { b.d2[count] = d2; b.slot[count] = (uint32_t)s; b.orig[count] = m.orig[s]; }
+            count++;
+            __syncwarp();
+            if (count > b.cap - 32) cut(b, count, bound, k, lane);
+          }
           const uint2 nd = m.node[s];
-          const float sf = __uint_as_float(nd.x);
+          const double sf = (double)__uint_as_float(nd.x);
+          // photons left of the split have float(c) <= sf, right of it float(c) >= sf: widen by one float ulp
+          const double wide = fabs(sf) * 1.1920929e-7 + 1.0e-44;
           const double qa = nd.y == 0 ? qx : (nd.y == 1 ? qy : qz);
+          const double oa = nd.y == 0 ? ox : (nd.y == 1 ? oy : oz);
           uint64_t near, far; double fd;
-          if (qa < (double)sf) { near = 2 * s + 1; far = 2 * s + 2; fd = (double)nextafterf(sf, -INFINITY) - qa; }
-          else { near = 2 * s + 2; far = 2 * s + 1; fd = qa - (double)nextafterf(sf, INFINITY); }
-          fd = fd > 0.0 ? fd : 0.0;
-          const double fd2 = fd * fd;
-          if (far < n && fd2 <= bound) { st_node[sp] = (uint32_t)far; st_d[sp] = fd2; sp++; }
-          if (near < n) s = near; else break;
+          if (qa < sf) { near = 2 * s + 1; far = 2 * s + 2; fd = (sf - wide) - qa; }
+          else { near = 2 * s + 2; far = 2 * s + 1; fd = qa - (sf + wide); }
+          fd = fmax(fd, oa);                                            // never closer than the parent cell
+          const double frd = (rd - oa * oa + fd * fd) * 0.99999999999999;   // rounding must not over-estimate
+          if (far < n && frd <= bound) {
+            if (lane == sp) {
+              sk_node = (uint32_t)far; sk_rd = frd;
+              sk_ox = nd.y == 0 ? fd : ox; sk_oy = nd.y == 1 ? fd : oy; sk_oz = nd.y == 2 ? fd : oz;
+            }
+            sp++;
+          }
+          if (near < n) { s = near; have = true; }
         }
+        finish(b, count, bound, k, lane);
+        if (count >= k || init >= ga.r2) break;
+        init = ga.r2;                                                   // the guess was too small: full radius
       }
-      exact_select(b, count, bound, k, lane);
+      guess = count >= k ? bound * 2.0 : ga.r2;
     }
     // ---- radiance estimate, photon_utils.cpp:80-161
     const int found = count;
@@ -222,7 +274,7 @@ gather_kernel(PhotonMapDev m, const double *__restrict__ lut, const GiGatherQuer
       const bool has_spec = ks[0] != 0.0 || ks[1] != 0.0 || ks[2] != 0.0;
       double max_d2 = 1.0e-6;                                                   // RN_EPSILON
       if (found < k) max_d2 = ga.r2;
-      else max_d2 = fmax(max_d2, bound);                                        // bound == max kept d^2 after exact_select
+      else max_d2 = fmax(max_d2, bound);                                        // bound == max kept d^2 after finish()
       double c1 = 1.0, c2 = 1.0, total_w = 0.0;
       if (ga.filter == GI_FILTER_CONE) c1 = 1.0 / (ga.fk * sqrt(max_d2));
       else if (ga.filter == GI_FILTER_GAUSS) { c1 = exp(-ga.fb); c2 = 1.0 / (2.0 * max_d2); }

@@ -7,6 +7,7 @@
 struct GiContext;
 namespace gi {
 #define GI_GATHER_WARPS 8          /* warps (= concurrent queries) per CTA */
+#define GI_GATHER_CHUNK 16         /* consecutive queries handled by one warp (coherent: neighbouring pixels) */
 struct GatherArgs {
   int k;                           /* estimate size (<= GI_MAX_K) */
   int cap;                         /* candidate slots per warp: power of two, >= max(256, 2k) */

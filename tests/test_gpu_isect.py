@@ -62,14 +62,19 @@ def test_cuda_matches_oracle_on_random_batches(gpu_ctx, oracle, name):
     assert_same_hits(ref2, gpu_ctx.intersect(sec), name + " secondary", check_prim=True)
 
 
-def test_empty_and_degenerate_batches(gpu_ctx):
-    gpu_ctx.upload_scene(gi_b200.HostScene(os.path.join(GOLDEN, "cornell.gisc")))
+def test_empty_and_degenerate_batches(gpu_ctx, oracle):
+    gisc = os.path.join(GOLDEN, "cornell.gisc")
+    gpu_ctx.upload_scene(gi_b200.HostScene(gisc))
     assert len(gpu_ctx.intersect(np.zeros((0, 6)))) == 0
-    # a ray pointing away from everything, and axis-parallel rays (zero direction components)
-    rays = np.array([[0, 0, 50, 0, 0, 1], [0, 0, 5, 0, 0, -1], [0.3, -0.2, 5, 0, 0, -1]], dtype=np.float64)
+    # a ray pointing away from everything, and axis-parallel rays (zero direction components, +-0)
+    rays = np.array([[0, 0, 50, 0, 0, 1], [0, 0, 5, 0, 0, -1], [0.3, -0.2, 5, 0, 0, -1], [0.3, 0.2, 5, -0.0, 0, -1],
+                     [0, 0.5, 0.5, 1, 0, 0], [0, 0.5, 0.5, 0, -1, 0], [0, 0.5, 0.5, 0, 1, -0.0]], dtype=np.float64)
     got = gpu_ctx.intersect(rays)
     assert got["hit"][0] == 0 and got["shape"][0] == -1 and got["t"][0] == 0
-    assert got["hit"][1] == 1 and got["hit"][2] == 1
+    assert got["hit"][1] == 1
+    h = oracle.load_scene(gisc)
+    assert_same_hits(oracle.intersect(h, rays), got, "axis-parallel", check_prim=True)
+    oracle.free_scene(h)
 
 
 def test_requires_a_scene():
