@@ -11,8 +11,11 @@
 //      size is known from n alone);
 //   2. the photon at offset `size of the left child subtree` inside its segment becomes node s; photons before it
 //      move to subtree 2s+1, after it to 2s+2;
-//   3. child boxes = parent box cut at the split; the split axis of a node is the longest axis of its box, as in
-//      the reference (R3Kdtree.cpp:1640, R3Box::LongestAxis R3Box.cpp:258-274).
+//   3. the split axis of a subtree is the longest axis of the TIGHT bounding box of its photons (segmented min/max
+//      with warp-aggregated atomics).  The reference splits on the longest axis of the inherited node box
+//      (R3Kdtree.cpp:1640, R3Box::LongestAxis R3Box.cpp:258-274); for photons lying on planes that rule keeps
+//      cutting along the plane normal, where every coordinate is equal and nothing is separated.  The choice of axis
+//      does not change any query result, only how much of the tree a query has to visit.
 // Splits are float32 (monotone rounding of the FP64 coordinate); the search widens them by one ulp, distances stay
 // FP64, so the k-nearest SET is exact (see gather.cu).  Only photons not yet placed take part in a level's sort.
 #include <cub/device/device_radix_sort.cuh>
@@ -69,34 +72,50 @@ __device__ __forceinline__ int longest_axis(const float *b) {          // R3Box:
   return dy > dz ? 1 : 2;
 }
 
-__global__ void bbox_kernel(const GiPhoton *__restrict__ ph, uint64_t n, uint32_t *obox /* 6 ordered floats */) {
-  float lo[3] = {FLT_MAX, FLT_MAX, FLT_MAX}, hi[3] = {-FLT_MAX, -FLT_MAX, -FLT_MAX};
-  for (uint64_t i = (uint64_t)blockIdx.x * blockDim.x + threadIdx.x; i < n; i += (uint64_t)gridDim.x * blockDim.x)
-    for (int k = 0; k < 3; k++) {
-      const float c = (float)ph[i].position[k];
-      lo[k] = fminf(lo[k], c); hi[k] = fmaxf(hi[k], c);
-    }
-  for (int k = 0; k < 3; k++) {
-    for (int o = 16; o > 0; o >>= 1) {
-      lo[k] = fminf(lo[k], __shfl_xor_sync(0xffffffffu, lo[k], o));
-      hi[k] = fmaxf(hi[k], __shfl_xor_sync(0xffffffffu, hi[k], o));
-    }
-    if ((threadIdx.x & 31) == 0) {
-      atomicMin(&obox[k], float_to_ordered(lo[k]));
-      atomicMax(&obox[3 + k], float_to_ordered(hi[k]));
-    }
+__global__ void init_kernel(uint64_t n, uint64_t *keys, uint32_t *vals) {
+  const uint64_t i = (uint64_t)blockIdx.x * blockDim.x + threadIdx.x;
+  if (i < n) { keys[i] = 0; vals[i] = (uint32_t)i; }
+}
+
+// bounds[s] = {min x,y,z ; max x,y,z} as ordered uints, for the subtrees s of this level
+__global__ void reset_bounds_kernel(uint64_t n, int level, uint32_t *bounds) {
+  const uint64_t s = (((uint64_t)1 << level) - 1) + (uint64_t)blockIdx.x * blockDim.x + threadIdx.x;
+  if (s >= n || s >= ((uint64_t)2 << level) - 1) return;
+  for (int k = 0; k < 3; k++) { bounds[6 * s + k] = 0xffffffffu; bounds[6 * s + 3 + k] = 0u; }
+}
+
+__global__ void bounds_kernel(const GiPhoton *__restrict__ ph, uint64_t first, uint64_t n, int level,
+                              const uint64_t *__restrict__ keys, const uint32_t *__restrict__ vals, uint32_t *bounds) {
+  const uint64_t p = first + (uint64_t)blockIdx.x * blockDim.x + threadIdx.x;
+  const bool live = p < n;
+  uint64_t tag = live ? (keys[p] >> 32) : ~(uint64_t)0;
+  const bool active = live && level_of(tag) == level;
+  uint32_t lo[3] = {0xffffffffu, 0xffffffffu, 0xffffffffu}, hi[3] = {0u, 0u, 0u};
+  if (active) {
+    const GiPhoton &q = ph[vals[p]];
+    for (int k = 0; k < 3; k++) lo[k] = hi[k] = float_to_ordered((float)q.position[k]);
+  }
+  // whole warp inside one subtree (the common case on the upper levels): reduce, one lane does the atomics
+  const uint64_t tag0 = __shfl_sync(0xffffffffu, tag, 0);
+  if (__all_sync(0xffffffffu, active && tag == tag0)) {
+    for (int k = 0; k < 3; k++)
+      for (int o = 16; o > 0; o >>= 1) {
+        lo[k] = min(lo[k], __shfl_xor_sync(0xffffffffu, lo[k], o));
+        hi[k] = max(hi[k], __shfl_xor_sync(0xffffffffu, hi[k], o));
+      }
+    if ((threadIdx.x & 31) == 0)
+      for (int k = 0; k < 3; k++) { atomicMin(&bounds[6 * tag + k], lo[k]); atomicMax(&bounds[6 * tag + 3 + k], hi[k]); }
+  } else if (active) {
+    for (int k = 0; k < 3; k++) { atomicMin(&bounds[6 * tag + k], lo[k]); atomicMax(&bounds[6 * tag + 3 + k], hi[k]); }
   }
 }
 
-__global__ void init_kernel(uint64_t n, const uint32_t *__restrict__ obox, float *boxes, uint8_t *axis, uint64_t *keys,
-                            uint32_t *vals) {
-  const uint64_t i = (uint64_t)blockIdx.x * blockDim.x + threadIdx.x;
-  if (i == 0) {
-    float b[6];
-    for (int k = 0; k < 6; k++) { b[k] = ordered_to_float(obox[k]); boxes[k] = b[k]; }
-    axis[0] = (uint8_t)longest_axis(b);
-  }
-  if (i < n) { keys[i] = 0; vals[i] = (uint32_t)i; }
+__global__ void axis_kernel(uint64_t n, int level, const uint32_t *__restrict__ bounds, uint8_t *axis) {
+  const uint64_t s = (((uint64_t)1 << level) - 1) + (uint64_t)blockIdx.x * blockDim.x + threadIdx.x;
+  if (s >= n || s >= ((uint64_t)2 << level) - 1) return;
+  float b[6];
+  for (int k = 0; k < 6; k++) b[k] = ordered_to_float(bounds[6 * s + k]);
+  axis[s] = (uint8_t)longest_axis(b);
 }
 
 // key = tag << 32 | ordered float coordinate on the split axis of subtree `tag`
@@ -123,24 +142,6 @@ __global__ void assign_kernel(uint64_t first, uint64_t n, int L, int level, uint
   else { heap_photon[s] = vals[p]; split[s] = ordered_to_float((uint32_t)key); }
 }
 
-__global__ void child_box_kernel(uint64_t n, int level, const float *__restrict__ split, float *boxes, uint8_t *axis) {
-  const uint64_t s = (((uint64_t)1 << level) - 1) + (uint64_t)blockIdx.x * blockDim.x + threadIdx.x;
-  if (s >= n || s >= ((uint64_t)2 << level) - 1) return;
-  float b[6];
-  for (int k = 0; k < 6; k++) b[k] = boxes[6 * s + k];
-  const int ax = axis[s];
-  const float sp = split[s];
-  for (int c = 0; c < 2; c++) {
-    const uint64_t ch = 2 * s + 1 + c;
-    if (ch >= n) break;
-    float cb[6];
-    for (int k = 0; k < 6; k++) cb[k] = b[k];
-    if (c == 0) cb[3 + ax] = sp; else cb[ax] = sp;
-    for (int k = 0; k < 6; k++) boxes[6 * ch + k] = cb[k];
-    axis[ch] = (uint8_t)longest_axis(cb);
-  }
-}
-
 __global__ void finalize_kernel(const GiPhoton *__restrict__ ph, uint64_t n, const uint32_t *__restrict__ heap_photon,
                                 const float *__restrict__ split, const uint8_t *__restrict__ axis, double *px, double *py,
                                 double *pz, uint2 *node, uint2 *shade, uint32_t *orig) {
@@ -163,38 +164,35 @@ cudaError_t build_photon_map(GiContext *ctx, PhotonMapStore &m, uint64_t n) {
   const GiPhoton *ph = (const GiPhoton *)m.raw;
   int L = 0; while (((uint64_t)1 << L) <= n) L++;                       // floor(log2 n) + 1
   uint64_t *keys[2] = {nullptr, nullptr}; uint32_t *vals[2] = {nullptr, nullptr};
-  uint32_t *heap_photon = nullptr, *obox = nullptr; float *split = nullptr, *boxes = nullptr; uint8_t *axis = nullptr;
+  uint32_t *heap_photon = nullptr, *bounds = nullptr; float *split = nullptr; uint8_t *axis = nullptr;
   void *tmp = nullptr; size_t tmp_bytes = 0;
   double *px = nullptr, *py = nullptr, *pz = nullptr; uint2 *node = nullptr, *shade = nullptr; uint32_t *orig = nullptr;
   const int B = 256;
   const unsigned G = (unsigned)((n + B - 1) / B);
   int cur = 0;
   for (int k = 0; k < 2; k++) { CKB(cudaMalloc(&keys[k], 8 * n)); CKB(cudaMalloc(&vals[k], 4 * n)); }
-  CKB(cudaMalloc(&heap_photon, 4 * n)); CKB(cudaMalloc(&split, 4 * n)); CKB(cudaMalloc(&boxes, 24 * n));
-  CKB(cudaMalloc(&axis, n)); CKB(cudaMalloc(&obox, 24));
+  CKB(cudaMalloc(&heap_photon, 4 * n)); CKB(cudaMalloc(&split, 4 * n)); CKB(cudaMalloc(&bounds, 24 * n));
+  CKB(cudaMalloc(&axis, n));
   CKB(cub::DeviceRadixSort::SortPairs(nullptr, tmp_bytes, keys[0], keys[1], vals[0], vals[1], (int)n, 0, 64, st));
   CKB(cudaMalloc(&tmp, tmp_bytes));
-  {
-    const uint32_t init[6] = {0xffffffffu, 0xffffffffu, 0xffffffffu, 0u, 0u, 0u};
-    CKB(cudaMemcpyAsync(obox, init, 24, cudaMemcpyHostToDevice, st));
-    unsigned gb = G < 1184u ? G : 1184u;
-    bbox_kernel<<<gb, B, 0, st>>>(ph, n, obox);
-    init_kernel<<<G, B, 0, st>>>(n, obox, boxes, axis, keys[0], vals[0]);
-    ctx->launches += 2;
-  }
+  init_kernel<<<G, B, 0, st>>>(n, keys[0], vals[0]);
+  ctx->launches++;
   for (int level = 0; level < L; level++) {
     const uint64_t first = level == 0 ? 0 : ((uint64_t)1 << (level - 1)) - 1;    // placed two levels up: final
     const uint64_t cnt = n - first;
     const unsigned g = (unsigned)((cnt + B - 1) / B);
+    const uint64_t level_nodes = (uint64_t)1 << level;
+    const unsigned gn = (unsigned)((level_nodes + B - 1) / B);
+    reset_bounds_kernel<<<gn, B, 0, st>>>(n, level, bounds);
+    bounds_kernel<<<g, B, 0, st>>>(ph, first, n, level, keys[cur], vals[cur], bounds);
+    axis_kernel<<<gn, B, 0, st>>>(n, level, bounds, axis);
     make_keys_kernel<<<g, B, 0, st>>>(ph, first, n, level, axis, keys[cur], vals[cur]);
     int end_bit = 33 + level; if (end_bit > 64) end_bit = 64;
     CKB(cub::DeviceRadixSort::SortPairs(tmp, tmp_bytes, keys[cur] + first, keys[cur ^ 1] + first, vals[cur] + first,
                                         vals[cur ^ 1] + first, (int)cnt, 0, end_bit, st));
     cur ^= 1;
     assign_kernel<<<g, B, 0, st>>>(first, n, L, level, keys[cur], vals[cur], heap_photon, split);
-    const uint64_t level_nodes = (uint64_t)1 << level;
-    child_box_kernel<<<(unsigned)((level_nodes + B - 1) / B), B, 0, st>>>(n, level, split, boxes, axis);
-    ctx->launches += 4;
+    ctx->launches += 6;
     CKB(cudaGetLastError());
   }
   CKB(cudaMalloc(&px, 8 * n)); CKB(cudaMalloc(&py, 8 * n)); CKB(cudaMalloc(&pz, 8 * n));
@@ -209,7 +207,7 @@ cudaError_t build_photon_map(GiContext *ctx, PhotonMapStore &m, uint64_t n) {
   px = py = pz = nullptr; node = shade = nullptr; orig = nullptr;
 done:
   for (int k = 0; k < 2; k++) { cudaFree(keys[k]); cudaFree(vals[k]); }
-  cudaFree(heap_photon); cudaFree(split); cudaFree(boxes); cudaFree(axis); cudaFree(obox); cudaFree(tmp);
+  cudaFree(heap_photon); cudaFree(split); cudaFree(bounds); cudaFree(axis); cudaFree(tmp);
   cudaFree(px); cudaFree(py); cudaFree(pz); cudaFree(node); cudaFree(shade); cudaFree(orig);
   return err;
 }
