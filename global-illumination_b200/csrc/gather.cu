@@ -12,8 +12,8 @@
 //   * Upper levels of the left-balanced tree are walked by the whole warp (uniform control flow, near child first,
 //     far child pushed with its plane distance; float32 split planes are widened by one ulp so pruning is
 //     conservative w.r.t. the FP64 coordinates).
-//   * The bottom GI_TILE_LEVELS levels below a node are a "tile": in heap layout they are <= 6 contiguous runs, read
-//     by the 32 lanes in two coalesced rounds of FP64 distance tests.
+//   * The bottom t levels below a node (t = 6..9 by estimate size) are a "tile": in heap layout they are t contiguous
+//     runs, read by the 32 lanes in (2^t - 1) / 32 coalesced rounds of FP64 distance tests.
 //   * Candidates (d^2, slot, photon index) are appended to a per-warp buffer in shared memory with ballot/popc.
 //     When the buffer runs full it is cut back with a 256-bin histogram of d^2 / bound (photons on a surface are
 //     uniform in d^2, so the boundary bin holds ~cap/256 candidates): everything up to the bin that contains the
@@ -30,14 +30,18 @@ namespace gi {
 #define FULL 0xffffffffu
 
 struct WarpBuf {
-  double *d2; uint32_t *slot; uint32_t *orig; uint32_t *hist; int cap;
+  double *d2; uint32_t *slot; uint32_t *hist;     // shared memory: candidates (d2, heap slot) + 256 histogram bins
+  int limit;                                      // cut the buffer back to k once it holds more than this
+  const uint32_t *orig;                           // global: heap slot -> photon index, read only to break exact d2 ties
+  int cap;
 };
 
 __device__ __forceinline__ bool lex_less(double da, uint32_t oa, double db, uint32_t ob) {
   return da < db || (da == db && oa < ob);
 }
 
-// warp-cooperative bitonic sort of buf[0..cap) ascending by (d2, orig); cap is a power of two
+// warp-cooperative bitonic sort of buf[0..cap) ascending by (d2, photon index); cap is a power of two.  Padding
+// entries carry d2 = +inf (and slot 0), real entries finite d2, so the index lookup happens only on real ties.
 __device__ void bitonic_sort(WarpBuf &b, int lane) {
   for (int k2 = 2; k2 <= b.cap; k2 <<= 1)
     for (int j = k2 >> 1; j > 0; j >>= 1) {
@@ -45,13 +49,11 @@ __device__ void bitonic_sort(WarpBuf &b, int lane) {
         const int x = i ^ j;
         if (x > i) {
           const double di = b.d2[i], dx = b.d2[x];
-          const uint32_t oi = b.orig[i], ox = b.orig[x];
+          const uint32_t si = b.slot[i], sx = b.slot[x];
           const bool up = (i & k2) == 0;
-          const bool sw = up ? lex_less(dx, ox, di, oi) : lex_less(di, oi, dx, ox);
-          if (sw) {
-            b.d2[i] = dx; b.d2[x] = di; b.orig[i] = ox; b.orig[x] = oi;
-            const uint32_t s = b.slot[i]; b.slot[i] = b.slot[x]; b.slot[x] = s;
-          }
+          bool x_less_i = dx < di, i_less_x = di < dx;
+          if (di == dx && di < INFINITY) { const uint32_t oi = b.orig[si], ox = b.orig[sx]; x_less_i = ox < oi; i_less_x = oi < ox; }
+          if (up ? x_less_i : i_less_x) { b.d2[i] = dx; b.d2[x] = di; b.slot[i] = sx; b.slot[x] = si; }
         }
       }
       __syncwarp();
@@ -60,7 +62,7 @@ __device__ void bitonic_sort(WarpBuf &b, int lane) {
 
 // slow exact path (heavy ties only): full sort, keep the first k
 __device__ void sort_select(WarpBuf &b, int &count, double &bound, int k, int lane) {
-  for (int i = count + lane; i < b.cap; i += 32) { b.d2[i] = INFINITY; b.orig[i] = 0xffffffffu; b.slot[i] = 0; }
+  for (int i = count + lane; i < b.cap; i += 32) { b.d2[i] = INFINITY; b.slot[i] = 0; }
   __syncwarp();
   bitonic_sort(b, lane);
   count = k;
@@ -110,7 +112,7 @@ __device__ void cut(WarpBuf &b, int &count, double &bound, int k, int lane) {
     }
     __syncwarp();
     double md = INFINITY; uint32_t mo = 0xffffffffu; int mi = -1;
-    if (lane < m) { mi = (int)b.hist[lane]; md = b.d2[mi]; mo = b.orig[mi]; }
+    if (lane < m) { mi = (int)b.hist[lane]; md = b.d2[mi]; mo = b.orig[b.slot[mi]]; }
     int rank = 0;
     for (int l = 0; l < m; l++) {
       const double od = __shfl_sync(FULL, md, l); const uint32_t oo = __shfl_sync(FULL, mo, l);
@@ -122,16 +124,16 @@ __device__ void cut(WarpBuf &b, int &count, double &bound, int k, int lane) {
   int newcount = 0; double mx = 0.0;
   for (int base = 0; base < count; base += 32) {
     const int i = base + lane;
-    double d = 0.0; uint32_t sl = 0, og = 0; bool keep = false;
+    double d = 0.0; uint32_t sl = 0; bool keep = false;
     if (i < count) {
-      d = b.d2[i]; sl = b.slot[i]; og = b.orig[i];
+      d = b.d2[i]; sl = b.slot[i];
       int bin = (int)(d * scale); bin = bin > 255 ? 255 : bin;
       keep = d >= 0.0 && bin <= B;
     }
     const unsigned mk = __ballot_sync(FULL, keep);
     const int pos = newcount + __popc(mk & ((1u << lane) - 1u));
     __syncwarp();
-    if (keep) { b.d2[pos] = d; b.slot[pos] = sl; b.orig[pos] = og; mx = fmax(mx, d); }
+    if (keep) { b.d2[pos] = d; b.slot[pos] = sl; mx = fmax(mx, d); }
     newcount += __popc(mk);
     __syncwarp();
   }
@@ -154,10 +156,10 @@ __device__ __forceinline__ void append(WarpBuf &b, const PhotonMapDev &m, int &c
   const unsigned mask = __ballot_sync(FULL, pred);
   if (mask == 0) return;
   const int pos = count + __popc(mask & ((1u << lane) - 1u));
-  if (pred) { b.d2[pos] = d2; b.slot[pos] = slot; b.orig[pos] = m.orig[slot]; }
+  if (pred) { b.d2[pos] = d2; b.slot[pos] = slot; }
   count += __popc(mask);
   __syncwarp();
-  if (count > b.cap - 32) cut(b, count, bound, k, lane);
+  if (count > b.limit) cut(b, count, bound, k, lane);
 }
 
 __device__ __forceinline__ double dist2(const PhotonMapDev &m, uint64_t slot, double qx, double qy, double qz) {
@@ -165,20 +167,22 @@ __device__ __forceinline__ double dist2(const PhotonMapDev &m, uint64_t slot, do
   return (dx * dx) + (dy * dy) + (dz * dz);
 }
 
-__global__ void __launch_bounds__(GI_GATHER_WARPS * 32, 3)
+template <int MINB>
+__global__ void __launch_bounds__(GI_GATHER_WARPS * 32, MINB)
 gather_kernel(PhotonMapDev m, const double *__restrict__ lut, const GiGatherQuery *__restrict__ queries, uint64_t nq,
               GatherArgs ga, int32_t *idx_out, int32_t *count_out, double *rgb_out) {
   extern __shared__ double smem[];
   const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
-  WarpBuf b; b.cap = ga.cap;
+  WarpBuf b; b.cap = ga.cap; b.orig = m.orig;
+  b.limit = ga.cap - 32 < ga.k + ga.slack ? ga.cap - 32 : ga.k + ga.slack;
   {
-    char *base = (char *)smem + (size_t)warp * ((size_t)ga.cap * 16 + 1024);
+    char *base = (char *)smem + (size_t)warp * ((size_t)ga.cap * 12 + 1024);
     b.d2 = (double *)base; b.slot = (uint32_t *)(base + (size_t)ga.cap * 8);
-    b.orig = b.slot + ga.cap; b.hist = b.orig + ga.cap;
+    b.hist = b.slot + ga.cap;
   }
   const int k = ga.k;
   const uint64_t n = m.n;
-  const int tile_level = m.levels - GI_TILE_LEVELS;        // nodes at this level or deeper are handled as tiles
+  const int tile_level = m.levels - ga.tile_levels;         // nodes at this level or deeper are handled as tiles
   const uint64_t warps_total = (uint64_t)gridDim.x * GI_GATHER_WARPS;
   const uint64_t nchunks = (nq + GI_GATHER_CHUNK - 1) / GI_GATHER_CHUNK;
   // Search radius carried from one query to the next: consecutive queries of a chunk are neighbouring pixels, so the
@@ -200,7 +204,8 @@ gather_kernel(PhotonMapDev m, const double *__restrict__ lut, const GiGatherQuer
         // the node's cell, and the per-axis offsets it is made of (Arya & Mount incremental distance)
         uint32_t sk_node = 0; double sk_rd = 0.0, sk_ox = 0.0, sk_oy = 0.0, sk_oz = 0.0;
         int sp = 0;
-        uint64_t s = 0; double rd = 0.0, ox = 0.0, oy = 0.0, oz = 0.0;
+        uint32_t s = 0; double rd = 0.0, ox = 0.0, oy = 0.0, oz = 0.0;
+        const uint32_t n32 = (uint32_t)n;
         bool have = true;
         while (true) {
           if (!have) {
@@ -211,55 +216,56 @@ gather_kernel(PhotonMapDev m, const double *__restrict__ lut, const GiGatherQuer
             if (rd > bound) continue;
           }
           have = false;
-          const int lvl = 63 - __clzll((long long)(s + 1));
+          const int lvl = 31 - __clz(s + 1);
           if (lvl >= tile_level) {
             // ---- tile: subtree of s, relative depth j occupies slots (s << j) + e, e in [2^j - 1, 2^(j+1) - 1)
-            const int h = m.levels - lvl;
-            const int total = (1 << h) - 1;
-            for (int e = lane; e < total + lane; e += 32) {            // uniform trip count for the ballots
-              bool pred = false; double d2 = 0.0; uint64_t slot = 0;
-              if (e < total) {
-                const int j = 31 - __clz(e + 1);
-                slot = (s << j) + (uint64_t)e;
-                if (slot < n) { d2 = dist2(m, slot, qx, qy, qz); pred = d2 <= bound; }
-              }
-              append(b, m, count, bound, k, lane, pred, d2, (uint32_t)slot);
+            const int total = (1 << (m.levels - lvl)) - 1;
+            for (int e0 = 0; e0 < total; e0 += 32) {                   // uniform trip count for the ballots
+              const int e = e0 + lane;
+              bool pred = false; double d2 = 0.0;
+              const int j = 31 - __clz(e + 1);
+              const uint32_t slot = (s << j) + (uint32_t)e;
+              if (e < total && slot < n32) { d2 = dist2(m, slot, qx, qy, qz); pred = d2 <= bound; }
+              append(b, m, count, bound, k, lane, pred, d2, slot);
             }
             continue;
           }
-          // ---- interior node: its own photon (same value in every lane: uniform branch), then near child first
-          const double d2 = dist2(m, s, qx, qy, qz);
+          // ---- upper node (one 32-byte record, same in every lane: uniform control flow): its own photon, then
+          //      the near child first
+          const double2 r0 = m.inode[2 * (size_t)s], r1 = m.inode[2 * (size_t)s + 1];
+          const double dx = qx - r0.x, dy = qy - r0.y, dz = qz - r1.x;
+          const double d2 = (dx * dx) + (dy * dy) + (dz * dz);
           if (d2 <= bound) {
-            if (lane == 0) { b.d2[count] = d2; b.slot[count] = (uint32_t)s; b.orig[count] = m.orig[s]; }
+            if (lane == 0) { b.d2[count] = d2; b.slot[count] = s; }
             count++;
             __syncwarp();
-            if (count > b.cap - 32) cut(b, count, bound, k, lane);
+            if (count > b.limit) cut(b, count, bound, k, lane);
           }
-          const uint2 nd = m.node[s];
-          const double sf = (double)__uint_as_float(nd.x);
+          const int axis = __double2hiint(r1.y);
+          const double sf = (double)__int_as_float(__double2loint(r1.y));
           // photons left of the split have float(c) <= sf, right of it float(c) >= sf: widen by one float ulp
           const double wide = fabs(sf) * 1.1920929e-7 + 1.0e-44;
-          const double qa = nd.y == 0 ? qx : (nd.y == 1 ? qy : qz);
-          const double oa = nd.y == 0 ? ox : (nd.y == 1 ? oy : oz);
-          uint64_t near, far; double fd;
-          if (qa < sf) { near = 2 * s + 1; far = 2 * s + 2; fd = (sf - wide) - qa; }
-          else { near = 2 * s + 2; far = 2 * s + 1; fd = qa - (sf + wide); }
+          const double qa = axis == 0 ? qx : (axis == 1 ? qy : qz);
+          const double oa = axis == 0 ? ox : (axis == 1 ? oy : oz);
+          const bool left = qa < sf;
+          const uint32_t near = 2 * s + (left ? 1 : 2), far = 2 * s + (left ? 2 : 1);
+          double fd = left ? (sf - wide) - qa : qa - (sf + wide);
           fd = fmax(fd, oa);                                            // never closer than the parent cell
           const double frd = (rd - oa * oa + fd * fd) * 0.99999999999999;   // rounding must not over-estimate
-          if (far < n && frd <= bound) {
+          if (far < n32 && frd <= bound) {
             if (lane == sp) {
-              sk_node = (uint32_t)far; sk_rd = frd;
-              sk_ox = nd.y == 0 ? fd : ox; sk_oy = nd.y == 1 ? fd : oy; sk_oz = nd.y == 2 ? fd : oz;
+              sk_node = far; sk_rd = frd;
+              sk_ox = axis == 0 ? fd : ox; sk_oy = axis == 1 ? fd : oy; sk_oz = axis == 2 ? fd : oz;
             }
             sp++;
           }
-          if (near < n) { s = near; have = true; }
+          if (near < n32) { s = near; have = true; }
         }
         finish(b, count, bound, k, lane);
         if (count >= k || init >= ga.r2) break;
-        init = ga.r2;                                                   // the guess was too small: full radius
+        init = fmin(ga.r2, init * 4.0);                                 // the guess was too small: widen and retry
       }
-      guess = count >= k ? bound * 2.0 : ga.r2;
+      guess = count >= k ? bound * ga.guess_factor : ga.r2;
     }
     // ---- radiance estimate, photon_utils.cpp:80-161
     const int found = count;
@@ -318,35 +324,43 @@ gather_kernel(PhotonMapDev m, const double *__restrict__ lut, const GiGatherQuer
     if (rgb_out && lane == 0) { rgb_out[3 * qi] = est[0]; rgb_out[3 * qi + 1] = est[1]; rgb_out[3 * qi + 2] = est[2]; }
     if (count_out && lane == 0) count_out[qi] = found;
     if (idx_out) {
-      // ascending photon indices: sort the index column alone (d2 = 0 makes (d2, orig) order == orig order)
-      for (int i = lane; i < b.cap; i += 32) { b.d2[i] = 0.0; if (i >= found) b.orig[i] = 0xffffffffu; }
+      // ascending photon indices: put the index into the d2 column (exact in a double) and sort on it
+      for (int i = lane; i < b.cap; i += 32) b.d2[i] = i < found ? (double)b.orig[b.slot[i]] : INFINITY;
       __syncwarp();
       bitonic_sort(b, lane);
-      for (int i = lane; i < k; i += 32) idx_out[qi * (uint64_t)k + i] = i < found ? (int32_t)b.orig[i] : -1;
+      for (int i = lane; i < k; i += 32) idx_out[qi * (uint64_t)k + i] = i < found ? (int32_t)b.d2[i] : -1;
     }
     __syncwarp();
   }
 }
 
-cudaError_t launch_gather(GiContext *ctx, const PhotonMapDev &m, const double *d_lut, const GiGatherQuery *d_q,
-                          uint64_t nq, const GatherArgs &ga, int32_t *d_idx, int32_t *d_count, double *d_rgb,
-                          cudaStream_t st) {
-  const size_t smem = (size_t)GI_GATHER_WARPS * ((size_t)ga.cap * 16 + 1024);
+template <int MINB>
+static cudaError_t launch_t(GiContext *ctx, const PhotonMapDev &m, const double *d_lut, const GiGatherQuery *d_q, uint64_t nq,
+                            const GatherArgs &ga, int32_t *d_idx, int32_t *d_count, double *d_rgb, cudaStream_t st) {
+  const size_t smem = (size_t)GI_GATHER_WARPS * ((size_t)ga.cap * 12 + 1024);
   static size_t configured = 0;
   if (smem > configured) {
-    cudaError_t e = cudaFuncSetAttribute(gather_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
+    cudaError_t e = cudaFuncSetAttribute(gather_kernel<MINB>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
     if (e != cudaSuccess) return e;
     configured = smem;
   }
   int per_sm = 1;
-  cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, gather_kernel, GI_GATHER_WARPS * 32, smem);
+  cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, gather_kernel<MINB>, GI_GATHER_WARPS * 32, smem);
   if (per_sm < 1) per_sm = 1;
-  uint64_t want = (nq + GI_GATHER_WARPS - 1) / GI_GATHER_WARPS;
-  uint64_t cap = (uint64_t)ctx->sm_count * per_sm;         // persistent: one resident wave, warps stride over queries
+  const uint64_t nchunks = (nq + GI_GATHER_CHUNK - 1) / GI_GATHER_CHUNK;
+  uint64_t want = (nchunks + GI_GATHER_WARPS - 1) / GI_GATHER_WARPS;
+  uint64_t cap = (uint64_t)ctx->sm_count * per_sm;         // persistent: one resident wave, warps stride over chunks
   unsigned grid = (unsigned)(want < cap ? want : cap);
-  gather_kernel<<<grid, GI_GATHER_WARPS * 32, smem, st>>>(m, d_lut, d_q, nq, ga, d_idx, d_count, d_rgb);
+  gather_kernel<MINB><<<grid, GI_GATHER_WARPS * 32, smem, st>>>(m, d_lut, d_q, nq, ga, d_idx, d_count, d_rgb);
   ctx->launches++;
   return cudaGetLastError();
+}
+
+cudaError_t launch_gather(GiContext *ctx, const PhotonMapDev &m, const double *d_lut, const GiGatherQuery *d_q,
+                          uint64_t nq, const GatherArgs &ga, int32_t *d_idx, int32_t *d_count, double *d_rgb,
+                          cudaStream_t st) {
+  if (ga.min_blocks >= 4) return launch_t<4>(ctx, m, d_lut, d_q, nq, ga, d_idx, d_count, d_rgb, st);
+  return launch_t<3>(ctx, m, d_lut, d_q, nq, ga, d_idx, d_count, d_rgb, st);
 }
 
 }  // namespace gi

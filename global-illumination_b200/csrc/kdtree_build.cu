@@ -144,7 +144,7 @@ __global__ void assign_kernel(uint64_t first, uint64_t n, int L, int level, uint
 
 __global__ void finalize_kernel(const GiPhoton *__restrict__ ph, uint64_t n, const uint32_t *__restrict__ heap_photon,
                                 const float *__restrict__ split, const uint8_t *__restrict__ axis, double *px, double *py,
-                                double *pz, uint2 *node, uint2 *shade, uint32_t *orig) {
+                                double *pz, uint2 *node, uint2 *shade, uint32_t *orig, double2 *inode, uint64_t n_inode) {
   const uint64_t i = (uint64_t)blockIdx.x * blockDim.x + threadIdx.x;
   if (i >= n) return;
   const uint32_t src = heap_photon[i];
@@ -154,6 +154,10 @@ __global__ void finalize_kernel(const GiPhoton *__restrict__ ph, uint64_t n, con
   shade[i] = make_uint2(b.z, b.w & 0xffffu);
   orig[i] = src;
   node[i] = make_uint2(__float_as_uint(split[i]), axis[i]);
+  if (i < n_inode) {
+    inode[2 * i] = make_double2(px[i], py[i]);
+    inode[2 * i + 1] = make_double2(pz[i], __hiloint2double((int)axis[i], (int)__float_as_uint(split[i])));
+  }
 }
 
 #define CKB(x) do { cudaError_t e_ = (x); if (e_ != cudaSuccess) { err = e_; goto done; } } while (0)
@@ -167,6 +171,7 @@ cudaError_t build_photon_map(GiContext *ctx, PhotonMapStore &m, uint64_t n) {
   uint32_t *heap_photon = nullptr, *bounds = nullptr; float *split = nullptr; uint8_t *axis = nullptr;
   void *tmp = nullptr; size_t tmp_bytes = 0;
   double *px = nullptr, *py = nullptr, *pz = nullptr; uint2 *node = nullptr, *shade = nullptr; uint32_t *orig = nullptr;
+  double2 *inode = nullptr; uint64_t n_inode = 0;
   const int B = 256;
   const unsigned G = (unsigned)((n + B - 1) / B);
   int cur = 0;
@@ -197,18 +202,21 @@ cudaError_t build_photon_map(GiContext *ctx, PhotonMapStore &m, uint64_t n) {
   }
   CKB(cudaMalloc(&px, 8 * n)); CKB(cudaMalloc(&py, 8 * n)); CKB(cudaMalloc(&pz, 8 * n));
   CKB(cudaMalloc(&node, 8 * n)); CKB(cudaMalloc(&shade, 8 * n)); CKB(cudaMalloc(&orig, 4 * n));
-  finalize_kernel<<<G, B, 0, st>>>(ph, n, heap_photon, split, axis, px, py, pz, node, shade, orig);
+  n_inode = L > GI_TILE_LEVELS_MIN ? ((uint64_t)1 << (L - GI_TILE_LEVELS_MIN)) - 1 : 0;   // every level that can be "upper"
+  if (n_inode > n) n_inode = n;
+  CKB(cudaMalloc(&inode, 32 * (n_inode ? n_inode : 1)));
+  finalize_kernel<<<G, B, 0, st>>>(ph, n, heap_photon, split, axis, px, py, pz, node, shade, orig, inode, n_inode);
   ctx->launches++;
   CKB(cudaGetLastError());
   CKB(cudaStreamSynchronize(st));
   m.dev.n = n; m.dev.levels = L; m.dev.px = px; m.dev.py = py; m.dev.pz = pz; m.dev.node = node; m.dev.shade = shade;
-  m.dev.orig = orig;
+  m.dev.orig = orig; m.dev.inode = inode; m.dev.n_inode = n_inode;
   m.built = true;
-  px = py = pz = nullptr; node = shade = nullptr; orig = nullptr;
+  px = py = pz = nullptr; node = shade = nullptr; orig = nullptr; inode = nullptr;
 done:
   for (int k = 0; k < 2; k++) { cudaFree(keys[k]); cudaFree(vals[k]); }
   cudaFree(heap_photon); cudaFree(split); cudaFree(bounds); cudaFree(axis); cudaFree(tmp);
-  cudaFree(px); cudaFree(py); cudaFree(pz); cudaFree(node); cudaFree(shade); cudaFree(orig);
+  cudaFree(px); cudaFree(py); cudaFree(pz); cudaFree(node); cudaFree(shade); cudaFree(orig); cudaFree(inode);
   return err;
 }
 

@@ -10,10 +10,14 @@
 // handful of coalesced runs ("node tiles") instead of node by node.
 #pragma once
 #include <stdint.h>
+#if defined(__CUDACC__)
+#include <cuda_runtime.h>
+#endif
 
 namespace gi {
 
-#define GI_TILE_LEVELS 6          /* a tile = a subtree of up to 63 photons, two warp-wide rounds */
+#define GI_TILE_LEVELS_MIN 6      /* a tile = the bottom t levels below a node, t chosen per launch in [6, 9]: */
+#define GI_TILE_LEVELS_MAX 9      /* a subtree of up to 2^t - 1 photons read in (2^t - 1) / 32 warp-wide rounds  */
 #define GI_MAX_K 512              /* largest estimate size (-gs/-cs) the gather kernel supports */
 
 struct PhotonMapDev {
@@ -21,6 +25,8 @@ struct PhotonMapDev {
   int32_t levels;                 /* floor(log2 n) + 1 */
   const double *px, *py, *pz;     /* heap order */
   const uint2 *node;              /* heap order: x = float bits of the split coordinate, y = split axis (0..2) */
+  const double2 *inode;           /* first n_inode heap slots again, packed for the warp-uniform walk of the upper    */
+  uint64_t n_inode;               /* levels: 2 x double2 = {x, y}, {z, split float bits | axis << 32}: one 32 B sector */
   const uint2 *shade;             /* heap order: x = rgbe bytes (r | g<<8 | b<<16 | e<<24), y = direction code */
   const uint32_t *orig;           /* heap order -> index in the order the photons were loaded / traced */
 };
