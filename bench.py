@@ -431,8 +431,10 @@ def run_ours(args):
                         "ms_per_step": e2e_ms},
                 "gpu_launches": int(launches), "clocks": clocks}
         traffic_file = os.path.join(ROOT, "profiles", "gather_traffic.json")
-        if os.path.exists(traffic_file):
-            line["roofline"]["traffic"] = json.load(open(traffic_file)).get("dram_bytes_per_launch")
+        if os.path.exists(traffic_file):       # ncu capture at a smaller launch: DRAM bytes per gather x this launch's gathers
+            tf = json.load(open(traffic_file))
+            line["roofline"]["traffic"] = tf["dram_bytes_per_launch"] / tf["queries_per_launch"] * n_q
+            line["roofline"]["traffic_note"] = "ncu dram bytes per gather (%s) scaled to this launch" % tf["source"]
         if world == 1 and not args.no_cpu_baseline:
             line["cpu_baseline"] = cpu_baseline(args, torch, rays, full, queries)
         print(json.dumps(line))
