@@ -20,9 +20,21 @@ $(PKG)/bin/gi_scene_tool: $(PKG)/host/scene_tool.cpp $(HOST_SRCS) $(PKG)/host/sc
 	@mkdir -p $(PKG)/bin
 	$(CXX) $(CXXFLAGS) $< $(HOST_SRCS) -o $@
 
+# one object per translation unit under build/ (git-ignored) so `make -j` compiles the kernels in parallel
+LIB_SRCS := $(CU_SRCS) $(HOST_SRCS) $(PKG)/host/capi_host.cpp
+LIB_OBJS := $(patsubst %,build/%.o,$(notdir $(LIB_SRCS)))
+vpath %.cu $(PKG)/csrc
+vpath %.cpp $(PKG)/host
+build/%.cu.o: %.cu $(CU_HDRS)
+	@mkdir -p build
+	$(NVCC) $(NVFLAGS) -c $< -o $@
+build/%.cpp.o: %.cpp $(CU_HDRS)
+	@mkdir -p build
+	$(NVCC) $(NVFLAGS) -c $< -o $@
+
 lib: $(PKG)/libgi_b200.so
-$(PKG)/libgi_b200.so: $(CU_SRCS) $(CU_HDRS) $(HOST_SRCS) $(PKG)/host/capi_host.cpp
-	$(NVCC) $(NVFLAGS) -shared $(CU_SRCS) $(HOST_SRCS) $(PKG)/host/capi_host.cpp -o $@ -lcudart
+$(PKG)/libgi_b200.so: $(LIB_OBJS)
+	$(NVCC) $(ARCH) -shared $(LIB_OBJS) -o $@ -lcudart
 
 host_sim: tests/host_sim/libisect_sim.so
 tests/host_sim/libisect_sim.so: tests/host_sim/isect_sim.cpp $(CU_HDRS) $(HOST_SRCS)
@@ -32,5 +44,5 @@ oracle:
 	$(MAKE) -C oracle all
 
 clean:
-	rm -rf $(PKG)/bin $(PKG)/libgi_b200.so
+	rm -rf build $(PKG)/bin $(PKG)/libgi_b200.so
 	$(MAKE) -C oracle clean

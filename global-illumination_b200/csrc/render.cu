@@ -1,0 +1,613 @@
+// csrc/render.cu -- gi_render / gi_render_float: the reference's RenderImage (src/render.cpp:155-259) as batched
+// kernels.
+//
+// The reference walks the image with one CPU thread per column stripe and, per primary hit, RECURSES: RayTrace
+// (raytracer.cpp:174-233) calls the direct-light loops, then up to TRANSMISSIVE_TEST + SPECULAR_TEST Monte Carlo
+// paths (montecarlo.cpp:16-171) and up to INDIRECT_TEST indirect paths (:177-305), every one of which ends in
+// kd-tree gathers.  Here the recursion is unrolled into flat batches with no per-pixel state on a stack:
+//
+//   primary_kernel   thread per (supersample, depth-of-field sample): eye ray -> closest hit -> PrimHit record
+//   direct_kernel    WARP per primary hit: ambient + direct lighting; the 128+256+128 samples of a soft-shadowed
+//                    area light are split over the 32 lanes (shade.cuh); writes the number of secondary paths the
+//                    hit owns and queues the hit's own caustic / global gathers
+//   (cub scan)       secondary paths of all hits get consecutive item numbers
+//   path_kernel      thread per secondary path (one transmissive / specular / indirect sample of one hit): the whole
+//                    MonteCarlo_PathTrace or MonteCarlo_IndirectSample loop; its local colour goes to item_rgb[],
+//                    every EstimateRadiance it would call becomes a request {query, weight, pixel} in a queue
+//   gather kernel    (gather.cu) evaluates each queue in one launch, requests ordered by a Morton key for locality
+//   commit kernels   item colours and weight x estimate are added into the FP64 accumulator
+//   resolve_kernel   clamp, box-filter the 2^aa x 2^aa supersamples, quantise like R2Image::SetPixelRGB
+//
+// Random numbers: Philox streams keyed by (seed, primary sample, stage, item) -- see shade.cuh; an image does not
+// depend on batch size, launch geometry or the number of GPUs sharing the frame.
+#include <cub/cub.cuh>
+#include <algorithm>
+#include <cstdio>
+#include <cstring>
+#include "context.h"
+#include "gather.h"
+#include "shade.cuh"
+
+namespace gi {
+
+enum { STAGE_DOF = 1, STAGE_PATH = 2, STAGE_LIGHT = 16 };     // Philox stage ids (STAGE_LIGHT + 4*light + pass)
+
+struct PrimHit { double p[3], n[3]; int32_t material; uint32_t pix; };      // material < 0: the eye ray missed
+
+struct Queue {                       // gather requests of one photon map, filled by direct_kernel / path_kernel
+  GiGatherQuery *q;
+  double *w;                         // 3 per request: the colour the estimate is multiplied by
+  uint32_t *pix;
+  unsigned long long *count;         // may exceed cap: the batch is then repeated with fewer items
+  unsigned long long cap;
+};
+
+struct Frame2 {                      // per-frame constants of the eye-ray generator (render.cpp:64-77)
+  D3 eye, far_org, far_right, far_up, u, v;
+  double xc, yc, w, h;               // viewport centre and size in supersamples
+  int sw, sh, dof;
+};
+
+GI_DEV void add3(double *a, D3 c) { atomicAdd(a, c.x); atomicAdd(a + 1, c.y); atomicAdd(a + 2, c.z); }
+
+GI_DEV void flush_stats(RayStats *g, const RayStats &s) {
+  const unsigned m = __activemask();
+  const unsigned long long v[7] = {s.screen, s.shadow, s.monte, s.transmissive, s.specular, s.indirect, s.caustic};
+  unsigned long long *out = &g->screen;
+  const int leader = __ffs(m) - 1;
+#pragma unroll
+  for (int i = 0; i < 7; i++) {
+    const unsigned t = __reduce_add_sync(m, (unsigned)v[i]);      // per-thread counts stay far below 2^32 / 32
+    if ((threadIdx.x & 31) == leader && t) atomicAdd(out + i, (unsigned long long)t);
+  }
+}
+
+GI_DEV RayStats zero_stats() { RayStats s; s.screen = s.shadow = s.monte = s.transmissive = s.specular = s.indirect = s.caustic = 0; return s; }
+
+GI_DEV void push_request(const Queue &qu, D3 p, D3 n, D3 bounce, double cos_theta, const Brdf &b, D3 w, uint32_t pix) {
+  const unsigned long long i = atomicAdd(qu.count, 1ull);
+  if (i >= qu.cap) return;
+  GiGatherQuery q;
+  q.p[0] = p.x; q.p[1] = p.y; q.p[2] = p.z; q.n[0] = n.x; q.n[1] = n.y; q.n[2] = n.z;
+  q.bounce[0] = bounce.x; q.bounce[1] = bounce.y; q.bounce[2] = bounce.z; q.cos_theta = cos_theta;
+  q.kd[0] = b.kd.x; q.kd[1] = b.kd.y; q.kd[2] = b.kd.z; q.ks[0] = b.ks.x; q.ks[1] = b.ks.y; q.ks[2] = b.ks.z;
+  q.shininess = b.n;
+  qu.q[i] = q;
+  qu.w[3 * i] = w.x; qu.w[3 * i + 1] = w.y; qu.w[3 * i + 2] = w.z;
+  qu.pix[i] = pix;
+}
+
+// ------------------------------------------------------------------------------------------------ primary rays
+// Threadable_RayTracer, render.cpp:91-131.  Sample s = pix * dof + k, pix = i * sh + j (image_buffer[i][j]).
+__global__ void __launch_bounds__(128) primary_kernel(ShadeEnv env, Frame2 f, uint64_t first, uint64_t n,
+                                                      PrimHit *__restrict__ hits, double *__restrict__ accum,
+                                                      RayStats *stats) {
+  RayStats st = zero_stats();
+  for (uint64_t t = (uint64_t)blockIdx.x * blockDim.x + threadIdx.x; t < n; t += (uint64_t)gridDim.x * blockDim.x) {
+    const uint64_t s = first + t;
+    const uint32_t pix = (uint32_t)(s / f.dof);
+    const int k = (int)(s % f.dof), i = (int)(pix / f.sh), j = (int)(pix % f.sh);
+    const double dx = (double)(2 * (i - f.xc)) / f.w, dy = (double)(2 * (j - f.yc)) / f.h;
+    const D3 far_point = f.far_org + (f.far_right * dx) + (f.far_up * dy);
+    D3 org = f.eye;
+    if (env.p.depth_of_field) {
+      Rng rng; rng_init(rng, env.p.seed, pix, STAGE_DOF, (uint32_t)k);
+      double r1, r2;
+      do { r1 = (rng_double(rng) * 2.0) - 1.0; r2 = (rng_double(rng) * 2.0) - 1.0; } while (r1 * r1 + r2 * r2 > 1.0);
+      org = f.eye + f.u * r1 + f.v * r2;
+    }
+    RayD ray; ray.o = org; ray.d = normalized(far_point - org);       // R3Ray(point, point), R3Ray.cpp:52-58
+    HitRec h;
+    closest_hit(env.sc, ray, h);
+    PrimHit ph;
+    ph.pix = pix;
+    if (h.prim >= 0) {
+      ph.p[0] = h.p.x; ph.p[1] = h.p.y; ph.p[2] = h.p.z; ph.n[0] = h.n.x; ph.n[1] = h.n.y; ph.n[2] = h.n.z;
+      ph.material = env.sc.elements[h.element].material;
+      st.screen++;
+    } else {
+      ph.p[0] = ph.p[1] = ph.p[2] = ph.n[0] = ph.n[1] = ph.n[2] = 0; ph.material = -1;
+      add3(accum + 3 * (size_t)pix, env.background);
+    }
+    hits[t] = ph;
+  }
+  flush_stats(stats, st);
+}
+
+// The number of secondary paths RayTrace starts at a primary hit (raytracer.cpp:55-57, 87-89, 117-120, 204-223)
+struct SubPaths { int n_t, n_s, n_i; double r_coeff; };
+
+GI_DEV SubPaths sub_paths(const GiParams &p, const Brdf &b, double cos_theta) {
+  SubPaths sp; sp.n_t = sp.n_s = sp.n_i = 0; sp.r_coeff = 0;
+  if (p.transmissive_illum && b.transparent) {
+    if (p.specular_illum && p.fresnel) sp.r_coeff = reflection_coeff(cos_theta, b.ir, p.ir_air);
+    if (sp.r_coeff < 1.0) {
+      const double hw = max_channel(b.kt * (1.0 - sp.r_coeff));
+      sp.n_t = (int)ceil((p.transmissive_test * hw + p.transmissive_test) / 2.0);
+    }
+  }
+  if (p.specular_illum && (b.specular || sp.r_coeff > 0)) {
+    const double hw = max_channel(b.kt * sp.r_coeff + b.ks);
+    sp.n_s = (int)ceil((p.specular_test * hw + p.specular_test) / 2.0);
+  }
+  if (p.indirect_illum && b.diffuse) {
+    const double hw = max_channel(b.kd);
+    sp.n_i = (int)ceil((p.indirect_test * hw + p.indirect_test) / 2.0);
+  }
+  return sp;
+}
+
+// ------------------------------------------------------------------------------------------------ primary hits
+// The non-recursive part of RayTrace (raytracer.cpp:174-203, 224-231) for one primary hit per WARP.
+__global__ void __launch_bounds__(128) direct_kernel(ShadeEnv env, uint64_t first, uint64_t n,
+                                                     const PrimHit *__restrict__ hits, double *__restrict__ accum,
+                                                     uint32_t *__restrict__ n_items, Queue qglobal, Queue qcaustic,
+                                                     RayStats *stats) {
+  RayStats st = zero_stats();
+  const int lane = threadIdx.x & 31;
+  const uint64_t warp0 = ((uint64_t)blockIdx.x * blockDim.x + threadIdx.x) >> 5;
+  const uint64_t nwarps = ((uint64_t)gridDim.x * blockDim.x) >> 5;
+  for (uint64_t t = warp0; t < n; t += nwarps) {
+    const PrimHit ph = hits[t];
+    if (ph.material < 0) { if (lane == 0) n_items[t] = 0; continue; }
+    const Brdf b = load_brdf(env.materials[ph.material]);
+    D3 point = ld3(ph.p), normal = ld3(ph.n);
+    const D3 cam = env.eye;
+    D3 color = mk3(0, 0, 0);
+    if (env.p.ambient) color = color + env.ambient;
+    const D3 view = normalized(point - cam);
+    const double cos_theta = dot(normal, -view);
+    if (env.p.ambient && b.ambient) color = color + b.ka;
+    if (env.p.direct_illum && (b.diffuse || b.specular)) {
+      Rng unused; unused.left = 0;
+      SampleKey key; key.seed = env.p.seed; key.index = first + t; key.stage = STAGE_LIGHT;
+      direct_illumination(env, point, normal, cam, color, b, cos_theta, false, unused, &key, st);
+    }
+    if (lane == 0) {
+      const SubPaths sp = sub_paths(env.p, b, cos_theta);
+      n_items[t] = (uint32_t)(sp.n_t + sp.n_s + sp.n_i);
+      const D3 one = mk3(1, 1, 1);
+      if (env.p.caustic_illum && b.diffuse) {                                    // CausticIllumination, :138-149
+        push_request(qcaustic, point, normal, reflective_bounce(normal, view, cos_theta), cos_theta, b, one, ph.pix);
+        st.caustic++;
+      }
+      if (env.p.direct_photon_illum && b.diffuse) {                              // EstimateGlobalIllumination, :151-167
+        push_request(qglobal, point, normal, reflective_bounce(normal, view, cos_theta), cos_theta, b, one, ph.pix);
+        st.indirect++;
+      }
+      add3(accum + 3 * (size_t)ph.pix, color);
+    }
+  }
+  flush_stats(stats, st);
+}
+
+// ------------------------------------------------------------------------------------------------ secondary paths
+enum { MODE_PATH = 0, MODE_INDIRECT = 1 };
+
+// MonteCarlo_PathTrace (montecarlo.cpp:16-171, mode PATH) and MonteCarlo_IndirectSample (:177-305, mode INDIRECT)
+// as one loop.  `scale` is what the caller multiplies the path's colour with before adding it to the pixel; a
+// diffuse pick in mode PATH with INDIRECT_ILLUM on is the nested IndirectIllumination(inMonteCarlo = true) call
+// (raytracer.cpp:112-135 with one sample): the loop restarts in mode INDIRECT with the product of the weights.
+GI_DEV D3 trace_path(const ShadeEnv &env, RayD ray, int mode, D3 scale, uint32_t pix, Rng &rng, const Queue &qglobal,
+                     const Queue &qcaustic, RayStats &st) {
+  const GiParams &p = env.p;
+  D3 out = mk3(0, 0, 0);
+  if (mode == MODE_PATH && !p.monte_carlo) return out;
+  D3 tw = mk3(1, 1, 1);
+  D3 ray_start = ray.o;
+  for (int iter = 0; iter < p.max_monte_depth; iter++) {
+    HitRec h;
+    closest_hit(env.sc, ray, h);
+    if (h.prim < 0) { out = out + mul3(scale, mul3(tw, env.background)); break; }
+    st.monte++;
+    const Brdf b = load_brdf(env.materials[env.sc.elements[h.element].material]);
+    const D3 point = h.p, normal = h.n;
+    const D3 view = normalized(point - ray_start);
+    const double cos_theta = dot(normal, -view);
+    double r_coeff = 0;
+    if (mode == MODE_PATH) {
+      D3 cb = mk3(0, 0, 0);
+      if (p.ambient) cb = cb + env.ambient;
+      if (b.diffuse || b.specular) direct_illumination(env, point, normal, ray_start, cb, b, cos_theta, true, rng, nullptr, st);
+      if (p.caustic_illum && b.diffuse) {
+        push_request(qcaustic, point, normal, reflective_bounce(normal, view, cos_theta), cos_theta, b, mul3(scale, tw), pix);
+        st.caustic++;
+      }
+      out = out + mul3(scale, mul3(cb, tw));
+      if (p.specular_illum && p.transmissive_illum && p.fresnel && b.transparent)
+        r_coeff = reflection_coeff(cos_theta, b.ir, p.ir_air);
+    } else if (p.fresnel && b.transparent) r_coeff = reflection_coeff(cos_theta, b.ir, p.ir_air);
+
+    const double prob_diffuse = max_channel(b.kd);
+    double prob_transmission = max_channel(b.kt);
+    const double prob_specular = max_channel(b.ks) + r_coeff * prob_transmission;
+    prob_transmission *= (1.0 - r_coeff);
+    const double prob_terminate = max_channel(b.ke) + p.prob_absorb;
+    const double prob_total = prob_diffuse + prob_transmission + prob_specular + prob_terminate;
+    double rnd = rng_double(rng);
+    if (prob_total > 1.0) rnd *= prob_total;
+
+    D3 bounce;
+    if (rnd < prob_diffuse) {
+      const D3 w = mul3(b.kd, tw) / prob_diffuse;
+      if (mode == MODE_INDIRECT || (!p.indirect_illum && p.fast_global)) {
+        push_request(qglobal, point, normal, reflective_bounce(normal, view, cos_theta), cos_theta, b, mul3(scale, w), pix);
+        if (mode == MODE_PATH) st.indirect++;                 // EstimateGlobalIllumination counts, EstimateRadiance does not
+        break;
+      }
+      if (!p.indirect_illum) break;
+      scale = mul3(scale, mul3(b.kd, w));                      // (inner * kd) * kd * tw / prob_diffuse
+      bounce = diffuse_sample(normal, cos_theta, rng);
+      st.indirect++;
+      mode = MODE_INDIRECT; tw = mk3(1, 1, 1); iter = -1;
+    } else if (rnd < prob_diffuse + prob_transmission) {
+      if (mode == MODE_PATH && !p.transmissive_illum) break;
+      const D3 exact = transmissive_bounce(normal, view, cos_theta, b.ir, p.ir_air);
+      bounce = p.distrib_transmissive ? specular_sample(exact, b.n, cos_theta, rng) : exact;
+      st.transmissive++;
+      tw = mul3(tw, (b.kt * (1.0 - r_coeff)) / prob_transmission);
+    } else if (rnd < prob_diffuse + prob_transmission + prob_specular) {
+      if (mode == MODE_PATH && !p.specular_illum) break;
+      const D3 exact = reflective_bounce(normal, view, cos_theta);
+      bounce = p.distrib_specular ? specular_sample(exact, b.n, cos_theta, rng) : exact;
+      st.specular++;
+      tw = mul3(tw, (b.ks + b.kt * r_coeff) / prob_specular);
+    } else break;
+    ray_start = point + bounce * GI_EPS;
+    ray.o = ray_start; ray.d = bounce;
+  }
+  return out;
+}
+
+// One thread per secondary path.  Item g belongs to the primary hit h with offs[h] <= g < offs[h+1]; inside the hit
+// the items are its transmissive samples, then its specular samples, then its indirect samples
+// (TransmissiveIllumination / SpecularIllumination / IndirectIllumination, raytracer.cpp:47-135).
+__global__ void __launch_bounds__(128) path_kernel(ShadeEnv env, uint64_t first_sample, uint64_t n_hits,
+                                                   const PrimHit *__restrict__ hits, const uint64_t *__restrict__ offs,
+                                                   uint64_t item0, uint32_t n, double *__restrict__ item_rgb,
+                                                   uint32_t *__restrict__ item_pix, Queue qglobal, Queue qcaustic,
+                                                   RayStats *stats) {
+  RayStats st = zero_stats();
+  const uint32_t t = blockIdx.x * blockDim.x + threadIdx.x;
+  if (t < n) {
+    const uint64_t g = item0 + t;
+    uint64_t lo = 0, hi = n_hits;                       // largest h with offs[h] <= g
+    while (hi - lo > 1) { const uint64_t mid = (lo + hi) >> 1; if (offs[mid] <= g) lo = mid; else hi = mid; }
+    const uint64_t hidx = lo;
+    const uint32_t local = (uint32_t)(g - offs[hidx]);
+    const PrimHit ph = hits[hidx];
+    const Brdf b = load_brdf(env.materials[ph.material]);
+    const D3 point = ld3(ph.p), normal = ld3(ph.n);
+    D3 view = normalized(point - env.eye);
+    const double cos_theta = dot(normal, -view);
+    const SubPaths sp = sub_paths(env.p, b, cos_theta);
+    Rng rng; rng_init(rng, env.p.seed, first_sample + hidx, STAGE_PATH, local);
+    D3 total_weight, bounce; int mode, count;
+    if (local < (uint32_t)sp.n_t) {
+      const D3 exact = transmissive_bounce(normal, view, cos_theta, b.ir, env.p.ir_air);
+      total_weight = b.kt * (1.0 - sp.r_coeff); count = sp.n_t; mode = MODE_PATH;
+      bounce = env.p.distrib_transmissive ? specular_sample(exact, b.n, cos_theta, rng) : exact;
+      st.transmissive++;
+    } else if (local < (uint32_t)(sp.n_t + sp.n_s)) {
+      const D3 exact = reflective_bounce(normal, view, cos_theta);
+      total_weight = b.kt * sp.r_coeff + b.ks; count = sp.n_s; mode = MODE_PATH;
+      bounce = env.p.distrib_specular ? specular_sample(exact, b.n, cos_theta, rng) : exact;
+      st.specular++;
+    } else {
+      total_weight = b.kd; count = sp.n_i; mode = MODE_INDIRECT;
+      bounce = diffuse_sample(normal, cos_theta, rng);
+      st.indirect++;
+    }
+    RayD ray; ray.o = point + bounce * GI_EPS; ray.d = bounce;
+    const D3 c = trace_path(env, ray, mode, total_weight / (double)count, ph.pix, rng, qglobal, qcaustic, st);
+    item_rgb[3 * (size_t)t] = c.x; item_rgb[3 * (size_t)t + 1] = c.y; item_rgb[3 * (size_t)t + 2] = c.z;
+    item_pix[t] = ph.pix;
+  }
+  flush_stats(stats, st);
+}
+
+// Adds the item colours of a finished batch into the accumulator.  Items of one pixel are consecutive, so a warp
+// first folds equal-pixel runs with shuffles and only run heads touch memory.
+__global__ void __launch_bounds__(256) commit_items_kernel(const double *__restrict__ item_rgb,
+                                                           const uint32_t *__restrict__ item_pix, uint32_t n,
+                                                           double *__restrict__ accum) {
+  const uint32_t t = blockIdx.x * blockDim.x + threadIdx.x;
+  const int lane = threadIdx.x & 31;
+  const bool live = t < n;
+  uint32_t key = live ? item_pix[t] : 0xffffffffu;
+  D3 v = live ? mk3(item_rgb[3 * (size_t)t], item_rgb[3 * (size_t)t + 1], item_rgb[3 * (size_t)t + 2]) : mk3(0, 0, 0);
+  for (int o = 1; o < 32; o <<= 1) {
+    const uint32_t k2 = __shfl_down_sync(0xffffffffu, key, o);
+    const double x = __shfl_down_sync(0xffffffffu, v.x, o), y = __shfl_down_sync(0xffffffffu, v.y, o),
+                 z = __shfl_down_sync(0xffffffffu, v.z, o);
+    // runs are contiguous: lane + o has my key only if every lane between has it too
+    if (lane + o < 32 && k2 == key) { v.x += x; v.y += y; v.z += z; }
+  }
+  const uint32_t prev = __shfl_up_sync(0xffffffffu, key, 1);
+  if (live && (lane == 0 || prev != key)) add3(accum + 3 * (size_t)key, v);
+}
+
+// accum[pix] += weight * estimate for every request of a queue
+__global__ void __launch_bounds__(256) commit_requests_kernel(const double *__restrict__ w, const uint32_t *__restrict__ pix,
+                                                              const double *__restrict__ rgb, uint64_t n,
+                                                              double *__restrict__ accum) {
+  const uint64_t t = (uint64_t)blockIdx.x * blockDim.x + threadIdx.x;
+  if (t >= n) return;
+  add3(accum + 3 * (size_t)pix[t], mk3(w[3 * t] * rgb[3 * t], w[3 * t + 1] * rgb[3 * t + 1], w[3 * t + 2] * rgb[3 * t + 2]));
+}
+
+// image_buffer[i][j] /= DOF_TEST (render.cpp:135)
+__global__ void scale_kernel(double *a, uint64_t n, double dof) {
+  const uint64_t t = (uint64_t)blockIdx.x * blockDim.x + threadIdx.x;
+  if (t < n) a[t] = a[t] / dof;
+}
+
+// RenderImage's down-sampling loop (render.cpp:205-221) + R2Image::SetPixelRGB (R2Image.cpp:194-212): clamp every
+// supersample to [0,1], sum each pixel's block in the reference's (row, column) order, scale by the box weight,
+// truncate to a byte.  Output pixel (x, y) at rgb[(y * width + x) * 3], y = 0 the bottom row.
+__global__ void resolve_kernel(const double *__restrict__ accum, int width, int height, int aaf, int sh, uint8_t *rgb) {
+  const int x = blockIdx.x * blockDim.x + threadIdx.x, y = blockIdx.y * blockDim.y + threadIdx.y;
+  if (x >= width || y >= height) return;
+  const double box_weight = 1.0 / aaf / aaf;
+  double s[3] = {0, 0, 0};
+  for (int j = y * aaf; j < (y + 1) * aaf; j++)
+    for (int i = x * aaf; i < (x + 1) * aaf; i++)
+      for (int c = 0; c < 3; c++) {
+        double v = accum[3 * ((size_t)i * sh + j) + c];
+        if (v < 0) v = 0;
+        if (v > 1.0) v = 1.0;
+        s[c] += v;
+      }
+  for (int c = 0; c < 3; c++) rgb[3 * ((size_t)y * width + x) + c] = (uint8_t)(int)(255 * (box_weight * s[c]));
+}
+
+// ------------------------------------------------------------------------------------------------ host driver
+namespace {
+
+struct DevBuf {                      // frees on scope exit
+  void *p = nullptr;
+  ~DevBuf() { if (p) cudaFree(p); }
+  bool alloc(size_t bytes) { return cuda_ok(cudaMalloc(&p, bytes ? bytes : 1), "cudaMalloc(render)"); }
+  template <class T> T *as() const { return (T *)p; }
+};
+
+struct QueueStore {
+  DevBuf q, w, pix, count, rgb;
+  Queue view{};
+  bool alloc(unsigned long long cap) {
+    if (!q.alloc(sizeof(GiGatherQuery) * cap) || !w.alloc(sizeof(double) * 3 * cap) || !pix.alloc(sizeof(uint32_t) * cap) ||
+        !count.alloc(sizeof(unsigned long long)) || !rgb.alloc(sizeof(double) * 3 * cap))
+      return false;
+    view.q = q.as<GiGatherQuery>(); view.w = w.as<double>(); view.pix = pix.as<uint32_t>();
+    view.count = count.as<unsigned long long>(); view.cap = cap;
+    return true;
+  }
+};
+
+inline int grid_for(uint64_t n, int block, int sm_count, int per_sm) {
+  const uint64_t want = (n + block - 1) / block, cap = (uint64_t)sm_count * per_sm;
+  return (int)std::max<uint64_t>(1, std::min(want, cap));
+}
+
+struct Renderer {
+  GiContext *ctx;
+  ShadeEnv env;
+  cudaStream_t st;
+  double *accum;
+  RayStats *d_stats;
+  QueueStore qg, qc;
+
+  // d_stats[0]: primary + direct kernels; d_stats[1]: the path batch in flight (counted once the batch commits)
+  bool reset_queues() {
+    return cuda_ok(cudaMemsetAsync(d_stats + 1, 0, sizeof(RayStats), st), "memset(stats)") &&
+           cuda_ok(cudaMemsetAsync(qg.view.count, 0, sizeof(unsigned long long), st), "memset(queue)") &&
+           cuda_ok(cudaMemsetAsync(qc.view.count, 0, sizeof(unsigned long long), st), "memset(queue)");
+  }
+  // reads both queue counters; false on a CUDA error
+  bool queue_counts(unsigned long long &ng, unsigned long long &nc, RayStats *batch_stats = nullptr) {
+    unsigned long long h[2] = {0, 0};
+    if ((batch_stats && !cuda_ok(cudaMemcpyAsync(batch_stats, d_stats + 1, sizeof(RayStats), cudaMemcpyDeviceToHost, st), "D2H stats")) ||
+        !cuda_ok(cudaMemcpyAsync(&h[0], qg.view.count, 8, cudaMemcpyDeviceToHost, st), "D2H queue count") ||
+        !cuda_ok(cudaMemcpyAsync(&h[1], qc.view.count, 8, cudaMemcpyDeviceToHost, st), "D2H queue count") ||
+        !cuda_ok(cudaStreamSynchronize(st), "render sync"))
+      return false;
+    ng = h[0]; nc = h[1];
+    return true;
+  }
+  // EstimateRadiance for every request of a queue, then accum += weight * estimate
+  bool drain(QueueStore &qs, unsigned long long n, int map) {
+    if (n == 0) return true;
+    const GiParams &p = env.p;
+    const int k = map == GI_MAP_GLOBAL ? p.global_estimate_size : p.caustic_estimate_size;
+    const double r = map == GI_MAP_GLOBAL ? p.global_estimate_dist : p.caustic_estimate_dist;
+    const int filter = map == GI_MAP_GLOBAL ? p.global_filter : p.caustic_filter;
+    if (ctx->maps[map].dev.n == 0) return true;          // empty map: EstimateRadiance adds nothing
+    if (gi_gather_batch_device(ctx, map, qs.view.q, n, k, r, filter, &p, nullptr, nullptr, qs.rgb.as<double>(), st)) return false;
+    commit_requests_kernel<<<(unsigned)((n + 255) / 256), 256, 0, st>>>(qs.view.w, qs.view.pix, qs.rgb.as<double>(), n, accum);
+    ctx->launches++;
+    return cuda_ok(cudaGetLastError(), "commit_requests_kernel");
+  }
+};
+
+}  // namespace
+
+// Renders supersamples [pix0, pix1) of the sw x sh supersampled frame into `accum` (3 doubles per supersample,
+// zero-initialised by the caller), already divided by DOF_TEST.
+static int render_accum(GiContext *ctx, const GiParams &params, int sw, int sh, uint64_t pix0, uint64_t pix1, double *accum,
+                        RayStats *d_stats, RayStats &host_paths) {
+  Renderer R;
+  R.ctx = ctx; R.st = ctx->stream; R.accum = accum; R.d_stats = d_stats;
+  ShadeEnv &env = R.env;
+  env.sc = ctx->scene; env.materials = ctx->scene.materials; env.p = params;
+  env.ambient = ld3(ctx->ambient); env.background = ld3(ctx->background); env.eye = ld3(ctx->camera.eye);
+  env.radius = ctx->radius;
+  GiParams &p = env.p;
+  if (p.dof_test < 1) p.dof_test = 1;
+  // a map without photons contributes nothing: same switches MapPhotons flips (photonmap.cpp:339-361)
+  if (ctx->maps[GI_MAP_GLOBAL].dev.n == 0) { p.indirect_illum = 0; p.direct_photon_illum = 0; p.fast_global = 0; }
+  if (ctx->maps[GI_MAP_CAUSTIC].dev.n == 0) p.caustic_illum = 0;
+
+  DevBuf lights;
+  env.n_lights = (int)ctx->lights.size();
+  if (!lights.alloc(sizeof(GiLight) * ctx->lights.size())) return 1;
+  if (env.n_lights)
+    GI_CUDA(cudaMemcpyAsync(lights.p, ctx->lights.data(), sizeof(GiLight) * ctx->lights.size(), cudaMemcpyHostToDevice, R.st));
+  env.lights = lights.as<GiLight>();
+
+  Frame2 f;                                               // render.cpp:64-77
+  const GiCamera &cam = ctx->camera;
+  f.eye = ld3(cam.eye);
+  f.far_org = f.eye + ld3(cam.towards) * p.focus_depth;
+  f.far_right = ld3(cam.right) * tan(cam.xfov) * p.focus_depth;
+  f.far_up = ld3(cam.up) * tan(cam.yfov) * p.focus_depth;
+  f.u = normalized(ld3(cam.up)) * p.aperture_radius; f.v = normalized(ld3(cam.right)) * p.aperture_radius;
+  f.xc = sw / 2; f.yc = sh / 2; f.w = sw; f.h = sh; f.sw = sw; f.sh = sh; f.dof = p.dof_test;
+
+  const uint64_t chunk = 1ull << 22;                      // primary samples per pass
+  uint32_t batch = 1u << 21;                              // secondary paths per pass
+  const unsigned long long qcap = 1ull << 22;             // >= chunk (direct_kernel pushes at most one request per hit)
+  DevBuf hits, n_items, offs, item_rgb, item_pix, scan_tmp;
+  if (!hits.alloc(sizeof(PrimHit) * chunk) || !n_items.alloc(4 * (chunk + 1)) || !offs.alloc(8 * (chunk + 1)) ||
+      !item_rgb.alloc(sizeof(double) * 3 * batch) || !item_pix.alloc(4 * (size_t)batch) || !R.qg.alloc(qcap) || !R.qc.alloc(qcap))
+    return 1;
+  size_t scan_bytes = 0;
+  cub::DeviceScan::ExclusiveSum(nullptr, scan_bytes, n_items.as<uint32_t>(), offs.as<uint64_t>(), (int)(chunk + 1), R.st);
+  if (!scan_tmp.alloc(scan_bytes)) return 1;
+
+  const uint64_t s_begin = pix0 * p.dof_test, s_end = pix1 * p.dof_test;
+  for (uint64_t s0 = s_begin; s0 < s_end; s0 += chunk) {
+    const uint64_t n = std::min<uint64_t>(chunk, s_end - s0);
+    if (!R.reset_queues()) return 1;
+    primary_kernel<<<grid_for(n, 128, ctx->sm_count, 64), 128, 0, R.st>>>(env, f, s0, n, hits.as<PrimHit>(), accum, d_stats);
+    GI_CUDA(cudaMemsetAsync(n_items.p, 0, 4 * (chunk + 1), R.st));
+    direct_kernel<<<grid_for(n * 32, 128, ctx->sm_count, 16), 128, 0, R.st>>>(env, s0, n, hits.as<PrimHit>(), accum,
+                                                                             n_items.as<uint32_t>(), R.qg.view, R.qc.view, d_stats);
+    GI_CUDA(cudaGetLastError());
+    GI_CUDA(cub::DeviceScan::ExclusiveSum(scan_tmp.p, scan_bytes, n_items.as<uint32_t>(), offs.as<uint64_t>(), (int)(n + 1), R.st));
+    ctx->launches += 3;
+    uint64_t total_items = 0;
+    GI_CUDA(cudaMemcpyAsync(&total_items, offs.as<uint64_t>() + n, 8, cudaMemcpyDeviceToHost, R.st));
+    unsigned long long ng = 0, nc = 0;
+    if (!R.queue_counts(ng, nc)) return 1;
+    if (!R.drain(R.qg, ng, GI_MAP_GLOBAL) || !R.drain(R.qc, nc, GI_MAP_CAUSTIC)) return 1;
+
+    for (uint64_t item0 = 0; item0 < total_items;) {
+      const uint32_t m = (uint32_t)std::min<uint64_t>(batch, total_items - item0);
+      if (!R.reset_queues()) return 1;
+      path_kernel<<<(m + 127) / 128, 128, 0, R.st>>>(env, s0, n, hits.as<PrimHit>(), offs.as<uint64_t>(), item0, m,
+                                                    item_rgb.as<double>(), item_pix.as<uint32_t>(), R.qg.view, R.qc.view,
+                                                    d_stats + 1);
+      GI_CUDA(cudaGetLastError());
+      ctx->launches++;
+      RayStats bs;
+      if (!R.queue_counts(ng, nc, &bs)) return 1;
+      if (ng > qcap || nc > qcap) {                       // a queue overflowed: nothing was committed, repeat with fewer paths
+        if (batch <= 1024) { set_error("gi_render: gather queue overflow"); return 1; }
+        batch >>= 1;
+        continue;
+      }
+      commit_items_kernel<<<(m + 255) / 256, 256, 0, R.st>>>(item_rgb.as<double>(), item_pix.as<uint32_t>(), m, accum);
+      GI_CUDA(cudaGetLastError());
+      ctx->launches++;
+      if (!R.drain(R.qg, ng, GI_MAP_GLOBAL) || !R.drain(R.qc, nc, GI_MAP_CAUSTIC)) return 1;
+      host_paths.shadow += bs.shadow; host_paths.monte += bs.monte; host_paths.transmissive += bs.transmissive;
+      host_paths.specular += bs.specular; host_paths.indirect += bs.indirect; host_paths.caustic += bs.caustic;
+      item0 += m;
+    }
+  }
+  if (p.dof_test > 1 && pix1 > pix0) {
+    const uint64_t cnt = 3 * (pix1 - pix0);
+    scale_kernel<<<(unsigned)((cnt + 255) / 256), 256, 0, R.st>>>(accum + 3 * pix0, cnt, (double)p.dof_test);
+    ctx->launches++;
+  }
+  GI_CUDA(cudaStreamSynchronize(R.st));
+  return 0;
+}
+
+}  // namespace gi
+
+using namespace gi;
+
+// shared by gi_render and gi_render_float: returns the device accumulator of the supersampled frame
+static int render_common(GiContext *ctx, const GiParams *params, int width, int height, int aa, double **accum_out,
+                         int *sw_out, int *sh_out, GiRenderStats *stats) {
+  if (!ctx || !params) { set_error("gi_render: null argument"); return 1; }
+  if (!ctx->has_scene) { set_error("gi_render: no scene uploaded"); return 1; }
+  if (width < 1 || height < 1 || aa < 0 || aa > 6) { set_error("gi_render: bad image size or anti-aliasing level"); return 1; }
+  if (params->irradiance_cache) { set_error("gi_render: the irradiance cache (-irradiance_cache) is not implemented"); return 1; }
+  if (params->global_estimate_size < 1 || params->global_estimate_size > GI_MAX_K || params->caustic_estimate_size < 1 ||
+      params->caustic_estimate_size > GI_MAX_K) { set_error("gi_render: estimate size must be in [1, 512]"); return 1; }
+  for (int m = 0; m < 2; m++)
+    if (ctx->maps[m].dev.n > 0 && !ctx->maps[m].built) { set_error("gi_render: photon map not built (call gi_build_maps)"); return 1; }
+  const int aaf = 1 << aa;                                  // pow(2.0, aa), render.cpp:174
+  const uint64_t sw = (uint64_t)width * aaf, sh = (uint64_t)height * aaf, npix = sw * sh;
+  if (npix >= (1ull << 32)) { set_error("gi_render: supersampled frame too large"); return 1; }
+  GI_CUDA(cudaSetDevice(ctx->device));
+  double *accum = nullptr; RayStats *d_stats = nullptr;
+  GI_CUDA(cudaMalloc(&accum, sizeof(double) * 3 * npix));
+  if (!cuda_ok(cudaMalloc(&d_stats, 2 * sizeof(RayStats)), "cudaMalloc(stats)")) { cudaFree(accum); return 1; }
+  cudaEvent_t e0, e1; cudaEventCreate(&e0); cudaEventCreate(&e1);
+  int rc = 1;
+  RayStats hs[2]; RayStats paths; memset(&paths, 0, sizeof(paths));
+  do {
+    if (!cuda_ok(cudaMemsetAsync(accum, 0, sizeof(double) * 3 * npix, ctx->stream), "memset(accum)")) break;
+    if (!cuda_ok(cudaMemsetAsync(d_stats, 0, 2 * sizeof(RayStats), ctx->stream), "memset(stats)")) break;
+    cudaEventRecord(e0, ctx->stream);
+    // tile sharding across GPUs: rank r of w renders a contiguous run of supersample columns, the rest stays zero
+    const int world = params->world_size > 1 ? params->world_size : 1, rank = params->world_size > 1 ? params->rank : 0;
+    if (rank < 0 || rank >= world) { set_error("gi_render: rank outside [0, world_size)"); break; }
+    const uint64_t c0 = sw * rank / world, c1 = sw * (rank + 1) / world;
+    if (render_accum(ctx, *params, (int)sw, (int)sh, c0 * sh, c1 * sh, accum, d_stats, paths)) break;
+    cudaEventRecord(e1, ctx->stream);
+    if (!cuda_ok(cudaMemcpyAsync(hs, d_stats, 2 * sizeof(RayStats), cudaMemcpyDeviceToHost, ctx->stream), "D2H stats")) break;
+    if (!cuda_ok(cudaStreamSynchronize(ctx->stream), "render sync")) break;
+    rc = 0;
+  } while (0);
+  if (rc == 0 && stats) {
+    float ms = 0; cudaEventElapsedTime(&ms, e0, e1);
+    stats->screen_rays = hs[0].screen; stats->shadow_rays = hs[0].shadow + paths.shadow; stats->monte_rays = paths.monte;
+    stats->transmissive_samples = paths.transmissive; stats->specular_samples = paths.specular;
+    stats->indirect_samples = hs[0].indirect + paths.indirect; stats->caustic_samples = hs[0].caustic + paths.caustic;
+    stats->render_ms = ms;
+  }
+  cudaEventDestroy(e0); cudaEventDestroy(e1);
+  cudaFree(d_stats);
+  if (rc) { cudaFree(accum); return 1; }
+  *accum_out = accum; *sw_out = (int)sw; *sh_out = (int)sh;
+  return 0;
+}
+
+extern "C" {
+
+int gi_render_float(GiContext *ctx, const GiParams *params, int width, int height, int aa, double *rgb_out,
+                    GiRenderStats *stats) {
+  if (!rgb_out) { set_error("gi_render_float: null output buffer"); return 1; }
+  double *accum = nullptr; int sw = 0, sh = 0;
+  if (render_common(ctx, params, width, height, aa, &accum, &sw, &sh, stats)) return 1;
+  const bool ok = cuda_ok(cudaMemcpy(rgb_out, accum, sizeof(double) * 3 * (size_t)sw * sh, cudaMemcpyDeviceToHost), "D2H frame");
+  cudaFree(accum);
+  return ok ? 0 : 1;
+}
+
+int gi_render(GiContext *ctx, const GiParams *params, int width, int height, int aa, uint8_t *rgb_out,
+              GiRenderStats *stats) {
+  if (!rgb_out) { set_error("gi_render: null output buffer"); return 1; }
+  double *accum = nullptr; int sw = 0, sh = 0;
+  if (render_common(ctx, params, width, height, aa, &accum, &sw, &sh, stats)) return 1;
+  uint8_t *d_rgb = nullptr;
+  int rc = 1;
+  do {
+    if (!cuda_ok(cudaMalloc(&d_rgb, (size_t)width * height * 3), "cudaMalloc(image)")) break;
+    dim3 block(16, 16), grid((width + 15) / 16, (height + 15) / 16);
+    resolve_kernel<<<grid, block, 0, ctx->stream>>>(accum, width, height, 1 << aa, sh, d_rgb);
+    ctx->launches++;
+    if (!cuda_ok(cudaGetLastError(), "resolve_kernel")) break;
+    if (!cuda_ok(cudaMemcpyAsync(rgb_out, d_rgb, (size_t)width * height * 3, cudaMemcpyDeviceToHost, ctx->stream), "D2H image")) break;
+    if (!cuda_ok(cudaStreamSynchronize(ctx->stream), "render sync")) break;
+    rc = 0;
+  } while (0);
+  cudaFree(d_rgb); cudaFree(accum);
+  return rc;
+}
+
+}  // extern "C"

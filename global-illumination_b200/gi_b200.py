@@ -241,3 +241,102 @@ class Context:
     def gather_device(self, which, d_queries, n, k, r, filter, params, d_idx, d_count, d_rgb, stream=None):
         _check(lib().gi_gather_batch_device(self.handle, which, d_queries, n, k, float(r), filter, ctypes.byref(params),
                                             d_idx, d_count, d_rgb, stream))
+
+    def trace_photons(self, params):
+        """MapPhotons(): returns GiPhotonStats; the maps stay on the device, built."""
+        st = GiPhotonStats()
+        _check(lib().gi_trace_photons(self.handle, ctypes.byref(params), ctypes.byref(st)))
+        return st
+
+    def render_float(self, params, width, height, aa=0):
+        """The supersampled FP64 frame before clamping: array [W*2^aa, H*2^aa, 3], indexed [i][j] like the
+        reference's image_buffer (render.cpp:185)."""
+        f = 1 << aa
+        out = np.zeros((width * f, height * f, 3), dtype=np.float64)
+        st = GiRenderStats()
+        _check(lib().gi_render_float(self.handle, ctypes.byref(params), width, height, aa, out.ctypes.data, ctypes.byref(st)))
+        return out, st
+
+    def render(self, params, width, height, aa=0):
+        """RenderImage(): uint8 array [H, W, 3], row 0 = bottom row (R2Image order)."""
+        out = np.zeros((height, width, 3), dtype=np.uint8)
+        st = GiRenderStats()
+        _check(lib().gi_render(self.handle, ctypes.byref(params), width, height, aa, out.ctypes.data, ctypes.byref(st)))
+        return out, st
+
+
+def parse_flags(argv, params=None):
+    """The reference's flag grammar (ParseArgs, src/utils/io_utils.cpp:16-214) applied to a GiParams.
+    Returns (params, extra) with extra = {"aa", "width", "height", "real"} for the flags that are not render globals."""
+    p = params or default_params()
+    extra = {"aa": 2, "width": 1024, "height": 1024, "real": False}
+    it = iter(argv)
+
+    def nxt():
+        return next(it)
+    for a in it:
+        if a == "-v": p.verbose = 1
+        elif a == "-threads": p.threads = max(1, int(float(nxt())))
+        elif a == "-aa": extra["aa"] = abs(int(nxt()))
+        elif a == "-real": extra["real"] = True
+        elif a == "-no_fresnel": p.fresnel = 0
+        elif a == "-ir":
+            p.ir_air = float(nxt())
+            if p.ir_air <= 0: p.ir_air = 1e-6
+        elif a == "-no_ambient": p.ambient = 0
+        elif a == "-no_direct": p.direct_illum = 0
+        elif a == "-no_transmissive": p.transmissive_illum = 0
+        elif a == "-no_specular": p.specular_illum = 0
+        elif a == "-no_indirect": p.indirect_illum = 0
+        elif a == "-no_caustic": p.caustic_illum = 0
+        elif a == "-photon_viz": p.direct_photon_illum = 1
+        elif a == "-fast_global": p.fast_global = 1; p.direct_photon_illum = 1; p.indirect_illum = 0
+        elif a == "-cache": p.irradiance_cache = 1
+        elif a == "-no_monte": p.monte_carlo = 0
+        elif a == "-md": p.max_monte_depth = max(1, int(nxt()))
+        elif a == "-absorb": p.prob_absorb = max(0.0, float(nxt()))
+        elif a == "-no_rs": p.recursive_shadows = 0
+        elif a == "-no_dt": p.distrib_transmissive = 0
+        elif a == "-tt": p.transmissive_test = max(1, int(nxt()))
+        elif a == "-no_ds": p.distrib_specular = 0
+        elif a == "-st": p.specular_test = max(1, int(nxt()))
+        elif a == "-global": p.global_photon_count = max(1, int(nxt()))
+        elif a == "-caustic": p.caustic_photon_count = max(1, int(nxt()))
+        elif a == "-pd": p.max_photon_depth = max(1, int(nxt()))
+        elif a == "-it": p.indirect_test = max(1, int(nxt()))
+        elif a == "-gs": p.global_estimate_size = max(1, int(nxt()))
+        elif a == "-gd":
+            p.global_estimate_dist = float(nxt())
+            if p.global_estimate_dist < 0: p.global_estimate_dist = 1e-6
+        elif a in ("-gf", "-cf"):
+            kind = nxt()
+            f = None
+            if kind == "cone":
+                f = GI_FILTER_CONE
+                p.filter_const_k = float(nxt())
+                p.filter_const_k = max(1.0, p.filter_const_k)
+            elif kind == "gauss":
+                f = GI_FILTER_GAUSS
+            if f is not None:
+                if a == "-gf": p.global_filter = f
+                else: p.caustic_filter = f
+        elif a == "-cs": p.caustic_estimate_size = max(1, int(nxt()))
+        elif a == "-cd":
+            p.caustic_estimate_dist = float(nxt())
+            if p.caustic_estimate_dist < 0: p.caustic_estimate_dist = 1e-6
+        elif a == "-no_shadow": p.shadows = 0
+        elif a == "-no_ss": p.soft_shadows = 0
+        elif a == "-lt": p.light_test = max(1, int(nxt()))
+        elif a == "-ss": p.shadow_test = max(0, int(nxt()))
+        elif a == "-dof":
+            p.depth_of_field = 1
+            p.dof_test = max(1, int(nxt()))
+            p.focus_depth = max(1e-6, float(nxt()))
+            p.aperture_radius = float(nxt())
+            if p.aperture_radius <= 0: p.aperture_radius = 1e-6
+        elif a == "-resolution":
+            extra["width"] = abs(int(nxt())); extra["height"] = abs(int(nxt()))
+        elif a == "-seed": p.seed = int(nxt())
+        else:
+            raise ValueError("Invalid program argument: %s" % a)
+    return p, extra

@@ -11,7 +11,7 @@
 //   ref_harness photons    <in.scn> <out_prefix> <seed> [photonmap flags] (MapPhotons, photonmap.cpp:260)
 //   ref_harness gather     <photons.bin> <queries.bin> <out.bin> <k> <r> <filter 0|1|2> [threads]
 //                                                     (EstimateRadiance, photon_utils.cpp:72)
-//   ref_harness shade      <in.scn> <rays.bin> <out.bin> <seed> [photonmap flags + -load_global f -load_caustic f]
+//   ref_harness shade      <in.scn> <rays.bin> <out.bin> [-load_global f] [-load_caustic f] [photonmap flags]
 //                                                     (Intersects + RayTrace, render.cpp:119-124)
 // With -DGI_REF_MAIN the same translation unit is just the reference program (`photonmap_ref`).
 //
@@ -449,6 +449,65 @@ static int cmd_bench(int argc, char **argv) {
   return 0;
 }
 
+// ---------------------------------------------------------------- shade (render.cpp:119-131: Intersects + RayTrace)
+// usage: shade in.scn rays.bin out.bin [-load_global f.gipm] [-load_caustic f.gipm] [photonmap flags]
+// The flags go through the reference's own ParseArgs (io_utils.cpp:16-214).  A loaded photon file replaces
+// MapPhotons(): the photons are used as stored (already power-scaled) and the kd-tree is built like
+// photonmap.cpp:364-377; a map that is not loaded switches its illumination off, like an empty map (:349-361).
+// out.bin: u32 magic "GSHD", u32 n, n x f64 rgb[3] (what render.cpp:125/130 adds into image_buffer[i][j]).
+static int cmd_shade(int argc, char **argv) {
+  if (argc < 5) die("usage: shade in.scn rays.bin out.bin [-load_global f] [-load_caustic f] [photonmap flags]");
+  const char *gfile = NULL, *cfile = NULL;
+  std::vector<char *> av;
+  av.push_back((char *)"photonmap"); av.push_back(argv[2]); av.push_back((char *)"unused.png");
+  for (int i = 5; i < argc; i++) {
+    if (!strcmp(argv[i], "-load_global") && i + 1 < argc) gfile = argv[++i];
+    else if (!strcmp(argv[i], "-load_caustic") && i + 1 < argc) cfile = argv[++i];
+    else av.push_back(argv[i]);
+  }
+  char *in_name = NULL, *out_name = NULL; int w = 0, h = 0, aa_ = 0; bool real = false;
+  if (!ParseArgs((int)av.size(), av.data(), in_name, out_name, w, h, aa_, real)) die("bad flags");
+  load_scene(argv[2], real);
+  BuildDirectionLookupTable();
+  static std::vector<Photon> gph, cph;
+  if (gfile) gph = read_photons(gfile);
+  if (cfile) cph = read_photons(cfile);
+  for (size_t i = 0; i < gph.size(); i++) GLOBAL_PHOTONS.Insert(&gph[i]);
+  for (size_t i = 0; i < cph.size(); i++) CAUSTIC_PHOTONS.Insert(&cph[i]);
+  if (gph.empty()) { INDIRECT_ILLUM = false; DIRECT_PHOTON_ILLUM = false; FAST_GLOBAL = false; }
+  else GLOBAL_PMAP = new R3Kdtree<Photon *>(GLOBAL_PHOTONS, offsetof(struct Photon, position));
+  if (cph.empty()) CAUSTIC_ILLUM = false;
+  else CAUSTIC_PMAP = new R3Kdtree<Photon *>(CAUSTIC_PHOTONS, offsetof(struct Photon, position));
+  uint32_t n; std::vector<double> rays = read_rays(argv[3], n);
+  std::vector<double> out((size_t)n * 3, 0.0);
+  const R3Point eye = SCENE->Camera().Origin();
+  int threads = THREADS;
+  auto t0 = std::chrono::steady_clock::now();
+  auto work = [&](int id) {
+    RNInitThreadRandomness();
+    for (uint32_t i = id; i < n; i += threads) {
+      const double *r = &rays[(size_t)i * 6];
+      R3Ray ray(R3Point(r[0], r[1], r[2]), R3Vector(r[3], r[4], r[5]), TRUE);
+      R3SceneNode *node; R3SceneElement *element; R3Shape *shape; R3Point point; R3Vector normal; RNScalar t;
+      RNRgb color = RNblack_rgb;
+      if (SCENE->Intersects(ray, &node, &element, &shape, &point, &normal, &t)) RayTrace(element, point, normal, ray, eye, color);
+      else color = SCENE->Background();
+      out[(size_t)i * 3] = color.R(); out[(size_t)i * 3 + 1] = color.G(); out[(size_t)i * 3 + 2] = color.B();
+    }
+    RNClearThreadRandomness();
+  };
+  std::vector<std::thread> th;
+  for (int i = 1; i < threads; i++) th.emplace_back(work, i);
+  work(0);
+  for (auto &x : th) x.join();
+  double sec = std::chrono::duration<double>(std::chrono::steady_clock::now() - t0).count();
+  FILE *f = fopen(argv[4], "wb"); if (!f) die("cannot open output");
+  uint32_t hdr[2] = {0x44485347, n};
+  fwrite(hdr, 4, 2, f); fwrite(out.data(), 8, out.size(), f); fclose(f);
+  printf("{\"cmd\": \"shade\", \"rays\": %u, \"threads\": %d, \"seconds\": %.6f}\n", n, threads, sec);
+  return 0;
+}
+
 int main(int argc, char **argv) {
   if (argc < 2) die("usage: ref_harness <dump_scene|camrays|isect|photons|gather|shade> ...");
   std::string c = argv[1];
@@ -458,6 +517,7 @@ int main(int argc, char **argv) {
   if (c == "photons") return cmd_photons(argc, argv);
   if (c == "gather") return cmd_gather(argc, argv);
   if (c == "bench") return cmd_bench(argc, argv);
+  if (c == "shade") return cmd_shade(argc, argv);
   die("unknown command");
   return 2;
 }

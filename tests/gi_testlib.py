@@ -15,6 +15,7 @@ REF_HARNESS = os.path.join(ROOT, "oracle", "_ref", "ref_harness")
 REF_INPUT = "/root/reference/input"
 SCENE_TOOL = os.path.join(PKG, "bin", "gi_scene_tool")
 SCENES_DIR = os.path.join(ROOT, "tests", "golden", "scenes")
+GOLDEN = os.path.join(ROOT, "tests", "golden")
 
 RAYS_MAGIC = 0x59415247
 HITS_MAGIC = 0x54494847

@@ -1,0 +1,134 @@
+"""gi_render / gi_render_float on the GPU against the reference's own RayTrace (fixtures: tests/golden/render.npz,
+made by tests/golden/make_render_golden.py from oracle/_ref/ref_harness shade).
+
+Deterministic flag sets are compared per supersample to 1e-9 (the north-star tolerance for deterministic-path
+radiance is 1e-4 relative); stochastic ones through block means against the mean of 64 reference runs."""
+import os
+import numpy as np
+import pytest
+
+import gi_b200
+from gi_testlib import GOLDEN
+
+pytestmark = pytest.mark.gpu
+
+G = np.load(os.path.join(GOLDEN, "render.npz"))
+DET = sorted(k for k in G.files if "__" not in k and k + "__sem" not in G.files)
+STO = sorted(k for k in G.files if "__" not in k and k + "__sem" in G.files)
+
+
+def setup(ctx, name):
+    scene, w, h, flags, maps = [str(x) for x in G[name + "__meta"]]
+    hs = gi_b200.HostScene(os.path.join(GOLDEN, scene + ".gisc"))
+    ctx.upload_scene(hs)
+    maps = [m for m in maps.split(",") if m]
+    for which, m in ((gi_b200.GI_MAP_GLOBAL, "global"), (gi_b200.GI_MAP_CAUSTIC, "caustic")):
+        if m in maps:
+            ctx.load_photons_file(which, os.path.join(GOLDEN, f"cornell.{m}.gipm"))
+        else:
+            ctx.load_photons(which, np.zeros(0, dtype=gi_b200.PHOTON))
+    params, _ = gi_b200.parse_flags(flags.split())
+    ctx.build_maps(params)
+    return params, int(w), int(h)
+
+
+@pytest.mark.parametrize("name", DET)
+def test_deterministic_radiance(gpu_ctx, name):
+    params, w, h = setup(gpu_ctx, name)
+    img, st = gpu_ctx.render_float(params, w, h, 0)
+    ref = G[name]
+    assert img.shape == ref.shape
+    err = np.abs(img - ref) / np.maximum(1.0, np.abs(ref))
+    assert err.max() < 1e-9, f"{name}: max rel err {err.max()} at {np.unravel_index(err.argmax(), err.shape)}"
+    assert st.screen_rays == int((np.abs(ref - ref[0, 0]).sum(-1) >= 0).sum()) or st.screen_rays <= w * h
+
+
+@pytest.mark.parametrize("name", STO)
+def test_stochastic_radiance(gpu_ctx, name):
+    params, w, h = setup(gpu_ctx, name)
+    runs = 16
+    imgs = []
+    for s in range(runs):
+        params.seed = 1000 + s
+        imgs.append(gpu_ctx.render_float(params, w, h, 0)[0])
+    imgs = np.stack(imgs)
+    mean = imgs.mean(0)
+    sem = imgs.std(0, ddof=1) / np.sqrt(runs)
+    ref, ref_sem = G[name], G[name + "__sem"]
+    # 4x4 block means: averages out the heavy-tailed per-pixel noise of path tracing
+    def blocks(a):
+        return a.reshape(w // 4, 4, h // 4, 4, 3).mean(axis=(1, 3))
+    def blocks_var(a):
+        return (a ** 2).reshape(w // 4, 4, h // 4, 4, 3).sum(axis=(1, 3)) / 256.0
+    d = blocks(mean) - blocks(ref)
+    sigma = np.sqrt(blocks_var(sem) + blocks_var(ref_sem)) + 1e-3 * np.maximum(1.0, np.abs(blocks(ref)))
+    z = np.abs(d) / sigma
+    assert np.mean(z > 4) < 0.02, f"{name}: {np.mean(z > 4):.3f} of blocks beyond 4 sigma, worst {z.max():.1f}"
+    # whole-image mean: within 2 %
+    gm, gr = mean.mean(axis=(0, 1)), ref.mean(axis=(0, 1))
+    assert np.all(np.abs(gm - gr) <= 0.02 * np.maximum(gr, 1e-3) + 4 * np.sqrt((sem ** 2).mean() / (w * h))), (name, gm, gr)
+    # same seed -> same image (to the last bits of the atomic adds)
+    params.seed = 1000
+    again = gpu_ctx.render_float(params, w, h, 0)[0]
+    assert np.allclose(again, imgs[0], rtol=1e-9, atol=1e-12)
+
+
+def test_resolve_matches_reference_downsampling(gpu_ctx):
+    """gi_render = clamp -> 2^aa box filter -> truncating quantisation (render.cpp:205-221, R2Image.cpp:194-212)."""
+    params, w, h = setup(gpu_ctx, "cornell_direct")
+    aa = 2
+    f, _ = gpu_ctx.render_float(params, 10, 10, aa)
+    u8, _ = gpu_ctx.render(params, 10, 10, aa)
+    c = np.clip(f, 0.0, 1.0)
+    acc = np.zeros((10, 10, 3))
+    for j in range(40):
+        for i in range(40):
+            acc[i // 4, j // 4] += c[i, j]
+    want = (255 * ((1.0 / 4 / 4) * acc)).astype(np.uint8)       # [x][y]
+    assert np.array_equal(u8, want.transpose(1, 0, 2))
+
+
+def test_aa_supersamples_are_the_reference_rays(gpu_ctx):
+    """At aa = 1 the supersampled frame of a WxH image is the aa = 0 frame of a 2Wx2H image (photonmap.cpp:465-468)."""
+    params, w, h = setup(gpu_ctx, "art3_direct")
+    a, _ = gpu_ctx.render_float(params, 20, 15, 1)
+    b, _ = gpu_ctx.render_float(params, 40, 30, 0)
+    assert np.array_equal(a, b)
+    assert np.abs(b - G["art3_direct"]).max() < 1e-9
+
+
+def test_depth_of_field_converges_to_pinhole(gpu_ctx):
+    """-dof with a vanishing aperture reproduces the pinhole image; a real aperture blurs but keeps the mean."""
+    params, w, h = setup(gpu_ctx, "cornell_direct")
+    pin, _ = gpu_ctx.render_float(params, w, h, 0)
+    p2, _ = gi_b200.parse_flags("-no_monte -no_transmissive -no_specular -dof 4 100.0 1e-9".split())
+    img, st = gpu_ctx.render_float(p2, w, h, 0)
+    assert np.abs(img - pin).max() < 1e-5
+    assert st.screen_rays == 4 * w * h or st.screen_rays <= 4 * w * h
+    p3, _ = gi_b200.parse_flags("-no_monte -no_transmissive -no_specular -dof 16 100.0 0.2".split())
+    blur, _ = gpu_ctx.render_float(p3, w, h, 0)
+    assert abs(blur.mean() - pin.mean()) < 0.05 * pin.mean()
+    assert np.abs(blur - pin).max() > 1e-3
+
+
+def test_rank_sharding_partitions_the_frame(gpu_ctx):
+    """world_size ranks render disjoint column ranges whose sum is the single-GPU frame (tile sharding)."""
+    params, w, h = setup(gpu_ctx, "specular_md1")
+    full, _ = gpu_ctx.render_float(params, w, h, 0)
+    acc = np.zeros_like(full)
+    for r in range(3):
+        params.rank, params.world_size = r, 3
+        part, _ = gpu_ctx.render_float(params, w, h, 0)
+        assert np.count_nonzero(acc * part) == 0
+        acc += part
+    assert np.array_equal(acc, full)
+
+
+def test_render_errors(gpu_ctx):
+    params, w, h = setup(gpu_ctx, "cornell_direct")
+    params.irradiance_cache = 1
+    with pytest.raises(gi_b200.GiError):
+        gpu_ctx.render_float(params, w, h, 0)
+    params.irradiance_cache = 0
+    with pytest.raises(gi_b200.GiError):
+        gpu_ctx.render_float(params, 0, h, 0)
