@@ -459,7 +459,9 @@ static int render_accum(GiContext *ctx, const GiParams &params, int sw, int sh, 
   f.eye = ld3(cam.eye);
   f.far_org = f.eye + ld3(cam.towards) * p.focus_depth;
   f.far_right = ld3(cam.right) * tan(cam.xfov) * p.focus_depth;
-  f.far_up = ld3(cam.up) * tan(cam.yfov) * p.focus_depth;
+  // SCENE->SetViewport() re-derives the vertical field of view from the frame's aspect ratio (R3Viewer.cpp:76-84)
+  const double yfov = atan(((double)sh / (double)sw) * tan(cam.xfov));
+  f.far_up = ld3(cam.up) * tan(yfov) * p.focus_depth;
   f.u = normalized(ld3(cam.up)) * p.aperture_radius; f.v = normalized(ld3(cam.right)) * p.aperture_radius;
   f.xc = sw / 2; f.yc = sh / 2; f.w = sw; f.h = sh; f.sw = sw; f.sh = sh; f.dof = p.dof_test;
 
