@@ -44,7 +44,20 @@ static int build_rec(Sim &s, std::vector<int> &idx, int lo, int hi, float *box_o
   return me;
 }
 
+#include "rng.cuh"
+
 extern "C" {
+
+// the renderer's Philox4x32-10 (csrc/rng.cuh) compiled for the host: known-answer + stream checks
+void sim_philox_block(const uint32_t *ctr, const uint32_t *key, uint32_t *out) {
+  uint32_t c0 = ctr[0], c1 = ctr[1], c2 = ctr[2], c3 = ctr[3], k0 = key[0], k1 = key[1];
+  for (int i = 0; i < 10; i++) { gi::philox_round(c0, c1, c2, c3, k0, k1); k0 += 0x9E3779B9u; k1 += 0xBB67AE85u; }
+  out[0] = c0; out[1] = c1; out[2] = c2; out[3] = c3;
+}
+void sim_rng_doubles(uint64_t seed, uint64_t index, uint32_t stage, uint32_t sample, int n, double *out) {
+  gi::Rng r; gi::rng_init(r, seed, index, stage, sample);
+  for (int i = 0; i < n; i++) out[i] = gi::rng_double(r);
+}
 
 void *sim_scene_load(const char *gisc) {
   Sim *s = new Sim(); std::string err;

@@ -55,11 +55,11 @@ def test_stochastic_radiance(gpu_ctx, name):
     mean = imgs.mean(0)
     sem = imgs.std(0, ddof=1) / np.sqrt(runs)
     ref, ref_sem = G[name], G[name + "__sem"]
-    # 4x4 block means: averages out the heavy-tailed per-pixel noise of path tracing
+    # 6x6 block means: averages out the heavy-tailed per-pixel noise of path tracing
     def blocks(a):
-        return a.reshape(w // 4, 4, h // 4, 4, 3).mean(axis=(1, 3))
+        return a.reshape(w // 6, 6, h // 6, 6, 3).mean(axis=(1, 3))
     def blocks_var(a):
-        return (a ** 2).reshape(w // 4, 4, h // 4, 4, 3).sum(axis=(1, 3)) / 256.0
+        return (a ** 2).reshape(w // 6, 6, h // 6, 6, 3).sum(axis=(1, 3)) / 36.0 ** 2
     d = blocks(mean) - blocks(ref)
     sigma = np.sqrt(blocks_var(sem) + blocks_var(ref_sem)) + 1e-3 * np.maximum(1.0, np.abs(blocks(ref)))
     z = np.abs(d) / sigma
@@ -67,6 +67,9 @@ def test_stochastic_radiance(gpu_ctx, name):
     # whole-image mean: within 2 %
     gm, gr = mean.mean(axis=(0, 1)), ref.mean(axis=(0, 1))
     assert np.all(np.abs(gm - gr) <= 0.02 * np.maximum(gr, 1e-3) + 4 * np.sqrt((sem ** 2).mean() / (w * h))), (name, gm, gr)
+    # the estimator has the reference's variance, not just its mean (a correlated sampler would pass the mean test)
+    ours_std, ref_std = imgs.std(0, ddof=1).mean(), G[name + "__std"].mean()
+    assert 0.8 * ref_std < ours_std < 1.25 * ref_std, (name, ours_std, ref_std)
     # same seed -> same image (to the last bits of the atomic adds)
     params.seed = 1000
     again = gpu_ctx.render_float(params, w, h, 0)[0]
@@ -105,9 +108,10 @@ def test_depth_of_field_converges_to_pinhole(gpu_ctx):
     img, st = gpu_ctx.render_float(p2, w, h, 0)
     assert np.abs(img - pin).max() < 1e-5
     assert st.screen_rays == 4 * w * h or st.screen_rays <= 4 * w * h
-    p3, _ = gi_b200.parse_flags("-no_monte -no_transmissive -no_specular -dof 16 100.0 0.2".split())
+    # focus on the back wall region: the image changes, but stays an image of the same scene
+    p3, _ = gi_b200.parse_flags("-no_monte -no_transmissive -no_specular -dof 16 6.0 0.05".split())
     blur, _ = gpu_ctx.render_float(p3, w, h, 0)
-    assert abs(blur.mean() - pin.mean()) < 0.05 * pin.mean()
+    assert abs(blur.mean() - pin.mean()) < 0.1 * pin.mean()
     assert np.abs(blur - pin).max() > 1e-3
 
 
