@@ -1,0 +1,381 @@
+// csrc/photon_trace.cu -- gi_trace_photons: the reference's MapPhotons (src/photonmap.cpp:260-436) on the GPU.
+//
+// The reference gives every CPU thread a share of the photon budget and lets it emit photons light by light in
+// adaptive rounds (Threadable_PhotonTracer, photonmap.cpp:144-257): each round emits
+// (target - stored) / average_stores_per_photon / slowdown + 1 photons, split over the lights by power, and
+// PhotonTrace (photontracer.cpp:28-176) follows every photon through its bounces with Russian roulette, storing it
+// at diffuse surfaces.  Here one round is ONE kernel launch with a thread per emitted photon; stored photons are
+// appended through an atomic cursor together with the key (emitted photon number, bounce), and once the rounds
+// are over the photons are sorted by that key, so a map depends on the seed only -- not on scheduling.  One rank =
+// one reference "thread": with world_size > 1 each rank traces COUNT / world_size photons on its own streams, the
+// host all-gathers them and applies the power scale (gi_scale_photon_power) before gi_build_maps.
+#include <cub/cub.cuh>
+#include <algorithm>
+#include <cmath>
+#include <cstring>
+#include <vector>
+#include "context.h"
+#include "kdtree_build.h"
+#include "shade.cuh"
+
+namespace gi {
+
+enum { STAGE_PHOTON = 8 };           // Philox stage = STAGE_PHOTON + map
+enum { MAP_GLOBAL = 0, MAP_CAUSTIC = 1 };
+
+struct PhotonSink { GiPhoton *photons; uint64_t *keys; unsigned long long *count; unsigned long long cap; };
+
+// RNRgb_to_RGBE, graphics_utils.cpp:50-62
+GI_DEV void rgbe_encode(D3 c, uint8_t *out) {
+  const double mx = max_channel(c);
+  if (!(mx > 0)) { out[0] = out[1] = out[2] = 0; int e; frexp(0.0, &e); out[3] = (uint8_t)(e + 128); return; }
+  int exponent;
+  const double mantissa = frexp(mx, &exponent);
+  out[0] = (uint8_t)(int)(256.0 * c.x / mx * mantissa);
+  out[1] = (uint8_t)(int)(256.0 * c.y / mx * mantissa);
+  out[2] = (uint8_t)(int)(256.0 * c.z / mx * mantissa);
+  out[3] = (uint8_t)(exponent + 128);
+}
+// RGBE_to_RNRgb, graphics_utils.cpp:65-79
+GI_DEV D3 rgbe_decode(const uint8_t *in) {
+  if (!in[3]) return mk3(0, 0, 0);
+  const double inverse = ldexp(1.0, ((int)in[3]) - 128 - 8);
+  return mk3(in[0], in[1], in[2]) * inverse;
+}
+
+// StorePhoton, photon_utils.cpp:40-66
+GI_DEV void store_photon(const PhotonSink &sink, D3 power, D3 incident, D3 point, uint64_t key) {
+  const unsigned long long i = atomicAdd(sink.count, 1ull);
+  if (i >= sink.cap) return;
+  const double PI = 3.14159265358979323846, TWO_PI = 6.28318530717958647692;
+  GiPhoton ph;
+  ph.position[0] = point.x; ph.position[1] = point.y; ph.position[2] = point.z;
+  rgbe_encode(power, ph.rgbe);
+  const int phi = (uint8_t)(int)(255.0 * (atan2(incident.y, incident.x) + PI) / (TWO_PI));
+  const int theta = (uint8_t)(int)(255.0 * acos(fmin(1.0, fmax(-1.0, incident.z))) / PI);
+  ph.direction = (uint16_t)(phi * 256 + theta);
+  ph.pad = 0;
+  sink.photons[i] = ph;
+  sink.keys[i] = key;
+}
+
+// PhotonTrace, photontracer.cpp:28-159
+GI_DEV void photon_trace(const ShadeEnv &env, RayD ray, D3 photon, int map_type, uint64_t id, Rng &rng, const PhotonSink &sink) {
+  const GiParams &p = env.p;
+  D3 ray_start = ray.o;
+  bool store = map_type == MAP_GLOBAL && !p.fast_global;
+  for (int iter = 0; iter < p.max_photon_depth; iter++) {
+    HitRec h;
+    closest_hit(env.sc, ray, h);
+    if (h.prim < 0) break;
+    const Brdf b = load_brdf(env.materials[env.sc.elements[h.element].material]);
+    const D3 point = h.p, normal = h.n;
+    const D3 view = normalized(point - ray_start);
+    const double cos_theta = dot(normal, -view);
+    if (b.diffuse && store) store_photon(sink, photon, view, point, (id << 8) | (uint64_t)(iter & 255));
+    double r_coeff = 0;
+    if (p.fresnel && b.transparent) r_coeff = reflection_coeff(cos_theta, b.ir, p.ir_air);
+    const double mc = max_channel(photon);
+    const double prob_diffuse = max_channel(mul3(b.kd, photon)) / mc;
+    double prob_transmission = max_channel(mul3(b.kt, photon)) / mc;
+    const double prob_specular = (max_channel(mul3(b.ks, photon)) / mc) + r_coeff * prob_transmission;
+    prob_transmission *= (1.0 - r_coeff);
+    const double prob_total = prob_diffuse + prob_transmission + prob_specular + p.prob_absorb;
+    double rnd = rng_double(rng);
+    if (prob_total > 1.0) rnd *= prob_total;
+    D3 bounce;
+    if (rnd < prob_diffuse) {
+      if (map_type == MAP_CAUSTIC) break;
+      store = true;
+      bounce = diffuse_sample(normal, cos_theta, rng);
+      photon = mul3(photon, b.kd / prob_diffuse);
+    } else if (rnd < prob_diffuse + prob_transmission) {
+      if (map_type == MAP_CAUSTIC) store = true;
+      const D3 exact = transmissive_bounce(normal, view, cos_theta, b.ir, p.ir_air);
+      bounce = p.distrib_transmissive ? specular_sample(exact, b.n, cos_theta, rng) : exact;
+      photon = mul3(photon, (b.kt * (1.0 - r_coeff)) / prob_transmission);
+    } else if (rnd < prob_diffuse + prob_transmission + prob_specular) {
+      if (map_type == MAP_CAUSTIC) store = true;
+      const D3 exact = reflective_bounce(normal, view, cos_theta);
+      bounce = p.distrib_specular ? specular_sample(exact, b.n, cos_theta, rng) : exact;
+      photon = mul3(photon, (b.ks + b.kt * r_coeff) / prob_specular);
+    } else break;
+    ray_start = point + bounce * GI_EPS;
+    ray.o = ray_start; ray.d = bounce;
+  }
+}
+
+// basis of a disk with normal n: EmitPhotons, photontracer.cpp:204-215 / 296-307
+GI_DEV void disk_basis(D3 n, double radius, D3 &u, D3 &v) {
+  u = mk3(n.y, -n.x, 0);
+  if (1.0 - fabs(n.z) < 0.1) u = mk3(n.z, 0, -n.x);
+  v = cross(u, n);
+  u = normalized(u) * radius; v = normalized(v) * radius;
+}
+
+// EmitPhotons (photontracer.cpp:182-373) for one round: thread t emits photon number id0 + t from the light whose
+// range [first[l], first[l+1]) holds t.
+__global__ void __launch_bounds__(128) emit_kernel(ShadeEnv env, D3 centroid, int map_type, uint64_t id0, uint64_t n,
+                                                   const uint64_t *__restrict__ first, PhotonSink sink) {
+  for (uint64_t t = (uint64_t)blockIdx.x * blockDim.x + threadIdx.x; t < n; t += (uint64_t)gridDim.x * blockDim.x) {
+    int li = 0;
+    while (li + 1 < env.n_lights && t >= first[li + 1]) li++;
+    const GiLight &l = env.lights[li];
+    D3 photon = ld3(l.color);                                           // NormalizeColor, graphics_utils.cpp:25-36
+    const double total = photon.x + photon.y + photon.z;
+    if (total > 0) photon = photon / total;
+    const uint64_t id = id0 + t;
+    Rng rng; rng_init(rng, env.p.seed, id, STAGE_PHOTON + map_type, 0);
+    const D3 ln = ld3(l.direction);
+    RayD ray;
+    if (l.type == GI_LIGHT_DIR) {
+      const D3 center = centroid - ln * env.radius * 3.0;
+      D3 u, v; disk_basis(ln, env.radius, u, v);
+      double r1, r2;
+      do { r1 = rng_double(rng) * 2.0 - 1.0; r2 = rng_double(rng) * 2.0 - 1.0; } while (r1 * r1 + r2 * r2 > 1.0);
+      ray.o = u * r1 + v * r2 + center + ln * GI_EPS; ray.d = ln;
+    } else if (l.type == GI_LIGHT_POINT) {
+      double x, y, z;
+      do { x = rng_double(rng) * 2.0 - 1.0; y = rng_double(rng) * 2.0 - 1.0; z = rng_double(rng) * 2.0 - 1.0; } while (x * x + y * y + z * z > 1.0);
+      ray.o = ld3(l.position); ray.d = normalized(mk3(x, y, z));
+    } else if (l.type == GI_LIGHT_SPOT) {
+      const double cutoff = fabs(cos(l.cutoff));
+      int attempts_left = 20;
+      D3 dir;
+      do { dir = specular_sample(ln, l.dropoff, 1.0, rng); } while (dot(dir, ln) < cutoff && attempts_left-- > 0);
+      if (attempts_left == 0) dir = specular_sample(ln, l.dropoff, cutoff, rng);   // sic (photontracer.cpp:279-282)
+      ray.o = ld3(l.position); ray.d = dir;
+    } else if (l.type == GI_LIGHT_AREA) {
+      D3 u, v; disk_basis(ln, l.radius, u, v);
+      double r1, r2;
+      do { r1 = rng_double(rng) * 2.0 - 1.0; r2 = rng_double(rng) * 2.0 - 1.0; } while (r1 * r1 + r2 * r2 > 1.0);
+      ray.o = u * r1 + v * r2 + ld3(l.position) + ln * GI_EPS;
+      ray.d = diffuse_sample(ln, 1.0, rng);
+    } else {
+      const D3 a1 = ld3(l.axis1) * l.len1, a2 = ld3(l.axis2) * l.len2;
+      const double r1 = rng_double(rng) - 0.5, r2 = rng_double(rng) - 0.5;
+      ray.o = a1 * r1 + a2 * r2 + ld3(l.position) + ln * GI_EPS;
+      ray.d = diffuse_sample(ln, 1.0, rng);
+    }
+    photon_trace(env, ray, photon, map_type, id, rng, sink);
+  }
+}
+
+// the power scale of MapPhotons (photonmap.cpp:339-361): decode, multiply, re-encode
+__global__ void scale_power_kernel(GiPhoton *ph, uint64_t n, double factor) {
+  const uint64_t t = (uint64_t)blockIdx.x * blockDim.x + threadIdx.x;
+  if (t >= n) return;
+  uint8_t e[4] = {ph[t].rgbe[0], ph[t].rgbe[1], ph[t].rgbe[2], ph[t].rgbe[3]};
+  const D3 c = rgbe_decode(e) * factor;
+  rgbe_encode(c, e);
+  ph[t].rgbe[0] = e[0]; ph[t].rgbe[1] = e[1]; ph[t].rgbe[2] = e[2]; ph[t].rgbe[3] = e[3];
+}
+
+__global__ void permute_kernel(const GiPhoton *__restrict__ in, const uint32_t *__restrict__ order, uint64_t n, GiPhoton *__restrict__ out) {
+  const uint64_t t = (uint64_t)blockIdx.x * blockDim.x + threadIdx.x;
+  if (t < n) out[t] = in[order[t]];
+}
+__global__ void iota_kernel(uint32_t *a, uint64_t n) {
+  const uint64_t t = (uint64_t)blockIdx.x * blockDim.x + threadIdx.x;
+  if (t < n) a[t] = (uint32_t)t;
+}
+
+// LightPower, graphics_utils.cpp:223-258
+static double light_power(const GiLight &l, double scene_radius) {
+  const double PI = 3.14159265358979323846, TWO_PI = 6.28318530717958647692;
+  double area = 1.0, flux = 4.0 * PI;
+  if (l.type == GI_LIGHT_DIR) { area = PI * pow(scene_radius, 2.0); flux = 1.0; }
+  else if (l.type == GI_LIGHT_AREA) { area = PI * pow(l.radius, 2.0); flux /= 2.0; }
+  else if (l.type == GI_LIGHT_RECT) {
+    const D3 a1 = ld3(l.axis1) * l.len1, a2 = ld3(l.axis2) * l.len2;
+    area = length(cross(a1, a2)); flux /= 2.0;
+  } else if (l.type == GI_LIGHT_SPOT) flux = TWO_PI / (l.dropoff + 1.0) * (1.0 - pow(cos(l.cutoff), l.dropoff + 1.0));
+  return (l.color[0] + l.color[1] + l.color[2]) * area * flux;
+}
+
+namespace {
+struct Buf {
+  void *p = nullptr;
+  ~Buf() { if (p) cudaFree(p); }
+  bool alloc(size_t bytes) { if (p) { cudaFree(p); p = nullptr; } return cuda_ok(cudaMalloc(&p, bytes ? bytes : 1), "cudaMalloc(photon trace)"); }
+  template <class T> T *as() const { return (T *)p; }
+};
+}  // namespace
+
+// One map: the adaptive rounds of Threadable_PhotonTracer.  Leaves the photons (sorted by emission key, unscaled)
+// in ctx->maps[map].raw.
+static int trace_map(GiContext *ctx, const ShadeEnv &env_in, int map_type, int target, const std::vector<double> &light_powers,
+                     double total_power, uint64_t id_base, uint64_t &emitted_out, int &rounds_out) {
+  ShadeEnv env = env_in;
+  cudaStream_t st = ctx->stream;
+  const int nl = env.n_lights;
+  unsigned long long cap = (unsigned long long)target + (unsigned long long)target / 2 + 65536;
+  Buf photons, keys, count, first;
+  if (!photons.alloc(sizeof(GiPhoton) * cap) || !keys.alloc(8 * cap) || !count.alloc(8) || !first.alloc(8 * (size_t)(nl + 1))) return 1;
+  GI_CUDA(cudaMemsetAsync(count.p, 0, 8, st));
+  unsigned long long stored = 0;
+  uint64_t emitted = 0;
+  // photonmap.cpp:157-196 (global) / :213-250 (caustic)
+  double average_bounce_rate = map_type == MAP_GLOBAL ? 4.0 : (double)env.p.max_photon_depth;
+  double slowdown_factor = 1.0;
+  int attempts_left = 10;
+  const D3 centroid = ld3(ctx->centroid);
+  while (stored < (unsigned long long)target && attempts_left > 0) {
+    const int emit_goal = (int)((int)(target - (long long)stored) / average_bounce_rate / slowdown_factor + 1);
+    std::vector<uint64_t> h_first(nl + 1, 0);
+    for (int i = 0; i < nl; i++) {
+      int num = (int)ceil(emit_goal * (light_powers[i] / total_power));
+      if (!ctx->lights[i].active || num < 0) num = 0;          // EmitPhotons returns at once for an inactive light,
+      h_first[i + 1] = h_first[i] + (uint64_t)num;             // but photons_assigned still counts its share (:169-172)
+    }
+    uint64_t assigned = 0;
+    for (int i = 0; i < nl; i++) assigned += (uint64_t)std::max(0, (int)ceil(emit_goal * (light_powers[i] / total_power)));
+    const uint64_t n = h_first[nl];
+    for (;;) {                                               // repeated only if the sink was too small
+      GI_CUDA(cudaMemcpyAsync(first.p, h_first.data(), 8 * (size_t)(nl + 1), cudaMemcpyHostToDevice, st));
+      PhotonSink sink{photons.as<GiPhoton>(), keys.as<uint64_t>(), count.as<unsigned long long>(), cap};
+      if (n > 0) {
+        const uint64_t want = (n + 127) / 128, gcap = (uint64_t)ctx->sm_count * 64;
+        emit_kernel<<<(unsigned)std::max<uint64_t>(1, std::min(want, gcap)), 128, 0, st>>>(env, centroid, map_type, id_base + emitted, n,
+                                                                                           first.as<uint64_t>(), sink);
+        ctx->launches++;
+        GI_CUDA(cudaGetLastError());
+      }
+      unsigned long long now = 0;
+      GI_CUDA(cudaMemcpyAsync(&now, count.p, 8, cudaMemcpyDeviceToHost, st));
+      GI_CUDA(cudaStreamSynchronize(st));
+      if (now <= cap) { stored = now; break; }
+      // grow the sink, keep what earlier rounds stored, and run this round again (same streams -> same photons)
+      const unsigned long long ncap = std::max(now + now / 2, cap * 2);
+      Buf np, nk;
+      if (!np.alloc(sizeof(GiPhoton) * ncap) || !nk.alloc(8 * ncap)) return 1;
+      GI_CUDA(cudaMemcpyAsync(np.p, photons.p, sizeof(GiPhoton) * stored, cudaMemcpyDeviceToDevice, st));
+      GI_CUDA(cudaMemcpyAsync(nk.p, keys.p, 8 * stored, cudaMemcpyDeviceToDevice, st));
+      GI_CUDA(cudaMemcpyAsync(count.p, &stored, 8, cudaMemcpyHostToDevice, st));
+      GI_CUDA(cudaStreamSynchronize(st));
+      std::swap(photons.p, np.p); std::swap(keys.p, nk.p);
+      cap = ncap;
+    }
+    emitted += assigned;
+    rounds_out++;
+    if (stored > 0 && emitted > 0) {
+      average_bounce_rate = ((double)stored) / emitted;
+      const double progress = map_type == MAP_GLOBAL ? (double)stored / emitted : (double)stored / target;
+      slowdown_factor = progress < 0.75 ? 2.0 : 1.0;
+    } else {
+      average_bounce_rate /= 2.0;
+      attempts_left--;
+    }
+  }
+  emitted_out = emitted;
+  // deterministic order: sort by (emitted photon number, bounce)
+  PhotonMapStore &m = ctx->maps[map_type];
+  free_map(m);
+  m.dev.n = stored;
+  if (stored == 0) return 0;
+  if (stored >= (1ull << 31)) { set_error("gi_trace_photons: more than 2^31 - 1 photons stored"); return 1; }
+  Buf keys2, order, order2, tmp;
+  if (!keys2.alloc(8 * stored) || !order.alloc(4 * stored) || !order2.alloc(4 * stored)) return 1;
+  const unsigned blocks = (unsigned)((stored + 255) / 256);
+  iota_kernel<<<blocks, 256, 0, st>>>(order.as<uint32_t>(), stored);
+  size_t tmp_bytes = 0;
+  cub::DeviceRadixSort::SortPairs(nullptr, tmp_bytes, keys.as<uint64_t>(), keys2.as<uint64_t>(), order.as<uint32_t>(),
+                                  order2.as<uint32_t>(), (int)stored, 0, 64, st);
+  if (!tmp.alloc(tmp_bytes)) return 1;
+  GI_CUDA(cub::DeviceRadixSort::SortPairs(tmp.p, tmp_bytes, keys.as<uint64_t>(), keys2.as<uint64_t>(), order.as<uint32_t>(),
+                                          order2.as<uint32_t>(), (int)stored, 0, 64, st));
+  GI_CUDA(cudaMalloc(&m.raw, sizeof(GiPhoton) * stored));
+  permute_kernel<<<blocks, 256, 0, st>>>(photons.as<GiPhoton>(), order2.as<uint32_t>(), stored, (GiPhoton *)m.raw);
+  ctx->launches += 4;
+  GI_CUDA(cudaGetLastError());
+  GI_CUDA(cudaStreamSynchronize(st));
+  return 0;
+}
+
+}  // namespace gi
+
+using namespace gi;
+
+extern "C" {
+
+int gi_scale_photon_power(GiContext *ctx, int map, double factor) {
+  if (!ctx || map < 0 || map > 1) { set_error("gi_scale_photon_power: bad argument"); return 1; }
+  PhotonMapStore &m = ctx->maps[map];
+  if (m.built) { set_error("gi_scale_photon_power: the map is already built"); return 1; }
+  if (m.dev.n == 0) return 0;
+  GI_CUDA(cudaSetDevice(ctx->device));
+  scale_power_kernel<<<(unsigned)((m.dev.n + 255) / 256), 256, 0, ctx->stream>>>((GiPhoton *)m.raw, m.dev.n, factor);
+  ctx->launches++;
+  GI_CUDA(cudaGetLastError());
+  GI_CUDA(cudaStreamSynchronize(ctx->stream));
+  return 0;
+}
+
+int gi_trace_photons(GiContext *ctx, const GiParams *params, GiPhotonStats *stats) {
+  if (!ctx || !params) { set_error("gi_trace_photons: null argument"); return 1; }
+  if (!ctx->has_scene) { set_error("gi_trace_photons: no scene uploaded"); return 1; }
+  GiPhotonStats s; memset(&s, 0, sizeof(s));
+  s.indirect_illum = params->indirect_illum; s.caustic_illum = params->caustic_illum; s.direct_photon_illum = params->direct_photon_illum;
+  if (stats) *stats = s;
+  GI_CUDA(cudaSetDevice(ctx->device));
+  free_map(ctx->maps[0]); free_map(ctx->maps[1]);
+  const int nl = (int)ctx->lights.size();
+  if (nl <= 0) return 0;                                       // MapPhotons corner case (photonmap.cpp:263-265)
+  std::vector<double> light_powers(nl, 0.0);
+  double total_power = 0;
+  for (int i = 0; i < nl; i++) {
+    if (!ctx->lights[i].active) continue;
+    light_powers[i] = light_power(ctx->lights[i], ctx->radius);
+    total_power += light_powers[i];
+  }
+  s.total_power = total_power;
+  if (total_power <= 0) { if (stats) *stats = s; return 0; }   // (:285-287)
+
+  ShadeEnv env;
+  env.sc = ctx->scene; env.materials = ctx->scene.materials; env.p = *params;
+  env.ambient = ld3(ctx->ambient); env.background = ld3(ctx->background); env.eye = ld3(ctx->camera.eye);
+  env.radius = ctx->radius; env.n_lights = nl;
+  GiLight *d_lights = nullptr;
+  GI_CUDA(cudaMalloc(&d_lights, sizeof(GiLight) * nl));
+  env.lights = d_lights;
+  int rc = 1;
+  cudaEvent_t e0, e1, e2; cudaEventCreate(&e0); cudaEventCreate(&e1); cudaEventCreate(&e2);
+  do {
+    if (!cuda_ok(cudaMemcpyAsync(d_lights, ctx->lights.data(), sizeof(GiLight) * nl, cudaMemcpyHostToDevice, ctx->stream), "H2D lights")) break;
+    // the budget split of MapPhotons (:289-321): every "thread" gets COUNT / THREADS, thread 0 the remainder
+    const int world = params->world_size > 1 ? params->world_size : 1, rank = params->world_size > 1 ? params->rank : 0;
+    if (rank < 0 || rank >= world) { set_error("gi_trace_photons: rank outside [0, world_size)"); break; }
+    const bool want_global = params->indirect_illum || params->direct_photon_illum, want_caustic = params->caustic_illum != 0;
+    auto share = [&](int count) { const int per = count / world; return rank == 0 ? count - per * (world - 1) : per; };
+    cudaEventRecord(e0, ctx->stream);
+    int rounds = 0;
+    // photon numbers of different ranks never collide: rank r owns [r << 40, (r + 1) << 40)
+    const uint64_t id_base = (uint64_t)rank << 40;
+    if (want_global && trace_map(ctx, env, MAP_GLOBAL, share(params->global_photon_count), light_powers, total_power, id_base,
+                                 s.global_emitted, rounds)) break;
+    if (want_caustic && trace_map(ctx, env, MAP_CAUSTIC, share(params->caustic_photon_count), light_powers, total_power, id_base,
+                                  s.caustic_emitted, rounds)) break;
+    cudaEventRecord(e1, ctx->stream);
+    s.rounds = rounds;
+    s.global_stored = ctx->maps[0].dev.n; s.caustic_stored = ctx->maps[1].dev.n;
+    if (world == 1) {
+      // power scale, flag updates and kd-tree builds of MapPhotons (:339-377)
+      if (want_global && s.global_stored == 0) { s.indirect_illum = 0; s.direct_photon_illum = 0; }
+      if (want_caustic && s.caustic_stored == 0) s.caustic_illum = 0;
+      if (s.global_stored && gi_scale_photon_power(ctx, 0, total_power / (double)s.global_emitted)) break;
+      if (s.caustic_stored && gi_scale_photon_power(ctx, 1, total_power / (double)s.caustic_emitted)) break;
+      if (gi_build_maps(ctx, params)) break;
+    }
+    cudaEventRecord(e2, ctx->stream);
+    if (!cuda_ok(cudaStreamSynchronize(ctx->stream), "trace sync")) break;
+    float a = 0, b = 0; cudaEventElapsedTime(&a, e0, e1); cudaEventElapsedTime(&b, e1, e2);
+    s.trace_ms = a; s.build_ms = b;
+    rc = 0;
+  } while (0);
+  cudaEventDestroy(e0); cudaEventDestroy(e1); cudaEventDestroy(e2);
+  cudaFree(d_lights);
+  if (rc == 0 && stats) *stats = s;
+  return rc;
+}
+
+}  // extern "C"

@@ -68,7 +68,8 @@ class GiPhotonStats(ctypes.Structure):
                 ("global_emitted", ctypes.c_uint64), ("caustic_emitted", ctypes.c_uint64),
                 ("indirect_illum", ctypes.c_int32), ("caustic_illum", ctypes.c_int32),
                 ("direct_photon_illum", ctypes.c_int32), ("rounds", ctypes.c_int32),
-                ("trace_ms", ctypes.c_double), ("build_ms", ctypes.c_double)]
+                ("trace_ms", ctypes.c_double), ("build_ms", ctypes.c_double),
+                ("total_power", ctypes.c_double)]
 
 
 class GiRenderStats(ctypes.Structure):
@@ -84,7 +85,7 @@ EXPORTS = ["gi_abi_version", "gi_last_error", "gi_create", "gi_destroy", "gi_def
            "gi_upload_scene", "gi_intersect_batch", "gi_intersect_batch_device",
            "gi_load_photons", "gi_load_photons_device", "gi_load_photons_file", "gi_dump_photons_file",
            "gi_photon_count", "gi_get_photons", "gi_build_maps", "gi_gather_batch", "gi_gather_batch_device",
-           "gi_trace_photons", "gi_render", "gi_render_float"]
+           "gi_trace_photons", "gi_scale_photon_power", "gi_render", "gi_render_float"]
 
 _lib = None
 
@@ -120,6 +121,7 @@ def lib():
         L.gi_gather_batch.argtypes = [vp, i32, vp, u64, i32, dbl, i32, ctypes.POINTER(GiParams), vp, vp, vp]
         L.gi_gather_batch_device.argtypes = [vp, i32, vp, u64, i32, dbl, i32, ctypes.POINTER(GiParams), vp, vp, vp, vp]
         L.gi_trace_photons.argtypes = [vp, ctypes.POINTER(GiParams), ctypes.POINTER(GiPhotonStats)]
+        L.gi_scale_photon_power.argtypes = [vp, i32, dbl]
         L.gi_render.argtypes = [vp, ctypes.POINTER(GiParams), i32, i32, i32, vp, ctypes.POINTER(GiRenderStats)]
         L.gi_render_float.argtypes = [vp, ctypes.POINTER(GiParams), i32, i32, i32, vp, ctypes.POINTER(GiRenderStats)]
         _lib = L
@@ -247,6 +249,9 @@ class Context:
         st = GiPhotonStats()
         _check(lib().gi_trace_photons(self.handle, ctypes.byref(params), ctypes.byref(st)))
         return st
+
+    def scale_photon_power(self, which, factor):
+        _check(lib().gi_scale_photon_power(self.handle, which, float(factor)))
 
     def render_float(self, params, width, height, aa=0):
         """The supersampled FP64 frame before clamping: array [W*2^aa, H*2^aa, 3], indexed [i][j] like the

@@ -26,7 +26,7 @@
 extern "C" {
 #endif
 
-#define GI_ABI_VERSION 1
+#define GI_ABI_VERSION 2
 
 /* ------------------------------------------------------------------------------------------------
  * Scene description (flattened R3Scene; src/R3Graphics/R3Scene.h).  Order is the order in which
@@ -189,6 +189,7 @@ typedef struct GiPhotonStats {       /* side effects of MapPhotons (photonmap.cp
   int32_t indirect_illum, caustic_illum, direct_photon_illum;   /* flags after the pass */
   int32_t rounds;
   double trace_ms, build_ms;
+  double total_power;                /* sum of LightPower() over the active lights (graphics_utils.cpp:223-258) */
 } GiPhotonStats;
 
 typedef struct GiRenderStats {       /* the -v block of RenderImage (render.cpp:224-255) */
@@ -246,6 +247,11 @@ int gi_gather_batch_device(GiContext *ctx, int map, const GiGatherQuery *d_queri
 
 /* MapPhotons() (photonmap.cpp:260-436): emission + tracing + power scaling; maps stay on the device */
 int gi_trace_photons(GiContext *ctx, const GiParams *params, GiPhotonStats *stats);
+/* With params->world_size > 1 gi_trace_photons traces this rank's share (COUNT / world_size photons, like one
+ * reference thread, photonmap.cpp:289-321) and stops before the power scale: the host all-gathers the photons,
+ * loads them (gi_load_photons_device), applies total_power / (emitted summed over ranks) with this call
+ * (the decode - multiply - encode loop of photonmap.cpp:339-361), then calls gi_build_maps. */
+int gi_scale_photon_power(GiContext *ctx, int map, double factor);
 
 /* RenderImage(aa, W, H) (render.cpp:155-259).  rgb_out: W*H*3 bytes, row 0 = bottom row like R2Image. */
 int gi_render(GiContext *ctx, const GiParams *params, int width, int height, int aa, uint8_t *rgb_out,

@@ -298,7 +298,8 @@ static void write_photons(const std::string &path, RNArray<Photon *> &arr) {
 static int cmd_photons(int argc, char **argv) {
   if (argc < 4) die("usage: photons in.scn out_prefix [-global N] [-caustic N] [-threads N] [-pd N]");
   for (int i = 4; i + 1 < argc; i += 2) {
-    if (!strcmp(argv[i], "-global")) GLOBAL_PHOTON_COUNT = atoi(argv[i + 1]);
+    if (!strcmp(argv[i], "-fast_global")) { FAST_GLOBAL = atoi(argv[i + 1]) != 0; if (FAST_GLOBAL) { DIRECT_PHOTON_ILLUM = true; INDIRECT_ILLUM = false; } }
+    else if (!strcmp(argv[i], "-global")) GLOBAL_PHOTON_COUNT = atoi(argv[i + 1]);
     else if (!strcmp(argv[i], "-caustic")) CAUSTIC_PHOTON_COUNT = atoi(argv[i + 1]);
     else if (!strcmp(argv[i], "-threads")) THREADS = atoi(argv[i + 1]);
     else if (!strcmp(argv[i], "-pd")) MAX_PHOTON_DEPTH = atoi(argv[i + 1]);

@@ -1,0 +1,141 @@
+"""gi_trace_photons on the GPU against statistics of the reference's MapPhotons (tests/golden/photons.npz, made by
+tests/golden/make_photon_golden.py from oracle/_ref/ref_harness photons).  The reference RNG is unseeded, so the
+comparison is distributional: stored counts, summed power, power per cell of an 8x8x8 grid, direction-code
+histograms -- each within counting noise."""
+import os
+import sys
+import numpy as np
+import pytest
+
+import gi_b200
+from gi_testlib import GOLDEN
+
+sys.path.insert(0, GOLDEN)
+from make_photon_golden import stats  # noqa: E402  (pure numpy helper; runs no reference code)
+
+pytestmark = pytest.mark.gpu
+G = np.load(os.path.join(GOLDEN, "photons.npz"))
+CASES = sorted(k[:-len("__target")] for k in G.files if k.endswith("__target"))
+
+
+def trace(ctx, case, seed=7):
+    scene = case.split("@")[0]
+    hs = gi_b200.HostScene(os.path.join(GOLDEN, scene + ".gisc"))
+    ctx.upload_scene(hs)
+    ng, nc = [int(x) for x in G[case + "__target"]]
+    flags = ["-global", str(ng), "-caustic", str(max(nc, 1)), "-seed", str(seed)]
+    if case.endswith("@fast_global"):
+        flags.append("-fast_global")
+    if nc == 0:
+        flags.append("-no_caustic")
+    params, _ = gi_b200.parse_flags(flags)
+    st = ctx.trace_photons(params)
+    tail = np.frombuffer(open(os.path.join(GOLDEN, scene + ".gisc"), "rb").read()[-128:], dtype="<f8")
+    return params, st, tail[6:9], tail[9:12]
+
+
+def close_hist(ours, ref, n_ours, n_ref, what):
+    """bins with enough photons agree within 5 sigma of counting noise + 3 %."""
+    fo, fr = ours / max(n_ours, 1), ref / max(n_ref, 1)
+    big = ref >= 400
+    sigma = np.sqrt(fr / n_ref + fr / n_ours)
+    bad = np.abs(fo - fr)[big] > 5 * sigma[big] + 0.03 * fr[big]
+    assert bad.mean() < 0.02 if big.any() else True, f"{what}: {bad.sum()} of {big.sum()} bins off"
+
+
+@pytest.mark.parametrize("case", CASES)
+def test_photon_maps_match_reference_statistics(gpu_ctx, case):
+    params, st, lo, hi = trace(gpu_ctx, case)
+    for which, m in ((gi_b200.GI_MAP_GLOBAL, "global"), (gi_b200.GI_MAP_CAUSTIC, "caustic")):
+        key = f"{case}__{m}__n"
+        if key not in G.files:
+            continue
+        target = int(G[case + "__target"][which])
+        ph = gpu_ctx.get_photons(which)
+        n_ref = int(G[key][0])
+        assert len(ph) == (st.global_stored if which == 0 else st.caustic_stored)
+        assert target <= len(ph) <= target * 1.03 + 300, (m, len(ph), target)
+        s = stats(ph, lo, hi)
+        ref_power = G[f"{case}__{m}__power"]
+        assert np.all(np.abs(s["power"] - ref_power) <= 0.05 * ref_power + 1e-9), (m, s["power"], ref_power)
+        rc = G[f"{case}__{m}__grid_count"]
+        close_hist(s["grid_count"], rc, len(ph), n_ref, f"{case} {m} grid count")
+        for c in range(3):
+            # power per cell: same test on the count-weighted scale
+            scale = rc.sum() / max(G[f"{case}__{m}__grid_power"][:, c].sum(), 1e-30)
+            close_hist(s["grid_power"][:, c] * scale * (ref_power[c] / max(s["power"][c], 1e-30)),
+                       G[f"{case}__{m}__grid_power"][:, c] * scale, len(ph), n_ref, f"{case} {m} grid power {c}")
+        close_hist(s["phi_hist"], G[f"{case}__{m}__phi_hist"], len(ph), n_ref, f"{case} {m} phi")
+        close_hist(s["theta_hist"], G[f"{case}__{m}__theta_hist"], len(ph), n_ref, f"{case} {m} theta")
+    assert st.total_power > 0 and st.rounds >= 1
+
+
+def test_trace_is_deterministic_per_seed(gpu_ctx):
+    _, st1, _, _ = trace(gpu_ctx, "glass_cube", seed=3)
+    a = gpu_ctx.get_photons(0).copy(); ac = gpu_ctx.get_photons(1).copy()
+    _, st2, _, _ = trace(gpu_ctx, "glass_cube", seed=3)
+    b = gpu_ctx.get_photons(0); bc = gpu_ctx.get_photons(1)
+    assert a.tobytes() == b.tobytes() and ac.tobytes() == bc.tobytes()
+    assert (st1.global_emitted, st1.caustic_emitted) == (st2.global_emitted, st2.caustic_emitted)
+    trace(gpu_ctx, "glass_cube", seed=4)
+    assert gpu_ctx.get_photons(0).tobytes() != a.tobytes()
+
+
+def test_traced_maps_are_built_and_renderable(gpu_ctx):
+    """MapPhotons leaves kd-trees behind: gathers and a photon_viz render work straight after gi_trace_photons."""
+    params, st, lo, hi = trace(gpu_ctx, "cornell")
+    ph = gpu_ctx.get_photons(0)
+    q = np.zeros(4, dtype=gi_b200.QUERY)
+    q["p"] = ph["position"][:4]; q["n"] = [0, 1, 0]; q["bounce"] = [0, 1, 0]; q["cos_theta"] = 1.0
+    q["kd"] = 0.5; q["shininess"] = 1.0
+    idx, cnt, rgb = gpu_ctx.gather(0, q, 50, 2.5)
+    assert np.all(cnt == 50)
+    p2, _ = gi_b200.parse_flags("-no_monte -no_transmissive -no_specular -no_indirect -no_caustic -no_direct -photon_viz".split())
+    img, rs = gpu_ctx.render_float(p2, 32, 32, 0)
+    assert rs.indirect_samples > 0 and img.mean() > 0.1
+
+
+def test_no_lights_and_disabled_maps(gpu_ctx):
+    hs = gi_b200.HostScene(os.path.join(GOLDEN, "lines.gisc"))        # a scene without lights
+    gpu_ctx.upload_scene(hs)
+    params, _ = gi_b200.parse_flags(["-global", "1000", "-caustic", "1000"])
+    st = gpu_ctx.trace_photons(params)
+    assert st.global_stored == 0 and st.caustic_stored == 0 and st.rounds == 0
+    hs = gi_b200.HostScene(os.path.join(GOLDEN, "box.gisc"))
+    gpu_ctx.upload_scene(hs)
+    params, _ = gi_b200.parse_flags(["-global", "5000", "-no_caustic", "-no_indirect"])
+    st = gpu_ctx.trace_photons(params)                                  # neither map wanted: nothing is traced
+    assert st.global_stored == 0 and st.caustic_stored == 0
+    params, _ = gi_b200.parse_flags(["-global", "5000", "-caustic", "2000"])
+    st = gpu_ctx.trace_photons(params)
+    assert st.global_stored >= 5000
+    # a scene with nothing specular stores no caustic photon: the flag is cleared like photonmap.cpp:359-361
+    if st.caustic_stored == 0:
+        assert st.caustic_illum == 0
+
+
+def test_rank_shares_and_power_scale(gpu_ctx):
+    """world_size = 2: each rank traces half the budget on its own streams and leaves the power scale to the host."""
+    scene = "glass_cube"
+    hs = gi_b200.HostScene(os.path.join(GOLDEN, scene + ".gisc"))
+    gpu_ctx.upload_scene(hs)
+    parts, emitted, total_power = [], 0, 0.0
+    for r in range(2):
+        params, _ = gi_b200.parse_flags(["-global", "20001", "-no_caustic", "-seed", "5"])
+        params.rank, params.world_size = r, 2
+        st = gpu_ctx.trace_photons(params)
+        want = 20001 - 10000 if r == 0 else 10000
+        assert want <= st.global_stored <= want * 1.05 + 300
+        parts.append(gpu_ctx.get_photons(0).copy()); emitted += st.global_emitted; total_power = st.total_power
+    assert parts[0][:100].tobytes() != parts[1][:100].tobytes()
+    allp = np.concatenate(parts)
+    gpu_ctx.load_photons(0, allp)
+    gpu_ctx.scale_photon_power(0, total_power / emitted)
+    gpu_ctx.build_maps()
+    # same total power as a single-rank trace of the whole budget
+    params, _ = gi_b200.parse_flags(["-global", "20001", "-no_caustic", "-seed", "5"])
+    from make_photon_golden import decode_rgbe
+    two = decode_rgbe(gpu_ctx.get_photons(0)["rgbe"]).sum(0)
+    gpu_ctx.trace_photons(params)
+    one = decode_rgbe(gpu_ctx.get_photons(0)["rgbe"]).sum(0)
+    assert np.all(np.abs(two - one) < 0.06 * one)
