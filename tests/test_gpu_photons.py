@@ -96,7 +96,8 @@ def test_traced_maps_are_built_and_renderable(gpu_ctx):
 
 
 def test_no_lights_and_disabled_maps(gpu_ctx):
-    hs = gi_b200.HostScene(os.path.join(GOLDEN, "lines.gisc"))        # a scene without lights
+    hs = gi_b200.HostScene(os.path.join(GOLDEN, "box.gisc"))
+    hs.view.n_lights = 0                                                # SCENE_NLIGHTS <= 0 (photonmap.cpp:263-265)
     gpu_ctx.upload_scene(hs)
     params, _ = gi_b200.parse_flags(["-global", "1000", "-caustic", "1000"])
     st = gpu_ctx.trace_photons(params)
