@@ -85,7 +85,8 @@ EXPORTS = ["gi_abi_version", "gi_last_error", "gi_create", "gi_destroy", "gi_def
            "gi_upload_scene", "gi_intersect_batch", "gi_intersect_batch_device",
            "gi_load_photons", "gi_load_photons_device", "gi_load_photons_file", "gi_dump_photons_file",
            "gi_photon_count", "gi_get_photons", "gi_build_maps", "gi_gather_batch", "gi_gather_batch_device",
-           "gi_trace_photons", "gi_scale_photon_power", "gi_render", "gi_render_float"]
+           "gi_trace_photons", "gi_scale_photon_power", "gi_render", "gi_render_float",
+           "gi_default_cli_options", "gi_parse_args", "gi_write_image"]
 
 _lib = None
 

@@ -1,0 +1,130 @@
+// host/photonmap_main.cpp -- `photonmap inputscenefile outputimagefile [-FLAGS]`: the reference's program
+// (src/photonmap.cpp:442-499) on top of the C ABI of include/gi_b200.h.  Same flags (gi_parse_args = ParseArgs),
+// same stages in the same order -- read scene, MapPhotons, RenderImage, write image -- and the same -v report
+// blocks; every stage runs on the GPU, and the program fails if there is none.
+//
+// Extra flags: -seed N (the reference RNG is unseeded), -device N, -save_global f / -save_caustic f and
+// -load_global f / -load_caustic f (photon maps as "GIPM" files, shared with oracle/ref_harness).
+#include <chrono>
+#include <cstdio>
+#include <cstdlib>
+#include <cstring>
+#include <string>
+#include <vector>
+#include "gi_b200.h"
+
+static double seconds_since(std::chrono::steady_clock::time_point t0) {
+  return std::chrono::duration<double>(std::chrono::steady_clock::now() - t0).count();
+}
+static int fail(const char *what) { fprintf(stderr, "%s: %s\n", what, gi_last_error()); return -1; }
+
+int main(int argc, char **argv) {
+  GiParams params; gi_default_params(&params);
+  GiCliOptions opt; gi_default_cli_options(&opt);
+  const char *save[2] = {nullptr, nullptr}, *load[2] = {nullptr, nullptr};
+  std::vector<const char *> av;
+  for (int i = 0; i < argc; i++) {
+    const bool has_value = i + 1 < argc;
+    if (has_value && !strcmp(argv[i], "-save_global")) save[0] = argv[++i];
+    else if (has_value && !strcmp(argv[i], "-save_caustic")) save[1] = argv[++i];
+    else if (has_value && !strcmp(argv[i], "-load_global")) load[0] = argv[++i];
+    else if (has_value && !strcmp(argv[i], "-load_caustic")) load[1] = argv[++i];
+    else av.push_back(argv[i]);
+  }
+  if (gi_parse_args((int)av.size(), av.data(), &params, &opt)) { fprintf(stderr, "%s\n", gi_last_error()); return 1; }
+
+  // ReadScene (io_utils.cpp:219-250)
+  auto t0 = std::chrono::steady_clock::now();
+  GiHostScene *host = nullptr;
+  if (gi_host_scene_load(opt.input_scene_name, opt.real_material, &host)) return fail("Unable to read scene");
+  GiScene scene;
+  gi_host_scene_view(host, &scene);
+  if (params.verbose) {
+    printf("Read scene from %s ...\n", opt.input_scene_name);
+    printf("  Time = %.2f seconds\n", seconds_since(t0));
+    printf("  # Nodes = %d\n", scene.n_nodes);
+    printf("  # Lights = %d\n", scene.n_lights);
+    fflush(stdout);
+  }
+
+  GiContext *ctx = nullptr;
+  if (gi_create(opt.device, &ctx)) return fail("photonmap");
+  t0 = std::chrono::steady_clock::now();
+  if (gi_upload_scene(ctx, &scene)) return fail("Unable to upload scene");
+  if (params.verbose) {
+    printf("Built GPU scene ...\n  Time = %.2f seconds\n  # Primitives = %d\n", seconds_since(t0), scene.n_prims);
+    fflush(stdout);
+  }
+
+  // MapPhotons (photonmap.cpp:260-436)
+  if (params.indirect_illum || params.caustic_illum || params.direct_photon_illum) {
+    t0 = std::chrono::steady_clock::now();
+    GiPhotonStats ps; memset(&ps, 0, sizeof(ps));
+    if (load[0] || load[1]) {
+      for (int m = 0; m < 2; m++)
+        if (load[m] && gi_load_photons_file(ctx, m, load[m])) return fail("Unable to load photon map");
+      if (gi_build_maps(ctx, &params)) return fail("Unable to build photon maps");
+      gi_photon_count(ctx, 0, &ps.global_stored); gi_photon_count(ctx, 1, &ps.caustic_stored);
+      if (!ps.global_stored) { params.indirect_illum = 0; params.direct_photon_illum = 0; }
+      if (!ps.caustic_stored) params.caustic_illum = 0;
+    } else {
+      if (params.verbose) {
+        if (params.indirect_illum || params.direct_photon_illum) printf("Building global photon map ...\n");
+        if (params.caustic_illum) printf("Building caustic photon map ...\n");
+      }
+      if (gi_trace_photons(ctx, &params, &ps)) return fail("Unable to trace photons");
+      if (scene.n_lights > 0 && ps.total_power > 0) {
+        params.indirect_illum = ps.indirect_illum; params.caustic_illum = ps.caustic_illum;
+        params.direct_photon_illum = ps.direct_photon_illum;
+      }
+    }
+    if (params.verbose) {
+      printf("Building kdtrees ...\n");
+      printf("Built photon map ...\n");
+      printf("  Total Time = %.2f seconds\n", seconds_since(t0));
+      printf("  Photon Tracing = %.2f seconds\n", ps.trace_ms / 1000.0);
+      printf("  KdTree Construction = %.2f seconds\n", ps.build_ms / 1000.0);
+      unsigned long long total = 0;
+      if (params.indirect_illum || params.direct_photon_illum) { printf("  # Global Photons Stored = %llu\n", (unsigned long long)ps.global_stored); total += ps.global_stored; }
+      if (params.caustic_illum) { printf("  # Caustic Photons Stored = %llu\n", (unsigned long long)ps.caustic_stored); total += ps.caustic_stored; }
+      printf("Total Photons Stored: %llu\n", total);
+      fflush(stdout);
+    }
+    for (int m = 0; m < 2; m++)
+      if (save[m] && gi_dump_photons_file(ctx, m, save[m])) return fail("Unable to save photon map");
+  }
+
+  // RenderImage (render.cpp:155-259)
+  if (params.verbose) printf("Rendering image ...\n");
+  std::vector<uint8_t> rgb((size_t)opt.width * opt.height * 3);
+  GiRenderStats rs; memset(&rs, 0, sizeof(rs));
+  if (gi_render(ctx, &params, opt.width, opt.height, opt.aa, rgb.data(), &rs)) return fail("Unable to render");
+  if (params.verbose) {
+    unsigned long long total = rs.screen_rays;
+    printf("Rendered image ...\n");
+    printf("  Time = %.2f seconds\n", rs.render_ms / 1000.0);
+    printf("  # Screen Rays = %llu\n", (unsigned long long)rs.screen_rays);
+    if (params.shadows) { printf("  # Shadow Rays = %llu\n", (unsigned long long)rs.shadow_rays); total += rs.shadow_rays; }
+    if (params.monte_carlo) { printf("  # Monte Carlo Rays = %llu\n", (unsigned long long)rs.monte_rays); total += rs.monte_rays; }
+    if (params.transmissive_illum) { printf("  # Transmissive Samples = %llu\n", (unsigned long long)rs.transmissive_samples); total += rs.transmissive_samples; }
+    if (params.specular_illum) { printf("  # Specular Samples = %llu\n", (unsigned long long)rs.specular_samples); total += rs.specular_samples; }
+    if (params.indirect_illum) { printf("  # Indirect Samples = %llu\n", (unsigned long long)rs.indirect_samples); total += rs.indirect_samples; }
+    if (params.caustic_illum) { printf("  # Caustic Samples = %llu\n", (unsigned long long)rs.caustic_samples); total += rs.caustic_samples; }
+    printf("Total Rays: %llu\n", total);
+    fflush(stdout);
+  }
+
+  // WriteImage (io_utils.cpp:271-291)
+  t0 = std::chrono::steady_clock::now();
+  if (gi_write_image(opt.output_image_name, rgb.data(), opt.width, opt.height)) { fprintf(stderr, "%s\n", gi_last_error()); return -1; }
+  if (params.verbose) {
+    printf("Wrote image to %s ...\n", opt.output_image_name);
+    printf("  Time = %.2f seconds\n", seconds_since(t0));
+    printf("  Width = %d\n", opt.width);
+    printf("  Height = %d\n", opt.height);
+    fflush(stdout);
+  }
+  gi_destroy(ctx);
+  gi_host_scene_free(host);
+  return 0;
+}

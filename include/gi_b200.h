@@ -207,6 +207,16 @@ int gi_create(int device, GiContext **out);                       /* fails if no
 void gi_destroy(GiContext *ctx);
 void gi_default_params(GiParams *p);                              /* photonmap.cpp:41-106 */
 
+/* the program arguments that are not render globals (photonmap.cpp:22-34) */
+typedef struct GiCliOptions {
+  const char *input_scene_name, *output_image_name;   /* point into argv */
+  int32_t width, height, aa, real_material;
+  int32_t device;                                     /* new: CUDA device index (-device N) */
+} GiCliOptions;
+void gi_default_cli_options(GiCliOptions *o);
+/* ParseArgs (src/utils/io_utils.cpp:16-214); argv[0] is the program name.  New flags: -seed N, -device N. */
+int gi_parse_args(int argc, const char *const *argv, GiParams *params, GiCliOptions *options);
+
 int gi_launch_count(GiContext *ctx, uint64_t *out);                /* kernels launched so far by this context */
 
 /* host-side .scn/.off loader (no device needed): ReadScene (src/utils/io_utils.cpp:219-250) ->
@@ -260,6 +270,10 @@ int gi_render(GiContext *ctx, const GiParams *params, int width, int height, int
  * column-major like image_buffer[i][j]) for parity tests */
 int gi_render_float(GiContext *ctx, const GiParams *params, int width, int height, int aa, double *rgb_out,
                     GiRenderStats *stats);
+
+/* R2Image::Write (R2Image.cpp:317-340) by file extension: .png, .ppm (ASCII, the reference's layout), .bmp.
+ * rgb is the gi_render frame (row 0 = bottom row). */
+int gi_write_image(const char *path, const uint8_t *rgb, int width, int height);
 
 #ifdef __cplusplus
 }

@@ -11,6 +11,7 @@
 //   ref_harness photons    <in.scn> <out_prefix> <seed> [photonmap flags] (MapPhotons, photonmap.cpp:260)
 //   ref_harness gather     <photons.bin> <queries.bin> <out.bin> <k> <r> <filter 0|1|2> [threads]
 //                                                     (EstimateRadiance, photon_utils.cpp:72)
+//   ref_harness parse      [photonmap flags]                               (ParseArgs, io_utils.cpp:16)
 //   ref_harness shade      <in.scn> <rays.bin> <out.bin> [-load_global f] [-load_caustic f] [photonmap flags]
 //                                                     (Intersects + RayTrace, render.cpp:119-124)
 // With -DGI_REF_MAIN the same translation unit is just the reference program (`photonmap_ref`).
@@ -509,6 +510,34 @@ static int cmd_shade(int argc, char **argv) {
   return 0;
 }
 
+// ---------------------------------------------------------------- parse (ParseArgs, io_utils.cpp:16-214)
+// usage: parse [photonmap flags]   -> one JSON object with every global the flags can touch
+static int cmd_parse(int argc, char **argv) {
+  std::vector<char *> av;
+  av.push_back((char *)"photonmap"); av.push_back((char *)"in.scn"); av.push_back((char *)"out.png");
+  for (int i = 2; i < argc; i++) av.push_back(argv[i]);
+  char *in_name = NULL, *out_name = NULL; int w = 1024, h = 1024, aa_ = 2; bool real = false;
+  if (!ParseArgs((int)av.size(), av.data(), in_name, out_name, w, h, aa_, real)) die("bad flags");
+  printf("{\"verbose\": %d, \"threads\": %d, \"fresnel\": %d, \"ir_air\": %.17g, \"ambient\": %d, \"direct_illum\": %d, "
+         "\"transmissive_illum\": %d, \"specular_illum\": %d, \"indirect_illum\": %d, \"caustic_illum\": %d, "
+         "\"direct_photon_illum\": %d, \"fast_global\": %d, \"irradiance_cache\": %d, \"shadows\": %d, \"soft_shadows\": %d, "
+         "\"light_test\": %d, \"shadow_test\": %d, \"monte_carlo\": %d, \"max_monte_depth\": %d, \"prob_absorb\": %.17g, "
+         "\"recursive_shadows\": %d, \"distrib_transmissive\": %d, \"transmissive_test\": %d, \"distrib_specular\": %d, "
+         "\"specular_test\": %d, \"depth_of_field\": %d, \"dof_test\": %d, \"focus_depth\": %.17g, \"aperture_radius\": %.17g, "
+         "\"global_photon_count\": %d, \"caustic_photon_count\": %d, \"max_photon_depth\": %d, \"indirect_test\": %d, "
+         "\"global_estimate_size\": %d, \"global_estimate_dist\": %.17g, \"global_filter\": %d, \"caustic_estimate_size\": %d, "
+         "\"caustic_estimate_dist\": %.17g, \"caustic_filter\": %d, \"filter_const_a\": %.17g, \"filter_const_b\": %.17g, "
+         "\"filter_const_k\": %.17g, \"width\": %d, \"height\": %d, \"aa\": %d, \"real_material\": %d}\n",
+         (int)VERBOSE, THREADS, (int)FRESNEL, IR_AIR, (int)AMBIENT, (int)DIRECT_ILLUM, (int)TRANSMISSIVE_ILLUM, (int)SPECULAR_ILLUM,
+         (int)INDIRECT_ILLUM, (int)CAUSTIC_ILLUM, (int)DIRECT_PHOTON_ILLUM, (int)FAST_GLOBAL, (int)IRRADIANCE_CACHE, (int)SHADOWS,
+         (int)SOFT_SHADOWS, LIGHT_TEST, SHADOW_TEST, (int)MONTE_CARLO, MAX_MONTE_DEPTH, PROB_ABSORB, (int)RECURSIVE_SHADOWS,
+         (int)DISTRIB_TRANSMISSIVE, TRANSMISSIVE_TEST, (int)DISTRIB_SPECULAR, SPECULAR_TEST, (int)DEPTH_OF_FIELD, DOF_TEST, FOCUS_DEPTH,
+         APERTURE_RADIUS, GLOBAL_PHOTON_COUNT, CAUSTIC_PHOTON_COUNT, MAX_PHOTON_DEPTH, INDIRECT_TEST, GLOBAL_ESTIMATE_SIZE,
+         GLOBAL_ESTIMATE_DIST, (int)GLOBAL_FILTER, CAUSTIC_ESTIMATE_SIZE, CAUSTIC_ESTIMATE_DIST, (int)CAUSTIC_FILTER, FILTER_CONST_A,
+         FILTER_CONST_B, FILTER_CONST_K, w, h, aa_, (int)real);
+  return 0;
+}
+
 int main(int argc, char **argv) {
   if (argc < 2) die("usage: ref_harness <dump_scene|camrays|isect|photons|gather|shade> ...");
   std::string c = argv[1];
@@ -519,6 +548,7 @@ int main(int argc, char **argv) {
   if (c == "gather") return cmd_gather(argc, argv);
   if (c == "bench") return cmd_bench(argc, argv);
   if (c == "shade") return cmd_shade(argc, argv);
+  if (c == "parse") return cmd_parse(argc, argv);
   die("unknown command");
   return 2;
 }

@@ -189,3 +189,50 @@ def _oracle_gather(self, photons, queries, k, r, filter=0, fa=0.918, fb=1.953, f
 
 
 Oracle.gather = _oracle_gather
+
+
+def read_png_rgb(path):
+    """Minimal PNG reader (8-bit RGB / RGBA, non-interlaced, all five filter types): returns uint8 [H, W, 3], top row first."""
+    import struct
+    import zlib
+    raw = open(path, "rb").read()
+    assert raw[:8] == b"\x89PNG\r\n\x1a\n", "not a PNG"
+    pos, idat, ihdr = 8, b"", None
+    while pos < len(raw):
+        n, typ = struct.unpack(">I4s", raw[pos:pos + 8])
+        body = raw[pos + 8:pos + 8 + n]
+        if typ == b"IHDR":
+            ihdr = struct.unpack(">IIBBBBB", body)
+        elif typ == b"IDAT":
+            idat += body
+        pos += 12 + n
+    w, h, depth, ctype, _, _, interlace = ihdr
+    assert depth == 8 and ctype in (2, 6) and interlace == 0
+    bpp = 3 if ctype == 2 else 4
+    data = np.frombuffer(zlib.decompress(idat), dtype=np.uint8).reshape(h, 1 + w * bpp)
+    out = np.zeros((h, w * bpp), dtype=np.int32)
+    prev = np.zeros(w * bpp, dtype=np.int32)
+    for y in range(h):
+        ft, line = int(data[y, 0]), data[y, 1:].astype(np.int32)
+        cur = np.zeros(w * bpp, dtype=np.int32)
+        if ft == 0:
+            cur = line.copy()
+        elif ft == 2:
+            cur = (line + prev) & 255
+        else:
+            for x in range(w * bpp):
+                a = cur[x - bpp] if x >= bpp else 0
+                b = prev[x]
+                c = prev[x - bpp] if x >= bpp else 0
+                if ft == 1:
+                    pred = a
+                elif ft == 3:
+                    pred = (a + b) >> 1
+                else:
+                    p = a + b - c
+                    pa, pb, pc = abs(p - a), abs(p - b), abs(p - c)
+                    pred = a if (pa <= pb and pa <= pc) else (b if pb <= pc else c)
+                cur[x] = (line[x] + pred) & 255
+        out[y] = cur
+        prev = cur
+    return out.reshape(h, w, bpp)[:, :, :3].astype(np.uint8)

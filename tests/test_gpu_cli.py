@@ -1,0 +1,55 @@
+"""The `photonmap` program end to end on the GPU against whole-program runs of the unmodified reference
+(oracle/_ref/photonmap_ref; decoded PNGs in tests/golden/cli_images.npz, see tests/golden/make_cli_golden.py)."""
+import os
+import subprocess
+import numpy as np
+import pytest
+
+from gi_testlib import GOLDEN, PKG, read_png_rgb
+
+pytestmark = pytest.mark.gpu
+G = np.load(os.path.join(GOLDEN, "cli_images.npz"))
+PHOTONMAP = os.path.join(PKG, "bin", "photonmap")
+NAMES = sorted(k for k in G.files if "__" not in k)
+
+
+@pytest.mark.parametrize("name", NAMES)
+def test_program_image_equals_reference_program(tmp_path, name):
+    scene, flags = [str(x) for x in G[name + "__meta"]]
+    out = tmp_path / "out.png"
+    r = subprocess.run([PHOTONMAP, os.path.join(GOLDEN, scene + ".gisc"), str(out), *flags.split(), "-v"],
+                       capture_output=True, text=True)
+    assert r.returncode == 0, r.stderr
+    assert "Rendered image ..." in r.stdout and "# Screen Rays" in r.stdout and "Wrote image to" in r.stdout
+    img = read_png_rgb(out)
+    ref = G[name]
+    assert img.shape == ref.shape
+    d = np.abs(img.astype(int) - ref.astype(int))
+    # truncating quantisation: a radiance that differs in the 16th digit can land on the other side of k/255
+    assert d.max() <= 1 and (d > 0).mean() < 1e-3, (d.max(), (d > 0).mean())
+
+
+def test_program_full_pipeline_and_photon_files(tmp_path):
+    """Photon tracing + caustic / indirect rendering through the CLI; -save_* then -load_* reproduces the image."""
+    scn = os.path.join(GOLDEN, "cornell.gisc")
+    a, b = tmp_path / "a.png", tmp_path / "b.ppm"
+    common = "-resolution 32 32 -aa 0 -global 3000 -caustic 3000 -it 4 -st 2 -tt 2 -lt 4 -ss 4 -md 4 -seed 9".split()
+    r = subprocess.run([PHOTONMAP, scn, str(a), *common, "-v", "-save_global", str(tmp_path / "g.gipm"), "-save_caustic",
+                        str(tmp_path / "c.gipm")], capture_output=True, text=True)
+    assert r.returncode == 0, r.stderr
+    assert "# Global Photons Stored" in r.stdout and "Total Rays:" in r.stdout
+    r = subprocess.run([PHOTONMAP, scn, str(b), *common, "-load_global", str(tmp_path / "g.gipm"), "-load_caustic",
+                        str(tmp_path / "c.gipm")], capture_output=True, text=True)
+    assert r.returncode == 0, r.stderr
+    img = read_png_rgb(a)
+    tok = open(b).read().split()
+    ppm = np.array(tok[4:], dtype=int).reshape(32, 32, 3)
+    assert np.abs(img.astype(int) - ppm).max() <= 1
+    assert img.mean() > 20
+
+
+def test_program_errors(tmp_path):
+    r = subprocess.run([PHOTONMAP, "/nonexistent.scn", str(tmp_path / "x.png")], capture_output=True, text=True)
+    assert r.returncode != 0 and "Unable" in r.stderr
+    r = subprocess.run([PHOTONMAP, os.path.join(GOLDEN, "box.gisc"), str(tmp_path / "x.png"), "-frobnicate"], capture_output=True, text=True)
+    assert r.returncode != 0 and "Invalid program argument" in r.stderr
