@@ -102,6 +102,18 @@ int gi_get_photons(GiContext *ctx, int map, GiPhoton *out, uint64_t capacity) {
   return 0;
 }
 
+// device-to-device variant for the multi-GPU path: the rank's photons go straight into the NCCL send buffer
+int gi_get_photons_device(GiContext *ctx, int map, GiPhoton *d_out, uint64_t capacity, void *stream) {
+  if (!ctx || map < 0 || map > 1) { set_error("gi_get_photons_device: bad argument"); return 1; }
+  PhotonMapStore &m = ctx->maps[map];
+  if (capacity < m.dev.n) { set_error("gi_get_photons_device: buffer too small"); return 1; }
+  if (m.dev.n == 0) return 0;
+  if (!d_out) { set_error("gi_get_photons_device: null buffer"); return 1; }
+  GI_CUDA(cudaSetDevice(ctx->device));
+  GI_CUDA(cudaMemcpyAsync(d_out, m.raw, sizeof(GiPhoton) * m.dev.n, cudaMemcpyDeviceToDevice, (cudaStream_t)stream));
+  return 0;
+}
+
 int gi_load_photons_file(GiContext *ctx, int map, const char *path) {
   FILE *f = path ? fopen(path, "rb") : nullptr;
   if (!f) { set_error(std::string("Unable to open photon file ") + (path ? path : "(null)")); return 1; }

@@ -555,10 +555,11 @@ static int render_common(GiContext *ctx, const GiParams *params, int width, int 
     if (!cuda_ok(cudaMemsetAsync(accum, 0, sizeof(double) * 3 * npix, ctx->stream), "memset(accum)")) break;
     if (!cuda_ok(cudaMemsetAsync(d_stats, 0, 2 * sizeof(RayStats), ctx->stream), "memset(stats)")) break;
     cudaEventRecord(e0, ctx->stream);
-    // tile sharding across GPUs: rank r of w renders a contiguous run of supersample columns, the rest stays zero
+    // tile sharding across GPUs: rank r of w renders a contiguous run of pixel columns, the rest stays zero
     const int world = params->world_size > 1 ? params->world_size : 1, rank = params->world_size > 1 ? params->rank : 0;
     if (rank < 0 || rank >= world) { set_error("gi_render: rank outside [0, world_size)"); break; }
-    const uint64_t c0 = sw * rank / world, c1 = sw * (rank + 1) / world;
+    // (whole OUTPUT pixel columns, so that every box-filter sum of the resolve stays on one rank)
+    const uint64_t c0 = (uint64_t)width * rank / world * aaf, c1 = (uint64_t)width * (rank + 1) / world * aaf;
     if (render_accum(ctx, *params, (int)sw, (int)sh, c0 * sh, c1 * sh, accum, d_stats, paths)) break;
     cudaEventRecord(e1, ctx->stream);
     if (!cuda_ok(cudaMemcpyAsync(hs, d_stats, 2 * sizeof(RayStats), cudaMemcpyDeviceToHost, ctx->stream), "D2H stats")) break;

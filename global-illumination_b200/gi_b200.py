@@ -84,7 +84,7 @@ EXPORTS = ["gi_abi_version", "gi_last_error", "gi_create", "gi_destroy", "gi_def
            "gi_host_scene_load", "gi_host_scene_view", "gi_host_scene_save", "gi_host_scene_free",
            "gi_upload_scene", "gi_intersect_batch", "gi_intersect_batch_device",
            "gi_load_photons", "gi_load_photons_device", "gi_load_photons_file", "gi_dump_photons_file",
-           "gi_photon_count", "gi_get_photons", "gi_build_maps", "gi_gather_batch", "gi_gather_batch_device",
+           "gi_photon_count", "gi_get_photons", "gi_get_photons_device", "gi_build_maps", "gi_gather_batch", "gi_gather_batch_device",
            "gi_trace_photons", "gi_scale_photon_power", "gi_render", "gi_render_float",
            "gi_default_cli_options", "gi_parse_args", "gi_write_image"]
 
@@ -118,6 +118,7 @@ def lib():
         L.gi_dump_photons_file.argtypes = [vp, i32, ctypes.c_char_p]
         L.gi_photon_count.argtypes = [vp, i32, ctypes.POINTER(u64)]
         L.gi_get_photons.argtypes = [vp, i32, vp, u64]
+        L.gi_get_photons_device.argtypes = [vp, i32, vp, u64, vp]
         L.gi_build_maps.argtypes = [vp, ctypes.POINTER(GiParams)]
         L.gi_gather_batch.argtypes = [vp, i32, vp, u64, i32, dbl, i32, ctypes.POINTER(GiParams), vp, vp, vp]
         L.gi_gather_batch_device.argtypes = [vp, i32, vp, u64, i32, dbl, i32, ctypes.POINTER(GiParams), vp, vp, vp, vp]
@@ -225,6 +226,9 @@ class Context:
         out = np.zeros(self.photon_count(which), dtype=PHOTON)
         _check(lib().gi_get_photons(self.handle, which, out.ctypes.data, len(out)))
         return out
+
+    def get_photons_device(self, which, d_out, capacity, stream=None):
+        _check(lib().gi_get_photons_device(self.handle, which, d_out, capacity, stream))
 
     def build_maps(self, params=None):
         p = params or default_params()

@@ -243,6 +243,8 @@ int gi_load_photons_file(GiContext *ctx, int map, const char *path);
 int gi_dump_photons_file(GiContext *ctx, int map, const char *path);
 int gi_photon_count(GiContext *ctx, int map, uint64_t *n_out);
 int gi_get_photons(GiContext *ctx, int map, GiPhoton *out, uint64_t capacity);   /* map order */
+/* same into a device buffer, asynchronously on `stream` (NULL = default stream): feeds the photon all-gather */
+int gi_get_photons_device(GiContext *ctx, int map, GiPhoton *d_out, uint64_t capacity, void *stream);
 int gi_build_maps(GiContext *ctx, const GiParams *params);
 
 /* EstimateRadiance over a batch (photon_utils.cpp:72-162): kNN index sets + radiance.
