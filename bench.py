@@ -52,6 +52,10 @@ def parse():
     ap.add_argument("--no-cpu-baseline", action="store_true")
     ap.add_argument("--cpu-rays", type=int, default=2_000_000)
     ap.add_argument("--cpu-queries", type=int, default=200_000)
+    ap.add_argument("--no-frame", action="store_true", help="skip the whole-program frame (photon pass + render) report")
+    ap.add_argument("--frame-scene", default="cornell")
+    ap.add_argument("--frame-res", type=int, default=512)
+    ap.add_argument("--frame-aa", type=int, default=1)
     return ap.parse_args()
 
 
@@ -412,6 +416,11 @@ def run_ours(args):
     rays_all, q_all = units.tolist()
     ms_per_step = total_ms / args.steps
 
+    frame = None
+    if not args.no_frame:
+        del rays_h, q_h, hits_h, rgb_h, cnt_h
+        frame = frame_report(args, torch, dist, ctx, dev, rank, world)
+
     if rank == 0:
         peak, peak_src = load_peaks()
         achieved = (n_q * GATHER_ALGO_BYTES) / (gather_ms * 1e-3) / 1e9
@@ -429,7 +438,7 @@ def run_ours(args):
                 "e2e": {"value": (rays_all + q_all) / (e2e_ms * 1e-3) / 1e6, "unit": "Mrays/s",
                         "h2d_bytes_per_step": n_rays * 48 + n_q * 136, "d2h_bytes_per_step": n_rays * 72 + n_q * 28,
                         "ms_per_step": e2e_ms},
-                "gpu_launches": int(launches), "clocks": clocks}
+                "gpu_launches": int(launches), "clocks": clocks, "frame": frame}
         traffic_file = os.path.join(ROOT, "profiles", "gather_traffic.json")
         if os.path.exists(traffic_file):       # ncu capture at a smaller launch: DRAM bytes per gather x this launch's gathers
             tf = json.load(open(traffic_file))
@@ -441,6 +450,51 @@ def run_ours(args):
     if world > 1:
         dist.barrier()
         dist.destroy_process_group()
+
+
+def frame_report(args, torch, dist, ctx, dev, rank, world):
+    """Whole-program frame outside the timed steps: BASELINE.json configs[0] (cornell 512 x 512 -aa 1, every flag at its
+    default: 2176 global + 10^7 caustic photons, k 50 / 225, lt/ss/tt/st 128, it 256) -- MapPhotons + RenderImage
+    through gi_trace_photons / gi_render, sharded over the ranks when N > 1 (photons per rank + one all-gather, pixel
+    columns per rank + one reduce).  Times are wall clock around synchronised calls, max over ranks."""
+    import gi_b200
+    import multi_gpu
+    scene = gi_b200.HostScene(os.path.join(GOLDEN, args.frame_scene + ".gisc"))
+    ctx.upload_scene(scene)
+    params, _ = gi_b200.parse_flags(["-seed", "1"])
+    W = H = args.frame_res
+    torch.cuda.synchronize()
+    if world > 1:
+        dist.barrier()
+    t0 = time.perf_counter()
+    if world > 1:
+        totals = multi_gpu.trace_photons_sharded(ctx, params, dist, torch, dev)
+        stored = (totals["global_stored"], totals["caustic_stored"])
+    else:
+        st = ctx.trace_photons(params)
+        params.indirect_illum, params.caustic_illum, params.direct_photon_illum = st.indirect_illum, st.caustic_illum, st.direct_photon_illum
+        stored = (int(st.global_stored), int(st.caustic_stored))
+    torch.cuda.synchronize(); t1 = time.perf_counter()
+    if world > 1:
+        img, rs = multi_gpu.render_sharded(ctx, params, W, H, args.frame_aa, dist, torch, dev)
+    else:
+        img, rs = ctx.render(params, W, H, args.frame_aa)
+    torch.cuda.synchronize(); t2 = time.perf_counter()
+    names = ["screen_rays", "shadow_rays", "monte_rays", "transmissive_samples", "specular_samples", "indirect_samples", "caustic_samples"]
+    c = torch.tensor([float(getattr(rs, n)) for n in names], dtype=torch.float64, device=dev)
+    t = torch.tensor([(t1 - t0) * 1e3, (t2 - t1) * 1e3, rs.render_ms], dtype=torch.float64, device=dev)
+    if world > 1:
+        dist.all_reduce(c, op=dist.ReduceOp.SUM); dist.all_reduce(t, op=dist.ReduceOp.MAX)
+    counters = dict(zip(names, [int(x) for x in c.tolist()]))
+    photon_ms, render_ms, render_kernel_ms = t.tolist()
+    total = sum(counters.values())
+    return {"workload": f"input/{args.frame_scene}.scn {W}x{H} -aa {args.frame_aa}, all flags default (BASELINE.json configs[0]): "
+                        "gi_trace_photons + gi_render, u8 frame back on the host",
+            "photon_pass_ms": photon_ms, "render_ms": render_ms, "frame_ms": photon_ms + render_ms, "render_device_ms": render_kernel_ms,
+            "photons_stored": {"global": stored[0], "caustic": stored[1]}, "ray_ops": total, "counters": counters,
+            "mray_ops_per_s": total / (render_ms * 1e-3) / 1e6,
+            "gathers_per_s": (counters["indirect_samples"] + counters["caustic_samples"]) / (render_ms * 1e-3),
+            "image_mean": float(img.mean()) if img is not None else None, "timing": "wall clock, max over ranks; not part of the timed steps"}
 
 
 def cpu_baseline(args, torch, rays, photons, queries):
