@@ -5,6 +5,7 @@
 // R3Scene::Intersects calls (R3Scene.cpp:471-479), e.g. the pixel loop of render.cpp:90-125.
 #include <cuda_runtime.h>
 #include <cstdio>
+#include <algorithm>
 #include <cstring>
 #include <mutex>
 #include "bvh_build.h"
@@ -26,6 +27,7 @@ void free_scene(GiContext *ctx) {
   for (void *p : ctx->scene_allocs) cudaFree(p);
   ctx->scene_allocs.clear();
   ctx->has_scene = false;
+  ctx->d_spec_boxes = nullptr; ctx->n_spec_boxes = -1;
   memset(&ctx->scene, 0, sizeof(ctx->scene));
 }
 
@@ -122,6 +124,34 @@ int gi_upload_scene(GiContext *ctx, const GiScene *scene) {
   ctx->launches += scene->n_prims > 1 ? 6 : 1;
   d.bvh = bvh;
   ctx->scene = d;
+  // world boxes of the shapes that can bounce a photon specularly (caustic-photon prefilter, photon_trace.cu)
+  {
+    std::vector<double> boxes;
+    const double margin = 1.0e-4 * (1.0 + (double)ps.abs_max);
+    for (int si = 0; si < scene->n_shapes; si++) {
+      const DevShape &sh = ps.shapes[si];
+      const int mat = ps.elements[sh.element].material;
+      if (mat < 0 || mat >= scene->n_materials) continue;
+      const GiMaterial &m = scene->materials[mat];
+      const bool spec = m.ks[0] != 0 || m.ks[1] != 0 || m.ks[2] != 0 || m.kt[0] != 0 || m.kt[1] != 0 || m.kt[2] != 0;
+      if (!spec || sh.n_prims <= 0) continue;
+      double b[6] = {1e300, 1e300, 1e300, -1e300, -1e300, -1e300};
+      for (int pi = sh.first_prim; pi < sh.first_prim + sh.n_prims; pi++)
+        for (int a = 0; a < 3; a++) {
+          b[a] = std::min(b[a], (double)ps.prim_boxes[(size_t)pi * 6 + a] - margin);
+          b[a + 3] = std::max(b[a + 3], (double)ps.prim_boxes[(size_t)pi * 6 + 3 + a] + margin);
+        }
+      boxes.insert(boxes.end(), b, b + 6);
+    }
+    ctx->n_spec_boxes = (int)(boxes.size() / 6);
+    ctx->d_spec_boxes = nullptr;
+    if (ctx->n_spec_boxes > 64) ctx->n_spec_boxes = -1;          // too many to test one by one: no prefilter
+    else if (ctx->n_spec_boxes > 0) {
+      const double *dp = nullptr;
+      if (!upload(ctx, boxes, &dp) || !cuda_ok(cudaStreamSynchronize(ctx->stream), "upload sync")) { free_scene(ctx); return 1; }
+      ctx->d_spec_boxes = const_cast<double *>(dp);
+    }
+  }
   ctx->lights.assign(scene->lights, scene->lights + scene->n_lights);
   ctx->materials.assign(scene->materials, scene->materials + scene->n_materials);
   ctx->camera = scene->camera;

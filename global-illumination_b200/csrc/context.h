@@ -22,6 +22,8 @@ struct GiContext {
   GiCamera camera{};
   double ambient[3] = {0, 0, 0}, background[3] = {0, 0, 0}, bbox_min[3] = {0, 0, 0}, bbox_max[3] = {0, 0, 0};
   double centroid[3] = {0, 0, 0}, radius = 0;
+  double *d_spec_boxes = nullptr;             // scene_allocs entry: boxes of the specular / transmissive shapes (photon_trace.cu)
+  int n_spec_boxes = -1;
   gi::PhotonMapStore maps[2];                 // GI_MAP_GLOBAL, GI_MAP_CAUSTIC
   uint64_t launches = 0;                      // kernels launched by this context (bench.py: gpu_launches)
 };

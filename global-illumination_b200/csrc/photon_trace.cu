@@ -12,6 +12,7 @@
 #include <cub/cub.cuh>
 #include <algorithm>
 #include <cmath>
+#include <cstdlib>
 #include <cstring>
 #include <vector>
 #include "context.h"
@@ -59,50 +60,47 @@ GI_DEV void store_photon(const PhotonSink &sink, D3 power, D3 incident, D3 point
   sink.keys[i] = key;
 }
 
-// PhotonTrace, photontracer.cpp:28-159
-GI_DEV void photon_trace(const ShadeEnv &env, RayD ray, D3 photon, int map_type, uint64_t id, Rng &rng, const PhotonSink &sink) {
+// One iteration of PhotonTrace's bounce loop (photontracer.cpp:64-158).  Returns false when the photon's walk ends.
+GI_DEV bool photon_bounce(const ShadeEnv &env, RayD &ray, D3 &photon, bool &store, int iter, int map_type, uint64_t id, Rng &rng,
+                          const PhotonSink &sink) {
   const GiParams &p = env.p;
-  D3 ray_start = ray.o;
-  bool store = map_type == MAP_GLOBAL && !p.fast_global;
-  for (int iter = 0; iter < p.max_photon_depth; iter++) {
-    HitRec h;
-    closest_hit(env.sc, ray, h);
-    if (h.prim < 0) break;
-    const Brdf b = load_brdf(env.materials[env.sc.elements[h.element].material]);
-    const D3 point = h.p, normal = h.n;
-    const D3 view = normalized(point - ray_start);
-    const double cos_theta = dot(normal, -view);
-    if (b.diffuse && store) store_photon(sink, photon, view, point, (id << 8) | (uint64_t)(iter & 255));
-    double r_coeff = 0;
-    if (p.fresnel && b.transparent) r_coeff = reflection_coeff(cos_theta, b.ir, p.ir_air);
-    const double mc = max_channel(photon);
-    const double prob_diffuse = max_channel(mul3(b.kd, photon)) / mc;
-    double prob_transmission = max_channel(mul3(b.kt, photon)) / mc;
-    const double prob_specular = (max_channel(mul3(b.ks, photon)) / mc) + r_coeff * prob_transmission;
-    prob_transmission *= (1.0 - r_coeff);
-    const double prob_total = prob_diffuse + prob_transmission + prob_specular + p.prob_absorb;
-    double rnd = rng_double(rng);
-    if (prob_total > 1.0) rnd *= prob_total;
-    D3 bounce;
-    if (rnd < prob_diffuse) {
-      if (map_type == MAP_CAUSTIC) break;
-      store = true;
-      bounce = diffuse_sample(normal, cos_theta, rng);
-      photon = mul3(photon, b.kd / prob_diffuse);
-    } else if (rnd < prob_diffuse + prob_transmission) {
-      if (map_type == MAP_CAUSTIC) store = true;
-      const D3 exact = transmissive_bounce(normal, view, cos_theta, b.ir, p.ir_air);
-      bounce = p.distrib_transmissive ? specular_sample(exact, b.n, cos_theta, rng) : exact;
-      photon = mul3(photon, (b.kt * (1.0 - r_coeff)) / prob_transmission);
-    } else if (rnd < prob_diffuse + prob_transmission + prob_specular) {
-      if (map_type == MAP_CAUSTIC) store = true;
-      const D3 exact = reflective_bounce(normal, view, cos_theta);
-      bounce = p.distrib_specular ? specular_sample(exact, b.n, cos_theta, rng) : exact;
-      photon = mul3(photon, (b.ks + b.kt * r_coeff) / prob_specular);
-    } else break;
-    ray_start = point + bounce * GI_EPS;
-    ray.o = ray_start; ray.d = bounce;
-  }
+  HitRec h;
+  closest_hit(env.sc, ray, h);
+  if (h.prim < 0) return false;
+  const Brdf b = load_brdf(env.materials[env.sc.elements[h.element].material]);
+  const D3 point = h.p, normal = h.n;
+  const D3 view = normalized(point - ray.o);                 // ray.o is the reference's ray_start
+  const double cos_theta = dot(normal, -view);
+  if (b.diffuse && store) store_photon(sink, photon, view, point, (id << 8) | (uint64_t)(iter & 255));
+  double r_coeff = 0;
+  if (p.fresnel && b.transparent) r_coeff = reflection_coeff(cos_theta, b.ir, p.ir_air);
+  const double mc = max_channel(photon);
+  const double prob_diffuse = max_channel(mul3(b.kd, photon)) / mc;
+  double prob_transmission = max_channel(mul3(b.kt, photon)) / mc;
+  const double prob_specular = (max_channel(mul3(b.ks, photon)) / mc) + r_coeff * prob_transmission;
+  prob_transmission *= (1.0 - r_coeff);
+  const double prob_total = prob_diffuse + prob_transmission + prob_specular + p.prob_absorb;
+  double rnd = rng_double(rng);
+  if (prob_total > 1.0) rnd *= prob_total;
+  D3 bounce;
+  if (rnd < prob_diffuse) {
+    if (map_type == MAP_CAUSTIC) return false;
+    store = true;
+    bounce = diffuse_sample(normal, cos_theta, rng);
+    photon = mul3(photon, b.kd / prob_diffuse);
+  } else if (rnd < prob_diffuse + prob_transmission) {
+    if (map_type == MAP_CAUSTIC) store = true;
+    const D3 exact = transmissive_bounce(normal, view, cos_theta, b.ir, p.ir_air);
+    bounce = p.distrib_transmissive ? specular_sample(exact, b.n, cos_theta, rng) : exact;
+    photon = mul3(photon, (b.kt * (1.0 - r_coeff)) / prob_transmission);
+  } else if (rnd < prob_diffuse + prob_transmission + prob_specular) {
+    if (map_type == MAP_CAUSTIC) store = true;
+    const D3 exact = reflective_bounce(normal, view, cos_theta);
+    bounce = p.distrib_specular ? specular_sample(exact, b.n, cos_theta, rng) : exact;
+    photon = mul3(photon, (b.ks + b.kt * r_coeff) / prob_specular);
+  } else return false;
+  ray.o = point + bounce * GI_EPS; ray.d = bounce;
+  return true;
 }
 
 // basis of a disk with normal n: EmitPhotons, photontracer.cpp:204-215 / 296-307
@@ -113,51 +111,139 @@ GI_DEV void disk_basis(D3 n, double radius, D3 &u, D3 &v) {
   u = normalized(u) * radius; v = normalized(v) * radius;
 }
 
-// EmitPhotons (photontracer.cpp:182-373) for one round: thread t emits photon number id0 + t from the light whose
-// range [first[l], first[l+1]) holds t.
-__global__ void __launch_bounds__(128) emit_kernel(ShadeEnv env, D3 centroid, int map_type, uint64_t id0, uint64_t n,
-                                                   const uint64_t *__restrict__ first, PhotonSink sink) {
-  for (uint64_t t = (uint64_t)blockIdx.x * blockDim.x + threadIdx.x; t < n; t += (uint64_t)gridDim.x * blockDim.x) {
-    int li = 0;
-    while (li + 1 < env.n_lights && t >= first[li + 1]) li++;
-    const GiLight &l = env.lights[li];
-    D3 photon = ld3(l.color);                                           // NormalizeColor, graphics_utils.cpp:25-36
-    const double total = photon.x + photon.y + photon.z;
-    if (total > 0) photon = photon / total;
-    const uint64_t id = id0 + t;
-    Rng rng; rng_init(rng, env.p.seed, id, STAGE_PHOTON + map_type, 0);
-    const D3 ln = ld3(l.direction);
-    RayD ray;
-    if (l.type == GI_LIGHT_DIR) {
-      const D3 center = centroid - ln * env.radius * 3.0;
-      D3 u, v; disk_basis(ln, env.radius, u, v);
-      double r1, r2;
-      do { r1 = rng_double(rng) * 2.0 - 1.0; r2 = rng_double(rng) * 2.0 - 1.0; } while (r1 * r1 + r2 * r2 > 1.0);
-      ray.o = u * r1 + v * r2 + center + ln * GI_EPS; ray.d = ln;
-    } else if (l.type == GI_LIGHT_POINT) {
-      double x, y, z;
-      do { x = rng_double(rng) * 2.0 - 1.0; y = rng_double(rng) * 2.0 - 1.0; z = rng_double(rng) * 2.0 - 1.0; } while (x * x + y * y + z * z > 1.0);
-      ray.o = ld3(l.position); ray.d = normalized(mk3(x, y, z));
-    } else if (l.type == GI_LIGHT_SPOT) {
-      const double cutoff = fabs(cos(l.cutoff));
-      int attempts_left = 20;
-      D3 dir;
-      do { dir = specular_sample(ln, l.dropoff, 1.0, rng); } while (dot(dir, ln) < cutoff && attempts_left-- > 0);
-      if (attempts_left == 0) dir = specular_sample(ln, l.dropoff, cutoff, rng);   // sic (photontracer.cpp:279-282)
-      ray.o = ld3(l.position); ray.d = dir;
-    } else if (l.type == GI_LIGHT_AREA) {
-      D3 u, v; disk_basis(ln, l.radius, u, v);
-      double r1, r2;
-      do { r1 = rng_double(rng) * 2.0 - 1.0; r2 = rng_double(rng) * 2.0 - 1.0; } while (r1 * r1 + r2 * r2 > 1.0);
-      ray.o = u * r1 + v * r2 + ld3(l.position) + ln * GI_EPS;
-      ray.d = diffuse_sample(ln, 1.0, rng);
-    } else {
-      const D3 a1 = ld3(l.axis1) * l.len1, a2 = ld3(l.axis2) * l.len2;
-      const double r1 = rng_double(rng) - 0.5, r2 = rng_double(rng) - 0.5;
-      ray.o = a1 * r1 + a2 * r2 + ld3(l.position) + ln * GI_EPS;
-      ray.d = diffuse_sample(ln, 1.0, rng);
+struct Round {                       // one emission round (photonmap.cpp:165-173): photon t of the round comes from the
+  int map_type;                      // light whose range [first[l], first[l+1]) holds t and has the number id0 + t
+  uint64_t id0;
+  const uint64_t *first;
+  D3 centroid;
+};
+
+// The emission part of EmitPhotons (photontracer.cpp:182-360) for photon t of a round: seeds the photon's stream and
+// samples its first ray.
+GI_DEV void emit_photon(const ShadeEnv &env, const Round &rd, uint64_t t, Rng &rng, RayD &ray, D3 &photon) {
+  int li = 0;
+  while (li + 1 < env.n_lights && t >= rd.first[li + 1]) li++;
+  const GiLight &l = env.lights[li];
+  photon = ld3(l.color);                                              // NormalizeColor, graphics_utils.cpp:25-36
+  const double total = photon.x + photon.y + photon.z;
+  if (total > 0) photon = photon / total;
+  rng_init(rng, env.p.seed, rd.id0 + t, STAGE_PHOTON + rd.map_type, 0);
+  const D3 ln = ld3(l.direction);
+  if (l.type == GI_LIGHT_DIR) {
+    const D3 center = rd.centroid - ln * env.radius * 3.0;
+    D3 u, v; disk_basis(ln, env.radius, u, v);
+    double r1, r2;
+    do { r1 = rng_double(rng) * 2.0 - 1.0; r2 = rng_double(rng) * 2.0 - 1.0; } while (r1 * r1 + r2 * r2 > 1.0);
+    ray.o = u * r1 + v * r2 + center + ln * GI_EPS; ray.d = ln;
+  } else if (l.type == GI_LIGHT_POINT) {
+    double x, y, z;
+    do { x = rng_double(rng) * 2.0 - 1.0; y = rng_double(rng) * 2.0 - 1.0; z = rng_double(rng) * 2.0 - 1.0; } while (x * x + y * y + z * z > 1.0);
+    ray.o = ld3(l.position); ray.d = normalized(mk3(x, y, z));
+  } else if (l.type == GI_LIGHT_SPOT) {
+    const double cutoff = fabs(cos(l.cutoff));
+    int attempts_left = 20;
+    D3 dir;
+    do { dir = specular_sample(ln, l.dropoff, 1.0, rng); } while (dot(dir, ln) < cutoff && attempts_left-- > 0);
+    if (attempts_left == 0) dir = specular_sample(ln, l.dropoff, cutoff, rng);     // sic (photontracer.cpp:279-282)
+    ray.o = ld3(l.position); ray.d = dir;
+  } else if (l.type == GI_LIGHT_AREA) {
+    D3 u, v; disk_basis(ln, l.radius, u, v);
+    double r1, r2;
+    do { r1 = rng_double(rng) * 2.0 - 1.0; r2 = rng_double(rng) * 2.0 - 1.0; } while (r1 * r1 + r2 * r2 > 1.0);
+    ray.o = u * r1 + v * r2 + ld3(l.position) + ln * GI_EPS;
+    ray.d = diffuse_sample(ln, 1.0, rng);
+  } else {
+    const D3 a1 = ld3(l.axis1) * l.len1, a2 = ld3(l.axis2) * l.len2;
+    const double r1 = rng_double(rng) - 0.5, r2 = rng_double(rng) - 0.5;
+    ray.o = a1 * r1 + a2 * r2 + ld3(l.position) + ln * GI_EPS;
+    ray.d = diffuse_sample(ln, 1.0, rng);
+  }
+}
+
+// Conservative test of a ray against the world boxes of every shape whose material can reflect or refract specularly
+// (ks or kt not black).  A CAUSTIC photon stores nothing before its first specular / transmissive bounce and ends at
+// a diffuse pick (photontracer.cpp:56-60, 106-110); a photon whose first ray misses all of these boxes can only meet
+// surfaces with kt = ks = 0, where both non-diffuse probabilities are zero -- its walk ends at the first hit without
+// side effects, whatever its random numbers.  Skipping it changes nothing but the time.
+GI_DEV bool may_hit_specular(const ShadeEnv &env, const RayD &ray) {
+  for (int i = 0; i < env.n_spec_boxes; i++) {
+    const double *b = env.spec_boxes + 6 * i;
+    double tmin = -1.0e-3, tmax = 1.0e30;
+    bool ok = true;
+    const double o[3] = {ray.o.x, ray.o.y, ray.o.z}, d[3] = {ray.d.x, ray.d.y, ray.d.z};
+#pragma unroll
+    for (int a = 0; a < 3; a++) {
+      if (fabs(d[a]) < 1.0e-12) { ok = ok && o[a] >= b[a] && o[a] <= b[a + 3]; continue; }
+      const double inv = 1.0 / d[a];
+      const double t1 = (b[a] - o[a]) * inv, t2 = (b[a + 3] - o[a]) * inv;
+      tmin = fmax(tmin, fmin(t1, t2)); tmax = fmin(tmax, fmax(t1, t2));
     }
-    photon_trace(env, ray, photon, map_type, id, rng, sink);
+    if (ok && tmin <= tmax) return true;
+  }
+  return false;
+}
+
+// CAUSTIC rounds, pass 1: thread per emitted photon; photons that may reach a specular surface are listed.
+__global__ void __launch_bounds__(256) emit_filter_kernel(ShadeEnv env, Round rd, uint64_t t0, uint32_t n, uint32_t *__restrict__ list,
+                                                          unsigned int *__restrict__ count) {
+  const uint32_t i = blockIdx.x * blockDim.x + threadIdx.x;
+  bool keep = false;
+  if (i < n) {
+    Rng rng; RayD ray; D3 photon;
+    emit_photon(env, rd, t0 + i, rng, ray, photon);
+    keep = may_hit_specular(env, ray);
+  }
+  const unsigned m = __ballot_sync(0xffffffffu, keep);
+  if (m) {
+    const int lane = threadIdx.x & 31;
+    unsigned base = 0;
+    if (lane == __ffs(m) - 1) base = atomicAdd(count, (unsigned)__popc(m));
+    base = __shfl_sync(0xffffffffu, base, __ffs(m) - 1);
+    if (keep) list[base + __popc(m & ((1u << lane) - 1u))] = i;
+  }
+}
+
+// Persistent photon tracer.  Every lane walks one photon; a lane whose photon ends takes the next one at once, so a
+// warp is never held up by its longest walk (most walks end at the first hit, a few go on for dozens of bounces
+// inside glass).  Work is handed out in blocks of 256 photons per warp from one global cursor.  `list` (may be NULL)
+// maps work item -> photon of the batch.
+__global__ void __launch_bounds__(128) trace_kernel(ShadeEnv env, Round rd, uint64_t t0, uint64_t n_items,
+                                                    const uint32_t *__restrict__ list, unsigned long long *cursor, PhotonSink sink) {
+  const int lane = threadIdx.x & 31;
+  bool active = false, store = false;
+  int iter = 0;
+  uint64_t id = 0;
+  RayD ray; D3 photon; Rng rng;
+  unsigned long long wbase = 0; int wleft = 0;
+  bool exhausted = false;
+  for (;;) {
+    unsigned idle = __ballot_sync(0xffffffffu, !active);
+    while (idle && !(exhausted && wleft == 0)) {
+      if (wleft == 0) {
+        unsigned long long b = 0;
+        if (lane == 0) b = atomicAdd(cursor, 256ull);
+        b = __shfl_sync(0xffffffffu, b, 0);
+        if (b >= n_items) { exhausted = true; break; }
+        wbase = b; wleft = (int)((n_items - b) < 256ull ? (n_items - b) : 256ull);
+      }
+      const int mine = __popc(idle & ((1u << lane) - 1u));
+      if (!active && mine < wleft) {
+        const unsigned long long w = wbase + mine;
+        const uint64_t t = t0 + (list ? (uint64_t)list[w] : (uint64_t)w);
+        emit_photon(env, rd, t, rng, ray, photon);
+        id = rd.id0 + t; iter = 0; active = true;
+        store = rd.map_type == MAP_GLOBAL && !env.p.fast_global;
+      }
+      const int taken = min(__popc(idle), wleft);
+      wbase += taken; wleft -= taken;
+      idle = __ballot_sync(0xffffffffu, !active);
+    }
+    if (!__any_sync(0xffffffffu, active)) break;
+    if (active) {
+      active = photon_bounce(env, ray, photon, store, iter, rd.map_type, id, rng, sink);
+      iter++;
+      if (iter >= env.p.max_photon_depth) active = false;
+    }
   }
 }
 
@@ -210,8 +296,10 @@ static int trace_map(GiContext *ctx, const ShadeEnv &env_in, int map_type, int t
   cudaStream_t st = ctx->stream;
   const int nl = env.n_lights;
   unsigned long long cap = (unsigned long long)target + (unsigned long long)target / 2 + 65536;
-  Buf photons, keys, count, first;
-  if (!photons.alloc(sizeof(GiPhoton) * cap) || !keys.alloc(8 * cap) || !count.alloc(8) || !first.alloc(8 * (size_t)(nl + 1))) return 1;
+  Buf photons, keys, count, first, cursor, list;
+  if (!photons.alloc(sizeof(GiPhoton) * cap) || !keys.alloc(8 * cap) || !count.alloc(8) || !first.alloc(8 * (size_t)(nl + 1)) ||
+      !cursor.alloc(16) || !list.alloc(map_type == MAP_CAUSTIC && env.n_spec_boxes >= 0 ? 4ull << 26 : 4))
+    return 1;
   GI_CUDA(cudaMemsetAsync(count.p, 0, 8, st));
   unsigned long long stored = 0;
   uint64_t emitted = 0;
@@ -234,11 +322,28 @@ static int trace_map(GiContext *ctx, const ShadeEnv &env_in, int map_type, int t
     for (;;) {                                               // repeated only if the sink was too small
       GI_CUDA(cudaMemcpyAsync(first.p, h_first.data(), 8 * (size_t)(nl + 1), cudaMemcpyHostToDevice, st));
       PhotonSink sink{photons.as<GiPhoton>(), keys.as<uint64_t>(), count.as<unsigned long long>(), cap};
-      if (n > 0) {
-        const uint64_t want = (n + 127) / 128, gcap = (uint64_t)ctx->sm_count * 64;
-        emit_kernel<<<(unsigned)std::max<uint64_t>(1, std::min(want, gcap)), 128, 0, st>>>(env, centroid, map_type, id_base + emitted, n,
-                                                                                           first.as<uint64_t>(), sink);
-        ctx->launches++;
+      Round rd; rd.map_type = map_type; rd.id0 = id_base + emitted; rd.first = first.as<uint64_t>(); rd.centroid = centroid;
+      const bool filter = map_type == MAP_CAUSTIC && env.n_spec_boxes >= 0;
+      const uint64_t batch = 1ull << 26;                      // photons per launch (bounds the survivor list)
+      for (uint64_t t0 = 0; t0 < n; t0 += batch) {
+        const uint64_t m = std::min(batch, n - t0);
+        uint64_t items = m;
+        GI_CUDA(cudaMemsetAsync(cursor.p, 0, 16, st));
+        if (filter) {
+          emit_filter_kernel<<<(unsigned)((m + 255) / 256), 256, 0, st>>>(env, rd, t0, (uint32_t)m, list.as<uint32_t>(),
+                                                                         (unsigned int *)(cursor.as<unsigned long long>() + 1));
+          ctx->launches++;
+          unsigned int kept = 0;
+          GI_CUDA(cudaMemcpyAsync(&kept, cursor.as<unsigned long long>() + 1, 4, cudaMemcpyDeviceToHost, st));
+          GI_CUDA(cudaStreamSynchronize(st));
+          items = kept;
+        }
+        if (items > 0) {
+          const uint64_t want = (items + 127) / 128, gcap = (uint64_t)ctx->sm_count * 8;     // persistent: 8 CTAs of 4 warps per SM
+          trace_kernel<<<(unsigned)std::max<uint64_t>(1, std::min(want, gcap)), 128, 0, st>>>(
+              env, rd, t0, items, filter ? list.as<uint32_t>() : nullptr, cursor.as<unsigned long long>(), sink);
+          ctx->launches++;
+        }
         GI_CUDA(cudaGetLastError());
       }
       unsigned long long now = 0;
@@ -335,6 +440,8 @@ int gi_trace_photons(GiContext *ctx, const GiParams *params, GiPhotonStats *stat
   env.sc = ctx->scene; env.materials = ctx->scene.materials; env.p = *params;
   env.ambient = ld3(ctx->ambient); env.background = ld3(ctx->background); env.eye = ld3(ctx->camera.eye);
   env.radius = ctx->radius; env.n_lights = nl;
+  env.spec_boxes = ctx->d_spec_boxes; env.n_spec_boxes = ctx->n_spec_boxes;
+  if (getenv("GI_NO_SPEC_FILTER")) env.n_spec_boxes = -1;
   GiLight *d_lights = nullptr;
   GI_CUDA(cudaMalloc(&d_lights, sizeof(GiLight) * nl));
   env.lights = d_lights;

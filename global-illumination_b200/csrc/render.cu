@@ -440,7 +440,7 @@ static int render_accum(GiContext *ctx, const GiParams &params, int sw, int sh, 
   ShadeEnv &env = R.env;
   env.sc = ctx->scene; env.materials = ctx->scene.materials; env.p = params;
   env.ambient = ld3(ctx->ambient); env.background = ld3(ctx->background); env.eye = ld3(ctx->camera.eye);
-  env.radius = ctx->radius;
+  env.radius = ctx->radius; env.spec_boxes = nullptr; env.n_spec_boxes = -1;
   GiParams &p = env.p;
   if (p.dof_test < 1) p.dof_test = 1;
   // a map without photons contributes nothing: same switches MapPhotons flips (photonmap.cpp:339-361)

@@ -108,6 +108,8 @@ struct ShadeEnv {                 // everything a shading thread needs besides t
   const DevMaterial *materials;
   D3 ambient, background, eye;    // eye = camera origin (RayTrace's `eye`, render.cpp:187)
   double radius;                  // SCENE_RADIUS
+  const double *spec_boxes;       // world boxes (min xyz, max xyz) of the shapes with ks or kt not black; photon tracing only
+  int n_spec_boxes;               // -1: list not available (too many shapes)
   GiParams p;
 };
 

@@ -140,3 +140,21 @@ def test_rank_shares_and_power_scale(gpu_ctx):
     gpu_ctx.trace_photons(params)
     one = decode_rgbe(gpu_ctx.get_photons(0)["rgbe"]).sum(0)
     assert np.all(np.abs(two - one) < 0.06 * one)
+
+
+def test_specular_prefilter_changes_nothing_but_time(gpu_ctx):
+    """Caustic photons whose first ray misses every specular / transmissive shape are skipped (photon_trace.cu:
+    may_hit_specular); the stored map must be byte-identical to the one traced without the prefilter."""
+    for scene in ("cornell", "jensen", "glass_cube"):
+        hs = gi_b200.HostScene(os.path.join(GOLDEN, scene + ".gisc"))
+        gpu_ctx.upload_scene(hs)
+        params, _ = gi_b200.parse_flags(["-global", "3000", "-caustic", "40000", "-seed", "11"])
+        st1 = gpu_ctx.trace_photons(params)
+        a = gpu_ctx.get_photons(1).tobytes(); ag = gpu_ctx.get_photons(0).tobytes()
+        os.environ["GI_NO_SPEC_FILTER"] = "1"
+        try:
+            st2 = gpu_ctx.trace_photons(params)
+        finally:
+            del os.environ["GI_NO_SPEC_FILTER"]
+        assert st1.caustic_emitted == st2.caustic_emitted and st1.caustic_stored == st2.caustic_stored > 0
+        assert gpu_ctx.get_photons(1).tobytes() == a and gpu_ctx.get_photons(0).tobytes() == ag
