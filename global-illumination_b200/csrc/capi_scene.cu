@@ -95,6 +95,7 @@ void gi_destroy(GiContext *ctx) {
   cudaSetDevice(ctx->device);
   free_scene(ctx);
   free_map(ctx->maps[0]); free_map(ctx->maps[1]);
+  if (ctx->render_ws && ctx->render_ws_free) ctx->render_ws_free(ctx->render_ws);
   if (ctx->stream) cudaStreamDestroy(ctx->stream);
   delete ctx;
 }

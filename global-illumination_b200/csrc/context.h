@@ -25,6 +25,8 @@ struct GiContext {
   double *d_spec_boxes = nullptr;             // scene_allocs entry: boxes of the specular / transmissive shapes (photon_trace.cu)
   int n_spec_boxes = -1;
   gi::PhotonMapStore maps[2];                 // GI_MAP_GLOBAL, GI_MAP_CAUSTIC
+  void *render_ws = nullptr;                  // render.cu's device workspace, created by the first gi_render
+  void (*render_ws_free)(void *) = nullptr;
   uint64_t launches = 0;                      // kernels launched by this context (bench.py: gpu_launches)
 };
 

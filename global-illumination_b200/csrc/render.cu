@@ -23,6 +23,7 @@
 #include <cub/cub.cuh>
 #include <algorithm>
 #include <cstdio>
+#include <cstdlib>
 #include <cstring>
 #include "context.h"
 #include "gather.h"
@@ -184,126 +185,152 @@ __global__ void __launch_bounds__(128) direct_kernel(ShadeEnv env, uint64_t firs
 // ------------------------------------------------------------------------------------------------ secondary paths
 enum { MODE_PATH = 0, MODE_INDIRECT = 1 };
 
+
 // MonteCarlo_PathTrace (montecarlo.cpp:16-171, mode PATH) and MonteCarlo_IndirectSample (:177-305, mode INDIRECT)
-// as one loop.  `scale` is what the caller multiplies the path's colour with before adding it to the pixel; a
+// share one loop body.  `scale` is what the caller multiplies the path's colour with before adding it to the pixel; a
 // diffuse pick in mode PATH with INDIRECT_ILLUM on is the nested IndirectIllumination(inMonteCarlo = true) call
-// (raytracer.cpp:112-135 with one sample): the loop restarts in mode INDIRECT with the product of the weights.
-GI_DEV D3 trace_path(const ShadeEnv &env, RayD ray, int mode, D3 scale, uint32_t pix, Rng &rng, const Queue &qglobal,
-                     const Queue &qcaustic, RayStats &st) {
+// (raytracer.cpp:112-135 with one sample): the walk goes on in mode INDIRECT with the product of the weights and a
+// fresh depth count.
+struct PathState {
+  RayD ray;                          // ray.o doubles as the reference's ray_start
+  D3 scale, tw, out;
+  Rng rng;
+  uint32_t pix, item;
+  int mode, iter;
+};
+
+// one iteration of the loop; returns false when the walk ends
+GI_DEV bool path_step(const ShadeEnv &env, PathState &s, const Queue &qglobal, const Queue &qcaustic, RayStats &st) {
   const GiParams &p = env.p;
-  D3 out = mk3(0, 0, 0);
-  if (mode == MODE_PATH && !p.monte_carlo) return out;
-  D3 tw = mk3(1, 1, 1);
-  D3 ray_start = ray.o;
-  for (int iter = 0; iter < p.max_monte_depth; iter++) {
-    HitRec h;
-    closest_hit(env.sc, ray, h);
-    if (h.prim < 0) { out = out + mul3(scale, mul3(tw, env.background)); break; }
-    st.monte++;
-    const Brdf b = load_brdf(env.materials[env.sc.elements[h.element].material]);
-    const D3 point = h.p, normal = h.n;
-    const D3 view = normalized(point - ray_start);
-    const double cos_theta = dot(normal, -view);
-    double r_coeff = 0;
-    if (mode == MODE_PATH) {
-      D3 cb = mk3(0, 0, 0);
-      if (p.ambient) cb = cb + env.ambient;
-      if (b.diffuse || b.specular) direct_illumination(env, point, normal, ray_start, cb, b, cos_theta, true, rng, nullptr, st);
-      if (p.caustic_illum && b.diffuse) {
-        push_request(qcaustic, point, normal, reflective_bounce(normal, view, cos_theta), cos_theta, b, mul3(scale, tw), pix);
-        st.caustic++;
-      }
-      out = out + mul3(scale, mul3(cb, tw));
-      if (p.specular_illum && p.transmissive_illum && p.fresnel && b.transparent)
-        r_coeff = reflection_coeff(cos_theta, b.ir, p.ir_air);
-    } else if (p.fresnel && b.transparent) r_coeff = reflection_coeff(cos_theta, b.ir, p.ir_air);
+  HitRec h;
+  closest_hit(env.sc, s.ray, h);
+  if (h.prim < 0) { s.out = s.out + mul3(s.scale, mul3(s.tw, env.background)); return false; }
+  st.monte++;
+  const Brdf b = load_brdf(env.materials[env.sc.elements[h.element].material]);
+  const D3 point = h.p, normal = h.n;
+  const D3 view = normalized(point - s.ray.o);
+  const double cos_theta = dot(normal, -view);
+  double r_coeff = 0;
+  if (s.mode == MODE_PATH) {
+    D3 cb = mk3(0, 0, 0);
+    if (p.ambient) cb = cb + env.ambient;
+    if (b.diffuse || b.specular) direct_illumination(env, point, normal, s.ray.o, cb, b, cos_theta, true, s.rng, nullptr, st);
+    if (p.caustic_illum && b.diffuse) {
+      push_request(qcaustic, point, normal, reflective_bounce(normal, view, cos_theta), cos_theta, b, mul3(s.scale, s.tw), s.pix);
+      st.caustic++;
+    }
+    s.out = s.out + mul3(s.scale, mul3(cb, s.tw));
+    if (p.specular_illum && p.transmissive_illum && p.fresnel && b.transparent) r_coeff = reflection_coeff(cos_theta, b.ir, p.ir_air);
+  } else if (p.fresnel && b.transparent) r_coeff = reflection_coeff(cos_theta, b.ir, p.ir_air);
 
-    const double prob_diffuse = max_channel(b.kd);
-    double prob_transmission = max_channel(b.kt);
-    const double prob_specular = max_channel(b.ks) + r_coeff * prob_transmission;
-    prob_transmission *= (1.0 - r_coeff);
-    const double prob_terminate = max_channel(b.ke) + p.prob_absorb;
-    const double prob_total = prob_diffuse + prob_transmission + prob_specular + prob_terminate;
-    double rnd = rng_double(rng);
-    if (prob_total > 1.0) rnd *= prob_total;
+  const double prob_diffuse = max_channel(b.kd);
+  double prob_transmission = max_channel(b.kt);
+  const double prob_specular = max_channel(b.ks) + r_coeff * prob_transmission;
+  prob_transmission *= (1.0 - r_coeff);
+  const double prob_terminate = max_channel(b.ke) + p.prob_absorb;
+  const double prob_total = prob_diffuse + prob_transmission + prob_specular + prob_terminate;
+  double rnd = rng_double(s.rng);
+  if (prob_total > 1.0) rnd *= prob_total;
 
-    D3 bounce;
-    if (rnd < prob_diffuse) {
-      const D3 w = mul3(b.kd, tw) / prob_diffuse;
-      if (mode == MODE_INDIRECT || (!p.indirect_illum && p.fast_global)) {
-        push_request(qglobal, point, normal, reflective_bounce(normal, view, cos_theta), cos_theta, b, mul3(scale, w), pix);
-        if (mode == MODE_PATH) st.indirect++;                 // EstimateGlobalIllumination counts, EstimateRadiance does not
-        break;
-      }
-      if (!p.indirect_illum) break;
-      scale = mul3(scale, mul3(b.kd, w));                      // (inner * kd) * kd * tw / prob_diffuse
-      bounce = diffuse_sample(normal, cos_theta, rng);
-      st.indirect++;
-      mode = MODE_INDIRECT; tw = mk3(1, 1, 1); iter = -1;
-    } else if (rnd < prob_diffuse + prob_transmission) {
-      if (mode == MODE_PATH && !p.transmissive_illum) break;
-      const D3 exact = transmissive_bounce(normal, view, cos_theta, b.ir, p.ir_air);
-      bounce = p.distrib_transmissive ? specular_sample(exact, b.n, cos_theta, rng) : exact;
-      st.transmissive++;
-      tw = mul3(tw, (b.kt * (1.0 - r_coeff)) / prob_transmission);
-    } else if (rnd < prob_diffuse + prob_transmission + prob_specular) {
-      if (mode == MODE_PATH && !p.specular_illum) break;
-      const D3 exact = reflective_bounce(normal, view, cos_theta);
-      bounce = p.distrib_specular ? specular_sample(exact, b.n, cos_theta, rng) : exact;
-      st.specular++;
-      tw = mul3(tw, (b.ks + b.kt * r_coeff) / prob_specular);
-    } else break;
-    ray_start = point + bounce * GI_EPS;
-    ray.o = ray_start; ray.d = bounce;
-  }
-  return out;
+  D3 bounce;
+  if (rnd < prob_diffuse) {
+    const D3 w = mul3(b.kd, s.tw) / prob_diffuse;
+    if (s.mode == MODE_INDIRECT || (!p.indirect_illum && p.fast_global)) {
+      push_request(qglobal, point, normal, reflective_bounce(normal, view, cos_theta), cos_theta, b, mul3(s.scale, w), s.pix);
+      if (s.mode == MODE_PATH) st.indirect++;                 // EstimateGlobalIllumination counts, EstimateRadiance does not
+      return false;
+    }
+    if (!p.indirect_illum) return false;
+    s.scale = mul3(s.scale, mul3(b.kd, w));                    // (inner * kd) * kd * tw / prob_diffuse
+    bounce = diffuse_sample(normal, cos_theta, s.rng);
+    st.indirect++;
+    s.mode = MODE_INDIRECT; s.tw = mk3(1, 1, 1); s.iter = -1;
+  } else if (rnd < prob_diffuse + prob_transmission) {
+    if (s.mode == MODE_PATH && !p.transmissive_illum) return false;
+    const D3 exact = transmissive_bounce(normal, view, cos_theta, b.ir, p.ir_air);
+    bounce = p.distrib_transmissive ? specular_sample(exact, b.n, cos_theta, s.rng) : exact;
+    st.transmissive++;
+    s.tw = mul3(s.tw, (b.kt * (1.0 - r_coeff)) / prob_transmission);
+  } else if (rnd < prob_diffuse + prob_transmission + prob_specular) {
+    if (s.mode == MODE_PATH && !p.specular_illum) return false;
+    const D3 exact = reflective_bounce(normal, view, cos_theta);
+    bounce = p.distrib_specular ? specular_sample(exact, b.n, cos_theta, s.rng) : exact;
+    st.specular++;
+    s.tw = mul3(s.tw, (b.ks + b.kt * r_coeff) / prob_specular);
+  } else return false;
+  s.ray.o = point + bounce * GI_EPS; s.ray.d = bounce;
+  s.iter++;
+  return s.iter < p.max_monte_depth;
 }
 
-// One thread per secondary path.  Item g belongs to the primary hit h with offs[h] <= g < offs[h+1]; inside the hit
-// the items are its transmissive samples, then its specular samples, then its indirect samples
+// Start of secondary path `g`: item g belongs to the primary hit h with offs[h] <= g < offs[h+1]; inside the hit the
+// items are its transmissive samples, then its specular samples, then its indirect samples
 // (TransmissiveIllumination / SpecularIllumination / IndirectIllumination, raytracer.cpp:47-135).
-__global__ void __launch_bounds__(128) path_kernel(ShadeEnv env, uint64_t first_sample, uint64_t n_hits,
-                                                   const PrimHit *__restrict__ hits, const uint64_t *__restrict__ offs,
-                                                   uint64_t item0, uint32_t n, double *__restrict__ item_rgb,
-                                                   uint32_t *__restrict__ item_pix, Queue qglobal, Queue qcaustic,
-                                                   RayStats *stats) {
+// Returns false if the path contributes nothing (MONTE_CARLO off).
+GI_DEV bool path_begin(const ShadeEnv &env, uint64_t first_sample, const PrimHit *__restrict__ hits,
+                       const uint64_t *__restrict__ offs, uint64_t g, uint32_t hidx, PathState &s, RayStats &st) {
+  const uint32_t local = (uint32_t)(g - offs[hidx]);
+  const PrimHit ph = hits[hidx];
+  const Brdf b = load_brdf(env.materials[ph.material]);
+  const D3 point = ld3(ph.p), normal = ld3(ph.n);
+  const D3 view = normalized(point - env.eye);
+  const double cos_theta = dot(normal, -view);
+  const SubPaths sp = sub_paths(env.p, b, cos_theta);
+  rng_init(s.rng, env.p.seed, first_sample + hidx, STAGE_PATH, local);
+  D3 total_weight, bounce; int count;
+  if (local < (uint32_t)sp.n_t) {
+    const D3 exact = transmissive_bounce(normal, view, cos_theta, b.ir, env.p.ir_air);
+    total_weight = b.kt * (1.0 - sp.r_coeff); count = sp.n_t; s.mode = MODE_PATH;
+    bounce = env.p.distrib_transmissive ? specular_sample(exact, b.n, cos_theta, s.rng) : exact;
+    st.transmissive++;
+  } else if (local < (uint32_t)(sp.n_t + sp.n_s)) {
+    const D3 exact = reflective_bounce(normal, view, cos_theta);
+    total_weight = b.kt * sp.r_coeff + b.ks; count = sp.n_s; s.mode = MODE_PATH;
+    bounce = env.p.distrib_specular ? specular_sample(exact, b.n, cos_theta, s.rng) : exact;
+    st.specular++;
+  } else {
+    total_weight = b.kd; count = sp.n_i; s.mode = MODE_INDIRECT;
+    bounce = diffuse_sample(normal, cos_theta, s.rng);
+    st.indirect++;
+  }
+  s.ray.o = point + bounce * GI_EPS; s.ray.d = bounce;
+  s.scale = total_weight / (double)count; s.tw = mk3(1, 1, 1); s.out = mk3(0, 0, 0);
+  s.pix = ph.pix; s.iter = 0;
+  return !(s.mode == MODE_PATH && !env.p.monte_carlo) && env.p.max_monte_depth > 0;
+}
+
+// One thread per secondary path, start to end.  (A persistent variant in which lanes take a new path as soon as
+// theirs ends -- the design of the photon tracer, photon_trace.cu -- was measured 15-20 % slower here: nearly every
+// secondary path is one or two bounces long, so there is little imbalance to win back and the refill costs more.)
+// MINB = resident CTAs per SM the kernel is compiled for: 6 -> 80 registers, 24 warps per SM; the kernel is
+// latency-bound (incoherent BVH walks), more warps beat fewer spills.
+template <int MINB>
+__global__ void __launch_bounds__(128, MINB) path_kernel(ShadeEnv env, uint64_t first_sample, const PrimHit *__restrict__ hits,
+                                                         const uint64_t *__restrict__ offs, const uint32_t *__restrict__ item_hit,
+                                                         uint64_t item0, uint32_t n, double *__restrict__ item_rgb,
+                                                         uint32_t *__restrict__ item_pix, Queue qglobal, Queue qcaustic, RayStats *stats) {
   RayStats st = zero_stats();
   const uint32_t t = blockIdx.x * blockDim.x + threadIdx.x;
   if (t < n) {
-    const uint64_t g = item0 + t;
-    uint64_t lo = 0, hi = n_hits;                       // largest h with offs[h] <= g
-    while (hi - lo > 1) { const uint64_t mid = (lo + hi) >> 1; if (offs[mid] <= g) lo = mid; else hi = mid; }
-    const uint64_t hidx = lo;
-    const uint32_t local = (uint32_t)(g - offs[hidx]);
-    const PrimHit ph = hits[hidx];
-    const Brdf b = load_brdf(env.materials[ph.material]);
-    const D3 point = ld3(ph.p), normal = ld3(ph.n);
-    D3 view = normalized(point - env.eye);
-    const double cos_theta = dot(normal, -view);
-    const SubPaths sp = sub_paths(env.p, b, cos_theta);
-    Rng rng; rng_init(rng, env.p.seed, first_sample + hidx, STAGE_PATH, local);
-    D3 total_weight, bounce; int mode, count;
-    if (local < (uint32_t)sp.n_t) {
-      const D3 exact = transmissive_bounce(normal, view, cos_theta, b.ir, env.p.ir_air);
-      total_weight = b.kt * (1.0 - sp.r_coeff); count = sp.n_t; mode = MODE_PATH;
-      bounce = env.p.distrib_transmissive ? specular_sample(exact, b.n, cos_theta, rng) : exact;
-      st.transmissive++;
-    } else if (local < (uint32_t)(sp.n_t + sp.n_s)) {
-      const D3 exact = reflective_bounce(normal, view, cos_theta);
-      total_weight = b.kt * sp.r_coeff + b.ks; count = sp.n_s; mode = MODE_PATH;
-      bounce = env.p.distrib_specular ? specular_sample(exact, b.n, cos_theta, rng) : exact;
-      st.specular++;
-    } else {
-      total_weight = b.kd; count = sp.n_i; mode = MODE_INDIRECT;
-      bounce = diffuse_sample(normal, cos_theta, rng);
-      st.indirect++;
-    }
-    RayD ray; ray.o = point + bounce * GI_EPS; ray.d = bounce;
-    const D3 c = trace_path(env, ray, mode, total_weight / (double)count, ph.pix, rng, qglobal, qcaustic, st);
-    item_rgb[3 * (size_t)t] = c.x; item_rgb[3 * (size_t)t + 1] = c.y; item_rgb[3 * (size_t)t + 2] = c.z;
-    item_pix[t] = ph.pix;
+    PathState s;
+    s.item = t;
+    bool active = path_begin(env, first_sample, hits, offs, item0 + t, item_hit[t] - 1, s, st);
+    while (active) active = path_step(env, s, qglobal, qcaustic, st);
+    item_rgb[3 * (size_t)t] = s.out.x; item_rgb[3 * (size_t)t + 1] = s.out.y; item_rgb[3 * (size_t)t + 2] = s.out.z;
+    item_pix[t] = s.pix;
   }
   flush_stats(stats, st);
+}
+
+// item -> primary hit for a batch of items [item0, item0 + m): every hit that owns items marks its first item with its
+// index, the rest is filled by an inclusive max-scan (item_hit[] is zero-initialised; indices are stored + 1).
+__global__ void __launch_bounds__(256) mark_items_kernel(const uint64_t *__restrict__ offs, const uint32_t *__restrict__ n_items,
+                                                         uint64_t n_hits, uint64_t item0, uint32_t m, uint32_t *__restrict__ item_hit) {
+  const uint64_t h = (uint64_t)blockIdx.x * blockDim.x + threadIdx.x;
+  if (h >= n_hits || n_items[h] == 0) return;
+  const uint64_t o = offs[h];
+  if (o >= item0 && o < item0 + m) item_hit[o - item0] = (uint32_t)h + 1;
+  else if (o < item0 && o + n_items[h] > item0) item_hit[0] = (uint32_t)h + 1;     // the hit the batch starts inside
 }
 
 // Adds the item colours of a finished batch into the accumulator.  Items of one pixel are consecutive, so a warp
@@ -334,6 +361,42 @@ __global__ void __launch_bounds__(256) commit_requests_kernel(const double *__re
   const uint64_t t = (uint64_t)blockIdx.x * blockDim.x + threadIdx.x;
   if (t >= n) return;
   add3(accum + 3 * (size_t)pix[t], mk3(w[3 * t] * rgb[3 * t], w[3 * t + 1] * rgb[3 * t + 1], w[3 * t + 2] * rgb[3 * t + 2]));
+}
+
+// Requests reach a queue in the order the path threads happened to push them, i.e. scattered over the scene.  Sorting
+// them along a Morton curve before the gather makes the 16 consecutive queries a gather warp takes neighbours in
+// space: the k-th distance of one query is then a good first search radius for the next (gather.cu), and the warps
+// of a CTA walk the same part of the kd-tree.
+GI_DEV uint32_t spread10(uint32_t v) {
+  v &= 1023u; v = (v | (v << 16)) & 0x030000FFu; v = (v | (v << 8)) & 0x0300F00Fu; v = (v | (v << 4)) & 0x030C30C3u;
+  return (v | (v << 2)) & 0x09249249u;
+}
+__global__ void __launch_bounds__(256) request_keys_kernel(const GiGatherQuery *__restrict__ q, uint64_t n, D3 lo, D3 inv,
+                                                           uint32_t *__restrict__ keys, uint32_t *__restrict__ order) {
+  const uint64_t t = (uint64_t)blockIdx.x * blockDim.x + threadIdx.x;
+  if (t >= n) return;
+  const double x = (q[t].p[0] - lo.x) * inv.x, y = (q[t].p[1] - lo.y) * inv.y, z = (q[t].p[2] - lo.z) * inv.z;
+  const uint32_t xi = (uint32_t)fmin(fmax(x * 1024.0, 0.0), 1023.0), yi = (uint32_t)fmin(fmax(y * 1024.0, 0.0), 1023.0),
+                 zi = (uint32_t)fmin(fmax(z * 1024.0, 0.0), 1023.0);
+  keys[t] = spread10(xi) | (spread10(yi) << 1) | (spread10(zi) << 2);
+  order[t] = (uint32_t)t;
+}
+// 136-byte records moved as 17 coalesced 8-byte words per request
+__global__ void __launch_bounds__(256) permute_requests_kernel(const double *__restrict__ in, const uint32_t *__restrict__ order,
+                                                               uint64_t n, double *__restrict__ out) {
+  const uint64_t t = (uint64_t)blockIdx.x * blockDim.x + threadIdx.x;
+  if (t >= n * 17) return;
+  const uint64_t r = t / 17, c = t % 17;
+  out[t] = in[(uint64_t)order[r] * 17 + c];
+}
+// accum[pix] += weight * estimate; request order[t] owns estimate t
+__global__ void __launch_bounds__(256) commit_sorted_kernel(const double *__restrict__ w, const uint32_t *__restrict__ pix,
+                                                            const uint32_t *__restrict__ order, const double *__restrict__ rgb,
+                                                            uint64_t n, double *__restrict__ accum) {
+  const uint64_t t = (uint64_t)blockIdx.x * blockDim.x + threadIdx.x;
+  if (t >= n) return;
+  const uint64_t r = order[t];
+  add3(accum + 3 * (size_t)pix[r], mk3(w[3 * r] * rgb[3 * t], w[3 * r + 1] * rgb[3 * t + 1], w[3 * r + 2] * rgb[3 * t + 2]));
 }
 
 // image_buffer[i][j] /= DOF_TEST (render.cpp:135)
@@ -367,12 +430,17 @@ namespace {
 struct DevBuf {                      // frees on scope exit
   void *p = nullptr;
   ~DevBuf() { if (p) cudaFree(p); }
-  bool alloc(size_t bytes) { return cuda_ok(cudaMalloc(&p, bytes ? bytes : 1), "cudaMalloc(render)"); }
+  bool alloc(size_t bytes) {
+    if (p) { cudaFree(p); p = nullptr; }
+    return cuda_ok(cudaMalloc(&p, bytes ? bytes : 1), "cudaMalloc(render)");
+  }
   template <class T> T *as() const { return (T *)p; }
 };
 
 struct QueueStore {
   DevBuf q, w, pix, count, rgb;
+  DevBuf sorted_q, keys, keys2, order, order2, sort_tmp;      // Morton ordering of the requests
+  size_t sort_bytes = 0;
   Queue view{};
   bool alloc(unsigned long long cap) {
     if (!q.alloc(sizeof(GiGatherQuery) * cap) || !w.alloc(sizeof(double) * 3 * cap) || !pix.alloc(sizeof(uint32_t) * cap) ||
@@ -380,9 +448,57 @@ struct QueueStore {
       return false;
     view.q = q.as<GiGatherQuery>(); view.w = w.as<double>(); view.pix = pix.as<uint32_t>();
     view.count = count.as<unsigned long long>(); view.cap = cap;
+    if (!sorted_q.alloc(sizeof(GiGatherQuery) * cap) || !keys.alloc(4 * cap) || !keys2.alloc(4 * cap) || !order.alloc(4 * cap) ||
+        !order2.alloc(4 * cap))
+      return false;
+    cub::DeviceRadixSort::SortPairs(nullptr, sort_bytes, keys.as<uint32_t>(), keys2.as<uint32_t>(), order.as<uint32_t>(),
+                                    order2.as<uint32_t>(), (int)cap, 0, 30);
+    return sort_tmp.alloc(sort_bytes);
+  }
+};
+
+// Device buffers of the render stages, allocated on the first gi_render of a context and kept until gi_destroy
+// (cudaMalloc / cudaFree of a few GB per frame costs tens of milliseconds and jitters).
+struct Workspace {
+  static constexpr uint64_t chunk = 1ull << 22;          // primary samples per pass
+  static constexpr uint32_t batch_max = 1u << 21;        // secondary paths per pass
+  static constexpr unsigned long long qcap = 1ull << 22; // >= chunk (direct_kernel pushes at most one request per hit)
+  DevBuf hits, n_items, offs, item_rgb, item_pix, scan_tmp, item_hit, hit_scan_tmp, lights, stats, accum;
+  QueueStore qg, qc;
+  size_t scan_bytes = 0, hit_scan_bytes = 0, accum_doubles = 0, n_lights = 0;
+  bool ready = false;
+  bool init(cudaStream_t st) {
+    if (ready) return true;
+    if (!hits.alloc(sizeof(PrimHit) * chunk) || !n_items.alloc(4 * (chunk + 1)) || !offs.alloc(8 * (chunk + 1)) ||
+        !item_rgb.alloc(sizeof(double) * 3 * batch_max) || !item_pix.alloc(4 * (size_t)batch_max) || !item_hit.alloc(4 * (size_t)batch_max) ||
+        !stats.alloc(2 * sizeof(RayStats)) || !qg.alloc(qcap) || !qc.alloc(qcap))
+      return false;
+    cub::DeviceScan::ExclusiveSum(nullptr, scan_bytes, n_items.as<uint32_t>(), offs.as<uint64_t>(), (int)(chunk + 1), st);
+    cub::DeviceScan::InclusiveScan(nullptr, hit_scan_bytes, item_hit.as<uint32_t>(), item_hit.as<uint32_t>(), cub::Max(), (int)batch_max, st);
+    if (!scan_tmp.alloc(scan_bytes) || !hit_scan_tmp.alloc(hit_scan_bytes)) return false;
+    ready = true;
+    return true;
+  }
+  bool fit_accum(size_t doubles) {
+    if (doubles <= accum_doubles) return true;
+    if (!accum.alloc(sizeof(double) * doubles)) { accum_doubles = 0; return false; }
+    accum_doubles = doubles;
+    return true;
+  }
+  bool fit_lights(size_t n) {
+    if (n <= n_lights && lights.p) return true;
+    if (!lights.alloc(sizeof(GiLight) * (n ? n : 1))) { n_lights = 0; return false; }
+    n_lights = n;
     return true;
   }
 };
+void free_workspace(void *p) { delete (Workspace *)p; }
+
+Workspace *workspace(GiContext *ctx) {
+  if (!ctx->render_ws) { ctx->render_ws = new Workspace(); ctx->render_ws_free = free_workspace; }
+  Workspace *w = (Workspace *)ctx->render_ws;
+  return w->init(ctx->stream) ? w : nullptr;
+}
 
 inline int grid_for(uint64_t n, int block, int sm_count, int per_sm) {
   const uint64_t want = (n + block - 1) / block, cap = (uint64_t)sm_count * per_sm;
@@ -395,7 +511,9 @@ struct Renderer {
   cudaStream_t st;
   double *accum;
   RayStats *d_stats;
-  QueueStore qg, qc;
+  QueueStore &qg, &qc;
+  bool sort_requests = true;
+  Renderer(Workspace &w) : qg(w.qg), qc(w.qc) {}
 
   // d_stats[0]: primary + direct kernels; d_stats[1]: the path batch in flight (counted once the batch commits)
   bool reset_queues() {
@@ -422,10 +540,27 @@ struct Renderer {
     const double r = map == GI_MAP_GLOBAL ? p.global_estimate_dist : p.caustic_estimate_dist;
     const int filter = map == GI_MAP_GLOBAL ? p.global_filter : p.caustic_filter;
     if (ctx->maps[map].dev.n == 0) return true;          // empty map: EstimateRadiance adds nothing
-    if (gi_gather_batch_device(ctx, map, qs.view.q, n, k, r, filter, &p, nullptr, nullptr, qs.rgb.as<double>(), st)) return false;
-    commit_requests_kernel<<<(unsigned)((n + 255) / 256), 256, 0, st>>>(qs.view.w, qs.view.pix, qs.rgb.as<double>(), n, accum);
-    ctx->launches++;
-    return cuda_ok(cudaGetLastError(), "commit_requests_kernel");
+    if (n < 4096 || !sort_requests) {
+      if (gi_gather_batch_device(ctx, map, qs.view.q, n, k, r, filter, &p, nullptr, nullptr, qs.rgb.as<double>(), st)) return false;
+      commit_requests_kernel<<<(unsigned)((n + 255) / 256), 256, 0, st>>>(qs.view.w, qs.view.pix, qs.rgb.as<double>(), n, accum);
+      ctx->launches++;
+      return cuda_ok(cudaGetLastError(), "commit_requests_kernel");
+    }
+    const D3 lo = ld3(ctx->bbox_min), hi = ld3(ctx->bbox_max);
+    const D3 inv = mk3(1.0 / fmax(hi.x - lo.x, 1e-300), 1.0 / fmax(hi.y - lo.y, 1e-300), 1.0 / fmax(hi.z - lo.z, 1e-300));
+    const unsigned blocks = (unsigned)((n + 255) / 256);
+    request_keys_kernel<<<blocks, 256, 0, st>>>(qs.view.q, n, lo, inv, qs.keys.as<uint32_t>(), qs.order.as<uint32_t>());
+    size_t bytes = qs.sort_bytes;
+    if (!cuda_ok(cub::DeviceRadixSort::SortPairs(qs.sort_tmp.p, bytes, qs.keys.as<uint32_t>(), qs.keys2.as<uint32_t>(),
+                                                 qs.order.as<uint32_t>(), qs.order2.as<uint32_t>(), (int)n, 0, 30, st), "sort requests"))
+      return false;
+    permute_requests_kernel<<<(unsigned)((n * 17 + 255) / 256), 256, 0, st>>>((const double *)qs.view.q, qs.order2.as<uint32_t>(), n,
+                                                                             qs.sorted_q.as<double>());
+    if (gi_gather_batch_device(ctx, map, qs.sorted_q.as<GiGatherQuery>(), n, k, r, filter, &p, nullptr, nullptr, qs.rgb.as<double>(), st))
+      return false;
+    commit_sorted_kernel<<<blocks, 256, 0, st>>>(qs.view.w, qs.view.pix, qs.order2.as<uint32_t>(), qs.rgb.as<double>(), n, accum);
+    ctx->launches += 7;
+    return cuda_ok(cudaGetLastError(), "sorted gather");
   }
 };
 
@@ -435,8 +570,12 @@ struct Renderer {
 // zero-initialised by the caller), already divided by DOF_TEST.
 static int render_accum(GiContext *ctx, const GiParams &params, int sw, int sh, uint64_t pix0, uint64_t pix1, double *accum,
                         RayStats *d_stats, RayStats &host_paths) {
-  Renderer R;
+  Workspace *wsp = workspace(ctx);
+  if (!wsp) return 1;
+  Workspace &ws = *wsp;
+  Renderer R(ws);
   R.ctx = ctx; R.st = ctx->stream; R.accum = accum; R.d_stats = d_stats;
+  if (const char *e = getenv("GI_SORT_REQUESTS")) R.sort_requests = atoi(e) != 0;
   ShadeEnv &env = R.env;
   env.sc = ctx->scene; env.materials = ctx->scene.materials; env.p = params;
   env.ambient = ld3(ctx->ambient); env.background = ld3(ctx->background); env.eye = ld3(ctx->camera.eye);
@@ -447,12 +586,11 @@ static int render_accum(GiContext *ctx, const GiParams &params, int sw, int sh, 
   if (ctx->maps[GI_MAP_GLOBAL].dev.n == 0) { p.indirect_illum = 0; p.direct_photon_illum = 0; p.fast_global = 0; }
   if (ctx->maps[GI_MAP_CAUSTIC].dev.n == 0) p.caustic_illum = 0;
 
-  DevBuf lights;
   env.n_lights = (int)ctx->lights.size();
-  if (!lights.alloc(sizeof(GiLight) * ctx->lights.size())) return 1;
+  if (!ws.fit_lights(ctx->lights.size())) return 1;
   if (env.n_lights)
-    GI_CUDA(cudaMemcpyAsync(lights.p, ctx->lights.data(), sizeof(GiLight) * ctx->lights.size(), cudaMemcpyHostToDevice, R.st));
-  env.lights = lights.as<GiLight>();
+    GI_CUDA(cudaMemcpyAsync(ws.lights.p, ctx->lights.data(), sizeof(GiLight) * ctx->lights.size(), cudaMemcpyHostToDevice, R.st));
+  env.lights = ws.lights.as<GiLight>();
 
   Frame2 f;                                               // render.cpp:64-77
   const GiCamera &cam = ctx->camera;
@@ -465,16 +603,14 @@ static int render_accum(GiContext *ctx, const GiParams &params, int sw, int sh, 
   f.u = normalized(ld3(cam.up)) * p.aperture_radius; f.v = normalized(ld3(cam.right)) * p.aperture_radius;
   f.xc = sw / 2; f.yc = sh / 2; f.w = sw; f.h = sh; f.sw = sw; f.sh = sh; f.dof = p.dof_test;
 
-  const uint64_t chunk = 1ull << 22;                      // primary samples per pass
-  uint32_t batch = 1u << 21;                              // secondary paths per pass
-  const unsigned long long qcap = 1ull << 22;             // >= chunk (direct_kernel pushes at most one request per hit)
-  DevBuf hits, n_items, offs, item_rgb, item_pix, scan_tmp;
-  if (!hits.alloc(sizeof(PrimHit) * chunk) || !n_items.alloc(4 * (chunk + 1)) || !offs.alloc(8 * (chunk + 1)) ||
-      !item_rgb.alloc(sizeof(double) * 3 * batch) || !item_pix.alloc(4 * (size_t)batch) || !R.qg.alloc(qcap) || !R.qc.alloc(qcap))
-    return 1;
-  size_t scan_bytes = 0;
-  cub::DeviceScan::ExclusiveSum(nullptr, scan_bytes, n_items.as<uint32_t>(), offs.as<uint64_t>(), (int)(chunk + 1), R.st);
-  if (!scan_tmp.alloc(scan_bytes)) return 1;
+  const uint64_t chunk = Workspace::chunk;
+  uint32_t batch = Workspace::batch_max;
+  const unsigned long long qcap = Workspace::qcap;
+  DevBuf &hits = ws.hits, &n_items = ws.n_items, &offs = ws.offs, &item_rgb = ws.item_rgb, &item_pix = ws.item_pix, &scan_tmp = ws.scan_tmp,
+         &item_hit = ws.item_hit, &hit_scan_tmp = ws.hit_scan_tmp;
+  size_t scan_bytes = ws.scan_bytes, hit_scan_bytes = ws.hit_scan_bytes;
+  int path_occ = 6;                                       // resident CTAs per SM: 4 (128 registers) or 6 (80 registers)
+  if (const char *e = getenv("GI_PATH_OCC")) path_occ = atoi(e);
 
   const uint64_t s_begin = pix0 * p.dof_test, s_end = pix1 * p.dof_test;
   for (uint64_t s0 = s_begin; s0 < s_end; s0 += chunk) {
@@ -496,9 +632,19 @@ static int render_accum(GiContext *ctx, const GiParams &params, int sw, int sh, 
     for (uint64_t item0 = 0; item0 < total_items;) {
       const uint32_t m = (uint32_t)std::min<uint64_t>(batch, total_items - item0);
       if (!R.reset_queues()) return 1;
-      path_kernel<<<(m + 127) / 128, 128, 0, R.st>>>(env, s0, n, hits.as<PrimHit>(), offs.as<uint64_t>(), item0, m,
-                                                    item_rgb.as<double>(), item_pix.as<uint32_t>(), R.qg.view, R.qc.view,
-                                                    d_stats + 1);
+      GI_CUDA(cudaMemsetAsync(item_hit.p, 0, 4 * (size_t)m, R.st));
+      mark_items_kernel<<<(unsigned)((n + 255) / 256), 256, 0, R.st>>>(offs.as<uint64_t>(), n_items.as<uint32_t>(), n, item0, m,
+                                                                      item_hit.as<uint32_t>());
+      GI_CUDA(cub::DeviceScan::InclusiveScan(hit_scan_tmp.p, hit_scan_bytes, item_hit.as<uint32_t>(), item_hit.as<uint32_t>(), cub::Max(),
+                                             (int)m, R.st));
+      {
+        auto launch = [&](auto kernel) {
+          kernel<<<(m + 127) / 128, 128, 0, R.st>>>(env, s0, hits.as<PrimHit>(), offs.as<uint64_t>(), item_hit.as<uint32_t>(), item0, m,
+                                                    item_rgb.as<double>(), item_pix.as<uint32_t>(), R.qg.view, R.qc.view, d_stats + 1);
+        };
+        if (path_occ <= 4) launch(path_kernel<4>); else launch(path_kernel<6>);
+      }
+      ctx->launches += 2;
       GI_CUDA(cudaGetLastError());
       ctx->launches++;
       RayStats bs;
@@ -545,9 +691,9 @@ static int render_common(GiContext *ctx, const GiParams *params, int width, int 
   const uint64_t sw = (uint64_t)width * aaf, sh = (uint64_t)height * aaf, npix = sw * sh;
   if (npix >= (1ull << 32)) { set_error("gi_render: supersampled frame too large"); return 1; }
   GI_CUDA(cudaSetDevice(ctx->device));
-  double *accum = nullptr; RayStats *d_stats = nullptr;
-  GI_CUDA(cudaMalloc(&accum, sizeof(double) * 3 * npix));
-  if (!cuda_ok(cudaMalloc(&d_stats, 2 * sizeof(RayStats)), "cudaMalloc(stats)")) { cudaFree(accum); return 1; }
+  Workspace *ws = workspace(ctx);
+  if (!ws || !ws->fit_accum(3 * npix)) return 1;
+  double *accum = ws->accum.as<double>(); RayStats *d_stats = ws->stats.as<RayStats>();
   cudaEvent_t e0, e1; cudaEventCreate(&e0); cudaEventCreate(&e1);
   int rc = 1;
   RayStats hs[2]; RayStats paths; memset(&paths, 0, sizeof(paths));
@@ -574,8 +720,7 @@ static int render_common(GiContext *ctx, const GiParams *params, int width, int 
     stats->render_ms = ms;
   }
   cudaEventDestroy(e0); cudaEventDestroy(e1);
-  cudaFree(d_stats);
-  if (rc) { cudaFree(accum); return 1; }
+  if (rc) return 1;
   *accum_out = accum; *sw_out = (int)sw; *sh_out = (int)sh;
   return 0;
 }
@@ -587,9 +732,7 @@ int gi_render_float(GiContext *ctx, const GiParams *params, int width, int heigh
   if (!rgb_out) { set_error("gi_render_float: null output buffer"); return 1; }
   double *accum = nullptr; int sw = 0, sh = 0;
   if (render_common(ctx, params, width, height, aa, &accum, &sw, &sh, stats)) return 1;
-  const bool ok = cuda_ok(cudaMemcpy(rgb_out, accum, sizeof(double) * 3 * (size_t)sw * sh, cudaMemcpyDeviceToHost), "D2H frame");
-  cudaFree(accum);
-  return ok ? 0 : 1;
+  return cuda_ok(cudaMemcpy(rgb_out, accum, sizeof(double) * 3 * (size_t)sw * sh, cudaMemcpyDeviceToHost), "D2H frame") ? 0 : 1;
 }
 
 int gi_render(GiContext *ctx, const GiParams *params, int width, int height, int aa, uint8_t *rgb_out,
@@ -609,7 +752,7 @@ int gi_render(GiContext *ctx, const GiParams *params, int width, int height, int
     if (!cuda_ok(cudaStreamSynchronize(ctx->stream), "render sync")) break;
     rc = 0;
   } while (0);
-  cudaFree(d_rgb); cudaFree(accum);
+  cudaFree(d_rgb);
   return rc;
 }
 
