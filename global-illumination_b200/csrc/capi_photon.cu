@@ -192,22 +192,29 @@ int gi_gather_batch(GiContext *ctx, int map, const GiGatherQuery *queries, uint6
   if (!queries) { set_error("gi_gather_batch: null query buffer"); return 1; }
   if (k < 1 || k > GI_MAX_K) { set_error("gi_gather_batch: estimate size must be in [1, 512]"); return 1; }
   GI_CUDA(cudaSetDevice(ctx->device));
-  GiGatherQuery *d_q = nullptr; int32_t *d_idx = nullptr, *d_cnt = nullptr; double *d_rgb = nullptr;
-  int rc = 1;
-  do {
-    if (!cuda_ok(cudaMalloc(&d_q, sizeof(GiGatherQuery) * n), "cudaMalloc(queries)")) break;
-    if (idx_out && !cuda_ok(cudaMalloc(&d_idx, sizeof(int32_t) * n * k), "cudaMalloc(idx)")) break;
-    if (count_out && !cuda_ok(cudaMalloc(&d_cnt, sizeof(int32_t) * n), "cudaMalloc(count)")) break;
-    if (rgb_out && !cuda_ok(cudaMalloc(&d_rgb, sizeof(double) * 3 * n), "cudaMalloc(rgb)")) break;
-    if (!cuda_ok(cudaMemcpyAsync(d_q, queries, sizeof(GiGatherQuery) * n, cudaMemcpyHostToDevice, ctx->stream), "H2D queries")) break;
-    if (gi_gather_batch_device(ctx, map, d_q, n, k, r, filter, params, d_idx, d_cnt, d_rgb, ctx->stream)) break;
-    if (idx_out && !cuda_ok(cudaMemcpyAsync(idx_out, d_idx, sizeof(int32_t) * n * k, cudaMemcpyDeviceToHost, ctx->stream), "D2H idx")) break;
-    if (count_out && !cuda_ok(cudaMemcpyAsync(count_out, d_cnt, sizeof(int32_t) * n, cudaMemcpyDeviceToHost, ctx->stream), "D2H count")) break;
-    if (rgb_out && !cuda_ok(cudaMemcpyAsync(rgb_out, d_rgb, sizeof(double) * 3 * n, cudaMemcpyDeviceToHost, ctx->stream), "D2H rgb")) break;
-    if (!cuda_ok(cudaStreamSynchronize(ctx->stream), "gather sync")) break;
-    rc = 0;
-  } while (0);
-  cudaFree(d_q); cudaFree(d_idx); cudaFree(d_cnt); cudaFree(d_rgb);
+  // two-slot pipeline like gi_intersect_batch: chunks of 2^20 queries (143 MB in, 29 MB out)
+  const uint64_t chunk = 1ull << 20;
+  int rc = 0;
+  for (uint64_t o = 0, c = 0; o < n && rc == 0; o += chunk, c++) {
+    const uint64_t m = n - o < chunk ? n - o : chunk;
+    const int slot = (int)(c & 1);
+    cudaStream_t st = ctx->pipe[slot];
+    GiScratch *sc = ctx->stage[slot];
+    if (!sc[0].fit(sizeof(GiGatherQuery) * chunk) || (rgb_out && !sc[1].fit(sizeof(double) * 3 * chunk)) ||
+        (count_out && !sc[2].fit(sizeof(int32_t) * chunk)) || (idx_out && !sc[3].fit(sizeof(int32_t) * chunk * k))) {
+      set_error("gi_gather_batch: out of device memory"); rc = 1; break;
+    }
+    GiGatherQuery *d_q = (GiGatherQuery *)sc[0].p;
+    double *d_rgb = rgb_out ? (double *)sc[1].p : nullptr;
+    int32_t *d_cnt = count_out ? (int32_t *)sc[2].p : nullptr, *d_idx = idx_out ? (int32_t *)sc[3].p : nullptr;
+    if (!cuda_ok(cudaMemcpyAsync(d_q, queries + o, sizeof(GiGatherQuery) * m, cudaMemcpyHostToDevice, st), "H2D queries") ||
+        gi_gather_batch_device(ctx, map, d_q, m, k, r, filter, params, d_idx, d_cnt, d_rgb, st) != 0 ||
+        (idx_out && !cuda_ok(cudaMemcpyAsync(idx_out + o * k, d_idx, sizeof(int32_t) * m * k, cudaMemcpyDeviceToHost, st), "D2H idx")) ||
+        (count_out && !cuda_ok(cudaMemcpyAsync(count_out + o, d_cnt, sizeof(int32_t) * m, cudaMemcpyDeviceToHost, st), "D2H count")) ||
+        (rgb_out && !cuda_ok(cudaMemcpyAsync(rgb_out + 3 * o, d_rgb, sizeof(double) * 3 * m, cudaMemcpyDeviceToHost, st), "D2H rgb")))
+      rc = 1;
+  }
+  if (!cuda_ok(cudaStreamSynchronize(ctx->pipe[0]), "gather sync") || !cuda_ok(cudaStreamSynchronize(ctx->pipe[1]), "gather sync")) rc = 1;
   return rc;
 }
 

@@ -85,7 +85,9 @@ int gi_create(int device, GiContext **out) {
   if (prop.major < 10) { set_error("gi_create: this library is built for sm_100a (B200) only"); return 1; }
   GiContext *ctx = new GiContext();
   ctx->device = device; ctx->sm_count = prop.multiProcessorCount;
-  if (!cuda_ok(cudaStreamCreateWithFlags(&ctx->stream, cudaStreamNonBlocking), "cudaStreamCreate")) { delete ctx; return 1; }
+  if (!cuda_ok(cudaStreamCreateWithFlags(&ctx->stream, cudaStreamNonBlocking), "cudaStreamCreate") ||
+      !cuda_ok(cudaStreamCreateWithFlags(&ctx->pipe[0], cudaStreamNonBlocking), "cudaStreamCreate") ||
+      !cuda_ok(cudaStreamCreateWithFlags(&ctx->pipe[1], cudaStreamNonBlocking), "cudaStreamCreate")) { delete ctx; return 1; }
   *out = ctx;
   return 0;
 }
@@ -96,6 +98,10 @@ void gi_destroy(GiContext *ctx) {
   free_scene(ctx);
   free_map(ctx->maps[0]); free_map(ctx->maps[1]);
   if (ctx->render_ws && ctx->render_ws_free) ctx->render_ws_free(ctx->render_ws);
+  for (int i = 0; i < 2; i++) {
+    for (int j = 0; j < 4; j++) ctx->stage[i][j].release();
+    if (ctx->pipe[i]) cudaStreamDestroy(ctx->pipe[i]);
+  }
   if (ctx->stream) cudaStreamDestroy(ctx->stream);
   delete ctx;
 }
@@ -185,16 +191,24 @@ int gi_intersect_batch(GiContext *ctx, const GiRay *rays, uint64_t n, GiHit *hit
   if (n == 0) return 0;
   if (!rays || !hits_out) { set_error("gi_intersect_batch: null buffer"); return 1; }
   GI_CUDA(cudaSetDevice(ctx->device));
-  GiRay *d_rays = nullptr; GiHit *d_hits = nullptr;
-  GI_CUDA(cudaMalloc(&d_rays, sizeof(GiRay) * n));
-  if (!cuda_ok(cudaMalloc(&d_hits, sizeof(GiHit) * n), "cudaMalloc(hits)")) { cudaFree(d_rays); return 1; }
-  int rc = 1;
-  if (cuda_ok(cudaMemcpyAsync(d_rays, rays, sizeof(GiRay) * n, cudaMemcpyHostToDevice, ctx->stream), "H2D rays") &&
-      gi_intersect_batch_device(ctx, d_rays, n, d_hits, ctx->stream) == 0 &&
-      cuda_ok(cudaMemcpyAsync(hits_out, d_hits, sizeof(GiHit) * n, cudaMemcpyDeviceToHost, ctx->stream), "D2H hits") &&
-      cuda_ok(cudaStreamSynchronize(ctx->stream), "intersect sync"))
-    rc = 0;
-  cudaFree(d_rays); cudaFree(d_hits);
+  // chunks of 2^21 rays alternate between the two pipeline slots: copy-in, kernel and copy-out of a chunk are ordered
+  // on its slot's stream, the other slot's copies overlap them (pinned host buffers make the copies asynchronous)
+  const uint64_t chunk = 1ull << 21;
+  int rc = 0;
+  for (uint64_t o = 0, c = 0; o < n && rc == 0; o += chunk, c++) {
+    const uint64_t m = n - o < chunk ? n - o : chunk;
+    const int slot = (int)(c & 1);
+    cudaStream_t st = ctx->pipe[slot];
+    if (!ctx->stage[slot][0].fit(sizeof(GiRay) * chunk) || !ctx->stage[slot][1].fit(sizeof(GiHit) * chunk)) {
+      set_error("gi_intersect_batch: out of device memory"); rc = 1; break;
+    }
+    GiRay *d_rays = (GiRay *)ctx->stage[slot][0].p; GiHit *d_hits = (GiHit *)ctx->stage[slot][1].p;
+    if (!cuda_ok(cudaMemcpyAsync(d_rays, rays + o, sizeof(GiRay) * m, cudaMemcpyHostToDevice, st), "H2D rays") ||
+        gi_intersect_batch_device(ctx, d_rays, m, d_hits, st) != 0 ||
+        !cuda_ok(cudaMemcpyAsync(hits_out + o, d_hits, sizeof(GiHit) * m, cudaMemcpyDeviceToHost, st), "D2H hits"))
+      rc = 1;
+  }
+  if (!cuda_ok(cudaStreamSynchronize(ctx->pipe[0]), "intersect sync") || !cuda_ok(cudaStreamSynchronize(ctx->pipe[1]), "intersect sync")) rc = 1;
   return rc;
 }
 

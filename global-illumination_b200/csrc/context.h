@@ -9,6 +9,20 @@
 #include "scene_dev.h"
 #include "photon_dev.h"
 
+// grow-only device buffer used by the host-buffer entry points to stage chunks (freed by gi_destroy)
+struct GiScratch {
+  void *p = nullptr; size_t cap = 0;
+  bool fit(size_t bytes) {
+    if (bytes <= cap) return true;
+    if (p) cudaFree(p);
+    p = nullptr; cap = 0;
+    if (cudaMalloc(&p, bytes) != cudaSuccess) { p = nullptr; return false; }
+    cap = bytes;
+    return true;
+  }
+  void release() { if (p) cudaFree(p); p = nullptr; cap = 0; }
+};
+
 struct GiContext {
   int device = 0;
   cudaStream_t stream = nullptr;
@@ -25,6 +39,10 @@ struct GiContext {
   double *d_spec_boxes = nullptr;             // scene_allocs entry: boxes of the specular / transmissive shapes (photon_trace.cu)
   int n_spec_boxes = -1;
   gi::PhotonMapStore maps[2];                 // GI_MAP_GLOBAL, GI_MAP_CAUSTIC
+  // Host-buffer calls (gi_intersect_batch, gi_gather_batch) run as a two-slot pipeline: while one chunk computes on
+  // pipe[0] the next chunk's inputs are copied in and the previous chunk's results copied out on pipe[1].
+  cudaStream_t pipe[2] = {nullptr, nullptr};
+  GiScratch stage[2][4];                      // per slot: input, and up to three outputs
   void *render_ws = nullptr;                  // render.cu's device workspace, created by the first gi_render
   void (*render_ws_free)(void *) = nullptr;
   uint64_t launches = 0;                      // kernels launched by this context (bench.py: gpu_launches)
