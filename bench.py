@@ -461,25 +461,26 @@ def frame_report(args, torch, dist, ctx, dev, rank, world):
     import multi_gpu
     scene = gi_b200.HostScene(os.path.join(GOLDEN, args.frame_scene + ".gisc"))
     ctx.upload_scene(scene)
-    params, _ = gi_b200.parse_flags(["-seed", "1"])
     W = H = args.frame_res
-    torch.cuda.synchronize()
-    if world > 1:
-        dist.barrier()
-    t0 = time.perf_counter()
-    if world > 1:
-        totals = multi_gpu.trace_photons_sharded(ctx, params, dist, torch, dev)
-        stored = (totals["global_stored"], totals["caustic_stored"])
-    else:
-        st = ctx.trace_photons(params)
-        params.indirect_illum, params.caustic_illum, params.direct_photon_illum = st.indirect_illum, st.caustic_illum, st.direct_photon_illum
-        stored = (int(st.global_stored), int(st.caustic_stored))
-    torch.cuda.synchronize(); t1 = time.perf_counter()
-    if world > 1:
-        img, rs = multi_gpu.render_sharded(ctx, params, W, H, args.frame_aa, dist, torch, dev)
-    else:
-        img, rs = ctx.render(params, W, H, args.frame_aa)
-    torch.cuda.synchronize(); t2 = time.perf_counter()
+    for attempt in range(2):        # the first pass pays one-time costs (workspace allocation, NCCL channel set-up); report the second
+        params, _ = gi_b200.parse_flags(["-seed", "1"])
+        torch.cuda.synchronize()
+        if world > 1:
+            dist.barrier()
+        t0 = time.perf_counter()
+        if world > 1:
+            totals = multi_gpu.trace_photons_sharded(ctx, params, dist, torch, dev)
+            stored = (totals["global_stored"], totals["caustic_stored"])
+        else:
+            st = ctx.trace_photons(params)
+            params.indirect_illum, params.caustic_illum, params.direct_photon_illum = st.indirect_illum, st.caustic_illum, st.direct_photon_illum
+            stored = (int(st.global_stored), int(st.caustic_stored))
+        torch.cuda.synchronize(); t1 = time.perf_counter()
+        if world > 1:
+            img, rs = multi_gpu.render_sharded(ctx, params, W, H, args.frame_aa, dist, torch, dev)
+        else:
+            img, rs = ctx.render(params, W, H, args.frame_aa)
+        torch.cuda.synchronize(); t2 = time.perf_counter()
     names = ["screen_rays", "shadow_rays", "monte_rays", "transmissive_samples", "specular_samples", "indirect_samples", "caustic_samples"]
     c = torch.tensor([float(getattr(rs, n)) for n in names], dtype=torch.float64, device=dev)
     t = torch.tensor([(t1 - t0) * 1e3, (t2 - t1) * 1e3, rs.render_ms], dtype=torch.float64, device=dev)
@@ -494,7 +495,7 @@ def frame_report(args, torch, dist, ctx, dev, rank, world):
             "photons_stored": {"global": stored[0], "caustic": stored[1]}, "ray_ops": total, "counters": counters,
             "mray_ops_per_s": total / (render_ms * 1e-3) / 1e6,
             "gathers_per_s": (counters["indirect_samples"] + counters["caustic_samples"]) / (render_ms * 1e-3),
-            "image_mean": float(img.mean()) if img is not None else None, "timing": "wall clock, max over ranks; not part of the timed steps"}
+            "image_mean": float(img.mean()) if img is not None else None, "timing": "wall clock of the second of two passes, max over ranks; not part of the timed steps"}
 
 
 def cpu_baseline(args, torch, rays, photons, queries):

@@ -33,7 +33,8 @@ namespace gi {
 
 enum { STAGE_DOF = 1, STAGE_PATH = 2, STAGE_LIGHT = 16 };     // Philox stage ids (STAGE_LIGHT + 4*light + pass)
 
-struct PrimHit { double p[3], n[3]; int32_t material; uint32_t pix; };      // material < 0: the eye ray missed
+struct PrimHit { double p[3], n[3]; int32_t material; uint32_t pix; uint32_t k, pad; };   // material < 0: the eye ray missed
+                                                                                          // k: depth-of-field sample of the pixel
 
 struct Queue {                       // gather requests of one photon map, filled by direct_kernel / path_kernel
   GiGatherQuery *q;
@@ -47,6 +48,7 @@ struct Frame2 {                      // per-frame constants of the eye-ray gener
   D3 eye, far_org, far_right, far_up, u, v;
   double xc, yc, w, h;               // viewport centre and size in supersamples
   int sw, sh, dof;
+  int aaf, rank, world;              // this rank renders the pixel columns x = rank (mod world): local column l is x = l * world + rank
 };
 
 GI_DEV void add3(double *a, D3 c) { atomicAdd(a, c.x); atomicAdd(a + 1, c.y); atomicAdd(a + 2, c.z); }
@@ -85,9 +87,11 @@ __global__ void __launch_bounds__(128) primary_kernel(ShadeEnv env, Frame2 f, ui
                                                       RayStats *stats) {
   RayStats st = zero_stats();
   for (uint64_t t = (uint64_t)blockIdx.x * blockDim.x + threadIdx.x; t < n; t += (uint64_t)gridDim.x * blockDim.x) {
-    const uint64_t s = first + t;
-    const uint32_t pix = (uint32_t)(s / f.dof);
-    const int k = (int)(s % f.dof), i = (int)(pix / f.sh), j = (int)(pix % f.sh);
+    const uint64_t s = first + t;                       // local sample number: (local supersample column, row, dof sample)
+    const uint64_t lp = s / f.dof;
+    const int k = (int)(s % f.dof), li = (int)(lp / f.sh), j = (int)(lp % f.sh);
+    const int i = ((li / f.aaf) * f.world + f.rank) * f.aaf + (li % f.aaf);
+    const uint32_t pix = (uint32_t)i * (uint32_t)f.sh + (uint32_t)j;
     const double dx = (double)(2 * (i - f.xc)) / f.w, dy = (double)(2 * (j - f.yc)) / f.h;
     const D3 far_point = f.far_org + (f.far_right * dx) + (f.far_up * dy);
     D3 org = f.eye;
@@ -101,7 +105,7 @@ __global__ void __launch_bounds__(128) primary_kernel(ShadeEnv env, Frame2 f, ui
     HitRec h;
     closest_hit(env.sc, ray, h);
     PrimHit ph;
-    ph.pix = pix;
+    ph.pix = pix; ph.k = (uint32_t)k; ph.pad = 0;
     if (h.prim >= 0) {
       ph.p[0] = h.p.x; ph.p[1] = h.p.y; ph.p[2] = h.p.z; ph.n[0] = h.n.x; ph.n[1] = h.n.y; ph.n[2] = h.n.z;
       ph.material = env.sc.elements[h.element].material;
@@ -140,7 +144,7 @@ GI_DEV SubPaths sub_paths(const GiParams &p, const Brdf &b, double cos_theta) {
 
 // ------------------------------------------------------------------------------------------------ primary hits
 // The non-recursive part of RayTrace (raytracer.cpp:174-203, 224-231) for one primary hit per WARP.
-__global__ void __launch_bounds__(128) direct_kernel(ShadeEnv env, uint64_t first, uint64_t n,
+__global__ void __launch_bounds__(128) direct_kernel(ShadeEnv env, uint64_t n,
                                                      const PrimHit *__restrict__ hits, double *__restrict__ accum,
                                                      uint32_t *__restrict__ n_items, Queue qglobal, Queue qcaustic,
                                                      RayStats *stats) {
@@ -161,7 +165,7 @@ __global__ void __launch_bounds__(128) direct_kernel(ShadeEnv env, uint64_t firs
     if (env.p.ambient && b.ambient) color = color + b.ka;
     if (env.p.direct_illum && (b.diffuse || b.specular)) {
       Rng unused; unused.left = 0;
-      SampleKey key; key.seed = env.p.seed; key.index = first + t; key.stage = STAGE_LIGHT;
+      SampleKey key; key.seed = env.p.seed; key.index = (uint64_t)ph.pix * (uint64_t)env.p.dof_test + ph.k; key.stage = STAGE_LIGHT;
       direct_illumination(env, point, normal, cam, color, b, cos_theta, false, unused, &key, st);
     }
     if (lane == 0) {
@@ -267,7 +271,7 @@ GI_DEV bool path_step(const ShadeEnv &env, PathState &s, const Queue &qglobal, c
 // items are its transmissive samples, then its specular samples, then its indirect samples
 // (TransmissiveIllumination / SpecularIllumination / IndirectIllumination, raytracer.cpp:47-135).
 // Returns false if the path contributes nothing (MONTE_CARLO off).
-GI_DEV bool path_begin(const ShadeEnv &env, uint64_t first_sample, const PrimHit *__restrict__ hits,
+GI_DEV bool path_begin(const ShadeEnv &env, const PrimHit *__restrict__ hits,
                        const uint64_t *__restrict__ offs, uint64_t g, uint32_t hidx, PathState &s, RayStats &st) {
   const uint32_t local = (uint32_t)(g - offs[hidx]);
   const PrimHit ph = hits[hidx];
@@ -276,7 +280,7 @@ GI_DEV bool path_begin(const ShadeEnv &env, uint64_t first_sample, const PrimHit
   const D3 view = normalized(point - env.eye);
   const double cos_theta = dot(normal, -view);
   const SubPaths sp = sub_paths(env.p, b, cos_theta);
-  rng_init(s.rng, env.p.seed, first_sample + hidx, STAGE_PATH, local);
+  rng_init(s.rng, env.p.seed, (uint64_t)ph.pix * (uint64_t)env.p.dof_test + ph.k, STAGE_PATH, local);
   D3 total_weight, bounce; int count;
   if (local < (uint32_t)sp.n_t) {
     const D3 exact = transmissive_bounce(normal, view, cos_theta, b.ir, env.p.ir_air);
@@ -305,7 +309,7 @@ GI_DEV bool path_begin(const ShadeEnv &env, uint64_t first_sample, const PrimHit
 // MINB = resident CTAs per SM the kernel is compiled for: 6 -> 80 registers, 24 warps per SM; the kernel is
 // latency-bound (incoherent BVH walks), more warps beat fewer spills.
 template <int MINB>
-__global__ void __launch_bounds__(128, MINB) path_kernel(ShadeEnv env, uint64_t first_sample, const PrimHit *__restrict__ hits,
+__global__ void __launch_bounds__(128, MINB) path_kernel(ShadeEnv env, const PrimHit *__restrict__ hits,
                                                          const uint64_t *__restrict__ offs, const uint32_t *__restrict__ item_hit,
                                                          uint64_t item0, uint32_t n, double *__restrict__ item_rgb,
                                                          uint32_t *__restrict__ item_pix, Queue qglobal, Queue qcaustic, RayStats *stats) {
@@ -314,7 +318,7 @@ __global__ void __launch_bounds__(128, MINB) path_kernel(ShadeEnv env, uint64_t 
   if (t < n) {
     PathState s;
     s.item = t;
-    bool active = path_begin(env, first_sample, hits, offs, item0 + t, item_hit[t] - 1, s, st);
+    bool active = path_begin(env, hits, offs, item0 + t, item_hit[t] - 1, s, st);
     while (active) active = path_step(env, s, qglobal, qcaustic, st);
     item_rgb[3 * (size_t)t] = s.out.x; item_rgb[3 * (size_t)t + 1] = s.out.y; item_rgb[3 * (size_t)t + 2] = s.out.z;
     item_pix[t] = s.pix;
@@ -566,9 +570,11 @@ struct Renderer {
 
 }  // namespace
 
-// Renders supersamples [pix0, pix1) of the sw x sh supersampled frame into `accum` (3 doubles per supersample,
-// zero-initialised by the caller), already divided by DOF_TEST.
-static int render_accum(GiContext *ctx, const GiParams &params, int sw, int sh, uint64_t pix0, uint64_t pix1, double *accum,
+// Renders this rank's pixel columns (x = rank mod world; all 2^aa x 2^aa supersamples of a pixel stay on one rank) of
+// the sw x sh supersampled frame into `accum` (3 doubles per supersample, zero-initialised by the caller), already
+// divided by DOF_TEST.  Columns are interleaved like the reference's `i % THREADS == id` (render.cpp:90): neighbouring
+// columns cost about the same, so the ranks finish together.
+static int render_accum(GiContext *ctx, const GiParams &params, int sw, int sh, int aaf, int rank, int world, double *accum,
                         RayStats *d_stats, RayStats &host_paths) {
   Workspace *wsp = workspace(ctx);
   if (!wsp) return 1;
@@ -602,6 +608,9 @@ static int render_accum(GiContext *ctx, const GiParams &params, int sw, int sh, 
   f.far_up = ld3(cam.up) * tan(yfov) * p.focus_depth;
   f.u = normalized(ld3(cam.up)) * p.aperture_radius; f.v = normalized(ld3(cam.right)) * p.aperture_radius;
   f.xc = sw / 2; f.yc = sh / 2; f.w = sw; f.h = sh; f.sw = sw; f.sh = sh; f.dof = p.dof_test;
+  f.aaf = aaf; f.rank = rank; f.world = world;
+  const int width = sw / aaf;
+  const uint64_t local_cols = (uint64_t)((width - rank + world - 1) / world) * aaf;       // supersample columns of this rank
 
   const uint64_t chunk = Workspace::chunk;
   uint32_t batch = Workspace::batch_max;
@@ -612,13 +621,13 @@ static int render_accum(GiContext *ctx, const GiParams &params, int sw, int sh, 
   int path_occ = 6;                                       // resident CTAs per SM: 4 (128 registers) or 6 (80 registers)
   if (const char *e = getenv("GI_PATH_OCC")) path_occ = atoi(e);
 
-  const uint64_t s_begin = pix0 * p.dof_test, s_end = pix1 * p.dof_test;
+  const uint64_t s_begin = 0, s_end = local_cols * sh * p.dof_test;
   for (uint64_t s0 = s_begin; s0 < s_end; s0 += chunk) {
     const uint64_t n = std::min<uint64_t>(chunk, s_end - s0);
     if (!R.reset_queues()) return 1;
     primary_kernel<<<grid_for(n, 128, ctx->sm_count, 64), 128, 0, R.st>>>(env, f, s0, n, hits.as<PrimHit>(), accum, d_stats);
     GI_CUDA(cudaMemsetAsync(n_items.p, 0, 4 * (chunk + 1), R.st));
-    direct_kernel<<<grid_for(n * 32, 128, ctx->sm_count, 16), 128, 0, R.st>>>(env, s0, n, hits.as<PrimHit>(), accum,
+    direct_kernel<<<grid_for(n * 32, 128, ctx->sm_count, 16), 128, 0, R.st>>>(env, n, hits.as<PrimHit>(), accum,
                                                                              n_items.as<uint32_t>(), R.qg.view, R.qc.view, d_stats);
     GI_CUDA(cudaGetLastError());
     GI_CUDA(cub::DeviceScan::ExclusiveSum(scan_tmp.p, scan_bytes, n_items.as<uint32_t>(), offs.as<uint64_t>(), (int)(n + 1), R.st));
@@ -639,7 +648,7 @@ static int render_accum(GiContext *ctx, const GiParams &params, int sw, int sh, 
                                              (int)m, R.st));
       {
         auto launch = [&](auto kernel) {
-          kernel<<<(m + 127) / 128, 128, 0, R.st>>>(env, s0, hits.as<PrimHit>(), offs.as<uint64_t>(), item_hit.as<uint32_t>(), item0, m,
+          kernel<<<(m + 127) / 128, 128, 0, R.st>>>(env, hits.as<PrimHit>(), offs.as<uint64_t>(), item_hit.as<uint32_t>(), item0, m,
                                                     item_rgb.as<double>(), item_pix.as<uint32_t>(), R.qg.view, R.qc.view, d_stats + 1);
         };
         if (path_occ <= 4) launch(path_kernel<4>); else launch(path_kernel<6>);
@@ -663,9 +672,9 @@ static int render_accum(GiContext *ctx, const GiParams &params, int sw, int sh, 
       item0 += m;
     }
   }
-  if (p.dof_test > 1 && pix1 > pix0) {
-    const uint64_t cnt = 3 * (pix1 - pix0);
-    scale_kernel<<<(unsigned)((cnt + 255) / 256), 256, 0, R.st>>>(accum + 3 * pix0, cnt, (double)p.dof_test);
+  if (p.dof_test > 1) {                                   // (zeros of the other ranks' columns stay zero)
+    const uint64_t cnt = 3 * (uint64_t)sw * sh;
+    scale_kernel<<<(unsigned)((cnt + 255) / 256), 256, 0, R.st>>>(accum, cnt, (double)p.dof_test);
     ctx->launches++;
   }
   GI_CUDA(cudaStreamSynchronize(R.st));
@@ -701,12 +710,10 @@ static int render_common(GiContext *ctx, const GiParams *params, int width, int 
     if (!cuda_ok(cudaMemsetAsync(accum, 0, sizeof(double) * 3 * npix, ctx->stream), "memset(accum)")) break;
     if (!cuda_ok(cudaMemsetAsync(d_stats, 0, 2 * sizeof(RayStats), ctx->stream), "memset(stats)")) break;
     cudaEventRecord(e0, ctx->stream);
-    // tile sharding across GPUs: rank r of w renders a contiguous run of pixel columns, the rest stays zero
+    // sharding across GPUs: rank r of w renders the pixel columns x = r (mod w), the rest of the frame stays zero
     const int world = params->world_size > 1 ? params->world_size : 1, rank = params->world_size > 1 ? params->rank : 0;
     if (rank < 0 || rank >= world) { set_error("gi_render: rank outside [0, world_size)"); break; }
-    // (whole OUTPUT pixel columns, so that every box-filter sum of the resolve stays on one rank)
-    const uint64_t c0 = (uint64_t)width * rank / world * aaf, c1 = (uint64_t)width * (rank + 1) / world * aaf;
-    if (render_accum(ctx, *params, (int)sw, (int)sh, c0 * sh, c1 * sh, accum, d_stats, paths)) break;
+    if (render_accum(ctx, *params, (int)sw, (int)sh, aaf, rank, world, accum, d_stats, paths)) break;
     cudaEventRecord(e1, ctx->stream);
     if (!cuda_ok(cudaMemcpyAsync(hs, d_stats, 2 * sizeof(RayStats), cudaMemcpyDeviceToHost, ctx->stream), "D2H stats")) break;
     if (!cuda_ok(cudaStreamSynchronize(ctx->stream), "render sync")) break;

@@ -4,7 +4,7 @@
                 reference's per-thread split, photonmap.cpp:289-321); ONE all-gather per map replicates the photons
                 (ragged: ranks store different counts), the emitted counts are all-reduced, every rank applies the
                 power scale and builds its own kd-trees.  No collective touches the gather / render data path.
-  render        rank r renders a contiguous range of pixel columns (gi_render with rank / world_size) into a
+  render        rank r renders the pixel columns x = r (mod world) (gi_render with rank / world_size) into a
                 zero-initialised frame; the frames are summed onto rank 0.
 
 torch.distributed is the plumbing (NCCL on the GPUs; the same functions run under gloo on CPU tensors for the tests).
@@ -31,10 +31,11 @@ def gather_ragged(dist, torch, local):
     return torch.cat(parts, dim=0).contiguous(), counts
 
 
-def column_range(width, rank, world):
-    """output pixel columns [c0, c1) of rank `rank` -- the split gi_render applies (csrc/render.cu): whole pixel
-    columns, so every 2^aa x 2^aa box-filter sum stays on one rank and the ranks' frames are disjoint"""
-    return width * rank // world, width * (rank + 1) // world
+def columns_of(width, rank, world):
+    """output pixel columns of rank `rank` -- the split gi_render applies (csrc/render.cu): x = rank (mod world), the
+    reference's own interleaving of columns over threads (render.cpp:90).  Whole pixel columns, so every 2^aa x 2^aa
+    box-filter sum stays on one rank and the ranks' frames are disjoint."""
+    return range(rank, width, world)
 
 
 def trace_photons_sharded(ctx, params, dist, torch, device):
