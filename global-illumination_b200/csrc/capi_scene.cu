@@ -218,4 +218,10 @@ int gi_launch_count(GiContext *ctx, uint64_t *out) {
   return 0;
 }
 
+int gi_queue_overflow_count(GiContext *ctx, uint64_t *out) {
+  if (!ctx || !out) { set_error("gi_queue_overflow_count: null argument"); return 1; }
+  *out = ctx->queue_overflows;
+  return 0;
+}
+
 }  // extern "C"

@@ -45,6 +45,7 @@ struct GiContext {
   GiScratch stage[2][4];                      // per slot: input, and up to three outputs
   void *render_ws = nullptr;                  // render.cu's device workspace, created by the first gi_render
   void (*render_ws_free)(void *) = nullptr;
+  uint64_t queue_overflows = 0;               // render path batches repeated because a gather-request queue ran full
   uint64_t launches = 0;                      // kernels launched by this context (bench.py: gpu_launches)
 };
 

@@ -614,7 +614,12 @@ static int render_accum(GiContext *ctx, const GiParams &params, int sw, int sh, 
 
   const uint64_t chunk = Workspace::chunk;
   uint32_t batch = Workspace::batch_max;
-  const unsigned long long qcap = Workspace::qcap;
+  unsigned long long qcap = Workspace::qcap;
+  // test hooks: a smaller path batch / request capacity of the path stage, to exercise the overflow-and-repeat branch
+  if (const char *e = getenv("GI_BATCH_MAX")) batch = (uint32_t)std::min<long long>(std::max<long long>(atoll(e), 1024), Workspace::batch_max);
+  if (const char *e = getenv("GI_QCAP")) qcap = (unsigned long long)std::min<long long>(std::max<long long>(atoll(e), 1024), (long long)Workspace::qcap);
+  Queue path_qg = R.qg.view, path_qc = R.qc.view;
+  path_qg.cap = path_qc.cap = qcap;
   DevBuf &hits = ws.hits, &n_items = ws.n_items, &offs = ws.offs, &item_rgb = ws.item_rgb, &item_pix = ws.item_pix, &scan_tmp = ws.scan_tmp,
          &item_hit = ws.item_hit, &hit_scan_tmp = ws.hit_scan_tmp;
   size_t scan_bytes = ws.scan_bytes, hit_scan_bytes = ws.hit_scan_bytes;
@@ -649,7 +654,7 @@ static int render_accum(GiContext *ctx, const GiParams &params, int sw, int sh, 
       {
         auto launch = [&](auto kernel) {
           kernel<<<(m + 127) / 128, 128, 0, R.st>>>(env, hits.as<PrimHit>(), offs.as<uint64_t>(), item_hit.as<uint32_t>(), item0, m,
-                                                    item_rgb.as<double>(), item_pix.as<uint32_t>(), R.qg.view, R.qc.view, d_stats + 1);
+                                                    item_rgb.as<double>(), item_pix.as<uint32_t>(), path_qg, path_qc, d_stats + 1);
         };
         if (path_occ <= 4) launch(path_kernel<4>); else launch(path_kernel<6>);
       }
@@ -661,6 +666,7 @@ static int render_accum(GiContext *ctx, const GiParams &params, int sw, int sh, 
       if (ng > qcap || nc > qcap) {                       // a queue overflowed: nothing was committed, repeat with fewer paths
         if (batch <= 1024) { set_error("gi_render: gather queue overflow"); return 1; }
         batch >>= 1;
+        ctx->queue_overflows++;
         continue;
       }
       commit_items_kernel<<<(m + 255) / 256, 256, 0, R.st>>>(item_rgb.as<double>(), item_pix.as<uint32_t>(), m, accum);

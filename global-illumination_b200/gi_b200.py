@@ -81,6 +81,7 @@ class GiRenderStats(ctypes.Structure):
 
 # every symbol include/gi_b200.h declares (tests check the built library exports all of them)
 EXPORTS = ["gi_abi_version", "gi_last_error", "gi_create", "gi_destroy", "gi_default_params", "gi_launch_count",
+           "gi_queue_overflow_count",
            "gi_host_scene_load", "gi_host_scene_view", "gi_host_scene_save", "gi_host_scene_free",
            "gi_upload_scene", "gi_intersect_batch", "gi_intersect_batch_device",
            "gi_load_photons", "gi_load_photons_device", "gi_load_photons_file", "gi_dump_photons_file",
@@ -105,6 +106,7 @@ def lib():
         L.gi_destroy.argtypes = [vp]; L.gi_destroy.restype = None
         L.gi_default_params.argtypes = [ctypes.POINTER(GiParams)]; L.gi_default_params.restype = None
         L.gi_launch_count.argtypes = [vp, ctypes.POINTER(u64)]
+        L.gi_queue_overflow_count.argtypes = [vp, ctypes.POINTER(u64)]
         L.gi_host_scene_load.argtypes = [ctypes.c_char_p, i32, ctypes.POINTER(vp)]
         L.gi_host_scene_view.argtypes = [vp, ctypes.POINTER(GiScene)]
         L.gi_host_scene_save.argtypes = [vp, ctypes.c_char_p]
@@ -190,6 +192,11 @@ class Context:
     def launch_count(self):
         n = ctypes.c_uint64()
         _check(lib().gi_launch_count(self.handle, ctypes.byref(n)))
+        return n.value
+
+    def queue_overflow_count(self):
+        n = ctypes.c_uint64()
+        _check(lib().gi_queue_overflow_count(self.handle, ctypes.byref(n)))
         return n.value
 
     def upload_scene(self, scene):

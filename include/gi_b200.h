@@ -218,6 +218,9 @@ void gi_default_cli_options(GiCliOptions *o);
 int gi_parse_args(int argc, const char *const *argv, GiParams *params, GiCliOptions *options);
 
 int gi_launch_count(GiContext *ctx, uint64_t *out);                /* kernels launched so far by this context */
+/* gi_render path batches that were repeated with fewer paths because a gather-request queue ran full (diagnostic;
+ * the environment variables GI_QCAP / GI_BATCH_MAX shrink the queue / the batch to provoke it in tests) */
+int gi_queue_overflow_count(GiContext *ctx, uint64_t *out);
 
 /* host-side .scn/.off loader (no device needed): ReadScene (src/utils/io_utils.cpp:219-250) ->
  * R3Scene::ReadFile (R3Scene.cpp:514-587) -> ReadPrinceton (:1463-1953) / R3Mesh::ReadOffFile

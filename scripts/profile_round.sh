@@ -1,7 +1,17 @@
-# GPU-box script: official bench line, reference arm, ncu launch list + full capture of the two hot kernels
-mkdir -p gpurun_out
-python bench.py > gpurun_out/bench_full.json 2> gpurun_out/bench_full.err; echo bench $?; tail -c 600 gpurun_out/bench_full.json
-timeout 900 python bench.py --impl reference --steps 2 --warmup 1 > gpurun_out/bench_ref.json 2> gpurun_out/bench_ref.err; echo ref $?; tail -c 400 gpurun_out/bench_ref.json
-SMALL="--steps 2 --warmup 3 --no-cpu-baseline --width 512 --height 512 --aa 1"
-python bench.py $SMALL > gpurun_out/plain.log 2>&1 && ncu --metrics gpu__time_duration.sum --clock-control none -c 600 --csv --log-file gpurun_out/launches.csv python bench.py $SMALL > gpurun_out/ncu1.log 2>&1; echo ncu1 $?
-python bench.py $SMALL > gpurun_out/plain2.log 2>&1 && ncu --set full --clock-control none --import-source on -k regex:"gather_kernel|intersect_kernel" -s 8 -c 2 -o gpurun_out/prof_r1 python bench.py $SMALL > gpurun_out/ncu2.log 2>&1; echo ncu2 $?
+#!/bin/bash
+# Round profile capture (GPU box, 1 GPU).  Every ncu command runs only after the same command exited 0 without ncu.
+# Outputs under gpurun_out/ ; the summaries that are judged get copied to profiles/ by hand.
+set -x
+R=${1:-r01}
+O=gpurun_out
+mkdir -p $O
+python bench.py --steps 5 --warmup 3 > $O/${R}_bench_n1.json 2> $O/${R}_bench_n1.err || exit 1
+python bench.py --impl reference --steps 2 --warmup 1 > $O/${R}_bench_reference_arm.json 2> $O/${R}_bench_ref.err
+# launch list of the bench command (small step so that ncu's serialised replay stays short)
+python bench.py --steps 2 --warmup 1 --width 512 --height 512 --aa 1 --no-cpu-baseline --no-frame > $O/b_small.log 2>&1 && \
+ncu --metrics gpu__time_duration.sum --clock-control none -c 400 --csv --log-file $O/${R}_launches_bench_small.csv \
+    python bench.py --steps 2 --warmup 1 --width 512 --height 512 --aa 1 --no-cpu-baseline --no-frame > $O/ncu_b.log 2>&1
+# launch list of a whole-program frame
+REPS=1 python scripts/render_perf.py cornell 256 1 > $O/f_small.log 2>&1 && \
+REPS=1 ncu --metrics gpu__time_duration.sum --clock-control none -c 8000 --csv --log-file $O/${R}_launches_frame_cornell256aa1.csv \
+    python scripts/render_perf.py cornell 256 1 > $O/ncu_f.log 2>&1

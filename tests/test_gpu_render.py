@@ -136,3 +136,24 @@ def test_render_errors(gpu_ctx):
     params.irradiance_cache = 0
     with pytest.raises(gi_b200.GiError):
         gpu_ctx.render_float(params, 0, h, 0)
+
+
+def test_queue_overflow_repeats_the_batch_with_the_same_result(gpu_ctx, monkeypatch):
+    """A path batch whose gather requests do not fit the request queue is repeated with half the paths; random numbers
+    are keyed by (seed, supersample, stage, item), so the frame and the counters do not change."""
+    params, w, h = setup(gpu_ctx, "cornell_full")
+    params.seed = 77
+    ref, st0 = gpu_ctx.render_float(params, 96, 96, 0)
+    before = gpu_ctx.queue_overflow_count()
+    monkeypatch.setenv("GI_BATCH_MAX", "32768")
+    monkeypatch.setenv("GI_QCAP", "6000")
+    img, st1 = gpu_ctx.render_float(params, 96, 96, 0)
+    assert gpu_ctx.queue_overflow_count() > before, "the hook did not provoke an overflow"
+    assert np.allclose(img, ref, rtol=1e-9, atol=1e-12)
+    for f in ("screen_rays", "shadow_rays", "monte_rays", "transmissive_samples", "specular_samples", "indirect_samples",
+              "caustic_samples"):
+        assert getattr(st0, f) == getattr(st1, f), f
+    monkeypatch.setenv("GI_BATCH_MAX", "1024")
+    monkeypatch.setenv("GI_QCAP", "1024")
+    with pytest.raises(gi_b200.GiError, match="overflow"):       # 1024 paths push more than 1024 requests: loud failure
+        gpu_ctx.render_float(params, 96, 96, 0)
