@@ -14,6 +14,7 @@
 #include "context.h"
 #include "gather.h"
 #include "gi_math.cuh"
+#include "irradiance_cache.h"
 #include "kdtree_build.h"
 
 namespace gi {
@@ -142,7 +143,6 @@ int gi_dump_photons_file(GiContext *ctx, int map, const char *path) {
 }
 
 int gi_build_maps(GiContext *ctx, const GiParams *params) {
-  (void)params;
   if (!ctx) { set_error("gi_build_maps: null context"); return 1; }
   GI_CUDA(cudaSetDevice(ctx->device));
   for (int k = 0; k < 2; k++) {
@@ -150,7 +150,52 @@ int gi_build_maps(GiContext *ctx, const GiParams *params) {
     if (m.built || m.dev.n == 0) continue;
     GI_CUDA(build_photon_map(ctx, m, m.dev.n));
   }
+  // photonmap.cpp:380-411: with -cache the global photons' colours become irradiance estimates
+  if (params && params->irradiance_cache && (params->indirect_illum || params->direct_photon_illum) &&
+      ctx->maps[GI_MAP_GLOBAL].dev.n > 0 && build_irradiance_cache(ctx, *params))
+    return 1;
   return 0;
+}
+
+int gi_cached_radiance_batch_device(GiContext *ctx, const GiGatherQuery *d_queries, uint64_t n, double r, double *d_rgb, void *stream) {
+  if (!ctx) { set_error("gi_cached_radiance_batch: null context"); return 1; }
+  PhotonMapStore &m = ctx->maps[GI_MAP_GLOBAL];
+  if (m.dev.n > 0 && !m.built) { set_error("gi_cached_radiance_batch: photon map not built (call gi_build_maps)"); return 1; }
+  if (m.dev.n > 0 && !m.cached) {
+    set_error("gi_cached_radiance_batch: the global map holds no irradiance cache (call gi_build_maps with irradiance_cache set)");
+    return 1;
+  }
+  if (n == 0) return 0;
+  if (!d_queries || !d_rgb) { set_error("gi_cached_radiance_batch: null buffer"); return 1; }
+  GI_CUDA(cudaSetDevice(ctx->device));
+  const double *lut = direction_lut(ctx);
+  if (!lut) return 1;
+  GI_CUDA(launch_cached_radiance(ctx, m.dev, lut, d_queries, n, r, d_rgb, (cudaStream_t)stream));
+  return 0;
+}
+
+int gi_cached_radiance_batch(GiContext *ctx, const GiGatherQuery *queries, uint64_t n, double r, double *rgb_out) {
+  if (!ctx) { set_error("gi_cached_radiance_batch: null context"); return 1; }
+  if (n == 0) return 0;
+  if (!queries || !rgb_out) { set_error("gi_cached_radiance_batch: null buffer"); return 1; }
+  GI_CUDA(cudaSetDevice(ctx->device));
+  const uint64_t chunk = 1ull << 20;
+  int rc = 0;
+  for (uint64_t o = 0, c = 0; o < n && rc == 0; o += chunk, c++) {
+    const uint64_t m = n - o < chunk ? n - o : chunk;
+    const int slot = (int)(c & 1);
+    cudaStream_t st = ctx->pipe[slot];
+    GiScratch *sc = ctx->stage[slot];
+    if (!sc[0].fit(sizeof(GiGatherQuery) * chunk) || !sc[1].fit(sizeof(double) * 3 * chunk)) {
+      set_error("gi_cached_radiance_batch: out of device memory"); rc = 1; break;
+    }
+    if (!cuda_ok(cudaMemcpyAsync(sc[0].p, queries + o, sizeof(GiGatherQuery) * m, cudaMemcpyHostToDevice, st), "H2D queries") ||
+        gi_cached_radiance_batch_device(ctx, (const GiGatherQuery *)sc[0].p, m, r, (double *)sc[1].p, st) != 0 ||
+        !cuda_ok(cudaMemcpyAsync(rgb_out + 3 * o, sc[1].p, sizeof(double) * 3 * m, cudaMemcpyDeviceToHost, st), "D2H rgb"))
+      rc = 1;
+  }
+  if (!cuda_ok(cudaStreamSynchronize(ctx->pipe[0]), "cache sync") || !cuda_ok(cudaStreamSynchronize(ctx->pipe[1]), "cache sync")) rc = 1;
+  return rc;
 }
 
 int gi_gather_batch_device(GiContext *ctx, int map, const GiGatherQuery *d_queries, uint64_t n, int k, double r,

@@ -35,6 +35,8 @@ struct PhotonMapStore {
   PhotonMapDev dev{};             /* device pointers (owned) */
   void *raw = nullptr;            /* GiPhoton[n] in load order (device), kept for dump / get */
   bool built = false;
+  bool cached = false;             /* colours hold cached irradiance (-cache pre-pass, irradiance_cache.cu) */
+  double cache_ms = 0;             /* wall time of that pre-pass */
   double bbox[6] = {0, 0, 0, 0, 0, 0};
 };
 

@@ -26,24 +26,6 @@ enum { MAP_GLOBAL = 0, MAP_CAUSTIC = 1 };
 
 struct PhotonSink { GiPhoton *photons; uint64_t *keys; unsigned long long *count; unsigned long long cap; };
 
-// RNRgb_to_RGBE, graphics_utils.cpp:50-62
-GI_DEV void rgbe_encode(D3 c, uint8_t *out) {
-  const double mx = max_channel(c);
-  if (!(mx > 0)) { out[0] = out[1] = out[2] = 0; int e; frexp(0.0, &e); out[3] = (uint8_t)(e + 128); return; }
-  int exponent;
-  const double mantissa = frexp(mx, &exponent);
-  out[0] = (uint8_t)(int)(256.0 * c.x / mx * mantissa);
-  out[1] = (uint8_t)(int)(256.0 * c.y / mx * mantissa);
-  out[2] = (uint8_t)(int)(256.0 * c.z / mx * mantissa);
-  out[3] = (uint8_t)(exponent + 128);
-}
-// RGBE_to_RNRgb, graphics_utils.cpp:65-79
-GI_DEV D3 rgbe_decode(const uint8_t *in) {
-  if (!in[3]) return mk3(0, 0, 0);
-  const double inverse = ldexp(1.0, ((int)in[3]) - 128 - 8);
-  return mk3(in[0], in[1], in[2]) * inverse;
-}
-
 // StorePhoton, photon_utils.cpp:40-66
 GI_DEV void store_photon(const PhotonSink &sink, D3 power, D3 incident, D3 point, uint64_t key) {
   const unsigned long long i = atomicAdd(sink.count, 1ull);
@@ -477,6 +459,8 @@ int gi_trace_photons(GiContext *ctx, const GiParams *params, GiPhotonStats *stat
     if (!cuda_ok(cudaStreamSynchronize(ctx->stream), "trace sync")) break;
     float a = 0, b = 0; cudaEventElapsedTime(&a, e0, e1); cudaEventElapsedTime(&b, e1, e2);
     s.trace_ms = a; s.build_ms = b;
+    s.cache_ms = ctx->maps[0].cached ? ctx->maps[0].cache_ms : 0.0;
+    s.build_ms -= s.cache_ms < s.build_ms ? s.cache_ms : 0.0;          // the reference times the two separately (:378,:410)
     rc = 0;
   } while (0);
   cudaEventDestroy(e0); cudaEventDestroy(e1); cudaEventDestroy(e2);

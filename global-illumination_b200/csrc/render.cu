@@ -178,7 +178,7 @@ __global__ void __launch_bounds__(128) direct_kernel(ShadeEnv env, uint64_t n,
       }
       if (env.p.direct_photon_illum && b.diffuse) {                              // EstimateGlobalIllumination, :151-167
         push_request(qglobal, point, normal, reflective_bounce(normal, view, cos_theta), cos_theta, b, one, ph.pix);
-        st.indirect++;
+        if (!env.p.irradiance_cache) st.indirect++;                              // raytracer.cpp:159-166
       }
       add3(accum + 3 * (size_t)ph.pix, color);
     }
@@ -241,7 +241,7 @@ GI_DEV bool path_step(const ShadeEnv &env, PathState &s, const Queue &qglobal, c
     const D3 w = mul3(b.kd, s.tw) / prob_diffuse;
     if (s.mode == MODE_INDIRECT || (!p.indirect_illum && p.fast_global)) {
       push_request(qglobal, point, normal, reflective_bounce(normal, view, cos_theta), cos_theta, b, mul3(s.scale, w), s.pix);
-      if (s.mode == MODE_PATH) st.indirect++;                 // EstimateGlobalIllumination counts, EstimateRadiance does not
+      if (s.mode == MODE_PATH && !p.irradiance_cache) st.indirect++;   // EstimateGlobalIllumination counts (not with -cache), EstimateRadiance does not
       return false;
     }
     if (!p.indirect_illum) return false;
@@ -544,8 +544,14 @@ struct Renderer {
     const double r = map == GI_MAP_GLOBAL ? p.global_estimate_dist : p.caustic_estimate_dist;
     const int filter = map == GI_MAP_GLOBAL ? p.global_filter : p.caustic_filter;
     if (ctx->maps[map].dev.n == 0) return true;          // empty map: EstimateRadiance adds nothing
+    // -cache: requests to the global map are EstimateCachedRadiance lookups (raytracer.cpp:159-162, montecarlo.cpp:251-254)
+    const bool cached = map == GI_MAP_GLOBAL && p.irradiance_cache;
+    auto estimate = [&](const GiGatherQuery *q) {
+      return cached ? gi_cached_radiance_batch_device(ctx, q, n, r, qs.rgb.as<double>(), st)
+                    : gi_gather_batch_device(ctx, map, q, n, k, r, filter, &p, nullptr, nullptr, qs.rgb.as<double>(), st);
+    };
     if (n < 4096 || !sort_requests) {
-      if (gi_gather_batch_device(ctx, map, qs.view.q, n, k, r, filter, &p, nullptr, nullptr, qs.rgb.as<double>(), st)) return false;
+      if (estimate(qs.view.q)) return false;
       commit_requests_kernel<<<(unsigned)((n + 255) / 256), 256, 0, st>>>(qs.view.w, qs.view.pix, qs.rgb.as<double>(), n, accum);
       ctx->launches++;
       return cuda_ok(cudaGetLastError(), "commit_requests_kernel");
@@ -560,8 +566,7 @@ struct Renderer {
       return false;
     permute_requests_kernel<<<(unsigned)((n * 17 + 255) / 256), 256, 0, st>>>((const double *)qs.view.q, qs.order2.as<uint32_t>(), n,
                                                                              qs.sorted_q.as<double>());
-    if (gi_gather_batch_device(ctx, map, qs.sorted_q.as<GiGatherQuery>(), n, k, r, filter, &p, nullptr, nullptr, qs.rgb.as<double>(), st))
-      return false;
+    if (estimate(qs.sorted_q.as<GiGatherQuery>())) return false;
     commit_sorted_kernel<<<blocks, 256, 0, st>>>(qs.view.w, qs.view.pix, qs.order2.as<uint32_t>(), qs.rgb.as<double>(), n, accum);
     ctx->launches += 7;
     return cuda_ok(cudaGetLastError(), "sorted gather");
@@ -697,7 +702,15 @@ static int render_common(GiContext *ctx, const GiParams *params, int width, int 
   if (!ctx || !params) { set_error("gi_render: null argument"); return 1; }
   if (!ctx->has_scene) { set_error("gi_render: no scene uploaded"); return 1; }
   if (width < 1 || height < 1 || aa < 0 || aa > 6) { set_error("gi_render: bad image size or anti-aliasing level"); return 1; }
-  if (params->irradiance_cache) { set_error("gi_render: the irradiance cache (-irradiance_cache) is not implemented"); return 1; }
+  {
+    const PhotonMapStore &gm = ctx->maps[GI_MAP_GLOBAL];
+    const bool uses_global = gm.dev.n > 0 && (params->indirect_illum || params->direct_photon_illum || params->fast_global);
+    if (uses_global && (params->irradiance_cache != 0) != gm.cached) {
+      set_error(gm.cached ? "gi_render: the global map holds cached irradiance (built with -cache) but irradiance_cache is off"
+                          : "gi_render: irradiance_cache is set but the global map was built without it (call gi_build_maps with the same params)");
+      return 1;
+    }
+  }
   if (params->global_estimate_size < 1 || params->global_estimate_size > GI_MAX_K || params->caustic_estimate_size < 1 ||
       params->caustic_estimate_size > GI_MAX_K) { set_error("gi_render: estimate size must be in [1, 512]"); return 1; }
   for (int m = 0; m < 2; m++)

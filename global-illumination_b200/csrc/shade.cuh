@@ -23,6 +23,25 @@ GI_DEV double max_channel(D3 c) {                       // MaxChannelVal, graphi
   if (c.z > m) m = c.z;
   return m;
 }
+
+// RNRgb_to_RGBE, graphics_utils.cpp:50-62
+GI_DEV void rgbe_encode(D3 c, uint8_t *out) {
+  const double mx = max_channel(c);
+  if (!(mx > 0)) { out[0] = out[1] = out[2] = 0; int e; frexp(0.0, &e); out[3] = (uint8_t)(e + 128); return; }
+  int exponent;
+  const double mantissa = frexp(mx, &exponent);
+  out[0] = (uint8_t)(int)(256.0 * c.x / mx * mantissa);
+  out[1] = (uint8_t)(int)(256.0 * c.y / mx * mantissa);
+  out[2] = (uint8_t)(int)(256.0 * c.z / mx * mantissa);
+  out[3] = (uint8_t)(exponent + 128);
+}
+// RGBE_to_RNRgb, graphics_utils.cpp:65-79
+GI_DEV D3 rgbe_decode(const uint8_t *in) {
+  if (!in[3]) return mk3(0, 0, 0);
+  const double inverse = ldexp(1.0, ((int)in[3]) - 128 - 8);
+  return mk3(in[0], in[1], in[2]) * inverse;
+}
+
 GI_DEV bool is_black(const double *c) { return c[0] == 0.0 && c[1] == 0.0 && c[2] == 0.0; }   // RNRgb::IsBlack
 
 struct Brdf {                                           // R3Brdf values + the flags RayTrace tests

@@ -69,7 +69,7 @@ class GiPhotonStats(ctypes.Structure):
                 ("indirect_illum", ctypes.c_int32), ("caustic_illum", ctypes.c_int32),
                 ("direct_photon_illum", ctypes.c_int32), ("rounds", ctypes.c_int32),
                 ("trace_ms", ctypes.c_double), ("build_ms", ctypes.c_double),
-                ("total_power", ctypes.c_double)]
+                ("total_power", ctypes.c_double), ("cache_ms", ctypes.c_double)]
 
 
 class GiRenderStats(ctypes.Structure):
@@ -81,7 +81,7 @@ class GiRenderStats(ctypes.Structure):
 
 # every symbol include/gi_b200.h declares (tests check the built library exports all of them)
 EXPORTS = ["gi_abi_version", "gi_last_error", "gi_create", "gi_destroy", "gi_default_params", "gi_launch_count",
-           "gi_queue_overflow_count",
+           "gi_queue_overflow_count", "gi_cached_radiance_batch", "gi_cached_radiance_batch_device",
            "gi_host_scene_load", "gi_host_scene_view", "gi_host_scene_save", "gi_host_scene_free",
            "gi_upload_scene", "gi_intersect_batch", "gi_intersect_batch_device",
            "gi_load_photons", "gi_load_photons_device", "gi_load_photons_file", "gi_dump_photons_file",
@@ -124,6 +124,8 @@ def lib():
         L.gi_build_maps.argtypes = [vp, ctypes.POINTER(GiParams)]
         L.gi_gather_batch.argtypes = [vp, i32, vp, u64, i32, dbl, i32, ctypes.POINTER(GiParams), vp, vp, vp]
         L.gi_gather_batch_device.argtypes = [vp, i32, vp, u64, i32, dbl, i32, ctypes.POINTER(GiParams), vp, vp, vp, vp]
+        L.gi_cached_radiance_batch.argtypes = [vp, vp, u64, dbl, vp]
+        L.gi_cached_radiance_batch_device.argtypes = [vp, vp, u64, dbl, vp, vp]
         L.gi_trace_photons.argtypes = [vp, ctypes.POINTER(GiParams), ctypes.POINTER(GiPhotonStats)]
         L.gi_scale_photon_power.argtypes = [vp, i32, dbl]
         L.gi_render.argtypes = [vp, ctypes.POINTER(GiParams), i32, i32, i32, vp, ctypes.POINTER(GiRenderStats)]
@@ -255,6 +257,16 @@ class Context:
     def gather_device(self, which, d_queries, n, k, r, filter, params, d_idx, d_count, d_rgb, stream=None):
         _check(lib().gi_gather_batch_device(self.handle, which, d_queries, n, k, float(r), filter, ctypes.byref(params),
                                             d_idx, d_count, d_rgb, stream))
+
+    def cached_radiance(self, queries, r):
+        """EstimateCachedRadiance per query on the global map (built with params.irradiance_cache): rgb[n, 3]."""
+        queries = np.ascontiguousarray(queries, dtype=QUERY)
+        rgb = np.zeros((len(queries), 3), dtype=np.float64)
+        _check(lib().gi_cached_radiance_batch(self.handle, queries.ctypes.data, len(queries), float(r), rgb.ctypes.data))
+        return rgb
+
+    def cached_radiance_device(self, d_queries, n, r, d_rgb, stream=None):
+        _check(lib().gi_cached_radiance_batch_device(self.handle, d_queries, n, float(r), d_rgb, stream))
 
     def trace_photons(self, params):
         """MapPhotons(): returns GiPhotonStats; the maps stay on the device, built."""

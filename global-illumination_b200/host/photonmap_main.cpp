@@ -63,7 +63,9 @@ int main(int argc, char **argv) {
     if (load[0] || load[1]) {
       for (int m = 0; m < 2; m++)
         if (load[m] && gi_load_photons_file(ctx, m, load[m])) return fail("Unable to load photon map");
+      const auto tb = std::chrono::steady_clock::now();
       if (gi_build_maps(ctx, &params)) return fail("Unable to build photon maps");
+      ps.build_ms = seconds_since(tb) * 1000.0;
       gi_photon_count(ctx, 0, &ps.global_stored); gi_photon_count(ctx, 1, &ps.caustic_stored);
       if (!ps.global_stored) { params.indirect_illum = 0; params.direct_photon_illum = 0; }
       if (!ps.caustic_stored) params.caustic_illum = 0;
@@ -79,11 +81,14 @@ int main(int argc, char **argv) {
       }
     }
     if (params.verbose) {
+      const bool cache = params.irradiance_cache && (params.indirect_illum || params.direct_photon_illum);
       printf("Building kdtrees ...\n");
+      if (cache) printf("Building irradiance cache ...\n");
       printf("Built photon map ...\n");
       printf("  Total Time = %.2f seconds\n", seconds_since(t0));
       printf("  Photon Tracing = %.2f seconds\n", ps.trace_ms / 1000.0);
       printf("  KdTree Construction = %.2f seconds\n", ps.build_ms / 1000.0);
+      if (cache) printf("  Irradiance Cache Computation = %.2f seconds\n", ps.cache_ms / 1000.0);
       unsigned long long total = 0;
       if (params.indirect_illum || params.direct_photon_illum) { printf("  # Global Photons Stored = %llu\n", (unsigned long long)ps.global_stored); total += ps.global_stored; }
       if (params.caustic_illum) { printf("  # Caustic Photons Stored = %llu\n", (unsigned long long)ps.caustic_stored); total += ps.caustic_stored; }

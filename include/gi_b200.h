@@ -26,7 +26,7 @@
 extern "C" {
 #endif
 
-#define GI_ABI_VERSION 2
+#define GI_ABI_VERSION 3
 
 /* ------------------------------------------------------------------------------------------------
  * Scene description (flattened R3Scene; src/R3Graphics/R3Scene.h).  Order is the order in which
@@ -190,6 +190,7 @@ typedef struct GiPhotonStats {       /* side effects of MapPhotons (photonmap.cp
   int32_t rounds;
   double trace_ms, build_ms;
   double total_power;                /* sum of LightPower() over the active lights (graphics_utils.cpp:223-258) */
+  double cache_ms;                   /* irradiance-cache pre-pass (photonmap.cpp:380-411), 0 without -cache */
 } GiPhotonStats;
 
 typedef struct GiRenderStats {       /* the -v block of RenderImage (render.cpp:224-255) */
@@ -259,6 +260,17 @@ int gi_gather_batch(GiContext *ctx, int map, const GiGatherQuery *queries, uint6
 int gi_gather_batch_device(GiContext *ctx, int map, const GiGatherQuery *d_queries, uint64_t n, int k, double r,
                            int filter, const GiParams *params, int32_t *d_idx, int32_t *d_count, double *d_rgb,
                            void *stream);
+
+/* The irradiance cache (-cache).  gi_build_maps with params->irradiance_cache (and indirect_illum or
+ * direct_photon_illum) set runs the pre-pass of MapPhotons (photonmap.cpp:380-411) once per loaded global map: every
+ * global photon's colour becomes its power + EstimateIrradiance at its position (photon_utils.cpp:208-246);
+ * gi_get_photons then returns the converted photons.  gi_cached_radiance_batch is a loop of
+ * EstimateCachedRadiance(point, normal, color, brdf, exact_bounce, cos_theta, GLOBAL_PMAP, r)
+ * (photon_utils.cpp:164-205) on that map; rgb_out: n*3 doubles.  Where no photon qualifies within r the result is
+ * black (the reference reads through a NULL pointer there). */
+int gi_cached_radiance_batch(GiContext *ctx, const GiGatherQuery *queries, uint64_t n, double r, double *rgb_out);
+int gi_cached_radiance_batch_device(GiContext *ctx, const GiGatherQuery *d_queries, uint64_t n, double r, double *d_rgb,
+                                    void *stream);
 
 /* MapPhotons() (photonmap.cpp:260-436): emission + tracing + power scaling; maps stay on the device */
 int gi_trace_photons(GiContext *ctx, const GiParams *params, GiPhotonStats *stats);

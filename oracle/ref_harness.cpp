@@ -11,6 +11,8 @@
 //   ref_harness photons    <in.scn> <out_prefix> <seed> [photonmap flags] (MapPhotons, photonmap.cpp:260)
 //   ref_harness gather     <photons.bin> <queries.bin> <out.bin> <k> <r> <filter 0|1|2> [threads]
 //                                                     (EstimateRadiance, photon_utils.cpp:72)
+//   ref_harness cache      <photons.bin> <queries.bin> <out.bin> <k> <r> <out_photons.bin>
+//                                                     (irradiance pre-pass photonmap.cpp:380-411 + EstimateCachedRadiance)
 //   ref_harness parse      [photonmap flags]                               (ParseArgs, io_utils.cpp:16)
 //   ref_harness shade      <in.scn> <rays.bin> <out.bin> [-load_global f] [-load_caustic f] [photonmap flags]
 //                                                     (Intersects + RayTrace, render.cpp:119-124)
@@ -376,6 +378,79 @@ static int cmd_gather(int argc, char **argv) {
   return 0;
 }
 
+// ---------------------------------------------------------------- irradiance cache (-cache)
+// The cache pre-pass is inlined in MapPhotons (photonmap.cpp:380-411), which also traces the photons; for a LOADED map
+// the same steps are restated here around the reference's own EstimateIrradiance (photon_utils.cpp:208-246): every
+// photon's colour becomes its own power + the irradiance estimate at its position, all estimates taken before any
+// colour is overwritten.
+static void irradiance_prepass(RNArray<Photon *> &photons, R3Kdtree<Photon *> *tree, int estimate_size, RNScalar estimate_dist) {
+  const int n = photons.NEntries();
+  std::vector<Photon> converted(n);
+  for (int i = 0; i < n; i++) {
+    converted[i] = *photons[i];
+    RNRgb irradiance = RGBE_to_RNRgb(converted[i].rgbe);
+    EstimateIrradiance(converted[i].position, irradiance, tree, estimate_size, estimate_dist);
+    RNRgb_to_RGBE(irradiance, converted[i].rgbe);
+  }
+  for (int i = 0; i < n; i++)
+    for (int j = 0; j < 4; j++) photons[i]->rgbe[j] = converted[i].rgbe[j];
+}
+
+// usage: cache photons.gipm queries.bin out.bin k r out_photons.gipm
+// Pre-pass on the loaded map (k = GLOBAL_ESTIMATE_SIZE, r = GLOBAL_ESTIMATE_DIST), converted photons written to
+// out_photons.gipm; then the reference's EstimateCachedRadiance (photon_utils.cpp:164-205) for every query.
+// out.bin has the `gather` layout with k = 1: count = 1 and the chosen photon's index, or count = -1 where no
+// photon qualifies inside r -- the reference would dereference NULL there (photon_utils.cpp:181-183), so the call
+// is skipped and the colour left black.
+static int cmd_cache(int argc, char **argv) {
+  if (argc < 8) die("usage: cache photons.gipm queries.bin out.bin k r out_photons.gipm");
+  static std::vector<Photon> ph; ph = read_photons(argv[2]);
+  FILE *f = fopen(argv[3], "rb"); if (!f) die("cannot open queries");
+  uint32_t hdr[2]; if (fread(hdr, 4, 2, f) != 2 || hdr[0] != 0x59525147) die("bad queries file");
+  uint32_t n = hdr[1]; std::vector<QueryRec> q(n);
+  if (n && fread(q.data(), sizeof(QueryRec), n, f) != n) die("short queries file");
+  fclose(f);
+  int k = atoi(argv[5]); double r = atof(argv[6]);
+  RNArray<Photon *> arr;
+  for (size_t i = 0; i < ph.size(); i++) arr.Insert(&ph[i]);
+  if (ph.empty()) die("empty photon map");
+  R3Kdtree<Photon *> *tree = new R3Kdtree<Photon *>(arr, offsetof(struct Photon, position));
+  BuildDirectionLookupTable();
+  irradiance_prepass(arr, tree, k, r);
+  write_photons(argv[7], arr);
+  struct Out { int32_t count, pad; double rgb[3]; };
+  std::vector<Out> out(n); std::vector<int32_t> idx(n, -1);
+  for (uint32_t i = 0; i < n; i++) {
+    const QueryRec &qq = q[i];
+    R3Point point(qq.p[0], qq.p[1], qq.p[2]); R3Vector normal(qq.n[0], qq.n[1], qq.n[2]);
+    R3Vector bounce(qq.bounce[0], qq.bounce[1], qq.bounce[2]);
+    R3Brdf brdf(RNblack_rgb, RNRgb(qq.kd[0], qq.kd[1], qq.kd[2]), RNRgb(qq.ks[0], qq.ks[1], qq.ks[2]), RNblack_rgb,
+                RNblack_rgb, qq.shininess, 1.0);
+    // which photon will the reference's loop settle on, if any?
+    Photon *p = NULL; RNLength d = 0;
+    while (true) {
+      p = tree->FindClosest(point, d + RN_EPSILON, r, &d);
+      if (!p) break;
+      const int dir = p->direction;
+      const RNScalar perp = normal.Dot(R3Vector(PHOTON_X_LOOKUP[dir], PHOTON_Y_LOOKUP[dir], PHOTON_Z_LOOKUP[dir]));
+      if (!((qq.cos_theta < 0 && perp < 0) || (qq.cos_theta > 0 && perp > 0))) break;
+    }
+    Out o; memset(&o, 0, sizeof(o));
+    RNRgb color = RNblack_rgb;
+    if (p) {
+      EstimateCachedRadiance(point, normal, color, &brdf, bounce, qq.cos_theta, tree, r);
+      o.count = 1; idx[i] = (int32_t)(p - ph.data());
+    } else o.count = -1;
+    o.rgb[0] = color.R(); o.rgb[1] = color.G(); o.rgb[2] = color.B();
+    out[i] = o;
+  }
+  f = fopen(argv[4], "wb"); if (!f) die("cannot open output");
+  uint32_t oh[4] = {0x54414747, n, 1u, 0};
+  fwrite(oh, 4, 4, f); fwrite(out.data(), sizeof(Out), n, f); fwrite(idx.data(), 4, idx.size(), f); fclose(f);
+  printf("{\"cmd\": \"cache\", \"photons\": %zu, \"queries\": %u, \"k\": %d}\n", ph.size(), n, k);
+  return 0;
+}
+
 // ---------------------------------------------------------------- bench: the hot path on all host threads
 // One "step" = R3Scene::Intersects over every ray of rays.bin + EstimateRadiance over every query of queries.bin
 // (kd-tree built once, outside the timed steps).  Prints one JSON line with the per-step seconds.
@@ -457,6 +532,7 @@ static int cmd_bench(int argc, char **argv) {
 // MapPhotons(): the photons are used as stored (already power-scaled) and the kd-tree is built like
 // photonmap.cpp:364-377; a map that is not loaded switches its illumination off, like an empty map (:349-361).
 // out.bin: u32 magic "GSHD", u32 n, n x f64 rgb[3] (what render.cpp:125/130 adds into image_buffer[i][j]).
+static void irradiance_prepass(RNArray<Photon *> &photons, R3Kdtree<Photon *> *tree, int estimate_size, RNScalar estimate_dist);
 static int cmd_shade(int argc, char **argv) {
   if (argc < 5) die("usage: shade in.scn rays.bin out.bin [-load_global f] [-load_caustic f] [photonmap flags]");
   const char *gfile = NULL, *cfile = NULL;
@@ -480,6 +556,8 @@ static int cmd_shade(int argc, char **argv) {
   else GLOBAL_PMAP = new R3Kdtree<Photon *>(GLOBAL_PHOTONS, offsetof(struct Photon, position));
   if (cph.empty()) CAUSTIC_ILLUM = false;
   else CAUSTIC_PMAP = new R3Kdtree<Photon *>(CAUSTIC_PHOTONS, offsetof(struct Photon, position));
+  if (IRRADIANCE_CACHE && (INDIRECT_ILLUM || DIRECT_PHOTON_ILLUM))
+    irradiance_prepass(GLOBAL_PHOTONS, GLOBAL_PMAP, GLOBAL_ESTIMATE_SIZE, GLOBAL_ESTIMATE_DIST);
   uint32_t n; std::vector<double> rays = read_rays(argv[3], n);
   std::vector<double> out((size_t)n * 3, 0.0);
   const R3Point eye = SCENE->Camera().Origin();
@@ -539,7 +617,7 @@ static int cmd_parse(int argc, char **argv) {
 }
 
 int main(int argc, char **argv) {
-  if (argc < 2) die("usage: ref_harness <dump_scene|camrays|isect|photons|gather|shade> ...");
+  if (argc < 2) die("usage: ref_harness <dump_scene|camrays|isect|photons|gather|cache|shade> ...");
   std::string c = argv[1];
   if (c == "dump_scene") return cmd_dump_scene(argc, argv);
   if (c == "camrays") return cmd_camrays(argc, argv);
@@ -548,6 +626,7 @@ int main(int argc, char **argv) {
   if (c == "gather") return cmd_gather(argc, argv);
   if (c == "bench") return cmd_bench(argc, argv);
   if (c == "shade") return cmd_shade(argc, argv);
+  if (c == "cache") return cmd_cache(argc, argv);
   if (c == "parse") return cmd_parse(argc, argv);
   die("unknown command");
   return 2;

@@ -191,6 +191,31 @@ def _oracle_gather(self, photons, queries, k, r, filter=0, fa=0.918, fb=1.953, f
 Oracle.gather = _oracle_gather
 
 
+def _oracle_irradiance_prepass(self, photons, k, r, threads=8):
+    """colours (n x 4 RGBE bytes) of the photons after the -cache pre-pass (oracle/restate_cache.cpp)"""
+    photons = np.ascontiguousarray(photons, dtype=GI_PHOTON)
+    out = np.zeros((len(photons), 4), dtype=np.uint8)
+    f = self.lib.oracle_irradiance_prepass
+    f.argtypes = [ctypes.c_void_p, ctypes.c_uint64, ctypes.c_int, ctypes.c_double, ctypes.c_void_p, ctypes.c_int]
+    assert f(photons.ctypes.data, len(photons), k, r, out.ctypes.data, threads) == 0
+    return out
+
+
+def _oracle_cached_radiance(self, photons, queries, r, threads=8):
+    """EstimateCachedRadiance per query on an already converted map: (idx[n], rgb[n, 3])"""
+    photons = np.ascontiguousarray(photons, dtype=GI_PHOTON); queries = np.ascontiguousarray(queries, dtype=GI_QUERY)
+    idx = np.full(len(queries), -1, dtype=np.int32); rgb = np.zeros((len(queries), 3), dtype=np.float64)
+    f = self.lib.oracle_cached_radiance
+    f.argtypes = [ctypes.c_void_p, ctypes.c_uint64, ctypes.c_void_p, ctypes.c_uint64, ctypes.c_double, ctypes.c_void_p,
+                  ctypes.c_void_p, ctypes.c_int]
+    assert f(photons.ctypes.data, len(photons), queries.ctypes.data, len(queries), r, idx.ctypes.data, rgb.ctypes.data, threads) == 0
+    return idx, rgb
+
+
+Oracle.irradiance_prepass = _oracle_irradiance_prepass
+Oracle.cached_radiance = _oracle_cached_radiance
+
+
 def read_png_rgb(path):
     """Minimal PNG reader (8-bit RGB / RGBA, non-interlaced, all five filter types): returns uint8 [H, W, 3], top row first."""
     import struct

@@ -43,6 +43,11 @@ DET = {
                     ("global",)),
     "cornell_viz_cone": ("cornell", 40, 40, "-no_monte -no_transmissive -no_specular -no_indirect -photon_viz -gf cone 1.2 -cf gauss",
                          ("global", "caustic")),
+    # irradiance cache (-cache): pre-pass on the loaded global map, EstimateCachedRadiance at the primary hit
+    "cornell_viz_cache": ("cornell", 40, 40, "-no_monte -no_transmissive -no_specular -no_indirect -no_caustic -photon_viz -cache",
+                          ("global",)),
+    "cornell_viz_cache_gs": ("cornell", 40, 40, "-no_monte -no_transmissive -no_specular -no_indirect -photon_viz -cache -gs 20 -gd 1.0",
+                             ("global", "caustic")),
     # depth-1 paths with caustic lookups at the path vertex and the fast-global estimate on a diffuse pick is random:
     # keep it out of the deterministic set
 }
@@ -57,6 +62,8 @@ STO = {
     "cornell_indirect": ("cornell", 24, 24, "-no_transmissive -no_specular -no_caustic -it 16 -md 6", ("global",), 64),
     "cornell_full": ("cornell", 24, 24, "-it 8 -st 4 -tt 4 -md 6", ("global", "caustic"), 64),
     "cornell_fast_global": ("cornell", 24, 24, "-fast_global -st 8 -tt 8 -md 6", ("global", "caustic"), 64),
+    "cornell_indirect_cache": ("cornell", 24, 24, "-no_transmissive -no_specular -no_caustic -it 16 -md 6 -cache", ("global",), 64),
+    "cornell_fast_global_cache": ("cornell", 24, 24, "-fast_global -cache -st 8 -tt 8 -md 6", ("global", "caustic"), 64),
 }
 
 
@@ -78,7 +85,13 @@ def shade(scene, w, h, flags, maps, tag, dof=False):
 def main():
     os.makedirs(TMP, exist_ok=True)
     out = {}
+    only = None
+    if len(sys.argv) > 2 and sys.argv[1] == "--only":          # add / refresh the named cases, keep the rest of the file
+        only = set(sys.argv[2].split(","))
+        out = dict(np.load(f"{HERE}/render.npz"))
     for name, (scene, w, h, flags, maps) in DET.items():
+        if only is not None and name not in only:
+            continue
         a = shade(scene, w, h, flags, maps, name)
         b = shade(scene, w, h, flags, maps, name + ".again")
         # (photon sums may differ in the last bits from run to run: the reference kd-tree returns its k nearest in a
@@ -88,6 +101,8 @@ def main():
         out[name + "__meta"] = np.array([scene, str(w), str(h), flags, ",".join(maps)])
         print(name, "mean", a.mean(axis=(0, 1)))
     for name, (scene, w, h, flags, maps, runs) in STO.items():
+        if only is not None and name not in only:
+            continue
         imgs = np.stack([shade(scene, w, h, flags, maps, f"{name}.{r}") for r in range(runs)])
         out[name] = imgs.mean(0)
         out[name + "__sem"] = imgs.std(0, ddof=1) / np.sqrt(runs)

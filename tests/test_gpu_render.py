@@ -129,9 +129,9 @@ def test_rank_sharding_partitions_the_frame(gpu_ctx):
 
 
 def test_render_errors(gpu_ctx):
-    params, w, h = setup(gpu_ctx, "cornell_direct")
+    params, w, h = setup(gpu_ctx, "cornell_viz_cone")          # global map loaded and built without -cache
     params.irradiance_cache = 1
-    with pytest.raises(gi_b200.GiError):
+    with pytest.raises(gi_b200.GiError, match="built without"):
         gpu_ctx.render_float(params, w, h, 0)
     params.irradiance_cache = 0
     with pytest.raises(gi_b200.GiError):
