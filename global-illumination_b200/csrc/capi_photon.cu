@@ -23,7 +23,7 @@ static const uint32_t PMAP_MAGIC = 0x4d504947u;   // "GIPM"
 
 void free_map(PhotonMapStore &m) {
   cudaFree((void *)m.dev.px); cudaFree((void *)m.dev.py); cudaFree((void *)m.dev.pz);
-  cudaFree((void *)m.dev.node); cudaFree((void *)m.dev.shade); cudaFree((void *)m.dev.orig); cudaFree((void *)m.dev.inode);
+  cudaFree((void *)m.dev.node); cudaFree((void *)m.dev.shade); cudaFree((void *)m.dev.orig); cudaFree((void *)m.dev.gbox);
   cudaFree(m.raw);
   m = PhotonMapStore();
 }
@@ -214,10 +214,6 @@ int gi_gather_batch_device(GiContext *ctx, int map, const GiGatherQuery *d_queri
   ga.k = k; ga.cap = pow2ceil(2 * k) < 256 ? 256 : pow2ceil(2 * k); ga.filter = filter; ga.r2 = r * r;
   ga.fa = params ? params->filter_const_a : 0.918; ga.fb = params ? params->filter_const_b : 1.953;
   ga.fk = params ? params->filter_const_k : 1.0;
-  ga.tile_levels = k <= 32 ? 6 : (k <= 128 ? 7 : 8);
-  if (const char *e = getenv("GI_TILE_LEVELS")) ga.tile_levels = atoi(e);
-  if (ga.tile_levels < GI_TILE_LEVELS_MIN) ga.tile_levels = GI_TILE_LEVELS_MIN;
-  if (ga.tile_levels > GI_TILE_LEVELS_MAX) ga.tile_levels = GI_TILE_LEVELS_MAX;
   ga.guess_factor = 1.1;
   ga.slack = ga.cap;
   ga.min_blocks = 3;

@@ -8,12 +8,13 @@
 // Phong weight, disk / cone / Gauss filters as photon_utils.cpp:109-158.  Documented tightening: exact d^2 ties at
 // the k-th place go to the photon with the lower index (the reference's choice depends on its randomised tree).
 //
-// Design: one warp per query.
-//   * Upper levels of the left-balanced tree are walked by the whole warp (uniform control flow, near child first,
-//     far child pushed with its plane distance; float32 split planes are widened by one ulp so pruning is
-//     conservative w.r.t. the FP64 coordinates).
-//   * The bottom t levels below a node (t = 6..9 by estimate size) are a "tile": in heap layout they are t contiguous
-//     runs, read by the 32 lanes in (2^t - 1) / 32 coalesced rounds of FP64 distance tests.
+// Design: one warp per query; the binary left-balanced tree is walked as a 32-ary tree of 5-level groups.
+//   * A group = a node and the four levels below it: 31 photons in 5 contiguous runs of the heap layout, tested by
+//     the 32 lanes in one round of FP64 distance tests.
+//   * Its 32 child groups are one contiguous run of slots; the tight FP64 boxes of their subtrees (gbox, built with
+//     the tree) are tested by the 32 lanes in one round, and the children whose box touches the search ball are
+//     entered nearest first (warp min-reduction on the float bits of the box distance).  Box distances are lower
+//     bounds of the FP64 photon distances, so nothing inside the ball is skipped.
 //   * Candidates (d^2, slot, photon index) are appended to a per-warp buffer in shared memory with ballot/popc.
 //     When the buffer runs full it is cut back with a 256-bin histogram of d^2 / bound (photons on a surface are
 //     uniform in d^2, so the boundary bin holds ~cap/256 candidates): everything up to the bin that contains the
@@ -28,6 +29,7 @@
 namespace gi {
 
 #define FULL 0xffffffffu
+#define GI_GATHER_WARP_EXTRA (1024 + GI_MAX_GROUPS * 32 * 4)   /* per-warp shared memory besides the candidates: histogram + walk keys */
 
 struct WarpBuf {
   double *d2; uint32_t *slot; uint32_t *hist;     // shared memory: candidates (d2, heap slot) + 256 histogram bins
@@ -176,17 +178,20 @@ gather_kernel(PhotonMapDev m, const double *__restrict__ lut, const GiGatherQuer
   WarpBuf b; b.cap = ga.cap; b.orig = m.orig;
   b.limit = ga.cap - 32 < ga.k + ga.slack ? ga.cap - 32 : ga.k + ga.slack;
   {
-    char *base = (char *)smem + (size_t)warp * ((size_t)ga.cap * 12 + 1024);
+    char *base = (char *)smem + (size_t)warp * ((size_t)ga.cap * 12 + GI_GATHER_WARP_EXTRA);
     b.d2 = (double *)base; b.slot = (uint32_t *)(base + (size_t)ga.cap * 8);
     b.hist = b.slot + ga.cap;
   }
+  uint32_t *keys = b.hist + 256;                            // GI_MAX_GROUPS x 32, each lane reads only its own column
+  const uint32_t NONE = 0xffffffffu;
   const int k = ga.k;
   const uint64_t n = m.n;
-  const int tile_level = m.levels - ga.tile_levels;         // nodes at this level or deeper are handled as tiles
+  const uint32_t n32 = (uint32_t)n;
+  const int jl = 31 - __clz(lane + 1);                      // relative depth of this lane's photon inside a group
   const uint64_t warps_total = (uint64_t)gridDim.x * GI_GATHER_WARPS;
   const uint64_t nchunks = (nq + GI_GATHER_CHUNK - 1) / GI_GATHER_CHUNK;
   // Search radius carried from one query to the next: consecutive queries of a chunk are neighbouring pixels, so the
-  // previous k-th distance (x2 in area) is tried first and the full radius only if fewer than k photons are inside.
+  // previous k-th distance (x guess_factor in area) is tried first and widened only if fewer than k photons are inside.
   double guess = ga.r2;
   for (uint64_t chunk = (uint64_t)blockIdx.x * GI_GATHER_WARPS + warp; chunk < nchunks; chunk += warps_total)
   for (uint64_t qi = chunk * GI_GATHER_CHUNK; qi < nq && qi < (chunk + 1) * GI_GATHER_CHUNK; qi++) {
@@ -200,66 +205,50 @@ gather_kernel(PhotonMapDev m, const double *__restrict__ lut, const GiGatherQuer
       double init = fmin(ga.r2, guess);
       while (true) {
         count = 0; bound = init;
-        // traversal stack spread over the lanes (entry i lives in lane i): node, squared distance from the query to
-        // the node's cell, and the per-axis offsets it is made of (Arya & Mount incremental distance)
-        uint32_t sk_node = 0; double sk_rd = 0.0, sk_ox = 0.0, sk_oy = 0.0, sk_oz = 0.0;
-        int sp = 0;
-        uint32_t s = 0; double rd = 0.0, ox = 0.0, oy = 0.0, oz = 0.0;
-        const uint32_t n32 = (uint32_t)n;
-        bool have = true;
+        // The tree is walked as a 32-ary tree of 5-level groups (photon_dev.h), depth first.  Row g of the walk keeps
+        // the root of the group it is in (st_root, held by lane g) and, per lane, the lower bound of the squared
+        // distance from the query to child group `lane` (keys[g][lane], float bits rounded down, NONE once visited
+        // or culled); children are entered nearest first and re-tested against the bound, which shrinks as the
+        // candidate buffer is cut.
+        uint32_t st_root = 0;
+        int g = 0;
+        uint32_t s = 0;
+        bool enter = true;
         while (true) {
-          if (!have) {
-            if (sp == 0) break;
-            --sp;
-            s = __shfl_sync(FULL, sk_node, sp); rd = __shfl_sync(FULL, sk_rd, sp);
-            ox = __shfl_sync(FULL, sk_ox, sp); oy = __shfl_sync(FULL, sk_oy, sp); oz = __shfl_sync(FULL, sk_oz, sp);
-            if (rd > bound) continue;
-          }
-          have = false;
-          const int lvl = 31 - __clz(s + 1);
-          if (lvl >= tile_level) {
-            // ---- tile: subtree of s, relative depth j occupies slots (s << j) + e, e in [2^j - 1, 2^(j+1) - 1)
-            const int total = (1 << (m.levels - lvl)) - 1;
-            for (int e0 = 0; e0 < total; e0 += 32) {                   // uniform trip count for the ballots
-              const int e = e0 + lane;
+          const int h = g == 0 ? m.h0 : GI_GROUP_LEVELS;
+          if (enter) {
+            // ---- the group's photons: relative depth j occupies slots (s << j) + e, e in [2^j - 1, 2^(j+1) - 1)
+            {
+              const uint32_t slot = (s << jl) + (uint32_t)lane;
               bool pred = false; double d2 = 0.0;
-              const int j = 31 - __clz(e + 1);
-              const uint32_t slot = (s << j) + (uint32_t)e;
-              if (e < total && slot < n32) { d2 = dist2(m, slot, qx, qy, qz); pred = d2 <= bound; }
+              if (lane < (1 << h) - 1 && slot < n32) { d2 = dist2(m, slot, qx, qy, qz); pred = d2 <= bound; }
               append(b, m, count, bound, k, lane, pred, d2, slot);
             }
-            continue;
-          }
-          // ---- upper node (one 32-byte record, same in every lane: uniform control flow): its own photon, then
-          //      the near child first
-          const double2 r0 = m.inode[2 * (size_t)s], r1 = m.inode[2 * (size_t)s + 1];
-          const double dx = qx - r0.x, dy = qy - r0.y, dz = qz - r1.x;
-          const double d2 = (dx * dx) + (dy * dy) + (dz * dz);
-          if (d2 <= bound) {
-            if (lane == 0) { b.d2[count] = d2; b.slot[count] = s; }
-            count++;
-            __syncwarp();
-            if (count > b.limit) cut(b, count, bound, k, lane);
-          }
-          const int axis = __double2hiint(r1.y);
-          const double sf = (double)__int_as_float(__double2loint(r1.y));
-          // photons left of the split have float(c) <= sf, right of it float(c) >= sf: widen by one float ulp
-          const double wide = fabs(sf) * 1.1920929e-7 + 1.0e-44;
-          const double qa = axis == 0 ? qx : (axis == 1 ? qy : qz);
-          const double oa = axis == 0 ? ox : (axis == 1 ? oy : oz);
-          const bool left = qa < sf;
-          const uint32_t near = 2 * s + (left ? 1 : 2), far = 2 * s + (left ? 2 : 1);
-          double fd = left ? (sf - wide) - qa : qa - (sf + wide);
-          fd = fmax(fd, oa);                                            // never closer than the parent cell
-          const double frd = (rd - oa * oa + fd * fd) * 0.99999999999999;   // rounding must not over-estimate
-          if (far < n32 && frd <= bound) {
-            if (lane == sp) {
-              sk_node = far; sk_rd = frd;
-              sk_ox = axis == 0 ? fd : ox; sk_oy = axis == 1 ? fd : oy; sk_oz = axis == 2 ? fd : oz;
+            if (g + 1 >= m.groups) { if (--g < 0) break; enter = false; continue; }      // bottom row: back to the parent
+            // ---- the 32 child groups: one box test per lane
+            const uint32_t c = (((s + 1) << h) - 1) + (uint32_t)lane;
+            uint32_t key = NONE;
+            if (lane < (1 << h) && c < n32) {
+              const double2 *bx = m.gbox + 3 * ((size_t)m.gbox_off[g + 1] + (c - ((1u << m.glevel[g + 1]) - 1u)));
+              const double2 X = bx[0], Y = bx[1], Z = bx[2];
+              const double dx = fmax(fmax(X.x - qx, qx - X.y), 0.0), dy = fmax(fmax(Y.x - qy, qy - Y.y), 0.0),
+                           dz = fmax(fmax(Z.x - qz, qz - Z.y), 0.0);
+              const double bd = ((dx * dx) + (dy * dy) + (dz * dz)) * 0.99999999999999;   // rounding must not over-estimate
+              if (bd <= bound) key = __float_as_uint(__double2float_rd(bd));
             }
-            sp++;
+            keys[g * 32 + lane] = key;
+            if (lane == g) st_root = s;
+            enter = false;
           }
-          if (near < n32) { s = near; have = true; }
+          // ---- nearest not yet visited child of row g
+          const uint32_t key = keys[g * 32 + lane];
+          const uint32_t mn = __reduce_min_sync(FULL, key);
+          if (mn == NONE || (double)__uint_as_float(mn) > bound) { if (--g < 0) break; continue; }
+          const int who = __ffs(__ballot_sync(FULL, key == mn)) - 1;
+          if (lane == who) keys[g * 32 + lane] = NONE;
+          const uint32_t root = __shfl_sync(FULL, st_root, g);
+          s = (((root + 1) << h) - 1) + (uint32_t)who;
+          g++; enter = true;
         }
         finish(b, count, bound, k, lane);
         if (count >= k || init >= ga.r2) break;
@@ -337,7 +326,7 @@ gather_kernel(PhotonMapDev m, const double *__restrict__ lut, const GiGatherQuer
 template <int MINB>
 static cudaError_t launch_t(GiContext *ctx, const PhotonMapDev &m, const double *d_lut, const GiGatherQuery *d_q, uint64_t nq,
                             const GatherArgs &ga, int32_t *d_idx, int32_t *d_count, double *d_rgb, cudaStream_t st) {
-  const size_t smem = (size_t)GI_GATHER_WARPS * ((size_t)ga.cap * 12 + 1024);
+  const size_t smem = (size_t)GI_GATHER_WARPS * ((size_t)ga.cap * 12 + GI_GATHER_WARP_EXTRA);
   static size_t configured = 0;
   if (smem > configured) {
     cudaError_t e = cudaFuncSetAttribute(gather_kernel<MINB>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);

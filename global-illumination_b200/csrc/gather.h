@@ -12,7 +12,6 @@ struct GatherArgs {
   int k;                           /* estimate size (<= GI_MAX_K) */
   int cap;                         /* candidate slots per warp: power of two, >= max(256, 2k) */
   int filter;                      /* GiFilter */
-  int tile_levels;                 /* bottom levels of the tree scanned as one tile */
   int min_blocks;                  /* 3: 80 registers / 24 warps per SM; 4: 64 registers / 32 warps per SM */
   int slack;                       /* the candidate buffer is cut back to k once it holds more than k + slack */
   double guess_factor;             /* next query's first search radius^2 = this factor x the last k-th d^2 */

@@ -144,7 +144,7 @@ __global__ void assign_kernel(uint64_t first, uint64_t n, int L, int level, uint
 
 __global__ void finalize_kernel(const GiPhoton *__restrict__ ph, uint64_t n, const uint32_t *__restrict__ heap_photon,
                                 const float *__restrict__ split, const uint8_t *__restrict__ axis, double *px, double *py,
-                                double *pz, uint2 *node, uint2 *shade, uint32_t *orig, double2 *inode, uint64_t n_inode) {
+                                double *pz, uint2 *node, uint2 *shade, uint32_t *orig) {
   const uint64_t i = (uint64_t)blockIdx.x * blockDim.x + threadIdx.x;
   if (i >= n) return;
   const uint32_t src = heap_photon[i];
@@ -154,9 +154,37 @@ __global__ void finalize_kernel(const GiPhoton *__restrict__ ph, uint64_t n, con
   shade[i] = make_uint2(b.z, b.w & 0xffffu);
   orig[i] = src;
   node[i] = make_uint2(__float_as_uint(split[i]), axis[i]);
-  if (i < n_inode) {
-    inode[2 * i] = make_double2(px[i], py[i]);
-    inode[2 * i + 1] = make_double2(pz[i], __hiloint2double((int)axis[i], (int)__float_as_uint(split[i])));
+}
+
+// Tight FP64 box of the subtree below every group root of row g (photon_dev.h): one warp per root takes the min / max
+// over the group's 31 photons and, unless this is the bottom row, over the boxes of its 32 child groups (row g + 1,
+// filled by the previous launch).
+__global__ void group_box_kernel(PhotonMapDev m, int g, double2 *gbox) {
+  const uint64_t w = ((uint64_t)blockIdx.x * blockDim.x + threadIdx.x) >> 5;
+  const int lane = threadIdx.x & 31;
+  const uint64_t first = ((uint64_t)1 << m.glevel[g]) - 1;
+  const uint64_t r = first + w;
+  if (r >= m.n || w >= ((uint64_t)1 << m.glevel[g])) return;
+  const double INF = __longlong_as_double(0x7ff0000000000000ll);
+  double lo[3] = {INF, INF, INF}, hi[3] = {-INF, -INF, -INF};
+  const int j = 31 - __clz(lane + 1);
+  const uint64_t slot = (r << j) + (uint64_t)lane;
+  if (lane < 31 && slot < m.n) { lo[0] = hi[0] = m.px[slot]; lo[1] = hi[1] = m.py[slot]; lo[2] = hi[2] = m.pz[slot]; }
+  if (g + 1 < m.groups) {
+    const uint64_t c = ((r + 1) << GI_GROUP_LEVELS) - 1 + (uint64_t)lane;
+    if (c < m.n) {
+      const double2 *b = gbox + 3 * ((size_t)m.gbox_off[g + 1] + (c - (((uint64_t)1 << m.glevel[g + 1]) - 1)));
+      for (int a = 0; a < 3; a++) { lo[a] = fmin(lo[a], b[a].x); hi[a] = fmax(hi[a], b[a].y); }
+    }
+  }
+  for (int a = 0; a < 3; a++)
+    for (int o = 16; o > 0; o >>= 1) {
+      lo[a] = fmin(lo[a], __shfl_xor_sync(0xffffffffu, lo[a], o));
+      hi[a] = fmax(hi[a], __shfl_xor_sync(0xffffffffu, hi[a], o));
+    }
+  if (lane == 0) {
+    double2 *b = gbox + 3 * ((size_t)m.gbox_off[g] + w);
+    for (int a = 0; a < 3; a++) b[a] = make_double2(lo[a], hi[a]);
   }
 }
 
@@ -171,7 +199,8 @@ cudaError_t build_photon_map(GiContext *ctx, PhotonMapStore &m, uint64_t n) {
   uint32_t *heap_photon = nullptr, *bounds = nullptr; float *split = nullptr; uint8_t *axis = nullptr;
   void *tmp = nullptr; size_t tmp_bytes = 0;
   double *px = nullptr, *py = nullptr, *pz = nullptr; uint2 *node = nullptr, *shade = nullptr; uint32_t *orig = nullptr;
-  double2 *inode = nullptr; uint64_t n_inode = 0;
+  double2 *gbox = nullptr; uint64_t n_box = 0;
+  PhotonMapDev d{};
   const int B = 256;
   const unsigned G = (unsigned)((n + B - 1) / B);
   int cur = 0;
@@ -202,21 +231,35 @@ cudaError_t build_photon_map(GiContext *ctx, PhotonMapStore &m, uint64_t n) {
   }
   CKB(cudaMalloc(&px, 8 * n)); CKB(cudaMalloc(&py, 8 * n)); CKB(cudaMalloc(&pz, 8 * n));
   CKB(cudaMalloc(&node, 8 * n)); CKB(cudaMalloc(&shade, 8 * n)); CKB(cudaMalloc(&orig, 4 * n));
-  n_inode = L > GI_TILE_LEVELS_MIN ? ((uint64_t)1 << (L - GI_TILE_LEVELS_MIN)) - 1 : 0;   // every level that can be "upper"
-  if (n_inode > n) n_inode = n;
-  CKB(cudaMalloc(&inode, 32 * (n_inode ? n_inode : 1)));
-  finalize_kernel<<<G, B, 0, st>>>(ph, n, heap_photon, split, axis, px, py, pz, node, shade, orig, inode, n_inode);
+  finalize_kernel<<<G, B, 0, st>>>(ph, n, heap_photon, split, axis, px, py, pz, node, shade, orig);
   ctx->launches++;
   CKB(cudaGetLastError());
+  d.n = n; d.levels = L; d.px = px; d.py = py; d.pz = pz; d.node = node; d.shade = shade; d.orig = orig;
+  // rows of 5-level groups (photon_dev.h) and their subtree boxes, bottom row first
+  d.groups = (L + GI_GROUP_LEVELS - 1) / GI_GROUP_LEVELS;
+  d.h0 = L - GI_GROUP_LEVELS * (d.groups - 1);
+  for (int g = 0; g < d.groups; g++) {
+    d.glevel[g] = g == 0 ? 0 : d.h0 + GI_GROUP_LEVELS * (g - 1);
+    d.gbox_off[g] = (uint32_t)n_box;
+    if (g > 0) { const uint64_t first = ((uint64_t)1 << d.glevel[g]) - 1; n_box += n - first < first + 1 ? n - first : first + 1; }
+  }
+  CKB(cudaMalloc(&gbox, 48 * (n_box ? n_box : 1)));
+  d.gbox = gbox;
+  for (int g = d.groups - 1; g >= 1; g--) {
+    const uint64_t first = ((uint64_t)1 << d.glevel[g]) - 1;
+    const uint64_t rows = n - first < first + 1 ? n - first : first + 1;
+    group_box_kernel<<<(unsigned)((rows * 32 + B - 1) / B), B, 0, st>>>(d, g, gbox);
+    ctx->launches++;
+  }
+  CKB(cudaGetLastError());
   CKB(cudaStreamSynchronize(st));
-  m.dev.n = n; m.dev.levels = L; m.dev.px = px; m.dev.py = py; m.dev.pz = pz; m.dev.node = node; m.dev.shade = shade;
-  m.dev.orig = orig; m.dev.inode = inode; m.dev.n_inode = n_inode;
+  m.dev = d;
   m.built = true;
-  px = py = pz = nullptr; node = shade = nullptr; orig = nullptr; inode = nullptr;
+  px = py = pz = nullptr; node = shade = nullptr; orig = nullptr; gbox = nullptr;
 done:
   for (int k = 0; k < 2; k++) { cudaFree(keys[k]); cudaFree(vals[k]); }
   cudaFree(heap_photon); cudaFree(split); cudaFree(bounds); cudaFree(axis); cudaFree(tmp);
-  cudaFree(px); cudaFree(py); cudaFree(pz); cudaFree(node); cudaFree(shade); cudaFree(orig); cudaFree(inode);
+  cudaFree(px); cudaFree(py); cudaFree(pz); cudaFree(node); cudaFree(shade); cudaFree(orig); cudaFree(gbox);
   return err;
 }
 

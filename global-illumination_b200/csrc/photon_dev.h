@@ -6,8 +6,11 @@
 //   search stream : px/py/pz (FP64, exact distances) + node[] = {float split, axis}  (what traversal touches)
 //   shade stream  : rgbe + direction code + original index                            (read for the k winners only)
 // In heap layout the subtree below node s occupies, at relative depth j, the contiguous run
-// [(s << j) + 2^j - 1, ...) of 2^j slots, so the bottom GI_TILE_LEVELS levels of the tree are read by a warp as a
-// handful of coalesced runs ("node tiles") instead of node by node.
+// [(s << j) + 2^j - 1, ...) of 2^j slots.  The search (gather.cu) therefore reads the tree in GROUPS of five levels:
+// the 31 photons of a group are 5 contiguous runs (one warp-wide round of distance tests) and its 32 child groups are
+// one contiguous run of slots whose tight FP64 bounding boxes (gbox) are tested by the 32 lanes at once -- the
+// binary tree is walked as a 32-ary one.  Rows of group roots sit at tree levels glevel[g]; the top group takes the
+// remainder (h0 = levels - 5 (groups - 1) in [1, 5]) so that every other group is exactly five levels deep.
 #pragma once
 #include <stdint.h>
 #if defined(__CUDACC__)
@@ -16,8 +19,8 @@
 
 namespace gi {
 
-#define GI_TILE_LEVELS_MIN 6      /* a tile = the bottom t levels below a node, t chosen per launch in [6, 9]: */
-#define GI_TILE_LEVELS_MAX 9      /* a subtree of up to 2^t - 1 photons read in (2^t - 1) / 32 warp-wide rounds  */
+#define GI_GROUP_LEVELS 5         /* 2^5 - 1 = 31 photons and 32 children per group: one warp-wide round each */
+#define GI_MAX_GROUPS 8           /* rows of groups: 32 tree levels at most (n < 2^32) */
 #define GI_MAX_K 512              /* largest estimate size (-gs/-cs) the gather kernel supports */
 
 struct PhotonMapDev {
@@ -25,8 +28,11 @@ struct PhotonMapDev {
   int32_t levels;                 /* floor(log2 n) + 1 */
   const double *px, *py, *pz;     /* heap order */
   const uint2 *node;              /* heap order: x = float bits of the split coordinate, y = split axis (0..2) */
-  const double2 *inode;           /* first n_inode heap slots again, packed for the warp-uniform walk of the upper    */
-  uint64_t n_inode;               /* levels: 2 x double2 = {x, y}, {z, split float bits | axis << 32}: one 32 B sector */
+  const double2 *gbox;            /* tight box of the subtree below every group root of rows 1..groups-1, row-major:   */
+                                  /* 3 x double2 {lo, hi} for x, y, z = 48 B; box of slot s in row g: gbox_off[g] + s - (2^glevel[g] - 1) */
+  int32_t groups, h0;             /* rows of groups; depth of the top group */
+  int32_t glevel[GI_MAX_GROUPS];  /* tree level of the group roots of row g (glevel[0] = 0) */
+  uint32_t gbox_off[GI_MAX_GROUPS];
   const uint2 *shade;             /* heap order: x = rgbe bytes (r | g<<8 | b<<16 | e<<24), y = direction code */
   const uint32_t *orig;           /* heap order -> index in the order the photons were loaded / traced */
 };

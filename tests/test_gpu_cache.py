@@ -87,7 +87,7 @@ def test_cache_matches_oracle_on_synthetic_maps(gpu_ctx, oracle, n, k, r, seed):
         idx, ref = oracle.cached_radiance(conv, q, radius)
         assert np.allclose(rgb, ref, rtol=1e-12, atol=1e-300), np.abs(rgb - ref).max()
         assert ((rgb == 0).all(1) >= (idx < 0)).all()
-    assert (idx >= 0).mean() > 0.5
+    assert (idx >= 0).mean() > (0.5 if n > 1 else 0.2)      # one photon: the side test alone rejects half
 
 
 def test_cache_empty_map(gpu_ctx):
