@@ -211,18 +211,30 @@ int gi_gather_batch_device(GiContext *ctx, int map, const GiGatherQuery *d_queri
   const double *lut = direction_lut(ctx);
   if (!lut) return 1;
   GatherArgs ga;
-  ga.k = k; ga.cap = pow2ceil(2 * k) < 256 ? 256 : pow2ceil(2 * k); ga.filter = filter; ga.r2 = r * r;
+  ga.k = k; ga.filter = filter; ga.r2 = r * r;
+  // candidate slots: k + half as many again (at least 96) + one round of 32 in flight; the index output sorts the
+  // buffer with a bitonic network and needs a power of two
+  ga.cap = d_idx ? (pow2ceil(2 * k) < 256 ? 256 : pow2ceil(2 * k)) : ((k + (k / 2 > 96 ? k / 2 : 96) + 31) / 32) * 32 + 32;
   ga.fa = params ? params->filter_const_a : 0.918; ga.fb = params ? params->filter_const_b : 1.953;
   ga.fk = params ? params->filter_const_k : 1.0;
   ga.guess_factor = 1.1;
   ga.slack = ga.cap;
-  ga.min_blocks = 3;
-  if (const char *e = getenv("GI_GATHER_OCC")) ga.min_blocks = atoi(e);
+  ga.max_warps = 0; ga.key_rows = 0;
+  if (const char *e = getenv("GI_GATHER_WARPS")) ga.max_warps = atoi(e);
   if (const char *e = getenv("GI_CUT_SLACK")) ga.slack = atoi(e);
   if (ga.slack < 32) ga.slack = 32;
   if (const char *e = getenv("GI_GUESS_FACTOR")) ga.guess_factor = atof(e);
   cudaStream_t st = (cudaStream_t)stream;      // NULL = the CUDA default stream, as documented
-  GI_CUDA(launch_gather(ctx, m.dev, lut, d_queries, n, ga, d_idx, d_count, d_rgb, st));
+  // batches are walked along a Morton curve (query_order.cu); small ones are not worth the sort
+  const uint32_t *order = nullptr;
+  bool sort = n >= 4096 && m.dev.n >= 4096;
+  if (const char *e = getenv("GI_SORT_QUERIES")) sort = atoi(e) != 0;
+  if (sort) {
+    bool failed = false;
+    order = morton_order(ctx, m, d_queries, n, st, &failed);
+    if (failed) return 1;
+  }
+  GI_CUDA(launch_gather(ctx, m.dev, lut, d_queries, order, n, ga, d_idx, d_count, d_rgb, st));
   return 0;
 }
 

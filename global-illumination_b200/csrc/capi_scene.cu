@@ -100,8 +100,10 @@ void gi_destroy(GiContext *ctx) {
   if (ctx->render_ws && ctx->render_ws_free) ctx->render_ws_free(ctx->render_ws);
   for (int i = 0; i < 2; i++) {
     for (int j = 0; j < 4; j++) ctx->stage[i][j].release();
+    for (int j = 0; j < 5; j++) ctx->order_ws[i][j].release();
     if (ctx->pipe[i]) cudaStreamDestroy(ctx->pipe[i]);
   }
+  for (int j = 0; j < 5; j++) ctx->order_ws[2][j].release();
   if (ctx->stream) cudaStreamDestroy(ctx->stream);
   delete ctx;
 }

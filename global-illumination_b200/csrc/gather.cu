@@ -29,13 +29,30 @@
 namespace gi {
 
 #define FULL 0xffffffffu
-#define GI_GATHER_WARP_EXTRA (1024 + GI_MAX_GROUPS * 32 * 4)   /* per-warp shared memory besides the candidates: histogram + walk keys */
+#define NONE 0xffffffffu
+#define GI_HIST_BINS 128          /* histogram of the exact cut (4 bins per lane) */
+/* per-warp shared memory: cap candidates (8 B d2 + 4 B slot), the histogram, one row of walk keys per group row above gp */
+#define GI_WARP_BYTES(cap, rows) ((size_t)(cap) * 12 + GI_HIST_BINS * 4 + (size_t)(rows) * 128)
+
+// The per-warp buffers are addressed through 32-bit shared-window addresses and ld/st.shared: with C++ pointers the
+// compiler re-derived the window base (S2R SR_CgaCtaId + 12 integer ops) in every iteration of the walk.
+__device__ __forceinline__ double lds_f64(uint32_t a) { double v; asm volatile("ld.shared.f64 %0, [%1];" : "=d"(v) : "r"(a)); return v; }
+__device__ __forceinline__ uint32_t lds_u32(uint32_t a) { uint32_t v; asm volatile("ld.shared.u32 %0, [%1];" : "=r"(v) : "r"(a)); return v; }
+__device__ __forceinline__ void sts_f64(uint32_t a, double v) { asm volatile("st.shared.f64 [%0], %1;" ::"r"(a), "d"(v)); }
+__device__ __forceinline__ void sts_u32(uint32_t a, uint32_t v) { asm volatile("st.shared.u32 [%0], %1;" ::"r"(a), "r"(v)); }
+__device__ __forceinline__ void red_u32(uint32_t a, uint32_t v) { asm volatile("red.shared.add.u32 [%0], %1;" ::"r"(a), "r"(v)); }
 
 struct WarpBuf {
-  double *d2; uint32_t *slot; uint32_t *hist;     // shared memory: candidates (d2, heap slot) + 256 histogram bins
+  uint32_t a_d2, a_slot, a_hist, a_keys;          // shared memory: candidates (d2, heap slot), histogram bins, walk keys
   int limit;                                      // cut the buffer back to k once it holds more than this
   const uint32_t *orig;                           // global: heap slot -> photon index, read only to break exact d2 ties
-  int cap;
+  int cap;                                        // candidate slots (a power of two when idx_out is wanted: bitonic sort)
+  __device__ __forceinline__ double d2(int i) const { return lds_f64(a_d2 + 8u * (uint32_t)i); }
+  __device__ __forceinline__ uint32_t slot(int i) const { return lds_u32(a_slot + 4u * (uint32_t)i); }
+  __device__ __forceinline__ uint32_t hist(int i) const { return lds_u32(a_hist + 4u * (uint32_t)i); }
+  __device__ __forceinline__ void set_d2(int i, double v) const { sts_f64(a_d2 + 8u * (uint32_t)i, v); }
+  __device__ __forceinline__ void set_slot(int i, uint32_t v) const { sts_u32(a_slot + 4u * (uint32_t)i, v); }
+  __device__ __forceinline__ void set_hist(int i, uint32_t v) const { sts_u32(a_hist + 4u * (uint32_t)i, v); }
 };
 
 __device__ __forceinline__ bool lex_less(double da, uint32_t oa, double db, uint32_t ob) {
@@ -44,83 +61,109 @@ __device__ __forceinline__ bool lex_less(double da, uint32_t oa, double db, uint
 
 // warp-cooperative bitonic sort of buf[0..cap) ascending by (d2, photon index); cap is a power of two.  Padding
 // entries carry d2 = +inf (and slot 0), real entries finite d2, so the index lookup happens only on real ties.
-__device__ void bitonic_sort(WarpBuf &b, int lane) {
+__device__ __noinline__ void bitonic_sort(const WarpBuf &b, int lane) {
   for (int k2 = 2; k2 <= b.cap; k2 <<= 1)
     for (int j = k2 >> 1; j > 0; j >>= 1) {
       for (int i = lane; i < b.cap; i += 32) {
         const int x = i ^ j;
         if (x > i) {
-          const double di = b.d2[i], dx = b.d2[x];
-          const uint32_t si = b.slot[i], sx = b.slot[x];
+          const double di = b.d2(i), dx = b.d2(x);
+          const uint32_t si = b.slot(i), sx = b.slot(x);
           const bool up = (i & k2) == 0;
           bool x_less_i = dx < di, i_less_x = di < dx;
           if (di == dx && di < INFINITY) { const uint32_t oi = b.orig[si], ox = b.orig[sx]; x_less_i = ox < oi; i_less_x = oi < ox; }
-          if (up ? x_less_i : i_less_x) { b.d2[i] = dx; b.d2[x] = di; b.slot[i] = sx; b.slot[x] = si; }
+          if (up ? x_less_i : i_less_x) { b.set_d2(i, dx); b.set_d2(x, di); b.set_slot(i, sx); b.set_slot(x, si); }
         }
       }
       __syncwarp();
     }
 }
 
-// slow exact path (heavy ties only): full sort, keep the first k
-__device__ void sort_select(WarpBuf &b, int &count, double &bound, int k, int lane) {
-  for (int i = count + lane; i < b.cap; i += 32) { b.d2[i] = INFINITY; b.slot[i] = 0; }
+// slow exact path (heavy exact ties, or a zero bound): every candidate counts the candidates that precede it in
+// (d2, photon index) order -- O(count^2 / 32) -- and the k first are kept.  Keep flags go through the histogram words.
+__device__ __noinline__ void rank_select(const WarpBuf &b, int &count, double &bound, int k, int lane) {
+  for (int base = 0; base < count; base += 32) {
+    const int i = base + lane;
+    const bool live = i < count;
+    const double di = live ? b.d2(i) : 0.0;
+    const uint32_t oi = live ? b.orig[b.slot(i)] : 0u;
+    int rank = 0;
+    for (int j = 0; j < count; j++) {
+      const double dj = b.d2(j);
+      if (dj < di) rank++;
+      else if (dj == di && live && b.orig[b.slot(j)] < oi) rank++;
+    }
+    const unsigned keep = __ballot_sync(FULL, live && rank < k);
+    if (lane == 0) b.set_hist(base >> 5, keep);
+  }
   __syncwarp();
-  bitonic_sort(b, lane);
-  count = k;
-  bound = fmin(bound, b.d2[k - 1]);
-  __syncwarp();
+  int newcount = 0; double mx = 0.0;
+  for (int base = 0; base < count; base += 32) {
+    const int i = base + lane;
+    const unsigned mk = b.hist(base >> 5);
+    const bool keep = (mk >> lane) & 1u;
+    double d = 0.0; uint32_t sl = 0;
+    if (keep) { d = b.d2(i); sl = b.slot(i); }
+    const int pos = newcount + __popc(mk & ((1u << lane) - 1u));
+    __syncwarp();
+    if (keep) { b.set_d2(pos, d); b.set_slot(pos, sl); mx = fmax(mx, d); }
+    newcount += __popc(mk);
+    __syncwarp();
+  }
+  for (int o = 16; o > 0; o >>= 1) mx = fmax(mx, __shfl_xor_sync(FULL, mx, o));
+  count = newcount; bound = fmin(bound, mx);
 }
 
 // Exact cut of the candidate buffer to the k smallest by (d2, orig).  Requires count > k.
-// A 256-bin histogram of d2 / bound locates the bin B that holds the k-th candidate; bins below B are kept whole,
+// A 128-bin histogram of d2 / bound locates the bin B that holds the k-th candidate; bins below B are kept whole,
 // and inside B (a handful of candidates, since surface photons are uniform in d2) each lane ranks one candidate
 // against the others by shuffles.  The bound becomes the largest kept d2.
-__device__ void cut(WarpBuf &b, int &count, double &bound, int k, int lane) {
-  if (!(bound > 0.0)) { sort_select(b, count, bound, k, lane); return; }
-  for (int i = lane; i < 256; i += 32) b.hist[i] = 0;
+__device__ __noinline__ void cut(const WarpBuf &b, int &count, double &bound, int k, int lane) {
+  if (!(bound > 0.0)) { rank_select(b, count, bound, k, lane); return; }
+  for (int i = lane; i < GI_HIST_BINS; i += 32) b.set_hist(i, 0);
   __syncwarp();
-  const double scale = 256.0 / bound;
+  const double scale = (double)GI_HIST_BINS / bound;
   for (int i = lane; i < count; i += 32) {
-    int bin = (int)(b.d2[i] * scale); bin = bin > 255 ? 255 : bin;
-    atomicAdd(&b.hist[bin], 1u);
+    int bin = (int)(b.d2(i) * scale); bin = bin > GI_HIST_BINS - 1 ? GI_HIST_BINS - 1 : bin;
+    red_u32(b.a_hist + 4u * (uint32_t)bin, 1u);
   }
   __syncwarp();
-  uint32_t h[8]; uint32_t s = 0;
-  for (int j = 0; j < 8; j++) { h[j] = b.hist[lane * 8 + j]; s += h[j]; }
+  constexpr int PER = GI_HIST_BINS / 32;
+  uint32_t h[PER]; uint32_t s = 0;
+  for (int j = 0; j < PER; j++) { h[j] = b.hist(lane * PER + j); s += h[j]; }
   uint32_t incl = s;
   for (int o = 1; o < 32; o <<= 1) { const uint32_t v = __shfl_up_sync(FULL, incl, o); if (lane >= o) incl += v; }
   const uint32_t excl = incl - s;
   const unsigned crossing = __ballot_sync(FULL, incl >= (uint32_t)k);
   const int owner = __ffs(crossing) - 1;                  // count > k  =>  some lane crosses
-  int B = 255, below = 0, m = 0;
+  int B = GI_HIST_BINS - 1, below = 0, m = 0;
   if (lane == owner) {
     uint32_t c = excl;
-    for (int j = 0; j < 8; j++) { if (c + h[j] >= (uint32_t)k) { B = lane * 8 + j; below = (int)c; m = (int)h[j]; break; } c += h[j]; }
+    for (int j = 0; j < PER; j++) { if (c + h[j] >= (uint32_t)k) { B = lane * PER + j; below = (int)c; m = (int)h[j]; break; } c += h[j]; }
   }
   B = __shfl_sync(FULL, B, owner); below = __shfl_sync(FULL, below, owner); m = __shfl_sync(FULL, m, owner);
   const int need = k - below;                             // candidates to keep from bin B, 1 <= need <= m
   __syncwarp();
   if (need < m) {
-    if (m > 32) { sort_select(b, count, bound, k, lane); return; }
+    if (m > 32) { rank_select(b, count, bound, k, lane); return; }
     int c = 0;                                            // list the members of bin B in hist[0..m)
     for (int base = 0; base < count; base += 32) {
       const int i = base + lane;
       bool inb = false;
-      if (i < count) { int bin = (int)(b.d2[i] * scale); bin = bin > 255 ? 255 : bin; inb = bin == B; }
+      if (i < count) { int bin = (int)(b.d2(i) * scale); bin = bin > GI_HIST_BINS - 1 ? GI_HIST_BINS - 1 : bin; inb = bin == B; }
       const unsigned mk = __ballot_sync(FULL, inb);
-      if (inb) b.hist[c + __popc(mk & ((1u << lane) - 1u))] = (uint32_t)i;
+      if (inb) b.set_hist(c + __popc(mk & ((1u << lane) - 1u)), (uint32_t)i);
       c += __popc(mk);
     }
     __syncwarp();
     double md = INFINITY; uint32_t mo = 0xffffffffu; int mi = -1;
-    if (lane < m) { mi = (int)b.hist[lane]; md = b.d2[mi]; mo = b.orig[b.slot[mi]]; }
+    if (lane < m) { mi = (int)b.hist(lane); md = b.d2(mi); mo = b.orig[b.slot(mi)]; }
     int rank = 0;
     for (int l = 0; l < m; l++) {
       const double od = __shfl_sync(FULL, md, l); const uint32_t oo = __shfl_sync(FULL, mo, l);
       rank += lex_less(od, oo, md, mo) ? 1 : 0;
     }
-    if (lane < m && rank >= need) b.d2[mi] = -1.0;        // dropped
+    if (lane < m && rank >= need) b.set_d2(mi, -1.0);     // dropped
     __syncwarp();
   }
   int newcount = 0; double mx = 0.0;
@@ -128,14 +171,14 @@ __device__ void cut(WarpBuf &b, int &count, double &bound, int k, int lane) {
     const int i = base + lane;
     double d = 0.0; uint32_t sl = 0; bool keep = false;
     if (i < count) {
-      d = b.d2[i]; sl = b.slot[i];
-      int bin = (int)(d * scale); bin = bin > 255 ? 255 : bin;
+      d = b.d2(i); sl = b.slot(i);
+      int bin = (int)(d * scale); bin = bin > GI_HIST_BINS - 1 ? GI_HIST_BINS - 1 : bin;
       keep = d >= 0.0 && bin <= B;
     }
     const unsigned mk = __ballot_sync(FULL, keep);
     const int pos = newcount + __popc(mk & ((1u << lane) - 1u));
     __syncwarp();
-    if (keep) { b.d2[pos] = d; b.slot[pos] = sl; mx = fmax(mx, d); }
+    if (keep) { b.set_d2(pos, d); b.set_slot(pos, sl); mx = fmax(mx, d); }
     newcount += __popc(mk);
     __syncwarp();
   }
@@ -144,58 +187,73 @@ __device__ void cut(WarpBuf &b, int &count, double &bound, int k, int lane) {
 }
 
 // after the traversal: exactly the k nearest (or everything found, if fewer); bound = largest kept d2 when k are held
-__device__ void finish(WarpBuf &b, int &count, double &bound, int k, int lane) {
+__device__ __forceinline__ void finish(const WarpBuf &b, int &count, double &bound, int k, int lane) {
   if (count > k) { cut(b, count, bound, k, lane); return; }
   if (count < k) return;
   double mx = 0.0;
-  for (int i = lane; i < count; i += 32) mx = fmax(mx, b.d2[i]);
+  for (int i = lane; i < count; i += 32) mx = fmax(mx, b.d2(i));
   for (int s = 16; s > 0; s >>= 1) mx = fmax(mx, __shfl_xor_sync(FULL, mx, s));
   bound = fmin(bound, mx);
 }
 
-__device__ __forceinline__ void append(WarpBuf &b, const PhotonMapDev &m, int &count, double &bound, int k, int lane,
-                                       bool pred, double d2, uint32_t slot) {
+__device__ __forceinline__ void append(const WarpBuf &b, int &count, double &bound, int k, int lane, bool pred, double d2,
+                                       uint32_t slot) {
   const unsigned mask = __ballot_sync(FULL, pred);
   if (mask == 0) return;
   const int pos = count + __popc(mask & ((1u << lane) - 1u));
-  if (pred) { b.d2[pos] = d2; b.slot[pos] = slot; }
+  if (pred) { b.set_d2(pos, d2); b.set_slot(pos, slot); }
   count += __popc(mask);
   __syncwarp();
   if (count > b.limit) cut(b, count, bound, k, lane);
 }
 
-__device__ __forceinline__ double dist2(const PhotonMapDev &m, uint64_t slot, double qx, double qy, double qz) {
-  const double dx = qx - m.px[slot], dy = qy - m.py[slot], dz = qz - m.pz[slot];   // v = query - photon; v.Dot(v)
+struct P3 { double x, y, z; };
+__device__ __forceinline__ P3 load_photon(const PhotonMapDev &m, uint32_t slot, bool valid) {
+  P3 p = {0.0, 0.0, 0.0};
+  if (valid) { p.x = m.px[slot]; p.y = m.py[slot]; p.z = m.pz[slot]; }
+  return p;
+}
+__device__ __forceinline__ double dist2(const P3 &p, double qx, double qy, double qz) {
+  const double dx = qx - p.x, dy = qy - p.y, dz = qz - p.z;                        // v = query - photon; v.Dot(v)
   return (dx * dx) + (dy * dy) + (dz * dz);
 }
+// lower bound (after rounding) of the squared distance from the query to anything inside a subtree box
+__device__ __forceinline__ double box_dist2(const double2 X, const double2 Y, const double2 Z, double qx, double qy, double qz) {
+  const double dx = fmax(fmax(X.x - qx, qx - X.y), 0.0), dy = fmax(fmax(Y.x - qy, qy - Y.y), 0.0),
+               dz = fmax(fmax(Z.x - qz, qz - Z.y), 0.0);
+  return ((dx * dx) + (dy * dy) + (dz * dz)) * 0.99999999999999;
+}
 
-template <int MINB>
-__global__ void __launch_bounds__(GI_GATHER_WARPS * 32, MINB)
-gather_kernel(PhotonMapDev m, const double *__restrict__ lut, const GiGatherQuery *__restrict__ queries, uint64_t nq,
-              GatherArgs ga, int32_t *idx_out, int32_t *count_out, double *rgb_out) {
+__global__ void __launch_bounds__(GI_GATHER_MAX_WARPS * 32, 1)
+gather_kernel(PhotonMapDev m, const double *__restrict__ lut, const GiGatherQuery *__restrict__ queries,
+              const uint32_t *__restrict__ order, uint64_t nq, GatherArgs ga, int32_t *idx_out, int32_t *count_out, double *rgb_out) {
   extern __shared__ double smem[];
   const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
   WarpBuf b; b.cap = ga.cap; b.orig = m.orig;
   b.limit = ga.cap - 32 < ga.k + ga.slack ? ga.cap - 32 : ga.k + ga.slack;
+  const int nwarps = blockDim.x >> 5;
   {
-    char *base = (char *)smem + (size_t)warp * ((size_t)ga.cap * 12 + GI_GATHER_WARP_EXTRA);
-    b.d2 = (double *)base; b.slot = (uint32_t *)(base + (size_t)ga.cap * 8);
-    b.hist = b.slot + ga.cap;
+    uint32_t base = (uint32_t)__cvta_generic_to_shared(smem) + (uint32_t)warp * (uint32_t)GI_WARP_BYTES(ga.cap, ga.key_rows);
+    asm volatile("" : "+r"(base));                          // opaque: keep it in a register instead of re-deriving it
+    b.a_d2 = base; b.a_slot = base + (uint32_t)ga.cap * 8u; b.a_hist = b.a_slot + (uint32_t)ga.cap * 4u;
+    b.a_keys = b.a_hist + GI_HIST_BINS * 4u;
   }
-  uint32_t *keys = b.hist + 256;                            // GI_MAX_GROUPS x 32, each lane reads only its own column
-  const uint32_t NONE = 0xffffffffu;
   const int k = ga.k;
   const uint64_t n = m.n;
   const uint32_t n32 = (uint32_t)n;
   const int jl = 31 - __clz(lane + 1);                      // relative depth of this lane's photon inside a group
-  const uint64_t warps_total = (uint64_t)gridDim.x * GI_GATHER_WARPS;
+  const int G = m.groups, gp = m.groups - 2;                // rows; gp = the row whose children are the bottom groups
+  const bool deep = m.hb > GI_GROUP_LEVELS;                 // bottom groups are 6 levels deep: a second round for level 6
+  const uint64_t warps_total = (uint64_t)gridDim.x * nwarps;
   const uint64_t nchunks = (nq + GI_GATHER_CHUNK - 1) / GI_GATHER_CHUNK;
   // Search radius carried from one query to the next: consecutive queries of a chunk are neighbouring pixels, so the
   // previous k-th distance (x guess_factor in area) is tried first and widened only if fewer than k photons are inside.
   double guess = ga.r2;
-  for (uint64_t chunk = (uint64_t)blockIdx.x * GI_GATHER_WARPS + warp; chunk < nchunks; chunk += warps_total)
-  for (uint64_t qi = chunk * GI_GATHER_CHUNK; qi < nq && qi < (chunk + 1) * GI_GATHER_CHUNK; qi++) {
-    // ---- query record: 17 doubles, one per lane, broadcast by shuffle
+  for (uint64_t chunk = (uint64_t)blockIdx.x * nwarps + warp; chunk < nchunks; chunk += warps_total)
+  for (uint64_t qs = chunk * GI_GATHER_CHUNK; qs < nq && qs < (chunk + 1) * GI_GATHER_CHUNK; qs++) {
+    // ---- query record: 17 doubles, one per lane, broadcast by shuffle.  order[] (optional) lists the queries along a
+    //      Morton curve, so that the queries of a warp and of a CTA are neighbours in space; results go to slot qi.
+    const uint64_t qi = order ? (uint64_t)order[qs] : qs;
     const double *qp = (const double *)(queries + qi);
     const double mine = lane < 17 ? qp[lane] : 0.0;
     const double qx = __shfl_sync(FULL, mine, 0), qy = __shfl_sync(FULL, mine, 1), qz = __shfl_sync(FULL, mine, 2);
@@ -205,47 +263,93 @@ gather_kernel(PhotonMapDev m, const double *__restrict__ lut, const GiGatherQuer
       double init = fmin(ga.r2, guess);
       while (true) {
         count = 0; bound = init;
-        // The tree is walked as a 32-ary tree of 5-level groups (photon_dev.h), depth first.  Row g of the walk keeps
-        // the root of the group it is in (st_root, held by lane g) and, per lane, the lower bound of the squared
-        // distance from the query to child group `lane` (keys[g][lane], float bits rounded down, NONE once visited
-        // or culled); children are entered nearest first and re-tested against the bound, which shrinks as the
-        // candidate buffer is cut.
+        // The tree is walked as a 32-ary tree of groups (photon_dev.h), depth first.
+        //   rows above gp: row g keeps the root of the group it is in (st_root, held by lane g) and, per lane, the
+        //     lower bound of the squared distance from the query to child group `lane` (keys[g][lane], float bits
+        //     rounded down, NONE once visited or culled); children are entered nearest first and re-tested against
+        //     the bound, which shrinks when the candidate buffer is cut.
+        //   row gp: the children are the bottom groups.  Those whose box touches the ball are scanned in slot order
+        //     (= space order), the photons of the next one being loaded while the current one is tested.
         uint32_t st_root = 0;
         int g = 0;
         uint32_t s = 0;
         bool enter = true;
-        while (true) {
+        if (G == 1) {                                                   // fewer than 64 photons: one group, no boxes
+          const uint32_t s1 = (uint32_t)lane + ((uint32_t)lane >= 31u ? n32 : 0u), s2 = 31u + (uint32_t)lane;
+          const P3 a = load_photon(m, s1, s1 < n32), c = load_photon(m, s2, deep && s2 < n32);
+          double d2 = dist2(a, qx, qy, qz);
+          append(b, count, bound, k, lane, s1 < n32 && d2 <= bound, d2, s1);
+          if (deep) { d2 = dist2(c, qx, qy, qz); append(b, count, bound, k, lane, s2 < n32 && d2 <= bound, d2, s2); }
+          g = -1;
+        }
+        while (g >= 0) {
           const int h = g == 0 ? m.h0 : GI_GROUP_LEVELS;
           if (enter) {
-            // ---- the group's photons: relative depth j occupies slots (s << j) + e, e in [2^j - 1, 2^(j+1) - 1)
-            {
-              const uint32_t slot = (s << jl) + (uint32_t)lane;
-              bool pred = false; double d2 = 0.0;
-              if (lane < (1 << h) - 1 && slot < n32) { d2 = dist2(m, slot, qx, qy, qz); pred = d2 <= bound; }
-              append(b, m, count, bound, k, lane, pred, d2, slot);
-            }
-            if (g + 1 >= m.groups) { if (--g < 0) break; enter = false; continue; }      // bottom row: back to the parent
-            // ---- the 32 child groups: one box test per lane
-            const uint32_t c = (((s + 1) << h) - 1) + (uint32_t)lane;
-            uint32_t key = NONE;
-            if (lane < (1 << h) && c < n32) {
+            // ---- issue both loads of the group: its photons (relative depth j occupies slots (s << j) + e,
+            //      e in [2^j - 1, 2^(j+1) - 1)) and the boxes of its 2^h children (one contiguous run of slots)
+            const uint32_t slot = (s << jl) + (uint32_t)lane;
+            const bool pv = lane < (1 << h) - 1 && slot < n32;
+            const uint32_t cbase = ((s + 1) << h) - 1;
+            const uint32_t c = cbase + (uint32_t)lane;
+            const bool cv = lane < (1 << h) && c < n32;
+            const P3 ph = load_photon(m, slot, pv);
+            double2 X = make_double2(0, 0), Y = X, Z = X;
+            if (cv) {
               const double2 *bx = m.gbox + 3 * ((size_t)m.gbox_off[g + 1] + (c - ((1u << m.glevel[g + 1]) - 1u)));
-              const double2 X = bx[0], Y = bx[1], Z = bx[2];
-              const double dx = fmax(fmax(X.x - qx, qx - X.y), 0.0), dy = fmax(fmax(Y.x - qy, qy - Y.y), 0.0),
-                           dz = fmax(fmax(Z.x - qz, qz - Z.y), 0.0);
-              const double bd = ((dx * dx) + (dy * dy) + (dz * dz)) * 0.99999999999999;   // rounding must not over-estimate
-              if (bd <= bound) key = __float_as_uint(__double2float_rd(bd));
+              X = bx[0]; Y = bx[1]; Z = bx[2];
             }
-            keys[g * 32 + lane] = key;
-            if (lane == g) st_root = s;
-            enter = false;
+            {
+              const double d2 = dist2(ph, qx, qy, qz);
+              append(b, count, bound, k, lane, pv && d2 <= bound, d2, slot);
+            }
+            const double bd = box_dist2(X, Y, Z, qx, qy, qz);
+            if (g == gp) {
+              // ---- bottom groups under this one
+              const float kf = cv ? __double2float_rd(bd) : INFINITY;
+              unsigned todo = __ballot_sync(FULL, (double)kf <= bound);
+              if (todo) {
+                uint32_t ls = cbase + (uint32_t)(__ffs(todo) - 1); todo &= todo - 1;
+                uint32_t s1 = (ls << jl) + (uint32_t)lane;
+                bool v1 = lane < 31 && s1 < n32;
+                P3 cur = load_photon(m, s1, v1);
+                while (true) {
+                  const uint32_t s2 = (((ls + 1) << GI_GROUP_LEVELS) - 1) + (uint32_t)lane;     // level 6 of the current group
+                  const bool v2 = deep && s2 < n32;
+                  const P3 low = load_photon(m, s2, v2);
+                  const bool more = todo != 0;
+                  uint32_t ls_n = 0, s1_n = 0; bool v1_n = false; P3 nxt = {0.0, 0.0, 0.0};
+                  if (more) {
+                    ls_n = cbase + (uint32_t)(__ffs(todo) - 1); todo &= todo - 1;
+                    s1_n = (ls_n << jl) + (uint32_t)lane; v1_n = lane < 31 && s1_n < n32;
+                    nxt = load_photon(m, s1_n, v1_n);
+                  }
+                  const double before = bound;
+                  double d2 = dist2(cur, qx, qy, qz);
+                  append(b, count, bound, k, lane, v1 && d2 <= bound, d2, s1);
+                  if (deep && __any_sync(FULL, v2)) {
+                    d2 = dist2(low, qx, qy, qz);
+                    append(b, count, bound, k, lane, v2 && d2 <= bound, d2, s2);
+                  }
+                  if (bound < before) todo &= __ballot_sync(FULL, (double)kf <= bound);       // the buffer was cut
+                  if (!more) break;
+                  ls = ls_n; s1 = s1_n; v1 = v1_n; cur = nxt;
+                }
+              }
+              --g; enter = false;
+              continue;                                                 // h belongs to the row just left
+            } else {
+              sts_u32(b.a_keys + 4u * (uint32_t)(g * 32 + lane), cv && bd <= bound ? __float_as_uint(__double2float_rd(bd)) : NONE);
+              if (lane == g) st_root = s;
+              enter = false;
+            }
           }
           // ---- nearest not yet visited child of row g
-          const uint32_t key = keys[g * 32 + lane];
+          const uint32_t ka = b.a_keys + 4u * (uint32_t)(g * 32 + lane);
+          const uint32_t key = lds_u32(ka);
           const uint32_t mn = __reduce_min_sync(FULL, key);
-          if (mn == NONE || (double)__uint_as_float(mn) > bound) { if (--g < 0) break; continue; }
+          if (mn == NONE || (double)__uint_as_float(mn) > bound) { --g; continue; }
           const int who = __ffs(__ballot_sync(FULL, key == mn)) - 1;
-          if (lane == who) keys[g * 32 + lane] = NONE;
+          if (lane == who) sts_u32(ka, NONE);
           const uint32_t root = __shfl_sync(FULL, st_root, g);
           s = (((root + 1) << h) - 1) + (uint32_t)who;
           g++; enter = true;
@@ -274,14 +378,14 @@ gather_kernel(PhotonMapDev m, const double *__restrict__ lut, const GiGatherQuer
       if (ga.filter == GI_FILTER_CONE) c1 = 1.0 / (ga.fk * sqrt(max_d2));
       else if (ga.filter == GI_FILTER_GAUSS) { c1 = exp(-ga.fb); c2 = 1.0 / (2.0 * max_d2); }
       for (int i = lane; i < found; i += 32) {
-        const uint2 sh = m.shade[b.slot[i]];
+        const uint2 sh = m.shade[b.slot(i)];
         const double *dir = lut + 3 * (size_t)(sh.y & 0xffffu);
         const double ix = dir[0], iy = dir[1], iz = dir[2];
         const double perp = (nx * ix) + (ny * iy) + (nz * iz);
         if ((cos_theta < 0 && perp < 0) || (cos_theta > 0 && perp > 0)) continue;
         const uint32_t e = sh.x >> 24;
         if (e == 0) { if (ga.filter == GI_FILTER_GAUSS) {
-            total_w += 1.0 - (1.0 - pow(c1, c2 * b.d2[i])) / (1.0 - c1); } continue; }
+            total_w += 1.0 - (1.0 - pow(c1, c2 * b.d2(i))) / (1.0 - c1); } continue; }
         const double inv = __longlong_as_double((long long)(e - 136 + 1023) << 52);   // ldexp(1.0, e - 128 - 8)
         double rgb[3] = {(double)(sh.x & 0xff) * inv, (double)((sh.x >> 8) & 0xff) * inv, (double)((sh.x >> 16) & 0xff) * inv};
         double cos_alpha = (bx * -ix) + (by * -iy) + (bz * -iz);
@@ -290,10 +394,10 @@ gather_kernel(PhotonMapDev m, const double *__restrict__ lut, const GiGatherQuer
         const double ap = fabs(perp);
         for (int c = 0; c < 3; c++) rgb[c] *= ap * kd[c] + pw * ks[c];
         if (ga.filter == GI_FILTER_CONE) {
-          const double w = 1.0 - c1 * sqrt(b.d2[i]);
+          const double w = 1.0 - c1 * sqrt(b.d2(i));
           for (int c = 0; c < 3; c++) rgb[c] *= w;
         } else if (ga.filter == GI_FILTER_GAUSS) {
-          const double w = 1.0 - (1.0 - pow(c1, c2 * b.d2[i])) / (1.0 - c1);
+          const double w = 1.0 - (1.0 - pow(c1, c2 * b.d2(i))) / (1.0 - c1);
           for (int c = 0; c < 3; c++) rgb[c] *= w;
           total_w += w;
         }
@@ -314,42 +418,42 @@ gather_kernel(PhotonMapDev m, const double *__restrict__ lut, const GiGatherQuer
     if (count_out && lane == 0) count_out[qi] = found;
     if (idx_out) {
       // ascending photon indices: put the index into the d2 column (exact in a double) and sort on it
-      for (int i = lane; i < b.cap; i += 32) b.d2[i] = i < found ? (double)b.orig[b.slot[i]] : INFINITY;
+      for (int i = lane; i < b.cap; i += 32) b.set_d2(i, i < found ? (double)b.orig[b.slot(i)] : INFINITY);
       __syncwarp();
       bitonic_sort(b, lane);
-      for (int i = lane; i < k; i += 32) idx_out[qi * (uint64_t)k + i] = i < found ? (int32_t)b.d2[i] : -1;
+      for (int i = lane; i < k; i += 32) idx_out[qi * (uint64_t)k + i] = i < found ? (int32_t)b.d2(i) : -1;
     }
     __syncwarp();
   }
 }
 
-template <int MINB>
-static cudaError_t launch_t(GiContext *ctx, const PhotonMapDev &m, const double *d_lut, const GiGatherQuery *d_q, uint64_t nq,
-                            const GatherArgs &ga, int32_t *d_idx, int32_t *d_count, double *d_rgb, cudaStream_t st) {
-  const size_t smem = (size_t)GI_GATHER_WARPS * ((size_t)ga.cap * 12 + GI_GATHER_WARP_EXTRA);
+// One CTA per SM (persistent, warps stride over chunks of consecutive queries): the warps of an SM then work on
+// neighbouring queries and share the kd-tree groups they read through L1.  As many warps as the candidate buffers
+// leave room for: 24 at the default estimate sizes (132 KB of shared memory, the rest of the 256 KB stays L1).
+cudaError_t launch_gather(GiContext *ctx, const PhotonMapDev &m, const double *d_lut, const GiGatherQuery *d_q,
+                          const uint32_t *d_order, uint64_t nq, const GatherArgs &ga_in, int32_t *d_idx, int32_t *d_count, double *d_rgb,
+                          cudaStream_t st) {
+  GatherArgs ga = ga_in;
+  ga.key_rows = m.groups > 2 ? m.groups - 2 : 0;
+  const size_t per_warp = GI_WARP_BYTES(ga.cap, ga.key_rows);
+  int warps = (int)((227 * 1024) / per_warp);
+  if (warps > GI_GATHER_MAX_WARPS) warps = GI_GATHER_MAX_WARPS;
+  if (ga.max_warps > 0 && warps > ga.max_warps) warps = ga.max_warps;
+  if (warps < 1) return cudaErrorInvalidValue;
+  const uint64_t nchunks = (nq + GI_GATHER_CHUNK - 1) / GI_GATHER_CHUNK;
+  if ((uint64_t)warps > nchunks) warps = (int)nchunks;
+  const size_t smem = (size_t)warps * per_warp;
   static size_t configured = 0;
   if (smem > configured) {
-    cudaError_t e = cudaFuncSetAttribute(gather_kernel<MINB>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
+    cudaError_t e = cudaFuncSetAttribute(gather_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
     if (e != cudaSuccess) return e;
     configured = smem;
   }
-  int per_sm = 1;
-  cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, gather_kernel<MINB>, GI_GATHER_WARPS * 32, smem);
-  if (per_sm < 1) per_sm = 1;
-  const uint64_t nchunks = (nq + GI_GATHER_CHUNK - 1) / GI_GATHER_CHUNK;
-  uint64_t want = (nchunks + GI_GATHER_WARPS - 1) / GI_GATHER_WARPS;
-  uint64_t cap = (uint64_t)ctx->sm_count * per_sm;         // persistent: one resident wave, warps stride over chunks
-  unsigned grid = (unsigned)(want < cap ? want : cap);
-  gather_kernel<MINB><<<grid, GI_GATHER_WARPS * 32, smem, st>>>(m, d_lut, d_q, nq, ga, d_idx, d_count, d_rgb);
+  const uint64_t want = (nchunks + warps - 1) / warps;
+  const unsigned grid = (unsigned)(want < (uint64_t)ctx->sm_count ? want : (uint64_t)ctx->sm_count);
+  gather_kernel<<<grid, warps * 32, smem, st>>>(m, d_lut, d_q, d_order, nq, ga, d_idx, d_count, d_rgb);
   ctx->launches++;
   return cudaGetLastError();
-}
-
-cudaError_t launch_gather(GiContext *ctx, const PhotonMapDev &m, const double *d_lut, const GiGatherQuery *d_q,
-                          uint64_t nq, const GatherArgs &ga, int32_t *d_idx, int32_t *d_count, double *d_rgb,
-                          cudaStream_t st) {
-  if (ga.min_blocks >= 4) return launch_t<4>(ctx, m, d_lut, d_q, nq, ga, d_idx, d_count, d_rgb, st);
-  return launch_t<3>(ctx, m, d_lut, d_q, nq, ga, d_idx, d_count, d_rgb, st);
 }
 
 }  // namespace gi

@@ -21,6 +21,8 @@
 #include <cub/device/device_radix_sort.cuh>
 #include <cuda_runtime.h>
 #include <float.h>
+#include <math.h>
+#include <string.h>
 #include <stdint.h>
 #include "context.h"
 #include "kdtree_build.h"
@@ -170,12 +172,15 @@ __global__ void group_box_kernel(PhotonMapDev m, int g, double2 *gbox) {
   const int j = 31 - __clz(lane + 1);
   const uint64_t slot = (r << j) + (uint64_t)lane;
   if (lane < 31 && slot < m.n) { lo[0] = hi[0] = m.px[slot]; lo[1] = hi[1] = m.py[slot]; lo[2] = hi[2] = m.pz[slot]; }
+  const uint64_t c = ((r + 1) << GI_GROUP_LEVELS) - 1 + (uint64_t)lane;     // relative depth 5 below r
   if (g + 1 < m.groups) {
-    const uint64_t c = ((r + 1) << GI_GROUP_LEVELS) - 1 + (uint64_t)lane;
     if (c < m.n) {
       const double2 *b = gbox + 3 * ((size_t)m.gbox_off[g + 1] + (c - (((uint64_t)1 << m.glevel[g + 1]) - 1)));
       for (int a = 0; a < 3; a++) { lo[a] = fmin(lo[a], b[a].x); hi[a] = fmax(hi[a], b[a].y); }
     }
+  } else if (m.hb > GI_GROUP_LEVELS && c < m.n) {                            // bottom row, six levels deep
+    lo[0] = fmin(lo[0], m.px[c]); hi[0] = fmax(hi[0], m.px[c]); lo[1] = fmin(lo[1], m.py[c]); hi[1] = fmax(hi[1], m.py[c]);
+    lo[2] = fmin(lo[2], m.pz[c]); hi[2] = fmax(hi[2], m.pz[c]);
   }
   for (int a = 0; a < 3; a++)
     for (int o = 16; o > 0; o >>= 1) {
@@ -236,8 +241,13 @@ cudaError_t build_photon_map(GiContext *ctx, PhotonMapStore &m, uint64_t n) {
   CKB(cudaGetLastError());
   d.n = n; d.levels = L; d.px = px; d.py = py; d.pz = pz; d.node = node; d.shade = shade; d.orig = orig;
   // rows of 5-level groups (photon_dev.h) and their subtree boxes, bottom row first
-  d.groups = (L + GI_GROUP_LEVELS - 1) / GI_GROUP_LEVELS;
-  d.h0 = L - GI_GROUP_LEVELS * (d.groups - 1);
+  {
+    const uint64_t last_cap = (uint64_t)1 << (L - 1), last = n - (last_cap - 1);      // slots / photons on the last level
+    d.hb = L <= GI_GROUP_LEVELS ? L : (2 * last < last_cap ? GI_GROUP_LEVELS + 1 : GI_GROUP_LEVELS);
+    const int rest = L - d.hb;                                                        // levels above the bottom row
+    d.groups = 1 + (rest + GI_GROUP_LEVELS - 1) / GI_GROUP_LEVELS;
+    d.h0 = d.groups == 1 ? d.hb : rest - GI_GROUP_LEVELS * (d.groups - 2);
+  }
   for (int g = 0; g < d.groups; g++) {
     d.glevel[g] = g == 0 ? 0 : d.h0 + GI_GROUP_LEVELS * (g - 1);
     d.gbox_off[g] = (uint32_t)n_box;
@@ -252,7 +262,17 @@ cudaError_t build_photon_map(GiContext *ctx, PhotonMapStore &m, uint64_t n) {
     ctx->launches++;
   }
   CKB(cudaGetLastError());
-  CKB(cudaStreamSynchronize(st));
+  {
+    // bounding box of the map (query_order.cu): the root's tight float bounds, one ulp outwards
+    uint32_t hb[6];
+    CKB(cudaMemcpyAsync(hb, bounds, sizeof(hb), cudaMemcpyDeviceToHost, st));
+    CKB(cudaStreamSynchronize(st));
+    for (int a = 0; a < 6; a++) {
+      const uint32_t o = hb[a], u = (o & 0x80000000u) ? (o & 0x7fffffffu) : ~o;
+      float f; memcpy(&f, &u, 4);
+      m.bbox[a] = (double)nextafterf(f, a < 3 ? -INFINITY : INFINITY);
+    }
+  }
   m.dev = d;
   m.built = true;
   px = py = pz = nullptr; node = shade = nullptr; orig = nullptr; gbox = nullptr;

@@ -9,8 +9,10 @@
 // [(s << j) + 2^j - 1, ...) of 2^j slots.  The search (gather.cu) therefore reads the tree in GROUPS of five levels:
 // the 31 photons of a group are 5 contiguous runs (one warp-wide round of distance tests) and its 32 child groups are
 // one contiguous run of slots whose tight FP64 bounding boxes (gbox) are tested by the 32 lanes at once -- the
-// binary tree is walked as a 32-ary one.  Rows of group roots sit at tree levels glevel[g]; the top group takes the
-// remainder (h0 = levels - 5 (groups - 1) in [1, 5]) so that every other group is exactly five levels deep.
+// binary tree is walked as a 32-ary one.  Rows of group roots sit at tree levels glevel[g].  The bottom row is hb = 5
+// or 6 levels deep: the last level of a left-balanced tree is only partly filled, and when it is less than half full
+// most 5-level bottom groups would hold 15 photons instead of 31, so the last level is then attached to the row above
+// it as a second round of at most 32 photons.  The top group takes the remainder (h0 in [1, 5]).
 #pragma once
 #include <stdint.h>
 #if defined(__CUDACC__)
@@ -30,7 +32,7 @@ struct PhotonMapDev {
   const uint2 *node;              /* heap order: x = float bits of the split coordinate, y = split axis (0..2) */
   const double2 *gbox;            /* tight box of the subtree below every group root of rows 1..groups-1, row-major:   */
                                   /* 3 x double2 {lo, hi} for x, y, z = 48 B; box of slot s in row g: gbox_off[g] + s - (2^glevel[g] - 1) */
-  int32_t groups, h0;             /* rows of groups; depth of the top group */
+  int32_t groups, h0, hb;         /* rows of groups; depth of the top group; depth of the bottom-row groups (one row: groups = 1, hb = levels) */
   int32_t glevel[GI_MAX_GROUPS];  /* tree level of the group roots of row g (glevel[0] = 0) */
   uint32_t gbox_off[GI_MAX_GROUPS];
   const uint2 *shade;             /* heap order: x = rgbe bytes (r | g<<8 | b<<16 | e<<24), y = direction code */
