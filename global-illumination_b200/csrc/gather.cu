@@ -81,7 +81,9 @@ __device__ __noinline__ void bitonic_sort(const WarpBuf &b, int lane) {
 
 // slow exact path (heavy exact ties, or a zero bound): every candidate counts the candidates that precede it in
 // (d2, photon index) order -- O(count^2 / 32) -- and the k first are kept.  Keep flags go through the histogram words.
-__device__ __noinline__ void rank_select(const WarpBuf &b, int &count, double &bound, int k, int lane) {
+struct Sel { double bound; int count; };           // search state: squared search radius, candidates held
+
+__device__ __noinline__ Sel rank_select(const WarpBuf b, int count, double bound, int k, int lane) {
   for (int base = 0; base < count; base += 32) {
     const int i = base + lane;
     const bool live = i < count;
@@ -111,15 +113,16 @@ __device__ __noinline__ void rank_select(const WarpBuf &b, int &count, double &b
     __syncwarp();
   }
   for (int o = 16; o > 0; o >>= 1) mx = fmax(mx, __shfl_xor_sync(FULL, mx, o));
-  count = newcount; bound = fmin(bound, mx);
+  Sel r; r.count = newcount; r.bound = fmin(bound, mx);
+  return r;
 }
 
 // Exact cut of the candidate buffer to the k smallest by (d2, orig).  Requires count > k.
 // A 128-bin histogram of d2 / bound locates the bin B that holds the k-th candidate; bins below B are kept whole,
 // and inside B (a handful of candidates, since surface photons are uniform in d2) each lane ranks one candidate
 // against the others by shuffles.  The bound becomes the largest kept d2.
-__device__ __noinline__ void cut(const WarpBuf &b, int &count, double &bound, int k, int lane) {
-  if (!(bound > 0.0)) { rank_select(b, count, bound, k, lane); return; }
+__device__ __noinline__ Sel cut(const WarpBuf b, int count, double bound, int k, int lane) {
+  if (!(bound > 0.0)) return rank_select(b, count, bound, k, lane);
   for (int i = lane; i < GI_HIST_BINS; i += 32) b.set_hist(i, 0);
   __syncwarp();
   const double scale = (double)GI_HIST_BINS / bound;
@@ -145,7 +148,7 @@ __device__ __noinline__ void cut(const WarpBuf &b, int &count, double &bound, in
   const int need = k - below;                             // candidates to keep from bin B, 1 <= need <= m
   __syncwarp();
   if (need < m) {
-    if (m > 32) { rank_select(b, count, bound, k, lane); return; }
+    if (m > 32) return rank_select(b, count, bound, k, lane);
     int c = 0;                                            // list the members of bin B in hist[0..m)
     for (int base = 0; base < count; base += 32) {
       const int i = base + lane;
@@ -183,12 +186,13 @@ __device__ __noinline__ void cut(const WarpBuf &b, int &count, double &bound, in
     __syncwarp();
   }
   for (int o = 16; o > 0; o >>= 1) mx = fmax(mx, __shfl_xor_sync(FULL, mx, o));
-  count = newcount; bound = fmin(bound, mx);
+  Sel r; r.count = newcount; r.bound = fmin(bound, mx);
+  return r;
 }
 
 // after the traversal: exactly the k nearest (or everything found, if fewer); bound = largest kept d2 when k are held
 __device__ __forceinline__ void finish(const WarpBuf &b, int &count, double &bound, int k, int lane) {
-  if (count > k) { cut(b, count, bound, k, lane); return; }
+  if (count > k) { const Sel r = cut(b, count, bound, k, lane); count = r.count; bound = r.bound; return; }
   if (count < k) return;
   double mx = 0.0;
   for (int i = lane; i < count; i += 32) mx = fmax(mx, b.d2(i));
@@ -196,20 +200,28 @@ __device__ __forceinline__ void finish(const WarpBuf &b, int &count, double &bou
   bound = fmin(bound, mx);
 }
 
-__device__ __forceinline__ void append(const WarpBuf &b, int &count, double &bound, int k, int lane, bool pred, double d2,
-                                       uint32_t slot) {
+__device__ __forceinline__ void append(const WarpBuf &b, int &count, double &bound, int k, int lane, uint32_t lt_mask, bool pred,
+                                       double d2, uint32_t slot) {
   const unsigned mask = __ballot_sync(FULL, pred);
   if (mask == 0) return;
-  const int pos = count + __popc(mask & ((1u << lane) - 1u));
+  const int pos = count + __popc(mask & lt_mask);
   if (pred) { b.set_d2(pos, d2); b.set_slot(pos, slot); }
   count += __popc(mask);
   __syncwarp();
-  if (count > b.limit) cut(b, count, bound, k, lane);
+  if (count > b.limit) { const Sel r = cut(b, count, bound, k, lane); count = r.count; bound = r.bound; }
 }
 
 struct P3 { double x, y, z; };
+// photons of a group: block gi of gpos, entry `lane` (+inf where the group has no photon: the distance test fails)
+__device__ __forceinline__ P3 load_group(const double *__restrict__ gpos_lane, uint32_t gi) {
+  const double *p = gpos_lane + (size_t)gi * 96;
+  P3 r; r.x = p[0]; r.y = p[32]; r.z = p[64];
+  return r;
+}
+// level 6 of a bottom group: a contiguous run of heap slots
 __device__ __forceinline__ P3 load_photon(const PhotonMapDev &m, uint32_t slot, bool valid) {
-  P3 p = {0.0, 0.0, 0.0};
+  const double INF = __longlong_as_double(0x7ff0000000000000ll);
+  P3 p = {INF, INF, INF};
   if (valid) { p.x = m.px[slot]; p.y = m.py[slot]; p.z = m.pz[slot]; }
   return p;
 }
@@ -242,8 +254,11 @@ gather_kernel(PhotonMapDev m, const double *__restrict__ lut, const GiGatherQuer
   const uint64_t n = m.n;
   const uint32_t n32 = (uint32_t)n;
   const int jl = 31 - __clz(lane + 1);                      // relative depth of this lane's photon inside a group
+  const uint32_t lt_mask = (1u << lane) - 1u;
+  const double *gpos_lane = m.gpos + lane;
   const int G = m.groups, gp = m.groups - 2;                // rows; gp = the row whose children are the bottom groups
   const bool deep = m.hb > GI_GROUP_LEVELS;                 // bottom groups are 6 levels deep: a second round for level 6
+  const uint32_t bottom_delta = G > 1 ? m.goff[G - 1] - ((1u << m.glevel[G - 1]) - 1u) : 0u;   // bottom group index - root slot
   const uint64_t warps_total = (uint64_t)gridDim.x * nwarps;
   const uint64_t nchunks = (nq + GI_GATHER_CHUNK - 1) / GI_GATHER_CHUNK;
   // Search radius carried from one query to the next: consecutive queries of a chunk are neighbouring pixels, so the
@@ -275,32 +290,30 @@ gather_kernel(PhotonMapDev m, const double *__restrict__ lut, const GiGatherQuer
         uint32_t s = 0;
         bool enter = true;
         if (G == 1) {                                                   // fewer than 64 photons: one group, no boxes
-          const uint32_t s1 = (uint32_t)lane + ((uint32_t)lane >= 31u ? n32 : 0u), s2 = 31u + (uint32_t)lane;
-          const P3 a = load_photon(m, s1, s1 < n32), c = load_photon(m, s2, deep && s2 < n32);
+          const uint32_t s1 = (uint32_t)lane, s2 = 31u + (uint32_t)lane;
+          const P3 a = load_group(gpos_lane, 0), c = load_photon(m, s2, deep && s2 < n32);
           double d2 = dist2(a, qx, qy, qz);
-          append(b, count, bound, k, lane, s1 < n32 && d2 <= bound, d2, s1);
-          if (deep) { d2 = dist2(c, qx, qy, qz); append(b, count, bound, k, lane, s2 < n32 && d2 <= bound, d2, s2); }
+          append(b, count, bound, k, lane, lt_mask, d2 <= bound, d2, s1);
+          if (deep) { d2 = dist2(c, qx, qy, qz); append(b, count, bound, k, lane, lt_mask, d2 <= bound, d2, s2); }
           g = -1;
         }
         while (g >= 0) {
           const int h = g == 0 ? m.h0 : GI_GROUP_LEVELS;
           if (enter) {
-            // ---- issue both loads of the group: its photons (relative depth j occupies slots (s << j) + e,
-            //      e in [2^j - 1, 2^(j+1) - 1)) and the boxes of its 2^h children (one contiguous run of slots)
-            const uint32_t slot = (s << jl) + (uint32_t)lane;
-            const bool pv = lane < (1 << h) - 1 && slot < n32;
+            // ---- issue both loads of the group: its photons and the boxes of its 2^h children (one contiguous run
+            //      of slots in row g + 1)
             const uint32_t cbase = ((s + 1) << h) - 1;
             const uint32_t c = cbase + (uint32_t)lane;
             const bool cv = lane < (1 << h) && c < n32;
-            const P3 ph = load_photon(m, slot, pv);
+            const P3 ph = load_group(gpos_lane, s + (m.goff[g] - ((1u << m.glevel[g]) - 1u)));
             double2 X = make_double2(0, 0), Y = X, Z = X;
             if (cv) {
-              const double2 *bx = m.gbox + 3 * ((size_t)m.gbox_off[g + 1] + (c - ((1u << m.glevel[g + 1]) - 1u)));
+              const double2 *bx = m.gbox + 3 * (size_t)(c + (m.goff[g + 1] - ((1u << m.glevel[g + 1]) - 1u)));
               X = bx[0]; Y = bx[1]; Z = bx[2];
             }
             {
               const double d2 = dist2(ph, qx, qy, qz);
-              append(b, count, bound, k, lane, pv && d2 <= bound, d2, slot);
+              append(b, count, bound, k, lane, lt_mask, d2 <= bound, d2, (s << jl) + (uint32_t)lane);
             }
             const double bd = box_dist2(X, Y, Z, qx, qy, qz);
             if (g == gp) {
@@ -309,30 +322,28 @@ gather_kernel(PhotonMapDev m, const double *__restrict__ lut, const GiGatherQuer
               unsigned todo = __ballot_sync(FULL, (double)kf <= bound);
               if (todo) {
                 uint32_t ls = cbase + (uint32_t)(__ffs(todo) - 1); todo &= todo - 1;
-                uint32_t s1 = (ls << jl) + (uint32_t)lane;
-                bool v1 = lane < 31 && s1 < n32;
-                P3 cur = load_photon(m, s1, v1);
+                P3 cur = load_group(gpos_lane, ls + bottom_delta);
                 while (true) {
                   const uint32_t s2 = (((ls + 1) << GI_GROUP_LEVELS) - 1) + (uint32_t)lane;     // level 6 of the current group
-                  const bool v2 = deep && s2 < n32;
-                  const P3 low = load_photon(m, s2, v2);
+                  const bool any2 = deep && (((ls + 1) << GI_GROUP_LEVELS) - 1) < n32;          // uniform
+                  P3 low = {0.0, 0.0, 0.0};
+                  if (any2) low = load_photon(m, s2, s2 < n32);
                   const bool more = todo != 0;
-                  uint32_t ls_n = 0, s1_n = 0; bool v1_n = false; P3 nxt = {0.0, 0.0, 0.0};
+                  uint32_t ls_n = 0; P3 nxt = {0.0, 0.0, 0.0};
                   if (more) {
                     ls_n = cbase + (uint32_t)(__ffs(todo) - 1); todo &= todo - 1;
-                    s1_n = (ls_n << jl) + (uint32_t)lane; v1_n = lane < 31 && s1_n < n32;
-                    nxt = load_photon(m, s1_n, v1_n);
+                    nxt = load_group(gpos_lane, ls_n + bottom_delta);
                   }
                   const double before = bound;
                   double d2 = dist2(cur, qx, qy, qz);
-                  append(b, count, bound, k, lane, v1 && d2 <= bound, d2, s1);
-                  if (deep && __any_sync(FULL, v2)) {
+                  append(b, count, bound, k, lane, lt_mask, d2 <= bound, d2, (ls << jl) + (uint32_t)lane);
+                  if (any2) {
                     d2 = dist2(low, qx, qy, qz);
-                    append(b, count, bound, k, lane, v2 && d2 <= bound, d2, s2);
+                    append(b, count, bound, k, lane, lt_mask, d2 <= bound, d2, s2);
                   }
                   if (bound < before) todo &= __ballot_sync(FULL, (double)kf <= bound);       // the buffer was cut
                   if (!more) break;
-                  ls = ls_n; s1 = s1_n; v1 = v1_n; cur = nxt;
+                  ls = ls_n; cur = nxt;
                 }
               }
               --g; enter = false;

@@ -158,24 +158,29 @@ __global__ void finalize_kernel(const GiPhoton *__restrict__ ph, uint64_t n, con
   node[i] = make_uint2(__float_as_uint(split[i]), axis[i]);
 }
 
-// Tight FP64 box of the subtree below every group root of row g (photon_dev.h): one warp per root takes the min / max
-// over the group's 31 photons and, unless this is the bottom row, over the boxes of its 32 child groups (row g + 1,
-// filled by the previous launch).
-__global__ void group_box_kernel(PhotonMapDev m, int g, double2 *gbox) {
+// Per group of row g (photon_dev.h): the position block gpos (x[32], y[32], z[32], +inf where the group has no photon)
+// and the tight FP64 box of the subtree below its root = min / max over the group's photons, over the boxes of its 32
+// child groups (row g + 1, filled by the previous launch) and, in a six-level bottom row, over its level-6 photons.
+// One warp per group.
+__global__ void group_kernel(PhotonMapDev m, int g, double *gpos, double2 *gbox) {
   const uint64_t w = ((uint64_t)blockIdx.x * blockDim.x + threadIdx.x) >> 5;
   const int lane = threadIdx.x & 31;
   const uint64_t first = ((uint64_t)1 << m.glevel[g]) - 1;
   const uint64_t r = first + w;
   if (r >= m.n || w >= ((uint64_t)1 << m.glevel[g])) return;
+  const int h = m.groups == 1 ? (m.hb < GI_GROUP_LEVELS ? m.hb : GI_GROUP_LEVELS) : (g == 0 ? m.h0 : GI_GROUP_LEVELS);
   const double INF = __longlong_as_double(0x7ff0000000000000ll);
   double lo[3] = {INF, INF, INF}, hi[3] = {-INF, -INF, -INF};
   const int j = 31 - __clz(lane + 1);
   const uint64_t slot = (r << j) + (uint64_t)lane;
-  if (lane < 31 && slot < m.n) { lo[0] = hi[0] = m.px[slot]; lo[1] = hi[1] = m.py[slot]; lo[2] = hi[2] = m.pz[slot]; }
-  const uint64_t c = ((r + 1) << GI_GROUP_LEVELS) - 1 + (uint64_t)lane;     // relative depth 5 below r
+  double p[3] = {INF, INF, INF};
+  if (lane < (1 << h) - 1 && slot < m.n) { p[0] = m.px[slot]; p[1] = m.py[slot]; p[2] = m.pz[slot]; for (int a = 0; a < 3; a++) lo[a] = hi[a] = p[a]; }
+  const size_t gi = (size_t)m.goff[g] + w;
+  for (int a = 0; a < 3; a++) gpos[gi * 96 + 32 * a + lane] = p[a];
+  const uint64_t c = ((r + 1) << h) - 1 + (uint64_t)lane;                    // relative depth h below r
   if (g + 1 < m.groups) {
-    if (c < m.n) {
-      const double2 *b = gbox + 3 * ((size_t)m.gbox_off[g + 1] + (c - (((uint64_t)1 << m.glevel[g + 1]) - 1)));
+    if (lane < (1 << h) && c < m.n) {
+      const double2 *b = gbox + 3 * ((size_t)m.goff[g + 1] + (c - (((uint64_t)1 << m.glevel[g + 1]) - 1)));
       for (int a = 0; a < 3; a++) { lo[a] = fmin(lo[a], b[a].x); hi[a] = fmax(hi[a], b[a].y); }
     }
   } else if (m.hb > GI_GROUP_LEVELS && c < m.n) {                            // bottom row, six levels deep
@@ -188,7 +193,7 @@ __global__ void group_box_kernel(PhotonMapDev m, int g, double2 *gbox) {
       hi[a] = fmax(hi[a], __shfl_xor_sync(0xffffffffu, hi[a], o));
     }
   if (lane == 0) {
-    double2 *b = gbox + 3 * ((size_t)m.gbox_off[g] + w);
+    double2 *b = gbox + 3 * gi;
     for (int a = 0; a < 3; a++) b[a] = make_double2(lo[a], hi[a]);
   }
 }
@@ -204,7 +209,7 @@ cudaError_t build_photon_map(GiContext *ctx, PhotonMapStore &m, uint64_t n) {
   uint32_t *heap_photon = nullptr, *bounds = nullptr; float *split = nullptr; uint8_t *axis = nullptr;
   void *tmp = nullptr; size_t tmp_bytes = 0;
   double *px = nullptr, *py = nullptr, *pz = nullptr; uint2 *node = nullptr, *shade = nullptr; uint32_t *orig = nullptr;
-  double2 *gbox = nullptr; uint64_t n_box = 0;
+  double2 *gbox = nullptr; double *gpos = nullptr; uint64_t n_groups = 0;
   PhotonMapDev d{};
   const int B = 256;
   const unsigned G = (unsigned)((n + B - 1) / B);
@@ -250,15 +255,17 @@ cudaError_t build_photon_map(GiContext *ctx, PhotonMapStore &m, uint64_t n) {
   }
   for (int g = 0; g < d.groups; g++) {
     d.glevel[g] = g == 0 ? 0 : d.h0 + GI_GROUP_LEVELS * (g - 1);
-    d.gbox_off[g] = (uint32_t)n_box;
-    if (g > 0) { const uint64_t first = ((uint64_t)1 << d.glevel[g]) - 1; n_box += n - first < first + 1 ? n - first : first + 1; }
+    d.goff[g] = (uint32_t)n_groups;
+    const uint64_t first = ((uint64_t)1 << d.glevel[g]) - 1;
+    n_groups += n - first < first + 1 ? n - first : first + 1;
   }
-  CKB(cudaMalloc(&gbox, 48 * (n_box ? n_box : 1)));
-  d.gbox = gbox;
-  for (int g = d.groups - 1; g >= 1; g--) {
+  CKB(cudaMalloc(&gbox, 48 * n_groups));
+  CKB(cudaMalloc(&gpos, 768 * n_groups));
+  d.gbox = gbox; d.gpos = gpos;
+  for (int g = d.groups - 1; g >= 0; g--) {
     const uint64_t first = ((uint64_t)1 << d.glevel[g]) - 1;
     const uint64_t rows = n - first < first + 1 ? n - first : first + 1;
-    group_box_kernel<<<(unsigned)((rows * 32 + B - 1) / B), B, 0, st>>>(d, g, gbox);
+    group_kernel<<<(unsigned)((rows * 32 + B - 1) / B), B, 0, st>>>(d, g, gpos, gbox);
     ctx->launches++;
   }
   CKB(cudaGetLastError());
@@ -275,11 +282,11 @@ cudaError_t build_photon_map(GiContext *ctx, PhotonMapStore &m, uint64_t n) {
   }
   m.dev = d;
   m.built = true;
-  px = py = pz = nullptr; node = shade = nullptr; orig = nullptr; gbox = nullptr;
+  px = py = pz = nullptr; node = shade = nullptr; orig = nullptr; gbox = nullptr; gpos = nullptr;
 done:
   for (int k = 0; k < 2; k++) { cudaFree(keys[k]); cudaFree(vals[k]); }
   cudaFree(heap_photon); cudaFree(split); cudaFree(bounds); cudaFree(axis); cudaFree(tmp);
-  cudaFree(px); cudaFree(py); cudaFree(pz); cudaFree(node); cudaFree(shade); cudaFree(orig); cudaFree(gbox);
+  cudaFree(px); cudaFree(py); cudaFree(pz); cudaFree(node); cudaFree(shade); cudaFree(orig); cudaFree(gbox); cudaFree(gpos);
   return err;
 }
 

@@ -30,11 +30,13 @@ struct PhotonMapDev {
   int32_t levels;                 /* floor(log2 n) + 1 */
   const double *px, *py, *pz;     /* heap order */
   const uint2 *node;              /* heap order: x = float bits of the split coordinate, y = split axis (0..2) */
-  const double2 *gbox;            /* tight box of the subtree below every group root of rows 1..groups-1, row-major:   */
-                                  /* 3 x double2 {lo, hi} for x, y, z = 48 B; box of slot s in row g: gbox_off[g] + s - (2^glevel[g] - 1) */
+  /* groups (see above), numbered row by row: group of root slot s in row g has index goff[g] + s - (2^glevel[g] - 1) */
+  const double *gpos;             /* per group 96 doubles: x[32], y[32], z[32] of its (up to) 31 photons, lane order = slot    */
+                                  /* order within the group; unused entries hold +inf, so their distance test fails by itself */
+  const double2 *gbox;            /* per group 3 x double2 {lo, hi} for x, y, z: tight box of the whole subtree below its root */
   int32_t groups, h0, hb;         /* rows of groups; depth of the top group; depth of the bottom-row groups (one row: groups = 1, hb = levels) */
   int32_t glevel[GI_MAX_GROUPS];  /* tree level of the group roots of row g (glevel[0] = 0) */
-  uint32_t gbox_off[GI_MAX_GROUPS];
+  uint32_t goff[GI_MAX_GROUPS];   /* index of the first group of row g */
   const uint2 *shade;             /* heap order: x = rgbe bytes (r | g<<8 | b<<16 | e<<24), y = direction code */
   const uint32_t *orig;           /* heap order -> index in the order the photons were loaded / traced */
 };
