@@ -212,7 +212,7 @@ int gi_gather_batch_device(GiContext *ctx, int map, const GiGatherQuery *d_queri
   if (!lut) return 1;
   GatherArgs ga;
   ga.k = k; ga.filter = filter; ga.r2 = r * r;
-  // candidate slots: k + half as many again (at least 96) + one round of 32 in flight; the index output sorts the
+  // candidate slots: k + half as many again (at least 96) + 32; the index output sorts the
   // buffer with a bitonic network and needs a power of two
   ga.cap = d_idx ? (pow2ceil(2 * k) < 256 ? 256 : pow2ceil(2 * k)) : ((k + (k / 2 > 96 ? k / 2 : 96) + 31) / 32) * 32 + 32;
   ga.fa = params ? params->filter_const_a : 0.918; ga.fb = params ? params->filter_const_b : 1.953;
@@ -227,7 +227,7 @@ int gi_gather_batch_device(GiContext *ctx, int map, const GiGatherQuery *d_queri
   cudaStream_t st = (cudaStream_t)stream;      // NULL = the CUDA default stream, as documented
   // batches are walked along a Morton curve (query_order.cu); small ones are not worth the sort
   const uint32_t *order = nullptr;
-  bool sort = n >= 4096 && m.dev.n >= 4096;
+  bool sort = n >= 4096;
   if (const char *e = getenv("GI_SORT_QUERIES")) sort = atoi(e) != 0;
   if (sort) {
     bool failed = false;

@@ -236,13 +236,14 @@ __device__ __forceinline__ double box_dist2(const double2 X, const double2 Y, co
   return ((dx * dx) + (dy * dy) + (dz * dz)) * 0.99999999999999;
 }
 
+template <bool DEEP>          // DEEP: bottom groups are 6 levels deep (m.hb == 6), a second round of 32 photons
 __global__ void __launch_bounds__(GI_GATHER_MAX_WARPS * 32, 1)
 gather_kernel(PhotonMapDev m, const double *__restrict__ lut, const GiGatherQuery *__restrict__ queries,
               const uint32_t *__restrict__ order, uint64_t nq, GatherArgs ga, int32_t *idx_out, int32_t *count_out, double *rgb_out) {
   extern __shared__ double smem[];
   const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
   WarpBuf b; b.cap = ga.cap; b.orig = m.orig;
-  b.limit = ga.cap - 32 < ga.k + ga.slack ? ga.cap - 32 : ga.k + ga.slack;
+  { const int room = ga.cap - (DEEP ? 64 : 32); b.limit = room < ga.k + ga.slack ? room : ga.k + ga.slack; }   // 32 (64) arrive at once
   const int nwarps = blockDim.x >> 5;
   {
     uint32_t base = (uint32_t)__cvta_generic_to_shared(smem) + (uint32_t)warp * (uint32_t)GI_WARP_BYTES(ga.cap, ga.key_rows);
@@ -257,7 +258,7 @@ gather_kernel(PhotonMapDev m, const double *__restrict__ lut, const GiGatherQuer
   const uint32_t lt_mask = (1u << lane) - 1u;
   const double *gpos_lane = m.gpos + lane;
   const int G = m.groups, gp = m.groups - 2;                // rows; gp = the row whose children are the bottom groups
-  const bool deep = m.hb > GI_GROUP_LEVELS;                 // bottom groups are 6 levels deep: a second round for level 6
+  const bool deep = DEEP;
   const uint32_t bottom_delta = G > 1 ? m.goff[G - 1] - ((1u << m.glevel[G - 1]) - 1u) : 0u;   // bottom group index - root slot
   const uint64_t warps_total = (uint64_t)gridDim.x * nwarps;
   const uint64_t nchunks = (nq + GI_GATHER_CHUNK - 1) / GI_GATHER_CHUNK;
@@ -317,33 +318,40 @@ gather_kernel(PhotonMapDev m, const double *__restrict__ lut, const GiGatherQuer
             }
             const double bd = box_dist2(X, Y, Z, qx, qy, qz);
             if (g == gp) {
-              // ---- bottom groups under this one
+              // ---- bottom groups under this one: branch-light loop, the next group's block is always in flight
               const float kf = cv ? __double2float_rd(bd) : INFINITY;
               unsigned todo = __ballot_sync(FULL, (double)kf <= bound);
               if (todo) {
                 uint32_t ls = cbase + (uint32_t)(__ffs(todo) - 1); todo &= todo - 1;
+                uint32_t s2 = (((ls + 1) << GI_GROUP_LEVELS) - 1) + (uint32_t)lane;             // level 6 of the current group
                 P3 cur = load_group(gpos_lane, ls + bottom_delta);
+                P3 low = {0.0, 0.0, 0.0};
+                if (DEEP) low = load_photon(m, s2, s2 < n32);
                 while (true) {
-                  const uint32_t s2 = (((ls + 1) << GI_GROUP_LEVELS) - 1) + (uint32_t)lane;     // level 6 of the current group
-                  const bool any2 = deep && (((ls + 1) << GI_GROUP_LEVELS) - 1) < n32;          // uniform
-                  P3 low = {0.0, 0.0, 0.0};
-                  if (any2) low = load_photon(m, s2, s2 < n32);
                   const bool more = todo != 0;
-                  uint32_t ls_n = 0; P3 nxt = {0.0, 0.0, 0.0};
-                  if (more) {
-                    ls_n = cbase + (uint32_t)(__ffs(todo) - 1); todo &= todo - 1;
-                    nxt = load_group(gpos_lane, ls_n + bottom_delta);
+                  const uint32_t ls_n = cbase + (more ? (uint32_t)(__ffs(todo) - 1) : 0u);      // child 0 always exists
+                  todo &= todo - 1;
+                  const uint32_t s2_n = (((ls_n + 1) << GI_GROUP_LEVELS) - 1) + (uint32_t)lane;
+                  const P3 nxt = load_group(gpos_lane, ls_n + bottom_delta);
+                  P3 low_n = {0.0, 0.0, 0.0};
+                  if (DEEP) low_n = load_photon(m, s2_n, s2_n < n32);
+                  double d2a = dist2(cur, qx, qy, qz), d2b = 0.0;
+                  bool pa = d2a <= bound, pb = false;
+                  if (DEEP) { d2b = dist2(low, qx, qy, qz); pb = d2b <= bound; }
+                  const unsigned ma = __ballot_sync(FULL, pa), mb = DEEP ? __ballot_sync(FULL, pb) : 0u;
+                  if (ma | mb) {
+                    const int na = __popc(ma);
+                    if (pa) { const int pos = count + __popc(ma & lt_mask); b.set_d2(pos, d2a); b.set_slot(pos, (ls << jl) + (uint32_t)lane); }
+                    if (DEEP && pb) { const int pos = count + na + __popc(mb & lt_mask); b.set_d2(pos, d2b); b.set_slot(pos, s2); }
+                    count += na + __popc(mb);
+                    __syncwarp();
+                    if (count > b.limit) {
+                      const Sel r = cut(b, count, bound, k, lane); count = r.count; bound = r.bound;
+                      todo &= __ballot_sync(FULL, (double)kf <= bound);
+                    }
                   }
-                  const double before = bound;
-                  double d2 = dist2(cur, qx, qy, qz);
-                  append(b, count, bound, k, lane, lt_mask, d2 <= bound, d2, (ls << jl) + (uint32_t)lane);
-                  if (any2) {
-                    d2 = dist2(low, qx, qy, qz);
-                    append(b, count, bound, k, lane, lt_mask, d2 <= bound, d2, s2);
-                  }
-                  if (bound < before) todo &= __ballot_sync(FULL, (double)kf <= bound);       // the buffer was cut
                   if (!more) break;
-                  ls = ls_n; cur = nxt;
+                  ls = ls_n; cur = nxt; s2 = s2_n; low = low_n;
                 }
               }
               --g; enter = false;
@@ -454,15 +462,18 @@ cudaError_t launch_gather(GiContext *ctx, const PhotonMapDev &m, const double *d
   const uint64_t nchunks = (nq + GI_GATHER_CHUNK - 1) / GI_GATHER_CHUNK;
   if ((uint64_t)warps > nchunks) warps = (int)nchunks;
   const size_t smem = (size_t)warps * per_warp;
-  static size_t configured = 0;
-  if (smem > configured) {
-    cudaError_t e = cudaFuncSetAttribute(gather_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
+  const bool deep = m.hb > GI_GROUP_LEVELS;
+  static size_t configured[2] = {0, 0};
+  if (smem > configured[deep]) {
+    cudaError_t e = deep ? cudaFuncSetAttribute(gather_kernel<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem)
+                         : cudaFuncSetAttribute(gather_kernel<false>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
     if (e != cudaSuccess) return e;
-    configured = smem;
+    configured[deep] = smem;
   }
   const uint64_t want = (nchunks + warps - 1) / warps;
   const unsigned grid = (unsigned)(want < (uint64_t)ctx->sm_count ? want : (uint64_t)ctx->sm_count);
-  gather_kernel<<<grid, warps * 32, smem, st>>>(m, d_lut, d_q, d_order, nq, ga, d_idx, d_count, d_rgb);
+  if (deep) gather_kernel<true><<<grid, warps * 32, smem, st>>>(m, d_lut, d_q, d_order, nq, ga, d_idx, d_count, d_rgb);
+  else gather_kernel<false><<<grid, warps * 32, smem, st>>>(m, d_lut, d_q, d_order, nq, ga, d_idx, d_count, d_rgb);
   ctx->launches++;
   return cudaGetLastError();
 }

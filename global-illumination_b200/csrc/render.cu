@@ -367,10 +367,9 @@ __global__ void __launch_bounds__(256) commit_requests_kernel(const double *__re
   add3(accum + 3 * (size_t)pix[t], mk3(w[3 * t] * rgb[3 * t], w[3 * t + 1] * rgb[3 * t + 1], w[3 * t + 2] * rgb[3 * t + 2]));
 }
 
-// Requests reach a queue in the order the path threads happened to push them, i.e. scattered over the scene.  Sorting
-// them along a Morton curve before the gather makes the 16 consecutive queries a gather warp takes neighbours in
-// space: the k-th distance of one query is then a good first search radius for the next (gather.cu), and the warps
-// of a CTA walk the same part of the kd-tree.
+// Requests reach a queue in the order the path threads happened to push them, i.e. scattered over the scene.  The
+// gather orders its batch along a Morton curve itself (query_order.cu); the irradiance-cache lookups (a thread per
+// request walking the kd-tree) are sorted here for the same reason: neighbouring threads then take the same branches.
 GI_DEV uint32_t spread10(uint32_t v) {
   v &= 1023u; v = (v | (v << 16)) & 0x030000FFu; v = (v | (v << 8)) & 0x0300F00Fu; v = (v | (v << 4)) & 0x030C30C3u;
   return (v | (v << 2)) & 0x09249249u;
@@ -550,7 +549,8 @@ struct Renderer {
       return cached ? gi_cached_radiance_batch_device(ctx, q, n, r, qs.rgb.as<double>(), st)
                     : gi_gather_batch_device(ctx, map, q, n, k, r, filter, &p, nullptr, nullptr, qs.rgb.as<double>(), st);
     };
-    if (n < 4096 || !sort_requests) {
+    // photon gathers order their batch themselves (query_order.cu); only the cache lookups are sorted here
+    if (n < 4096 || !sort_requests || !cached) {
       if (estimate(qs.view.q)) return false;
       commit_requests_kernel<<<(unsigned)((n + 255) / 256), 256, 0, st>>>(qs.view.w, qs.view.pix, qs.rgb.as<double>(), n, accum);
       ctx->launches++;
