@@ -23,7 +23,7 @@ static const uint32_t PMAP_MAGIC = 0x4d504947u;   // "GIPM"
 
 void free_map(PhotonMapStore &m) {
   cudaFree((void *)m.dev.px); cudaFree((void *)m.dev.py); cudaFree((void *)m.dev.pz);
-  cudaFree((void *)m.dev.node); cudaFree((void *)m.dev.shade); cudaFree((void *)m.dev.orig); cudaFree((void *)m.dev.gbox); cudaFree((void *)m.dev.gpos);
+  cudaFree((void *)m.dev.node); cudaFree((void *)m.dev.shade); cudaFree((void *)m.dev.orig); cudaFree((void *)m.dev.cbox); cudaFree((void *)m.dev.gpos); cudaFree((void *)m.dev.srec);
   cudaFree(m.raw);
   m = PhotonMapStore();
 }
@@ -145,10 +145,12 @@ int gi_dump_photons_file(GiContext *ctx, int map, const char *path) {
 int gi_build_maps(GiContext *ctx, const GiParams *params) {
   if (!ctx) { set_error("gi_build_maps: null context"); return 1; }
   GI_CUDA(cudaSetDevice(ctx->device));
+  const double *lut = direction_lut(ctx);
+  if (!lut) return 1;
   for (int k = 0; k < 2; k++) {
     PhotonMapStore &m = ctx->maps[k];
     if (m.built || m.dev.n == 0) continue;
-    GI_CUDA(build_photon_map(ctx, m, m.dev.n));
+    GI_CUDA(build_photon_map(ctx, m, m.dev.n, lut));
   }
   // photonmap.cpp:380-411: with -cache the global photons' colours become irradiance estimates
   if (params && params->irradiance_cache && (params->indirect_illum || params->direct_photon_illum) &&

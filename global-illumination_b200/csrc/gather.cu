@@ -230,9 +230,11 @@ __device__ __forceinline__ double dist2(const P3 &p, double qx, double qy, doubl
   return (dx * dx) + (dy * dy) + (dz * dz);
 }
 // lower bound (after rounding) of the squared distance from the query to anything inside a subtree box
-__device__ __forceinline__ double box_dist2(const double2 X, const double2 Y, const double2 Z, double qx, double qy, double qz) {
-  const double dx = fmax(fmax(X.x - qx, qx - X.y), 0.0), dy = fmax(fmax(Y.x - qy, qy - Y.y), 0.0),
-               dz = fmax(fmax(Z.x - qz, qz - Z.y), 0.0);
+// (box of child `lane` of group gi, from the group's cbox block; +inf when there is no such child)
+__device__ __forceinline__ double box_dist2(const double *__restrict__ cbox_lane, uint32_t gi, double qx, double qy, double qz) {
+  const double *b = cbox_lane + (size_t)gi * 192;
+  const double lx = b[0], hx = b[32], ly = b[64], hy = b[96], lz = b[128], hz = b[160];
+  const double dx = fmax(fmax(lx - qx, qx - hx), 0.0), dy = fmax(fmax(ly - qy, qy - hy), 0.0), dz = fmax(fmax(lz - qz, qz - hz), 0.0);
   return ((dx * dx) + (dy * dy) + (dz * dz)) * 0.99999999999999;
 }
 
@@ -256,7 +258,7 @@ gather_kernel(PhotonMapDev m, const double *__restrict__ lut, const GiGatherQuer
   const uint32_t n32 = (uint32_t)n;
   const int jl = 31 - __clz(lane + 1);                      // relative depth of this lane's photon inside a group
   const uint32_t lt_mask = (1u << lane) - 1u;
-  const double *gpos_lane = m.gpos + lane;
+  const double *gpos_lane = m.gpos + lane, *cbox_lane = m.cbox + lane;
   const int G = m.groups, gp = m.groups - 2;                // rows; gp = the row whose children are the bottom groups
   const bool deep = DEEP;
   const uint32_t bottom_delta = G > 1 ? m.goff[G - 1] - ((1u << m.glevel[G - 1]) - 1u) : 0u;   // bottom group index - root slot
@@ -301,25 +303,18 @@ gather_kernel(PhotonMapDev m, const double *__restrict__ lut, const GiGatherQuer
         while (g >= 0) {
           const int h = g == 0 ? m.h0 : GI_GROUP_LEVELS;
           if (enter) {
-            // ---- issue both loads of the group: its photons and the boxes of its 2^h children (one contiguous run
-            //      of slots in row g + 1)
+            // ---- the group's photons and the boxes of its 32 children (both blocks are loaded before either is used)
             const uint32_t cbase = ((s + 1) << h) - 1;
-            const uint32_t c = cbase + (uint32_t)lane;
-            const bool cv = lane < (1 << h) && c < n32;
-            const P3 ph = load_group(gpos_lane, s + (m.goff[g] - ((1u << m.glevel[g]) - 1u)));
-            double2 X = make_double2(0, 0), Y = X, Z = X;
-            if (cv) {
-              const double2 *bx = m.gbox + 3 * (size_t)(c + (m.goff[g + 1] - ((1u << m.glevel[g + 1]) - 1u)));
-              X = bx[0]; Y = bx[1]; Z = bx[2];
-            }
+            const uint32_t gi = s + (m.goff[g] - ((1u << m.glevel[g]) - 1u));
+            const P3 ph = load_group(gpos_lane, gi);
+            const double bd = box_dist2(cbox_lane, gi, qx, qy, qz);
             {
               const double d2 = dist2(ph, qx, qy, qz);
               append(b, count, bound, k, lane, lt_mask, d2 <= bound, d2, (s << jl) + (uint32_t)lane);
             }
-            const double bd = box_dist2(X, Y, Z, qx, qy, qz);
             if (g == gp) {
               // ---- bottom groups under this one: branch-light loop, the next group's block is always in flight
-              const float kf = cv ? __double2float_rd(bd) : INFINITY;
+              const float kf = __double2float_rd(bd);
               unsigned todo = __ballot_sync(FULL, (double)kf <= bound);
               if (todo) {
                 uint32_t ls = cbase + (uint32_t)(__ffs(todo) - 1); todo &= todo - 1;
@@ -357,7 +352,7 @@ gather_kernel(PhotonMapDev m, const double *__restrict__ lut, const GiGatherQuer
               --g; enter = false;
               continue;                                                 // h belongs to the row just left
             } else {
-              sts_u32(b.a_keys + 4u * (uint32_t)(g * 32 + lane), cv && bd <= bound ? __float_as_uint(__double2float_rd(bd)) : NONE);
+              sts_u32(b.a_keys + 4u * (uint32_t)(g * 32 + lane), bd <= bound ? __float_as_uint(__double2float_rd(bd)) : NONE);
               if (lane == g) st_root = s;
               enter = false;
             }
@@ -397,9 +392,10 @@ gather_kernel(PhotonMapDev m, const double *__restrict__ lut, const GiGatherQuer
       if (ga.filter == GI_FILTER_CONE) c1 = 1.0 / (ga.fk * sqrt(max_d2));
       else if (ga.filter == GI_FILTER_GAUSS) { c1 = exp(-ga.fb); c2 = 1.0 / (2.0 * max_d2); }
       for (int i = lane; i < found; i += 32) {
-        const uint2 sh = m.shade[b.slot(i)];
-        const double *dir = lut + 3 * (size_t)(sh.y & 0xffffu);
-        const double ix = dir[0], iy = dir[1], iz = dir[2];
+        const double2 *rec = m.srec + 2 * (size_t)b.slot(i);
+        const double2 ra = rec[0], rb = rec[1];
+        const double ix = ra.x, iy = ra.y, iz = rb.x;
+        const uint2 sh = make_uint2((uint32_t)__double2loint(rb.y), (uint32_t)__double2hiint(rb.y));
         const double perp = (nx * ix) + (ny * iy) + (nz * iz);
         if ((cos_theta < 0 && perp < 0) || (cos_theta > 0 && perp > 0)) continue;
         const uint32_t e = sh.x >> 24;

@@ -76,9 +76,13 @@ __global__ void apply_raw_kernel(GiPhoton *__restrict__ ph, uint64_t n, const ui
   const uint32_t v = rgbe[t];
   ph[t].rgbe[0] = (uint8_t)v; ph[t].rgbe[1] = (uint8_t)(v >> 8); ph[t].rgbe[2] = (uint8_t)(v >> 16); ph[t].rgbe[3] = (uint8_t)(v >> 24);
 }
-__global__ void apply_heap_kernel(uint2 *__restrict__ shade, const uint32_t *__restrict__ orig, uint64_t n, const uint32_t *__restrict__ rgbe) {
+__global__ void apply_heap_kernel(uint2 *__restrict__ shade, double2 *__restrict__ srec, const uint32_t *__restrict__ orig, uint64_t n,
+                                  const uint32_t *__restrict__ rgbe) {
   const uint64_t t = (uint64_t)blockIdx.x * blockDim.x + threadIdx.x;
-  if (t < n) shade[t].x = rgbe[orig[t]];
+  if (t >= n) return;
+  const uint32_t v = rgbe[orig[t]];
+  shade[t].x = v;
+  srec[2 * t + 1].y = __hiloint2double(__double2hiint(srec[2 * t + 1].y), (int)v);    // the estimate's copy (photon_dev.h)
 }
 
 // R3Kdtree::FindClosest(position, min_distance, max_distance): the photon with the smallest d^2 in
@@ -182,7 +186,7 @@ int build_irradiance_cache(GiContext *ctx, const GiParams &p) {
   }
   const unsigned blocks = (unsigned)((n + 255) / 256);
   apply_raw_kernel<<<blocks, 256, 0, st>>>((GiPhoton *)m.raw, n, d_rgbe);
-  apply_heap_kernel<<<blocks, 256, 0, st>>>((uint2 *)m.dev.shade, m.dev.orig, n, d_rgbe);
+  apply_heap_kernel<<<blocks, 256, 0, st>>>((uint2 *)m.dev.shade, (double2 *)m.dev.srec, m.dev.orig, n, d_rgbe);
   ctx->launches += 2;
   const bool ok = cuda_ok(cudaGetLastError(), "irradiance cache") && cuda_ok(cudaStreamSynchronize(st), "irradiance cache sync");
   cleanup();

@@ -146,7 +146,7 @@ __global__ void assign_kernel(uint64_t first, uint64_t n, int L, int level, uint
 
 __global__ void finalize_kernel(const GiPhoton *__restrict__ ph, uint64_t n, const uint32_t *__restrict__ heap_photon,
                                 const float *__restrict__ split, const uint8_t *__restrict__ axis, double *px, double *py,
-                                double *pz, uint2 *node, uint2 *shade, uint32_t *orig) {
+                                double *pz, uint2 *node, uint2 *shade, uint32_t *orig, const double *__restrict__ lut, double2 *srec) {
   const uint64_t i = (uint64_t)blockIdx.x * blockDim.x + threadIdx.x;
   if (i >= n) return;
   const uint32_t src = heap_photon[i];
@@ -156,13 +156,16 @@ __global__ void finalize_kernel(const GiPhoton *__restrict__ ph, uint64_t n, con
   shade[i] = make_uint2(b.z, b.w & 0xffffu);
   orig[i] = src;
   node[i] = make_uint2(__float_as_uint(split[i]), axis[i]);
+  const double *dir = lut + 3 * (size_t)(b.w & 0xffffu);
+  srec[2 * i] = make_double2(dir[0], dir[1]);
+  srec[2 * i + 1] = make_double2(dir[2], __hiloint2double((int)(b.w & 0xffffu), (int)b.z));
 }
 
 // Per group of row g (photon_dev.h): the position block gpos (x[32], y[32], z[32], +inf where the group has no photon)
 // and the tight FP64 box of the subtree below its root = min / max over the group's photons, over the boxes of its 32
-// child groups (row g + 1, filled by the previous launch) and, in a six-level bottom row, over its level-6 photons.
-// One warp per group.
-__global__ void group_kernel(PhotonMapDev m, int g, double *gpos, double2 *gbox) {
+// child groups (its own cbox block, filled by the previous launch for row g + 1) and, in a six-level bottom row, over
+// its level-6 photons.  The box goes into the parent group's cbox block.  One warp per group.
+__global__ void group_kernel(PhotonMapDev m, int g, double *gpos, double *cbox) {
   const uint64_t w = ((uint64_t)blockIdx.x * blockDim.x + threadIdx.x) >> 5;
   const int lane = threadIdx.x & 31;
   const uint64_t first = ((uint64_t)1 << m.glevel[g]) - 1;
@@ -177,30 +180,37 @@ __global__ void group_kernel(PhotonMapDev m, int g, double *gpos, double2 *gbox)
   if (lane < (1 << h) - 1 && slot < m.n) { p[0] = m.px[slot]; p[1] = m.py[slot]; p[2] = m.pz[slot]; for (int a = 0; a < 3; a++) lo[a] = hi[a] = p[a]; }
   const size_t gi = (size_t)m.goff[g] + w;
   for (int a = 0; a < 3; a++) gpos[gi * 96 + 32 * a + lane] = p[a];
-  const uint64_t c = ((r + 1) << h) - 1 + (uint64_t)lane;                    // relative depth h below r
   if (g + 1 < m.groups) {
-    if (lane < (1 << h) && c < m.n) {
-      const double2 *b = gbox + 3 * ((size_t)m.goff[g + 1] + (c - (((uint64_t)1 << m.glevel[g + 1]) - 1)));
-      for (int a = 0; a < 3; a++) { lo[a] = fmin(lo[a], b[a].x); hi[a] = fmax(hi[a], b[a].y); }
+    const double *b = cbox + gi * 192 + lane;                                  // boxes of my children (inf where none)
+    for (int a = 0; a < 3; a++) { lo[a] = fmin(lo[a], b[64 * a]); hi[a] = fmax(hi[a], b[64 * a + 32]); }
+  } else if (m.hb > GI_GROUP_LEVELS) {                                         // bottom row, six levels deep
+    const uint64_t c = ((r + 1) << h) - 1 + (uint64_t)lane;
+    if (c < m.n) {
+      lo[0] = fmin(lo[0], m.px[c]); hi[0] = fmax(hi[0], m.px[c]); lo[1] = fmin(lo[1], m.py[c]); hi[1] = fmax(hi[1], m.py[c]);
+      lo[2] = fmin(lo[2], m.pz[c]); hi[2] = fmax(hi[2], m.pz[c]);
     }
-  } else if (m.hb > GI_GROUP_LEVELS && c < m.n) {                            // bottom row, six levels deep
-    lo[0] = fmin(lo[0], m.px[c]); hi[0] = fmax(hi[0], m.px[c]); lo[1] = fmin(lo[1], m.py[c]); hi[1] = fmax(hi[1], m.py[c]);
-    lo[2] = fmin(lo[2], m.pz[c]); hi[2] = fmax(hi[2], m.pz[c]);
   }
   for (int a = 0; a < 3; a++)
     for (int o = 16; o > 0; o >>= 1) {
       lo[a] = fmin(lo[a], __shfl_xor_sync(0xffffffffu, lo[a], o));
       hi[a] = fmax(hi[a], __shfl_xor_sync(0xffffffffu, hi[a], o));
     }
-  if (lane == 0) {
-    double2 *b = gbox + 3 * gi;
-    for (int a = 0; a < 3; a++) b[a] = make_double2(lo[a], hi[a]);
+  if (lane == 0 && g > 0) {
+    const int hp = g == 1 ? m.h0 : GI_GROUP_LEVELS;                            // depth of the parent row
+    const uint64_t pr = ((r + 1) >> hp) - 1, child = (r + 1) & (((uint64_t)1 << hp) - 1);
+    double *b = cbox + ((size_t)m.goff[g - 1] + (pr - (((uint64_t)1 << m.glevel[g - 1]) - 1))) * 192 + child;
+    for (int a = 0; a < 3; a++) { b[64 * a] = lo[a]; b[64 * a + 32] = hi[a]; }
   }
+}
+// cbox starts as "no child anywhere": lo = +inf, hi = -inf
+__global__ void cbox_init_kernel(double *cbox, uint64_t n_doubles) {
+  const uint64_t i = (uint64_t)blockIdx.x * blockDim.x + threadIdx.x;
+  if (i < n_doubles) cbox[i] = ((i >> 5) & 1) ? -__longlong_as_double(0x7ff0000000000000ll) : __longlong_as_double(0x7ff0000000000000ll);
 }
 
 #define CKB(x) do { cudaError_t e_ = (x); if (e_ != cudaSuccess) { err = e_; goto done; } } while (0)
 
-cudaError_t build_photon_map(GiContext *ctx, PhotonMapStore &m, uint64_t n) {
+cudaError_t build_photon_map(GiContext *ctx, PhotonMapStore &m, uint64_t n, const double *d_lut) {
   cudaError_t err = cudaSuccess;
   cudaStream_t st = ctx->stream;
   const GiPhoton *ph = (const GiPhoton *)m.raw;
@@ -209,7 +219,7 @@ cudaError_t build_photon_map(GiContext *ctx, PhotonMapStore &m, uint64_t n) {
   uint32_t *heap_photon = nullptr, *bounds = nullptr; float *split = nullptr; uint8_t *axis = nullptr;
   void *tmp = nullptr; size_t tmp_bytes = 0;
   double *px = nullptr, *py = nullptr, *pz = nullptr; uint2 *node = nullptr, *shade = nullptr; uint32_t *orig = nullptr;
-  double2 *gbox = nullptr; double *gpos = nullptr; uint64_t n_groups = 0;
+  double *cbox = nullptr, *gpos = nullptr; double2 *srec = nullptr; uint64_t n_groups = 0, n_upper = 0;
   PhotonMapDev d{};
   const int B = 256;
   const unsigned G = (unsigned)((n + B - 1) / B);
@@ -240,11 +250,11 @@ cudaError_t build_photon_map(GiContext *ctx, PhotonMapStore &m, uint64_t n) {
     CKB(cudaGetLastError());
   }
   CKB(cudaMalloc(&px, 8 * n)); CKB(cudaMalloc(&py, 8 * n)); CKB(cudaMalloc(&pz, 8 * n));
-  CKB(cudaMalloc(&node, 8 * n)); CKB(cudaMalloc(&shade, 8 * n)); CKB(cudaMalloc(&orig, 4 * n));
-  finalize_kernel<<<G, B, 0, st>>>(ph, n, heap_photon, split, axis, px, py, pz, node, shade, orig);
+  CKB(cudaMalloc(&node, 8 * n)); CKB(cudaMalloc(&shade, 8 * n)); CKB(cudaMalloc(&orig, 4 * n)); CKB(cudaMalloc(&srec, 32 * n));
+  finalize_kernel<<<G, B, 0, st>>>(ph, n, heap_photon, split, axis, px, py, pz, node, shade, orig, d_lut, srec);
   ctx->launches++;
   CKB(cudaGetLastError());
-  d.n = n; d.levels = L; d.px = px; d.py = py; d.pz = pz; d.node = node; d.shade = shade; d.orig = orig;
+  d.n = n; d.levels = L; d.px = px; d.py = py; d.pz = pz; d.node = node; d.shade = shade; d.orig = orig; d.srec = srec;
   // rows of 5-level groups (photon_dev.h) and their subtree boxes, bottom row first
   {
     const uint64_t last_cap = (uint64_t)1 << (L - 1), last = n - (last_cap - 1);      // slots / photons on the last level
@@ -259,13 +269,15 @@ cudaError_t build_photon_map(GiContext *ctx, PhotonMapStore &m, uint64_t n) {
     const uint64_t first = ((uint64_t)1 << d.glevel[g]) - 1;
     n_groups += n - first < first + 1 ? n - first : first + 1;
   }
-  CKB(cudaMalloc(&gbox, 48 * n_groups));
+  n_upper = d.groups > 1 ? d.goff[d.groups - 1] : 0;                    // groups above the bottom row
+  CKB(cudaMalloc(&cbox, 1536 * (n_upper ? n_upper : 1)));
   CKB(cudaMalloc(&gpos, 768 * n_groups));
-  d.gbox = gbox; d.gpos = gpos;
+  d.cbox = cbox; d.gpos = gpos;
+  if (n_upper) { cbox_init_kernel<<<(unsigned)((n_upper * 192 + B - 1) / B), B, 0, st>>>(cbox, n_upper * 192); ctx->launches++; }
   for (int g = d.groups - 1; g >= 0; g--) {
     const uint64_t first = ((uint64_t)1 << d.glevel[g]) - 1;
     const uint64_t rows = n - first < first + 1 ? n - first : first + 1;
-    group_kernel<<<(unsigned)((rows * 32 + B - 1) / B), B, 0, st>>>(d, g, gpos, gbox);
+    group_kernel<<<(unsigned)((rows * 32 + B - 1) / B), B, 0, st>>>(d, g, gpos, cbox);
     ctx->launches++;
   }
   CKB(cudaGetLastError());
@@ -282,11 +294,11 @@ cudaError_t build_photon_map(GiContext *ctx, PhotonMapStore &m, uint64_t n) {
   }
   m.dev = d;
   m.built = true;
-  px = py = pz = nullptr; node = shade = nullptr; orig = nullptr; gbox = nullptr; gpos = nullptr;
+  px = py = pz = nullptr; node = shade = nullptr; orig = nullptr; cbox = nullptr; gpos = nullptr; srec = nullptr;
 done:
   for (int k = 0; k < 2; k++) { cudaFree(keys[k]); cudaFree(vals[k]); }
   cudaFree(heap_photon); cudaFree(split); cudaFree(bounds); cudaFree(axis); cudaFree(tmp);
-  cudaFree(px); cudaFree(py); cudaFree(pz); cudaFree(node); cudaFree(shade); cudaFree(orig); cudaFree(gbox); cudaFree(gpos);
+  cudaFree(px); cudaFree(py); cudaFree(pz); cudaFree(node); cudaFree(shade); cudaFree(orig); cudaFree(cbox); cudaFree(gpos); cudaFree(srec);
   return err;
 }
 

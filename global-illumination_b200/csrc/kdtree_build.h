@@ -5,5 +5,5 @@
 struct GiContext;
 namespace gi {
 // builds m.dev from m.raw (GiPhoton[n] on the device); synchronises ctx->stream
-cudaError_t build_photon_map(GiContext *ctx, PhotonMapStore &m, uint64_t n);
+cudaError_t build_photon_map(GiContext *ctx, PhotonMapStore &m, uint64_t n, const double *d_lut);   /* d_lut: the 65536 x 3 direction table */
 }  // namespace gi

@@ -33,11 +33,14 @@ struct PhotonMapDev {
   /* groups (see above), numbered row by row: group of root slot s in row g has index goff[g] + s - (2^glevel[g] - 1) */
   const double *gpos;             /* per group 96 doubles: x[32], y[32], z[32] of its (up to) 31 photons, lane order = slot    */
                                   /* order within the group; unused entries hold +inf, so their distance test fails by itself */
-  const double2 *gbox;            /* per group 3 x double2 {lo, hi} for x, y, z: tight box of the whole subtree below its root */
+  const double *cbox;             /* per group above the bottom row 192 doubles: lo_x[32], hi_x[32], lo_y[32], hi_y[32], lo_z[32],  */
+                                  /* hi_z[32] = tight boxes of the subtrees of its 32 child groups (lo = +inf, hi = -inf: no child) */
   int32_t groups, h0, hb;         /* rows of groups; depth of the top group; depth of the bottom-row groups (one row: groups = 1, hb = levels) */
   int32_t glevel[GI_MAX_GROUPS];  /* tree level of the group roots of row g (glevel[0] = 0) */
   uint32_t goff[GI_MAX_GROUPS];   /* index of the first group of row g */
   const uint2 *shade;             /* heap order: x = rgbe bytes (r | g<<8 | b<<16 | e<<24), y = direction code */
+  const double2 *srec;            /* heap order, 32 B: {dir.x, dir.y}, {dir.z, bits: rgbe | code << 32}: the estimate's view of a */
+                                  /* photon -- the incident direction already looked up (photon_utils.cpp:253-272), one sector  */
   const uint32_t *orig;           /* heap order -> index in the order the photons were loaded / traced */
 };
 
