@@ -218,13 +218,6 @@ __device__ __forceinline__ P3 load_group(const double *__restrict__ gpos_lane, u
   P3 r; r.x = p[0]; r.y = p[32]; r.z = p[64];
   return r;
 }
-// level 6 of a bottom group: a contiguous run of heap slots
-__device__ __forceinline__ P3 load_photon(const PhotonMapDev &m, uint32_t slot, bool valid) {
-  const double INF = __longlong_as_double(0x7ff0000000000000ll);
-  P3 p = {INF, INF, INF};
-  if (valid) { p.x = m.px[slot]; p.y = m.py[slot]; p.z = m.pz[slot]; }
-  return p;
-}
 __device__ __forceinline__ double dist2(const P3 &p, double qx, double qy, double qz) {
   const double dx = qx - p.x, dy = qy - p.y, dz = qz - p.z;                        // v = query - photon; v.Dot(v)
   return (dx * dx) + (dy * dy) + (dz * dz);
@@ -255,13 +248,12 @@ gather_kernel(PhotonMapDev m, const double *__restrict__ lut, const GiGatherQuer
   }
   const int k = ga.k;
   const uint64_t n = m.n;
-  const uint32_t n32 = (uint32_t)n;
   const int jl = 31 - __clz(lane + 1);                      // relative depth of this lane's photon inside a group
   const uint32_t lt_mask = (1u << lane) - 1u;
   const double *gpos_lane = m.gpos + lane, *cbox_lane = m.cbox + lane;
   const int G = m.groups, gp = m.groups - 2;                // rows; gp = the row whose children are the bottom groups
-  const bool deep = DEEP;
-  const uint32_t bottom_delta = G > 1 ? m.goff[G - 1] - ((1u << m.glevel[G - 1]) - 1u) : 0u;   // bottom group index - root slot
+  const uint32_t bottom_first = (1u << m.glevel[G - 1]) - 1u;                                   // root slot of the first bottom group
+  const uint32_t bottom_delta = m.goff[G - 1] - bottom_first;                                   // bottom group index - root slot
   const uint64_t warps_total = (uint64_t)gridDim.x * nwarps;
   const uint64_t nchunks = (nq + GI_GATHER_CHUNK - 1) / GI_GATHER_CHUNK;
   // Search radius carried from one query to the next: consecutive queries of a chunk are neighbouring pixels, so the
@@ -294,10 +286,13 @@ gather_kernel(PhotonMapDev m, const double *__restrict__ lut, const GiGatherQuer
         bool enter = true;
         if (G == 1) {                                                   // fewer than 64 photons: one group, no boxes
           const uint32_t s1 = (uint32_t)lane, s2 = 31u + (uint32_t)lane;
-          const P3 a = load_group(gpos_lane, 0), c = load_photon(m, s2, deep && s2 < n32);
+          const P3 a = load_group(gpos_lane, 0);
           double d2 = dist2(a, qx, qy, qz);
           append(b, count, bound, k, lane, lt_mask, d2 <= bound, d2, s1);
-          if (deep) { d2 = dist2(c, qx, qy, qz); append(b, count, bound, k, lane, lt_mask, d2 <= bound, d2, s2); }
+          if (DEEP) {
+            const P3 c = load_group(gpos_lane, m.x6_base);
+            d2 = dist2(c, qx, qy, qz); append(b, count, bound, k, lane, lt_mask, d2 <= bound, d2, s2);
+          }
           g = -1;
         }
         while (g >= 0) {
@@ -318,26 +313,31 @@ gather_kernel(PhotonMapDev m, const double *__restrict__ lut, const GiGatherQuer
               unsigned todo = __ballot_sync(FULL, (double)kf <= bound);
               if (todo) {
                 uint32_t ls = cbase + (uint32_t)(__ffs(todo) - 1); todo &= todo - 1;
-                uint32_t s2 = (((ls + 1) << GI_GROUP_LEVELS) - 1) + (uint32_t)lane;             // level 6 of the current group
+                bool has6 = DEEP && ls - bottom_first < m.x6_blocks;                            // uniform: the group has a level 6
                 P3 cur = load_group(gpos_lane, ls + bottom_delta);
                 P3 low = {0.0, 0.0, 0.0};
-                if (DEEP) low = load_photon(m, s2, s2 < n32);
+                if (has6) low = load_group(gpos_lane, m.x6_base + (ls - bottom_first));
                 while (true) {
                   const bool more = todo != 0;
                   const uint32_t ls_n = cbase + (more ? (uint32_t)(__ffs(todo) - 1) : 0u);      // child 0 always exists
                   todo &= todo - 1;
-                  const uint32_t s2_n = (((ls_n + 1) << GI_GROUP_LEVELS) - 1) + (uint32_t)lane;
+                  const bool has6_n = DEEP && ls_n - bottom_first < m.x6_blocks;
                   const P3 nxt = load_group(gpos_lane, ls_n + bottom_delta);
                   P3 low_n = {0.0, 0.0, 0.0};
-                  if (DEEP) low_n = load_photon(m, s2_n, s2_n < n32);
-                  double d2a = dist2(cur, qx, qy, qz), d2b = 0.0;
-                  bool pa = d2a <= bound, pb = false;
-                  if (DEEP) { d2b = dist2(low, qx, qy, qz); pb = d2b <= bound; }
-                  const unsigned ma = __ballot_sync(FULL, pa), mb = DEEP ? __ballot_sync(FULL, pb) : 0u;
+                  if (has6_n) low_n = load_group(gpos_lane, m.x6_base + (ls_n - bottom_first));
+                  const double d2a = dist2(cur, qx, qy, qz);
+                  double d2b = 0.0;
+                  const bool pa = d2a <= bound; bool pb = false;
+                  unsigned mb = 0u;
+                  if (has6) { d2b = dist2(low, qx, qy, qz); pb = d2b <= bound; mb = __ballot_sync(FULL, pb); }
+                  const unsigned ma = __ballot_sync(FULL, pa);
                   if (ma | mb) {
                     const int na = __popc(ma);
                     if (pa) { const int pos = count + __popc(ma & lt_mask); b.set_d2(pos, d2a); b.set_slot(pos, (ls << jl) + (uint32_t)lane); }
-                    if (DEEP && pb) { const int pos = count + na + __popc(mb & lt_mask); b.set_d2(pos, d2b); b.set_slot(pos, s2); }
+                    if (pb) {
+                      const int pos = count + na + __popc(mb & lt_mask);
+                      b.set_d2(pos, d2b); b.set_slot(pos, (((ls + 1) << GI_GROUP_LEVELS) - 1) + (uint32_t)lane);
+                    }
                     count += na + __popc(mb);
                     __syncwarp();
                     if (count > b.limit) {
@@ -346,7 +346,7 @@ gather_kernel(PhotonMapDev m, const double *__restrict__ lut, const GiGatherQuer
                     }
                   }
                   if (!more) break;
-                  ls = ls_n; cur = nxt; s2 = s2_n; low = low_n;
+                  ls = ls_n; cur = nxt; low = low_n; has6 = has6_n;
                 }
               }
               --g; enter = false;
@@ -370,7 +370,7 @@ gather_kernel(PhotonMapDev m, const double *__restrict__ lut, const GiGatherQuer
         }
         finish(b, count, bound, k, lane);
         if (count >= k || init >= ga.r2) break;
-        init = fmin(ga.r2, init * 4.0);                                 // the guess was too small: widen and retry
+        init = init > 0.0 ? fmin(ga.r2, init * 4.0) : ga.r2;            // the guess was too small: widen and retry
       }
       guess = count >= k ? bound * ga.guess_factor : ga.r2;
     }

@@ -202,6 +202,16 @@ __global__ void group_kernel(PhotonMapDev m, int g, double *gpos, double *cbox) 
     for (int a = 0; a < 3; a++) { b[64 * a] = lo[a]; b[64 * a + 32] = hi[a]; }
   }
 }
+// level 6 of a six-level bottom row: runs of 32 consecutive heap slots -> position blocks x6_base + j
+__global__ void level6_kernel(PhotonMapDev m, double *gpos) {
+  const uint64_t t = (uint64_t)blockIdx.x * blockDim.x + threadIdx.x;
+  if (t >= (uint64_t)m.x6_blocks * 32) return;
+  const uint64_t slot = (((uint64_t)1 << (m.levels - 1)) - 1) + t;
+  const double INF = __longlong_as_double(0x7ff0000000000000ll);
+  const bool v = slot < m.n;
+  double *o = gpos + ((size_t)m.x6_base + (t >> 5)) * 96 + (t & 31);
+  o[0] = v ? m.px[slot] : INF; o[32] = v ? m.py[slot] : INF; o[64] = v ? m.pz[slot] : INF;
+}
 // cbox starts as "no child anywhere": lo = +inf, hi = -inf
 __global__ void cbox_init_kernel(double *cbox, uint64_t n_doubles) {
   const uint64_t i = (uint64_t)blockIdx.x * blockDim.x + threadIdx.x;
@@ -271,8 +281,11 @@ cudaError_t build_photon_map(GiContext *ctx, PhotonMapStore &m, uint64_t n, cons
   }
   n_upper = d.groups > 1 ? d.goff[d.groups - 1] : 0;                    // groups above the bottom row
   CKB(cudaMalloc(&cbox, 1536 * (n_upper ? n_upper : 1)));
-  CKB(cudaMalloc(&gpos, 768 * n_groups));
+  d.x6_base = (uint32_t)n_groups;
+  d.x6_blocks = d.hb > GI_GROUP_LEVELS ? (uint32_t)((n - ((((uint64_t)1 << (L - 1)) - 1)) + 31) / 32) : 0u;
+  CKB(cudaMalloc(&gpos, 768 * (n_groups + d.x6_blocks)));
   d.cbox = cbox; d.gpos = gpos;
+  if (d.x6_blocks) { level6_kernel<<<(unsigned)(((uint64_t)d.x6_blocks * 32 + B - 1) / B), B, 0, st>>>(d, gpos); ctx->launches++; }
   if (n_upper) { cbox_init_kernel<<<(unsigned)((n_upper * 192 + B - 1) / B), B, 0, st>>>(cbox, n_upper * 192); ctx->launches++; }
   for (int g = d.groups - 1; g >= 0; g--) {
     const uint64_t first = ((uint64_t)1 << d.glevel[g]) - 1;

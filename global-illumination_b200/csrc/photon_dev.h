@@ -33,6 +33,8 @@ struct PhotonMapDev {
   /* groups (see above), numbered row by row: group of root slot s in row g has index goff[g] + s - (2^glevel[g] - 1) */
   const double *gpos;             /* per group 96 doubles: x[32], y[32], z[32] of its (up to) 31 photons, lane order = slot    */
                                   /* order within the group; unused entries hold +inf, so their distance test fails by itself */
+  uint32_t x6_base, x6_blocks;    /* six-level bottom row: level 6 of bottom group number j (j < x6_blocks: left-balanced) is block   */
+                                  /* x6_base + j of gpos, again +inf padded                                                     */
   const double *cbox;             /* per group above the bottom row 192 doubles: lo_x[32], hi_x[32], lo_y[32], hi_y[32], lo_z[32],  */
                                   /* hi_z[32] = tight boxes of the subtrees of its 32 child groups (lo = +inf, hi = -inf: no child) */
   int32_t groups, h0, hb;         /* rows of groups; depth of the top group; depth of the bottom-row groups (one row: groups = 1, hb = levels) */
