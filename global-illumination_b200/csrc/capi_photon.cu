@@ -248,7 +248,8 @@ int gi_gather_batch(GiContext *ctx, int map, const GiGatherQuery *queries, uint6
   if (k < 1 || k > GI_MAX_K) { set_error("gi_gather_batch: estimate size must be in [1, 512]"); return 1; }
   GI_CUDA(cudaSetDevice(ctx->device));
   // two-slot pipeline like gi_intersect_batch: chunks of 2^20 queries (143 MB in, 29 MB out)
-  const uint64_t chunk = 1ull << 20;
+  uint64_t chunk = 1ull << 20;
+  if (const char *e = getenv("GI_PIPE_CHUNK_LOG2")) { const int l = atoi(e); if (l >= 12 && l <= 24) chunk = 1ull << l; }
   int rc = 0;
   for (uint64_t o = 0, c = 0; o < n && rc == 0; o += chunk, c++) {
     const uint64_t m = n - o < chunk ? n - o : chunk;

@@ -81,7 +81,7 @@ __device__ __noinline__ void bitonic_sort(const WarpBuf &b, int lane) {
 
 // slow exact path (heavy exact ties, or a zero bound): every candidate counts the candidates that precede it in
 // (d2, photon index) order -- O(count^2 / 32) -- and the k first are kept.  Keep flags go through the histogram words.
-struct Sel { double bound; int count; };           // search state: squared search radius, candidates held
+struct Sel { double bound; int count; int raw; };  // search state: squared search radius, candidates held, buffer entries they occupy
 
 __device__ __noinline__ Sel rank_select(const WarpBuf b, int count, double bound, int k, int lane) {
   for (int base = 0; base < count; base += 32) {
@@ -113,15 +113,16 @@ __device__ __noinline__ Sel rank_select(const WarpBuf b, int count, double bound
     __syncwarp();
   }
   for (int o = 16; o > 0; o >>= 1) mx = fmax(mx, __shfl_xor_sync(FULL, mx, o));
-  Sel r; r.count = newcount; r.bound = fmin(bound, mx);
+  Sel r; r.count = newcount; r.raw = newcount; r.bound = fmin(bound, mx);
   return r;
 }
 
 // Exact cut of the candidate buffer to the k smallest by (d2, orig).  Requires count > k.
 // A 128-bin histogram of d2 / bound locates the bin B that holds the k-th candidate; bins below B are kept whole,
 // and inside B (a handful of candidates, since surface photons are uniform in d2) each lane ranks one candidate
-// against the others by shuffles.  The bound becomes the largest kept d2.
-__device__ __noinline__ Sel cut(const WarpBuf b, int count, double bound, int k, int lane) {
+// against the others by shuffles.  The bound becomes the largest kept d2.  compact = false (the last cut of a search
+// whose indices are not wanted): dropped candidates are only marked with d2 = -1 and stay where they are (raw = count).
+__device__ __noinline__ Sel cut(const WarpBuf b, int count, double bound, int k, int lane, bool compact) {
   if (!(bound > 0.0)) return rank_select(b, count, bound, k, lane);
   for (int i = lane; i < GI_HIST_BINS; i += 32) b.set_hist(i, 0);
   __syncwarp();
@@ -169,6 +170,19 @@ __device__ __noinline__ Sel cut(const WarpBuf b, int count, double bound, int k,
     if (lane < m && rank >= need) b.set_d2(mi, -1.0);     // dropped
     __syncwarp();
   }
+  if (!compact) {
+    double mx = 0.0;
+    for (int i = lane; i < count; i += 32) {
+      const double d = b.d2(i);
+      int bin = (int)(d * scale); bin = bin > GI_HIST_BINS - 1 ? GI_HIST_BINS - 1 : bin;
+      if (bin > B) b.set_d2(i, -1.0);
+      else if (d >= 0.0) mx = fmax(mx, d);
+    }
+    for (int o = 16; o > 0; o >>= 1) mx = fmax(mx, __shfl_xor_sync(FULL, mx, o));
+    __syncwarp();
+    Sel r; r.count = k; r.raw = count; r.bound = fmin(bound, mx);
+    return r;
+  }
   int newcount = 0; double mx = 0.0;
   for (int base = 0; base < count; base += 32) {
     const int i = base + lane;
@@ -186,13 +200,15 @@ __device__ __noinline__ Sel cut(const WarpBuf b, int count, double bound, int k,
     __syncwarp();
   }
   for (int o = 16; o > 0; o >>= 1) mx = fmax(mx, __shfl_xor_sync(FULL, mx, o));
-  Sel r; r.count = newcount; r.bound = fmin(bound, mx);
+  Sel r; r.count = newcount; r.raw = newcount; r.bound = fmin(bound, mx);
   return r;
 }
 
 // after the traversal: exactly the k nearest (or everything found, if fewer); bound = largest kept d2 when k are held
-__device__ __forceinline__ void finish(const WarpBuf &b, int &count, double &bound, int k, int lane) {
-  if (count > k) { const Sel r = cut(b, count, bound, k, lane); count = r.count; bound = r.bound; return; }
+// (raw: buffer entries to look at -- more than count after a cut that did not compact; dropped ones have d2 < 0)
+__device__ __forceinline__ void finish(const WarpBuf &b, int &count, int &raw, double &bound, int k, int lane, bool compact) {
+  raw = count;
+  if (count > k) { const Sel r = cut(b, count, bound, k, lane, compact); count = r.count; raw = r.raw; bound = r.bound; return; }
   if (count < k) return;
   double mx = 0.0;
   for (int i = lane; i < count; i += 32) mx = fmax(mx, b.d2(i));
@@ -208,7 +224,7 @@ __device__ __forceinline__ void append(const WarpBuf &b, int &count, double &bou
   if (pred) { b.set_d2(pos, d2); b.set_slot(pos, slot); }
   count += __popc(mask);
   __syncwarp();
-  if (count > b.limit) { const Sel r = cut(b, count, bound, k, lane); count = r.count; bound = r.bound; }
+  if (count > b.limit) { const Sel r = cut(b, count, bound, k, lane, true); count = r.count; bound = r.bound; }
 }
 
 struct P3 { double x, y, z; };
@@ -267,7 +283,7 @@ gather_kernel(PhotonMapDev m, const double *__restrict__ lut, const GiGatherQuer
     const double *qp = (const double *)(queries + qi);
     const double mine = lane < 17 ? qp[lane] : 0.0;
     const double qx = __shfl_sync(FULL, mine, 0), qy = __shfl_sync(FULL, mine, 1), qz = __shfl_sync(FULL, mine, 2);
-    int count = 0;
+    int count = 0, raw = 0;
     double bound = ga.r2;
     if (n > 0) {
       double init = fmin(ga.r2, guess);
@@ -341,7 +357,7 @@ gather_kernel(PhotonMapDev m, const double *__restrict__ lut, const GiGatherQuer
                     count += na + __popc(mb);
                     __syncwarp();
                     if (count > b.limit) {
-                      const Sel r = cut(b, count, bound, k, lane); count = r.count; bound = r.bound;
+                      const Sel r = cut(b, count, bound, k, lane, true); count = r.count; bound = r.bound;
                       todo &= __ballot_sync(FULL, (double)kf <= bound);
                     }
                   }
@@ -368,7 +384,7 @@ gather_kernel(PhotonMapDev m, const double *__restrict__ lut, const GiGatherQuer
           s = (((root + 1) << h) - 1) + (uint32_t)who;
           g++; enter = true;
         }
-        finish(b, count, bound, k, lane);
+        finish(b, count, raw, bound, k, lane, idx_out != nullptr);
         if (count >= k || init >= ga.r2) break;
         init = init > 0.0 ? fmin(ga.r2, init * 4.0) : ga.r2;            // the guess was too small: widen and retry
       }
@@ -391,7 +407,9 @@ gather_kernel(PhotonMapDev m, const double *__restrict__ lut, const GiGatherQuer
       double c1 = 1.0, c2 = 1.0, total_w = 0.0;
       if (ga.filter == GI_FILTER_CONE) c1 = 1.0 / (ga.fk * sqrt(max_d2));
       else if (ga.filter == GI_FILTER_GAUSS) { c1 = exp(-ga.fb); c2 = 1.0 / (2.0 * max_d2); }
-      for (int i = lane; i < found; i += 32) {
+      for (int i = lane; i < raw; i += 32) {
+        const double d2i = b.d2(i);
+        if (d2i < 0.0) continue;                                                // dropped by the last cut
         const double2 *rec = m.srec + 2 * (size_t)b.slot(i);
         const double2 ra = rec[0], rb = rec[1];
         const double ix = ra.x, iy = ra.y, iz = rb.x;
@@ -400,7 +418,7 @@ gather_kernel(PhotonMapDev m, const double *__restrict__ lut, const GiGatherQuer
         if ((cos_theta < 0 && perp < 0) || (cos_theta > 0 && perp > 0)) continue;
         const uint32_t e = sh.x >> 24;
         if (e == 0) { if (ga.filter == GI_FILTER_GAUSS) {
-            total_w += 1.0 - (1.0 - pow(c1, c2 * b.d2(i))) / (1.0 - c1); } continue; }
+            total_w += 1.0 - (1.0 - pow(c1, c2 * d2i)) / (1.0 - c1); } continue; }
         const double inv = __longlong_as_double((long long)(e - 136 + 1023) << 52);   // ldexp(1.0, e - 128 - 8)
         double rgb[3] = {(double)(sh.x & 0xff) * inv, (double)((sh.x >> 8) & 0xff) * inv, (double)((sh.x >> 16) & 0xff) * inv};
         double cos_alpha = (bx * -ix) + (by * -iy) + (bz * -iz);
@@ -409,10 +427,10 @@ gather_kernel(PhotonMapDev m, const double *__restrict__ lut, const GiGatherQuer
         const double ap = fabs(perp);
         for (int c = 0; c < 3; c++) rgb[c] *= ap * kd[c] + pw * ks[c];
         if (ga.filter == GI_FILTER_CONE) {
-          const double w = 1.0 - c1 * sqrt(b.d2(i));
+          const double w = 1.0 - c1 * sqrt(d2i);
           for (int c = 0; c < 3; c++) rgb[c] *= w;
         } else if (ga.filter == GI_FILTER_GAUSS) {
-          const double w = 1.0 - (1.0 - pow(c1, c2 * b.d2(i))) / (1.0 - c1);
+          const double w = 1.0 - (1.0 - pow(c1, c2 * d2i)) / (1.0 - c1);
           for (int c = 0; c < 3; c++) rgb[c] *= w;
           total_w += w;
         }
