@@ -221,7 +221,8 @@ int gi_gather_batch_device(GiContext *ctx, int map, const GiGatherQuery *d_queri
   ga.fk = params ? params->filter_const_k : 1.0;
   ga.guess_factor = 1.1;
   ga.slack = ga.cap;
-  ga.max_warps = 0; ga.key_rows = 0;
+  ga.max_warps = 0; ga.key_rows = 0; ga.range = 0;
+  if (const char *e = getenv("GI_GATHER_RANGE")) ga.range = atoi(e);
   if (const char *e = getenv("GI_GATHER_WARPS")) ga.max_warps = atoi(e);
   if (const char *e = getenv("GI_CUT_SLACK")) ga.slack = atoi(e);
   if (ga.slack < 32) ga.slack = 32;

@@ -104,6 +104,7 @@ void gi_destroy(GiContext *ctx) {
     if (ctx->pipe[i]) cudaStreamDestroy(ctx->pipe[i]);
   }
   for (int j = 0; j < 5; j++) ctx->order_ws[2][j].release();
+  cudaFree(ctx->gather_counters);
   if (ctx->stream) cudaStreamDestroy(ctx->stream);
   delete ctx;
 }

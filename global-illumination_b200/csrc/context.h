@@ -44,6 +44,7 @@ struct GiContext {
   cudaStream_t pipe[2] = {nullptr, nullptr};
   GiScratch stage[2][4];                      // per slot: input, and up to three outputs
   GiScratch order_ws[3][5];                   // query_order.cu, per stream slot (pipe[0], pipe[1], any other): keys x2, order x2, sort temp
+  void *gather_counters = nullptr;            // gather.cu: launch-wide chunk counters, one per stream slot
   void *render_ws = nullptr;                  // render.cu's device workspace, created by the first gi_render
   void (*render_ws_free)(void *) = nullptr;
   uint64_t queue_overflows = 0;               // render path batches repeated because a gather-request queue ran full

@@ -250,12 +250,12 @@ __device__ __forceinline__ double box_dist2(const double *__restrict__ cbox_lane
 template <bool DEEP>          // DEEP: bottom groups are 6 levels deep (m.hb == 6), a second round of 32 photons
 __global__ void __launch_bounds__(GI_GATHER_MAX_WARPS * 32, 1)
 gather_kernel(PhotonMapDev m, const double *__restrict__ lut, const GiGatherQuery *__restrict__ queries,
-              const uint32_t *__restrict__ order, uint64_t nq, GatherArgs ga, int32_t *idx_out, int32_t *count_out, double *rgb_out) {
+              const uint32_t *__restrict__ order, uint64_t nq, GatherArgs ga, unsigned long long *work_counter, int32_t *idx_out,
+              int32_t *count_out, double *rgb_out) {
   extern __shared__ double smem[];
   const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
   WarpBuf b; b.cap = ga.cap; b.orig = m.orig;
   { const int room = ga.cap - (DEEP ? 64 : 32); b.limit = room < ga.k + ga.slack ? room : ga.k + ga.slack; }   // 32 (64) arrive at once
-  const int nwarps = blockDim.x >> 5;
   {
     uint32_t base = (uint32_t)__cvta_generic_to_shared(smem) + (uint32_t)warp * (uint32_t)GI_WARP_BYTES(ga.cap, ga.key_rows);
     asm volatile("" : "+r"(base));                          // opaque: keep it in a register instead of re-deriving it
@@ -270,12 +270,36 @@ gather_kernel(PhotonMapDev m, const double *__restrict__ lut, const GiGatherQuer
   const int G = m.groups, gp = m.groups - 2;                // rows; gp = the row whose children are the bottom groups
   const uint32_t bottom_first = (1u << m.glevel[G - 1]) - 1u;                                   // root slot of the first bottom group
   const uint32_t bottom_delta = m.goff[G - 1] - bottom_first;                                   // bottom group index - root slot
-  const uint64_t warps_total = (uint64_t)gridDim.x * nwarps;
+  // Work distribution: queries cost very different amounts (a caustic map is dense in a few places), so chunks are
+  // handed out dynamically -- but in RANGES of consecutive chunks per CTA, so that the warps of an SM stay on
+  // neighbouring queries (L1).  A warp takes a ticket from the CTA's counter; the warp whose ticket opens a new range
+  // fetches it from the launch-wide counter and publishes it (generation-tagged slot), the others wait that moment.
+  __shared__ unsigned int s_ticket;
+  __shared__ volatile unsigned int s_gen[8];
+  __shared__ volatile unsigned long long s_base[8];
+  if (threadIdx.x == 0) s_ticket = 0;
+  if (threadIdx.x < 8) s_gen[threadIdx.x] = 0;
+  __syncthreads();
+  const unsigned int range = (unsigned int)ga.range;
   const uint64_t nchunks = (nq + GI_GATHER_CHUNK - 1) / GI_GATHER_CHUNK;
   // Search radius carried from one query to the next: consecutive queries of a chunk are neighbouring pixels, so the
   // previous k-th distance (x guess_factor in area) is tried first and widened only if fewer than k photons are inside.
   double guess = ga.r2;
-  for (uint64_t chunk = (uint64_t)blockIdx.x * nwarps + warp; chunk < nchunks; chunk += warps_total)
+  while (true) {
+  unsigned long long chunk = 0;
+  if (lane == 0) {
+    const unsigned int t = atomicAdd(&s_ticket, 1u);
+    const unsigned int rn = t / range, off = t - rn * range, sl = rn & 7u;
+    if (off == 0) {
+      const unsigned long long base = atomicAdd(work_counter, (unsigned long long)range);
+      s_base[sl] = base; __threadfence_block(); s_gen[sl] = rn + 1u;
+    } else {
+      while (s_gen[sl] < rn + 1u) { }                     // brief: the opener already holds ticket rn * range
+    }
+    chunk = s_base[sl] + off;
+  }
+  chunk = __shfl_sync(FULL, chunk, 0);
+  if (chunk >= nchunks) break;
   for (uint64_t qs = chunk * GI_GATHER_CHUNK; qs < nq && qs < (chunk + 1) * GI_GATHER_CHUNK; qs++) {
     // ---- query record: 17 doubles, one per lane, broadcast by shuffle.  order[] (optional) lists the queries along a
     //      Morton curve, so that the queries of a warp and of a CTA are neighbours in space; results go to slot qi.
@@ -458,9 +482,19 @@ gather_kernel(PhotonMapDev m, const double *__restrict__ lut, const GiGatherQuer
     }
     __syncwarp();
   }
+  }   // chunks
 }
 
-// One CTA per SM (persistent, warps stride over chunks of consecutive queries): the warps of an SM then work on
+// launch-wide chunk counter, one per stream slot of the context (pipe[0], pipe[1], any other stream)
+static unsigned long long *work_counter(GiContext *ctx, cudaStream_t st) {
+  if (!ctx->gather_counters && cudaMalloc(&ctx->gather_counters, 3 * sizeof(unsigned long long)) != cudaSuccess) {
+    ctx->gather_counters = nullptr;
+    return nullptr;
+  }
+  return (unsigned long long *)ctx->gather_counters + (st == ctx->pipe[0] ? 0 : (st == ctx->pipe[1] ? 1 : 2));
+}
+
+// One CTA per SM (persistent, warps take chunks of consecutive queries): the warps of an SM then work on
 // neighbouring queries and share the kd-tree groups they read through L1.  As many warps as the candidate buffers
 // leave room for: 24 at the default estimate sizes (132 KB of shared memory, the rest of the 256 KB stays L1).
 cudaError_t launch_gather(GiContext *ctx, const PhotonMapDev &m, const double *d_lut, const GiGatherQuery *d_q,
@@ -484,10 +518,22 @@ cudaError_t launch_gather(GiContext *ctx, const PhotonMapDev &m, const double *d
     if (e != cudaSuccess) return e;
     configured[deep] = smem;
   }
+  // range of consecutive chunks a CTA fetches at a time: 4 per warp, fewer when the launch is small (balance)
+  {
+    uint64_t r = nchunks / ((uint64_t)ctx->sm_count * 8);
+    r = r / warps * warps;
+    if (r < (uint64_t)warps) r = warps;
+    if (r > (uint64_t)4 * warps) r = (uint64_t)4 * warps;
+    ga.range = (int)r;
+    if (ga_in.range > 0) ga.range = ga_in.range;
+  }
+  unsigned long long *counter = work_counter(ctx, st);
+  if (!counter) return cudaErrorMemoryAllocation;
+  { cudaError_t e = cudaMemsetAsync(counter, 0, sizeof(unsigned long long), st); if (e != cudaSuccess) return e; }
   const uint64_t want = (nchunks + warps - 1) / warps;
   const unsigned grid = (unsigned)(want < (uint64_t)ctx->sm_count ? want : (uint64_t)ctx->sm_count);
-  if (deep) gather_kernel<true><<<grid, warps * 32, smem, st>>>(m, d_lut, d_q, d_order, nq, ga, d_idx, d_count, d_rgb);
-  else gather_kernel<false><<<grid, warps * 32, smem, st>>>(m, d_lut, d_q, d_order, nq, ga, d_idx, d_count, d_rgb);
+  if (deep) gather_kernel<true><<<grid, warps * 32, smem, st>>>(m, d_lut, d_q, d_order, nq, ga, counter, d_idx, d_count, d_rgb);
+  else gather_kernel<false><<<grid, warps * 32, smem, st>>>(m, d_lut, d_q, d_order, nq, ga, counter, d_idx, d_count, d_rgb);
   ctx->launches++;
   return cudaGetLastError();
 }

@@ -13,6 +13,7 @@ struct GatherArgs {
   int cap;                         /* candidate slots per warp: a multiple of 32, > k + 32; a power of two if indices are wanted */
   int filter;                      /* GiFilter */
   int max_warps;                   /* test / tuning hook: at most this many warps per CTA (0 = as many as fit) */
+  int range;                       /* chunks a CTA fetches at a time from the launch-wide counter (0 = chosen by launch_gather) */
   int key_rows;                    /* set by launch_gather: group rows above the bottom-parent row */
   int slack;                       /* the candidate buffer is cut back to k once it holds more than k + slack */
   double guess_factor;             /* next query's first search radius^2 = this factor x the last k-th d^2 */

@@ -117,3 +117,41 @@ def test_full_size_properties(gpu_ctx):
         else:
             order = inside[np.lexsort((inside, d2[inside]))][:k]
             assert np.array_equal(np.sort(order), ids)
+
+
+def check_rgb(ref, got, rtol=1e-9):
+    rcnt, rrgb = ref[1], ref[2]; cnt, rgb = got[1], got[2]
+    assert np.array_equal(rcnt, cnt)
+    scale = np.abs(rrgb).max(axis=1, keepdims=True)
+    assert (np.abs(rgb - rrgb) <= rtol * scale + 1e-300).all()
+
+
+@pytest.mark.parametrize("n,k,r,nq", [(100000, 225, 0.05, 6000), (20000, 50, 0.3, 5000), (3000, 512, 2.0, 4500)])
+def test_radiance_only_path_on_sorted_batches(gpu_ctx, oracle, n, k, r, nq):
+    """What the renderer and the bench run: no index output (the last cut marks instead of compacting, the candidate
+    buffer is not a power of two) and batches of >= 4096 queries, which are walked along a Morton curve."""
+    ph = synthetic_photons(n, seed=7 * n + k)
+    q = surface_queries(nq, seed=k + 1)
+    gpu_ctx.load_photons(gi_b200.GI_MAP_CAUSTIC, ph)
+    gpu_ctx.build_maps()
+    for filt in (0, 1, 2):
+        ref = oracle.gather(ph, q, k, r, filt, threads=os.cpu_count() or 8)
+        check_rgb(ref, gpu_ctx.gather(gi_b200.GI_MAP_CAUSTIC, q, k, r, filt, want_idx=False))
+        check(ref, gpu_ctx.gather(gi_b200.GI_MAP_CAUSTIC, q, k, r, filt))
+
+
+def test_dense_blob_seen_from_a_distance(gpu_ctx, oracle):
+    """A caustic map is dense in a few places.  For a query at some distance from such a blob every candidate lies in a
+    thin shell of d^2: the cut's histogram must refine the crowded bin (levels) instead of falling back to ranking."""
+    rng = np.random.default_rng(11)
+    ph = synthetic_photons(62000, 21)
+    ph["position"][2000:] = np.array([0.3, -1.0, 0.2]) + rng.normal(scale=[2e-3, 0.0, 2e-3], size=(60000, 3))   # blob on the floor
+    q = surface_queries(512, seed=5)
+    ang = rng.uniform(0, 2 * np.pi, 512); dist = rng.uniform(0.0, 0.25, 512)
+    q["p"] = np.array([0.3, -1.0, 0.2]) + np.stack([np.cos(ang) * dist, np.zeros(512), np.sin(ang) * dist], axis=1)
+    gpu_ctx.load_photons(gi_b200.GI_MAP_CAUSTIC, ph)
+    gpu_ctx.build_maps()
+    for k, r in ((225, 0.225), (50, 0.4)):
+        ref = oracle.gather(ph, q, k, r, 0, threads=os.cpu_count() or 8)
+        check(ref, gpu_ctx.gather(gi_b200.GI_MAP_CAUSTIC, q, k, r, 0))
+        check_rgb(ref, gpu_ctx.gather(gi_b200.GI_MAP_CAUSTIC, q, k, r, 0, want_idx=False))
