@@ -117,18 +117,31 @@ __device__ __noinline__ Sel rank_select(const WarpBuf b, int count, double bound
   return r;
 }
 
+// Histogram bin of a candidate in the cut: monotone in d2, LOGARITHMIC in the gap to the bound -- 8 bins per octave of
+// bound - d2, read off the exponent and the top three mantissa bits of the gap, relative to those of the bound (bin 0:
+// gap = bound, bin 127: gap < bound / 65536).  Photons on a surface are uniform in d2 and put a handful of candidates
+// into the bin of the k-th one; a query at some distance from a dense blob of a caustic map sees ALL its candidates in a
+// thin shell of d2 just below the bound, which a linear histogram over [0, bound) cannot resolve (every cut then fell
+// to the O(n^2) ranking: 30-50 ms launches in a cornell frame) -- the logarithmic bins resolve a shell of any thickness
+// down to bound / 65536.  Dropped candidates (d2 = -1) land in bin 0; every caller tests d2 >= 0 as well.
+__device__ __forceinline__ int cut_bin(double d, double bound, int base) {
+  int v = (__double2hiint(bound - d) >> 17) - base;
+  v = v < 0 ? 0 : (v > GI_HIST_BINS - 1 ? GI_HIST_BINS - 1 : v);
+  return GI_HIST_BINS - 1 - v;
+}
+
 // Exact cut of the candidate buffer to the k smallest by (d2, orig).  Requires count > k.
-// A 128-bin histogram of d2 / bound locates the bin B that holds the k-th candidate; bins below B are kept whole,
-// and inside B (a handful of candidates, since surface photons are uniform in d2) each lane ranks one candidate
+// A 128-bin histogram (cut_bin) locates the bin B that holds the k-th candidate; bins below B are kept whole,
+// and inside B (about a dozen candidates) each lane ranks one candidate
 // against the others by shuffles.  The bound becomes the largest kept d2.  compact = false (the last cut of a search
 // whose indices are not wanted): dropped candidates are only marked with d2 = -1 and stay where they are (raw = count).
 __device__ __noinline__ Sel cut(const WarpBuf b, int count, double bound, int k, int lane, bool compact) {
   if (!(bound > 0.0)) return rank_select(b, count, bound, k, lane);
   for (int i = lane; i < GI_HIST_BINS; i += 32) b.set_hist(i, 0);
   __syncwarp();
-  const double scale = (double)GI_HIST_BINS / bound;
+  const int scale = (__double2hiint(bound) >> 17) - (GI_HIST_BINS - 1);      // cut_bin: code of the gap that maps to bin 0
   for (int i = lane; i < count; i += 32) {
-    int bin = (int)(b.d2(i) * scale); bin = bin > GI_HIST_BINS - 1 ? GI_HIST_BINS - 1 : bin;
+    const int bin = cut_bin(b.d2(i), bound, scale);
     red_u32(b.a_hist + 4u * (uint32_t)bin, 1u);
   }
   __syncwarp();
@@ -154,7 +167,7 @@ __device__ __noinline__ Sel cut(const WarpBuf b, int count, double bound, int k,
     for (int base = 0; base < count; base += 32) {
       const int i = base + lane;
       bool inb = false;
-      if (i < count) { int bin = (int)(b.d2(i) * scale); bin = bin > GI_HIST_BINS - 1 ? GI_HIST_BINS - 1 : bin; inb = bin == B; }
+      if (i < count) { const int bin = cut_bin(b.d2(i), bound, scale); inb = bin == B; }
       const unsigned mk = __ballot_sync(FULL, inb);
       if (inb) b.set_hist(c + __popc(mk & ((1u << lane) - 1u)), (uint32_t)i);
       c += __popc(mk);
@@ -174,7 +187,7 @@ __device__ __noinline__ Sel cut(const WarpBuf b, int count, double bound, int k,
     double mx = 0.0;
     for (int i = lane; i < count; i += 32) {
       const double d = b.d2(i);
-      int bin = (int)(d * scale); bin = bin > GI_HIST_BINS - 1 ? GI_HIST_BINS - 1 : bin;
+      const int bin = cut_bin(d, bound, scale);
       if (bin > B) b.set_d2(i, -1.0);
       else if (d >= 0.0) mx = fmax(mx, d);
     }
@@ -189,7 +202,7 @@ __device__ __noinline__ Sel cut(const WarpBuf b, int count, double bound, int k,
     double d = 0.0; uint32_t sl = 0; bool keep = false;
     if (i < count) {
       d = b.d2(i); sl = b.slot(i);
-      int bin = (int)(d * scale); bin = bin > GI_HIST_BINS - 1 ? GI_HIST_BINS - 1 : bin;
+      const int bin = cut_bin(d, bound, scale);
       keep = d >= 0.0 && bin <= B;
     }
     const unsigned mk = __ballot_sync(FULL, keep);
