@@ -23,7 +23,7 @@ static const uint32_t PMAP_MAGIC = 0x4d504947u;   // "GIPM"
 
 void free_map(PhotonMapStore &m) {
   cudaFree((void *)m.dev.px); cudaFree((void *)m.dev.py); cudaFree((void *)m.dev.pz);
-  cudaFree((void *)m.dev.node); cudaFree((void *)m.dev.shade); cudaFree((void *)m.dev.orig); cudaFree((void *)m.dev.cbox); cudaFree((void *)m.dev.gpos); cudaFree((void *)m.dev.srec);
+  cudaFree((void *)m.dev.node); cudaFree((void *)m.dev.shade); cudaFree((void *)m.dev.orig); cudaFree((void *)m.dev.cbox); cudaFree((void *)m.dev.gpos); cudaFree((void *)m.dev.srec); cudaFree((void *)m.dev.hint);
   cudaFree(m.raw);
   m = PhotonMapStore();
 }

@@ -229,6 +229,7 @@ cudaError_t build_photon_map(GiContext *ctx, PhotonMapStore &m, uint64_t n, cons
   uint32_t *heap_photon = nullptr, *bounds = nullptr; float *split = nullptr; uint8_t *axis = nullptr;
   void *tmp = nullptr; size_t tmp_bytes = 0;
   double *px = nullptr, *py = nullptr, *pz = nullptr; uint2 *node = nullptr, *shade = nullptr; uint32_t *orig = nullptr;
+  double *hint = nullptr;
   double *cbox = nullptr, *gpos = nullptr; double2 *srec = nullptr; uint64_t n_groups = 0, n_upper = 0;
   PhotonMapDev d{};
   const int B = 256;
@@ -285,6 +286,9 @@ cudaError_t build_photon_map(GiContext *ctx, PhotonMapStore &m, uint64_t n, cons
   d.x6_blocks = d.hb > GI_GROUP_LEVELS ? (uint32_t)((n - ((((uint64_t)1 << (L - 1)) - 1)) + 31) / 32) : 0u;
   CKB(cudaMalloc(&gpos, 768 * (n_groups + d.x6_blocks)));
   d.cbox = cbox; d.gpos = gpos;
+  CKB(cudaMalloc(&hint, 2 * sizeof(double)));
+  CKB(cudaMemsetAsync(hint, 0, 2 * sizeof(double), st));
+  d.hint = hint;
   if (d.x6_blocks) { level6_kernel<<<(unsigned)(((uint64_t)d.x6_blocks * 32 + B - 1) / B), B, 0, st>>>(d, gpos); ctx->launches++; }
   if (n_upper) { cbox_init_kernel<<<(unsigned)((n_upper * 192 + B - 1) / B), B, 0, st>>>(cbox, n_upper * 192); ctx->launches++; }
   for (int g = d.groups - 1; g >= 0; g--) {
@@ -307,11 +311,11 @@ cudaError_t build_photon_map(GiContext *ctx, PhotonMapStore &m, uint64_t n, cons
   }
   m.dev = d;
   m.built = true;
-  px = py = pz = nullptr; node = shade = nullptr; orig = nullptr; cbox = nullptr; gpos = nullptr; srec = nullptr;
+  px = py = pz = nullptr; node = shade = nullptr; orig = nullptr; cbox = nullptr; gpos = nullptr; srec = nullptr; hint = nullptr;
 done:
   for (int k = 0; k < 2; k++) { cudaFree(keys[k]); cudaFree(vals[k]); }
   cudaFree(heap_photon); cudaFree(split); cudaFree(bounds); cudaFree(axis); cudaFree(tmp);
-  cudaFree(px); cudaFree(py); cudaFree(pz); cudaFree(node); cudaFree(shade); cudaFree(orig); cudaFree(cbox); cudaFree(gpos); cudaFree(srec);
+  cudaFree(px); cudaFree(py); cudaFree(pz); cudaFree(node); cudaFree(shade); cudaFree(orig); cudaFree(cbox); cudaFree(gpos); cudaFree(srec); cudaFree(hint);
   return err;
 }
 

@@ -40,6 +40,8 @@ struct PhotonMapDev {
   int32_t groups, h0, hb;         /* rows of groups; depth of the top group; depth of the bottom-row groups (one row: groups = 1, hb = levels) */
   int32_t glevel[GI_MAX_GROUPS];  /* tree level of the group roots of row g (glevel[0] = 0) */
   uint32_t goff[GI_MAX_GROUPS];   /* index of the first group of row g */
+  double *hint;                   /* {estimate size, k-th d2 x guess factor} left behind by the last gather launch on this map: */
+                                  /* the first search radius of the next launch's warps (zeroed = none yet)                */
   const uint2 *shade;             /* heap order: x = rgbe bytes (r | g<<8 | b<<16 | e<<24), y = direction code */
   const double2 *srec;            /* heap order, 32 B: {dir.x, dir.y}, {dir.z, bits: rgbe | code << 32}: the estimate's view of a */
                                   /* photon -- the incident direction already looked up (photon_utils.cpp:253-272), one sector  */
