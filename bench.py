@@ -462,6 +462,7 @@ def frame_report(args, torch, dist, ctx, dev, rank, world):
     scene = gi_b200.HostScene(os.path.join(GOLDEN, args.frame_scene + ".gisc"))
     ctx.upload_scene(scene)
     W = H = args.frame_res
+    split = None
     for attempt in range(2):        # the first pass pays one-time costs (workspace allocation, NCCL channel set-up); report the second
         params, _ = gi_b200.parse_flags(["-seed", "1"])
         torch.cuda.synchronize()
@@ -475,6 +476,7 @@ def frame_report(args, torch, dist, ctx, dev, rank, world):
             st = ctx.trace_photons(params)
             params.indirect_illum, params.caustic_illum, params.direct_photon_illum = st.indirect_illum, st.caustic_illum, st.direct_photon_illum
             stored = (int(st.global_stored), int(st.caustic_stored))
+            split = {"trace_ms": float(st.trace_ms), "kd_build_ms": float(st.build_ms)}
         torch.cuda.synchronize(); t1 = time.perf_counter()
         if world > 1:
             img, rs = multi_gpu.render_sharded(ctx, params, W, H, args.frame_aa, dist, torch, dev)
@@ -491,7 +493,7 @@ def frame_report(args, torch, dist, ctx, dev, rank, world):
     total = sum(counters.values())
     return {"workload": f"input/{args.frame_scene}.scn {W}x{H} -aa {args.frame_aa}, all flags default (BASELINE.json configs[0]): "
                         "gi_trace_photons + gi_render, u8 frame back on the host",
-            "photon_pass_ms": photon_ms, "render_ms": render_ms, "frame_ms": photon_ms + render_ms, "render_device_ms": render_kernel_ms,
+            "photon_pass_ms": photon_ms, "photon_pass_split": split, "render_ms": render_ms, "frame_ms": photon_ms + render_ms, "render_device_ms": render_kernel_ms,
             "photons_stored": {"global": stored[0], "caustic": stored[1]}, "ray_ops": total, "counters": counters,
             "mray_ops_per_s": total / (render_ms * 1e-3) / 1e6,
             "gathers_per_s": (counters["indirect_samples"] + counters["caustic_samples"]) / (render_ms * 1e-3),

@@ -85,6 +85,14 @@ int gi_create(int device, GiContext **out) {
   if (prop.major < 10) { set_error("gi_create: this library is built for sm_100a (B200) only"); return 1; }
   GiContext *ctx = new GiContext();
   ctx->device = device; ctx->sm_count = prop.multiProcessorCount;
+  {
+    // keep memory freed to the device's stream-ordered pool (kd-tree build temporaries) instead of returning it to the driver
+    cudaMemPool_t pool;
+    if (cudaDeviceGetDefaultMemPool(&pool, ctx->device) == cudaSuccess) {
+      unsigned long long keep = ~0ull;
+      cudaMemPoolSetAttribute(pool, cudaMemPoolAttrReleaseThreshold, &keep);
+    }
+  }
   if (!cuda_ok(cudaStreamCreateWithFlags(&ctx->stream, cudaStreamNonBlocking), "cudaStreamCreate") ||
       !cuda_ok(cudaStreamCreateWithFlags(&ctx->pipe[0], cudaStreamNonBlocking), "cudaStreamCreate") ||
       !cuda_ok(cudaStreamCreateWithFlags(&ctx->pipe[1], cudaStreamNonBlocking), "cudaStreamCreate")) { delete ctx; return 1; }

@@ -235,11 +235,13 @@ cudaError_t build_photon_map(GiContext *ctx, PhotonMapStore &m, uint64_t n, cons
   const int B = 256;
   const unsigned G = (unsigned)((n + B - 1) / B);
   int cur = 0;
-  for (int k = 0; k < 2; k++) { CKB(cudaMalloc(&keys[k], 8 * n)); CKB(cudaMalloc(&vals[k], 4 * n)); }
-  CKB(cudaMalloc(&heap_photon, 4 * n)); CKB(cudaMalloc(&split, 4 * n)); CKB(cudaMalloc(&bounds, 24 * n));
-  CKB(cudaMalloc(&axis, n));
+  // temporaries come from the device's stream-ordered pool (gi_create keeps freed pool memory): a frame rebuilds its
+  // maps every time, and cudaMalloc / cudaFree of ~1 GB cost more than the build itself on a busy device
+  for (int k = 0; k < 2; k++) { CKB(cudaMallocAsync(&keys[k], 8 * n, st)); CKB(cudaMallocAsync(&vals[k], 4 * n, st)); }
+  CKB(cudaMallocAsync(&heap_photon, 4 * n, st)); CKB(cudaMallocAsync(&split, 4 * n, st)); CKB(cudaMallocAsync(&bounds, 24 * n, st));
+  CKB(cudaMallocAsync(&axis, n, st));
   CKB(cub::DeviceRadixSort::SortPairs(nullptr, tmp_bytes, keys[0], keys[1], vals[0], vals[1], (int)n, 0, 64, st));
-  CKB(cudaMalloc(&tmp, tmp_bytes));
+  CKB(cudaMallocAsync(&tmp, tmp_bytes, st));
   init_kernel<<<G, B, 0, st>>>(n, keys[0], vals[0]);
   ctx->launches++;
   for (int level = 0; level < L; level++) {
@@ -313,8 +315,10 @@ cudaError_t build_photon_map(GiContext *ctx, PhotonMapStore &m, uint64_t n, cons
   m.built = true;
   px = py = pz = nullptr; node = shade = nullptr; orig = nullptr; cbox = nullptr; gpos = nullptr; srec = nullptr; hint = nullptr;
 done:
-  for (int k = 0; k < 2; k++) { cudaFree(keys[k]); cudaFree(vals[k]); }
-  cudaFree(heap_photon); cudaFree(split); cudaFree(bounds); cudaFree(axis); cudaFree(tmp);
+  {
+    void *temps[] = {keys[0], keys[1], vals[0], vals[1], heap_photon, split, bounds, axis, tmp};
+    for (void *t : temps) if (t) cudaFreeAsync(t, st);
+  }
   cudaFree(px); cudaFree(py); cudaFree(pz); cudaFree(node); cudaFree(shade); cudaFree(orig); cudaFree(cbox); cudaFree(gpos); cudaFree(srec); cudaFree(hint);
   return err;
 }
