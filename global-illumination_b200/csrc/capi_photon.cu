@@ -248,17 +248,21 @@ int gi_gather_batch(GiContext *ctx, int map, const GiGatherQuery *queries, uint6
   if (!queries) { set_error("gi_gather_batch: null query buffer"); return 1; }
   if (k < 1 || k > GI_MAX_K) { set_error("gi_gather_batch: estimate size must be in [1, 512]"); return 1; }
   GI_CUDA(cudaSetDevice(ctx->device));
-  // two-slot pipeline like gi_intersect_batch: chunks of 2^20 queries (143 MB in, 29 MB out)
-  uint64_t chunk = 1ull << 20;
-  if (const char *e = getenv("GI_PIPE_CHUNK_LOG2")) { const int l = atoi(e); if (l >= 12 && l <= 24) chunk = 1ull << l; }
+  // two-slot pipeline like gi_intersect_batch.  Chunks grow from 2^18 to 2^21 queries (2^20 with index output: its
+  // staging buffer is k times larger): a small first chunk starts the kernels early, large later ones keep the
+  // launches efficient (a persistent launch pays a ramp and a tail of a few hundred queries per warp).
+  uint64_t cmax = idx_out ? 1ull << 20 : 1ull << 21;
+  if (const char *e = getenv("GI_PIPE_CHUNK_LOG2")) { const int l = atoi(e); if (l >= 12 && l <= 24) cmax = 1ull << l; }
+  uint64_t chunk = cmax < (1ull << 18) ? cmax : 1ull << 18;
   int rc = 0;
-  for (uint64_t o = 0, c = 0; o < n && rc == 0; o += chunk, c++) {
+  for (uint64_t o = 0, c = 0; o < n && rc == 0; o += chunk, chunk = chunk * 2 < cmax ? chunk * 2 : cmax, c++) {
     const uint64_t m = n - o < chunk ? n - o : chunk;
     const int slot = (int)(c & 1);
     cudaStream_t st = ctx->pipe[slot];
     GiScratch *sc = ctx->stage[slot];
-    if (!sc[0].fit(sizeof(GiGatherQuery) * chunk) || (rgb_out && !sc[1].fit(sizeof(double) * 3 * chunk)) ||
-        (count_out && !sc[2].fit(sizeof(int32_t) * chunk)) || (idx_out && !sc[3].fit(sizeof(int32_t) * chunk * k))) {
+    const uint64_t room = n < cmax ? n : cmax;             // sized once for the largest chunk: growing means cudaFree + cudaMalloc
+    if (!sc[0].fit(sizeof(GiGatherQuery) * room) || (rgb_out && !sc[1].fit(sizeof(double) * 3 * room)) ||
+        (count_out && !sc[2].fit(sizeof(int32_t) * room)) || (idx_out && !sc[3].fit(sizeof(int32_t) * room * k))) {
       set_error("gi_gather_batch: out of device memory"); rc = 1; break;
     }
     GiGatherQuery *d_q = (GiGatherQuery *)sc[0].p;
