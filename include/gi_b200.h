@@ -260,6 +260,10 @@ int gi_gather_batch(GiContext *ctx, int map, const GiGatherQuery *queries, uint6
 int gi_gather_batch_device(GiContext *ctx, int map, const GiGatherQuery *d_queries, uint64_t n, int k, double r,
                            int filter, const GiParams *params, int32_t *d_idx, int32_t *d_count, double *d_rgb,
                            void *stream);
+/* The _device variant enqueues on `stream` and returns without waiting.  Batches of >= 4096 queries are processed along a
+ * Morton curve (results stay at the caller's index); the ordering scratch, the chunk counter and the radius hint live
+ * in the context, so calls on ONE context must not run concurrently on different caller streams (order them with
+ * events, or use one context per stream).  n < 2^31 per device batch; the host-buffer call has no such limit. */
 
 /* The irradiance cache (-cache).  gi_build_maps with params->irradiance_cache (and indirect_illum or
  * direct_photon_illum) set runs the pre-pass of MapPhotons (photonmap.cpp:380-411) once per loaded global map: every
