@@ -188,8 +188,9 @@ __global__ void __launch_bounds__(256) emit_filter_kernel(ShadeEnv env, Round rd
 // Persistent photon tracer.  Every lane walks one photon; a lane whose photon ends takes the next one at once, so a
 // warp is never held up by its longest walk (most walks end at the first hit, a few go on for dozens of bounces
 // inside glass).  Work is handed out in blocks of 256 photons per warp from one global cursor.  `list` (may be NULL)
-// maps work item -> photon of the batch.
-__global__ void __launch_bounds__(128) trace_kernel(ShadeEnv env, Round rd, uint64_t t0, uint64_t n_items,
+// maps work item -> photon of the batch.  Compiled for 6 CTAs per SM (80 registers, 24 warps; 168 registers unbounded):
+// the walks are latency-bound like the render's path kernel -- jensen's photon pass 129 -> 110 ms, cornell unchanged.
+__global__ void __launch_bounds__(128, 6) trace_kernel(ShadeEnv env, Round rd, uint64_t t0, uint64_t n_items,
                                                     const uint32_t *__restrict__ list, unsigned long long *cursor, PhotonSink sink) {
   const int lane = threadIdx.x & 31;
   bool active = false, store = false;
