@@ -103,6 +103,18 @@ __global__ void refit_kernel(const uint64_t *__restrict__ keys, int n, const int
   }
 }
 
+// Depth of the tree = the longest leaf-to-root chain.  The traversal stacks of isect.cuh hold at most one pending sibling
+// per level of the descent, so depth <= GI_STACK means they cannot overflow.  (A radix tree over unique 62-bit keys
+// -- 30-bit Morton code + 32-bit primitive index -- splits on a strictly increasing bit position per level, so the depth is
+// at most 62 by construction; the check makes the guarantee explicit and gi_upload_scene fails if it were ever broken.)
+__global__ void depth_kernel(int n, const int *__restrict__ parent_internal, const int *__restrict__ parent_leaf, int *max_depth) {
+  int leaf = blockIdx.x * blockDim.x + threadIdx.x;
+  if (leaf >= n) return;
+  int d = 0;
+  for (int cur = parent_leaf[leaf]; cur >= 0; cur = parent_internal[cur]) d++;
+  atomicMax(max_depth, d);
+}
+
 __global__ void single_prim_kernel(const float *prim_boxes, float4 *bvh) {
   const float *b = prim_boxes;
   bvh[0] = make_float4(b[0], b[1], b[2], b[3]);
@@ -114,11 +126,12 @@ __global__ void single_prim_kernel(const float *prim_boxes, float4 *bvh) {
 #define CK(x) do { cudaError_t e_ = (x); if (e_ != cudaSuccess) { err = e_; goto done; } } while (0)
 
 cudaError_t build_bvh(const float *d_prim_boxes, int n, const float lo[3], const float hi[3], float4 *d_bvh,
-                      cudaStream_t stream) {
+                      cudaStream_t stream, int *depth_out) {
   cudaError_t err = cudaSuccess;
   uint64_t *keys_in = nullptr, *keys_out = nullptr;
   int2 *children = nullptr; int *parent_internal = nullptr, *parent_leaf = nullptr, *flags = nullptr;
   float *node_boxes = nullptr; void *tmp = nullptr; size_t tmp_bytes = 0;
+  if (depth_out) *depth_out = n > 0 ? 1 : 0;
   if (n <= 0) return cudaSuccess;
   if (n == 1) {
     single_prim_kernel<<<1, 1, 0, stream>>>(d_prim_boxes, d_bvh);
@@ -147,7 +160,13 @@ cudaError_t build_bvh(const float *d_prim_boxes, int n, const float lo[3], const
     refit_kernel<<<G, B, 0, stream>>>(keys_out, n, children, parent_internal, parent_leaf, d_prim_boxes, node_boxes,
                                       flags, d_bvh);
     CK(cudaGetLastError());
+    CK(cudaMemsetAsync(flags, 0, sizeof(int), stream));                 // reused as the depth cell
+    depth_kernel<<<G, B, 0, stream>>>(n, parent_internal, parent_leaf, flags);
+    CK(cudaGetLastError());
+    int depth = 0;
+    CK(cudaMemcpyAsync(&depth, flags, sizeof(int), cudaMemcpyDeviceToHost, stream));
     CK(cudaStreamSynchronize(stream));
+    if (depth_out) *depth_out = depth;
   }
 done:
   cudaFree(keys_in); cudaFree(keys_out); cudaFree(children); cudaFree(parent_internal); cudaFree(parent_leaf);

@@ -136,10 +136,18 @@ int gi_upload_scene(GiContext *ctx, const GiScene *scene) {
   float4 *bvh = nullptr;
   if (!cuda_ok(cudaMalloc(&bvh, sizeof(float4) * 4 * (size_t)d.n_bvh_nodes), "cudaMalloc(bvh)")) { free_scene(ctx); return 1; }
   ctx->scene_allocs.push_back(bvh);
+  int bvh_depth = 0;
   if (!cuda_ok(cudaMemsetAsync(bvh, 0, sizeof(float4) * 4 * (size_t)d.n_bvh_nodes, ctx->stream), "memset(bvh)") ||
-      !cuda_ok(build_bvh(d_boxes, scene->n_prims, ps.lo, ps.hi, bvh, ctx->stream), "build_bvh") ||
+      !cuda_ok(build_bvh(d_boxes, scene->n_prims, ps.lo, ps.hi, bvh, ctx->stream, &bvh_depth), "build_bvh") ||
       !cuda_ok(cudaStreamSynchronize(ctx->stream), "upload sync")) { free_scene(ctx); return 1; }
-  ctx->launches += scene->n_prims > 1 ? 6 : 1;
+  // closest_hit / find_poisoned_meshes keep at most one pending sibling per level: a deeper tree would drop subtrees
+  if (bvh_depth > GI_STACK) {
+    free_scene(ctx);
+    set_error("gi_upload_scene: BVH depth " + std::to_string(bvh_depth) + " exceeds the traversal stack (" + std::to_string(GI_STACK) + ")");
+    return 1;
+  }
+  ctx->bvh_depth = bvh_depth;
+  ctx->launches += scene->n_prims > 1 ? 7 : 1;
   d.bvh = bvh;
   ctx->scene = d;
   // world boxes of the shapes that can bounce a photon specularly (caustic-photon prefilter, photon_trace.cu)

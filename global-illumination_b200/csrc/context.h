@@ -38,6 +38,7 @@ struct GiContext {
   double centroid[3] = {0, 0, 0}, radius = 0;
   double *d_spec_boxes = nullptr;             // scene_allocs entry: boxes of the specular / transmissive shapes (photon_trace.cu)
   int n_spec_boxes = -1;
+  int bvh_depth = 0;                          // longest root-to-leaf chain of the scene BVH (<= GI_STACK, checked at upload)
   gi::PhotonMapStore maps[2];                 // GI_MAP_GLOBAL, GI_MAP_CAUSTIC
   // Host-buffer calls (gi_intersect_batch, gi_gather_batch) run as a two-slot pipeline: while one chunk computes on
   // pipe[0] the next chunk's inputs are copied in and the previous chunk's results copied out on pipe[1].

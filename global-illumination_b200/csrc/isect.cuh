@@ -212,9 +212,9 @@ GI_DEV bool ray_cylinder(const RayD &ray, const double *b, D3 *hp, D3 *hn, doubl
   return true;
 }
 
-// dispatch on GiShapeType (0 triangle, 1 sphere, 2 box, 3 cylinder, 4 cone, 5 circle).  The cone is left
-// unsupported: the reference's version is unfinished (no cap, zero normal, R3Isect.cpp:1259-1274) and no
-// input scene uses it.
+// dispatch on GiShapeType (0 triangle, 1 sphere, 2 box, 3 cylinder, 4 cone, 5 circle).  A cone never gets here:
+// gi_upload_scene refuses scenes that hold one (scene_prep.h; the reference's version is unfinished -- no cap, zero
+// normal, R3Isect.cpp:1259-1274 -- and no input scene uses it).
 GI_DEV bool ray_prim(const DevScene &sc, int prim, int type, const RayD &r, D3 *hp, D3 *hn, double *ht) {
   const double2 *a = sc.prim_a + 2 * (size_t)prim;
   const double *b = sc.prim_b + GI_PRIM_B_STRIDE * (size_t)prim;
@@ -289,6 +289,9 @@ GI_DEV bool tie_wins(const Cand &c, const Cand &best) {
 }
 
 #define GI_MAX_POISON 4
+// Traversal stack: one pending sibling per level of the descent.  gi_upload_scene measures the depth of the built BVH
+// (bvh_build.cu: depth_kernel) and refuses a scene deeper than this, so the `sp < GI_STACK` guards below never drop a
+// subtree.  (The LBVH over unique 62-bit keys is at most 62 levels deep by construction.)
 #define GI_STACK 64
 
 struct LeafCache {            // culls already decided for the current candidate's element / shape

@@ -102,7 +102,13 @@ inline bool prepare_scene(const GiScene &s, PreparedScene &out, std::string &err
       case GI_SHAPE_BOX:
         memcpy(b, p.d, 6 * sizeof(double)); memcpy(lb, p.d, sizeof(lb));
         break;
-      case GI_SHAPE_CYLINDER: case GI_SHAPE_CONE:
+      case GI_SHAPE_CONE:
+        // SURVEY.md §8 A6 "flagged unsupported": the reference's own intersector is unfinished (no base cap, ZERO normal,
+        // R3Isect.cpp:1201-1275), so a cone cannot be shaded there either; refusing by name beats rendering it as nothing
+        err = "cone primitives are not supported (the reference's R3Intersects(ray, cone) is unfinished: no cap, zero normal, "
+              "R3Isect.cpp:1201-1275); primitive " + std::to_string(i);
+        return false;
+      case GI_SHAPE_CYLINDER:
         memcpy(b, p.d, 7 * sizeof(double));
         for (int k = 0; k < 3; k++) {
           lb[k] = fmin(p.d[k], p.d[3 + k]) - p.d[6]; lb[3 + k] = fmax(p.d[k], p.d[3 + k]) + p.d[6];

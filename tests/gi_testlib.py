@@ -49,6 +49,19 @@ def read_ref_hits(path):
         return np.frombuffer(f.read(), dtype=REF_HIT).copy()
 
 
+def golden_gisc(name):
+    """path of the flattened scene tests/golden/<name>.gisc; large ones are committed gzip'd and unpacked on first use
+    (the unpacked copy is git-ignored)"""
+    p = os.path.join(GOLDEN, name + ".gisc")
+    if not os.path.exists(p) and os.path.exists(p + ".gz"):
+        import gzip
+        tmp = p + ".tmp%d" % os.getpid()
+        with gzip.open(p + ".gz", "rb") as f, open(tmp, "wb") as g:
+            g.write(f.read())
+        os.replace(tmp, p)
+    return p
+
+
 def have_ref_harness():
     return os.path.exists(REF_HARNESS)
 

@@ -59,7 +59,7 @@ def test_loader_errors_are_reported():
         gi_b200.HostScene("/nonexistent/scene.scn")
 
 
-@pytest.mark.parametrize("name", ["cornell", "stilllife", "teapot", "transform", "cylinder"])
+@pytest.mark.parametrize("name", ["cornell", "stilllife", "teapot", "transform", "cylinder", "circle", "art2", "distributed_lit"])
 def test_flattened_scene_equals_reference_scene_graph(name, tmp_path):
     """text dump of our flattened scene == `ref_harness dump_scene` of the reference's R3Scene (committed fixture)"""
     out = str(tmp_path / "dump.txt")

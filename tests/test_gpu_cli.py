@@ -53,3 +53,33 @@ def test_program_errors(tmp_path):
     assert r.returncode != 0 and "Unable" in r.stderr
     r = subprocess.run([PHOTONMAP, os.path.join(GOLDEN, "box.gisc"), str(tmp_path / "x.png"), "-frobnicate"], capture_output=True, text=True)
     assert r.returncode != 0 and "Invalid program argument" in r.stderr
+
+
+def test_stock_distributed_scene_exits_cleanly(tmp_path):
+    """BASELINE.json configs[4].  The stock input/distributed.scn has ONE light, black "to suppress automatic generation
+    of light sources": MapPhotons returns at `total_power <= 0` (photonmap.cpp:286-289) leaving both maps NULL with
+    INDIRECT_ILLUM / CAUSTIC_ILLUM still on, and the reference then crashes in the first EstimateRadiance (exit 139,
+    SURVEY.md §0).  Defined deviation here: no photons => indirect and caustic contribute nothing, the program renders
+    the rest (ambient + emission + specular / transmissive paths) and exits 0."""
+    out = tmp_path / "d.png"
+    r = subprocess.run([PHOTONMAP, os.path.join(GOLDEN, "scn", "distributed.scn"), str(out), "-resolution", "48", "48", "-aa", "1",
+                        "-st", "4", "-tt", "4", "-md", "8", "-v"], capture_output=True, text=True)
+    assert r.returncode == 0, r.stderr
+    assert "Total Photons Stored: 0" in r.stdout and "# Screen Rays" in r.stdout
+    img = read_png_rgb(out)
+    assert img.shape == (48, 48, 3)
+    assert img.max() == 255 and img.mean() > 1.0        # the emissive ceiling panel (ke 4 4 4) is visible, the rest is dark
+
+
+def test_lit_distributed_variant_renders_with_both_maps(tmp_path):
+    """the bench variant (tests/golden/scn/distributed_lit.scn: rect light at the ceiling panel) traces both maps"""
+    out = tmp_path / "d.png"
+    r = subprocess.run([PHOTONMAP, os.path.join(GOLDEN, "scn", "distributed_lit.scn"), str(out), "-resolution", "48", "48", "-aa", "0",
+                        "-global", "2000", "-caustic", "20000", "-it", "8", "-st", "4", "-tt", "4", "-lt", "8", "-ss", "8", "-md", "8",
+                        "-seed", "3", "-v"], capture_output=True, text=True)
+    assert r.returncode == 0, r.stderr
+    line = {l.split("=")[0].strip(): l.split("=")[1].strip() for l in r.stdout.splitlines() if "=" in l}
+    assert int(line["# Global Photons Stored"]) >= 2000 and int(line["# Caustic Photons Stored"]) >= 20000
+    assert int(line["# Indirect Samples"]) > 0 and int(line["# Caustic Samples"]) > 0
+    img = read_png_rgb(out)
+    assert img.mean() > 20 and (img > 0).mean() > 0.5

@@ -155,3 +155,91 @@ def test_dense_blob_seen_from_a_distance(gpu_ctx, oracle):
         ref = oracle.gather(ph, q, k, r, 0, threads=os.cpu_count() or 8)
         check(ref, gpu_ctx.gather(gi_b200.GI_MAP_CAUSTIC, q, k, r, 0))
         check_rgb(ref, gpu_ctx.gather(gi_b200.GI_MAP_CAUSTIC, q, k, r, 0, want_idx=False))
+
+
+# ---------------------------------------------------------------------------------------------- BASELINE-size maps
+def _scene_queries(gpu_ctx, scene_gisc, n_side, ph, n_on_photons, seed):
+    """gather queries as RayTrace sets them up: at the primary hits of an n_side x n_side camera grid, plus queries
+    sitting on randomly chosen photons of the map (inside the dense caustic spots, where all k are found)"""
+    from gi_testlib import queries_from_hits
+    hs = gi_b200.HostScene(scene_gisc)
+    gpu_ctx.upload_scene(hs)
+    cam = hs.view.camera
+    i, j = np.meshgrid(np.arange(float(n_side)), np.arange(float(n_side)), indexing="ij")
+    dx = (2.0 * (i - n_side // 2) / n_side).reshape(-1, 1); dy = (2.0 * (j - n_side // 2) / n_side).reshape(-1, 1)
+    eye = np.array(cam.eye[:])
+    d = np.array(cam.towards[:]) + np.array(cam.right[:]) * np.tan(cam.xfov) * dx + np.array(cam.up[:]) * np.tan(cam.yfov) * dy
+    d /= np.sqrt(d[:, 0] * d[:, 0] + d[:, 1] * d[:, 1] + d[:, 2] * d[:, 2])[:, None]
+    rays = np.concatenate([np.broadcast_to(eye, d.shape), d], axis=1)
+    q = queries_from_hits(rays, gpu_ctx.intersect(rays))
+    rng = np.random.default_rng(seed)
+    extra = q[rng.integers(0, len(q), n_on_photons)].copy()
+    extra["p"] = ph["position"][rng.integers(0, len(ph), n_on_photons)] + rng.normal(scale=1e-4, size=(n_on_photons, 3))
+    return np.concatenate([q, extra])
+
+
+def _reference_gather(tmp_path, gipm, q, k, r, filt):
+    from gi_testlib import ref_harness, write_queries, read_ref_gather
+    write_queries(tmp_path / "q.bin", q)
+    ref_harness("gather", gipm, tmp_path / "q.bin", tmp_path / "g.bin", k, r, filt, os.cpu_count() or 8)
+    cnt, rgb, idx = read_ref_gather(tmp_path / "g.bin")
+    return idx, cnt, rgb
+
+
+def _have_ref():
+    from gi_testlib import have_ref_harness
+    return have_ref_harness()
+
+
+@pytest.mark.skipif(not _have_ref(), reason="needs oracle/_ref/ref_harness (built where the reference tree exists; travels to the GPU box)")
+@pytest.mark.parametrize("case", ["cornell_1e7", "jensen_reftraced_3e6"])
+def test_large_caustic_maps_against_live_reference_kdtree(gpu_ctx, tmp_path, case):
+    """The kNN contract at the BASELINE sizes, against the reference's own R3Kdtree::FindClosestQuick + EstimateRadiance
+    (R3Kdtree.cpp:688-848, photon_utils.cpp:72-162) run LIVE on the same map file: identical index sets and counts,
+    radiance to 1e-9, k = 225 / 50, all three filters.
+      cornell_1e7           cornell's DEFAULT caustic map (-caustic 10000000: ~1e7 photons, four rows of groups) traced by
+                            gi_trace_photons (statistically the reference's map, tests/test_gpu_photons.py);
+                            GI_SLOW_TESTS=1 lets the reference's MapPhotons trace it instead (minutes of CPU)
+      jensen_reftraced_3e6  jensen.scn (configs[1]) with -caustic 3000000 traced by the reference's MapPhotons itself"""
+    from gi_testlib import golden_gisc, ref_harness
+    scene = case.split("_")[0]
+    gipm = str(tmp_path / "caustic.gipm")
+    if case == "jensen_reftraced_3e6" or os.environ.get("GI_SLOW_TESTS"):
+        want = 3_000_000 if scene == "jensen" else 10_000_000
+        ref_harness("photons", os.path.join(GOLDEN, "scn", scene + ".scn"), tmp_path / "ref", "-global", 2176, "-caustic", want,
+                    "-threads", os.cpu_count() or 8)
+        gipm = str(tmp_path / "ref.caustic.gipm")
+        gpu_ctx.load_photons_file(gi_b200.GI_MAP_CAUSTIC, gipm)
+        gpu_ctx.build_maps()
+    else:
+        want = 10_000_000
+        gpu_ctx.upload_scene(gi_b200.HostScene(golden_gisc(scene)))
+        p, _ = gi_b200.parse_flags(["-seed", "5", "-no_indirect"])
+        st = gpu_ctx.trace_photons(p)
+        assert st.caustic_stored >= want
+        gpu_ctx.dump_photons_file(gi_b200.GI_MAP_CAUSTIC, gipm)
+    ph = read_photons(gipm)
+    assert len(ph) >= want
+    q = _scene_queries(gpu_ctx, golden_gisc(scene), 40, ph, 600, seed=1)
+    assert len(q) >= 2000
+    full = 0
+    for k, r, filt in ((225, 0.225, 0), (225, 0.225, 2), (50, 0.05, 1)):
+        ref = _reference_gather(tmp_path, gipm, q, k, r, filt)
+        check(ref, gpu_ctx.gather(gi_b200.GI_MAP_CAUSTIC, q, k, r, filt))
+        check_rgb(ref, gpu_ctx.gather(gi_b200.GI_MAP_CAUSTIC, q, k, r, filt, want_idx=False))
+        full += int((ref[1] == k).sum())
+    assert full > 1000                                  # the dense spots were really exercised
+
+
+@pytest.mark.parametrize("mp,k,filt", [("caustic", 225, 0), ("caustic", 225, 1), ("caustic", 225, 2), ("caustic", 50, 0),
+                                       ("global", 50, 0), ("global", 50, 2)])
+def test_jensen_reference_maps(gpu_ctx, mp, k, filt):
+    """jensen.scn (BASELINE configs[1]: rect light, glass + mirror sphere) maps traced by the reference's MapPhotons,
+    gathers by the reference's kd-tree and estimator (tests/golden/jensen.gather.npz, make_jensen_golden.py)"""
+    fx = np.load(os.path.join(GOLDEN, "jensen.gather.npz"))
+    which = gi_b200.GI_MAP_CAUSTIC if mp == "caustic" else gi_b200.GI_MAP_GLOBAL
+    gpu_ctx.load_photons(which, fx[mp + "_photons"].view(gi_b200.PHOTON).reshape(-1))
+    gpu_ctx.build_maps()
+    key = f"{mp}_{k}_{filt}"
+    got = gpu_ctx.gather(which, fx["queries"].view(GI_QUERY).reshape(-1), k, float(fx[key + "_r"][0]), filt)
+    check((fx[f"{mp}_{k}_idx"], fx[key + "_count"], fx[key + "_rgb"]), got)

@@ -9,7 +9,7 @@ import os
 import numpy as np
 import pytest
 
-from gi_testlib import GI_HIT, ROOT, REF_INPUT, have_ref_harness, ref_harness, flatten_scene, read_rays, write_rays, \
+from gi_testlib import golden_gisc, GI_HIT, ROOT, REF_INPUT, have_ref_harness, ref_harness, flatten_scene, read_rays, write_rays, \
     read_ref_hits, random_rays
 
 GOLDEN = os.path.join(ROOT, "tests", "golden")
@@ -41,7 +41,7 @@ def test_golden_set_is_complete():
 @pytest.mark.parametrize("name", SCENES)
 def test_oracle_matches_reference(oracle, name):
     d = np.load(os.path.join(GOLDEN, name + ".isect.npz"))
-    h = oracle.load_scene(os.path.join(GOLDEN, name + ".gisc"))
+    h = oracle.load_scene(golden_gisc(name))
     got = oracle.intersect(h, d["rays"], threads=4)
     oracle.free_scene(h)
     assert_same_hits(d["hits"], got, name)
@@ -50,7 +50,7 @@ def test_oracle_matches_reference(oracle, name):
 @pytest.mark.parametrize("name", SCENES)
 def test_device_code_on_cpu_matches_reference(sim, name):
     d = np.load(os.path.join(GOLDEN, name + ".isect.npz"))
-    s = sim.sim_scene_load(os.path.join(GOLDEN, name + ".gisc").encode())
+    s = sim.sim_scene_load(golden_gisc(name).encode())
     assert s
     rays = np.ascontiguousarray(d["rays"], dtype=np.float64)
     got = np.zeros(len(rays), dtype=GI_HIT)
