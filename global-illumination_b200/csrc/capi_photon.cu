@@ -20,6 +20,7 @@
 namespace gi {
 
 static const uint32_t PMAP_MAGIC = 0x4d504947u;   // "GIPM"
+static const uint32_t PMAP_VERSION = 1u;
 
 void free_map(PhotonMapStore &m) {
   cudaFree((void *)m.dev.px); cudaFree((void *)m.dev.py); cudaFree((void *)m.dev.pz);
@@ -30,9 +31,8 @@ void free_map(PhotonMapStore &m) {
 
 // BuildDirectionLookupTable (src/utils/photon_utils.cpp:253-272), built on the host with the same libm calls and
 // kept in HBM (1.5 MB, L2-resident): entry [phi * 256 + theta] = normalised (x, y, z)
-static double *g_lut[64] = {nullptr};
-static const double *direction_lut(GiContext *ctx) {
-  if (ctx->device < 64 && g_lut[ctx->device]) return g_lut[ctx->device];
+const double *direction_lut(GiContext *ctx) {
+  if (ctx->d_lut) return ctx->d_lut;
   std::vector<double> h(65536 * 3);
   const double PI = 3.14159265358979323846, TWO_PI = 6.28318530717958647692;   // RN_PI / RN_TWO_PI (RNScalar.h)
   for (int phi = 0; phi < 256; phi++)
@@ -45,7 +45,7 @@ static const double *direction_lut(GiContext *ctx) {
   double *d = nullptr;
   if (!cuda_ok(cudaMalloc(&d, h.size() * 8), "cudaMalloc(lut)")) return nullptr;
   if (!cuda_ok(cudaMemcpy(d, h.data(), h.size() * 8, cudaMemcpyHostToDevice), "cudaMemcpy(lut)")) { cudaFree(d); return nullptr; }
-  if (ctx->device < 64) g_lut[ctx->device] = d;
+  ctx->d_lut = d;
   return d;
 }
 
@@ -115,30 +115,44 @@ int gi_get_photons_device(GiContext *ctx, int map, GiPhoton *d_out, uint64_t cap
   return 0;
 }
 
+// The header is not trusted: magic, version and the photon count against the bytes that are really in the file are
+// checked before anything is allocated, and no C++ exception crosses the extern "C" boundary.
 int gi_load_photons_file(GiContext *ctx, int map, const char *path) {
+  if (!ctx || map < 0 || map > 1) { set_error("gi_load_photons_file: bad argument"); return 1; }
   FILE *f = path ? fopen(path, "rb") : nullptr;
   if (!f) { set_error(std::string("Unable to open photon file ") + (path ? path : "(null)")); return 1; }
-  uint32_t hdr[2]; uint64_t n = 0;
-  if (fread(hdr, 4, 2, f) != 2 || hdr[0] != PMAP_MAGIC || fread(&n, 8, 1, f) != 1) {
-    fclose(f); set_error(std::string("Bad photon file ") + path); return 1;
-  }
-  std::vector<GiPhoton> ph(n);
-  if (n && fread(ph.data(), sizeof(GiPhoton), n, f) != n) { fclose(f); set_error(std::string("Truncated photon file ") + path); return 1; }
+  int rc = 1;
+  try {
+    uint32_t hdr[2]; uint64_t n = 0;
+    if (fread(hdr, 4, 2, f) != 2 || hdr[0] != PMAP_MAGIC || fread(&n, 8, 1, f) != 1) throw std::string("Bad photon file ");
+    if (hdr[1] != PMAP_VERSION) throw std::string("Unsupported photon file version in ");
+    if (n >= ((uint64_t)1 << 31)) throw std::string("Bad photon count in photon file ");
+    const long body = ftell(f);
+    if (body < 0 || fseek(f, 0, SEEK_END) != 0) throw std::string("Bad photon file ");
+    const long end = ftell(f);
+    if (end < body || (uint64_t)(end - body) < n * sizeof(GiPhoton) || fseek(f, body, SEEK_SET) != 0) throw std::string("Truncated photon file ");
+    std::vector<GiPhoton> ph(n);
+    if (n && fread(ph.data(), sizeof(GiPhoton), n, f) != n) throw std::string("Truncated photon file ");
+    rc = gi_load_photons(ctx, map, ph.data(), n);
+  } catch (const std::string &what) { set_error(what + path);
+  } catch (const std::exception &e) { set_error(std::string("gi_load_photons_file: ") + e.what()); }
   fclose(f);
-  return gi_load_photons(ctx, map, ph.data(), n);
+  return rc;
 }
 
 int gi_dump_photons_file(GiContext *ctx, int map, const char *path) {
   if (!ctx || map < 0 || map > 1 || !path) { set_error("gi_dump_photons_file: bad argument"); return 1; }
-  const uint64_t n = ctx->maps[map].dev.n;
-  std::vector<GiPhoton> ph(n);
-  if (gi_get_photons(ctx, map, ph.data(), n)) return 1;
-  FILE *f = fopen(path, "wb");
-  if (!f) { set_error(std::string("Unable to open photon file ") + path); return 1; }
-  uint32_t hdr[2] = {PMAP_MAGIC, 1};
-  bool ok = fwrite(hdr, 4, 2, f) == 2 && fwrite(&n, 8, 1, f) == 1 && (n == 0 || fwrite(ph.data(), sizeof(GiPhoton), n, f) == n);
-  fclose(f);
-  if (!ok) { set_error(std::string("Unable to write photon file ") + path); return 1; }
+  try {
+    const uint64_t n = ctx->maps[map].dev.n;
+    std::vector<GiPhoton> ph(n);
+    if (gi_get_photons(ctx, map, ph.data(), n)) return 1;
+    FILE *f = fopen(path, "wb");
+    if (!f) { set_error(std::string("Unable to open photon file ") + path); return 1; }
+    uint32_t hdr[2] = {PMAP_MAGIC, PMAP_VERSION};
+    bool ok = fwrite(hdr, 4, 2, f) == 2 && fwrite(&n, 8, 1, f) == 1 && (n == 0 || fwrite(ph.data(), sizeof(GiPhoton), n, f) == n);
+    ok = (fclose(f) == 0) && ok;
+    if (!ok) { set_error(std::string("Unable to write photon file ") + path); return 1; }
+  } catch (const std::exception &e) { set_error(std::string("gi_dump_photons_file: ") + e.what()); return 1; }
   return 0;
 }
 

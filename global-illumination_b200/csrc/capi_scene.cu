@@ -113,6 +113,7 @@ void gi_destroy(GiContext *ctx) {
   }
   for (int j = 0; j < 5; j++) ctx->order_ws[2][j].release();
   cudaFree(ctx->gather_counters);
+  cudaFree(ctx->d_lut);
   if (ctx->stream) cudaStreamDestroy(ctx->stream);
   delete ctx;
 }

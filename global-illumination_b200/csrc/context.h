@@ -45,6 +45,8 @@ struct GiContext {
   cudaStream_t pipe[2] = {nullptr, nullptr};
   GiScratch stage[2][4];                      // per slot: input, and up to three outputs
   GiScratch order_ws[3][5];                   // query_order.cu, per stream slot (pipe[0], pipe[1], any other): keys x2, order x2, sort temp
+  size_t gather_smem_configured[2] = {0, 0};  // gather.cu: dynamic shared memory the two kernel variants are configured for on this device
+  double *d_lut = nullptr;                    // capi_photon.cu: the 65536 x 3 incident-direction table (photon_utils.cpp:253-272)
   void *gather_counters = nullptr;            // gather.cu: launch-wide chunk counters, one per stream slot
   void *render_ws = nullptr;                  // render.cu's device workspace, created by the first gi_render
   void (*render_ws_free)(void *) = nullptr;

@@ -310,10 +310,13 @@ gather_kernel(PhotonMapDev m, const double *__restrict__ lut, const GiGatherQuer
     if (off == 0) {
       const unsigned long long base = atomicAdd(work_counter, (unsigned long long)range);
       s_base[sl] = base; __threadfence_block(); s_gen[sl] = rn + 1u;
+      chunk = base;
     } else {
-      while (s_gen[sl] < rn + 1u) { }                     // brief: the opener already holds ticket rn * range
+      // brief: the opener already holds ticket rn * range.  Exactly this range's generation: launch_gather keeps
+      // range >= warps, so at most two ranges are open at a time and the 8 slots never alias
+      while (s_gen[sl] != rn + 1u) { }
+      chunk = s_base[sl] + off;
     }
-    chunk = s_base[sl] + off;
   }
   chunk = __shfl_sync(FULL, chunk, 0);
   if (chunk >= nchunks) break;
@@ -529,12 +532,12 @@ cudaError_t launch_gather(GiContext *ctx, const PhotonMapDev &m, const double *d
   if ((uint64_t)warps > nchunks) warps = (int)nchunks;
   const size_t smem = (size_t)warps * per_warp;
   const bool deep = m.hb > GI_GROUP_LEVELS;
-  static size_t configured[2] = {0, 0};
-  if (smem > configured[deep]) {
+  // the attribute is per DEVICE (and per kernel instantiation): remembered in the context, which is bound to one device
+  if (smem > ctx->gather_smem_configured[deep]) {
     cudaError_t e = deep ? cudaFuncSetAttribute(gather_kernel<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem)
                          : cudaFuncSetAttribute(gather_kernel<false>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
     if (e != cudaSuccess) return e;
-    configured[deep] = smem;
+    ctx->gather_smem_configured[deep] = smem;
   }
   // range of consecutive chunks a CTA fetches at a time: 4 per warp, fewer when the launch is small (balance)
   {
@@ -543,7 +546,7 @@ cudaError_t launch_gather(GiContext *ctx, const PhotonMapDev &m, const double *d
     if (r < (uint64_t)warps) r = warps;
     if (r > (uint64_t)4 * warps) r = (uint64_t)4 * warps;
     ga.range = (int)r;
-    if (ga_in.range > 0) ga.range = ga_in.range;
+    if (ga_in.range > 0) ga.range = ga_in.range < warps ? warps : ga_in.range;     // (tuning hook) never below one chunk per warp
   }
   unsigned long long *counter = work_counter(ctx, st);
   if (!counter) return cudaErrorMemoryAllocation;

@@ -64,6 +64,10 @@ STO = {
     "cornell_fast_global": ("cornell", 24, 24, "-fast_global -st 8 -tt 8 -md 6", ("global", "caustic"), 64),
     "cornell_indirect_cache": ("cornell", 24, 24, "-no_transmissive -no_specular -no_caustic -it 16 -md 6 -cache", ("global",), 64),
     "cornell_fast_global_cache": ("cornell", 24, 24, "-fast_global -cache -st 8 -tt 8 -md 6", ("global", "caustic"), 64),
+    # EVERY flag at its default (lt / ss / tt / st 128, it 256, md 128, k 50 / 225): the sample counts of the metric's frame.
+    # 32 reference runs; the fixture also keeps the two half-means so that the test can state a PSNR against the
+    # reference's own run-to-run noise floor.
+    "cornell_defaults": ("cornell", 48, 48, "", ("global", "caustic"), 32),
 }
 
 
@@ -107,6 +111,8 @@ def main():
         out[name] = imgs.mean(0)
         out[name + "__sem"] = imgs.std(0, ddof=1) / np.sqrt(runs)
         out[name + "__std"] = imgs.std(0, ddof=1)
+        if name == "cornell_defaults":
+            out[name + "__half_a"] = imgs[: runs // 2].mean(0); out[name + "__half_b"] = imgs[runs // 2:].mean(0)
         out[name + "__meta"] = np.array([scene, str(w), str(h), flags, ",".join(maps)])
         print(name, "mean", imgs.mean(axis=(0, 1, 2)), "max sem", out[name + "__sem"].max())
     np.savez_compressed(f"{HERE}/render.npz", **out)

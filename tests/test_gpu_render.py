@@ -76,6 +76,29 @@ def test_stochastic_radiance(gpu_ctx, name):
     assert np.allclose(again, imgs[0], rtol=1e-9, atol=1e-12)
 
 
+def test_default_flags_frame_psnr_against_converged_reference(gpu_ctx):
+    """North-star bullet "full Monte Carlo images within a stated RMSE/PSNR of a converged reference render", at the
+    DEFAULT sample counts of the metric's frame (lt / ss / tt / st 128, it 256, md 128, k 50 / 225): cornell 48 x 48.
+    Reference = mean of 32 runs of the reference's own RayTrace; its own noise floor (16-run half against 16-run half,
+    clamped to [0, 1] like the output image) is 43.7 dB / RMSE 0.0065.  STATED THRESHOLD: the mean of 16 of our frames
+    is within PSNR >= 42 dB (RMSE <= 0.008 on a [0, 1] scale) of the 32-run reference mean -- an unbiased estimator with
+    the reference's variance lands at ~45 dB (variance 1/16 + 1/32 against 2/16 between the halves)."""
+    name = "cornell_defaults"
+    params, w, h = setup(gpu_ctx, name)
+    imgs = []
+    for s in range(16):
+        params.seed = 500 + s
+        imgs.append(gpu_ctx.render_float(params, w, h, 0)[0])
+    ours = np.clip(np.stack(imgs).mean(0), 0.0, 1.0)
+    ref = np.clip(G[name], 0.0, 1.0)
+    floor_mse = ((np.clip(G[name + "__half_a"], 0, 1) - np.clip(G[name + "__half_b"], 0, 1)) ** 2).mean()
+    mse = ((ours - ref) ** 2).mean()
+    psnr, floor = 10 * np.log10(1.0 / mse), 10 * np.log10(1.0 / floor_mse)
+    print(f"default-flags cornell 48x48: PSNR {psnr:.2f} dB (RMSE {np.sqrt(mse):.5f}); reference half-vs-half floor {floor:.2f} dB")
+    assert psnr >= 42.0, (psnr, floor)
+    assert psnr >= floor - 1.0, (psnr, floor)
+
+
 def test_resolve_matches_reference_downsampling(gpu_ctx):
     """gi_render = clamp -> 2^aa box filter -> truncating quantisation (render.cpp:205-221, R2Image.cpp:194-212)."""
     params, w, h = setup(gpu_ctx, "cornell_direct")
