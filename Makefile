@@ -39,7 +39,7 @@ build/%.cpp.o: %.cpp $(CU_HDRS)
 
 lib: $(PKG)/libgi_b200.so
 $(PKG)/libgi_b200.so: $(LIB_OBJS)
-	$(NVCC) $(ARCH) -shared $(LIB_OBJS) -o $@ -lcudart
+	$(NVCC) $(ARCH) -shared $(LIB_OBJS) -o $@ -lcudart -ldl
 
 host_sim: tests/host_sim/libisect_sim.so
 tests/host_sim/libisect_sim.so: tests/host_sim/isect_sim.cpp $(CU_HDRS) $(HOST_SRCS)

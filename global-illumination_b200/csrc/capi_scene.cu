@@ -9,6 +9,7 @@
 #include <cstring>
 #include <mutex>
 #include "bvh_build.h"
+#include "comm.h"
 #include "context.h"
 #include "isect.cuh"
 #include "scene_prep.h"
@@ -103,6 +104,7 @@ int gi_create(int device, GiContext **out) {
 void gi_destroy(GiContext *ctx) {
   if (!ctx) return;
   cudaSetDevice(ctx->device);
+  comm_release(ctx);
   free_scene(ctx);
   free_map(ctx->maps[0]); free_map(ctx->maps[1]);
   if (ctx->render_ws && ctx->render_ws_free) ctx->render_ws_free(ctx->render_ws);

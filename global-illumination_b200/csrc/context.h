@@ -50,6 +50,7 @@ struct GiContext {
   void *gather_counters = nullptr;            // gather.cu: launch-wide chunk counters, one per stream slot
   void *render_ws = nullptr;                  // render.cu's device workspace, created by the first gi_render
   void (*render_ws_free)(void *) = nullptr;
+  void *comm = nullptr;                       // comm.cu: NCCL communicator + rank / world of this context (nullptr = single GPU)
   uint64_t queue_overflows = 0;               // render path batches repeated because a gather-request queue ran full
   uint64_t launches = 0;                      // kernels launched by this context (bench.py: gpu_launches)
 };

@@ -6,15 +6,16 @@
 // PhotonTrace (photontracer.cpp:28-176) follows every photon through its bounces with Russian roulette, storing it
 // at diffuse surfaces.  Here one round is ONE kernel launch with a thread per emitted photon; stored photons are
 // appended through an atomic cursor together with the key (emitted photon number, bounce), and once the rounds
-// are over the photons are sorted by that key, so a map depends on the seed only -- not on scheduling.  One rank =
-// one reference "thread": with world_size > 1 each rank traces COUNT / world_size photons on its own streams, the
-// host all-gathers them and applies the power scale (gi_scale_photon_power) before gi_build_maps.
+// are over the photons are sorted by that key, so a map depends on the seed only -- not on scheduling, and not on the
+// number of GPUs: with a communicator attached (comm.cu) rank r traces the photons t = r (mod world) of every round, the
+// stored counts are all-reduced per round, and one ragged all-gather over NVLink replicates the photons at the end.
 #include <cub/cub.cuh>
 #include <algorithm>
 #include <cmath>
 #include <cstdlib>
 #include <cstring>
 #include <vector>
+#include "comm.h"
 #include "context.h"
 #include "kdtree_build.h"
 #include "shade.cuh"
@@ -98,6 +99,7 @@ struct Round {                       // one emission round (photonmap.cpp:165-17
   uint64_t id0;
   const uint64_t *first;
   D3 centroid;
+  uint32_t rank, world;              // this GPU takes the photons t = rank (mod world) of the round: work item w is t = w * world + rank
 };
 
 // The emission part of EmitPhotons (photontracer.cpp:182-360) for photon t of a round: seeds the photon's stream and
@@ -166,13 +168,13 @@ GI_DEV bool may_hit_specular(const ShadeEnv &env, const RayD &ray) {
 }
 
 // CAUSTIC rounds, pass 1: thread per emitted photon; photons that may reach a specular surface are listed.
-__global__ void __launch_bounds__(256) emit_filter_kernel(ShadeEnv env, Round rd, uint64_t t0, uint32_t n, uint32_t *__restrict__ list,
+__global__ void __launch_bounds__(256) emit_filter_kernel(ShadeEnv env, Round rd, uint64_t w0, uint32_t n, uint32_t *__restrict__ list,
                                                           unsigned int *__restrict__ count) {
   const uint32_t i = blockIdx.x * blockDim.x + threadIdx.x;
   bool keep = false;
   if (i < n) {
     Rng rng; RayD ray; D3 photon;
-    emit_photon(env, rd, t0 + i, rng, ray, photon);
+    emit_photon(env, rd, (w0 + i) * rd.world + rd.rank, rng, ray, photon);
     keep = may_hit_specular(env, ray);
   }
   const unsigned m = __ballot_sync(0xffffffffu, keep);
@@ -190,9 +192,13 @@ __global__ void __launch_bounds__(256) emit_filter_kernel(ShadeEnv env, Round rd
 // inside glass).  Work is handed out in blocks of 256 photons per warp from one global cursor.  `list` (may be NULL)
 // maps work item -> photon of the batch.  Compiled for 6 CTAs per SM (80 registers, 24 warps; 168 registers unbounded):
 // the walks are latency-bound like the render's path kernel -- jensen's photon pass 129 -> 110 ms, cornell unchanged.
-__global__ void __launch_bounds__(128, 6) trace_kernel(ShadeEnv env, Round rd, uint64_t t0, uint64_t n_items,
+// n_items_dev (may be NULL): the number of work items, left in device memory by emit_filter_kernel -- the host does not
+// wait for the filter to know it.
+__global__ void __launch_bounds__(128, 6) trace_kernel(ShadeEnv env, Round rd, uint64_t w0, uint64_t n_items_host,
+                                                    const unsigned int *__restrict__ n_items_dev,
                                                     const uint32_t *__restrict__ list, unsigned long long *cursor, PhotonSink sink) {
   const int lane = threadIdx.x & 31;
+  const uint64_t n_items = n_items_dev ? (uint64_t)*n_items_dev : n_items_host;
   bool active = false, store = false;
   int iter = 0;
   uint64_t id = 0;
@@ -212,7 +218,7 @@ __global__ void __launch_bounds__(128, 6) trace_kernel(ShadeEnv env, Round rd, u
       const int mine = __popc(idle & ((1u << lane) - 1u));
       if (!active && mine < wleft) {
         const unsigned long long w = wbase + mine;
-        const uint64_t t = t0 + (list ? (uint64_t)list[w] : (uint64_t)w);
+        const uint64_t t = (w0 + (list ? (uint64_t)list[w] : (uint64_t)w)) * rd.world + rd.rank;
         emit_photon(env, rd, t, rng, ray, photon);
         id = rd.id0 + t; iter = 0; active = true;
         store = rd.map_type == MAP_GLOBAL && !env.p.fast_global;
@@ -263,28 +269,37 @@ static double light_power(const GiLight &l, double scene_radius) {
 }
 
 namespace {
+// stream-ordered pool allocations (gi_create keeps freed pool memory): a frame traces its maps every time, and
+// cudaMalloc / cudaFree of a few hundred MB per map cost more than the kernels on a busy device
 struct Buf {
-  void *p = nullptr;
-  ~Buf() { if (p) cudaFree(p); }
-  bool alloc(size_t bytes) { if (p) { cudaFree(p); p = nullptr; } return cuda_ok(cudaMalloc(&p, bytes ? bytes : 1), "cudaMalloc(photon trace)"); }
+  void *p = nullptr; cudaStream_t st = nullptr;
+  ~Buf() { release(); }
+  void release() { if (p) cudaFreeAsync(p, st); p = nullptr; }
+  bool alloc(size_t bytes, cudaStream_t s) { release(); st = s; return cuda_ok(cudaMallocAsync(&p, bytes ? bytes : 1, s), "cudaMallocAsync(photon trace)"); }
   template <class T> T *as() const { return (T *)p; }
 };
 }  // namespace
 
-// One map: the adaptive rounds of Threadable_PhotonTracer.  Leaves the photons (sorted by emission key, unscaled)
-// in ctx->maps[map].raw.
+// One map: the adaptive rounds of Threadable_PhotonTracer, shared by all ranks of the context's communicator.
+// A round emits n photons numbered id0 .. id0 + n - 1 over ALL ranks; rank r traces the photons t = r (mod world).  The
+// stored counts are all-reduced after every round, so every rank computes the same next goal and the union of the
+// photons is the same for any number of ranks.  At the end the photons (with their keys) are all-gathered and sorted
+// by (photon number, bounce) on every rank: the map in ctx->maps[map].raw is byte-identical everywhere.
 static int trace_map(GiContext *ctx, const ShadeEnv &env_in, int map_type, int target, const std::vector<double> &light_powers,
-                     double total_power, uint64_t id_base, uint64_t &emitted_out, int &rounds_out) {
+                     double total_power, uint64_t &emitted_out, int &rounds_out) {
   ShadeEnv env = env_in;
   cudaStream_t st = ctx->stream;
   const int nl = env.n_lights;
-  unsigned long long cap = (unsigned long long)target + (unsigned long long)target / 2 + 65536;
+  const uint32_t world = (uint32_t)comm_world(ctx), rank = (uint32_t)comm_rank(ctx);
+  unsigned long long cap = ((unsigned long long)target + (unsigned long long)target / 2) / world + 65536;     // this rank's sink
+  const bool filter = map_type == MAP_CAUSTIC && env.n_spec_boxes >= 0;
+  const uint64_t batch = 1ull << 26;                          // work items per launch (bounds the survivor list)
   Buf photons, keys, count, first, cursor, list;
-  if (!photons.alloc(sizeof(GiPhoton) * cap) || !keys.alloc(8 * cap) || !count.alloc(8) || !first.alloc(8 * (size_t)(nl + 1)) ||
-      !cursor.alloc(16) || !list.alloc(map_type == MAP_CAUSTIC && env.n_spec_boxes >= 0 ? 4ull << 26 : 4))
+  if (!photons.alloc(sizeof(GiPhoton) * cap, st) || !keys.alloc(8 * cap, st) || !count.alloc(16, st) || !first.alloc(8 * (size_t)(nl + 1), st) ||
+      !cursor.alloc(16, st) || !list.alloc(filter ? 4 * batch : 4, st))
     return 1;
-  GI_CUDA(cudaMemsetAsync(count.p, 0, 8, st));
-  unsigned long long stored = 0;
+  GI_CUDA(cudaMemsetAsync(count.p, 0, 16, st));
+  unsigned long long stored = 0, stored_local = 0;            // over all ranks / in this rank's sink
   uint64_t emitted = 0;
   // photonmap.cpp:157-196 (global) / :213-250 (caustic)
   double average_bounce_rate = map_type == MAP_GLOBAL ? 4.0 : (double)env.p.max_photon_depth;
@@ -302,48 +317,50 @@ static int trace_map(GiContext *ctx, const ShadeEnv &env_in, int map_type, int t
     uint64_t assigned = 0;
     for (int i = 0; i < nl; i++) assigned += (uint64_t)std::max(0, (int)ceil(emit_goal * (light_powers[i] / total_power)));
     const uint64_t n = h_first[nl];
-    for (;;) {                                               // repeated only if the sink was too small
+    const uint64_t n_local = n > rank ? (n - rank + world - 1) / world : 0;      // photons t = rank (mod world), t < n
+    for (;;) {                                               // repeated only if this rank's sink was too small
       GI_CUDA(cudaMemcpyAsync(first.p, h_first.data(), 8 * (size_t)(nl + 1), cudaMemcpyHostToDevice, st));
       PhotonSink sink{photons.as<GiPhoton>(), keys.as<uint64_t>(), count.as<unsigned long long>(), cap};
-      Round rd; rd.map_type = map_type; rd.id0 = id_base + emitted; rd.first = first.as<uint64_t>(); rd.centroid = centroid;
-      const bool filter = map_type == MAP_CAUSTIC && env.n_spec_boxes >= 0;
-      const uint64_t batch = 1ull << 26;                      // photons per launch (bounds the survivor list)
-      for (uint64_t t0 = 0; t0 < n; t0 += batch) {
-        const uint64_t m = std::min(batch, n - t0);
-        uint64_t items = m;
+      Round rd; rd.map_type = map_type; rd.id0 = emitted; rd.first = first.as<uint64_t>(); rd.centroid = centroid;
+      rd.rank = rank; rd.world = world;
+      for (uint64_t w0 = 0; w0 < n_local; w0 += batch) {
+        const uint64_t m = std::min(batch, n_local - w0);
         GI_CUDA(cudaMemsetAsync(cursor.p, 0, 16, st));
+        unsigned int *kept = (unsigned int *)(cursor.as<unsigned long long>() + 1);
         if (filter) {
-          emit_filter_kernel<<<(unsigned)((m + 255) / 256), 256, 0, st>>>(env, rd, t0, (uint32_t)m, list.as<uint32_t>(),
-                                                                         (unsigned int *)(cursor.as<unsigned long long>() + 1));
-          ctx->launches++;
-          unsigned int kept = 0;
-          GI_CUDA(cudaMemcpyAsync(&kept, cursor.as<unsigned long long>() + 1, 4, cudaMemcpyDeviceToHost, st));
-          GI_CUDA(cudaStreamSynchronize(st));
-          items = kept;
-        }
-        if (items > 0) {
-          const uint64_t want = (items + 127) / 128, gcap = (uint64_t)ctx->sm_count * 8;     // persistent: 8 CTAs of 4 warps per SM
-          trace_kernel<<<(unsigned)std::max<uint64_t>(1, std::min(want, gcap)), 128, 0, st>>>(
-              env, rd, t0, items, filter ? list.as<uint32_t>() : nullptr, cursor.as<unsigned long long>(), sink);
+          emit_filter_kernel<<<(unsigned)((m + 255) / 256), 256, 0, st>>>(env, rd, w0, (uint32_t)m, list.as<uint32_t>(), kept);
           ctx->launches++;
         }
+        // persistent: 8 CTAs of 4 warps per SM; with the filter the item count stays on the device (no host round trip)
+        const uint64_t want = (m + 127) / 128, gcap = (uint64_t)ctx->sm_count * 8;
+        trace_kernel<<<(unsigned)std::max<uint64_t>(1, std::min(want, gcap)), 128, 0, st>>>(
+            env, rd, w0, m, filter ? kept : nullptr, filter ? list.as<uint32_t>() : nullptr, cursor.as<unsigned long long>(), sink);
+        ctx->launches++;
         GI_CUDA(cudaGetLastError());
       }
       unsigned long long now = 0;
       GI_CUDA(cudaMemcpyAsync(&now, count.p, 8, cudaMemcpyDeviceToHost, st));
       GI_CUDA(cudaStreamSynchronize(st));
-      if (now <= cap) { stored = now; break; }
+      if (now <= cap) { stored_local = now; break; }
       // grow the sink, keep what earlier rounds stored, and run this round again (same streams -> same photons)
       const unsigned long long ncap = std::max(now + now / 2, cap * 2);
       Buf np, nk;
-      if (!np.alloc(sizeof(GiPhoton) * ncap) || !nk.alloc(8 * ncap)) return 1;
-      GI_CUDA(cudaMemcpyAsync(np.p, photons.p, sizeof(GiPhoton) * stored, cudaMemcpyDeviceToDevice, st));
-      GI_CUDA(cudaMemcpyAsync(nk.p, keys.p, 8 * stored, cudaMemcpyDeviceToDevice, st));
-      GI_CUDA(cudaMemcpyAsync(count.p, &stored, 8, cudaMemcpyHostToDevice, st));
+      if (!np.alloc(sizeof(GiPhoton) * ncap, st) || !nk.alloc(8 * ncap, st)) return 1;
+      GI_CUDA(cudaMemcpyAsync(np.p, photons.p, sizeof(GiPhoton) * stored_local, cudaMemcpyDeviceToDevice, st));
+      GI_CUDA(cudaMemcpyAsync(nk.p, keys.p, 8 * stored_local, cudaMemcpyDeviceToDevice, st));
+      GI_CUDA(cudaMemcpyAsync(count.p, &stored_local, 8, cudaMemcpyHostToDevice, st));
       GI_CUDA(cudaStreamSynchronize(st));
       std::swap(photons.p, np.p); std::swap(keys.p, nk.p);
       cap = ncap;
     }
+    // the round's stored count over all ranks drives the next goal (photonmap.cpp:175-192)
+    if (world > 1) {
+      uint64_t *tot = count.as<uint64_t>() + 1;
+      GI_CUDA(cudaMemcpyAsync(tot, count.p, 8, cudaMemcpyDeviceToDevice, st));
+      if (!comm_allreduce_sum_u64(ctx, tot, 1, st)) return 1;
+      GI_CUDA(cudaMemcpyAsync(&stored, tot, 8, cudaMemcpyDeviceToHost, st));
+      GI_CUDA(cudaStreamSynchronize(st));
+    } else stored = stored_local;
     emitted += assigned;
     rounds_out++;
     if (stored > 0 && emitted > 0) {
@@ -356,24 +373,43 @@ static int trace_map(GiContext *ctx, const ShadeEnv &env_in, int map_type, int t
     }
   }
   emitted_out = emitted;
-  // deterministic order: sort by (emitted photon number, bounce)
   PhotonMapStore &m = ctx->maps[map_type];
   free_map(m);
   m.dev.n = stored;
   if (stored == 0) return 0;
   if (stored >= (1ull << 31)) { set_error("gi_trace_photons: more than 2^31 - 1 photons stored"); return 1; }
+  // replicate: counts, then ONE ragged all-gather of the photons and one of their keys (comm.cu)
+  Buf all_photons, all_keys, counts_dev;
+  const GiPhoton *src_photons = photons.as<GiPhoton>(); uint64_t *src_keys = keys.as<uint64_t>();
+  if (world > 1) {
+    std::vector<uint64_t> h_counts(world, 0), bytes32(world), off32(world), bytes8(world), off8(world);
+    if (!counts_dev.alloc(8 * (size_t)(world + 1), st)) return 1;
+    GI_CUDA(cudaMemcpyAsync(counts_dev.as<uint64_t>() + world, count.p, 8, cudaMemcpyDeviceToDevice, st));
+    if (!comm_allgather_u64(ctx, counts_dev.as<uint64_t>() + world, counts_dev.as<uint64_t>(), 1, st)) return 1;
+    GI_CUDA(cudaMemcpyAsync(h_counts.data(), counts_dev.p, 8 * (size_t)world, cudaMemcpyDeviceToHost, st));
+    GI_CUDA(cudaStreamSynchronize(st));
+    uint64_t total = 0;
+    for (uint32_t r = 0; r < world; r++) { off32[r] = 32 * total; off8[r] = 8 * total; bytes32[r] = 32 * h_counts[r]; bytes8[r] = 8 * h_counts[r]; total += h_counts[r]; }
+    if (total != stored) { set_error("gi_trace_photons: ranks disagree on the stored photon count"); return 1; }
+    if (!all_photons.alloc(32 * total, st) || !all_keys.alloc(8 * total, st)) return 1;
+    if (!comm_allgatherv(ctx, photons.p, all_photons.p, bytes32.data(), off32.data(), st) ||
+        !comm_allgatherv(ctx, keys.p, all_keys.p, bytes8.data(), off8.data(), st)) return 1;
+    src_photons = all_photons.as<GiPhoton>(); src_keys = all_keys.as<uint64_t>();
+  }
+  // deterministic order: sort by (emitted photon number, bounce) -- only the key bits that can be set take part
   Buf keys2, order, order2, tmp;
-  if (!keys2.alloc(8 * stored) || !order.alloc(4 * stored) || !order2.alloc(4 * stored)) return 1;
+  if (!keys2.alloc(8 * stored, st) || !order.alloc(4 * stored, st) || !order2.alloc(4 * stored, st)) return 1;
   const unsigned blocks = (unsigned)((stored + 255) / 256);
   iota_kernel<<<blocks, 256, 0, st>>>(order.as<uint32_t>(), stored);
+  int end_bit = 8; while (end_bit < 64 && (emitted >> (end_bit - 8)) != 0) end_bit++;
   size_t tmp_bytes = 0;
-  cub::DeviceRadixSort::SortPairs(nullptr, tmp_bytes, keys.as<uint64_t>(), keys2.as<uint64_t>(), order.as<uint32_t>(),
-                                  order2.as<uint32_t>(), (int)stored, 0, 64, st);
-  if (!tmp.alloc(tmp_bytes)) return 1;
-  GI_CUDA(cub::DeviceRadixSort::SortPairs(tmp.p, tmp_bytes, keys.as<uint64_t>(), keys2.as<uint64_t>(), order.as<uint32_t>(),
-                                          order2.as<uint32_t>(), (int)stored, 0, 64, st));
+  cub::DeviceRadixSort::SortPairs(nullptr, tmp_bytes, src_keys, keys2.as<uint64_t>(), order.as<uint32_t>(),
+                                  order2.as<uint32_t>(), (int)stored, 0, end_bit, st);
+  if (!tmp.alloc(tmp_bytes, st)) return 1;
+  GI_CUDA(cub::DeviceRadixSort::SortPairs(tmp.p, tmp_bytes, src_keys, keys2.as<uint64_t>(), order.as<uint32_t>(),
+                                          order2.as<uint32_t>(), (int)stored, 0, end_bit, st));
   GI_CUDA(cudaMalloc(&m.raw, sizeof(GiPhoton) * stored));
-  permute_kernel<<<blocks, 256, 0, st>>>(photons.as<GiPhoton>(), order2.as<uint32_t>(), stored, (GiPhoton *)m.raw);
+  permute_kernel<<<blocks, 256, 0, st>>>(src_photons, order2.as<uint32_t>(), stored, (GiPhoton *)m.raw);
   ctx->launches += 4;
   GI_CUDA(cudaGetLastError());
   GI_CUDA(cudaStreamSynchronize(st));
@@ -432,30 +468,26 @@ int gi_trace_photons(GiContext *ctx, const GiParams *params, GiPhotonStats *stat
   cudaEvent_t e0, e1, e2; cudaEventCreate(&e0); cudaEventCreate(&e1); cudaEventCreate(&e2);
   do {
     if (!cuda_ok(cudaMemcpyAsync(d_lights, ctx->lights.data(), sizeof(GiLight) * nl, cudaMemcpyHostToDevice, ctx->stream), "H2D lights")) break;
-    // the budget split of MapPhotons (:289-321): every "thread" gets COUNT / THREADS, thread 0 the remainder
-    const int world = params->world_size > 1 ? params->world_size : 1, rank = params->world_size > 1 ? params->rank : 0;
-    if (rank < 0 || rank >= world) { set_error("gi_trace_photons: rank outside [0, world_size)"); break; }
+    // The budget split of MapPhotons (:289-321) -- COUNT / THREADS photons per worker -- becomes a split of every
+    // emission round over the ranks of the communicator (trace_map); without one this context traces everything.
+    if (params->world_size > 1 && !comm_attached(ctx)) {
+      set_error("gi_trace_photons: params->world_size > 1 needs a communicator (gi_comm_init_rank / gi_comm_init_all)");
+      break;
+    }
     const bool want_global = params->indirect_illum || params->direct_photon_illum, want_caustic = params->caustic_illum != 0;
-    auto share = [&](int count) { const int per = count / world; return rank == 0 ? count - per * (world - 1) : per; };
     cudaEventRecord(e0, ctx->stream);
     int rounds = 0;
-    // photon numbers of different ranks never collide: rank r owns [r << 40, (r + 1) << 40)
-    const uint64_t id_base = (uint64_t)rank << 40;
-    if (want_global && trace_map(ctx, env, MAP_GLOBAL, share(params->global_photon_count), light_powers, total_power, id_base,
-                                 s.global_emitted, rounds)) break;
-    if (want_caustic && trace_map(ctx, env, MAP_CAUSTIC, share(params->caustic_photon_count), light_powers, total_power, id_base,
-                                  s.caustic_emitted, rounds)) break;
+    if (want_global && trace_map(ctx, env, MAP_GLOBAL, params->global_photon_count, light_powers, total_power, s.global_emitted, rounds)) break;
+    if (want_caustic && trace_map(ctx, env, MAP_CAUSTIC, params->caustic_photon_count, light_powers, total_power, s.caustic_emitted, rounds)) break;
     cudaEventRecord(e1, ctx->stream);
     s.rounds = rounds;
     s.global_stored = ctx->maps[0].dev.n; s.caustic_stored = ctx->maps[1].dev.n;
-    if (world == 1) {
-      // power scale, flag updates and kd-tree builds of MapPhotons (:339-377)
-      if (want_global && s.global_stored == 0) { s.indirect_illum = 0; s.direct_photon_illum = 0; }
-      if (want_caustic && s.caustic_stored == 0) s.caustic_illum = 0;
-      if (s.global_stored && gi_scale_photon_power(ctx, 0, total_power / (double)s.global_emitted)) break;
-      if (s.caustic_stored && gi_scale_photon_power(ctx, 1, total_power / (double)s.caustic_emitted)) break;
-      if (gi_build_maps(ctx, params)) break;
-    }
+    // power scale, flag updates and kd-tree builds of MapPhotons (:339-377); counts are global, every rank does the same
+    if (want_global && s.global_stored == 0) { s.indirect_illum = 0; s.direct_photon_illum = 0; }
+    if (want_caustic && s.caustic_stored == 0) s.caustic_illum = 0;
+    if (s.global_stored && gi_scale_photon_power(ctx, 0, total_power / (double)s.global_emitted)) break;
+    if (s.caustic_stored && gi_scale_photon_power(ctx, 1, total_power / (double)s.caustic_emitted)) break;
+    if (gi_build_maps(ctx, params)) break;
     cudaEventRecord(e2, ctx->stream);
     if (!cuda_ok(cudaStreamSynchronize(ctx->stream), "trace sync")) break;
     float a = 0, b = 0; cudaEventElapsedTime(&a, e0, e1); cudaEventElapsedTime(&b, e1, e2);

@@ -25,6 +25,7 @@
 #include <cstdio>
 #include <cstdlib>
 #include <cstring>
+#include "comm.h"
 #include "context.h"
 #include "gather.h"
 #include "shade.cuh"
@@ -427,6 +428,37 @@ __global__ void resolve_kernel(const double *__restrict__ accum, int width, int 
   for (int c = 0; c < 3; c++) rgb[3 * ((size_t)y * width + x) + c] = (uint8_t)(int)(255 * (box_weight * s[c]));
 }
 
+// Multi-GPU frame (comm.cu): rank r owns the pixel columns x = r (mod world).  resolve_strip_kernel is resolve_kernel for
+// those columns only, written as a compact strip [y][l][3] with l = x / world; on rank 0 assemble_kernel interleaves the
+// gathered strips (strip of rank r starts at byte off[r]) into the frame.
+__global__ void resolve_strip_kernel(const double *__restrict__ accum, int width, int height, int aaf, int sh, int rank, int world,
+                                     uint8_t *strip) {
+  const int l = blockIdx.x * blockDim.x + threadIdx.x, y = blockIdx.y * blockDim.y + threadIdx.y;
+  const int ncols = (width - rank + world - 1) / world;
+  if (l >= ncols || y >= height) return;
+  const int x = l * world + rank;
+  const double box_weight = 1.0 / aaf / aaf;
+  double s[3] = {0, 0, 0};
+  for (int j = y * aaf; j < (y + 1) * aaf; j++)
+    for (int i = x * aaf; i < (x + 1) * aaf; i++)
+      for (int c = 0; c < 3; c++) {
+        double v = accum[3 * ((size_t)i * sh + j) + c];
+        if (v < 0) v = 0;
+        if (v > 1.0) v = 1.0;
+        s[c] += v;
+      }
+  for (int c = 0; c < 3; c++) strip[3 * ((size_t)y * ncols + l) + c] = (uint8_t)(int)(255 * (box_weight * s[c]));
+}
+__global__ void assemble_kernel(const uint8_t *__restrict__ strips, const uint64_t *__restrict__ off, int width, int height, int world,
+                                uint8_t *rgb) {
+  const int x = blockIdx.x * blockDim.x + threadIdx.x, y = blockIdx.y * blockDim.y + threadIdx.y;
+  if (x >= width || y >= height) return;
+  const int r = x % world, l = x / world, ncols = (width - r + world - 1) / world;
+  const uint8_t *src = strips + off[r] + 3 * ((size_t)y * ncols + l);
+  uint8_t *dst = rgb + 3 * ((size_t)y * width + x);
+  dst[0] = src[0]; dst[1] = src[1]; dst[2] = src[2];
+}
+
 // ------------------------------------------------------------------------------------------------ host driver
 namespace {
 
@@ -466,7 +498,8 @@ struct Workspace {
   static constexpr uint64_t chunk = 1ull << 22;          // primary samples per pass
   static constexpr uint32_t batch_max = 1u << 21;        // secondary paths per pass
   static constexpr unsigned long long qcap = 1ull << 22; // >= chunk (direct_kernel pushes at most one request per hit)
-  DevBuf hits, n_items, offs, item_rgb, item_pix, scan_tmp, item_hit, hit_scan_tmp, lights, stats, accum;
+  DevBuf hits, n_items, offs, item_rgb, item_pix, scan_tmp, item_hit, hit_scan_tmp, lights, stats, accum, image, strips, comm_tmp;
+  size_t image_bytes = 0, strips_bytes = 0;
   QueueStore qg, qc;
   size_t scan_bytes = 0, hit_scan_bytes = 0, accum_doubles = 0, n_lights = 0;
   bool ready = false;
@@ -487,6 +520,18 @@ struct Workspace {
     if (!accum.alloc(sizeof(double) * doubles)) { accum_doubles = 0; return false; }
     accum_doubles = doubles;
     return true;
+  }
+  bool fit_image(size_t bytes) {
+    if (bytes <= image_bytes) return true;
+    if (!image.alloc(bytes)) { image_bytes = 0; return false; }
+    image_bytes = bytes;
+    return true;
+  }
+  bool fit_strips(size_t bytes) {
+    if (bytes <= strips_bytes) return true;
+    if (!strips.alloc(bytes)) { strips_bytes = 0; return false; }
+    strips_bytes = bytes;
+    return comm_tmp.p || comm_tmp.alloc(8 * 64 + 8 * 8);          // strip offsets of up to 64 ranks + the 7 counters
   }
   bool fit_lights(size_t n) {
     if (n <= n_lights && lights.p) return true;
@@ -729,8 +774,12 @@ static int render_common(GiContext *ctx, const GiParams *params, int width, int 
     if (!cuda_ok(cudaMemsetAsync(accum, 0, sizeof(double) * 3 * npix, ctx->stream), "memset(accum)")) break;
     if (!cuda_ok(cudaMemsetAsync(d_stats, 0, 2 * sizeof(RayStats), ctx->stream), "memset(stats)")) break;
     cudaEventRecord(e0, ctx->stream);
-    // sharding across GPUs: rank r of w renders the pixel columns x = r (mod w), the rest of the frame stays zero
-    const int world = params->world_size > 1 ? params->world_size : 1, rank = params->world_size > 1 ? params->rank : 0;
+    // sharding across GPUs: rank r of w renders the pixel columns x = r (mod w), the rest of the frame stays zero.
+    // The communicator of the context decides; without one params->rank / world_size select the columns (test hook).
+    const bool comm = comm_attached(ctx);
+    const int world = comm ? comm_world(ctx) : (params->world_size > 1 ? params->world_size : 1);
+    const int rank = comm ? comm_rank(ctx) : (params->world_size > 1 ? params->rank : 0);
+    if (world > 64) { set_error("gi_render: at most 64 ranks"); break; }
     if (rank < 0 || rank >= world) { set_error("gi_render: rank outside [0, world_size)"); break; }
     if (render_accum(ctx, *params, (int)sw, (int)sh, aaf, rank, world, accum, d_stats, paths)) break;
     cudaEventRecord(e1, ctx->stream);
@@ -763,23 +812,65 @@ int gi_render_float(GiContext *ctx, const GiParams *params, int width, int heigh
 
 int gi_render(GiContext *ctx, const GiParams *params, int width, int height, int aa, uint8_t *rgb_out,
               GiRenderStats *stats) {
-  if (!rgb_out) { set_error("gi_render: null output buffer"); return 1; }
+  const bool sharded = ctx && comm_attached(ctx) && comm_world(ctx) > 1;
+  if (!rgb_out && !(sharded && comm_rank(ctx) != 0)) { set_error("gi_render: null output buffer"); return 1; }
   double *accum = nullptr; int sw = 0, sh = 0;
   if (render_common(ctx, params, width, height, aa, &accum, &sw, &sh, stats)) return 1;
-  uint8_t *d_rgb = nullptr;
-  int rc = 1;
-  do {
-    if (!cuda_ok(cudaMalloc(&d_rgb, (size_t)width * height * 3), "cudaMalloc(image)")) break;
-    dim3 block(16, 16), grid((width + 15) / 16, (height + 15) / 16);
-    resolve_kernel<<<grid, block, 0, ctx->stream>>>(accum, width, height, 1 << aa, sh, d_rgb);
+  Workspace *ws = workspace(ctx);
+  const size_t frame_bytes = (size_t)width * height * 3;
+  if (!ws || !ws->fit_image(frame_bytes)) return 1;
+  uint8_t *d_rgb = ws->image.as<uint8_t>();
+  cudaStream_t st = ctx->stream;
+  dim3 block(16, 16);
+  if (!sharded) {
+    dim3 grid((width + 15) / 16, (height + 15) / 16);
+    resolve_kernel<<<grid, block, 0, st>>>(accum, width, height, 1 << aa, sh, d_rgb);
     ctx->launches++;
-    if (!cuda_ok(cudaGetLastError(), "resolve_kernel")) break;
-    if (!cuda_ok(cudaMemcpyAsync(rgb_out, d_rgb, (size_t)width * height * 3, cudaMemcpyDeviceToHost, ctx->stream), "D2H image")) break;
-    if (!cuda_ok(cudaStreamSynchronize(ctx->stream), "render sync")) break;
-    rc = 0;
-  } while (0);
-  cudaFree(d_rgb);
-  return rc;
+    GI_CUDA(cudaGetLastError());
+    GI_CUDA(cudaMemcpyAsync(rgb_out, d_rgb, frame_bytes, cudaMemcpyDeviceToHost, st));
+    GI_CUDA(cudaStreamSynchronize(st));
+    return 0;
+  }
+  // ---- multi-GPU: own column strip -> gather to rank 0 -> interleave; ray counters summed over the ranks
+  const int world = comm_world(ctx), rank = comm_rank(ctx);
+  std::vector<uint64_t> bytes_of(world), off(world);
+  uint64_t total = 0;
+  for (int r = 0; r < world; r++) { bytes_of[r] = 3ull * height * ((width - r + world - 1) / world); off[r] = total; total += bytes_of[r]; }
+  if (!ws->fit_strips(frame_bytes + bytes_of[0])) return 1;              // [all strips (rank 0) | my strip]
+  uint8_t *d_all = ws->strips.as<uint8_t>(), *d_mine = d_all + frame_bytes;
+  uint64_t *d_off = ws->comm_tmp.as<uint64_t>(), *d_cnt = d_off + 64;
+  const int ncols = (width - rank + world - 1) / world;
+  if (ncols > 0) {
+    dim3 grid((ncols + 15) / 16, (height + 15) / 16);
+    resolve_strip_kernel<<<grid, block, 0, st>>>(accum, width, height, 1 << aa, sh, rank, world, d_mine);
+    ctx->launches++;
+    GI_CUDA(cudaGetLastError());
+  }
+  if (!comm_gatherv_root0(ctx, d_mine, d_all, bytes_of.data(), off.data(), st)) return 1;
+  if (stats) {
+    uint64_t h[7] = {stats->screen_rays, stats->shadow_rays, stats->monte_rays, stats->transmissive_samples, stats->specular_samples,
+                     stats->indirect_samples, stats->caustic_samples};
+    GI_CUDA(cudaMemcpyAsync(d_cnt, h, sizeof(h), cudaMemcpyHostToDevice, st));
+    if (!comm_allreduce_sum_u64(ctx, d_cnt, 7, st)) return 1;
+    GI_CUDA(cudaMemcpyAsync(h, d_cnt, sizeof(h), cudaMemcpyDeviceToHost, st));
+    GI_CUDA(cudaStreamSynchronize(st));
+    stats->screen_rays = h[0]; stats->shadow_rays = h[1]; stats->monte_rays = h[2]; stats->transmissive_samples = h[3];
+    stats->specular_samples = h[4]; stats->indirect_samples = h[5]; stats->caustic_samples = h[6];
+  } else {
+    // every rank makes the same collective calls
+    GI_CUDA(cudaMemsetAsync(d_cnt, 0, 7 * 8, st));
+    if (!comm_allreduce_sum_u64(ctx, d_cnt, 7, st)) return 1;
+  }
+  if (rank == 0) {
+    GI_CUDA(cudaMemcpyAsync(d_off, off.data(), 8 * (size_t)world, cudaMemcpyHostToDevice, st));
+    dim3 grid((width + 15) / 16, (height + 15) / 16);
+    assemble_kernel<<<grid, block, 0, st>>>(d_all, d_off, width, height, world, d_rgb);
+    ctx->launches++;
+    GI_CUDA(cudaGetLastError());
+    GI_CUDA(cudaMemcpyAsync(rgb_out, d_rgb, frame_bytes, cudaMemcpyDeviceToHost, st));
+  }
+  GI_CUDA(cudaStreamSynchronize(st));
+  return 0;
 }
 
 }  // extern "C"

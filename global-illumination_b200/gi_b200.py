@@ -87,7 +87,8 @@ EXPORTS = ["gi_abi_version", "gi_last_error", "gi_create", "gi_destroy", "gi_def
            "gi_load_photons", "gi_load_photons_device", "gi_load_photons_file", "gi_dump_photons_file",
            "gi_photon_count", "gi_get_photons", "gi_get_photons_device", "gi_build_maps", "gi_gather_batch", "gi_gather_batch_device",
            "gi_trace_photons", "gi_scale_photon_power", "gi_render", "gi_render_float",
-           "gi_default_cli_options", "gi_parse_args", "gi_write_image"]
+           "gi_default_cli_options", "gi_parse_args", "gi_write_image",
+           "gi_comm_unique_id", "gi_comm_init_rank", "gi_comm_init_all", "gi_comm_info", "gi_comm_destroy"]
 
 _lib = None
 
@@ -130,6 +131,11 @@ def lib():
         L.gi_scale_photon_power.argtypes = [vp, i32, dbl]
         L.gi_render.argtypes = [vp, ctypes.POINTER(GiParams), i32, i32, i32, vp, ctypes.POINTER(GiRenderStats)]
         L.gi_render_float.argtypes = [vp, ctypes.POINTER(GiParams), i32, i32, i32, vp, ctypes.POINTER(GiRenderStats)]
+        L.gi_comm_unique_id.argtypes = [vp]
+        L.gi_comm_init_rank.argtypes = [vp, vp, i32, i32]
+        L.gi_comm_init_all.argtypes = [ctypes.POINTER(vp), i32]
+        L.gi_comm_info.argtypes = [vp, ctypes.POINTER(i32), ctypes.POINTER(i32)]
+        L.gi_comm_destroy.argtypes = [vp]
         _lib = L
     return _lib
 
@@ -141,6 +147,19 @@ class GiError(RuntimeError):
 def _check(rc):
     if rc != 0:
         raise GiError(lib().gi_last_error().decode(errors="replace"))
+
+
+def comm_unique_id():
+    """128 bytes (an ncclUniqueId) made by rank 0; hand them to every rank's Context.comm_init_rank"""
+    buf = ctypes.create_string_buffer(128)
+    _check(lib().gi_comm_unique_id(buf))
+    return buf.raw
+
+
+def comm_init_all(contexts):
+    """one process driving several GPUs: rank i = contexts[i] (ncclCommInitAll)"""
+    arr = (ctypes.c_void_p * len(contexts))(*[c.handle for c in contexts])
+    _check(lib().gi_comm_init_all(arr, len(contexts)))
 
 
 def default_params():
@@ -190,6 +209,18 @@ class Context:
             self.close()
         except Exception:
             pass
+
+    def comm_init_rank(self, unique_id, rank, world):
+        buf = ctypes.create_string_buffer(bytes(unique_id), 128)
+        _check(lib().gi_comm_init_rank(self.handle, buf, rank, world))
+
+    def comm_info(self):
+        r, w = ctypes.c_int(), ctypes.c_int()
+        _check(lib().gi_comm_info(self.handle, ctypes.byref(r), ctypes.byref(w)))
+        return r.value, w.value
+
+    def comm_destroy(self):
+        _check(lib().gi_comm_destroy(self.handle))
 
     def launch_count(self):
         n = ctypes.c_uint64()
@@ -286,11 +317,13 @@ class Context:
         _check(lib().gi_render_float(self.handle, ctypes.byref(params), width, height, aa, out.ctypes.data, ctypes.byref(st)))
         return out, st
 
-    def render(self, params, width, height, aa=0):
-        """RenderImage(): uint8 array [H, W, 3], row 0 = bottom row (R2Image order)."""
-        out = np.zeros((height, width, 3), dtype=np.uint8)
+    def render(self, params, width, height, aa=0, want_image=True):
+        """RenderImage(): uint8 array [H, W, 3], row 0 = bottom row (R2Image order).  With a communicator attached the
+        frame arrives on rank 0 only; the other ranks pass want_image=False and get None."""
+        out = np.zeros((height, width, 3), dtype=np.uint8) if want_image else None
         st = GiRenderStats()
-        _check(lib().gi_render(self.handle, ctypes.byref(params), width, height, aa, out.ctypes.data, ctypes.byref(st)))
+        _check(lib().gi_render(self.handle, ctypes.byref(params), width, height, aa, out.ctypes.data if want_image else None,
+                               ctypes.byref(st)))
         return out, st
 
 

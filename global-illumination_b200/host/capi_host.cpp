@@ -60,7 +60,7 @@ void gi_default_params(GiParams *p) {
 }
 
 // ParseArgs (src/utils/io_utils.cpp:16-214): same flags, same clamping, same order dependence.  Extra flags of this
-// implementation: -seed N, -device N.  Returns 0 on success; an unknown flag or a missing file name is an error.
+// implementation: -seed N, -device N, -gpus N.  Returns 0 on success; an unknown flag or a missing file name is an error.
 int gi_parse_args(int argc, const char *const *argv, GiParams *p, GiCliOptions *o) {
   if (!p || !o || (argc > 0 && !argv)) { gi::set_error("gi_parse_args: null argument"); return 1; }
   int i = 1;
@@ -136,6 +136,7 @@ int gi_parse_args(int argc, const char *const *argv, GiParams *p, GiCliOptions *
     }
     else if (is("-seed")) { if (!next(v)) return 1; p->seed = strtoull(v, nullptr, 10); }
     else if (is("-device")) { if (!next(v)) return 1; o->device = atoi(v); }
+    else if (is("-gpus")) { if (!next(v)) return 1; o->gpus = atoi(v); if (o->gpus < 1) o->gpus = 1; }
     else { gi::set_error(std::string("Invalid program argument: ") + a); return 1; }
   }
   if (!o->input_scene_name || !o->output_image_name) { gi::set_error("Usage: photonmap inputscenefile outputimagefile [-FLAGS]"); return 1; }
@@ -153,7 +154,7 @@ int gi_write_image(const char *path, const uint8_t *rgb, int width, int height) 
 void gi_default_cli_options(GiCliOptions *o) {       // src/photonmap.cpp:22-34
   if (!o) return;
   memset(o, 0, sizeof(*o));
-  o->width = 1024; o->height = 1024; o->aa = 2; o->real_material = 0; o->device = 0;
+  o->width = 1024; o->height = 1024; o->aa = 2; o->real_material = 0; o->device = 0; o->gpus = 1;
 }
 
 }  // extern "C"

@@ -3,13 +3,16 @@
 // same stages in the same order -- read scene, MapPhotons, RenderImage, write image -- and the same -v report
 // blocks; every stage runs on the GPU, and the program fails if there is none.
 //
-// Extra flags: -seed N (the reference RNG is unseeded), -device N, -save_global f / -save_caustic f and
+// Extra flags: -seed N (the reference RNG is unseeded), -device N, -gpus N (N GPUs of this box share the photon pass and
+// the frame: one context + one host thread per GPU, NCCL between them), -save_global f / -save_caustic f and
 // -load_global f / -load_caustic f (photon maps as "GIPM" files, shared with oracle/ref_harness).
 #include <chrono>
 #include <cstdio>
 #include <cstdlib>
 #include <cstring>
 #include <string>
+#include <thread>
+#include <unistd.h>
 #include <vector>
 #include "gi_b200.h"
 
@@ -47,76 +50,98 @@ int main(int argc, char **argv) {
     fflush(stdout);
   }
 
-  GiContext *ctx = nullptr;
-  if (gi_create(opt.device, &ctx)) return fail("photonmap");
+  // one context per GPU; -gpus N: devices device .. device + N - 1 share the photon pass and the frame (gi_b200.h, multi-GPU)
+  const int ngpu = opt.gpus > 1 ? opt.gpus : 1;
+  std::vector<GiContext *> ctxs(ngpu, nullptr);
   t0 = std::chrono::steady_clock::now();
-  if (gi_upload_scene(ctx, &scene)) return fail("Unable to upload scene");
+  for (int r = 0; r < ngpu; r++) {
+    if (gi_create(opt.device + r, &ctxs[r])) return fail("photonmap");
+    if (gi_upload_scene(ctxs[r], &scene)) return fail("Unable to upload scene");
+  }
+  if (ngpu > 1 && gi_comm_init_all(ctxs.data(), ngpu)) return fail("Unable to set up the GPU communicator");
   if (params.verbose) {
     printf("Built GPU scene ...\n  Time = %.2f seconds\n  # Primitives = %d\n", seconds_since(t0), scene.n_prims);
+    if (ngpu > 1) printf("  # GPUs = %d\n", ngpu);
     fflush(stdout);
   }
-
-  // MapPhotons (photonmap.cpp:260-436)
-  if (params.indirect_illum || params.caustic_illum || params.direct_photon_illum) {
-    t0 = std::chrono::steady_clock::now();
-    GiPhotonStats ps; memset(&ps, 0, sizeof(ps));
-    if (load[0] || load[1]) {
+  std::vector<uint8_t> rgb((size_t)opt.width * opt.height * 3);
+  std::vector<int> status(ngpu, 0);
+  // what the reference's main() does between ReadScene and WriteImage, once per GPU; rank 0 reports and owns the image
+  auto run_rank = [&](int r) -> int {
+    GiContext *ctx = ctxs[r];
+    GiParams prm = params;
+    const bool talk = prm.verbose && r == 0;
+    // MapPhotons (photonmap.cpp:260-436)
+    if (prm.indirect_illum || prm.caustic_illum || prm.direct_photon_illum) {
+      const auto t0 = std::chrono::steady_clock::now();
+      GiPhotonStats ps; memset(&ps, 0, sizeof(ps));
+      if (load[0] || load[1]) {
+        for (int m = 0; m < 2; m++)
+          if (load[m] && gi_load_photons_file(ctx, m, load[m])) return fail("Unable to load photon map");
+        const auto tb = std::chrono::steady_clock::now();
+        if (gi_build_maps(ctx, &prm)) return fail("Unable to build photon maps");
+        ps.build_ms = seconds_since(tb) * 1000.0;
+        gi_photon_count(ctx, 0, &ps.global_stored); gi_photon_count(ctx, 1, &ps.caustic_stored);
+        if (!ps.global_stored) { prm.indirect_illum = 0; prm.direct_photon_illum = 0; }
+        if (!ps.caustic_stored) prm.caustic_illum = 0;
+      } else {
+        if (talk) {
+          if (prm.indirect_illum || prm.direct_photon_illum) printf("Building global photon map ...\n");
+          if (prm.caustic_illum) printf("Building caustic photon map ...\n");
+        }
+        if (gi_trace_photons(ctx, &prm, &ps)) return fail("Unable to trace photons");
+        if (scene.n_lights > 0 && ps.total_power > 0) {
+          prm.indirect_illum = ps.indirect_illum; prm.caustic_illum = ps.caustic_illum;
+          prm.direct_photon_illum = ps.direct_photon_illum;
+        }
+      }
+      if (talk) {
+        const bool cache = prm.irradiance_cache && (prm.indirect_illum || prm.direct_photon_illum);
+        printf("Building kdtrees ...\n");
+        if (cache) printf("Building irradiance cache ...\n");
+        printf("Built photon map ...\n");
+        printf("  Total Time = %.2f seconds\n", seconds_since(t0));
+        printf("  Photon Tracing = %.2f seconds\n", ps.trace_ms / 1000.0);
+        printf("  KdTree Construction = %.2f seconds\n", ps.build_ms / 1000.0);
+        if (cache) printf("  Irradiance Cache Computation = %.2f seconds\n", ps.cache_ms / 1000.0);
+        unsigned long long total = 0;
+        if (prm.indirect_illum || prm.direct_photon_illum) { printf("  # Global Photons Stored = %llu\n", (unsigned long long)ps.global_stored); total += ps.global_stored; }
+        if (prm.caustic_illum) { printf("  # Caustic Photons Stored = %llu\n", (unsigned long long)ps.caustic_stored); total += ps.caustic_stored; }
+        printf("Total Photons Stored: %llu\n", total);
+        fflush(stdout);
+      }
       for (int m = 0; m < 2; m++)
-        if (load[m] && gi_load_photons_file(ctx, m, load[m])) return fail("Unable to load photon map");
-      const auto tb = std::chrono::steady_clock::now();
-      if (gi_build_maps(ctx, &params)) return fail("Unable to build photon maps");
-      ps.build_ms = seconds_since(tb) * 1000.0;
-      gi_photon_count(ctx, 0, &ps.global_stored); gi_photon_count(ctx, 1, &ps.caustic_stored);
-      if (!ps.global_stored) { params.indirect_illum = 0; params.direct_photon_illum = 0; }
-      if (!ps.caustic_stored) params.caustic_illum = 0;
-    } else {
-      if (params.verbose) {
-        if (params.indirect_illum || params.direct_photon_illum) printf("Building global photon map ...\n");
-        if (params.caustic_illum) printf("Building caustic photon map ...\n");
-      }
-      if (gi_trace_photons(ctx, &params, &ps)) return fail("Unable to trace photons");
-      if (scene.n_lights > 0 && ps.total_power > 0) {
-        params.indirect_illum = ps.indirect_illum; params.caustic_illum = ps.caustic_illum;
-        params.direct_photon_illum = ps.direct_photon_illum;
-      }
+        if (r == 0 && save[m] && gi_dump_photons_file(ctx, m, save[m])) return fail("Unable to save photon map");
     }
-    if (params.verbose) {
-      const bool cache = params.irradiance_cache && (params.indirect_illum || params.direct_photon_illum);
-      printf("Building kdtrees ...\n");
-      if (cache) printf("Building irradiance cache ...\n");
-      printf("Built photon map ...\n");
-      printf("  Total Time = %.2f seconds\n", seconds_since(t0));
-      printf("  Photon Tracing = %.2f seconds\n", ps.trace_ms / 1000.0);
-      printf("  KdTree Construction = %.2f seconds\n", ps.build_ms / 1000.0);
-      if (cache) printf("  Irradiance Cache Computation = %.2f seconds\n", ps.cache_ms / 1000.0);
-      unsigned long long total = 0;
-      if (params.indirect_illum || params.direct_photon_illum) { printf("  # Global Photons Stored = %llu\n", (unsigned long long)ps.global_stored); total += ps.global_stored; }
-      if (params.caustic_illum) { printf("  # Caustic Photons Stored = %llu\n", (unsigned long long)ps.caustic_stored); total += ps.caustic_stored; }
-      printf("Total Photons Stored: %llu\n", total);
+
+    // RenderImage (render.cpp:155-259)
+    if (talk) printf("Rendering image ...\n");
+    GiRenderStats rs; memset(&rs, 0, sizeof(rs));
+    if (gi_render(ctx, &prm, opt.width, opt.height, opt.aa, r == 0 ? rgb.data() : nullptr, &rs)) return fail("Unable to render");
+    if (talk) {
+      unsigned long long total = rs.screen_rays;
+      printf("Rendered image ...\n");
+      printf("  Time = %.2f seconds\n", rs.render_ms / 1000.0);
+      printf("  # Screen Rays = %llu\n", (unsigned long long)rs.screen_rays);
+      if (prm.shadows) { printf("  # Shadow Rays = %llu\n", (unsigned long long)rs.shadow_rays); total += rs.shadow_rays; }
+      if (prm.monte_carlo) { printf("  # Monte Carlo Rays = %llu\n", (unsigned long long)rs.monte_rays); total += rs.monte_rays; }
+      if (prm.transmissive_illum) { printf("  # Transmissive Samples = %llu\n", (unsigned long long)rs.transmissive_samples); total += rs.transmissive_samples; }
+      if (prm.specular_illum) { printf("  # Specular Samples = %llu\n", (unsigned long long)rs.specular_samples); total += rs.specular_samples; }
+      if (prm.indirect_illum) { printf("  # Indirect Samples = %llu\n", (unsigned long long)rs.indirect_samples); total += rs.indirect_samples; }
+      if (prm.caustic_illum) { printf("  # Caustic Samples = %llu\n", (unsigned long long)rs.caustic_samples); total += rs.caustic_samples; }
+      printf("Total Rays: %llu\n", total);
       fflush(stdout);
     }
-    for (int m = 0; m < 2; m++)
-      if (save[m] && gi_dump_photons_file(ctx, m, save[m])) return fail("Unable to save photon map");
-  }
 
-  // RenderImage (render.cpp:155-259)
-  if (params.verbose) printf("Rendering image ...\n");
-  std::vector<uint8_t> rgb((size_t)opt.width * opt.height * 3);
-  GiRenderStats rs; memset(&rs, 0, sizeof(rs));
-  if (gi_render(ctx, &params, opt.width, opt.height, opt.aa, rgb.data(), &rs)) return fail("Unable to render");
-  if (params.verbose) {
-    unsigned long long total = rs.screen_rays;
-    printf("Rendered image ...\n");
-    printf("  Time = %.2f seconds\n", rs.render_ms / 1000.0);
-    printf("  # Screen Rays = %llu\n", (unsigned long long)rs.screen_rays);
-    if (params.shadows) { printf("  # Shadow Rays = %llu\n", (unsigned long long)rs.shadow_rays); total += rs.shadow_rays; }
-    if (params.monte_carlo) { printf("  # Monte Carlo Rays = %llu\n", (unsigned long long)rs.monte_rays); total += rs.monte_rays; }
-    if (params.transmissive_illum) { printf("  # Transmissive Samples = %llu\n", (unsigned long long)rs.transmissive_samples); total += rs.transmissive_samples; }
-    if (params.specular_illum) { printf("  # Specular Samples = %llu\n", (unsigned long long)rs.specular_samples); total += rs.specular_samples; }
-    if (params.indirect_illum) { printf("  # Indirect Samples = %llu\n", (unsigned long long)rs.indirect_samples); total += rs.indirect_samples; }
-    if (params.caustic_illum) { printf("  # Caustic Samples = %llu\n", (unsigned long long)rs.caustic_samples); total += rs.caustic_samples; }
-    printf("Total Rays: %llu\n", total);
-    fflush(stdout);
+    return 0;
+  };
+  if (ngpu == 1) { if (run_rank(0)) return -1; }
+  else {
+    // NCCL collectives inside gi_trace_photons / gi_render need all ranks in flight: one host thread per GPU
+    std::vector<std::thread> th;
+    for (int r = 0; r < ngpu; r++)
+      th.emplace_back([&, r] { status[r] = run_rank(r); if (status[r]) { fflush(stdout); fflush(stderr); _exit(255); } });   // a dead rank would hang the others
+    for (auto &t : th) t.join();
   }
 
   // WriteImage (io_utils.cpp:271-291)
@@ -129,7 +154,7 @@ int main(int argc, char **argv) {
     printf("  Height = %d\n", opt.height);
     fflush(stdout);
   }
-  gi_destroy(ctx);
+  for (GiContext *c : ctxs) gi_destroy(c);
   gi_host_scene_free(host);
   return 0;
 }

@@ -26,7 +26,7 @@
 extern "C" {
 #endif
 
-#define GI_ABI_VERSION 3
+#define GI_ABI_VERSION 4
 
 /* ------------------------------------------------------------------------------------------------
  * Scene description (flattened R3Scene; src/R3Graphics/R3Scene.h).  Order is the order in which
@@ -180,7 +180,7 @@ typedef struct GiParams {
   int32_t caustic_filter;
   double filter_const_a, filter_const_b, filter_const_k;
   uint64_t seed;                     /* new: counter-based RNG seed (reference is unseeded) */
-  int32_t rank, world_size;          /* new: photon / tile sharding across GPUs */
+  int32_t rank, world_size;          /* new: gi_render* without a communicator renders only the pixel columns x = rank (mod world_size) */
 } GiParams;
 
 typedef struct GiPhotonStats {       /* side effects of MapPhotons (photonmap.cpp:339-361) */
@@ -212,10 +212,11 @@ void gi_default_params(GiParams *p);                              /* photonmap.c
 typedef struct GiCliOptions {
   const char *input_scene_name, *output_image_name;   /* point into argv */
   int32_t width, height, aa, real_material;
-  int32_t device;                                     /* new: CUDA device index (-device N) */
+  int32_t device;                                     /* new: CUDA device index (-device N); with -gpus: the first of N */
+  int32_t gpus;                                       /* new: -gpus N, devices device .. device + N - 1 share the frame (default 1) */
 } GiCliOptions;
 void gi_default_cli_options(GiCliOptions *o);
-/* ParseArgs (src/utils/io_utils.cpp:16-214); argv[0] is the program name.  New flags: -seed N, -device N. */
+/* ParseArgs (src/utils/io_utils.cpp:16-214); argv[0] is the program name.  New flags: -seed N, -device N, -gpus N. */
 int gi_parse_args(int argc, const char *const *argv, GiParams *params, GiCliOptions *options);
 
 int gi_launch_count(GiContext *ctx, uint64_t *out);                /* kernels launched so far by this context */
@@ -278,11 +279,37 @@ int gi_cached_radiance_batch_device(GiContext *ctx, const GiGatherQuery *d_queri
 
 /* MapPhotons() (photonmap.cpp:260-436): emission + tracing + power scaling; maps stay on the device */
 int gi_trace_photons(GiContext *ctx, const GiParams *params, GiPhotonStats *stats);
-/* With params->world_size > 1 gi_trace_photons traces this rank's share (COUNT / world_size photons, like one
- * reference thread, photonmap.cpp:289-321) and stops before the power scale: the host all-gathers the photons,
- * loads them (gi_load_photons_device), applies total_power / (emitted summed over ranks) with this call
- * (the decode - multiply - encode loop of photonmap.cpp:339-361), then calls gi_build_maps. */
+/* The power scale of MapPhotons on a loaded, not yet built map (the decode - multiply - encode loop of
+ * photonmap.cpp:339-361); gi_trace_photons applies it itself. */
 int gi_scale_photon_power(GiContext *ctx, int map, double factor);
+
+/* ------------------------------------------------------------------------------------------------
+ * Multi-GPU (one 8 x B200 box): one GiContext per GPU, tied together by an NCCL communicator over NVLink / NVSwitch.
+ * A rank takes the place of one worker thread of the reference: MapPhotons splits the photon budget over its threads
+ * (photonmap.cpp:294-329) and RenderImage strides the pixel columns over them (render.cpp:80-90,188-198).  Scene and
+ * photon maps are replicated (1e8 photons = 3.2 GB); nothing is exchanged while rendering.
+ *   one process, N devices:  gi_create x N, gi_upload_scene x N, gi_comm_init_all(ctxs, N), then one host thread per
+ *                            context calls gi_trace_photons / gi_render (`photonmap -gpus N` does exactly this);
+ *   one process per GPU:     rank 0 calls gi_comm_unique_id, the host hands the 128 bytes to every rank (MPI,
+ *                            torch.distributed, a file ...), every rank calls gi_comm_init_rank.
+ * With a communicator attached:
+ *   gi_trace_photons  traces this rank's share of every emission round: photon t of a round belongs to rank
+ *                     t mod world, random streams are keyed by the GLOBAL photon number and the stored counts are
+ *                     all-reduced after every round, so the adaptive schedule (photonmap.cpp:163-192) and the final map
+ *                     are byte-identical for ANY number of ranks; one ragged all-gather replicates the photons, every
+ *                     rank applies the power scale and builds its kd-trees.  GiPhotonStats holds global totals.
+ *   gi_render         renders the pixel columns x = rank (mod world) and gathers the 8-bit column strips to rank 0:
+ *                     rgb_out is written on rank 0 only (may be NULL elsewhere); GiRenderStats counters are summed
+ *                     over the ranks.  gi_render_float returns this rank's columns (zeros elsewhere), no exchange.
+ * Every rank must make the same calls with the same parameters.  params->rank / world_size are ignored when a
+ * communicator is attached.  NCCL is bound at run time (dlopen libnccl.so.2); without it only these calls fail.
+ * ---------------------------------------------------------------------------------------------- */
+typedef struct GiUniqueId { char bytes[128]; } GiUniqueId;        /* an ncclUniqueId */
+int gi_comm_unique_id(GiUniqueId *out);
+int gi_comm_init_rank(GiContext *ctx, const GiUniqueId *id, int rank, int world);
+int gi_comm_init_all(GiContext **ctxs, int n);                    /* rank i = ctxs[i]; contexts on distinct devices */
+int gi_comm_info(GiContext *ctx, int *rank, int *world);          /* 0 / 1 without a communicator */
+int gi_comm_destroy(GiContext *ctx);                              /* also done by gi_destroy */
 
 /* RenderImage(aa, W, H) (render.cpp:155-259).  rgb_out: W*H*3 bytes, row 0 = bottom row like R2Image. */
 int gi_render(GiContext *ctx, const GiParams *params, int width, int height, int aa, uint8_t *rgb_out,

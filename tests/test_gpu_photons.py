@@ -115,31 +115,26 @@ def test_no_lights_and_disabled_maps(gpu_ctx):
         assert st.caustic_illum == 0
 
 
-def test_rank_shares_and_power_scale(gpu_ctx):
-    """world_size = 2: each rank traces half the budget on its own streams and leaves the power scale to the host."""
-    scene = "glass_cube"
-    hs = gi_b200.HostScene(os.path.join(GOLDEN, scene + ".gisc"))
+def test_sharding_needs_a_communicator_and_power_scale_entry(gpu_ctx):
+    """The photon pass shards over the ranks of an NCCL communicator (gi_comm_init_*; tests/test_gpu_multi.py); asking for
+    world_size > 1 without one is an error, not a silent single-rank trace.  gi_scale_photon_power is the decode -
+    multiply - encode loop of photonmap.cpp:339-361 on a loaded map."""
+    hs = gi_b200.HostScene(os.path.join(GOLDEN, "glass_cube.gisc"))
     gpu_ctx.upload_scene(hs)
-    parts, emitted, total_power = [], 0, 0.0
-    for r in range(2):
-        params, _ = gi_b200.parse_flags(["-global", "20001", "-no_caustic", "-seed", "5"])
-        params.rank, params.world_size = r, 2
-        st = gpu_ctx.trace_photons(params)
-        want = 20001 - 10000 if r == 0 else 10000
-        assert want <= st.global_stored <= want * 1.05 + 300
-        parts.append(gpu_ctx.get_photons(0).copy()); emitted += st.global_emitted; total_power = st.total_power
-    assert parts[0][:100].tobytes() != parts[1][:100].tobytes()
-    allp = np.concatenate(parts)
-    gpu_ctx.load_photons(0, allp)
-    gpu_ctx.scale_photon_power(0, total_power / emitted)
-    gpu_ctx.build_maps()
-    # same total power as a single-rank trace of the whole budget
-    params, _ = gi_b200.parse_flags(["-global", "20001", "-no_caustic", "-seed", "5"])
-    from make_photon_golden import decode_rgbe
-    two = decode_rgbe(gpu_ctx.get_photons(0)["rgbe"]).sum(0)
+    params, _ = gi_b200.parse_flags(["-global", "2000", "-no_caustic", "-seed", "5"])
+    params.rank, params.world_size = 0, 2
+    with pytest.raises(gi_b200.GiError, match="communicator"):
+        gpu_ctx.trace_photons(params)
+    assert gpu_ctx.comm_info() == (0, 1)
+    params.rank, params.world_size = 0, 1
     gpu_ctx.trace_photons(params)
-    one = decode_rgbe(gpu_ctx.get_photons(0)["rgbe"]).sum(0)
-    assert np.all(np.abs(two - one) < 0.06 * one)
+    from make_photon_golden import decode_rgbe
+    ph = gpu_ctx.get_photons(0)
+    before = decode_rgbe(ph["rgbe"]).sum(0)
+    gpu_ctx.load_photons(0, ph)
+    gpu_ctx.scale_photon_power(0, 0.25)
+    after = decode_rgbe(gpu_ctx.get_photons(0)["rgbe"]).sum(0)
+    assert np.all(np.abs(after - 0.25 * before) <= 0.01 * 0.25 * before)      # RGBE re-quantisation: 8-bit mantissas
 
 
 def test_specular_prefilter_changes_nothing_but_time(gpu_ctx):

@@ -1,6 +1,7 @@
-"""world_size-2 gloo tests (CPU) of the multi-GPU host logic in global-illumination_b200/multi_gpu.py: the ragged
-photon all-gather, the emitted-count reduction and power scale, and the frame assembly -- with a stand-in context
-that records what the C ABI would be asked to do (no kernels run here; the GPU path is tests/test_gpu_multi.py)."""
+"""world_size-2 gloo tests (CPU) of the multi-GPU host side (global-illumination_b200/multi_gpu.py): the communicator
+bootstrap over torch.distributed, and the two partitions the C side applies -- photons t = rank (mod world) of every
+emission round, pixel columns x = rank (mod world) -- replayed with a stand-in context whose "collectives" are gloo
+calls.  No kernels run here; the GPU path is tests/test_gpu_multi.py (NCCL)."""
 import os
 import sys
 
@@ -10,123 +11,141 @@ import pytest
 ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
 
 
-class FakeStats:
-    def __init__(self, rank):
-        self.global_emitted = 1000 + 10 * rank; self.caustic_emitted = 0 if rank else 0
-        self.total_power = 12.5; self.trace_ms = 1.0
-        self.global_stored = 0; self.caustic_stored = 0
-
-
 class FakeContext:
-    """photons live in numpy arrays; `ptr` arguments are torch tensors' data_ptr() of CPU tensors"""
-    def __init__(self, rank, torch):
-        self.rank, self.torch = rank, torch
-        self.maps = {0: None, 1: None}; self.scaled = {}; self.built = False; self.render_calls = []
-        self._tensors = {}
+    """records what the C ABI would be asked to do; gi_trace_photons / gi_render replayed on the CPU with gloo standing in
+    for the NCCL calls of csrc/comm.cu (same partitions, same assembly)"""
+    def __init__(self, dist, torch):
+        self.dist, self.torch = dist, torch
+        self.comm = None; self.map = None
+
+    def comm_init_rank(self, unique_id, rank, world):
+        assert len(unique_id) == 128
+        self.comm = (bytes(unique_id), rank, world)
+
+    def comm_info(self):
+        return self.comm[1], self.comm[2]
 
     def trace_photons(self, params):
-        assert (params.rank, params.world_size) == (self.rank, 2)
-        rng = np.random.default_rng(self.rank)
-        self.maps[0] = rng.integers(0, 255, size=(5 + 3 * self.rank, 32), dtype=np.uint8)      # ragged: 5 and 8 photons
-        self.maps[1] = np.zeros((0, 32), dtype=np.uint8)                                       # no caustic photon anywhere
-        return FakeStats(self.rank)
-
-    def photon_count(self, which):
-        return len(self.maps[which])
-
-    def get_photons_device(self, which, ptr, capacity, stream=None):
-        import ctypes
-        ctypes.memmove(ptr, self.maps[which].ctypes.data, self.maps[which].nbytes)
-
-    def load_photons_device(self, which, ptr, n):
-        import ctypes
-        buf = np.zeros((n, 32), dtype=np.uint8)
-        if n:
-            ctypes.memmove(buf.ctypes.data, ptr, buf.nbytes)
-        self.maps[which] = buf
-
-    def scale_photon_power(self, which, factor):
-        self.scaled[which] = factor
-
-    def build_maps(self, params=None):
-        self.built = True
-
-    def render(self, params, width, height, aa):
+        """rounds of n photons; photon t 'stores' iff hash(t) is small; per-round all-reduce of the counts; final gather +
+        sort by photon number -- trace_map of csrc/photon_trace.cu in miniature"""
         import multi_gpu
+        torch, dist = self.torch, self.dist
+        _, rank, world = self.comm
+        target, stored, emitted, mine = 40, 0, 0, []
+        rate = 4.0
+        rounds = 0
+        while stored < target:
+            n = int((target - stored) / rate + 1) * 8
+            ids = [emitted + t for t in multi_gpu.round_share(n, rank, world)]
+            mine += [i for i in ids if (i * 2654435761) % 7 == 0]
+            c = torch.tensor([len(mine)], dtype=torch.int64); dist.all_reduce(c)
+            stored = int(c.item()); emitted += n; rounds += 1
+            rate = max(stored / emitted, 1e-3)
+        counts = [torch.zeros(1, dtype=torch.int64) for _ in range(world)]
+        dist.all_gather(counts, torch.tensor([len(mine)], dtype=torch.int64))
+        counts = [int(x.item()) for x in counts]
+        pad = torch.zeros(max(counts), dtype=torch.int64); pad[:len(mine)] = torch.tensor(mine, dtype=torch.int64)
+        out = [torch.zeros(max(counts), dtype=torch.int64) for _ in range(world)]
+        dist.all_gather(out, pad)
+        self.map = np.sort(np.concatenate([o.numpy()[:c] for o, c in zip(out, counts)]))
+
+        class St:
+            pass
+        st = St(); st.total_power = 12.5; st.indirect_illum, st.caustic_illum, st.direct_photon_illum = 1, 0, 0
+        st.global_stored, st.global_emitted, st.rounds = stored, emitted, rounds
+        return st
+
+    def render(self, params, width, height, aa, want_image=True):
+        import multi_gpu
+        torch, dist = self.torch, self.dist
+        _, rank, world = self.comm
+        cols = list(multi_gpu.columns_of(width, rank, world))
+        strip = np.zeros((height, len(cols), 3), dtype=np.uint8)
+        for l, x in enumerate(cols):
+            strip[:, l] = (x * 7 + np.arange(height)[:, None] * 3 + np.arange(3)) % 251
+        ncols = [len(list(multi_gpu.columns_of(width, r, world))) for r in range(world)]
+        out = [torch.zeros(height * max(ncols) * 3, dtype=torch.uint8) for _ in range(world)]
+        pad = torch.zeros(height * max(ncols) * 3, dtype=torch.uint8); pad[:strip.size] = torch.from_numpy(strip.reshape(-1))
+        dist.all_gather(out, pad)
+        if not want_image:
+            return None, None
         img = np.zeros((height, width, 3), dtype=np.uint8)
-        img[:, list(multi_gpu.columns_of(width, params.rank, params.world_size))] = 50 + 100 * params.rank
-        self.render_calls.append((params.rank, params.world_size))
+        for r in range(world):
+            s = out[r].numpy()[: height * ncols[r] * 3].reshape(height, ncols[r], 3)
+            img[:, list(multi_gpu.columns_of(width, r, world))] = s
         return img, None
 
 
-def _worker(rank, port, out):
+def _worker(rank, world, port, out):
     sys.path.insert(0, os.path.join(ROOT, "global-illumination_b200"))
     import torch
     import torch.distributed as dist
     import gi_b200
     import multi_gpu
-    os.environ.update(MASTER_ADDR="127.0.0.1", MASTER_PORT=str(port), RANK=str(rank), WORLD_SIZE="2")
-    dist.init_process_group("gloo", rank=rank, world_size=2)
+    os.environ.update(MASTER_ADDR="127.0.0.1", MASTER_PORT=str(port), RANK=str(rank), WORLD_SIZE=str(world))
+    dist.init_process_group("gloo", rank=rank, world_size=world)
     dev = torch.device("cpu")
     res = {}
-    # ragged gather
-    local = torch.arange((3 + 2 * rank) * 4, dtype=torch.int64).reshape(-1, 4) + 1000 * rank
-    full, counts = multi_gpu.gather_ragged(dist, torch, local)
-    res["counts"] = counts; res["full"] = full.numpy().copy()
-    empty, c2 = multi_gpu.gather_ragged(dist, torch, torch.zeros((0, 4), dtype=torch.int64))
-    res["empty"] = (tuple(empty.shape), c2)
-    # photon pass
-    ctx = FakeContext(rank, torch)
+    ctx = FakeContext(dist, torch)
+    # bootstrap: rank 0's id reaches everyone (the real gi_comm_unique_id needs NCCL; any 128 bytes do here)
+    orig = gi_b200.comm_unique_id
+    gi_b200.comm_unique_id = lambda: bytes((7 * i + 3) % 256 for i in range(128))
+    try:
+        res["rank_world"] = multi_gpu.attach_communicator(ctx, dist, torch, dev)
+    finally:
+        gi_b200.comm_unique_id = orig
+    res["comm"] = ctx.comm
     params = gi_b200.GiParams(); params.indirect_illum = 1; params.caustic_illum = 1
-    totals = multi_gpu.trace_photons_sharded(ctx, params, dist, torch, dev)
-    res["totals"] = totals; res["global_map"] = ctx.maps[0].copy(); res["scaled"] = dict(ctx.scaled); res["built"] = ctx.built
-    res["flags"] = (params.indirect_illum, params.caustic_illum, params.rank, params.world_size)
-    # frame assembly
-    img, _ = multi_gpu.render_sharded(ctx, params, 7, 3, 1, dist, torch, dev)
+    st = multi_gpu.trace_photons_sharded(ctx, params)
+    res["map"] = ctx.map; res["flags"] = (params.indirect_illum, params.caustic_illum); res["emitted"] = st.global_emitted
+    res["rounds"] = st.rounds
+    img, _ = multi_gpu.render_sharded(ctx, params, 7, 3, 1)
     res["img"] = img
     out.put((rank, res))
     dist.destroy_process_group()
 
 
-def test_world_size_2_host_logic():
+def _run(world):
     import torch.multiprocessing as mp
     ctxm = mp.get_context("spawn")
     q = ctxm.Queue()
-    port = 29500 + os.getpid() % 2000
-    procs = [ctxm.Process(target=_worker, args=(r, port, q)) for r in range(2)]
+    port = 29500 + (os.getpid() * 7 + world) % 2000
+    procs = [ctxm.Process(target=_worker, args=(r, world, port, q)) for r in range(world)]
     for p in procs:
         p.start()
-    got = dict(q.get(timeout=120) for _ in range(2))
+    got = dict(q.get(timeout=120) for _ in range(world))
     for p in procs:
         p.join(timeout=60)
         assert p.exitcode == 0
+    return got
+
+
+def test_world_size_2_host_logic():
+    got = _run(2)
+    want_id = bytes((7 * i + 3) % 256 for i in range(128))
     for r in range(2):
-        res = got[r]
-        assert res["counts"] == [3, 5]
-        want = np.concatenate([np.arange(12).reshape(3, 4), np.arange(20).reshape(5, 4) + 1000])
-        assert np.array_equal(res["full"], want)
-        assert res["empty"] == ((0, 4), [0, 0])
-        t = res["totals"]
-        assert t["global_emitted"] == 2010 and t["global_stored"] == 13 and t["global_per_rank"] == [5, 8]
-        assert t["caustic_stored"] == 0
-        assert res["scaled"] == {0: pytest.approx(12.5 / 2010)}          # total_power / emitted summed over ranks
-        assert res["built"] and res["flags"] == (1, 0, 0, 1)             # empty caustic map switches caustics off
-    # both ranks hold the same replicated map: rank 0's photons then rank 1's
-    assert np.array_equal(got[0]["global_map"], got[1]["global_map"])
-    rng0, rng1 = np.random.default_rng(0), np.random.default_rng(1)
-    assert np.array_equal(got[0]["global_map"][:5], rng0.integers(0, 255, size=(5, 32), dtype=np.uint8))
-    assert np.array_equal(got[0]["global_map"][5:], rng1.integers(0, 255, size=(8, 32), dtype=np.uint8))
+        assert got[r]["rank_world"] == (r, 2)
+        assert got[r]["comm"] == (want_id, r, 2)
+        assert got[r]["flags"] == (1, 0)                   # an empty caustic map switches caustics off on every rank
+    assert np.array_equal(got[0]["map"], got[1]["map"])    # replicated
     img = got[0]["img"]
     assert got[1]["img"] is None and img.shape == (3, 7, 3)
-    assert np.all(img[:, 0::2] == 50) and np.all(img[:, 1::2] == 150)
+    want = (np.arange(7)[None, :, None] * 7 + np.arange(3)[:, None, None] * 3 + np.arange(3)[None, None, :]) % 251
+    assert np.array_equal(img, want.astype(np.uint8))
+    # the same schedule and the same map for any number of ranks: replay with one rank in this process
+    one = _run(1)
+    assert np.array_equal(one[0]["map"], got[0]["map"]) and one[0]["emitted"] == got[0]["emitted"] and one[0]["rounds"] == got[0]["rounds"]
+    assert np.array_equal(one[0]["img"], img)
 
 
-def test_column_ranges_partition_the_frame():
+def test_partitions_cover_everything_once():
     sys.path.insert(0, os.path.join(ROOT, "global-illumination_b200"))
     import multi_gpu
-    for width in (1, 7, 64, 1023):
+    for n in (0, 1, 7, 64, 1023):
         for world in (1, 2, 3, 8):
-            cols = []
+            cols, ph = [], []
             for r in range(world):
-                cols += list(multi_gpu.columns_of(width, r, world))
-            assert sorted(cols) == list(range(width))
+                cols += list(multi_gpu.columns_of(n, r, world)); ph += list(multi_gpu.round_share(n, r, world))
+                # the counts the C side computes in closed form (render.cu: local columns, photon_trace.cu: n_local)
+                assert len(list(multi_gpu.columns_of(n, r, world))) == (n - r + world - 1) // world if n > r else True
+            assert sorted(cols) == list(range(n)) and sorted(ph) == list(range(n))
