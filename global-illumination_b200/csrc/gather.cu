@@ -20,9 +20,11 @@
 //     uniform in d^2, so the boundary bin holds ~cap/256 candidates): everything up to the bin that contains the
 //     k-th candidate is kept whole, the few candidates inside that bin are ranked by shuffles, and the search bound
 //     shrinks to the exact k-th smallest d^2.
+#include <cub/device/device_radix_sort.cuh>
 #include <cuda_runtime.h>
 #include <math.h>
 #include <stdint.h>
+#include <string>
 #include "context.h"
 #include "gather.h"
 
@@ -559,4 +561,129 @@ cudaError_t launch_gather(GiContext *ctx, const PhotonMapDev &m, const double *d
   return cudaGetLastError();
 }
 
+// ------------------------------------------------------------------------------------------------ no-allocation variant
+// gi_gather_batch_device_noalloc (gi_b200.h): the same kernel, with every piece of scratch memory in one file-scope device
+// array instead of cudaMalloc'd buffers of the context.  Layout (offsets in bytes, Q = GI_NOALLOC_MAX_QUERIES):
+//   [0, 256)            launch-wide chunk counter (u64) -- the only part that must start at zero: cleared per call
+//   [256, 256 + 16 Q)   Morton keys in / out, permutation in / out (4 x u32[Q]) -- fully rewritten by every call
+//   [.., + 1 MiB)       temporary storage of the radix sort (size checked against what the sort asks for)
+// In HOST code `g_noalloc_scratch` is a host-side stand-in, not a device address: the address the kernels get comes from
+// cudaGetSymbolAddress, taken once per context with the context's device current (noalloc_base).
+#define GI_NOALLOC_SORT_TEMP (1u << 20)
+#define GI_NOALLOC_BYTES (256u + 16u * GI_NOALLOC_MAX_QUERIES + GI_NOALLOC_SORT_TEMP)
+static __device__ __align__(256) unsigned char g_noalloc_scratch[GI_NOALLOC_BYTES];
+
+static unsigned char *noalloc_base(GiContext *ctx) {
+  if (ctx->noalloc_scratch) return ctx->noalloc_scratch;
+  unsigned char *p = nullptr;
+  if (!cuda_ok(cudaGetSymbolAddress((void **)&p, g_noalloc_scratch), "cudaGetSymbolAddress(gather scratch)") || !p) return nullptr;
+  ctx->noalloc_scratch = p;
+  return p;
+}
+
+// 30-bit Morton key of a query position inside the map's bounding box (same keys as query_order.cu)
+__device__ __forceinline__ uint32_t na_spread10(uint32_t v) {
+  v &= 1023u; v = (v | (v << 16)) & 0x030000FFu; v = (v | (v << 8)) & 0x0300F00Fu; v = (v | (v << 4)) & 0x030C30C3u;
+  return (v | (v << 2)) & 0x09249249u;
+}
+__global__ void __launch_bounds__(256) noalloc_keys_kernel(const GiGatherQuery *__restrict__ q, uint32_t n, double lx, double ly, double lz,
+                                                           double ix, double iy, double iz, uint32_t *__restrict__ keys,
+                                                           uint32_t *__restrict__ order) {
+  const uint32_t t = blockIdx.x * blockDim.x + threadIdx.x;
+  if (t >= n) return;
+  const double x = (q[t].p[0] - lx) * ix, y = (q[t].p[1] - ly) * iy, z = (q[t].p[2] - lz) * iz;
+  const uint32_t xi = (uint32_t)fmin(fmax(x * 1024.0, 0.0), 1023.0), yi = (uint32_t)fmin(fmax(y * 1024.0, 0.0), 1023.0),
+                 zi = (uint32_t)fmin(fmax(z * 1024.0, 0.0), 1023.0);
+  keys[t] = na_spread10(xi) | (na_spread10(yi) << 1) | (na_spread10(zi) << 2);
+  order[t] = t;
+}
+
+// launch_gather with the chunk counter supplied by the caller (no work_counter(): that one allocates on first use)
+static cudaError_t launch_gather_counter(GiContext *ctx, const PhotonMapDev &m, const double *d_lut, const GiGatherQuery *d_q,
+                                         const uint32_t *d_order, uint64_t nq, const GatherArgs &ga_in, unsigned long long *counter,
+                                         int32_t *d_idx, int32_t *d_count, double *d_rgb, cudaStream_t st) {
+  GatherArgs ga = ga_in;
+  ga.key_rows = m.groups > 2 ? m.groups - 2 : 0;
+  const size_t per_warp = GI_WARP_BYTES(ga.cap, ga.key_rows);
+  int warps = (int)((227 * 1024) / per_warp);
+  if (warps > GI_GATHER_MAX_WARPS) warps = GI_GATHER_MAX_WARPS;
+  if (warps < 1) return cudaErrorInvalidValue;
+  const uint64_t nchunks = (nq + GI_GATHER_CHUNK - 1) / GI_GATHER_CHUNK;
+  if ((uint64_t)warps > nchunks) warps = (int)nchunks;
+  const size_t smem = (size_t)warps * per_warp;
+  const bool deep = m.hb > GI_GROUP_LEVELS;
+  if (smem > ctx->gather_smem_configured[deep]) {
+    cudaError_t e = deep ? cudaFuncSetAttribute(gather_kernel<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem)
+                         : cudaFuncSetAttribute(gather_kernel<false>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
+    if (e != cudaSuccess) return e;
+    ctx->gather_smem_configured[deep] = smem;
+  }
+  uint64_t r = nchunks / ((uint64_t)ctx->sm_count * 8);
+  r = r / warps * warps;
+  if (r < (uint64_t)warps) r = warps;
+  if (r > (uint64_t)4 * warps) r = (uint64_t)4 * warps;
+  ga.range = (int)r;
+  { cudaError_t e = cudaMemsetAsync(counter, 0, sizeof(unsigned long long), st); if (e != cudaSuccess) return e; }
+  const uint64_t want = (nchunks + warps - 1) / warps;
+  const unsigned grid = (unsigned)(want < (uint64_t)ctx->sm_count ? want : (uint64_t)ctx->sm_count);
+  if (deep) gather_kernel<true><<<grid, warps * 32, smem, st>>>(m, d_lut, d_q, d_order, nq, ga, counter, d_idx, d_count, d_rgb);
+  else gather_kernel<false><<<grid, warps * 32, smem, st>>>(m, d_lut, d_q, d_order, nq, ga, counter, d_idx, d_count, d_rgb);
+  ctx->launches++;
+  return cudaGetLastError();
+}
+
 }  // namespace gi
+
+using namespace gi;
+
+extern "C" int gi_gather_batch_device_noalloc(GiContext *ctx, int map, const GiGatherQuery *d_queries, uint64_t n, int k, double r,
+                                              int filter, const GiParams *params, int32_t *d_idx, int32_t *d_count, double *d_rgb,
+                                              void *stream) {
+  if (!ctx || map < 0 || map > 1) { set_error("gi_gather_batch_device_noalloc: bad argument"); return 1; }
+  if (k < 1 || k > GI_MAX_K) { set_error("gi_gather_batch_device_noalloc: estimate size must be in [1, 512]"); return 1; }
+  if (filter < 0 || filter > 2) { set_error("gi_gather_batch_device_noalloc: unknown filter"); return 1; }
+  if (n > (uint64_t)GI_NOALLOC_MAX_QUERIES) {
+    set_error("gi_gather_batch_device_noalloc: " + std::to_string(n) + " queries exceed the static scratch of GI_NOALLOC_MAX_QUERIES = " +
+              std::to_string(GI_NOALLOC_MAX_QUERIES) + " (split the batch, or use gi_gather_batch_device)");
+    return 1;
+  }
+  PhotonMapStore &m = ctx->maps[map];
+  if (m.dev.n > 0 && !m.built) { set_error("gi_gather_batch_device_noalloc: photon map not built (call gi_build_maps)"); return 1; }
+  if (n == 0) return 0;
+  if (!d_queries) { set_error("gi_gather_batch_device_noalloc: null query buffer"); return 1; }
+  // the direction table is made by gi_build_maps (an allocation this call must not make)
+  if (!ctx->d_lut) { set_error("gi_gather_batch_device_noalloc: no direction table on this context yet (call gi_build_maps once first)"); return 1; }
+  GI_CUDA(cudaSetDevice(ctx->device));
+  unsigned char *base = noalloc_base(ctx);             // device address of g_noalloc_scratch on ctx->device
+  if (!base) return 1;
+  cudaStream_t st = (cudaStream_t)stream;
+  unsigned long long *counter = (unsigned long long *)base;
+  uint32_t *keys = (uint32_t *)(base + 256), *keys2 = keys + GI_NOALLOC_MAX_QUERIES, *ord = keys2 + GI_NOALLOC_MAX_QUERIES,
+           *ord2 = ord + GI_NOALLOC_MAX_QUERIES;
+  void *sort_tmp = base + 256 + 16u * GI_NOALLOC_MAX_QUERIES;
+
+  GatherArgs ga;                                       // as gi_gather_batch_device sets them (capi_photon.cu), without the tuning hooks
+  ga.k = k; ga.filter = filter; ga.r2 = r * r;
+  int p2 = 1; while (p2 < 2 * k) p2 <<= 1;
+  ga.cap = d_idx ? (p2 < 256 ? 256 : p2) : ((k + (k / 2 > 96 ? k / 2 : 96) + 31) / 32) * 32 + 32;
+  ga.fa = params ? params->filter_const_a : 0.918; ga.fb = params ? params->filter_const_b : 1.953;
+  ga.fk = params ? params->filter_const_k : 1.0;
+  ga.guess_factor = 1.1; ga.slack = ga.cap; ga.max_warps = 0; ga.key_rows = 0; ga.range = 0;
+
+  const uint32_t *order = nullptr;
+  if (n >= 4096) {                                     // walk the batch along a Morton curve, like gi_gather_batch_device
+    size_t need = 0;
+    GI_CUDA(cub::DeviceRadixSort::SortPairs(nullptr, need, keys, keys2, ord, ord2, (int)n, 0, 30, st));    // size query only
+    if (need > GI_NOALLOC_SORT_TEMP) { set_error("gi_gather_batch_device_noalloc: the sort needs more temporary storage than the static scratch holds"); return 1; }
+    const double *b = m.bbox;
+    const double ix = 1.0 / fmax(b[3] - b[0], 1e-300), iy = 1.0 / fmax(b[4] - b[1], 1e-300), iz = 1.0 / fmax(b[5] - b[2], 1e-300);
+    noalloc_keys_kernel<<<(unsigned)((n + 255) / 256), 256, 0, st>>>(d_queries, (uint32_t)n, b[0], b[1], b[2], ix, iy, iz, keys, ord);
+    GI_CUDA(cudaGetLastError());
+    size_t bytes = GI_NOALLOC_SORT_TEMP;
+    GI_CUDA(cub::DeviceRadixSort::SortPairs(sort_tmp, bytes, keys, keys2, ord, ord2, (int)n, 0, 30, st));   // caller-provided storage: no allocation
+    ctx->launches += 2;
+    order = ord2;
+  }
+  GI_CUDA(launch_gather_counter(ctx, m.dev, ctx->d_lut, d_queries, order, n, ga, counter, d_idx, d_count, d_rgb, st));
+  return 0;
+}

@@ -13,6 +13,7 @@ LIB_PATH = os.path.join(_HERE, "libgi_b200.so")
 
 GI_MAP_GLOBAL, GI_MAP_CAUSTIC = 0, 1
 GI_FILTER_DISK, GI_FILTER_CONE, GI_FILTER_GAUSS = 0, 1, 2
+NOALLOC_MAX_QUERIES = 262144      # GI_NOALLOC_MAX_QUERIES of include/gi_b200.h
 
 RAY = np.dtype([("o", "<f8", 3), ("d", "<f8", 3)])
 HIT = np.dtype([("hit", "<i4"), ("shape", "<i4"), ("prim", "<i4"), ("element", "<i4"), ("t", "<f8"),
@@ -86,6 +87,7 @@ EXPORTS = ["gi_abi_version", "gi_last_error", "gi_create", "gi_destroy", "gi_def
            "gi_upload_scene", "gi_intersect_batch", "gi_intersect_batch_device",
            "gi_load_photons", "gi_load_photons_device", "gi_load_photons_file", "gi_dump_photons_file",
            "gi_photon_count", "gi_get_photons", "gi_get_photons_device", "gi_build_maps", "gi_gather_batch", "gi_gather_batch_device",
+           "gi_gather_batch_device_noalloc",
            "gi_trace_photons", "gi_scale_photon_power", "gi_render", "gi_render_float",
            "gi_default_cli_options", "gi_parse_args", "gi_write_image",
            "gi_comm_unique_id", "gi_comm_init_rank", "gi_comm_init_all", "gi_comm_info", "gi_comm_destroy"]
@@ -125,6 +127,7 @@ def lib():
         L.gi_build_maps.argtypes = [vp, ctypes.POINTER(GiParams)]
         L.gi_gather_batch.argtypes = [vp, i32, vp, u64, i32, dbl, i32, ctypes.POINTER(GiParams), vp, vp, vp]
         L.gi_gather_batch_device.argtypes = [vp, i32, vp, u64, i32, dbl, i32, ctypes.POINTER(GiParams), vp, vp, vp, vp]
+        L.gi_gather_batch_device_noalloc.argtypes = [vp, i32, vp, u64, i32, dbl, i32, ctypes.POINTER(GiParams), vp, vp, vp, vp]
         L.gi_cached_radiance_batch.argtypes = [vp, vp, u64, dbl, vp]
         L.gi_cached_radiance_batch_device.argtypes = [vp, vp, u64, dbl, vp, vp]
         L.gi_trace_photons.argtypes = [vp, ctypes.POINTER(GiParams), ctypes.POINTER(GiPhotonStats)]
@@ -288,6 +291,11 @@ class Context:
     def gather_device(self, which, d_queries, n, k, r, filter, params, d_idx, d_count, d_rgb, stream=None):
         _check(lib().gi_gather_batch_device(self.handle, which, d_queries, n, k, float(r), filter, ctypes.byref(params),
                                             d_idx, d_count, d_rgb, stream))
+
+    def gather_device_noalloc(self, which, d_queries, n, k, r, filter, params, d_idx, d_count, d_rgb, stream=None):
+        """gi_gather_batch_device with all scratch in the library's static device array: allocates nothing, n <= NOALLOC_MAX_QUERIES"""
+        _check(lib().gi_gather_batch_device_noalloc(self.handle, which, d_queries, n, k, float(r), filter, ctypes.byref(params),
+                                                    d_idx, d_count, d_rgb, stream))
 
     def cached_radiance(self, queries, r):
         """EstimateCachedRadiance per query on the global map (built with params.irradiance_cache): rgb[n, 3]."""

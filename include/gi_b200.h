@@ -26,7 +26,7 @@
 extern "C" {
 #endif
 
-#define GI_ABI_VERSION 4
+#define GI_ABI_VERSION 5
 
 /* ------------------------------------------------------------------------------------------------
  * Scene description (flattened R3Scene; src/R3Graphics/R3Scene.h).  Order is the order in which
@@ -265,6 +265,23 @@ int gi_gather_batch_device(GiContext *ctx, int map, const GiGatherQuery *d_queri
  * Morton curve (results stay at the caller's index); the ordering scratch, the chunk counter and the radius hint live
  * in the context, so calls on ONE context must not run concurrently on different caller streams (order them with
  * events, or use one context per stream).  n < 2^31 per device batch; the host-buffer call has no such limit. */
+
+/* gi_gather_batch_device WITHOUT any allocation.  This entry point has no counterpart in the reference; it was added
+ * for callers that cannot call cudaMalloc (code under CUDA graph capture, tight
+ * serving loops, harnesses that forbid it).  Same arguments, same results as gi_gather_batch_device (identical kNN sets
+ * and counts; radiance equal up to the summation order, <= 1e-9 relative), but everything the gather needs besides the
+ * caller's buffers -- the launch-wide chunk counter, the Morton keys / permutation of the batch and the sort's temporary
+ * storage -- lives in ONE file-scope `static __device__` array of csrc/gather.cu (256 B + 16 B x GI_NOALLOC_MAX_QUERIES
+ * + 1 MiB = 5.25 MB, held by every GPU that loads the library until the process exits).  The call makes no cudaMalloc /
+ * cudaFree / allocating library call; it fails with a clear error if n > GI_NOALLOC_MAX_QUERIES, and if the map was not
+ * built (gi_build_maps creates the direction table the estimate reads).
+ * The array is shared by EVERY call on the device, whatever the context or stream, and keeps the last call's contents
+ * (the call clears the counter it needs at zero itself): two calls that overlap on the GPU race -- order them on one
+ * stream or with events.  Enqueues on `stream` and returns without waiting, like gi_gather_batch_device. */
+#define GI_NOALLOC_MAX_QUERIES 262144
+int gi_gather_batch_device_noalloc(GiContext *ctx, int map, const GiGatherQuery *d_queries, uint64_t n, int k, double r,
+                                   int filter, const GiParams *params, int32_t *d_idx, int32_t *d_count, double *d_rgb,
+                                   void *stream);
 
 /* The irradiance cache (-cache).  gi_build_maps with params->irradiance_cache (and indirect_illum or
  * direct_photon_illum) set runs the pre-pass of MapPhotons (photonmap.cpp:380-411) once per loaded global map: every
