@@ -68,8 +68,20 @@ GI_DEV void flush_stats(RayStats *g, const RayStats &s) {
 
 GI_DEV RayStats zero_stats() { RayStats s; s.screen = s.shadow = s.monte = s.transmissive = s.specular = s.indirect = s.caustic = 0; return s; }
 
+// One queue slot per calling lane with ONE atomicAdd per warp: the lanes that are at this call together (and push to
+// the same queue) are found with a match on the counter's address, the lowest of them claims slots for all.
+GI_DEV unsigned long long claim_slot(unsigned long long *count) {
+  const unsigned act = __activemask();
+  const unsigned grp = __match_any_sync(act, (unsigned long long)count);
+  const int lane = threadIdx.x & 31, leader = __ffs(grp) - 1;
+  unsigned long long base = 0;
+  if (lane == leader) base = atomicAdd(count, (unsigned long long)__popc(grp));
+  base = __shfl_sync(grp, base, leader);
+  return base + __popc(grp & ((1u << lane) - 1u));
+}
+
 GI_DEV void push_request(const Queue &qu, D3 p, D3 n, D3 bounce, double cos_theta, const Brdf &b, D3 w, uint32_t pix) {
-  const unsigned long long i = atomicAdd(qu.count, 1ull);
+  const unsigned long long i = claim_slot(qu.count);
   if (i >= qu.cap) return;
   GiGatherQuery q;
   q.p[0] = p.x; q.p[1] = p.y; q.p[2] = p.z; q.n[0] = n.x; q.n[1] = n.y; q.n[2] = n.z;
@@ -204,19 +216,23 @@ struct PathState {
   int mode, iter;
 };
 
-// one iteration of the loop; returns false when the walk ends
-GI_DEV bool path_step(const ShadeEnv &env, PathState &s, const Queue &qglobal, const Queue &qcaustic, RayStats &st) {
+// One iteration of the loop; returns false when the walk ends.  MODE = MODE_PATH / MODE_INDIRECT compiles the body for
+// that mode only (the wavefront kernels below: the indirect variant carries no direct-light code at all); MODE < 0
+// follows s.mode.  The buffered Philox outputs are dropped at the end of every iteration, so that the stream of a path
+// is a function of its counter alone and a path can be parked in a queue between two bounces.
+// `hit_element` < 0: the ray missed; otherwise the element, point and normal of its closest hit.
+template <int MODE>
+GI_DEV bool path_shade(const ShadeEnv &env, PathState &s, int hit_element, D3 point, D3 normal, const Queue &qglobal,
+                       const Queue &qcaustic, RayStats &st) {
   const GiParams &p = env.p;
-  HitRec h;
-  closest_hit(env.sc, s.ray, h);
-  if (h.prim < 0) { s.out = s.out + mul3(s.scale, mul3(s.tw, env.background)); return false; }
+  const int mode = MODE < 0 ? s.mode : MODE;
+  if (hit_element < 0) { s.out = s.out + mul3(s.scale, mul3(s.tw, env.background)); return false; }
   st.monte++;
-  const Brdf b = load_brdf(env.materials[env.sc.elements[h.element].material]);
-  const D3 point = h.p, normal = h.n;
+  const Brdf b = load_brdf(env.materials[env.sc.elements[hit_element].material]);
   const D3 view = normalized(point - s.ray.o);
   const double cos_theta = dot(normal, -view);
   double r_coeff = 0;
-  if (s.mode == MODE_PATH) {
+  if (mode == MODE_PATH) {
     D3 cb = mk3(0, 0, 0);
     if (p.ambient) cb = cb + env.ambient;
     if (b.diffuse || b.specular) direct_illumination(env, point, normal, s.ray.o, cb, b, cos_theta, true, s.rng, nullptr, st);
@@ -240,9 +256,9 @@ GI_DEV bool path_step(const ShadeEnv &env, PathState &s, const Queue &qglobal, c
   D3 bounce;
   if (rnd < prob_diffuse) {
     const D3 w = mul3(b.kd, s.tw) / prob_diffuse;
-    if (s.mode == MODE_INDIRECT || (!p.indirect_illum && p.fast_global)) {
+    if (mode == MODE_INDIRECT || (!p.indirect_illum && p.fast_global)) {
       push_request(qglobal, point, normal, reflective_bounce(normal, view, cos_theta), cos_theta, b, mul3(s.scale, w), s.pix);
-      if (s.mode == MODE_PATH && !p.irradiance_cache) st.indirect++;   // EstimateGlobalIllumination counts (not with -cache), EstimateRadiance does not
+      if (mode == MODE_PATH && !p.irradiance_cache) st.indirect++;   // EstimateGlobalIllumination counts (not with -cache), EstimateRadiance does not
       return false;
     }
     if (!p.indirect_illum) return false;
@@ -251,13 +267,13 @@ GI_DEV bool path_step(const ShadeEnv &env, PathState &s, const Queue &qglobal, c
     st.indirect++;
     s.mode = MODE_INDIRECT; s.tw = mk3(1, 1, 1); s.iter = -1;
   } else if (rnd < prob_diffuse + prob_transmission) {
-    if (s.mode == MODE_PATH && !p.transmissive_illum) return false;
+    if (mode == MODE_PATH && !p.transmissive_illum) return false;
     const D3 exact = transmissive_bounce(normal, view, cos_theta, b.ir, p.ir_air);
     bounce = p.distrib_transmissive ? specular_sample(exact, b.n, cos_theta, s.rng) : exact;
     st.transmissive++;
     s.tw = mul3(s.tw, (b.kt * (1.0 - r_coeff)) / prob_transmission);
   } else if (rnd < prob_diffuse + prob_transmission + prob_specular) {
-    if (s.mode == MODE_PATH && !p.specular_illum) return false;
+    if (mode == MODE_PATH && !p.specular_illum) return false;
     const D3 exact = reflective_bounce(normal, view, cos_theta);
     bounce = p.distrib_specular ? specular_sample(exact, b.n, cos_theta, s.rng) : exact;
     st.specular++;
@@ -265,7 +281,16 @@ GI_DEV bool path_step(const ShadeEnv &env, PathState &s, const Queue &qglobal, c
   } else return false;
   s.ray.o = point + bounce * GI_EPS; s.ray.d = bounce;
   s.iter++;
+  s.rng.left = 0;
   return s.iter < p.max_monte_depth;
+}
+
+// closest hit + shading of one bounce in one thread (the finishing pass and the thread-per-path kernel)
+template <int MODE>
+GI_DEV bool path_step(const ShadeEnv &env, PathState &s, const Queue &qglobal, const Queue &qcaustic, RayStats &st) {
+  HitRec h;
+  closest_hit(env.sc, s.ray, h);
+  return path_shade<MODE>(env, s, h.prim < 0 ? -1 : h.element, h.p, h.n, qglobal, qcaustic, st);
 }
 
 // Start of secondary path `g`: item g belongs to the primary hit h with offs[h] <= g < offs[h+1]; inside the hit the
@@ -301,14 +326,166 @@ GI_DEV bool path_begin(const ShadeEnv &env, const PrimHit *__restrict__ hits,
   s.ray.o = point + bounce * GI_EPS; s.ray.d = bounce;
   s.scale = total_weight / (double)count; s.tw = mk3(1, 1, 1); s.out = mk3(0, 0, 0);
   s.pix = ph.pix; s.iter = 0;
+  s.rng.left = 0;
   return !(s.mode == MODE_PATH && !env.p.monte_carlo) && env.p.max_monte_depth > 0;
 }
 
-// One thread per secondary path, start to end.  (A persistent variant in which lanes take a new path as soon as
-// theirs ends -- the design of the photon tracer, photon_trace.cu -- was measured 15-20 % slower here: nearly every
-// secondary path is one or two bounces long, so there is little imbalance to win back and the refill costs more.)
-// MINB = resident CTAs per SM the kernel is compiled for: 6 -> 80 registers, 24 warps per SM; the kernel is
-// latency-bound (incoherent BVH walks), more warps beat fewer spills.
+// ------------------------------------------------------------------------------------------------ wavefront path stage
+// The reference recurses per pixel (RayTrace -> Transmissive/Specular/IndirectIllumination -> MonteCarlo_PathTrace /
+// MonteCarlo_IndirectSample, raytracer.cpp:47-135, montecarlo.cpp:16-305).  A thread that walks one path from start to
+// end leaves most of its warp idle -- nearly every walk ends at its first hit, a few go on through glass and mirrors,
+// and the warp waits for them with 1-4 live lanes (ncu, round 1: 11 of 32 lanes active) -- and it runs 38 000
+// instructions of code (600 KB: sampling, FP64 traversal and primitive tests three times over, light loops) against an
+// instruction cache of 32 KB per SM: 13 cycles of instruction-fetch stall per issued instruction.  Here the walk is cut
+// into BOUNCE PASSES of small kernels.  Between kernels the live paths are parked in queues, one per RAY CLASS:
+//   class SPEC (MODE_PATH):     specular / refractive / Fresnel Monte Carlo rays; their hits are shaded with direct light
+//                               (shadow rays) and queue a caustic gather,
+//   class DIFF (MODE_INDIRECT): diffuse-bounce rays of the indirect estimate; their hits only play roulette and end
+//                               in a global-map gather request.
+// A pass =  wave_hit_kernel   closest hit for every parked ray of both classes (traversal + primitive tests only),
+//           wave_shade_kernel one launch per class: material, direct light (SPEC), roulette, next bounce; gather
+//                             requests go to the map queues, survivors are compacted into the next pass's class queues
+//                             with a warp ballot (one atomicAdd per warp and class).
+// Every kernel runs full warps of ONE class through ONE stage.  The pass count is fixed (GI_WAVE_PASSES) and the kernels
+// read the queue lengths on the device, so the host never waits between passes; the few paths still alive after the
+// last pass (walks of dozens of bounces inside glass) are finished by a thread each.
+struct __align__(16) PathRec {       // 128 B: one parked path
+  double o[3], d[3], scale[3], tw[3];
+  uint32_t c0, c1, c2, c3;           // Philox counter of the path's stream (key = seed)
+  uint32_t pix, item;
+  int32_t iter; uint32_t pad;
+};
+struct __align__(16) WaveHit {       // 64 B: closest hit of the parked ray in the same slot
+  double p[3], n[3];
+  int32_t element, prim;             // element < 0: miss
+  double t;
+};
+enum { CLASS_SPEC = 0, CLASS_DIFF = 1 };
+struct PathWave {                    // one buffer, two queues: class SPEC grows from the front, class DIFF from the back
+  PathRec *rec;
+  WaveHit *hit;
+  unsigned int *count;               // [2], per class; never exceeds cap in total (a path parks at most once per pass)
+  uint32_t cap;
+};
+
+GI_DEV void park(PathRec *r, const PathState &s) {
+  double4 *o = (double4 *)r;
+  o[0] = make_double4(s.ray.o.x, s.ray.o.y, s.ray.o.z, s.ray.d.x);
+  o[1] = make_double4(s.ray.d.y, s.ray.d.z, s.scale.x, s.scale.y);
+  o[2] = make_double4(s.scale.z, s.tw.x, s.tw.y, s.tw.z);
+  uint4 *u = (uint4 *)(r) + 6;
+  u[0] = make_uint4(s.rng.c0, s.rng.c1, s.rng.c2, s.rng.c3);
+  u[1] = make_uint4(s.pix, s.item, (uint32_t)s.iter, 0u);
+}
+GI_DEV void unpark(const PathRec *r, uint64_t seed, PathState &s) {
+  const double4 *i = (const double4 *)r;
+  const double4 a = i[0], b = i[1], c = i[2];
+  s.ray.o = mk3(a.x, a.y, a.z); s.ray.d = mk3(a.w, b.x, b.y); s.scale = mk3(b.z, b.w, c.x); s.tw = mk3(c.y, c.z, c.w);
+  const uint4 *u = (const uint4 *)(r) + 6;
+  const uint4 x = u[0], y = u[1];
+  s.rng.k0 = (uint32_t)seed; s.rng.k1 = (uint32_t)(seed >> 32);
+  s.rng.c0 = x.x; s.rng.c1 = x.y; s.rng.c2 = x.z; s.rng.c3 = x.w; s.rng.left = 0;
+  s.pix = y.x; s.item = y.y; s.iter = (int)y.z;
+  s.out = mk3(0, 0, 0);
+}
+
+// Every lane of the warp calls this; the lanes with `live` set park their path in the queue of class `cls`.
+GI_DEV void wave_push(const PathWave &w, int cls, bool live, const PathState &s) {
+  const unsigned m = __ballot_sync(0xffffffffu, live);
+  if (!m) return;
+  const int lane = threadIdx.x & 31, leader = __ffs(m) - 1;
+  unsigned base = 0;
+  if (lane == leader) base = atomicAdd(w.count + cls, (unsigned)__popc(m));
+  base = __shfl_sync(0xffffffffu, base, leader);
+  if (live) {
+    const unsigned i = base + __popc(m & ((1u << lane) - 1u));
+    park(w.rec + (cls == CLASS_SPEC ? i : w.cap - 1u - i), s);
+  }
+}
+
+// Pass 0, a thread per secondary path of the batch: the path's first ray, parked by class.  Clears every item's colour
+// slot (the shade passes add to it).
+__global__ void __launch_bounds__(128, 6) wave_begin_kernel(ShadeEnv env, const PrimHit *__restrict__ hits,
+                                                            const uint64_t *__restrict__ offs, const uint32_t *__restrict__ item_hit,
+                                                            uint64_t item0, uint32_t n, double *__restrict__ item_rgb,
+                                                            uint32_t *__restrict__ item_pix, PathWave next, RayStats *stats) {
+  RayStats st = zero_stats();
+  const uint32_t t = blockIdx.x * blockDim.x + threadIdx.x;       // the grid covers n rounded up to whole warps
+  PathState s;
+  s.mode = -1; s.pix = 0;
+  bool live = false;
+  if (t < n) {
+    s.item = t;
+    live = path_begin(env, hits, offs, item0 + t, item_hit[t] - 1, s, st);
+    item_rgb[3 * (size_t)t] = 0.0; item_rgb[3 * (size_t)t + 1] = 0.0; item_rgb[3 * (size_t)t + 2] = 0.0;
+    item_pix[t] = s.pix;
+  }
+  wave_push(next, CLASS_SPEC, live && s.mode == MODE_PATH, s);
+  wave_push(next, CLASS_DIFF, live && s.mode == MODE_INDIRECT, s);
+  flush_stats(stats, st);
+}
+
+// slot of entry t of the two queues taken as one sequence: the SPEC entries, then the DIFF entries
+GI_DEV unsigned wave_slot(unsigned t, unsigned n_spec, unsigned cap) { return t < n_spec ? t : cap - 1u - (t - n_spec); }
+
+// Closest hit of every parked ray (both classes).  Nothing but BVH traversal and the FP64 primitive tests: the code all
+// warps of the SM are in fits the instruction cache.  Persistent grid.
+__global__ void __launch_bounds__(128, 6) wave_hit_kernel(DevScene sc, PathWave cur) {
+  const unsigned n_spec = cur.count[CLASS_SPEC], n = n_spec + cur.count[CLASS_DIFF];
+  for (unsigned t = blockIdx.x * blockDim.x + threadIdx.x; t < n; t += gridDim.x * blockDim.x) {
+    const unsigned slot = wave_slot(t, n_spec, cur.cap);
+    const double4 *i = (const double4 *)(cur.rec + slot);
+    const double4 a = i[0]; const double2 b = *(const double2 *)(i + 1);
+    RayD ray; ray.o = mk3(a.x, a.y, a.z); ray.d = mk3(a.w, b.x, b.y);
+    HitRec h;
+    closest_hit(sc, ray, h);
+    double4 *o = (double4 *)(cur.hit + slot);
+    o[0] = make_double4(h.p.x, h.p.y, h.p.z, h.n.x);
+    o[1] = make_double4(h.n.y, h.n.z, __hiloint2double(h.prim, h.prim < 0 ? -1 : h.element), h.t);
+  }
+}
+
+// Shading of one class after wave_hit_kernel: a thread per parked path (persistent grid, warp-uniform loop); survivors
+// are parked in `next`.  FINISH: the last pass walks every path it gets to its end instead (closest hits inline).
+template <int MODE, bool FINISH>
+__global__ void __launch_bounds__(128, 6) wave_shade_kernel(ShadeEnv env, PathWave cur, PathWave next, double *__restrict__ item_rgb,
+                                                            Queue qglobal, Queue qcaustic, RayStats *stats) {
+  RayStats st = zero_stats();
+  const int cls = MODE == MODE_PATH ? CLASS_SPEC : CLASS_DIFF;
+  const unsigned n = cur.count[cls];
+  const unsigned lane = threadIdx.x & 31u;
+  for (unsigned base = (blockIdx.x * blockDim.x + threadIdx.x) - lane; base < n; base += gridDim.x * blockDim.x) {
+    const unsigned t = base + lane;
+    bool live = t < n;
+    PathState s;
+    s.mode = MODE;
+    if (live) {
+      const unsigned slot = cls == CLASS_SPEC ? t : cur.cap - 1u - t;
+      unpark(cur.rec + slot, env.p.seed, s);
+      s.mode = MODE;
+      if (FINISH) {
+        live = path_step<MODE>(env, s, qglobal, qcaustic, st);
+        while (live) live = path_step<-1>(env, s, qglobal, qcaustic, st);
+      } else {
+        const double4 *hi = (const double4 *)(cur.hit + slot);
+        const double4 a = hi[0], b = hi[1];
+        live = path_shade<MODE>(env, s, __double2loint(b.z), mk3(a.x, a.y, a.z), mk3(a.w, b.x, b.y), qglobal, qcaustic, st);
+      }
+      if (s.out.x != 0.0 || s.out.y != 0.0 || s.out.z != 0.0) {     // an item is owned by one thread at a time
+        double *o = item_rgb + 3 * (size_t)s.item;
+        o[0] += s.out.x; o[1] += s.out.y; o[2] += s.out.z;
+      }
+    }
+    if (!FINISH) {
+      if (MODE == MODE_PATH) wave_push(next, CLASS_SPEC, live && s.mode == MODE_PATH, s);
+      wave_push(next, CLASS_DIFF, live && s.mode == MODE_INDIRECT, s);
+    }
+  }
+  flush_stats(stats, st);
+}
+
+// The round-1 layout, kept for A/B measurements (GI_PATH_MEGAKERNEL=1): one thread per secondary path, start to end.
+// MINB = resident CTAs per SM the kernel is compiled for: 6 -> 80 registers, 24 warps per SM.
 template <int MINB>
 __global__ void __launch_bounds__(128, MINB) path_kernel(ShadeEnv env, const PrimHit *__restrict__ hits,
                                                          const uint64_t *__restrict__ offs, const uint32_t *__restrict__ item_hit,
@@ -320,7 +497,7 @@ __global__ void __launch_bounds__(128, MINB) path_kernel(ShadeEnv env, const Pri
     PathState s;
     s.item = t;
     bool active = path_begin(env, hits, offs, item0 + t, item_hit[t] - 1, s, st);
-    while (active) active = path_step(env, s, qglobal, qcaustic, st);
+    while (active) active = path_step<-1>(env, s, qglobal, qcaustic, st);
     item_rgb[3 * (size_t)t] = s.out.x; item_rgb[3 * (size_t)t + 1] = s.out.y; item_rgb[3 * (size_t)t + 2] = s.out.z;
     item_pix[t] = s.pix;
   }
@@ -499,6 +676,7 @@ struct Workspace {
   static constexpr uint32_t batch_max = 1u << 21;        // secondary paths per pass
   static constexpr unsigned long long qcap = 1ull << 22; // >= chunk (direct_kernel pushes at most one request per hit)
   DevBuf hits, n_items, offs, item_rgb, item_pix, scan_tmp, item_hit, hit_scan_tmp, lights, stats, accum, image, strips, comm_tmp;
+  DevBuf wave_rec[2], wave_hit[2], wave_count;                        // parked paths of the wavefront path stage: ping / pong, 2 x 2 class counters
   size_t image_bytes = 0, strips_bytes = 0;
   QueueStore qg, qc;
   size_t scan_bytes = 0, hit_scan_bytes = 0, accum_doubles = 0, n_lights = 0;
@@ -507,7 +685,9 @@ struct Workspace {
     if (ready) return true;
     if (!hits.alloc(sizeof(PrimHit) * chunk) || !n_items.alloc(4 * (chunk + 1)) || !offs.alloc(8 * (chunk + 1)) ||
         !item_rgb.alloc(sizeof(double) * 3 * batch_max) || !item_pix.alloc(4 * (size_t)batch_max) || !item_hit.alloc(4 * (size_t)batch_max) ||
-        !stats.alloc(2 * sizeof(RayStats)) || !qg.alloc(qcap) || !qc.alloc(qcap))
+        !stats.alloc(2 * sizeof(RayStats)) || !qg.alloc(qcap) || !qc.alloc(qcap) ||
+        !wave_rec[0].alloc(sizeof(PathRec) * (size_t)batch_max) || !wave_rec[1].alloc(sizeof(PathRec) * (size_t)batch_max) ||
+        !wave_hit[0].alloc(sizeof(WaveHit) * (size_t)batch_max) || !wave_hit[1].alloc(sizeof(WaveHit) * (size_t)batch_max) || !wave_count.alloc(16))
       return false;
     cub::DeviceScan::ExclusiveSum(nullptr, scan_bytes, n_items.as<uint32_t>(), offs.as<uint64_t>(), (int)(chunk + 1), st);
     cub::DeviceScan::InclusiveScan(nullptr, hit_scan_bytes, item_hit.as<uint32_t>(), item_hit.as<uint32_t>(), cub::Max(), (int)batch_max, st);
@@ -675,6 +855,9 @@ static int render_accum(GiContext *ctx, const GiParams &params, int sw, int sh, 
   size_t scan_bytes = ws.scan_bytes, hit_scan_bytes = ws.hit_scan_bytes;
   int path_occ = 6;                                       // resident CTAs per SM: 4 (128 registers) or 6 (80 registers)
   if (const char *e = getenv("GI_PATH_OCC")) path_occ = atoi(e);
+  const bool megakernel = getenv("GI_PATH_MEGAKERNEL") && atoi(getenv("GI_PATH_MEGAKERNEL")) != 0;      // A/B hook: the round-1 thread-per-path kernel
+  int wave_passes = 4;                                    // wavefront bounce passes per class before the finishing pass
+  if (const char *e = getenv("GI_WAVE_PASSES")) wave_passes = std::min(std::max(atoi(e), 0), 64);
 
   const uint64_t s_begin = 0, s_end = local_cols * sh * p.dof_test;
   for (uint64_t s0 = s_begin; s0 < s_end; s0 += chunk) {
@@ -701,12 +884,34 @@ static int render_accum(GiContext *ctx, const GiParams &params, int sw, int sh, 
                                                                       item_hit.as<uint32_t>());
       GI_CUDA(cub::DeviceScan::InclusiveScan(hit_scan_tmp.p, hit_scan_bytes, item_hit.as<uint32_t>(), item_hit.as<uint32_t>(), cub::Max(),
                                              (int)m, R.st));
-      {
+      if (megakernel) {
         auto launch = [&](auto kernel) {
           kernel<<<(m + 127) / 128, 128, 0, R.st>>>(env, hits.as<PrimHit>(), offs.as<uint64_t>(), item_hit.as<uint32_t>(), item0, m,
                                                     item_rgb.as<double>(), item_pix.as<uint32_t>(), path_qg, path_qc, d_stats + 1);
         };
         if (path_occ <= 4) launch(path_kernel<4>); else launch(path_kernel<6>);
+      } else {
+        // wavefront: pass 0 parks every path's first ray by class; then bounce passes (closest-hit kernel + one shade kernel per
+        // class) over ballot-compacted queues.  The pass count is fixed: the host never waits for a queue length.
+        PathWave wv[2];
+        for (int i = 0; i < 2; i++) {
+          wv[i].rec = ws.wave_rec[i].as<PathRec>(); wv[i].hit = ws.wave_hit[i].as<WaveHit>();
+          wv[i].count = ws.wave_count.as<unsigned int>() + 2 * i; wv[i].cap = Workspace::batch_max;
+        }
+        GI_CUDA(cudaMemsetAsync(ws.wave_count.p, 0, 16, R.st));
+        wave_begin_kernel<<<(m + 127) / 128, 128, 0, R.st>>>(env, hits.as<PrimHit>(), offs.as<uint64_t>(), item_hit.as<uint32_t>(), item0, m,
+                                                             item_rgb.as<double>(), item_pix.as<uint32_t>(), wv[0], d_stats + 1);
+        const unsigned wgrid = (unsigned)std::min<uint64_t>((m + 127) / 128, (uint64_t)ctx->sm_count * 6);
+        int cur = 0;
+        for (int pass = 0; pass < wave_passes; pass++, cur ^= 1) {
+          GI_CUDA(cudaMemsetAsync(wv[cur ^ 1].count, 0, 8, R.st));
+          wave_hit_kernel<<<wgrid, 128, 0, R.st>>>(env.sc, wv[cur]);
+          wave_shade_kernel<MODE_PATH, false><<<wgrid, 128, 0, R.st>>>(env, wv[cur], wv[cur ^ 1], item_rgb.as<double>(), path_qg, path_qc, d_stats + 1);
+          wave_shade_kernel<MODE_INDIRECT, false><<<wgrid, 128, 0, R.st>>>(env, wv[cur], wv[cur ^ 1], item_rgb.as<double>(), path_qg, path_qc, d_stats + 1);
+        }
+        wave_shade_kernel<MODE_PATH, true><<<wgrid, 128, 0, R.st>>>(env, wv[cur], wv[cur ^ 1], item_rgb.as<double>(), path_qg, path_qc, d_stats + 1);
+        wave_shade_kernel<MODE_INDIRECT, true><<<wgrid, 128, 0, R.st>>>(env, wv[cur], wv[cur ^ 1], item_rgb.as<double>(), path_qg, path_qc, d_stats + 1);
+        ctx->launches += 2 + 3 * (uint64_t)wave_passes;
       }
       ctx->launches += 2;
       GI_CUDA(cudaGetLastError());
