@@ -660,7 +660,7 @@ struct QueueStore {
       return false;
     view.q = q.as<GiGatherQuery>(); view.w = w.as<double>(); view.pix = pix.as<uint32_t>();
     view.count = count.as<unsigned long long>(); view.cap = cap;
-    if (!sorted_q.alloc(sizeof(GiGatherQuery) * cap) || !keys.alloc(4 * cap) || !keys2.alloc(4 * cap) || !order.alloc(4 * cap) ||
+    if (!keys.alloc(4 * cap) || !keys2.alloc(4 * cap) || !order.alloc(4 * cap) ||
         !order2.alloc(4 * cap))
       return false;
     cub::DeviceRadixSort::SortPairs(nullptr, sort_bytes, keys.as<uint32_t>(), keys2.as<uint32_t>(), order.as<uint32_t>(),
@@ -673,8 +673,8 @@ struct QueueStore {
 // (cudaMalloc / cudaFree of a few GB per frame costs tens of milliseconds and jitters).
 struct Workspace {
   static constexpr uint64_t chunk = 1ull << 22;          // primary samples per pass
-  static constexpr uint32_t batch_max = 1u << 21;        // secondary paths per pass
-  static constexpr unsigned long long qcap = 1ull << 22; // >= chunk (direct_kernel pushes at most one request per hit)
+  static constexpr uint32_t batch_max = 1u << 23;        // secondary paths per pass (the serial tail of a batch -- a few walks of dozens of bounces -- is paid once per batch)
+  static constexpr unsigned long long qcap = 1ull << 23; // >= chunk (direct_kernel pushes at most one request per hit)
   DevBuf hits, n_items, offs, item_rgb, item_pix, scan_tmp, item_hit, hit_scan_tmp, lights, stats, accum, image, strips, comm_tmp;
   DevBuf wave_rec[2], wave_hit[2], wave_count;                        // parked paths of the wavefront path stage: ping / pong, 2 x 2 class counters
   size_t image_bytes = 0, strips_bytes = 0;
@@ -789,6 +789,7 @@ struct Renderer {
     if (!cuda_ok(cub::DeviceRadixSort::SortPairs(qs.sort_tmp.p, bytes, qs.keys.as<uint32_t>(), qs.keys2.as<uint32_t>(),
                                                  qs.order.as<uint32_t>(), qs.order2.as<uint32_t>(), (int)n, 0, 30, st), "sort requests"))
       return false;
+    if (!qs.sorted_q.p && !qs.sorted_q.alloc(sizeof(GiGatherQuery) * qs.view.cap)) return false;      // -cache only: allocated on first use
     permute_requests_kernel<<<(unsigned)((n * 17 + 255) / 256), 256, 0, st>>>((const double *)qs.view.q, qs.order2.as<uint32_t>(), n,
                                                                              qs.sorted_q.as<double>());
     if (estimate(qs.sorted_q.as<GiGatherQuery>())) return false;
