@@ -1,19 +1,30 @@
 #!/usr/bin/env python
-"""bench.py -- the hot path of the photon-mapping renderer on B200: closest-hit ray casting + photon kNN gather.
+"""bench.py -- the hot path of the photon-mapping renderer on B200: photon-map build + closest-hit ray casting + photon
+kNN gather, sharded the way the renderer shards a frame.
 
-One "step" = one pass of the hot path over one frame's worth of synthetic input of BASELINE.json configs[1]
-(jensen scene, 1024 x 1024, aa 2  =>  4096 x 4096 = 16.8 M primary rays): gi_intersect_batch over every camera ray,
-then gi_gather_batch (k = 225, r = 0.225, the reference's caustic defaults) at every primary hit point against a
-10^7-photon map (the reference's default caustic map size) laid on the scene's surfaces.
-metric = Mrays/s in the reference's own accounting (render.cpp:224-255 counts gather samples as rays), with the
-two stages also reported separately (mrays_per_s_intersect, gathers_per_s).
+One "step" = one pass of the hot path over one frame's worth of synthetic input of BASELINE.json configs[1] (jensen scene,
+1024 x 1024, aa 2  =>  4096 x 4096 = 16.8 M primary rays PER GPU), in the order MapPhotons / RenderImage run it:
+  1. photon map: the 10^7 photons (the reference's default caustic map size; laid on the scene's surfaces) sit sharded
+     over the ranks, photons/N each; gi_load_photons_sharded_device replicates them with ONE ragged NCCL all-gather over
+     NVLink (N = 1: a device copy) and gi_build_maps builds the left-balanced kd-tree on every rank;
+  2. gi_intersect_batch_device over the rank's camera rays -- rank r owns the pixel columns x = r (mod N) of a
+     (1024 N) x 1024 aa 2 frame, the renderer's own column split (render.cpp:90), so per-GPU work is fixed (weak scaling);
+  3. gi_gather_batch_device (k = 225, r = 0.225, the reference's caustic defaults) at every primary hit;
+  4. the rank's radiance goes through clamp / box filter / u8 (torch glue, timed, not counted as ours) and the 8-bit
+     column strips are gathered to rank 0 (NCCL), as gi_render does with its strips.
+metric = Mrays/s in the reference's own accounting (render.cpp:224-255 counts gather samples as rays); the stages are
+also reported separately (mrays_per_s_intersect, gathers_per_s, kd_build_ms ...).
 
   python bench.py [--gpus N --steps K --warmup W]          our arm (N > 1: launched by torch.distributed.run)
   python bench.py --impl reference ...                      the reference's own CPU code (oracle/_ref) on the host cores
 
-`value` is measured with all inputs resident in HBM; `e2e` goes through the host-buffer C-ABI calls (pinned host
-memory in, host results out, copies inside the timed region).  torch is used for device buffers, events and
-torch.distributed only; every kernel in the timed region is ours (libgi_b200.so).
+`value` is measured with all inputs resident in HBM; `e2e` goes through the host-buffer C-ABI calls (pinned host memory
+in, host results out, copies inside the timed region).  torch is used for device buffers, events, the resolve glue and
+torch.distributed only; every other kernel in the timed region is ours (libgi_b200.so).
+After the timed steps the line also carries: `frames` (the metric's own frame -- cornell 1024 x 1024 aa 2, all flags
+default -- and cornell 512 x 512 aa 1, through gi_trace_photons + gi_render, sharded over the N ranks inside the C ABI,
+with per-stage device milliseconds), `gathers_small_map` (k = 50 on a 2176-photon map: the regime of 97 % of a default
+frame's gathers) and `intersect_mesh` (violin.scn, 104 k triangles).
 """
 import argparse
 import ctypes
@@ -22,7 +33,6 @@ import os
 import subprocess
 import sys
 import tempfile
-import threading
 import time
 
 import numpy as np
@@ -37,6 +47,7 @@ K, R, FILTER = 225, 0.225, 0
 B_PHOTON = 32          # bytes per photon touched in the parity layout: 24 B FP64 position + 8 B shade record
 GATHER_ALGO_BYTES = K * B_PHOTON + 52      # k x B_photon + query in / rgb out
 RAY_ALGO_BYTES = 48 + 72                   # GiRay in + GiHit out
+METRIC = "Mrays/s (closest-hit rays + photon kNN gather samples, reference accounting; photon-map replicate + kd build inside the step)"
 
 
 def parse():
@@ -52,10 +63,10 @@ def parse():
     ap.add_argument("--no-cpu-baseline", action="store_true")
     ap.add_argument("--cpu-rays", type=int, default=2_000_000)
     ap.add_argument("--cpu-queries", type=int, default=200_000)
-    ap.add_argument("--no-frame", action="store_true", help="skip the whole-program frame (photon pass + render) report")
-    ap.add_argument("--frame-scene", default="cornell")
-    ap.add_argument("--frame-res", type=int, default=512)
-    ap.add_argument("--frame-aa", type=int, default=1)
+    ap.add_argument("--frames", default="default", choices=["none", "small", "default", "all"],
+                    help="whole-program frames after the timed steps: small = cornell 512^2 aa 1; default = + the metric's "
+                         "cornell 1024^2 aa 2; all = + BASELINE.json configs 3-5 (minutes)")
+    ap.add_argument("--no-extras", action="store_true", help="skip the small-map gather and mesh intersect sections")
     return ap.parse_args()
 
 
@@ -114,23 +125,24 @@ class ClockSampler:
         return out
 
 
-def camera_rays(torch, cam, W, H, dev, jitter=0.0):
+def camera_rays(torch, cam, W, H, dev, cols=None):
     """render.cpp:64-117 without depth of field: far_point = eye + towards*F + right*tan(xfov)*F*dx + up*tan(yfov)*F*dy,
-    dx = 2(i - W/2)/W, dy = 2(j - H/2)/H, rays normalised (R3Ray ctor).  Column-major like image_buffer[i][j]."""
+    dx = 2(i - W/2)/W, dy = 2(j - H/2)/H, rays normalised (R3Ray ctor).  Column-major like image_buffer[i][j];
+    `cols` = the supersample columns i to generate (default: all W)."""
     f64 = torch.float64
     eye = torch.tensor(list(cam.eye), dtype=f64, device=dev)
     tow = torch.tensor(list(cam.towards), dtype=f64, device=dev)
     up = torch.tensor(list(cam.up), dtype=f64, device=dev)
     right = torch.tensor(list(cam.right), dtype=f64, device=dev)
     F = 100.0
-    i = torch.arange(W, dtype=f64, device=dev) + jitter
-    j = torch.arange(H, dtype=f64, device=dev) + jitter
+    i = torch.arange(W, dtype=f64, device=dev) if cols is None else cols.to(f64)
+    j = torch.arange(H, dtype=f64, device=dev)
     dx = (2.0 * (i - (W // 2)) / W)[:, None, None]
     dy = (2.0 * (j - (H // 2)) / H)[None, :, None]
     far = eye + tow * F + right * (np.tan(cam.xfov) * F) * dx + up * (np.tan(cam.yfov) * F) * dy
     d = far - eye
     d = d / torch.sqrt((d[..., 0] * d[..., 0] + d[..., 1] * d[..., 1] + d[..., 2] * d[..., 2]))[..., None]
-    rays = torch.empty((W, H, 6), dtype=f64, device=dev)
+    rays = torch.empty((i.shape[0], H, 6), dtype=f64, device=dev)
     rays[..., 0:3] = eye
     rays[..., 3:6] = d
     return rays.reshape(-1, 6).contiguous()
@@ -146,7 +158,8 @@ def hits_fields(torch, hits_u8):
 
 def make_queries(torch, rays, hits_u8):
     """GiGatherQuery records at the hit points, set up as CausticIllumination is called from RayTrace
-    (raytracer.cpp:138-149, 174-190): cos_theta = n.(-view), exact_bounce = mirror direction."""
+    (raytracer.cpp:138-149, 174-190): cos_theta = n.(-view), exact_bounce = mirror direction.
+    Returns (queries [n_q, 17], index of each query's ray)."""
     hit, f = hits_fields(torch, hits_u8)
     m = hit == 1
     d = rays[m, 3:6]; p = f[m, 3:6]; n = f[m, 6:9]
@@ -155,7 +168,7 @@ def make_queries(torch, rays, hits_u8):
     q[:, 0:3] = p; q[:, 3:6] = n; q[:, 6:9] = d + 2.0 * cos[:, None] * n; q[:, 9] = cos
     q[:, 10:13] = torch.tensor([0.5, 0.5, 0.5], dtype=torch.float64, device=rays.device)
     q[:, 13:16] = 0.0; q[:, 16] = 1.0
-    return q.contiguous()
+    return q.contiguous(), torch.nonzero(m).reshape(-1)
 
 
 def make_photons(torch, ctx, scene, n, seed, dev):
@@ -187,20 +200,28 @@ def make_photons(torch, ctx, scene, n, seed, dev):
     return out
 
 
+def config_dict(args, world=1):
+    n = (args.width << args.aa) * (args.height << args.aa)
+    return {"workload": f"input/{SCENE}.scn {args.width}x{args.height} -aa {args.aa} per GPU: photon map of {args.photons} photons "
+                        f"(sharded over the ranks, all-gathered, kd-tree built per rank) + closest hit for all {n} primary rays + "
+                        f"caustic-style photon gather (k={K}, r={R}, disk filter) at every primary hit + 8-bit strips to rank 0",
+            "photons": args.photons, "k": K, "r": R, "ranks": world,
+            "split": "photons/N per rank + one all-gather; pixel columns x = rank (mod N) of a (width x N) frame; strips gathered to rank 0",
+            "l2": "inputs larger than L2 (0.8 GB rays, 2.3 GB queries, 0.32 GB photons per step)"}
+
+
+def step_value(n_rays, n_q, isect_rate, gather_rate, build_s):
+    """Mrays/s of a step with the given unit counts from per-stage rates (rays/s, gathers/s) and the map build time"""
+    return (n_rays + n_q) / (n_rays / isect_rate + n_q / gather_rate + build_s) / 1e6
+
+
 # ------------------------------------------------------------------------------------------- reference / CPU arm
 REF_HARNESS = os.path.join(ROOT, "oracle", "_ref", "ref_harness")
-SCENE_TOOL = os.path.join(ROOT, "global-illumination_b200", "bin", "gi_scene_tool")
-
-
-def export_scene_scn(tmp):
-    """the reference binary reads .scn only: write the flattened jensen scene back out as Princeton text"""
-    scn = os.path.join(tmp, SCENE + ".scn")
-    subprocess.run([SCENE_TOOL, "export", os.path.join(GOLDEN, SCENE + ".gisc"), scn], check=True)
-    return scn
+STOCK_SCN = os.path.join(GOLDEN, "scn", SCENE + ".scn")        # a copy of the reference's input/jensen.scn
 
 
 def ref_bench(tmp, scn, rays, photons_u8, queries, steps, warmup, threads):
-    """time the reference's R3Scene::Intersects + EstimateRadiance (oracle/_ref/ref_harness bench) on host threads"""
+    """time the reference's R3Scene::Intersects + EstimateRadiance + R3Kdtree build (oracle/_ref/ref_harness bench)"""
     from gi_testlib import write_rays, write_queries, GI_QUERY
     write_rays(os.path.join(tmp, "rays.bin"), rays)
     q = np.zeros(len(queries), dtype=GI_QUERY)
@@ -216,24 +237,20 @@ def ref_bench(tmp, scn, rays, photons_u8, queries, steps, warmup, threads):
     return json.loads(out.strip().splitlines()[-1])
 
 
-def cpu_inputs_numpy(args, tmp, scn, n_rays, n_queries, threads):
-    """inputs of the same workload generated WITHOUT the GPU (reference arm): camera-ray sample, photons at the
-    reference's own closest hits of random rays, queries at the reference's primary hits"""
-    from gi_testlib import write_rays, read_ref_hits, random_rays
-    import gi_b200
-    scene = gi_b200.HostScene(os.path.join(GOLDEN, SCENE + ".gisc"))
-    cam = scene.view.camera
-    W, H = args.width << args.aa, args.height << args.aa
-    rng = np.random.default_rng(1)
-    pick = rng.choice(W * H, size=min(n_rays, W * H), replace=False)
-    i = (pick // H).astype(np.float64); j = (pick % H).astype(np.float64)
-    eye = np.array(cam.eye[:]); tow = np.array(cam.towards[:]); up = np.array(cam.up[:]); right = np.array(cam.right[:])
-    F = 100.0
-    dx = (2.0 * (i - (W // 2)) / W)[:, None]; dy = (2.0 * (j - (H // 2)) / H)[:, None]
-    far = eye + tow * F + right * (np.tan(cam.xfov) * F) * dx + up * (np.tan(cam.yfov) * F) * dy
-    d = far - eye
-    d /= np.sqrt(d[:, 0] * d[:, 0] + d[:, 1] * d[:, 1] + d[:, 2] * d[:, 2])[:, None]
-    rays = np.concatenate([np.broadcast_to(eye, d.shape), d], axis=1)
+def reference_inputs(args, tmp, scn, n_rays, n_queries, threads):
+    """inputs of the same workload made by the REFERENCE alone (no GPU, no library of ours): `ref_harness camrays` at a
+    reduced resolution = a uniform sample of the frame's camera rays, photons at the reference's own closest hits of
+    random rays inside R3Scene::BBox(), queries at the reference's primary hits"""
+    from gi_testlib import write_rays, read_rays, read_ref_hits, random_rays
+    side = max(16, int(round(np.sqrt(n_rays))))
+    subprocess.run([REF_HARNESS, "camrays", scn, str(side), str(side), os.path.join(tmp, "cam.bin")], check=True, capture_output=True)
+    rays = read_rays(os.path.join(tmp, "cam.bin"))
+    subprocess.run([REF_HARNESS, "dump_scene", scn, os.path.join(tmp, "scene.txt")], check=True, capture_output=True)
+    bbox = None
+    for line in open(os.path.join(tmp, "scene.txt")):
+        if line.startswith("bbox"):
+            bbox = [float(x) for x in line.split()[1:7]]
+    lo, hi = np.array(bbox[:3]), np.array(bbox[3:])
 
     def ref_isect(r):
         write_rays(os.path.join(tmp, "gen.bin"), r)
@@ -241,13 +258,16 @@ def cpu_inputs_numpy(args, tmp, scn, n_rays, n_queries, threads):
                        check=True, capture_output=True)
         return read_ref_hits(os.path.join(tmp, "gen.hits"))
 
-    h = ref_isect(rays[:n_queries])
-    m = h["hit"] == 1
-    dd = rays[:n_queries][m, 3:6]; n = h["n"][m]; cos = -(n * dd).sum(1)
-    q = np.zeros((m.sum(), 17))
-    q[:, 0:3] = h["p"][m]; q[:, 3:6] = n; q[:, 6:9] = dd + 2.0 * cos[:, None] * n; q[:, 9] = cos
+    rng = np.random.default_rng(1)
+    pick = rng.choice(len(rays), size=min(n_queries, len(rays)), replace=False)
+    h = ref_isect(rays)
+    hit_fraction = float((h["hit"] == 1).mean())
+    hq = h[pick]; rq = rays[pick]
+    m = hq["hit"] == 1
+    dd = rq[m, 3:6]; n = hq["n"][m]; cos = -(n * dd).sum(1)
+    q = np.zeros((int(m.sum()), 17))
+    q[:, 0:3] = hq["p"][m]; q[:, 3:6] = n; q[:, 6:9] = dd + 2.0 * cos[:, None] * n; q[:, 9] = cos
     q[:, 10:13] = 0.5; q[:, 16] = 1.0
-    lo = np.array(scene.view.bbox_min[:]); hi = np.array(scene.view.bbox_max[:])
     ph = np.zeros((args.photons, 32), dtype=np.uint8); filled = 0; seed = 50
     while filled < args.photons:
         rr = random_rays(min(int((args.photons - filled) * 1.3) + 1024, 4_000_000), lo, hi, seed, scale=1.0); seed += 1
@@ -258,10 +278,13 @@ def cpu_inputs_numpy(args, tmp, scn, n_rays, n_queries, threads):
         ph[filled:filled + c, 24:27] = rng.integers(1, 256, (c, 3)); ph[filled:filled + c, 27] = 120
         ph[filled:filled + c, 28:30] = rng.integers(0, 256, (c, 2))
         filled += c
-    return rays, ph.reshape(-1), q
+    return rays, ph.reshape(-1), q, hit_fraction
 
 
 def run_reference(args):
+    """The reference's own CPU code on the box's host cores: R3Scene::Intersects, EstimateRadiance and the R3Kdtree build,
+    each timed on a bounded sample; `value` = the step's unit counts (all primary rays, a gather at every hit, one map
+    build) at those measured rates -- the same mix the GPU arm times, not the sample's."""
     rank = int(os.environ.get("RANK", "0"))
     if rank != 0:
         return
@@ -270,31 +293,25 @@ def run_reference(args):
         return
     threads = os.cpu_count() or 1
     with tempfile.TemporaryDirectory() as tmp:
-        scn = export_scene_scn(tmp)
-        rays, ph, q = cpu_inputs_numpy(args, tmp, scn, args.cpu_rays, args.cpu_queries, threads)
-        r = ref_bench(tmp, scn, rays, ph, q, args.steps, args.warmup, threads)
-    sec = r["isect_seconds_per_step"] + r["gather_seconds_per_step"]
-    units = len(rays) + len(q)
-    val = units / sec / 1e6
-    sample = (f"{len(rays)} camera rays + {len(q)} gathers (k={K}, r={R}) per step, a uniform sample of the "
-              f"{args.width}x{args.height} aa {args.aa} frame; {args.photons}-photon map; kd-tree build "
-              f"({r['kd_build_seconds']:.1f} s, single-threaded) not timed")
-    line = {"impl": "reference", "metric": "Mrays/s (closest-hit rays + photon kNN gather samples, reference accounting)",
-            "value": val, "unit": "Mrays/s", "n_gpus": args.gpus, "steps": args.steps, "warmup": args.warmup,
-            "ms_per_step": sec * 1e3, "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "f64",
-            "data": "synthetic", "config": config_dict(args),
-            "mrays_per_s_intersect": len(rays) / r["isect_seconds_per_step"] / 1e6,
-            "gathers_per_s": len(q) / r["gather_seconds_per_step"],
+        rays, ph, q, hit_fraction = reference_inputs(args, tmp, STOCK_SCN, args.cpu_rays, args.cpu_queries, threads)
+        r = ref_bench(tmp, STOCK_SCN, rays, ph, q, args.steps, args.warmup, threads)
+    n_rays = (args.width << args.aa) * (args.height << args.aa)
+    n_q = int(round(n_rays * hit_fraction))
+    isect_rate = len(rays) / r["isect_seconds_per_step"]; gather_rate = len(q) / r["gather_seconds_per_step"]
+    val = step_value(n_rays, n_q, isect_rate, gather_rate, r["kd_build_seconds"])
+    sec = (n_rays + n_q) / (val * 1e6)
+    sample = (f"timed per step: {len(rays)} camera rays ({args.width}x{args.height} aa {args.aa} frame sampled uniformly by ref_harness camrays) "
+              f"and {len(q)} gathers (k={K}, r={R}) at their hits, {args.photons}-photon map, stock input/{SCENE}.scn; "
+              f"R3Kdtree build {r['kd_build_seconds']:.1f} s (single-threaded, timed once); value = the full step "
+              f"({n_rays} rays + {n_q} gathers + 1 build) at these rates")
+    line = {"impl": "reference", "metric": METRIC, "value": val, "unit": "Mrays/s", "n_gpus": args.gpus, "steps": args.steps,
+            "warmup": args.warmup, "ms_per_step": sec * 1e3, "higher_is_better": True, "scaling": "weak", "vs_baseline": None,
+            "dtype": "f64", "data": "synthetic", "config": config_dict(args),
+            "mrays_per_s_intersect": isect_rate / 1e6, "gathers_per_s": gather_rate, "kd_build_ms": r["kd_build_seconds"] * 1e3,
+            "step_units": {"rays": n_rays, "gathers": n_q, "map_builds": 1},
             "cpu_baseline": {"value": val, "unit": "Mrays/s", "cores": threads, "kind": "reference", "sample": sample},
             "e2e": {"value": val, "unit": "Mrays/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0}}
     print(json.dumps(line))
-
-
-def config_dict(args):
-    return {"workload": f"input/{SCENE}.scn {args.width}x{args.height} -aa {args.aa}: closest hit for all "
-                        f"{(args.width << args.aa) * (args.height << args.aa)} primary rays + caustic-style photon gather "
-                        f"(k={K}, r={R}, disk filter) at every primary hit, {args.photons}-photon map on the scene surfaces",
-            "photons": args.photons, "k": K, "r": R, "l2": "inputs larger than L2 (0.8 GB rays, 2.3 GB queries per step)"}
 
 
 # ------------------------------------------------------------------------------------------- our arm (B200)
@@ -302,6 +319,7 @@ def run_ours(args):
     import torch
     import torch.distributed as dist
     import gi_b200
+    import multi_gpu
 
     rank = int(os.environ.get("RANK", "0")); world = int(os.environ.get("WORLD_SIZE", "1"))
     local_rank = int(os.environ.get("LOCAL_RANK", "0"))
@@ -313,47 +331,65 @@ def run_ours(args):
         dist.init_process_group("nccl", device_id=dev)
 
     ctx = gi_b200.Context(local_rank)
+    if world > 1:
+        multi_gpu.attach_communicator(ctx, dist, torch, dev)     # NCCL communicator of the C ABI (ncclUniqueId from rank 0)
     scene = gi_b200.HostScene(os.path.join(GOLDEN, SCENE + ".gisc"))
     ctx.upload_scene(scene)
     work_stream = torch.cuda.Stream(device=dev)          # a real (non-default) stream: kernels and events both go here
     torch.cuda.set_stream(work_stream)
     stream = work_stream.cuda_stream
-    W, H = args.width << args.aa, args.height << args.aa
-    n_rays = W * H
-    # weak scaling: every rank renders its own full frame (sub-pixel offset per rank so the inputs differ)
-    rays = camera_rays(torch, scene.view.camera, W, H, dev, jitter=0.01 * rank)
+    aaf = 1 << args.aa
+    W, H = args.width * aaf, args.height * aaf
+    # weak scaling: the frame is `world` times wider, rank r renders its pixel columns x = r (mod world)
+    px = torch.arange(args.width, device=dev) * world + rank
+    cols = (px[:, None] * aaf + torch.arange(aaf, device=dev)[None, :]).reshape(-1)
+    rays = camera_rays(torch, scene.view.camera, W * world, H, dev, cols)
+    n_rays = rays.shape[0]
     hits = torch.empty(n_rays * 72, dtype=torch.uint8, device=dev)
 
-    # ---- photon map: each rank lays down photons/world photons, one NCCL all-gather replicates the map
-    per_rank = args.photons // world
-    local_ph = make_photons(torch, ctx, scene, per_rank, 100 + rank, dev)
-    allgather_ms = 0.0
-    if world > 1:
-        full = torch.empty((per_rank * world, 32), dtype=torch.uint8, device=dev)
-        e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
-        dist.barrier(); torch.cuda.synchronize()
-        e0.record(); dist.all_gather_into_tensor(full, local_ph); e1.record(); torch.cuda.synchronize()
-        allgather_ms = e0.elapsed_time(e1)
-    else:
-        full = local_ph
-    n_ph = full.shape[0]
-    ctx.load_photons_device(gi_b200.GI_MAP_CAUSTIC, full.data_ptr(), n_ph)
-    torch.cuda.synchronize(); t0 = time.perf_counter()
-    ctx.build_maps()
-    torch.cuda.synchronize(); kd_build_ms = (time.perf_counter() - t0) * 1e3
+    # ---- photon shares: each rank lays down photons/world photons of the map
+    per_rank = args.photons // world + (1 if rank < args.photons % world else 0)
+    share = make_photons(torch, ctx, scene, per_rank, 100 + rank, dev)
+    params = gi_b200.default_params()
 
+    def replicate_and_build():
+        ctx.load_photons_sharded_device(gi_b200.GI_MAP_CAUSTIC, share.data_ptr(), per_rank)     # all-gather over NVLink (N > 1)
+        ctx.build_maps(params)
+
+    replicate_and_build()
     ctx.intersect_device(rays.data_ptr(), n_rays, hits.data_ptr(), stream)
     torch.cuda.synchronize()
-    queries = make_queries(torch, rays, hits)
+    queries, q_ray = make_queries(torch, rays, hits)
     n_q = queries.shape[0]
     rgb = torch.empty((n_q, 3), dtype=torch.float64, device=dev)
     cnt = torch.empty(n_q, dtype=torch.int32, device=dev)
-    params = gi_b200.default_params()
+    acc = torch.empty((n_rays, 3), dtype=torch.float64, device=dev)
+    strips = [torch.empty((args.width, args.height, 3), dtype=torch.uint8, device=dev) for _ in range(world)] if rank == 0 else None
 
-    def step():
+    def resolve_and_gather():
+        """render.cpp:205-221 on the rank's columns (torch glue): radiance per supersample -> clamp -> box filter -> u8
+        strip; strips to rank 0"""
+        acc.zero_(); acc.index_copy_(0, q_ray, rgb)
+        s = acc.clamp_(0.0, 1.0).view(args.width, aaf, args.height, aaf, 3).sum(dim=(1, 3)) * (1.0 / (aaf * aaf))
+        strip = (s * 255.0).to(torch.uint8)
+        if world > 1:
+            dist.gather(strip, strips, dst=0)
+        return strip
+
+    NEV = 6
+    def step(ev=None, s=0):
+        if ev: ev[NEV * s].record()
+        ctx.load_photons_sharded_device(gi_b200.GI_MAP_CAUSTIC, share.data_ptr(), per_rank)
+        if ev: ev[NEV * s + 1].record()
+        ctx.build_maps(params)
+        if ev: ev[NEV * s + 2].record()
         ctx.intersect_device(rays.data_ptr(), n_rays, hits.data_ptr(), stream)
+        if ev: ev[NEV * s + 3].record()
         ctx.gather_device(gi_b200.GI_MAP_CAUSTIC, queries.data_ptr(), n_q, K, R, FILTER, params, None, cnt.data_ptr(),
                           rgb.data_ptr(), stream)
+        if ev: ev[NEV * s + 4].record()
+        resolve_and_gather()
+        if ev: ev[NEV * s + 5].record()
 
     for _ in range(args.warmup):
         step()
@@ -363,27 +399,28 @@ def run_ours(args):
     sampler = ClockSampler(local_rank)
     if rank == 0:
         sampler.start()
-    ev = [torch.cuda.Event(enable_timing=True) for _ in range(2 * args.steps + 1)]
+    ev = [torch.cuda.Event(enable_timing=True) for _ in range(NEV * args.steps + 1)]
     launches0 = ctx.launch_count()
     torch.cuda.synchronize()
-    ev[0].record()
     for s in range(args.steps):
-        ctx.intersect_device(rays.data_ptr(), n_rays, hits.data_ptr(), stream)
-        ev[2 * s + 1].record()
-        ctx.gather_device(gi_b200.GI_MAP_CAUSTIC, queries.data_ptr(), n_q, K, R, FILTER, params, None, cnt.data_ptr(),
-                          rgb.data_ptr(), stream)
-        ev[2 * s + 2].record()
+        step(ev, s)
+    ev[-1].record()
     torch.cuda.synchronize()
     if world > 1:
         dist.barrier()
     clocks = sampler.stop() if rank == 0 else None
     launches = ctx.launch_count() - launches0
     total_ms = ev[0].elapsed_time(ev[-1])
-    isect_ms = sum(ev[2 * s].elapsed_time(ev[2 * s + 1]) for s in range(args.steps)) / args.steps
-    gather_ms = sum(ev[2 * s + 1].elapsed_time(ev[2 * s + 2]) for s in range(args.steps)) / args.steps
+
+    def stage(i):
+        return sum(ev[NEV * s + i].elapsed_time(ev[NEV * s + i + 1] if i < NEV - 1 else (ev[NEV * (s + 1)] if s + 1 < args.steps else ev[-1]))
+                   for s in range(args.steps)) / args.steps
+    replicate_ms, build_ms, isect_ms, gather_ms, resolve_ms = (stage(i) for i in range(5))
     found_full = int((cnt == K).sum().item())
 
     # ---- end to end through the host-buffer C ABI: pinned host inputs, H2D + kernels + D2H inside the timed region
+    share_h = torch.empty((per_rank, 32), dtype=torch.uint8, pin_memory=True); share_h.copy_(share)
+    share_d = torch.empty_like(share)
     rays_h = torch.empty((n_rays, 6), dtype=torch.float64, pin_memory=True); rays_h.copy_(rays)
     q_h = torch.empty((n_q, 17), dtype=torch.float64, pin_memory=True); q_h.copy_(queries)
     hits_h = torch.empty(n_rays * 72, dtype=torch.uint8, pin_memory=True)
@@ -392,6 +429,12 @@ def run_ours(args):
     L = gi_b200.lib()
 
     def e2e_step():
+        if world > 1:
+            share_d.copy_(share_h, non_blocking=True); torch.cuda.current_stream().synchronize()
+            ctx.load_photons_sharded_device(gi_b200.GI_MAP_CAUSTIC, share_d.data_ptr(), per_rank)
+        else:
+            gi_b200._check(L.gi_load_photons(ctx.handle, gi_b200.GI_MAP_CAUSTIC, share_h.data_ptr(), per_rank))
+        ctx.build_maps(params)
         gi_b200._check(L.gi_intersect_batch(ctx.handle, rays_h.data_ptr(), n_rays, hits_h.data_ptr()))
         gi_b200._check(L.gi_gather_batch(ctx.handle, gi_b200.GI_MAP_CAUSTIC, q_h.data_ptr(), n_q, K, R, FILTER,
                                          ctypes.byref(params), None, cnt_h.data_ptr(), rgb_h.data_ptr()))
@@ -405,127 +448,231 @@ def run_ours(args):
         e2e_step()
     torch.cuda.synchronize()
     e2e_s = (time.perf_counter() - t0) / e2e_steps
+    del share_h, share_d, rays_h, q_h, hits_h, rgb_h, cnt_h
 
     # ---- max over ranks
-    t = torch.tensor([total_ms, isect_ms, gather_ms, e2e_s * 1e3], dtype=torch.float64, device=dev)
+    t = torch.tensor([total_ms, replicate_ms, build_ms, isect_ms, gather_ms, resolve_ms, e2e_s * 1e3], dtype=torch.float64, device=dev)
     units = torch.tensor([float(n_rays), float(n_q)], dtype=torch.float64, device=dev)
     if world > 1:
         dist.all_reduce(t, op=dist.ReduceOp.MAX)
         dist.all_reduce(units, op=dist.ReduceOp.SUM)
-    total_ms, isect_ms, gather_ms, e2e_ms = t.tolist()
+    total_ms, replicate_ms, build_ms, isect_ms, gather_ms, resolve_ms, e2e_ms = t.tolist()
     rays_all, q_all = units.tolist()
     ms_per_step = total_ms / args.steps
 
-    frame = None
-    if not args.no_frame:
-        del rays_h, q_h, hits_h, rgb_h, cnt_h
-        frame = frame_report(args, torch, dist, ctx, dev, rank, world)
+    extras = {}
+    if not args.no_extras:
+        extras = extra_sections(args, torch, ctx, scene, dev, rank, queries, stream, clocks)
+    frames = None
+    if args.frames != "none":
+        del acc, rgb, cnt, hits, rays, queries
+        torch.cuda.empty_cache()
+        frames = frame_reports(args, torch, dist, ctx, dev, rank, world)
 
     if rank == 0:
         peak, peak_src = load_peaks()
         achieved = (n_q * GATHER_ALGO_BYTES) / (gather_ms * 1e-3) / 1e9
-        line = {"metric": "Mrays/s (closest-hit rays + photon kNN gather samples, reference accounting)",
-                "value": (rays_all + q_all) / (ms_per_step * 1e-3) / 1e6, "unit": "Mrays/s", "n_gpus": world,
+        line = {"metric": METRIC, "value": (rays_all + q_all) / (ms_per_step * 1e-3) / 1e6, "unit": "Mrays/s", "n_gpus": world,
                 "steps": args.steps, "warmup": args.warmup, "ms_per_step": ms_per_step, "higher_is_better": True,
-                "scaling": "weak", "vs_baseline": None, "dtype": "f64", "data": "synthetic", "config": config_dict(args),
+                "scaling": "weak", "vs_baseline": None, "dtype": "f64", "data": "synthetic", "config": config_dict(args, world),
+                "step_units": {"rays": int(rays_all), "gathers": int(q_all), "map_builds": 1},
                 "mrays_per_s_intersect": rays_all / (isect_ms * 1e-3) / 1e6, "gathers_per_s": q_all / (gather_ms * 1e-3),
-                "intersect_ms": isect_ms, "gather_ms": gather_ms, "kd_build_ms": kd_build_ms, "photon_allgather_ms": allgather_ms,
-                "photons_in_map": n_ph, "queries_with_k_photons": found_full,
+                "stage_ms": {"photon_replicate": replicate_ms, "kd_build": build_ms, "intersect": isect_ms, "gather": gather_ms,
+                             "resolve_glue_and_strip_gather": resolve_ms},
+                "value_render_stages_only": (rays_all + q_all) / ((isect_ms + gather_ms) * 1e-3) / 1e6,
+                "intersect_ms": isect_ms, "gather_ms": gather_ms, "kd_build_ms": build_ms, "photon_allgather_ms": replicate_ms,
+                "photons_in_map": args.photons, "queries_with_k_photons": found_full,
                 "roofline": {"kernel": "gather_kernel", "bound": "hbm", "achieved": achieved, "peak": peak, "unit": "GB/s",
                              "frac": achieved / peak, "traffic": None, "peak_source": peak_src,
                              "algorithmic_bytes_per_gather": GATHER_ALGO_BYTES,
                              "intersect_kernel_GBps": (n_rays * RAY_ALGO_BYTES) / (isect_ms * 1e-3) / 1e9},
                 "e2e": {"value": (rays_all + q_all) / (e2e_ms * 1e-3) / 1e6, "unit": "Mrays/s",
-                        "h2d_bytes_per_step": n_rays * 48 + n_q * 136, "d2h_bytes_per_step": n_rays * 72 + n_q * 28,
-                        "ms_per_step": e2e_ms},
-                "gpu_launches": int(launches), "clocks": clocks, "frame": frame}
+                        "h2d_bytes_per_step": per_rank * 32 + n_rays * 48 + n_q * 136, "d2h_bytes_per_step": n_rays * 72 + n_q * 28,
+                        "ms_per_step": e2e_ms,
+                        "note": "per rank: photon share, rays and queries from pinned host memory, hits / counts / radiance back to "
+                                "host memory; the strip gather to rank 0 is not repeated here"},
+                "gpu_launches": int(launches), "torch_glue_launches_per_step": "index_copy, clamp, sum, mul, cast (+ NCCL gather)",
+                "clocks": clocks, "frames": frames}
+        line.update(extras)
         traffic_file = os.path.join(ROOT, "profiles", "gather_traffic.json")
         if os.path.exists(traffic_file):       # ncu capture at a smaller launch: DRAM bytes per gather x this launch's gathers
             tf = json.load(open(traffic_file))
             line["roofline"]["traffic"] = tf["dram_bytes_per_launch"] / tf["queries_per_launch"] * n_q
             line["roofline"]["traffic_note"] = "ncu dram bytes per gather (%s) scaled to this launch" % tf["source"]
         if world == 1 and not args.no_cpu_baseline:
-            line["cpu_baseline"] = cpu_baseline(args, torch, rays, full, queries)
+            line["cpu_baseline"] = cpu_baseline(args, n_rays, n_q)
         print(json.dumps(line))
     if world > 1:
         dist.barrier()
         dist.destroy_process_group()
 
 
-def frame_report(args, torch, dist, ctx, dev, rank, world):
-    """Whole-program frame outside the timed steps: BASELINE.json configs[0] (cornell 512 x 512 -aa 1, every flag at its
-    default: 2176 global + 10^7 caustic photons, k 50 / 225, lt/ss/tt/st 128, it 256) -- MapPhotons + RenderImage
-    through gi_trace_photons / gi_render, sharded over the ranks when N > 1 (photons per rank + one all-gather, pixel
-    columns per rank + one reduce).  Times are wall clock around synchronised calls, max over ranks."""
+def extra_sections(args, torch, ctx, scene, dev, rank, queries, stream, clocks):
+    """Two more regimes of the hot path, each with its own roofline entry (rank 0 only; no collectives):
+    gathers_small_map  k = 50, r = the default global estimate distance, on a 2176-photon map -- the global-map gathers that
+                       make up 97 % of a default frame's gathers (bound: instruction issue, the map lives in L1);
+    intersect_mesh     closest hit on violin.scn (104 300 triangles, the one mesh that stresses the BVH): camera rays
+                       (coherent) and uniformly random rays (incoherent)."""
     import gi_b200
-    import multi_gpu
-    scene = gi_b200.HostScene(os.path.join(GOLDEN, args.frame_scene + ".gisc"))
+    from gi_testlib import golden_gisc
+    if rank != 0:
+        return {}
+    out = {}
+    params = gi_b200.default_params()
+    sm_mhz = (clocks or {}).get("sm_mhz") or 1965.0
+    issue_peak = 148 * 4 * sm_mhz * 1e6 / 1e9          # G warp-instructions/s: 4 schedulers per SM, one issue per cycle
+    # ---- small map
+    small = make_photons(torch, ctx, scene, 2176, 7, dev)
+    ctx.load_photons_device(gi_b200.GI_MAP_GLOBAL, small.data_ptr(), 2176)
+    ctx.build_maps(params)
+    nq = min(queries.shape[0], 1 << 23)
+    rgb = torch.empty((nq, 3), dtype=torch.float64, device=dev)
+    k, r = int(params.global_estimate_size), float(params.global_estimate_dist)
+    e = [torch.cuda.Event(enable_timing=True) for _ in range(2)]
+    for it in range(4):
+        if it == 1: e[0].record()
+        ctx.gather_device(gi_b200.GI_MAP_GLOBAL, queries.data_ptr(), nq, k, r, int(params.global_filter), params, None, None, rgb.data_ptr(), stream)
+    e[1].record(); torch.cuda.synchronize()
+    ms = e[0].elapsed_time(e[1]) / 3
+    rate = nq / (ms * 1e-3)
+    ipg = None
+    f = os.path.join(ROOT, "profiles", "gather_small_map.json")
+    if os.path.exists(f):
+        ipg = json.load(open(f)).get("warp_instructions_per_gather")
+    out["gathers_small_map"] = {"photons": 2176, "k": k, "r": r, "queries": nq, "ms": ms, "gathers_per_s": rate,
+                                "roofline": {"kernel": "gather_kernel", "bound": "issue", "achieved": rate * ipg / 1e9 if ipg else None,
+                                             "peak": issue_peak, "unit": "Gwarp-instr/s", "frac": rate * ipg / 1e9 / issue_peak if ipg else None,
+                                             "warp_instructions_per_gather": ipg, "source": "profiles/gather_small_map.json (ncu)"}}
+    ctx.load_photons_device(gi_b200.GI_MAP_GLOBAL, small.data_ptr(), 0)
+    del rgb
+    # ---- mesh
+    try:
+        vs = gi_b200.HostScene(golden_gisc("violin"))
+    except Exception as ex:      # the fixture is optional on a box without tests/golden
+        out["intersect_mesh"] = {"unavailable": str(ex)}
+        return out
+    ctx.upload_scene(vs)
+    side = 2048
+    cam = camera_rays(torch, vs.view.camera, side, side, dev)
+    n = cam.shape[0]
+    g = torch.Generator(device=dev); g.manual_seed(11)
+    lo = torch.tensor(list(vs.view.bbox_min), dtype=torch.float64, device=dev); hi = torch.tensor(list(vs.view.bbox_max), dtype=torch.float64, device=dev)
+    o = lo + torch.rand((n, 3), generator=g, dtype=torch.float64, device=dev) * (hi - lo)
+    d = torch.randn((n, 3), generator=g, dtype=torch.float64, device=dev); d = d / torch.sqrt((d * d).sum(1))[:, None]
+    rnd = torch.cat([o, d], dim=1).contiguous()
+    hits = torch.empty(n * 72, dtype=torch.uint8, device=dev)
+    res = {}
+    for name, rr in (("camera", cam), ("random", rnd)):
+        for it in range(4):
+            if it == 1: e[0].record()
+            ctx.intersect_device(rr.data_ptr(), n, hits.data_ptr(), stream)
+        e[1].record(); torch.cuda.synchronize()
+        ms = e[0].elapsed_time(e[1]) / 3
+        hit, _ = hits_fields(torch, hits)
+        res[name] = {"rays": n, "ms": ms, "mrays_per_s": n / (ms * 1e-3) / 1e6, "hit_fraction": float((hit == 1).double().mean().item()),
+                     "GBps_algorithmic": n * RAY_ALGO_BYTES / (ms * 1e-3) / 1e9}
+    peak, _ = load_peaks()
+    out["intersect_mesh"] = {"scene": "violin.scn (104300 triangles)", "resolution": f"{side}x{side}", **res,
+                             "roofline": {"kernel": "intersect_kernel", "bound": "hbm", "achieved": res["random"]["GBps_algorithmic"], "peak": peak,
+                                          "unit": "GB/s", "frac": res["random"]["GBps_algorithmic"] / peak,
+                                          "note": "latency / FP64-issue bound (incoherent BVH walks), far from the HBM roofline; reported per SURVEY 8(d)"}}
     ctx.upload_scene(scene)
-    W = H = args.frame_res
-    split = None
-    for attempt in range(2):        # the first pass pays one-time costs (workspace allocation, NCCL channel set-up); report the second
-        params, _ = gi_b200.parse_flags(["-seed", "1"])
+    return out
+
+
+FRAME_CONFIGS = {      # BASELINE.json configs as whole-program frames: (scene, width, height, aa, extra flags)
+    "cornell_512_aa1": ("cornell", 512, 512, 1, []),
+    "cornell_1024_aa2": ("cornell", 1024, 1024, 2, []),
+    "jensen_1024_aa2": ("jensen", 1024, 1024, 2, []),
+    "teapot_1024": ("teapot", 1024, 1024, 0, []),
+    "stilllife_2048": ("stilllife", 2048, 2048, 0, []),
+    "violin_2048": ("violin", 2048, 2048, 0, []),
+    "distributed_lit_4096_aa2_10x_photons": ("distributed_lit", 4096, 4096, 2, ["-caustic", "100000000"]),
+}
+
+
+def frame_reports(args, torch, dist, ctx, dev, rank, world):
+    names = {"small": ["cornell_512_aa1"], "default": ["cornell_512_aa1", "cornell_1024_aa2"],
+             "all": list(FRAME_CONFIGS)}[args.frames]
+    out = {}
+    for i, name in enumerate(names):
+        # the first frame of the process pays one-time costs (workspace allocation, NCCL channel set-up): it is run twice
+        # and the second pass is reported; the later frames run once
+        out[name] = one_frame(name, 2 if i == 0 else 1, torch, dist, ctx, dev, rank, world)
+    return out
+
+
+def one_frame(name, passes, torch, dist, ctx, dev, rank, world):
+    """MapPhotons + RenderImage through gi_trace_photons / gi_render with every flag at its default (2176 global + 10^7
+    caustic photons, k 50 / 225, lt/ss/tt/st 128, it 256), sharded over the ranks by the library (photon rounds per rank +
+    all-gather, pixel columns per rank + strips to rank 0).  Wall clock around synchronised calls and per-stage device
+    times (gi_stage_times), max over ranks."""
+    import gi_b200
+    from gi_testlib import golden_gisc
+    sname, W, H, aa, flags = FRAME_CONFIGS[name]
+    scene = gi_b200.HostScene(golden_gisc(sname))
+    ctx.upload_scene(scene)
+    ctx.stage_timing(True)
+    pass_ms = []
+    for attempt in range(passes):
+        params, _ = gi_b200.parse_flags(["-seed", "1"] + flags)
         torch.cuda.synchronize()
         if world > 1:
             dist.barrier()
         t0 = time.perf_counter()
-        if world > 1:
-            totals = multi_gpu.trace_photons_sharded(ctx, params, dist, torch, dev)
-            stored = (totals["global_stored"], totals["caustic_stored"])
-        else:
-            st = ctx.trace_photons(params)
-            params.indirect_illum, params.caustic_illum, params.direct_photon_illum = st.indirect_illum, st.caustic_illum, st.direct_photon_illum
-            stored = (int(st.global_stored), int(st.caustic_stored))
-            split = {"trace_ms": float(st.trace_ms), "kd_build_ms": float(st.build_ms)}
+        st = ctx.trace_photons(params)
+        params.indirect_illum, params.caustic_illum, params.direct_photon_illum = st.indirect_illum, st.caustic_illum, st.direct_photon_illum
         torch.cuda.synchronize(); t1 = time.perf_counter()
-        if world > 1:
-            img, rs = multi_gpu.render_sharded(ctx, params, W, H, args.frame_aa, dist, torch, dev)
-        else:
-            img, rs = ctx.render(params, W, H, args.frame_aa)
+        img, rs = ctx.render(params, W, H, aa, want_image=(rank == 0))
         torch.cuda.synchronize(); t2 = time.perf_counter()
-    names = ["screen_rays", "shadow_rays", "monte_rays", "transmissive_samples", "specular_samples", "indirect_samples", "caustic_samples"]
-    c = torch.tensor([float(getattr(rs, n)) for n in names], dtype=torch.float64, device=dev)
-    t = torch.tensor([(t1 - t0) * 1e3, (t2 - t1) * 1e3, rs.render_ms], dtype=torch.float64, device=dev)
+        pass_ms.append([(t1 - t0) * 1e3, (t2 - t1) * 1e3])
+    stages = ctx.stage_times()
+    ctx.stage_timing(False)
+    cnames = ["screen_rays", "shadow_rays", "monte_rays", "transmissive_samples", "specular_samples", "indirect_samples", "caustic_samples"]
+    counters = {n: int(getattr(rs, n)) for n in cnames}           # already summed over the ranks by gi_render
+    snames = sorted(stages)
+    t = torch.tensor([(t1 - t0) * 1e3, (t2 - t1) * 1e3, rs.render_ms] + [stages[n] for n in snames], dtype=torch.float64, device=dev)
     if world > 1:
-        dist.all_reduce(c, op=dist.ReduceOp.SUM); dist.all_reduce(t, op=dist.ReduceOp.MAX)
-    counters = dict(zip(names, [int(x) for x in c.tolist()]))
-    photon_ms, render_ms, render_kernel_ms = t.tolist()
+        dist.all_reduce(t, op=dist.ReduceOp.MAX)
+    tl = t.tolist()
+    photon_ms, render_ms, render_dev_ms = tl[:3]
     total = sum(counters.values())
-    return {"workload": f"input/{args.frame_scene}.scn {W}x{H} -aa {args.frame_aa}, all flags default (BASELINE.json configs[0]): "
-                        "gi_trace_photons + gi_render, u8 frame back on the host",
-            "photon_pass_ms": photon_ms, "photon_pass_split": split, "render_ms": render_ms, "frame_ms": photon_ms + render_ms, "render_device_ms": render_kernel_ms,
-            "photons_stored": {"global": stored[0], "caustic": stored[1]}, "ray_ops": total, "counters": counters,
+    return {"workload": f"input/{sname}.scn {W}x{H} -aa {aa} {' '.join(flags)} (all other flags default): gi_trace_photons + gi_render, u8 frame on rank 0's host",
+            "ranks": world, "frame_ms": photon_ms + render_ms, "photon_pass_ms": photon_ms, "render_ms": render_ms, "render_device_ms": render_dev_ms,
+            "stage_ms_max_over_ranks": dict(zip(snames, tl[3:])),
+            "photons_stored": {"global": int(st.global_stored), "caustic": int(st.caustic_stored)}, "ray_ops": total, "counters": counters,
             "mray_ops_per_s": total / (render_ms * 1e-3) / 1e6,
             "gathers_per_s": (counters["indirect_samples"] + counters["caustic_samples"]) / (render_ms * 1e-3),
-            "image_mean": float(img.mean()) if img is not None else None, "timing": "wall clock of the second of two passes, max over ranks; not part of the timed steps"}
+            "image_mean": float(img.mean()) if img is not None else None, "passes_ms_this_rank": pass_ms,
+            "timing": "wall clock around synchronised calls, max over ranks (%s pass); stage times are CUDA events inside the library" % ("second" if passes > 1 else "single")}
 
 
-def cpu_baseline(args, torch, rays, photons, queries):
-    """the reference's own code (oracle/_ref, R3Scene::Intersects + EstimateRadiance) on all host cores, on a bounded
-    uniform sample of the same step; falls back to the oracle restatement where the reference was not built"""
+def cpu_baseline(args, n_rays, n_q):
+    """the reference's own code (oracle/_ref: R3Scene::Intersects, EstimateRadiance, R3Kdtree build) on all host cores, on a
+    bounded sample of the same step (inputs made by the reference alone, stock scene file); value = the step's unit counts
+    at the measured per-stage rates.  Falls back to the oracle restatement where the reference was not built."""
     threads = os.cpu_count() or 1
-    g = torch.Generator(device="cpu"); g.manual_seed(3)
-    ri = torch.randperm(rays.shape[0], generator=g)[: args.cpu_rays].to(rays.device)
-    qi = torch.randperm(queries.shape[0], generator=g)[: args.cpu_queries].to(rays.device)
-    r = rays[ri].cpu().numpy(); q = queries[qi].cpu().numpy(); ph = photons.reshape(-1).cpu().numpy()
-    sample = (f"{len(r)} camera rays + {len(q)} gathers (k={K}, r={R}), uniform sample of the step; same "
-              f"{len(ph) // 32}-photon map; kd-tree build not timed")
     with tempfile.TemporaryDirectory() as tmp:
         if os.path.exists(REF_HARNESS):
-            res = ref_bench(tmp, export_scene_scn(tmp), r, ph, q, 1, 0, threads)
-            sec = res["isect_seconds_per_step"] + res["gather_seconds_per_step"]
-            return {"value": (len(r) + len(q)) / sec / 1e6, "unit": "Mrays/s", "cores": threads, "kind": "reference",
-                    "sample": sample, "mrays_per_s_intersect": len(r) / res["isect_seconds_per_step"] / 1e6,
-                    "gathers_per_s": len(q) / res["gather_seconds_per_step"], "kd_build_seconds": res["kd_build_seconds"]}
-    from gi_testlib import Oracle, GI_PHOTON, GI_QUERY
+            rays, ph, q, _ = reference_inputs(args, tmp, STOCK_SCN, args.cpu_rays, args.cpu_queries, threads)
+            res = ref_bench(tmp, STOCK_SCN, rays, ph, q, 1, 0, threads)
+            ri = len(rays) / res["isect_seconds_per_step"]; rg = len(q) / res["gather_seconds_per_step"]
+            sample = (f"timed: {len(rays)} camera rays + {len(q)} gathers (k={K}, r={R}), uniform sample of the frame, and one R3Kdtree build of the "
+                      f"{args.photons}-photon map ({res['kd_build_seconds']:.1f} s, single-threaded); value = the step's {n_rays} rays + {n_q} gathers + "
+                      f"1 build at these rates")
+            return {"value": step_value(n_rays, n_q, ri, rg, res["kd_build_seconds"]), "unit": "Mrays/s", "cores": threads, "kind": "reference",
+                    "sample": sample, "mrays_per_s_intersect": ri / 1e6, "gathers_per_s": rg, "kd_build_seconds": res["kd_build_seconds"]}
+    from gi_testlib import Oracle, GI_PHOTON, GI_QUERY, random_rays, synthetic_photons
     o = Oracle()
     h = o.load_scene(os.path.join(GOLDEN, SCENE + ".gisc"))
-    q = q[:2000]
+    r = random_rays(args.cpu_rays, (-1, -1, -3), (6.5, 6.5, 6.5), 3)
+    ph = synthetic_photons(200000, 5, lo=(0, 0, -2), hi=(5.5, 5.5, 5.6))
+    qq = np.zeros(2000, dtype=GI_QUERY); qq["p"] = ph["position"][:2000]; qq["n"] = (0, 1, 0); qq["kd"] = 0.5
     t0 = time.perf_counter(); o.intersect(h, r, threads=threads); t1 = time.perf_counter()
-    qq = np.zeros(len(q), dtype=GI_QUERY); qq.view(np.float64).reshape(-1, 17)[:] = q
     o.gather(ph.view(GI_PHOTON), qq, K, R, FILTER, threads=threads, want_idx=False); t2 = time.perf_counter()
-    return {"value": (len(r) + len(q)) / (t2 - t0) / 1e6, "unit": "Mrays/s", "cores": threads, "kind": "port",
-            "sample": sample + " (brute-force oracle gather, 2000 queries)"}
+    ri = len(r) / (t1 - t0); rg = len(qq) / (t2 - t1)
+    return {"value": step_value(n_rays, n_q, ri, rg, 0.0), "unit": "Mrays/s", "cores": threads, "kind": "port",
+            "sample": f"{len(r)} random rays + 2000 brute-force oracle gathers on a 200000-photon map; no tree build in the port"}
 
 
 def main():

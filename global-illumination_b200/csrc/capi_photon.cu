@@ -11,6 +11,7 @@
 #include <cstring>
 #include <cstdlib>
 #include <vector>
+#include "comm.h"
 #include "context.h"
 #include "gather.h"
 #include "gi_math.cuh"
@@ -22,11 +23,26 @@ namespace gi {
 static const uint32_t PMAP_MAGIC = 0x4d504947u;   // "GIPM"
 static const uint32_t PMAP_VERSION = 1u;
 
+// Every array of a map comes from the device's stream-ordered pool (cudaMallocAsync on the context's stream; gi_create
+// keeps freed pool memory): a frame -- and a bench step -- loads and rebuilds its maps every time, and cudaFree +
+// cudaMalloc of the 1.7 GB a 10^7-photon map holds cost 20 ms, half as much again as the kd-tree build itself.
+// The device is synchronised first, like cudaFree does implicitly: a gather launched on a caller's stream may still read
+// the arrays.
 void free_map(PhotonMapStore &m) {
-  cudaFree((void *)m.dev.px); cudaFree((void *)m.dev.py); cudaFree((void *)m.dev.pz);
-  cudaFree((void *)m.dev.node); cudaFree((void *)m.dev.shade); cudaFree((void *)m.dev.orig); cudaFree((void *)m.dev.cbox); cudaFree((void *)m.dev.gpos); cudaFree((void *)m.dev.srec); cudaFree((void *)m.dev.hint);
-  cudaFree(m.raw);
+  void *ptrs[] = {(void *)m.dev.px, (void *)m.dev.py, (void *)m.dev.pz, (void *)m.dev.node, (void *)m.dev.shade, (void *)m.dev.orig,
+                  (void *)m.dev.cbox, (void *)m.dev.gpos, (void *)m.dev.srec, (void *)m.dev.hint, m.raw};
+  bool any = false;
+  for (void *p : ptrs) any = any || p;
+  if (any) {
+    cudaDeviceSynchronize();
+    for (void *p : ptrs) if (p) cudaFreeAsync(p, (cudaStream_t)m.stream);
+  }
   m = PhotonMapStore();
+}
+
+bool alloc_raw(GiContext *ctx, PhotonMapStore &m, uint64_t n) {
+  m.stream = (void *)ctx->stream;
+  return cuda_ok(cudaMallocAsync(&m.raw, sizeof(GiPhoton) * (n ? n : 1), ctx->stream), "cudaMallocAsync(photons)");
 }
 
 // BuildDirectionLookupTable (src/utils/photon_utils.cpp:253-272), built on the host with the same libm calls and
@@ -66,7 +82,7 @@ int gi_load_photons(GiContext *ctx, int map, const GiPhoton *photons, uint64_t n
   free_map(m);
   m.dev.n = n;
   if (n == 0) return 0;
-  GI_CUDA(cudaMalloc(&m.raw, sizeof(GiPhoton) * n));
+  if (!alloc_raw(ctx, m, n)) return 1;
   GI_CUDA(cudaMemcpyAsync(m.raw, photons, sizeof(GiPhoton) * n, cudaMemcpyHostToDevice, ctx->stream));
   GI_CUDA(cudaStreamSynchronize(ctx->stream));
   return 0;
@@ -81,10 +97,45 @@ int gi_load_photons_device(GiContext *ctx, int map, const GiPhoton *d_photons, u
   free_map(m);
   m.dev.n = n;
   if (n == 0) return 0;
-  GI_CUDA(cudaMalloc(&m.raw, sizeof(GiPhoton) * n));
+  if (!alloc_raw(ctx, m, n)) return 1;
   GI_CUDA(cudaMemcpyAsync(m.raw, d_photons, sizeof(GiPhoton) * n, cudaMemcpyDeviceToDevice, ctx->stream));
   GI_CUDA(cudaStreamSynchronize(ctx->stream));
   return 0;
+}
+
+// Multi-GPU load: every rank of the context's communicator passes ITS share of the photons (device memory); the shares
+// are concatenated in rank order on every rank by one ragged all-gather over NVLink straight into the map's photon array
+// (no padding, no staging copy).  Without a communicator this is gi_load_photons_device.
+int gi_load_photons_sharded_device(GiContext *ctx, int map, const GiPhoton *d_share, uint64_t n_share) {
+  if (!ctx || map < 0 || map > 1) { set_error("gi_load_photons_sharded_device: bad argument"); return 1; }
+  if (n_share > 0 && !d_share) { set_error("gi_load_photons_sharded_device: null photon buffer"); return 1; }
+  const int world = comm_world(ctx);
+  if (world <= 1) return gi_load_photons_device(ctx, map, d_share, n_share);
+  GI_CUDA(cudaSetDevice(ctx->device));
+  cudaStream_t st = ctx->stream;
+  PhotonMapStore &m = ctx->maps[map];
+  free_map(m);
+  uint64_t *d_counts = nullptr;                           // [world] gathered + [1] mine
+  GI_CUDA(cudaMallocAsync((void **)&d_counts, 8 * (size_t)(world + 1), st));
+  int rc = 1;
+  do {
+    std::vector<uint64_t> h(world, 0), bytes_of(world), off(world);
+    if (!cuda_ok(cudaMemcpyAsync(d_counts + world, &n_share, 8, cudaMemcpyHostToDevice, st), "H2D share size")) break;
+    if (!comm_allgather_u64(ctx, d_counts + world, d_counts, 1, st)) break;
+    if (!cuda_ok(cudaMemcpyAsync(h.data(), d_counts, 8 * (size_t)world, cudaMemcpyDeviceToHost, st), "D2H share sizes")) break;
+    if (!cuda_ok(cudaStreamSynchronize(st), "share sizes sync")) break;
+    uint64_t total = 0;
+    for (int r = 0; r < world; r++) { off[r] = sizeof(GiPhoton) * total; bytes_of[r] = sizeof(GiPhoton) * h[r]; total += h[r]; }
+    if (total >= ((uint64_t)1 << 31)) { set_error("gi_load_photons_sharded_device: at most 2^31 - 1 photons per map"); break; }
+    m.dev.n = total;
+    if (total == 0) { rc = 0; break; }
+    if (!alloc_raw(ctx, m, total)) { m.dev.n = 0; break; }
+    if (!comm_allgatherv(ctx, d_share, m.raw, bytes_of.data(), off.data(), st)) break;
+    if (!cuda_ok(cudaStreamSynchronize(st), "photon all-gather sync")) break;
+    rc = 0;
+  } while (0);
+  cudaFreeAsync(d_counts, st);
+  return rc;
 }
 
 int gi_photon_count(GiContext *ctx, int map, uint64_t *n_out) {

@@ -114,6 +114,7 @@ void gi_destroy(GiContext *ctx) {
     if (ctx->pipe[i]) cudaStreamDestroy(ctx->pipe[i]);
   }
   for (int j = 0; j < 5; j++) ctx->order_ws[2][j].release();
+  ctx->clock.release();
   cudaFree(ctx->gather_counters);
   cudaFree(ctx->d_lut);
   if (ctx->stream) cudaStreamDestroy(ctx->stream);
@@ -237,6 +238,24 @@ int gi_intersect_batch(GiContext *ctx, const GiRay *rays, uint64_t n, GiHit *hit
 int gi_launch_count(GiContext *ctx, uint64_t *out) {
   if (!ctx || !out) { set_error("gi_launch_count: null argument"); return 1; }
   *out = ctx->launches;
+  return 0;
+}
+
+int gi_stage_timing(GiContext *ctx, int enable) {
+  if (!ctx) { set_error("gi_stage_timing: null argument"); return 1; }
+  ctx->clock.on = enable != 0;
+  return 0;
+}
+
+int gi_stage_times(GiContext *ctx, GiStageTimes *out) {
+  if (!ctx || !out) { set_error("gi_stage_times: null argument"); return 1; }
+  const double *m = ctx->clock.ms;
+  out->emit_filter_ms = m[ST_EMIT_FILTER]; out->trace_ms = m[ST_TRACE]; out->photon_exchange_ms = m[ST_PHOTON_EXCHANGE];
+  out->photon_sort_ms = m[ST_PHOTON_SORT]; out->kd_build_ms = m[ST_KD_BUILD];
+  out->primary_ms = m[ST_PRIMARY]; out->direct_ms = m[ST_DIRECT]; out->path_begin_ms = m[ST_PATH_BEGIN]; out->path_hit_ms = m[ST_PATH_HIT];
+  out->path_shade_ms = m[ST_PATH_SHADE]; out->path_finish_ms = m[ST_PATH_FINISH]; out->gather_global_ms = m[ST_GATHER_GLOBAL];
+  out->gather_caustic_ms = m[ST_GATHER_CAUSTIC]; out->commit_ms = m[ST_COMMIT]; out->resolve_ms = m[ST_RESOLVE];
+  out->frame_exchange_ms = m[ST_FRAME_EXCHANGE];
   return 0;
 }
 

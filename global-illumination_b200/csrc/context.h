@@ -8,6 +8,7 @@
 #include "gi_b200.h"
 #include "scene_dev.h"
 #include "photon_dev.h"
+#include "stage_clock.h"
 
 // grow-only device buffer used by the host-buffer entry points to stage chunks (freed by gi_destroy)
 struct GiScratch {
@@ -52,6 +53,7 @@ struct GiContext {
   void *render_ws = nullptr;                  // render.cu's device workspace, created by the first gi_render
   void (*render_ws_free)(void *) = nullptr;
   void *comm = nullptr;                       // comm.cu: NCCL communicator + rank / world of this context (nullptr = single GPU)
+  gi::StageClock clock;                        // per-stage device times (gi_stage_timing / gi_stage_times), off by default
   uint64_t queue_overflows = 0;               // render path batches repeated because a gather-request queue ran full
   uint64_t launches = 0;                      // kernels launched by this context (bench.py: gpu_launches)
 };
@@ -61,6 +63,7 @@ void set_error(const std::string &msg);
 bool cuda_ok(cudaError_t e, const char *what);
 void free_scene(GiContext *ctx);
 void free_map(PhotonMapStore &m);
+bool alloc_raw(GiContext *ctx, PhotonMapStore &m, uint64_t n);   // m.raw = GiPhoton[n] from the stream-ordered pool
 }  // namespace gi
 
 #define GI_CUDA(call) do { if (!gi::cuda_ok((call), #call)) return 1; } while (0)

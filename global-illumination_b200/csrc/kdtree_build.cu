@@ -262,8 +262,10 @@ cudaError_t build_photon_map(GiContext *ctx, PhotonMapStore &m, uint64_t n, cons
     ctx->launches += 6;
     CKB(cudaGetLastError());
   }
-  CKB(cudaMalloc(&px, 8 * n)); CKB(cudaMalloc(&py, 8 * n)); CKB(cudaMalloc(&pz, 8 * n));
-  CKB(cudaMalloc(&node, 8 * n)); CKB(cudaMalloc(&shade, 8 * n)); CKB(cudaMalloc(&orig, 4 * n)); CKB(cudaMalloc(&srec, 32 * n));
+  // the map's own arrays: from the same pool (freed by free_map with cudaFreeAsync on this stream)
+  m.stream = (void *)st;
+  CKB(cudaMallocAsync(&px, 8 * n, st)); CKB(cudaMallocAsync(&py, 8 * n, st)); CKB(cudaMallocAsync(&pz, 8 * n, st));
+  CKB(cudaMallocAsync(&node, 8 * n, st)); CKB(cudaMallocAsync(&shade, 8 * n, st)); CKB(cudaMallocAsync(&orig, 4 * n, st)); CKB(cudaMallocAsync(&srec, 32 * n, st));
   finalize_kernel<<<G, B, 0, st>>>(ph, n, heap_photon, split, axis, px, py, pz, node, shade, orig, d_lut, srec);
   ctx->launches++;
   CKB(cudaGetLastError());
@@ -283,12 +285,12 @@ cudaError_t build_photon_map(GiContext *ctx, PhotonMapStore &m, uint64_t n, cons
     n_groups += n - first < first + 1 ? n - first : first + 1;
   }
   n_upper = d.groups > 1 ? d.goff[d.groups - 1] : 0;                    // groups above the bottom row
-  CKB(cudaMalloc(&cbox, 1536 * (n_upper ? n_upper : 1)));
+  CKB(cudaMallocAsync(&cbox, 1536 * (n_upper ? n_upper : 1), st));
   d.x6_base = (uint32_t)n_groups;
   d.x6_blocks = d.hb > GI_GROUP_LEVELS ? (uint32_t)((n - ((((uint64_t)1 << (L - 1)) - 1)) + 31) / 32) : 0u;
-  CKB(cudaMalloc(&gpos, 768 * (n_groups + d.x6_blocks)));
+  CKB(cudaMallocAsync(&gpos, 768 * (n_groups + d.x6_blocks), st));
   d.cbox = cbox; d.gpos = gpos;
-  CKB(cudaMalloc(&hint, 2 * sizeof(double)));
+  CKB(cudaMallocAsync(&hint, 2 * sizeof(double), st));
   CKB(cudaMemsetAsync(hint, 0, 2 * sizeof(double), st));
   d.hint = hint;
   if (d.x6_blocks) { level6_kernel<<<(unsigned)(((uint64_t)d.x6_blocks * 32 + B - 1) / B), B, 0, st>>>(d, gpos); ctx->launches++; }
@@ -319,7 +321,7 @@ done:
     void *temps[] = {keys[0], keys[1], vals[0], vals[1], heap_photon, split, bounds, axis, tmp};
     for (void *t : temps) if (t) cudaFreeAsync(t, st);
   }
-  cudaFree(px); cudaFree(py); cudaFree(pz); cudaFree(node); cudaFree(shade); cudaFree(orig); cudaFree(cbox); cudaFree(gpos); cudaFree(srec); cudaFree(hint);
+  { void *own[] = {px, py, pz, node, shade, orig, cbox, gpos, srec, hint}; for (void *t : own) if (t) cudaFreeAsync(t, st); }      // only after a failure
   return err;
 }
 

@@ -51,6 +51,7 @@ struct PhotonMapDev {
 struct PhotonMapStore {
   PhotonMapDev dev{};             /* device pointers (owned) */
   void *raw = nullptr;            /* GiPhoton[n] in load order (device), kept for dump / get */
+  void *stream = nullptr;         /* the cudaStream_t whose stream-ordered pool every array of this map came from (free_map) */
   bool built = false;
   bool cached = false;             /* colours hold cached irradiance (-cache pre-pass, irradiance_cache.cu) */
   double cache_ms = 0;             /* wall time of that pre-pass */

@@ -328,19 +328,24 @@ static int trace_map(GiContext *ctx, const ShadeEnv &env_in, int map_type, int t
         GI_CUDA(cudaMemsetAsync(cursor.p, 0, 16, st));
         unsigned int *kept = (unsigned int *)(cursor.as<unsigned long long>() + 1);
         if (filter) {
+          ctx->clock.begin(ST_EMIT_FILTER, st);
           emit_filter_kernel<<<(unsigned)((m + 255) / 256), 256, 0, st>>>(env, rd, w0, (uint32_t)m, list.as<uint32_t>(), kept);
+          ctx->clock.end(st);
           ctx->launches++;
         }
+        ctx->clock.begin(ST_TRACE, st);
         // persistent: 8 CTAs of 4 warps per SM; with the filter the item count stays on the device (no host round trip)
         const uint64_t want = (m + 127) / 128, gcap = (uint64_t)ctx->sm_count * 8;
         trace_kernel<<<(unsigned)std::max<uint64_t>(1, std::min(want, gcap)), 128, 0, st>>>(
             env, rd, w0, m, filter ? kept : nullptr, filter ? list.as<uint32_t>() : nullptr, cursor.as<unsigned long long>(), sink);
+        ctx->clock.end(st);
         ctx->launches++;
         GI_CUDA(cudaGetLastError());
       }
       unsigned long long now = 0;
       GI_CUDA(cudaMemcpyAsync(&now, count.p, 8, cudaMemcpyDeviceToHost, st));
       GI_CUDA(cudaStreamSynchronize(st));
+      ctx->clock.collect();
       if (now <= cap) { stored_local = now; break; }
       // grow the sink, keep what earlier rounds stored, and run this round again (same streams -> same photons)
       const unsigned long long ncap = std::max(now + now / 2, cap * 2);
@@ -382,6 +387,7 @@ static int trace_map(GiContext *ctx, const ShadeEnv &env_in, int map_type, int t
   Buf all_photons, all_keys, counts_dev;
   const GiPhoton *src_photons = photons.as<GiPhoton>(); uint64_t *src_keys = keys.as<uint64_t>();
   if (world > 1) {
+    ctx->clock.begin(ST_PHOTON_EXCHANGE, st);
     std::vector<uint64_t> h_counts(world, 0), bytes32(world), off32(world), bytes8(world), off8(world);
     if (!counts_dev.alloc(8 * (size_t)(world + 1), st)) return 1;
     GI_CUDA(cudaMemcpyAsync(counts_dev.as<uint64_t>() + world, count.p, 8, cudaMemcpyDeviceToDevice, st));
@@ -395,7 +401,9 @@ static int trace_map(GiContext *ctx, const ShadeEnv &env_in, int map_type, int t
     if (!comm_allgatherv(ctx, photons.p, all_photons.p, bytes32.data(), off32.data(), st) ||
         !comm_allgatherv(ctx, keys.p, all_keys.p, bytes8.data(), off8.data(), st)) return 1;
     src_photons = all_photons.as<GiPhoton>(); src_keys = all_keys.as<uint64_t>();
+    ctx->clock.end(st);
   }
+  ctx->clock.begin(ST_PHOTON_SORT, st);
   // deterministic order: sort by (emitted photon number, bounce) -- only the key bits that can be set take part
   Buf keys2, order, order2, tmp;
   if (!keys2.alloc(8 * stored, st) || !order.alloc(4 * stored, st) || !order2.alloc(4 * stored, st)) return 1;
@@ -408,11 +416,13 @@ static int trace_map(GiContext *ctx, const ShadeEnv &env_in, int map_type, int t
   if (!tmp.alloc(tmp_bytes, st)) return 1;
   GI_CUDA(cub::DeviceRadixSort::SortPairs(tmp.p, tmp_bytes, src_keys, keys2.as<uint64_t>(), order.as<uint32_t>(),
                                           order2.as<uint32_t>(), (int)stored, 0, end_bit, st));
-  GI_CUDA(cudaMalloc(&m.raw, sizeof(GiPhoton) * stored));
+  if (!alloc_raw(ctx, m, stored)) return 1;
   permute_kernel<<<blocks, 256, 0, st>>>(src_photons, order2.as<uint32_t>(), stored, (GiPhoton *)m.raw);
+  ctx->clock.end(st);
   ctx->launches += 4;
   GI_CUDA(cudaGetLastError());
   GI_CUDA(cudaStreamSynchronize(st));
+  ctx->clock.collect();
   return 0;
 }
 
@@ -475,6 +485,7 @@ int gi_trace_photons(GiContext *ctx, const GiParams *params, GiPhotonStats *stat
       break;
     }
     const bool want_global = params->indirect_illum || params->direct_photon_illum, want_caustic = params->caustic_illum != 0;
+    ctx->clock.reset_photon();
     cudaEventRecord(e0, ctx->stream);
     int rounds = 0;
     if (want_global && trace_map(ctx, env, MAP_GLOBAL, params->global_photon_count, light_powers, total_power, s.global_emitted, rounds)) break;
@@ -492,6 +503,8 @@ int gi_trace_photons(GiContext *ctx, const GiParams *params, GiPhotonStats *stat
     if (!cuda_ok(cudaStreamSynchronize(ctx->stream), "trace sync")) break;
     float a = 0, b = 0; cudaEventElapsedTime(&a, e0, e1); cudaEventElapsedTime(&b, e1, e2);
     s.trace_ms = a; s.build_ms = b;
+    ctx->clock.collect();
+    if (ctx->clock.on) ctx->clock.ms[ST_KD_BUILD] = b;
     s.cache_ms = ctx->maps[0].cached ? ctx->maps[0].cache_ms : 0.0;
     s.build_ms -= s.cache_ms < s.build_ms ? s.cache_ms : 0.0;          // the reference times the two separately (:378,:410)
     rc = 0;

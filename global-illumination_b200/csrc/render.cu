@@ -757,6 +757,7 @@ struct Renderer {
         !cuda_ok(cudaMemcpyAsync(&h[1], qc.view.count, 8, cudaMemcpyDeviceToHost, st), "D2H queue count") ||
         !cuda_ok(cudaStreamSynchronize(st), "render sync"))
       return false;
+    ctx->clock.collect();
     ng = h[0]; nc = h[1];
     return true;
   }
@@ -775,12 +776,19 @@ struct Renderer {
                     : gi_gather_batch_device(ctx, map, q, n, k, r, filter, &p, nullptr, nullptr, qs.rgb.as<double>(), st);
     };
     // photon gathers order their batch themselves (query_order.cu); only the cache lookups are sorted here
+    StageClock &clk = ctx->clock;
+    const int gstage = map == GI_MAP_GLOBAL ? ST_GATHER_GLOBAL : ST_GATHER_CAUSTIC;
     if (n < 4096 || !sort_requests || !cached) {
+      clk.begin(gstage, st);
       if (estimate(qs.view.q)) return false;
+      clk.end(st);
+      clk.begin(ST_COMMIT, st);
       commit_requests_kernel<<<(unsigned)((n + 255) / 256), 256, 0, st>>>(qs.view.w, qs.view.pix, qs.rgb.as<double>(), n, accum);
+      clk.end(st);
       ctx->launches++;
       return cuda_ok(cudaGetLastError(), "commit_requests_kernel");
     }
+    clk.begin(gstage, st);
     const D3 lo = ld3(ctx->bbox_min), hi = ld3(ctx->bbox_max);
     const D3 inv = mk3(1.0 / fmax(hi.x - lo.x, 1e-300), 1.0 / fmax(hi.y - lo.y, 1e-300), 1.0 / fmax(hi.z - lo.z, 1e-300));
     const unsigned blocks = (unsigned)((n + 255) / 256);
@@ -793,7 +801,10 @@ struct Renderer {
     permute_requests_kernel<<<(unsigned)((n * 17 + 255) / 256), 256, 0, st>>>((const double *)qs.view.q, qs.order2.as<uint32_t>(), n,
                                                                              qs.sorted_q.as<double>());
     if (estimate(qs.sorted_q.as<GiGatherQuery>())) return false;
+    clk.end(st);
+    clk.begin(ST_COMMIT, st);
     commit_sorted_kernel<<<blocks, 256, 0, st>>>(qs.view.w, qs.view.pix, qs.order2.as<uint32_t>(), qs.rgb.as<double>(), n, accum);
+    clk.end(st);
     ctx->launches += 7;
     return cuda_ok(cudaGetLastError(), "sorted gather");
   }
@@ -864,10 +875,15 @@ static int render_accum(GiContext *ctx, const GiParams &params, int sw, int sh, 
   for (uint64_t s0 = s_begin; s0 < s_end; s0 += chunk) {
     const uint64_t n = std::min<uint64_t>(chunk, s_end - s0);
     if (!R.reset_queues()) return 1;
+    StageClock &clk = ctx->clock;
+    clk.begin(ST_PRIMARY, R.st);
     primary_kernel<<<grid_for(n, 128, ctx->sm_count, 64), 128, 0, R.st>>>(env, f, s0, n, hits.as<PrimHit>(), accum, d_stats);
+    clk.end(R.st);
     GI_CUDA(cudaMemsetAsync(n_items.p, 0, 4 * (chunk + 1), R.st));
+    clk.begin(ST_DIRECT, R.st);
     direct_kernel<<<grid_for(n * 32, 128, ctx->sm_count, 16), 128, 0, R.st>>>(env, n, hits.as<PrimHit>(), accum,
                                                                              n_items.as<uint32_t>(), R.qg.view, R.qc.view, d_stats);
+    clk.end(R.st);
     GI_CUDA(cudaGetLastError());
     GI_CUDA(cub::DeviceScan::ExclusiveSum(scan_tmp.p, scan_bytes, n_items.as<uint32_t>(), offs.as<uint64_t>(), (int)(n + 1), R.st));
     ctx->launches += 3;
@@ -886,11 +902,13 @@ static int render_accum(GiContext *ctx, const GiParams &params, int sw, int sh, 
       GI_CUDA(cub::DeviceScan::InclusiveScan(hit_scan_tmp.p, hit_scan_bytes, item_hit.as<uint32_t>(), item_hit.as<uint32_t>(), cub::Max(),
                                              (int)m, R.st));
       if (megakernel) {
+        clk.begin(ST_PATH_SHADE, R.st);
         auto launch = [&](auto kernel) {
           kernel<<<(m + 127) / 128, 128, 0, R.st>>>(env, hits.as<PrimHit>(), offs.as<uint64_t>(), item_hit.as<uint32_t>(), item0, m,
                                                     item_rgb.as<double>(), item_pix.as<uint32_t>(), path_qg, path_qc, d_stats + 1);
         };
         if (path_occ <= 4) launch(path_kernel<4>); else launch(path_kernel<6>);
+        clk.end(R.st);
       } else {
         // wavefront: pass 0 parks every path's first ray by class; then bounce passes (closest-hit kernel + one shade kernel per
         // class) over ballot-compacted queues.  The pass count is fixed: the host never waits for a queue length.
@@ -900,18 +918,26 @@ static int render_accum(GiContext *ctx, const GiParams &params, int sw, int sh, 
           wv[i].count = ws.wave_count.as<unsigned int>() + 2 * i; wv[i].cap = Workspace::batch_max;
         }
         GI_CUDA(cudaMemsetAsync(ws.wave_count.p, 0, 16, R.st));
+        clk.begin(ST_PATH_BEGIN, R.st);
         wave_begin_kernel<<<(m + 127) / 128, 128, 0, R.st>>>(env, hits.as<PrimHit>(), offs.as<uint64_t>(), item_hit.as<uint32_t>(), item0, m,
                                                              item_rgb.as<double>(), item_pix.as<uint32_t>(), wv[0], d_stats + 1);
+        clk.end(R.st);
         const unsigned wgrid = (unsigned)std::min<uint64_t>((m + 127) / 128, (uint64_t)ctx->sm_count * 6);
         int cur = 0;
         for (int pass = 0; pass < wave_passes; pass++, cur ^= 1) {
           GI_CUDA(cudaMemsetAsync(wv[cur ^ 1].count, 0, 8, R.st));
+          clk.begin(ST_PATH_HIT, R.st);
           wave_hit_kernel<<<wgrid, 128, 0, R.st>>>(env.sc, wv[cur]);
+          clk.end(R.st);
+          clk.begin(ST_PATH_SHADE, R.st);
           wave_shade_kernel<MODE_PATH, false><<<wgrid, 128, 0, R.st>>>(env, wv[cur], wv[cur ^ 1], item_rgb.as<double>(), path_qg, path_qc, d_stats + 1);
           wave_shade_kernel<MODE_INDIRECT, false><<<wgrid, 128, 0, R.st>>>(env, wv[cur], wv[cur ^ 1], item_rgb.as<double>(), path_qg, path_qc, d_stats + 1);
+          clk.end(R.st);
         }
+        clk.begin(ST_PATH_FINISH, R.st);
         wave_shade_kernel<MODE_PATH, true><<<wgrid, 128, 0, R.st>>>(env, wv[cur], wv[cur ^ 1], item_rgb.as<double>(), path_qg, path_qc, d_stats + 1);
         wave_shade_kernel<MODE_INDIRECT, true><<<wgrid, 128, 0, R.st>>>(env, wv[cur], wv[cur ^ 1], item_rgb.as<double>(), path_qg, path_qc, d_stats + 1);
+        clk.end(R.st);
         ctx->launches += 2 + 3 * (uint64_t)wave_passes;
       }
       ctx->launches += 2;
@@ -925,7 +951,9 @@ static int render_accum(GiContext *ctx, const GiParams &params, int sw, int sh, 
         ctx->queue_overflows++;
         continue;
       }
+      clk.begin(ST_COMMIT, R.st);
       commit_items_kernel<<<(m + 255) / 256, 256, 0, R.st>>>(item_rgb.as<double>(), item_pix.as<uint32_t>(), m, accum);
+      clk.end(R.st);
       GI_CUDA(cudaGetLastError());
       ctx->launches++;
       if (!R.drain(R.qg, ng, GI_MAP_GLOBAL) || !R.drain(R.qc, nc, GI_MAP_CAUSTIC)) return 1;
@@ -940,6 +968,7 @@ static int render_accum(GiContext *ctx, const GiParams &params, int sw, int sh, 
     ctx->launches++;
   }
   GI_CUDA(cudaStreamSynchronize(R.st));
+  ctx->clock.collect();
   return 0;
 }
 
@@ -977,6 +1006,7 @@ static int render_common(GiContext *ctx, const GiParams *params, int width, int 
   int rc = 1;
   RayStats hs[2]; RayStats paths; memset(&paths, 0, sizeof(paths));
   do {
+    ctx->clock.reset_render();
     if (!cuda_ok(cudaMemsetAsync(accum, 0, sizeof(double) * 3 * npix, ctx->stream), "memset(accum)")) break;
     if (!cuda_ok(cudaMemsetAsync(d_stats, 0, 2 * sizeof(RayStats), ctx->stream), "memset(stats)")) break;
     cudaEventRecord(e0, ctx->stream);
@@ -1030,11 +1060,14 @@ int gi_render(GiContext *ctx, const GiParams *params, int width, int height, int
   dim3 block(16, 16);
   if (!sharded) {
     dim3 grid((width + 15) / 16, (height + 15) / 16);
+    ctx->clock.begin(ST_RESOLVE, st);
     resolve_kernel<<<grid, block, 0, st>>>(accum, width, height, 1 << aa, sh, d_rgb);
+    ctx->clock.end(st);
     ctx->launches++;
     GI_CUDA(cudaGetLastError());
     GI_CUDA(cudaMemcpyAsync(rgb_out, d_rgb, frame_bytes, cudaMemcpyDeviceToHost, st));
     GI_CUDA(cudaStreamSynchronize(st));
+    ctx->clock.collect();
     return 0;
   }
   // ---- multi-GPU: own column strip -> gather to rank 0 -> interleave; ray counters summed over the ranks
@@ -1048,11 +1081,15 @@ int gi_render(GiContext *ctx, const GiParams *params, int width, int height, int
   const int ncols = (width - rank + world - 1) / world;
   if (ncols > 0) {
     dim3 grid((ncols + 15) / 16, (height + 15) / 16);
+    ctx->clock.begin(ST_RESOLVE, st);
     resolve_strip_kernel<<<grid, block, 0, st>>>(accum, width, height, 1 << aa, sh, rank, world, d_mine);
+    ctx->clock.end(st);
     ctx->launches++;
     GI_CUDA(cudaGetLastError());
   }
+  ctx->clock.begin(ST_FRAME_EXCHANGE, st);
   if (!comm_gatherv_root0(ctx, d_mine, d_all, bytes_of.data(), off.data(), st)) return 1;
+  ctx->clock.end(st);
   if (stats) {
     uint64_t h[7] = {stats->screen_rays, stats->shadow_rays, stats->monte_rays, stats->transmissive_samples, stats->specular_samples,
                      stats->indirect_samples, stats->caustic_samples};
@@ -1076,6 +1113,7 @@ int gi_render(GiContext *ctx, const GiParams *params, int width, int height, int
     GI_CUDA(cudaMemcpyAsync(rgb_out, d_rgb, frame_bytes, cudaMemcpyDeviceToHost, st));
   }
   GI_CUDA(cudaStreamSynchronize(st));
+  ctx->clock.collect();
   return 0;
 }
 

@@ -80,6 +80,13 @@ class GiRenderStats(ctypes.Structure):
                 ("render_ms", ctypes.c_double)]
 
 
+class GiStageTimes(ctypes.Structure):
+    _fields_ = [(n, ctypes.c_double) for n in
+                ("emit_filter_ms", "trace_ms", "photon_exchange_ms", "photon_sort_ms", "kd_build_ms",
+                 "primary_ms", "direct_ms", "path_begin_ms", "path_hit_ms", "path_shade_ms", "path_finish_ms", "gather_global_ms",
+                 "gather_caustic_ms", "commit_ms", "resolve_ms", "frame_exchange_ms")]
+
+
 # every symbol include/gi_b200.h declares (tests check the built library exports all of them)
 EXPORTS = ["gi_abi_version", "gi_last_error", "gi_create", "gi_destroy", "gi_default_params", "gi_launch_count",
            "gi_queue_overflow_count", "gi_cached_radiance_batch", "gi_cached_radiance_batch_device",
@@ -87,7 +94,7 @@ EXPORTS = ["gi_abi_version", "gi_last_error", "gi_create", "gi_destroy", "gi_def
            "gi_upload_scene", "gi_intersect_batch", "gi_intersect_batch_device",
            "gi_load_photons", "gi_load_photons_device", "gi_load_photons_file", "gi_dump_photons_file",
            "gi_photon_count", "gi_get_photons", "gi_get_photons_device", "gi_build_maps", "gi_gather_batch", "gi_gather_batch_device",
-           "gi_gather_batch_device_noalloc",
+           "gi_gather_batch_device_noalloc", "gi_stage_timing", "gi_stage_times", "gi_load_photons_sharded_device",
            "gi_trace_photons", "gi_scale_photon_power", "gi_render", "gi_render_float",
            "gi_default_cli_options", "gi_parse_args", "gi_write_image",
            "gi_comm_unique_id", "gi_comm_init_rank", "gi_comm_init_all", "gi_comm_info", "gi_comm_destroy"]
@@ -109,6 +116,8 @@ def lib():
         L.gi_destroy.argtypes = [vp]; L.gi_destroy.restype = None
         L.gi_default_params.argtypes = [ctypes.POINTER(GiParams)]; L.gi_default_params.restype = None
         L.gi_launch_count.argtypes = [vp, ctypes.POINTER(u64)]
+        L.gi_stage_timing.argtypes = [vp, i32]
+        L.gi_stage_times.argtypes = [vp, ctypes.POINTER(GiStageTimes)]
         L.gi_queue_overflow_count.argtypes = [vp, ctypes.POINTER(u64)]
         L.gi_host_scene_load.argtypes = [ctypes.c_char_p, i32, ctypes.POINTER(vp)]
         L.gi_host_scene_view.argtypes = [vp, ctypes.POINTER(GiScene)]
@@ -119,6 +128,7 @@ def lib():
         L.gi_intersect_batch_device.argtypes = [vp, vp, u64, vp, vp]
         L.gi_load_photons.argtypes = [vp, i32, vp, u64]
         L.gi_load_photons_device.argtypes = [vp, i32, vp, u64]
+        L.gi_load_photons_sharded_device.argtypes = [vp, i32, vp, u64]
         L.gi_load_photons_file.argtypes = [vp, i32, ctypes.c_char_p]
         L.gi_dump_photons_file.argtypes = [vp, i32, ctypes.c_char_p]
         L.gi_photon_count.argtypes = [vp, i32, ctypes.POINTER(u64)]
@@ -230,6 +240,15 @@ class Context:
         _check(lib().gi_launch_count(self.handle, ctypes.byref(n)))
         return n.value
 
+    def stage_timing(self, on=True):
+        _check(lib().gi_stage_timing(self.handle, 1 if on else 0))
+
+    def stage_times(self):
+        """per-stage device milliseconds of the last trace_photons / render of this context (dict)"""
+        t = GiStageTimes()
+        _check(lib().gi_stage_times(self.handle, ctypes.byref(t)))
+        return {n: float(getattr(t, n)) for n, _ in GiStageTimes._fields_}
+
     def queue_overflow_count(self):
         n = ctypes.c_uint64()
         _check(lib().gi_queue_overflow_count(self.handle, ctypes.byref(n)))
@@ -253,6 +272,10 @@ class Context:
 
     def load_photons_device(self, which, d_ptr, n):
         _check(lib().gi_load_photons_device(self.handle, which, d_ptr, n))
+
+    def load_photons_sharded_device(self, which, d_ptr, n_share):
+        """collective: this rank's share (device pointer); the map holds the shares of all ranks in rank order"""
+        _check(lib().gi_load_photons_sharded_device(self.handle, which, d_ptr, n_share))
 
     def load_photons_file(self, which, path):
         _check(lib().gi_load_photons_file(self.handle, which, path.encode()))

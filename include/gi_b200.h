@@ -224,6 +224,20 @@ int gi_launch_count(GiContext *ctx, uint64_t *out);                /* kernels la
  * the environment variables GI_QCAP / GI_BATCH_MAX shrink the queue / the batch to provoke it in tests) */
 int gi_queue_overflow_count(GiContext *ctx, uint64_t *out);
 
+/* Per-stage device times of the last gi_trace_photons and the last gi_render* of a context, in milliseconds (CUDA events on
+ * the context's stream; the reference prints wall-clock totals only: the -v blocks of photonmap.cpp:331-377 and
+ * render.cpp:224-255).  Off by default; gi_stage_timing(ctx, 1) switches the event pairs on (a few microseconds per
+ * stage launch, no extra synchronisation). */
+typedef struct GiStageTimes {
+  /* gi_trace_photons */
+  double emit_filter_ms, trace_ms, photon_exchange_ms, photon_sort_ms, kd_build_ms;
+  /* gi_render / gi_render_float */
+  double primary_ms, direct_ms, path_begin_ms, path_hit_ms, path_shade_ms, path_finish_ms, gather_global_ms, gather_caustic_ms,
+         commit_ms, resolve_ms, frame_exchange_ms;
+} GiStageTimes;
+int gi_stage_timing(GiContext *ctx, int enable);
+int gi_stage_times(GiContext *ctx, GiStageTimes *out);
+
 /* host-side .scn/.off loader (no device needed): ReadScene (src/utils/io_utils.cpp:219-250) ->
  * R3Scene::ReadFile (R3Scene.cpp:514-587) -> ReadPrinceton (:1463-1953) / R3Mesh::ReadOffFile
  * (R3Mesh.cpp:4075-4215).  `path` ending in .gisc reads a flattened scene saved by gi_host_scene_save. */
@@ -327,6 +341,13 @@ int gi_comm_init_rank(GiContext *ctx, const GiUniqueId *id, int rank, int world)
 int gi_comm_init_all(GiContext **ctxs, int n);                    /* rank i = ctxs[i]; contexts on distinct devices */
 int gi_comm_info(GiContext *ctx, int *rank, int *world);          /* 0 / 1 without a communicator */
 int gi_comm_destroy(GiContext *ctx);                              /* also done by gi_destroy */
+
+/* Loading a map whose photons sit sharded over the ranks (device memory): stands in for the ONE GLOBAL_PHOTONS /
+ * CAUSTIC_PHOTONS array that all worker threads of the reference insert into (photonmap.cpp:117-118, StorePhoton,
+ * photon_utils.cpp:40-66).  Every rank passes its share; one ragged all-gather over NVLink concatenates the shares in
+ * rank order straight into the map's photon array on every rank (no padding, no staging copy); gi_build_maps then builds
+ * the kd-tree locally.  Collective: every rank must call it.  Without a communicator: gi_load_photons_device. */
+int gi_load_photons_sharded_device(GiContext *ctx, int map, const GiPhoton *d_share, uint64_t n_share);
 
 /* RenderImage(aa, W, H) (render.cpp:155-259).  rgb_out: W*H*3 bytes, row 0 = bottom row like R2Image. */
 int gi_render(GiContext *ctx, const GiParams *params, int width, int height, int aa, uint8_t *rgb_out,
