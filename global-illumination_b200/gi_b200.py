@@ -13,6 +13,7 @@ LIB_PATH = os.path.join(_HERE, "libgi_b200.so")
 
 GI_MAP_GLOBAL, GI_MAP_CAUSTIC = 0, 1
 GI_FILTER_DISK, GI_FILTER_CONE, GI_FILTER_GAUSS = 0, 1, 2
+GI_VIEW_GLOBAL_PHOTONS, GI_VIEW_CAUSTIC_PHOTONS, GI_VIEW_RAYS, GI_VIEW_PATHS = 0, 1, 2, 3
 NOALLOC_MAX_QUERIES = 262144      # GI_NOALLOC_MAX_QUERIES of include/gi_b200.h
 
 RAY = np.dtype([("o", "<f8", 3), ("d", "<f8", 3)])
@@ -94,7 +95,7 @@ EXPORTS = ["gi_abi_version", "gi_last_error", "gi_create", "gi_destroy", "gi_def
            "gi_upload_scene", "gi_intersect_batch", "gi_intersect_batch_device",
            "gi_load_photons", "gi_load_photons_device", "gi_load_photons_file", "gi_dump_photons_file",
            "gi_photon_count", "gi_get_photons", "gi_get_photons_device", "gi_build_maps", "gi_gather_batch", "gi_gather_batch_device",
-           "gi_gather_batch_device_noalloc", "gi_stage_timing", "gi_stage_times", "gi_load_photons_sharded_device",
+           "gi_gather_batch_device_noalloc", "gi_stage_timing", "gi_stage_times", "gi_load_photons_sharded_device", "gi_debug_view",
            "gi_trace_photons", "gi_scale_photon_power", "gi_render", "gi_render_float",
            "gi_default_cli_options", "gi_parse_args", "gi_write_image",
            "gi_comm_unique_id", "gi_comm_init_rank", "gi_comm_init_all", "gi_comm_info", "gi_comm_destroy"]
@@ -117,6 +118,7 @@ def lib():
         L.gi_default_params.argtypes = [ctypes.POINTER(GiParams)]; L.gi_default_params.restype = None
         L.gi_launch_count.argtypes = [vp, ctypes.POINTER(u64)]
         L.gi_stage_timing.argtypes = [vp, i32]
+        L.gi_debug_view.argtypes = [vp, i32, ctypes.POINTER(GiParams), i32, i32, i32, vp]
         L.gi_stage_times.argtypes = [vp, ctypes.POINTER(GiStageTimes)]
         L.gi_queue_overflow_count.argtypes = [vp, ctypes.POINTER(u64)]
         L.gi_host_scene_load.argtypes = [ctypes.c_char_p, i32, ctypes.POINTER(vp)]
@@ -248,6 +250,13 @@ class Context:
         t = GiStageTimes()
         _check(lib().gi_stage_times(self.handle, ctypes.byref(t)))
         return {n: float(getattr(t, n)) for n, _ in GiStageTimes._fields_}
+
+    def debug_view(self, kind, width, height, draw_shapes=True, params=None):
+        """one of the reference's debug views (visualize.cpp) as a uint8 array [H, W, 3], row 0 = bottom row"""
+        out = np.zeros((height, width, 3), dtype=np.uint8)
+        p = params or default_params()
+        _check(lib().gi_debug_view(self.handle, kind, ctypes.byref(p), width, height, 1 if draw_shapes else 0, out.ctypes.data))
+        return out
 
     def queue_overflow_count(self):
         n = ctypes.c_uint64()

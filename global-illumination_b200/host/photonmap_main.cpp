@@ -5,7 +5,8 @@
 //
 // Extra flags: -seed N (the reference RNG is unseeded), -device N, -gpus N (N GPUs of this box share the photon pass and
 // the frame: one context + one host thread per GPU, NCCL between them), -save_global f / -save_caustic f and
-// -load_global f / -load_caustic f (photon maps as "GIPM" files, shared with oracle/ref_harness).
+// -load_global f / -load_caustic f (photon maps as "GIPM" files, shared with oracle/ref_harness), and the debug views of the
+// reference's `visualize` program as image files: -viz_global f / -viz_caustic f / -viz_rays f / -viz_paths f.
 #include <chrono>
 #include <cstdio>
 #include <cstdlib>
@@ -25,6 +26,7 @@ int main(int argc, char **argv) {
   GiParams params; gi_default_params(&params);
   GiCliOptions opt; gi_default_cli_options(&opt);
   const char *save[2] = {nullptr, nullptr}, *load[2] = {nullptr, nullptr};
+  const char *viz[4] = {nullptr, nullptr, nullptr, nullptr};        // GiDebugView order
   std::vector<const char *> av;
   for (int i = 0; i < argc; i++) {
     const bool has_value = i + 1 < argc;
@@ -32,6 +34,10 @@ int main(int argc, char **argv) {
     else if (has_value && !strcmp(argv[i], "-save_caustic")) save[1] = argv[++i];
     else if (has_value && !strcmp(argv[i], "-load_global")) load[0] = argv[++i];
     else if (has_value && !strcmp(argv[i], "-load_caustic")) load[1] = argv[++i];
+    else if (has_value && !strcmp(argv[i], "-viz_global")) viz[GI_VIEW_GLOBAL_PHOTONS] = argv[++i];
+    else if (has_value && !strcmp(argv[i], "-viz_caustic")) viz[GI_VIEW_CAUSTIC_PHOTONS] = argv[++i];
+    else if (has_value && !strcmp(argv[i], "-viz_rays")) viz[GI_VIEW_RAYS] = argv[++i];
+    else if (has_value && !strcmp(argv[i], "-viz_paths")) viz[GI_VIEW_PATHS] = argv[++i];
     else av.push_back(argv[i]);
   }
   if (gi_parse_args((int)av.size(), av.data(), &params, &opt)) { fprintf(stderr, "%s\n", gi_last_error()); return 1; }
@@ -112,6 +118,15 @@ int main(int argc, char **argv) {
       }
       for (int m = 0; m < 2; m++)
         if (r == 0 && save[m] && gi_dump_photons_file(ctx, m, save[m])) return fail("Unable to save photon map");
+    }
+
+    // the debug views of `visualize` (visualize.cpp:268-298, 589-700, 1366-1424), from rank 0's copy of the maps
+    for (int v = 0; v < 4; v++) {
+      if (r != 0 || !viz[v]) continue;
+      std::vector<uint8_t> view((size_t)opt.width * opt.height * 3);
+      if (gi_debug_view(ctx, v, &prm, opt.width, opt.height, 1, view.data())) return fail("Unable to draw debug view");
+      if (gi_write_image(viz[v], view.data(), opt.width, opt.height)) return fail("Unable to write debug view");
+      if (talk) printf("Wrote debug view to %s ...\n", viz[v]);
     }
 
     // RenderImage (render.cpp:155-259)

@@ -26,7 +26,7 @@
 extern "C" {
 #endif
 
-#define GI_ABI_VERSION 5
+#define GI_ABI_VERSION 6
 
 /* ------------------------------------------------------------------------------------------------
  * Scene description (flattened R3Scene; src/R3Graphics/R3Scene.h).  Order is the order in which
@@ -356,6 +356,19 @@ int gi_render(GiContext *ctx, const GiParams *params, int width, int height, int
  * column-major like image_buffer[i][j]) for parity tests */
 int gi_render_float(GiContext *ctx, const GiParams *params, int width, int height, int aa, double *rgb_out,
                     GiRenderStats *stats);
+
+/* The debug views of the reference's `visualize` program (src/visualize.cpp), headless: the pictures it draws with
+ * OpenGL through the scene camera, rasterised by CUDA splat / line kernels into a z-buffered frame (no graphics stack).
+ *   GI_VIEW_GLOBAL_PHOTONS / GI_VIEW_CAUSTIC_PHOTONS  DrawStoredGlobal / DrawStoredCaustic (visualize.cpp:1366-1424):
+ *        per stored photon a sphere of radius 0.01 in the hue of its power and a span along its incident direction;
+ *   GI_VIEW_RAYS    DrawRays (:268-298): hit point and normal of a 20 x 20 grid of eye rays;
+ *   GI_VIEW_PATHS   DrawPaths + MonteCarlo_PathTrace (:436-530, :589-700): the specular / refractive walks (<= 10 bounces)
+ *        of a 25 x 25 grid of eye rays, one span per segment coloured by the pixel (params->seed drives the roulette).
+ * draw_shapes != 0 also draws the scene's surfaces (grey head-light shade) so that geometry hides what lies behind it, and
+ * fills empty pixels with the scene's background colour (black otherwise).  rgb_out: W*H*3 bytes, row 0 = bottom row.
+ * params may be NULL (defaults). */
+enum GiDebugView { GI_VIEW_GLOBAL_PHOTONS = 0, GI_VIEW_CAUSTIC_PHOTONS = 1, GI_VIEW_RAYS = 2, GI_VIEW_PATHS = 3 };
+int gi_debug_view(GiContext *ctx, int kind, const GiParams *params, int width, int height, int draw_shapes, uint8_t *rgb_out);
 
 /* R2Image::Write (R2Image.cpp:317-340) by file extension: .png, .ppm (ASCII, the reference's layout), .bmp.
  * rgb is the gi_render frame (row 0 = bottom row). */
