@@ -4,21 +4,35 @@
 // PartitionPoints (src/R3Shapes/R3Kdtree.cpp:1624-1671, 1552-1620): a single-threaded recursive build with
 // randomised quickselect and 31-photon leaf buckets (15 s for 1e7 photons on the CPU).
 //
-// Here: level-synchronous, sort-based construction of Jensen's left-balanced tree.  Every photon carries the id
-// ("tag") of the subtree it currently belongs to.  For level l = 0..L-1:
-//   1. key = (tag, float32 coordinate on the subtree's split axis); radix sort (key, photon id) -- after the sort
-//      the photons of subtree s are contiguous and start at a closed-form offset (left-balanced => every subtree
-//      size is known from n alone);
-//   2. the photon at offset `size of the left child subtree` inside its segment becomes node s; photons before it
-//      move to subtree 2s+1, after it to 2s+2;
-//   3. the split axis of a subtree is the longest axis of the TIGHT bounding box of its photons (segmented min/max
-//      with warp-aggregated atomics).  The reference splits on the longest axis of the inherited node box
-//      (R3Kdtree.cpp:1640, R3Box::LongestAxis R3Box.cpp:258-274); for photons lying on planes that rule keeps
-//      cutting along the plane normal, where every coordinate is equal and nothing is separated.  The choice of axis
-//      does not change any query result, only how much of the tree a query has to visit.
+// Here: level-synchronous construction of Jensen's left-balanced tree from three PRESORTED lists (the idea of Brown's
+// O(k n log n) build): the photon ids are sorted once along x, once along y and once along z (three 32-bit radix sorts);
+// after that no level sorts anything.  The lists are kept in IN-ORDER layout: a subtree owns one contiguous range
+// [begin, begin + size) of all three lists, its pivot sits at begin + (size of the left child subtree), the children own
+// the ranges on either side (left-balanced => every size is closed-form in n).  For level l = 0..L-1:
+//   choose    thread per subtree: the TIGHT bounding box of its photons is read off the two ends of its range in the three
+//             lists (no reduction, no atomics); split axis = longest axis of that box; pivot = the entry at the median
+//             position of that axis' list -> node s of the heap.  The reference splits on the longest axis of the
+//             inherited node box (R3Kdtree.cpp:1640, R3Box::LongestAxis R3Box.cpp:258-274); for photons lying on planes
+//             that rule keeps cutting along the plane normal, where every coordinate is equal and nothing is separated.
+//             The choice of axis does not change any query result, only how much of the tree a query has to visit.
+//   partition one segmented scan over the three lists of packed (left, right) counters whose OUTPUT ITERATOR moves every
+//             entry to its place (single pass, cub's decoupled look-back).  A list entry is 16 bytes {photon id,
+//             ordered float x, y, z}, so which side of the pivot an entry falls on is decided from the entry itself:
+//             the lists are ordered by (coordinate, id), hence side = compare((entry's split-axis key, id), (pivot's)) --
+//             no per-photon state, every access is coalesced.  Every range of every list is stably partitioned into left
+//             entries, the pivot, right entries: the lists of the children are sorted again, in place in the in-order
+//             layout; a per-position array says which subtree a position belongs to (the ranges coincide in the lists).
+// Per level that is ~110 bytes of coalesced traffic per photon and three launches, against a full 64-bit radix sort of all unplaced
+// photons plus a bounding-box pass of atomics in the first version of this file (10^7 photons: 41 ms -> see DESIGN.md);
+// GI_KD_SORT_BUILD=1 selects the old sort-per-level build for A/B measurements.
 // Splits are float32 (monotone rounding of the FP64 coordinate); the search widens them by one ulp, distances stay
-// FP64, so the k-nearest SET is exact (see gather.cu).  Only photons not yet placed take part in a level's sort.
+// FP64, so the k-nearest SET is exact (see gather.cu).
 #include <cub/device/device_radix_sort.cuh>
+#include <cub/device/device_scan.cuh>
+#include <thrust/iterator/counting_iterator.h>
+#include <thrust/iterator/transform_iterator.h>
+#include <stdlib.h>
+#include <iterator>
 #include <cuda_runtime.h>
 #include <float.h>
 #include <math.h>
@@ -218,6 +232,121 @@ __global__ void cbox_init_kernel(double *cbox, uint64_t n_doubles) {
   if (i < n_doubles) cbox[i] = ((i >> 5) & 1) ? -__longlong_as_double(0x7ff0000000000000ll) : __longlong_as_double(0x7ff0000000000000ll);
 }
 
+// ------------------------------------------------------------------------------------------------ presorted build
+#define KD_DONE 0xffffffffu          /* pseg: the position holds a placed pivot */
+
+__global__ void presort_keys_kernel(const GiPhoton *__restrict__ ph, uint64_t n, int a, uint32_t *keys, uint32_t *ids) {
+  const uint64_t i = (uint64_t)blockIdx.x * blockDim.x + threadIdx.x;
+  if (i < n) { keys[i] = float_to_ordered((float)ph[i].position[a]); ids[i] = (uint32_t)i; }
+}
+// list entry = {photon id, ordered float x, y, z}
+__global__ void entries_kernel(const GiPhoton *__restrict__ ph, uint64_t n, const uint32_t *__restrict__ sorted_ids, uint4 *list, uint32_t *pseg) {
+  const uint64_t j = (uint64_t)blockIdx.x * blockDim.x + threadIdx.x;
+  if (j >= n) return;
+  const uint32_t id = sorted_ids[j];
+  const GiPhoton &q = ph[id];
+  list[j] = make_uint4(id, float_to_ordered((float)q.position[0]), float_to_ordered((float)q.position[1]), float_to_ordered((float)q.position[2]));
+  if (pseg) pseg[j] = 0u;
+}
+__device__ __forceinline__ uint32_t entry_key(const uint4 &e, int a) { return a == 0 ? e.y : (a == 1 ? e.z : e.w); }
+
+struct Lists { const uint4 *l[3]; };
+struct ListsOut { uint4 *l[3]; };
+struct Pivots {                      // per subtree (heap index) of the level being built
+  const uint32_t *segbegin; const uint8_t *axis; const uint32_t *key; const uint32_t *id;
+};
+
+// thread per subtree of the level: tight box from the ends of its range in the three lists, axis, pivot, children's ranges
+__global__ void choose_kernel(uint64_t n, int L, int level, Lists in, uint32_t *segbegin, uint32_t *heap_photon, uint32_t *pivot_key,
+                              float *split, uint8_t *axis, uint32_t *root_bounds) {
+  const uint64_t s = (((uint64_t)1 << level) - 1) + (uint64_t)blockIdx.x * blockDim.x + threadIdx.x;
+  if (s >= n || s >= ((uint64_t)2 << level) - 1) return;
+  const uint32_t begin = level == 0 ? 0u : segbegin[s];
+  const uint64_t sz = subtree_size(s, n, L);
+  uint32_t ob[6]; float b[6];
+  for (int a = 0; a < 3; a++) {
+    ob[a] = entry_key(in.l[a][begin], a); ob[3 + a] = entry_key(in.l[a][begin + sz - 1], a);
+    b[a] = ordered_to_float(ob[a]); b[3 + a] = ordered_to_float(ob[3 + a]);
+  }
+  const int ax = longest_axis(b);
+  const uint64_t m = subtree_size(2 * s + 1, n, L);
+  const uint4 pv = in.l[ax][begin + m];
+  heap_photon[s] = pv.x; pivot_key[s] = entry_key(pv, ax); split[s] = ordered_to_float(entry_key(pv, ax)); axis[s] = (uint8_t)ax;
+  if (level == 0) segbegin[0] = 0u;
+  if (2 * s + 1 < n) segbegin[2 * s + 1] = begin;
+  if (2 * s + 2 < n) segbegin[2 * s + 2] = begin + (uint32_t)m + 1u;
+  if (s == 0) for (int k = 0; k < 6; k++) root_bounds[k] = ob[k];
+}
+
+// 0: left of the pivot, 1: right, 2: the pivot itself -- in the order (split-axis key, photon id) of the split-axis list
+__device__ __forceinline__ int entry_side(const uint4 &e, int ax, uint32_t pkey, uint32_t pid) {
+  const uint32_t k = entry_key(e, ax);
+  if (k < pkey || (k == pkey && e.x < pid)) return 0;
+  return (k == pkey && e.x == pid) ? 2 : 1;
+}
+
+// The stable partition of every range of every list is ONE segmented inclusive scan whose output iterator does the
+// scatter.  Scan value: low word = left entries, bits 32..62 = right entries, bit 63 = "reset" (the running counts start
+// again here).  Neighbouring subtrees of a level are always separated by a placed pivot in the in-order layout, so the
+// reset sits on the placed positions (and on position 0 of each list); cub's single-pass scan (decoupled look-back)
+// carries the counts across thread blocks, and the assignment of the scan result to output element t moves entry t to
+// its place -- no scan array, no second pass.
+#define KD_RESET (1ull << 63)
+struct SegScanOp {
+  __host__ __device__ __forceinline__ unsigned long long operator()(unsigned long long a, unsigned long long b) const {
+    return (b & KD_RESET) ? b : (((a & ~KD_RESET) + (b & ~KD_RESET)) | (a & KD_RESET));
+  }
+};
+struct SideCount {
+  Lists in; const uint32_t *pseg; Pivots pv; uint64_t n;
+  __device__ __forceinline__ unsigned long long operator()(unsigned long long t) const {
+    const int a = (t >= n) + (t >= 2 * n);
+    const uint64_t j = t - (unsigned long long)a * n;
+    const uint32_t s = pseg[j];
+    if (s == KD_DONE) return KD_RESET;
+    const int sd = entry_side(in.l[a][j], pv.axis[s], pv.key[s], pv.id[s]);
+    return (sd == 0 ? 1ull : (sd == 1 ? (1ull << 32) : 0ull)) | (j == 0 ? KD_RESET : 0ull);
+  }
+};
+struct ScatterCtx { Lists in; ListsOut out; const uint32_t *pseg; uint32_t *pseg_next; Pivots pv; uint64_t n; int L; };
+struct ScatterRef {                  // proxy reference: assigning the inclusive scan value of element t performs its move
+  const ScatterCtx *c; unsigned long long t;
+  __device__ __forceinline__ const ScatterRef &operator=(unsigned long long v) const {
+    const ScatterCtx &x = *c;
+    const int a = (t >= x.n) + (t >= 2 * x.n);
+    const uint64_t j = t - (unsigned long long)a * x.n;
+    const uint32_t s = x.pseg[j];
+    if (s == KD_DONE) { if (a == 0) x.pseg_next[j] = KD_DONE; return *this; }
+    const uint4 e = x.in.l[a][j];
+    const int sd = entry_side(e, x.pv.axis[s], x.pv.key[s], x.pv.id[s]);
+    const uint64_t begin = x.pv.segbegin[s];
+    const uint64_t m = subtree_size(2 * (uint64_t)s + 1, x.n, x.L);
+    const unsigned long long incl = v & ~KD_RESET;
+    uint64_t pos;
+    if (sd == 0) pos = begin + ((incl & 0xffffffffull) - 1ull);
+    else if (sd == 1) pos = begin + m + 1 + ((incl >> 32) - 1ull);
+    else pos = begin + m;
+    x.out.l[a][pos] = e;
+    if (a == 0) x.pseg_next[pos] = sd == 0 ? 2u * s + 1u : (sd == 1 ? 2u * s + 2u : KD_DONE);
+    return *this;
+  }
+};
+struct ScatterIterator {
+  using iterator_category = std::random_access_iterator_tag;
+  using value_type = unsigned long long;
+  using difference_type = long long;
+  using pointer = void;
+  using reference = ScatterRef;
+  const ScatterCtx *c; unsigned long long t;
+  __host__ __device__ __forceinline__ ScatterRef operator*() const { return ScatterRef{c, t}; }
+  __host__ __device__ __forceinline__ ScatterRef operator[](difference_type i) const { return ScatterRef{c, t + (unsigned long long)i}; }
+  __host__ __device__ __forceinline__ ScatterIterator operator+(difference_type i) const { return ScatterIterator{c, t + (unsigned long long)i}; }
+  __host__ __device__ __forceinline__ ScatterIterator operator-(difference_type i) const { return ScatterIterator{c, t - (unsigned long long)i}; }
+  __host__ __device__ __forceinline__ ScatterIterator &operator+=(difference_type i) { t += (unsigned long long)i; return *this; }
+  __host__ __device__ __forceinline__ ScatterIterator &operator++() { ++t; return *this; }
+  __host__ __device__ __forceinline__ difference_type operator-(const ScatterIterator &o) const { return (difference_type)(t - o.t); }
+};
+
 #define CKB(x) do { cudaError_t e_ = (x); if (e_ != cudaSuccess) { err = e_; goto done; } } while (0)
 
 cudaError_t build_photon_map(GiContext *ctx, PhotonMapStore &m, uint64_t n, const double *d_lut) {
@@ -228,6 +357,11 @@ cudaError_t build_photon_map(GiContext *ctx, PhotonMapStore &m, uint64_t n, cons
   uint64_t *keys[2] = {nullptr, nullptr}; uint32_t *vals[2] = {nullptr, nullptr};
   uint32_t *heap_photon = nullptr, *bounds = nullptr; float *split = nullptr; uint8_t *axis = nullptr;
   void *tmp = nullptr; size_t tmp_bytes = 0;
+  uint4 *lists[6] = {nullptr, nullptr, nullptr, nullptr, nullptr, nullptr}; uint32_t *pseg[2] = {nullptr, nullptr}, *segbegin = nullptr, *pivot_key = nullptr;
+  uint32_t *skeys[2] = {nullptr, nullptr}, *sids[2] = {nullptr, nullptr}; ScatterCtx *sctx_dev = nullptr;
+  // A/B hook: the sort-per-level build.  It also takes maps of 2^30 photons and more (the packed counters of the scan
+  // hold the left entries of all three lists in 32 bits).
+  const bool sort_build = (getenv("GI_KD_SORT_BUILD") && atoi(getenv("GI_KD_SORT_BUILD")) != 0) || n >= ((uint64_t)1 << 30);
   double *px = nullptr, *py = nullptr, *pz = nullptr; uint2 *node = nullptr, *shade = nullptr; uint32_t *orig = nullptr;
   double *hint = nullptr;
   double *cbox = nullptr, *gpos = nullptr; double2 *srec = nullptr; uint64_t n_groups = 0, n_upper = 0;
@@ -237,9 +371,10 @@ cudaError_t build_photon_map(GiContext *ctx, PhotonMapStore &m, uint64_t n, cons
   int cur = 0;
   // temporaries come from the device's stream-ordered pool (gi_create keeps freed pool memory): a frame rebuilds its
   // maps every time, and cudaMalloc / cudaFree of ~1 GB cost more than the build itself on a busy device
-  for (int k = 0; k < 2; k++) { CKB(cudaMallocAsync(&keys[k], 8 * n, st)); CKB(cudaMallocAsync(&vals[k], 4 * n, st)); }
-  CKB(cudaMallocAsync(&heap_photon, 4 * n, st)); CKB(cudaMallocAsync(&split, 4 * n, st)); CKB(cudaMallocAsync(&bounds, 24 * n, st));
+  CKB(cudaMallocAsync(&heap_photon, 4 * n, st)); CKB(cudaMallocAsync(&split, 4 * n, st)); CKB(cudaMallocAsync(&bounds, sort_build ? 24 * n : 256, st));
   CKB(cudaMallocAsync(&axis, n, st));
+  if (sort_build) {
+  for (int k = 0; k < 2; k++) { CKB(cudaMallocAsync(&keys[k], 8 * n, st)); CKB(cudaMallocAsync(&vals[k], 4 * n, st)); }
   CKB(cub::DeviceRadixSort::SortPairs(nullptr, tmp_bytes, keys[0], keys[1], vals[0], vals[1], (int)n, 0, 64, st));
   CKB(cudaMallocAsync(&tmp, tmp_bytes, st));
   init_kernel<<<G, B, 0, st>>>(n, keys[0], vals[0]);
@@ -261,6 +396,57 @@ cudaError_t build_photon_map(GiContext *ctx, PhotonMapStore &m, uint64_t n, cons
     assign_kernel<<<g, B, 0, st>>>(first, n, L, level, keys[cur], vals[cur], heap_photon, split);
     ctx->launches += 6;
     CKB(cudaGetLastError());
+  }
+  } else {
+    // ---- presorted lists (see the header of this file)
+    for (int k = 0; k < 6; k++) CKB(cudaMallocAsync(&lists[k], 16 * n, st));      // [0..2]: ping, [3..5]: pong
+    for (int k = 0; k < 2; k++) CKB(cudaMallocAsync(&pseg[k], 4 * n, st));
+    CKB(cudaMallocAsync(&segbegin, 4 * n, st)); CKB(cudaMallocAsync(&pivot_key, 4 * n, st));
+    CKB(cudaMallocAsync(&skeys[0], 4 * n, st)); CKB(cudaMallocAsync(&skeys[1], 4 * n, st)); CKB(cudaMallocAsync(&sids[0], 4 * n, st));
+    CKB(cudaMallocAsync(&sids[1], 4 * n, st));
+    size_t sort_bytes = 0, scan_bytes = 0;
+    CKB(cub::DeviceRadixSort::SortPairs(nullptr, sort_bytes, skeys[0], skeys[1], sids[0], sids[1], (int)n, 0, 32, st));
+    SideCount fn; fn.n = n; fn.pseg = pseg[0]; fn.pv.segbegin = segbegin; fn.pv.axis = axis; fn.pv.key = pivot_key; fn.pv.id = heap_photon;
+    for (int a = 0; a < 3; a++) fn.in.l[a] = lists[a];
+    CKB(cudaMallocAsync(&sctx_dev, 2 * sizeof(ScatterCtx), st));            // the output iterator reads its context from device memory
+    {
+      auto it = thrust::make_transform_iterator(thrust::counting_iterator<unsigned long long>(0ull), fn);
+      CKB(cub::DeviceScan::InclusiveScan(nullptr, scan_bytes, it, ScatterIterator{sctx_dev, 0ull}, SegScanOp(), (size_t)(3 * n), st));
+    }
+    tmp_bytes = sort_bytes > scan_bytes ? sort_bytes : scan_bytes;
+    CKB(cudaMallocAsync(&tmp, tmp_bytes, st));
+    for (int a = 0; a < 3; a++) {
+      presort_keys_kernel<<<G, B, 0, st>>>(ph, n, a, skeys[0], sids[0]);
+      size_t bytes = tmp_bytes;
+      CKB(cub::DeviceRadixSort::SortPairs(tmp, bytes, skeys[0], skeys[1], sids[0], sids[1], (int)n, 0, 32, st));
+      entries_kernel<<<G, B, 0, st>>>(ph, n, sids[1], lists[a], a == 0 ? pseg[0] : nullptr);
+      ctx->launches += 5;
+    }
+    int pp = 0;                                            // lists[3 pp ..] and pseg[pp] describe the level being built
+    {
+      ScatterCtx h[2];
+      for (int q = 0; q < 2; q++) {
+        for (int a = 0; a < 3; a++) { h[q].in.l[a] = lists[3 * q + a]; h[q].out.l[a] = lists[3 * (q ^ 1) + a]; }
+        h[q].pseg = pseg[q]; h[q].pseg_next = pseg[q ^ 1]; h[q].pv = fn.pv; h[q].n = n; h[q].L = L;
+      }
+      CKB(cudaMemcpyAsync(sctx_dev, h, sizeof(h), cudaMemcpyHostToDevice, st));
+      CKB(cudaStreamSynchronize(st));                       // h lives on this stack frame
+    }
+    for (int level = 0; level < L; level++) {
+      const uint64_t level_nodes = (uint64_t)1 << level;
+      const unsigned gn = (unsigned)((level_nodes + B - 1) / B);
+      Lists in;
+      for (int a = 0; a < 3; a++) in.l[a] = lists[3 * pp + a];
+      choose_kernel<<<gn, B, 0, st>>>(n, L, level, in, segbegin, heap_photon, pivot_key, split, axis, bounds);
+      if (level + 1 == L) { ctx->launches++; break; }      // the last level only places its pivots
+      fn.in = in; fn.pseg = pseg[pp];
+      auto it = thrust::make_transform_iterator(thrust::counting_iterator<unsigned long long>(0ull), fn);
+      size_t bytes = tmp_bytes;
+      CKB(cub::DeviceScan::InclusiveScan(tmp, bytes, it, ScatterIterator{sctx_dev + pp, 0ull}, SegScanOp(), (size_t)(3 * n), st));
+      pp ^= 1;
+      ctx->launches += 3;
+      CKB(cudaGetLastError());
+    }
   }
   // the map's own arrays: from the same pool (freed by free_map with cudaFreeAsync on this stream)
   m.stream = (void *)st;
@@ -318,7 +504,8 @@ cudaError_t build_photon_map(GiContext *ctx, PhotonMapStore &m, uint64_t n, cons
   px = py = pz = nullptr; node = shade = nullptr; orig = nullptr; cbox = nullptr; gpos = nullptr; srec = nullptr; hint = nullptr;
 done:
   {
-    void *temps[] = {keys[0], keys[1], vals[0], vals[1], heap_photon, split, bounds, axis, tmp};
+    void *temps[] = {keys[0], keys[1], vals[0], vals[1], heap_photon, split, bounds, axis, tmp, lists[0], lists[1], lists[2], lists[3], lists[4], lists[5],
+                     pseg[0], pseg[1], segbegin, pivot_key, sctx_dev, skeys[0], skeys[1], sids[0], sids[1]};
     for (void *t : temps) if (t) cudaFreeAsync(t, st);
   }
   { void *own[] = {px, py, pz, node, shade, orig, cbox, gpos, srec, hint}; for (void *t : own) if (t) cudaFreeAsync(t, st); }      // only after a failure
