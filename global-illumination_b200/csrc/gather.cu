@@ -24,6 +24,7 @@
 #include <cuda_runtime.h>
 #include <math.h>
 #include <stdint.h>
+#include <stdlib.h>
 #include <string>
 #include "context.h"
 #include "gather.h"
@@ -35,6 +36,9 @@ namespace gi {
 #define GI_HIST_BINS 128          /* histogram of the exact cut (4 bins per lane) */
 /* per-warp shared memory: cap candidates (8 B d2 + 4 B slot), the histogram, one row of walk keys per group row above gp */
 #define GI_WARP_BYTES(cap, rows) ((size_t)(cap) * 12 + GI_HIST_BINS * 4 + (size_t)(rows) * 128)
+/* STAGE: + a two-slot ring of bottom-row position blocks (x[32] y[32] z[32], and the level-6 block of a six-level row) */
+#define GI_STAGE_SLOT_BYTES(deep) ((deep) ? 1536u : 768u)
+#define GI_STAGE_BYTES(deep) (2u * GI_STAGE_SLOT_BYTES(deep))
 
 // The per-warp buffers are addressed through 32-bit shared-window addresses and ld/st.shared: with C++ pointers the
 // compiler re-derived the window base (S2R SR_CgaCtaId + 12 integer ops) in every iteration of the walk.
@@ -43,6 +47,14 @@ __device__ __forceinline__ uint32_t lds_u32(uint32_t a) { uint32_t v; asm volati
 __device__ __forceinline__ void sts_f64(uint32_t a, double v) { asm volatile("st.shared.f64 [%0], %1;" ::"r"(a), "d"(v)); }
 __device__ __forceinline__ void sts_u32(uint32_t a, uint32_t v) { asm volatile("st.shared.u32 [%0], %1;" ::"r"(a), "r"(v)); }
 __device__ __forceinline__ void red_u32(uint32_t a, uint32_t v) { asm volatile("red.shared.add.u32 [%0], %1;" ::"r"(a), "r"(v)); }
+
+// cp.async (LDGSTS): 8 bytes global -> shared without passing through a register; .ca keeps the line in L1, where the
+// other warps of the SM (neighbouring queries) find it
+__device__ __forceinline__ void cp_async8(uint32_t dst, const void *src) {
+  asm volatile("cp.async.ca.shared.global [%0], [%1], 8;" ::"r"(dst), "l"(src) : "memory");
+}
+__device__ __forceinline__ void cp_async_commit() { asm volatile("cp.async.commit_group;" ::: "memory"); }
+template <int N> __device__ __forceinline__ void cp_async_wait() { asm volatile("cp.async.wait_group %0;" ::"n"(N) : "memory"); }
 
 struct WarpBuf {
   uint32_t a_d2, a_slot, a_hist, a_keys;          // shared memory: candidates (d2, heap slot), histogram bins, walk keys
@@ -262,7 +274,208 @@ __device__ __forceinline__ double box_dist2(const double *__restrict__ cbox_lane
   return ((dx * dx) + (dy * dy) + (dz * dz)) * 0.99999999999999;
 }
 
-template <bool DEEP>          // DEEP: bottom groups are 6 levels deep (m.hb == 6), a second round of 32 photons
+// The tail of a query, shared by the walking kernel and the small-map kernel: radiance estimate over the kept candidates
+// (photon_utils.cpp:80-161) and the outputs.  `mine` = word `lane` of the query record (17 doubles), bound = the largest
+// kept d^2 when k candidates are held, raw = buffer entries to look at (dropped ones carry d2 < 0).
+__device__ __forceinline__ void estimate_and_store(const WarpBuf &b, const PhotonMapDev &m, const GatherArgs &ga, double mine, int count, int raw,
+                                                   double bound, int k, int lane, uint64_t qi, int32_t *idx_out, int32_t *count_out,
+                                                   double *rgb_out) {
+  // ---- radiance estimate, photon_utils.cpp:80-161
+  const int found = count;
+  double est[3] = {0.0, 0.0, 0.0};
+  if (found > 0 && rgb_out) {
+    const double nx = __shfl_sync(FULL, mine, 3), ny = __shfl_sync(FULL, mine, 4), nz = __shfl_sync(FULL, mine, 5);
+    const double bx = __shfl_sync(FULL, mine, 6), by = __shfl_sync(FULL, mine, 7), bz = __shfl_sync(FULL, mine, 8);
+    const double cos_theta = __shfl_sync(FULL, mine, 9);
+    double kd[3], ks[3];
+    for (int c = 0; c < 3; c++) { kd[c] = __shfl_sync(FULL, mine, 10 + c); ks[c] = __shfl_sync(FULL, mine, 13 + c); }
+    const double shin = __shfl_sync(FULL, mine, 16);
+    const bool has_spec = ks[0] != 0.0 || ks[1] != 0.0 || ks[2] != 0.0;
+    double max_d2 = 1.0e-6;                                                   // RN_EPSILON
+    if (found < k) max_d2 = ga.r2;
+    else max_d2 = fmax(max_d2, bound);                                        // bound == max kept d^2 after finish()
+    double c1 = 1.0, c2 = 1.0, total_w = 0.0;
+    if (ga.filter == GI_FILTER_CONE) c1 = 1.0 / (ga.fk * sqrt(max_d2));
+    else if (ga.filter == GI_FILTER_GAUSS) { c1 = exp(-ga.fb); c2 = 1.0 / (2.0 * max_d2); }
+    for (int i = lane; i < raw; i += 32) {
+      const double d2i = b.d2(i);
+      if (d2i < 0.0) continue;                                                // dropped by the last cut
+      const double2 *rec = m.srec + 2 * (size_t)b.slot(i);
+      const double2 ra = rec[0], rb = rec[1];
+      const double ix = ra.x, iy = ra.y, iz = rb.x;
+      const uint2 sh = make_uint2((uint32_t)__double2loint(rb.y), (uint32_t)__double2hiint(rb.y));
+      const double perp = (nx * ix) + (ny * iy) + (nz * iz);
+      if ((cos_theta < 0 && perp < 0) || (cos_theta > 0 && perp > 0)) continue;
+      const uint32_t e = sh.x >> 24;
+      if (e == 0) { if (ga.filter == GI_FILTER_GAUSS) {
+          total_w += 1.0 - (1.0 - pow(c1, c2 * d2i)) / (1.0 - c1); } continue; }
+      const double inv = __longlong_as_double((long long)(e - 136 + 1023) << 52);   // ldexp(1.0, e - 128 - 8)
+      double rgb[3] = {(double)(sh.x & 0xff) * inv, (double)((sh.x >> 8) & 0xff) * inv, (double)((sh.x >> 16) & 0xff) * inv};
+      double cos_alpha = (bx * -ix) + (by * -iy) + (bz * -iz);
+      if (cos_alpha < 0) cos_alpha = 0;
+      const double pw = has_spec ? pow(cos_alpha, shin) : 0.0;
+      const double ap = fabs(perp);
+      for (int c = 0; c < 3; c++) rgb[c] *= ap * kd[c] + pw * ks[c];
+      if (ga.filter == GI_FILTER_CONE) {
+        const double w = 1.0 - c1 * sqrt(d2i);
+        for (int c = 0; c < 3; c++) rgb[c] *= w;
+      } else if (ga.filter == GI_FILTER_GAUSS) {
+        const double w = 1.0 - (1.0 - pow(c1, c2 * d2i)) / (1.0 - c1);
+        for (int c = 0; c < 3; c++) rgb[c] *= w;
+        total_w += w;
+      }
+      for (int c = 0; c < 3; c++) est[c] += rgb[c];
+    }
+    for (int o = 16; o > 0; o >>= 1) {
+      for (int c = 0; c < 3; c++) est[c] += __shfl_xor_sync(FULL, est[c], o);
+      total_w += __shfl_xor_sync(FULL, total_w, o);
+    }
+    const double PI = 3.14159265358979323846;
+    if (ga.filter == GI_FILTER_DISK && max_d2 > 0) { for (int c = 0; c < 3; c++) est[c] /= PI * max_d2; }
+    else if (ga.filter == GI_FILTER_CONE && max_d2 > 0) { for (int c = 0; c < 3; c++) est[c] /= (1.0 - 2.0 / 3.0 / ga.fk) * PI * max_d2; }
+    else if (ga.filter == GI_FILTER_GAUSS && total_w > 0 && max_d2 > 0) {
+      for (int c = 0; c < 3; c++) est[c] *= ga.fa * (found / total_w) / (PI * max_d2);
+    } else { est[0] = est[1] = est[2] = 0.0; }
+  }
+  if (rgb_out && lane == 0) { rgb_out[3 * qi] = est[0]; rgb_out[3 * qi + 1] = est[1]; rgb_out[3 * qi + 2] = est[2]; }
+  if (count_out && lane == 0) count_out[qi] = found;
+  if (idx_out) {
+    // ascending photon indices: put the index into the d2 column (exact in a double) and sort on it
+    for (int i = lane; i < b.cap; i += 32) b.set_d2(i, i < found ? (double)b.orig[b.slot(i)] : INFINITY);
+    __syncwarp();
+    bitonic_sort(b, lane);
+    for (int i = lane; i < k; i += 32) idx_out[qi * (uint64_t)k + i] = i < found ? (int32_t)b.d2(i) : -1;
+  }
+}
+
+// ------------------------------------------------------------------------------------------------ small maps
+// A default frame sends 97 % of its gathers to the GLOBAL map: ~2 000 photons (52 KB of positions: it lives in L1), k = 50,
+// billions of queries.  Walking a kd-tree per query is the wrong shape for that.  Here a warp takes a CHUNK of 32 queries
+// that are neighbours on the Morton curve (millimetres apart, against a k-th distance of decimetres) and
+//   1. finds the exact k-th distance R of the chunk's first query c by brute force over the whole map,
+//   2. collects ONCE the pool of photons within R + 2 rho of c (rho = the chunk's radius around c): every query q of the
+//      chunk has its k nearest within R + |q - c| of itself (that ball contains c's), hence within R + 2 rho of c,
+//   3. ranks every query against the pool only (a few dozen photons): exact FP64 distances, the same histogram cut and
+//      the same estimate as the walking kernel -- identical kNN sets, ties by photon index.
+// A chunk whose pool does not fit (scattered queries: small unsorted batches) scans the whole map per query instead.
+#define GI_SMALL_MAX_PHOTONS 8192
+#define GI_SMALL_POOL 256            /* pool entries per chunk (u16 heap slots) */
+#define GI_SMALL_CHUNK 32
+#define GI_SMALL_WARPS 24
+#define GI_SMALL_WARP_BYTES(cap) (GI_WARP_BYTES(cap, 0) + GI_SMALL_POOL * 2)
+
+__device__ __forceinline__ uint32_t lds_u16(uint32_t a) { uint16_t v; asm volatile("ld.shared.u16 %0, [%1];" : "=h"(v) : "r"(a)); return v; }
+__device__ __forceinline__ void sts_u16(uint32_t a, uint32_t v) { asm volatile("st.shared.u16 [%0], %1;" ::"r"(a), "h"((uint16_t)v)); }
+
+__global__ void __launch_bounds__(GI_SMALL_WARPS * 32, 1)
+gather_small_kernel(PhotonMapDev m, const GiGatherQuery *__restrict__ queries, const uint32_t *__restrict__ order, uint64_t nq,
+                    GatherArgs ga, unsigned long long *work_counter, int32_t *idx_out, int32_t *count_out, double *rgb_out) {
+  extern __shared__ double smem[];
+  const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+  WarpBuf b; b.cap = ga.cap; b.orig = m.orig;
+  { const int room = ga.cap - 32; b.limit = room < ga.k + ga.slack ? room : ga.k + ga.slack; }
+  uint32_t a_pool;
+  {
+    uint32_t base = (uint32_t)__cvta_generic_to_shared(smem) + (uint32_t)warp * (uint32_t)GI_SMALL_WARP_BYTES(ga.cap);
+    asm volatile("" : "+r"(base));
+    b.a_d2 = base; b.a_slot = base + (uint32_t)ga.cap * 8u; b.a_hist = b.a_slot + (uint32_t)ga.cap * 4u; b.a_keys = 0;
+    a_pool = b.a_hist + GI_HIST_BINS * 4u;
+  }
+  const int k = ga.k;
+  const uint32_t n = (uint32_t)m.n;
+  const uint32_t lt_mask = (1u << lane) - 1u;
+  const uint64_t nchunks = (nq + GI_SMALL_CHUNK - 1) / GI_SMALL_CHUNK;
+  while (true) {
+    unsigned long long chunk = 0;
+    if (lane == 0) chunk = atomicAdd(work_counter, 1ull);
+    chunk = __shfl_sync(FULL, chunk, 0);
+    if (chunk >= nchunks) break;
+    const uint64_t q0 = chunk * GI_SMALL_CHUNK;
+    const int nqc = (int)(nq - q0 < GI_SMALL_CHUNK ? nq - q0 : GI_SMALL_CHUNK);
+    // lane i holds query i of the chunk
+    uint64_t my_qi = 0; double mx = 0.0, my = 0.0, mz = 0.0;
+    if (lane < nqc) {
+      my_qi = order ? (uint64_t)order[q0 + lane] : q0 + lane;
+      const double *qp = (const double *)(queries + my_qi);
+      mx = qp[0]; my = qp[1]; mz = qp[2];
+    }
+    const double cx = __shfl_sync(FULL, mx, 0), cy = __shfl_sync(FULL, my, 0), cz = __shfl_sync(FULL, mz, 0);
+    double my_rho2 = 0.0;
+    if (lane < nqc) { const double dx = mx - cx, dy = my - cy, dz = mz - cz; my_rho2 = (dx * dx) + (dy * dy) + (dz * dz); }
+    double rho2 = my_rho2;
+    for (int o = 16; o > 0; o >>= 1) rho2 = fmax(rho2, __shfl_xor_sync(FULL, rho2, o));
+    // ---- 1. the chunk centre's exact k nearest, brute force over the map (heap order; px / py / pz are L1-resident)
+    int count = 0, raw = 0;
+    double bound = ga.r2;
+    for (uint32_t base = 0; base < n; base += 32) {
+      const uint32_t slot = base + (uint32_t)lane;
+      bool pred = false; double d2 = 0.0;
+      if (slot < n) { const P3 p = {m.px[slot], m.py[slot], m.pz[slot]}; d2 = dist2(p, cx, cy, cz); pred = d2 <= bound; }
+      append(b, count, bound, k, lane, lt_mask, pred, d2, slot);
+    }
+    finish(b, count, raw, bound, k, lane, true);
+    const bool centre_full = count >= k;
+    const double Rc = sqrt(centre_full ? bound : ga.r2);
+    // ---- 2. the pool: everything within Rc + 2 rho of the centre
+    const double Rp = (Rc + 2.0 * sqrt(rho2)) * (1.0 + 1.0e-9);
+    const double Rp2 = Rp * Rp;
+    int npool = 0;
+    for (uint32_t base = 0; base < n && npool <= GI_SMALL_POOL; base += 32) {
+      const uint32_t slot = base + (uint32_t)lane;
+      bool pred = false;
+      if (slot < n) { const P3 p = {m.px[slot], m.py[slot], m.pz[slot]}; pred = dist2(p, cx, cy, cz) <= Rp2; }
+      const unsigned mask = __ballot_sync(FULL, pred);
+      const int at = npool + __popc(mask & lt_mask);
+      if (pred && at < GI_SMALL_POOL) sts_u16(a_pool + 2u * (uint32_t)at, slot);
+      npool += __popc(mask);
+    }
+    const bool pooled = npool <= GI_SMALL_POOL;
+    __syncwarp();
+    // ---- 3. every query of the chunk against the pool
+    for (int qq = 0; qq < nqc; qq++) {
+      const uint64_t qi = __shfl_sync(FULL, my_qi, qq);
+      const double qx = __shfl_sync(FULL, mx, qq), qy = __shfl_sync(FULL, my, qq), qz = __shfl_sync(FULL, mz, qq);
+      const double *qp = (const double *)(queries + qi);
+      const double mine = lane < 17 ? qp[lane] : 0.0;
+      count = 0; raw = 0;
+      bound = ga.r2;
+      if (centre_full) {                                    // k photons lie within Rc of c, hence within Rc + |q - c| of q
+        const double rq = (Rc + sqrt(__shfl_sync(FULL, my_rho2, qq))) * (1.0 + 1.0e-12);
+        bound = fmin(ga.r2, rq * rq);
+      }
+      if (n > 0) {
+        if (pooled) {
+          for (int base = 0; base < npool; base += 32) {
+            const int i = base + lane;
+            bool pred = false; double d2 = 0.0; uint32_t slot = 0;
+            if (i < npool) {
+              slot = lds_u16(a_pool + 2u * (uint32_t)i);
+              const P3 p = {m.px[slot], m.py[slot], m.pz[slot]};
+              d2 = dist2(p, qx, qy, qz); pred = d2 <= bound;
+            }
+            append(b, count, bound, k, lane, lt_mask, pred, d2, slot);
+          }
+        } else {
+          for (uint32_t base = 0; base < n; base += 32) {
+            const uint32_t slot = base + (uint32_t)lane;
+            bool pred = false; double d2 = 0.0;
+            if (slot < n) { const P3 p = {m.px[slot], m.py[slot], m.pz[slot]}; d2 = dist2(p, qx, qy, qz); pred = d2 <= bound; }
+            append(b, count, bound, k, lane, lt_mask, pred, d2, slot);
+          }
+        }
+        finish(b, count, raw, bound, k, lane, idx_out != nullptr);
+      }
+      estimate_and_store(b, m, ga, mine, count, raw, bound, k, lane, qi, idx_out, count_out, rgb_out);
+      __syncwarp();
+    }
+  }
+}
+
+// DEEP: bottom groups are 6 levels deep (m.hb == 6), a second round of 32 photons.
+// STAGE: the position blocks of the bottom-row scan are staged in shared memory by cp.async (a two-slot ring per warp:
+// the copy of the next touched group is in flight while the current one is tested) instead of being prefetched into
+// 6-12 FP64 registers per lane.
+template <bool DEEP, bool STAGE>
 __global__ void __launch_bounds__(GI_GATHER_MAX_WARPS * 32, 1)
 gather_kernel(PhotonMapDev m, const double *__restrict__ lut, const GiGatherQuery *__restrict__ queries,
               const uint32_t *__restrict__ order, uint64_t nq, GatherArgs ga, unsigned long long *work_counter, int32_t *idx_out,
@@ -272,11 +485,14 @@ gather_kernel(PhotonMapDev m, const double *__restrict__ lut, const GiGatherQuer
   WarpBuf b; b.cap = ga.cap; b.orig = m.orig;
   { const int room = ga.cap - (DEEP ? 64 : 32); b.limit = room < ga.k + ga.slack ? room : ga.k + ga.slack; }   // 32 (64) arrive at once
   {
-    uint32_t base = (uint32_t)__cvta_generic_to_shared(smem) + (uint32_t)warp * (uint32_t)GI_WARP_BYTES(ga.cap, ga.key_rows);
+    uint32_t base = (uint32_t)__cvta_generic_to_shared(smem) +
+                    (uint32_t)warp * ((uint32_t)GI_WARP_BYTES(ga.cap, ga.key_rows) + (STAGE ? GI_STAGE_BYTES(DEEP) : 0u));
     asm volatile("" : "+r"(base));                          // opaque: keep it in a register instead of re-deriving it
     b.a_d2 = base; b.a_slot = base + (uint32_t)ga.cap * 8u; b.a_hist = b.a_slot + (uint32_t)ga.cap * 4u;
     b.a_keys = b.a_hist + GI_HIST_BINS * 4u;
   }
+  // STAGE: this lane's words of ring slot 0 (x at +0, y at +256, z at +512; level 6 at +768 ...); slot 1 follows
+  const uint32_t a_stage = b.a_keys + (uint32_t)ga.key_rows * 128u + 8u * (uint32_t)lane;
   const int k = ga.k;
   const uint64_t n = m.n;
   const int jl = 31 - __clz(lane + 1);                      // relative depth of this lane's photon inside a group
@@ -373,7 +589,65 @@ gather_kernel(PhotonMapDev m, const double *__restrict__ lut, const GiGatherQuer
               // ---- bottom groups under this one: branch-light loop, the next group's block is always in flight
               const float kf = __double2float_rd(bd);
               unsigned todo = __ballot_sync(FULL, (double)kf <= bound);
-              if (todo) {
+              if (todo && STAGE) {
+                // ---- staged variant: the blocks go global -> shared by cp.async, one group ahead
+                uint32_t ls = cbase + (uint32_t)(__ffs(todo) - 1); todo &= todo - 1;
+                bool has6 = DEEP && ls - bottom_first < m.x6_blocks;
+                uint32_t slot_a = a_stage;
+                {
+                  const double *p = gpos_lane + (size_t)(ls + bottom_delta) * 96;
+                  cp_async8(slot_a, p); cp_async8(slot_a + 256u, p + 32); cp_async8(slot_a + 512u, p + 64);
+                  if (has6) {
+                    const double *q6 = gpos_lane + (size_t)(m.x6_base + (ls - bottom_first)) * 96;
+                    cp_async8(slot_a + 768u, q6); cp_async8(slot_a + 1024u, q6 + 32); cp_async8(slot_a + 1280u, q6 + 64);
+                  }
+                  cp_async_commit();
+                }
+                while (true) {
+                  const bool more = todo != 0;
+                  const uint32_t ls_n = cbase + (more ? (uint32_t)(__ffs(todo) - 1) : 0u);
+                  todo &= todo - 1;
+                  const bool has6_n = DEEP && ls_n - bottom_first < m.x6_blocks;
+                  const uint32_t other = a_stage + (slot_a == a_stage ? GI_STAGE_SLOT_BYTES(DEEP) : 0u);
+                  if (more) {
+                    const double *p = gpos_lane + (size_t)(ls_n + bottom_delta) * 96;
+                    cp_async8(other, p); cp_async8(other + 256u, p + 32); cp_async8(other + 512u, p + 64);
+                    if (has6_n) {
+                      const double *q6 = gpos_lane + (size_t)(m.x6_base + (ls_n - bottom_first)) * 96;
+                      cp_async8(other + 768u, q6); cp_async8(other + 1024u, q6 + 32); cp_async8(other + 1280u, q6 + 64);
+                    }
+                  }
+                  cp_async_commit();
+                  cp_async_wait<1>();                                   // everything but the group just committed has landed
+                  P3 cur; cur.x = lds_f64(slot_a); cur.y = lds_f64(slot_a + 256u); cur.z = lds_f64(slot_a + 512u);
+                  const double d2a = dist2(cur, qx, qy, qz);
+                  double d2b = 0.0;
+                  const bool pa = d2a <= bound; bool pb = false;
+                  unsigned mb = 0u;
+                  if (has6) {
+                    P3 low; low.x = lds_f64(slot_a + 768u); low.y = lds_f64(slot_a + 1024u); low.z = lds_f64(slot_a + 1280u);
+                    d2b = dist2(low, qx, qy, qz); pb = d2b <= bound; mb = __ballot_sync(FULL, pb);
+                  }
+                  const unsigned ma = __ballot_sync(FULL, pa);
+                  if (ma | mb) {
+                    const int na = __popc(ma);
+                    if (pa) { const int pos = count + __popc(ma & lt_mask); b.set_d2(pos, d2a); b.set_slot(pos, (ls << jl) + (uint32_t)lane); }
+                    if (pb) {
+                      const int pos = count + na + __popc(mb & lt_mask);
+                      b.set_d2(pos, d2b); b.set_slot(pos, (((ls + 1) << GI_GROUP_LEVELS) - 1) + (uint32_t)lane);
+                    }
+                    count += na + __popc(mb);
+                    __syncwarp();
+                    if (count > b.limit) {
+                      const Sel r = cut(b, count, bound, k, lane, true); count = r.count; bound = r.bound;
+                      todo &= __ballot_sync(FULL, (double)kf <= bound);
+                    }
+                  }
+                  if (!more) break;
+                  ls = ls_n; has6 = has6_n; slot_a = other;
+                }
+                cp_async_wait<0>();
+              } else if (todo) {
                 uint32_t ls = cbase + (uint32_t)(__ffs(todo) - 1); todo &= todo - 1;
                 bool has6 = DEEP && ls - bottom_first < m.x6_blocks;                            // uniform: the group has a level 6
                 P3 cur = load_group(gpos_lane, ls + bottom_delta);
@@ -436,72 +710,7 @@ gather_kernel(PhotonMapDev m, const double *__restrict__ lut, const GiGatherQuer
       }
       guess = count >= k ? bound * ga.guess_factor : ga.r2;
     }
-    // ---- radiance estimate, photon_utils.cpp:80-161
-    const int found = count;
-    double est[3] = {0.0, 0.0, 0.0};
-    if (found > 0 && rgb_out) {
-      const double nx = __shfl_sync(FULL, mine, 3), ny = __shfl_sync(FULL, mine, 4), nz = __shfl_sync(FULL, mine, 5);
-      const double bx = __shfl_sync(FULL, mine, 6), by = __shfl_sync(FULL, mine, 7), bz = __shfl_sync(FULL, mine, 8);
-      const double cos_theta = __shfl_sync(FULL, mine, 9);
-      double kd[3], ks[3];
-      for (int c = 0; c < 3; c++) { kd[c] = __shfl_sync(FULL, mine, 10 + c); ks[c] = __shfl_sync(FULL, mine, 13 + c); }
-      const double shin = __shfl_sync(FULL, mine, 16);
-      const bool has_spec = ks[0] != 0.0 || ks[1] != 0.0 || ks[2] != 0.0;
-      double max_d2 = 1.0e-6;                                                   // RN_EPSILON
-      if (found < k) max_d2 = ga.r2;
-      else max_d2 = fmax(max_d2, bound);                                        // bound == max kept d^2 after finish()
-      double c1 = 1.0, c2 = 1.0, total_w = 0.0;
-      if (ga.filter == GI_FILTER_CONE) c1 = 1.0 / (ga.fk * sqrt(max_d2));
-      else if (ga.filter == GI_FILTER_GAUSS) { c1 = exp(-ga.fb); c2 = 1.0 / (2.0 * max_d2); }
-      for (int i = lane; i < raw; i += 32) {
-        const double d2i = b.d2(i);
-        if (d2i < 0.0) continue;                                                // dropped by the last cut
-        const double2 *rec = m.srec + 2 * (size_t)b.slot(i);
-        const double2 ra = rec[0], rb = rec[1];
-        const double ix = ra.x, iy = ra.y, iz = rb.x;
-        const uint2 sh = make_uint2((uint32_t)__double2loint(rb.y), (uint32_t)__double2hiint(rb.y));
-        const double perp = (nx * ix) + (ny * iy) + (nz * iz);
-        if ((cos_theta < 0 && perp < 0) || (cos_theta > 0 && perp > 0)) continue;
-        const uint32_t e = sh.x >> 24;
-        if (e == 0) { if (ga.filter == GI_FILTER_GAUSS) {
-            total_w += 1.0 - (1.0 - pow(c1, c2 * d2i)) / (1.0 - c1); } continue; }
-        const double inv = __longlong_as_double((long long)(e - 136 + 1023) << 52);   // ldexp(1.0, e - 128 - 8)
-        double rgb[3] = {(double)(sh.x & 0xff) * inv, (double)((sh.x >> 8) & 0xff) * inv, (double)((sh.x >> 16) & 0xff) * inv};
-        double cos_alpha = (bx * -ix) + (by * -iy) + (bz * -iz);
-        if (cos_alpha < 0) cos_alpha = 0;
-        const double pw = has_spec ? pow(cos_alpha, shin) : 0.0;
-        const double ap = fabs(perp);
-        for (int c = 0; c < 3; c++) rgb[c] *= ap * kd[c] + pw * ks[c];
-        if (ga.filter == GI_FILTER_CONE) {
-          const double w = 1.0 - c1 * sqrt(d2i);
-          for (int c = 0; c < 3; c++) rgb[c] *= w;
-        } else if (ga.filter == GI_FILTER_GAUSS) {
-          const double w = 1.0 - (1.0 - pow(c1, c2 * d2i)) / (1.0 - c1);
-          for (int c = 0; c < 3; c++) rgb[c] *= w;
-          total_w += w;
-        }
-        for (int c = 0; c < 3; c++) est[c] += rgb[c];
-      }
-      for (int o = 16; o > 0; o >>= 1) {
-        for (int c = 0; c < 3; c++) est[c] += __shfl_xor_sync(FULL, est[c], o);
-        total_w += __shfl_xor_sync(FULL, total_w, o);
-      }
-      const double PI = 3.14159265358979323846;
-      if (ga.filter == GI_FILTER_DISK && max_d2 > 0) { for (int c = 0; c < 3; c++) est[c] /= PI * max_d2; }
-      else if (ga.filter == GI_FILTER_CONE && max_d2 > 0) { for (int c = 0; c < 3; c++) est[c] /= (1.0 - 2.0 / 3.0 / ga.fk) * PI * max_d2; }
-      else if (ga.filter == GI_FILTER_GAUSS && total_w > 0 && max_d2 > 0) {
-        for (int c = 0; c < 3; c++) est[c] *= ga.fa * (found / total_w) / (PI * max_d2);
-      } else { est[0] = est[1] = est[2] = 0.0; }
-    }
-    if (rgb_out && lane == 0) { rgb_out[3 * qi] = est[0]; rgb_out[3 * qi + 1] = est[1]; rgb_out[3 * qi + 2] = est[2]; }
-    if (count_out && lane == 0) count_out[qi] = found;
-    if (idx_out) {
-      // ascending photon indices: put the index into the d2 column (exact in a double) and sort on it
-      for (int i = lane; i < b.cap; i += 32) b.set_d2(i, i < found ? (double)b.orig[b.slot(i)] : INFINITY);
-      __syncwarp();
-      bitonic_sort(b, lane);
-      for (int i = lane; i < k; i += 32) idx_out[qi * (uint64_t)k + i] = i < found ? (int32_t)b.d2(i) : -1;
-    }
+    estimate_and_store(b, m, ga, mine, count, raw, bound, k, lane, qi, idx_out, count_out, rgb_out);
     __syncwarp();
   }
   }   // chunks
@@ -524,8 +733,34 @@ cudaError_t launch_gather(GiContext *ctx, const PhotonMapDev &m, const double *d
                           const uint32_t *d_order, uint64_t nq, const GatherArgs &ga_in, int32_t *d_idx, int32_t *d_count, double *d_rgb,
                           cudaStream_t st) {
   GatherArgs ga = ga_in;
+  // maps of a few thousand photons (the global map of a default frame): chunk-pooled brute force, no tree walk
+  static const bool small_on = getenv("GI_GATHER_SMALL") && atoi(getenv("GI_GATHER_SMALL")) != 0;       // A/B hook
+  if (m.n > 0 && m.n <= GI_SMALL_MAX_PHOTONS && small_on) {
+    const size_t per_warp_s = GI_SMALL_WARP_BYTES(ga.cap);
+    int warps_s = GI_SMALL_WARPS;
+    while (warps_s > 1 && (size_t)warps_s * per_warp_s > 160 * 1024) warps_s -= 4;
+    const size_t smem_s = (size_t)warps_s * per_warp_s;
+    if (smem_s > ctx->gather_small_smem_configured) {
+      cudaError_t e = cudaFuncSetAttribute(gather_small_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem_s);
+      if (e != cudaSuccess) return e;
+      ctx->gather_small_smem_configured = smem_s;
+    }
+    unsigned long long *counter = work_counter(ctx, st);
+    if (!counter) return cudaErrorMemoryAllocation;
+    { cudaError_t e = cudaMemsetAsync(counter, 0, sizeof(unsigned long long), st); if (e != cudaSuccess) return e; }
+    const uint64_t nchunks_s = (nq + GI_SMALL_CHUNK - 1) / GI_SMALL_CHUNK;
+    const uint64_t want_s = (nchunks_s + warps_s - 1) / warps_s, cap_s = (uint64_t)ctx->sm_count;
+    gather_small_kernel<<<(unsigned)(want_s < cap_s ? want_s : cap_s), warps_s * 32, smem_s, st>>>(m, d_q, d_order, nq, ga, counter, d_idx, d_count, d_rgb);
+    ctx->launches++;
+    return cudaGetLastError();
+  }
   ga.key_rows = m.groups > 2 ? m.groups - 2 : 0;
-  const size_t per_warp = GI_WARP_BYTES(ga.cap, ga.key_rows);
+  const bool deep = m.hb > GI_GROUP_LEVELS;
+  // GI_GATHER_STAGE=1: the cp.async-staged bottom-row scan (measured slower than register prefetch, see
+  // docs/experiments/r02_gather_cp_async_stage.md; kept selectable)
+  static const bool stage_env = getenv("GI_GATHER_STAGE") && atoi(getenv("GI_GATHER_STAGE")) != 0;
+  const bool stage = stage_env && m.groups >= 2;
+  const size_t per_warp = GI_WARP_BYTES(ga.cap, ga.key_rows) + (stage ? GI_STAGE_BYTES(deep) : 0u);
   int warps = (int)((227 * 1024) / per_warp);
   if (warps > GI_GATHER_MAX_WARPS) warps = GI_GATHER_MAX_WARPS;
   if (ga.max_warps > 0 && warps > ga.max_warps) warps = ga.max_warps;
@@ -533,13 +768,18 @@ cudaError_t launch_gather(GiContext *ctx, const PhotonMapDev &m, const double *d
   const uint64_t nchunks = (nq + GI_GATHER_CHUNK - 1) / GI_GATHER_CHUNK;
   if ((uint64_t)warps > nchunks) warps = (int)nchunks;
   const size_t smem = (size_t)warps * per_warp;
-  const bool deep = m.hb > GI_GROUP_LEVELS;
   // the attribute is per DEVICE (and per kernel instantiation): remembered in the context, which is bound to one device
-  if (smem > ctx->gather_smem_configured[deep]) {
-    cudaError_t e = deep ? cudaFuncSetAttribute(gather_kernel<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem)
-                         : cudaFuncSetAttribute(gather_kernel<false>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
+  const int variant = (deep ? 1 : 0) + (stage ? 2 : 0);
+  if (smem > ctx->gather_smem_configured[variant]) {
+    cudaError_t e = cudaSuccess;
+    switch (variant) {
+      case 0: e = cudaFuncSetAttribute(gather_kernel<false, false>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem); break;
+      case 1: e = cudaFuncSetAttribute(gather_kernel<true, false>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem); break;
+      case 2: e = cudaFuncSetAttribute(gather_kernel<false, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem); break;
+      default: e = cudaFuncSetAttribute(gather_kernel<true, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem); break;
+    }
     if (e != cudaSuccess) return e;
-    ctx->gather_smem_configured[deep] = smem;
+    ctx->gather_smem_configured[variant] = smem;
   }
   // range of consecutive chunks a CTA fetches at a time: 4 per warp, fewer when the launch is small (balance)
   {
@@ -555,8 +795,12 @@ cudaError_t launch_gather(GiContext *ctx, const PhotonMapDev &m, const double *d
   { cudaError_t e = cudaMemsetAsync(counter, 0, sizeof(unsigned long long), st); if (e != cudaSuccess) return e; }
   const uint64_t want = (nchunks + warps - 1) / warps;
   const unsigned grid = (unsigned)(want < (uint64_t)ctx->sm_count ? want : (uint64_t)ctx->sm_count);
-  if (deep) gather_kernel<true><<<grid, warps * 32, smem, st>>>(m, d_lut, d_q, d_order, nq, ga, counter, d_idx, d_count, d_rgb);
-  else gather_kernel<false><<<grid, warps * 32, smem, st>>>(m, d_lut, d_q, d_order, nq, ga, counter, d_idx, d_count, d_rgb);
+  switch (variant) {
+    case 0: gather_kernel<false, false><<<grid, warps * 32, smem, st>>>(m, d_lut, d_q, d_order, nq, ga, counter, d_idx, d_count, d_rgb); break;
+    case 1: gather_kernel<true, false><<<grid, warps * 32, smem, st>>>(m, d_lut, d_q, d_order, nq, ga, counter, d_idx, d_count, d_rgb); break;
+    case 2: gather_kernel<false, true><<<grid, warps * 32, smem, st>>>(m, d_lut, d_q, d_order, nq, ga, counter, d_idx, d_count, d_rgb); break;
+    default: gather_kernel<true, true><<<grid, warps * 32, smem, st>>>(m, d_lut, d_q, d_order, nq, ga, counter, d_idx, d_count, d_rgb); break;
+  }
   ctx->launches++;
   return cudaGetLastError();
 }
@@ -613,8 +857,8 @@ static cudaError_t launch_gather_counter(GiContext *ctx, const PhotonMapDev &m, 
   const size_t smem = (size_t)warps * per_warp;
   const bool deep = m.hb > GI_GROUP_LEVELS;
   if (smem > ctx->gather_smem_configured[deep]) {
-    cudaError_t e = deep ? cudaFuncSetAttribute(gather_kernel<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem)
-                         : cudaFuncSetAttribute(gather_kernel<false>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
+    cudaError_t e = deep ? cudaFuncSetAttribute(gather_kernel<true, false>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem)
+                         : cudaFuncSetAttribute(gather_kernel<false, false>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
     if (e != cudaSuccess) return e;
     ctx->gather_smem_configured[deep] = smem;
   }
@@ -626,8 +870,8 @@ static cudaError_t launch_gather_counter(GiContext *ctx, const PhotonMapDev &m, 
   { cudaError_t e = cudaMemsetAsync(counter, 0, sizeof(unsigned long long), st); if (e != cudaSuccess) return e; }
   const uint64_t want = (nchunks + warps - 1) / warps;
   const unsigned grid = (unsigned)(want < (uint64_t)ctx->sm_count ? want : (uint64_t)ctx->sm_count);
-  if (deep) gather_kernel<true><<<grid, warps * 32, smem, st>>>(m, d_lut, d_q, d_order, nq, ga, counter, d_idx, d_count, d_rgb);
-  else gather_kernel<false><<<grid, warps * 32, smem, st>>>(m, d_lut, d_q, d_order, nq, ga, counter, d_idx, d_count, d_rgb);
+  if (deep) gather_kernel<true, false><<<grid, warps * 32, smem, st>>>(m, d_lut, d_q, d_order, nq, ga, counter, d_idx, d_count, d_rgb);
+  else gather_kernel<false, false><<<grid, warps * 32, smem, st>>>(m, d_lut, d_q, d_order, nq, ga, counter, d_idx, d_count, d_rgb);
   ctx->launches++;
   return cudaGetLastError();
 }
