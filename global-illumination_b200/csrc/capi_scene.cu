@@ -114,6 +114,7 @@ void gi_destroy(GiContext *ctx) {
     if (ctx->pipe[i]) cudaStreamDestroy(ctx->pipe[i]);
   }
   for (int j = 0; j < 5; j++) ctx->order_ws[2][j].release();
+  for (int j = 0; j < 3; j++) ctx->small_ws[j].release();
   ctx->clock.release();
   cudaFree(ctx->gather_counters);
   cudaFree(ctx->d_lut);

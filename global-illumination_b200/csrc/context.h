@@ -47,6 +47,7 @@ struct GiContext {
   GiScratch stage[2][4];                      // per slot: input, and up to three outputs
   GiScratch order_ws[3][5];                   // query_order.cu, per stream slot (pipe[0], pipe[1], any other): keys x2, order x2, sort temp
   size_t gather_smem_configured[4] = {0, 0, 0, 0};  // gather.cu: dynamic shared memory the kernel variants (deep x staged) are configured for on this device
+  GiScratch small_ws[3];                      // gather.cu: chunk records + pools of the small-map kernels, per stream slot
   size_t gather_small_smem_configured = 0;     // gather.cu: the same for the small-map kernel
   unsigned char *noalloc_scratch = nullptr;   // gather.cu: device address of its static scratch array on this context's device (cudaGetSymbolAddress, once)
   double *d_lut = nullptr;                    // capi_photon.cu: the 65536 x 3 incident-direction table (photon_utils.cpp:253-272)

@@ -24,6 +24,7 @@
 #include <cuda_runtime.h>
 #include <math.h>
 #include <stdint.h>
+#include <stdio.h>
 #include <stdlib.h>
 #include <string>
 #include "context.h"
@@ -358,28 +359,239 @@ __device__ __forceinline__ void estimate_and_store(const WarpBuf &b, const Photo
 //   3. ranks every query against the pool only (a few dozen photons): exact FP64 distances, the same histogram cut and
 //      the same estimate as the walking kernel -- identical kNN sets, ties by photon index.
 // A chunk whose pool does not fit (scattered queries: small unsorted batches) scans the whole map per query instead.
+// debug counters of the small-map kernel (GI_GATHER_DEBUG=1 prints them after every launch): chunks, chunks whose pool did
+// not fit, chunks ranked by the slow (histogram) path, pool entries, centre searches that found fewer than k
+__device__ unsigned long long g_small_dbg[8];
 #define GI_SMALL_MAX_PHOTONS 8192
 #define GI_SMALL_POOL 256            /* pool entries per chunk (u16 heap slots) */
 #define GI_SMALL_CHUNK 32
 #define GI_SMALL_WARPS 24
-#define GI_SMALL_WARP_BYTES(cap) (GI_WARP_BYTES(cap, 0) + GI_SMALL_POOL * 2)
+#define GI_SMALL_SHELL 16            /* shell entries per lane kept for the exact pick of the k-th (8 B d2 + 2 B slot each) */
 
 __device__ __forceinline__ uint32_t lds_u16(uint32_t a) { uint16_t v; asm volatile("ld.shared.u16 %0, [%1];" : "=h"(v) : "r"(a)); return v; }
 __device__ __forceinline__ void sts_u16(uint32_t a, uint32_t v) { asm volatile("st.shared.u16 [%0], %1;" ::"r"(a), "h"((uint16_t)v)); }
 
+// ---- thread-per-query ranking of a chunk (small-map kernel, radiance only).  Every lane owns one query of the chunk; the
+// pool is walked by all lanes together, so every photon is one uniform (broadcast) load and the distance test, the
+// selection and the estimate run for 32 queries per instruction.  The exact k-th (d2, photon index) of a lane is found
+// without storing distances: up to three passes refine a 16-bin histogram (packed 16-bit counters in four registers, bins
+// with exact edges) around the bin that holds the k-th candidate; what is left in that bin (usually one or two photons)
+// is ordered exactly by repeated minimum extraction.
+struct ThreadQuery { double nx, ny, nz, bx, by, bz, cos_theta, kd0, kd1, kd2, ks0, ks1, ks2, shin; };
+
+__device__ __forceinline__ double bin_edge(double lo, double hi, double w, int j) { return j >= 16 ? hi : lo + (double)j * w; }
+
+// one photon's term of the estimate (the loop body of estimate_and_store, photon_utils.cpp:96-150)
+__device__ __forceinline__ void photon_term(const GatherArgs &ga, const ThreadQuery &q, bool has_spec, const double2 ra, const double2 rb,
+                                            double d2i, double c1, double c2, double &e0, double &e1, double &e2, double &total_w) {
+  const double ix = ra.x, iy = ra.y, iz = rb.x;
+  const uint32_t shx = (uint32_t)__double2loint(rb.y);
+  const double perp = (q.nx * ix) + (q.ny * iy) + (q.nz * iz);
+  if ((q.cos_theta < 0 && perp < 0) || (q.cos_theta > 0 && perp > 0)) return;
+  const uint32_t e = shx >> 24;
+  if (e == 0) { if (ga.filter == GI_FILTER_GAUSS) total_w += 1.0 - (1.0 - pow(c1, c2 * d2i)) / (1.0 - c1); return; }
+  const double inv = __longlong_as_double((long long)(e - 136 + 1023) << 52);
+  double r0 = (double)(shx & 0xff) * inv, r1 = (double)((shx >> 8) & 0xff) * inv, r2 = (double)((shx >> 16) & 0xff) * inv;
+  double cos_alpha = (q.bx * -ix) + (q.by * -iy) + (q.bz * -iz);
+  if (cos_alpha < 0) cos_alpha = 0;
+  const double pw = has_spec ? pow(cos_alpha, q.shin) : 0.0;
+  const double ap = fabs(perp);
+  r0 *= ap * q.kd0 + pw * q.ks0; r1 *= ap * q.kd1 + pw * q.ks1; r2 *= ap * q.kd2 + pw * q.ks2;
+  if (ga.filter == GI_FILTER_CONE) { const double w = 1.0 - c1 * sqrt(d2i); r0 *= w; r1 *= w; r2 *= w; }
+  else if (ga.filter == GI_FILTER_GAUSS) { const double w = 1.0 - (1.0 - pow(c1, c2 * d2i)) / (1.0 - c1); r0 *= w; r1 *= w; r2 *= w; total_w += w; }
+  e0 += r0; e1 += r1; e2 += r2;
+}
+
+// np pool entries: heap slots in shared memory (pooled) or simply all slots 0 .. np-1 of the map.
+// active: this lane owns a query; bound: its search bound (all of its k nearest lie within, d2 <= bound).
+__device__ __forceinline__ void rank_chunk_per_thread(const PhotonMapDev &m, const GatherArgs &ga, uint32_t a_pool, uint32_t a_shell, bool pooled, int np, bool active,
+                                                      const GiGatherQuery *__restrict__ queries, uint64_t qi, double qx, double qy, double qz,
+                                                      double bound, double shell_lo, int32_t *count_out, double *rgb_out) {
+  const int k = ga.k;
+  const int dbg_lane = threadIdx.x & 31;
+  // ---- selection: [lo, hi) narrows around the k-th smallest d2; `below` = candidates with d2 < lo
+  double lo = 0.0, hi = __longlong_as_double(__double_as_longlong(bound) + 1);       // d2 <= bound  <=>  d2 < hi
+  int below = 0, need = 0;
+  bool done = !active;
+  double thr_d2 = 0.0; uint32_t thr_idx = 0; bool thr_strict = true;                   // kept: d2 < thr_d2, or (!strict) d2 == thr_d2 and index <= thr_idx
+  // Fast path.  The k-th distance of a query q lies in the shell [Rc - |q - c|, Rc + |q - c|] around the centre's k-th
+  // distance Rc (fewer than k photons are nearer to c than Rc, at least k are within Rc): ONE pass counts the candidates
+  // below the shell and keeps the handful inside it in registers, the k-th is then picked among those by rank.
+  {
+    // shell lists in shared memory, entry t of lane l: d2 at a_shell + 8 (32 t + l), slot at a_shell + 8 * 32 * S + 2 (32 t + l)
+    constexpr int S = GI_SMALL_SHELL;
+    const uint32_t a_sd2 = a_shell + 8u * (uint32_t)dbg_lane, a_ss = a_shell + 8u * 32u * S + 2u * (uint32_t)dbg_lane;
+    int nb = 0, ns = 0;
+#pragma unroll 4
+    for (int i = 0; i < np; i++) {
+      const uint32_t slot = pooled ? lds_u16(a_pool + 2u * (uint32_t)i) : (uint32_t)i;
+      const P3 p = {m.px[slot], m.py[slot], m.pz[slot]};
+      const double d2 = dist2(p, qx, qy, qz);
+      if (d2 < shell_lo) nb++;
+      else if (d2 < hi) {
+        if (ns < S) { sts_f64(a_sd2 + 256u * (uint32_t)ns, d2); sts_u16(a_ss + 64u * (uint32_t)ns, slot); }
+        ns++;
+      }
+    }
+    const bool fits = ns <= S && nb < k;
+    if (__all_sync(FULL, fits || !active)) {
+      if (active) {
+        if (nb + ns <= k) { thr_d2 = hi; thr_strict = true; }                          // the whole shell is kept
+        else {
+          const int want = k - nb - 1;                                                 // rank of the k-th inside the shell, 0 <= want < ns
+          for (int t = 0; t < ns; t++) {
+            const double dt = lds_f64(a_sd2 + 256u * (uint32_t)t);
+            int rank = 0, ties = 0;
+            for (int u = 0; u < ns; u++) { const double du = lds_f64(a_sd2 + 256u * (uint32_t)u); rank += du < dt ? 1 : 0; ties += du == dt ? 1 : 0; }
+            if (rank <= want && want < rank + ties) {                                  // the k-th has this d2
+              const uint32_t ot = m.orig[lds_u16(a_ss + 64u * (uint32_t)t)];
+              int r2 = rank;
+              if (ties > 1)
+                for (int u = 0; u < ns; u++)
+                  if (lds_f64(a_sd2 + 256u * (uint32_t)u) == dt && m.orig[lds_u16(a_ss + 64u * (uint32_t)u)] < ot) r2++;
+              if (r2 == want) { thr_d2 = dt; thr_idx = ot; thr_strict = false; break; }
+            }
+          }
+        }
+      }
+      done = true;
+    } else if (dbg_lane == 0) atomicAdd(&g_small_dbg[2], 1ull);
+    __syncwarp();
+  }
+  for (int pass = 0; pass < 3; pass++) {
+    if (__all_sync(FULL, done)) break;
+    const double w = (hi - lo) * (1.0 / 16.0);
+    const double scale = w > 0.0 ? 1.0 / w : 0.0;
+    unsigned long long c0 = 0ull, c1 = 0ull, c2 = 0ull, c3 = 0ull;                 // 16 counters of 16 bits (np <= 8192)
+#pragma unroll 2
+    for (int i = 0; i < np; i++) {
+      const uint32_t slot = pooled ? lds_u16(a_pool + 2u * (uint32_t)i) : (uint32_t)i;
+      const P3 p = {m.px[slot], m.py[slot], m.pz[slot]};
+      const double d2 = dist2(p, qx, qy, qz);
+      if (d2 >= lo && d2 < hi) {
+        int bin = (int)((d2 - lo) * scale);
+        bin = bin > 15 ? 15 : bin;
+        if (bin > 0 && d2 < bin_edge(lo, hi, w, bin)) bin--;                           // exact edges: the next pass tests against them
+        else if (bin < 15 && d2 >= bin_edge(lo, hi, w, bin + 1)) bin++;
+        const unsigned long long inc = 1ull << (16 * (bin & 3));
+        const int word = bin >> 2;
+        c0 += word == 0 ? inc : 0ull; c1 += word == 1 ? inc : 0ull; c2 += word == 2 ? inc : 0ull; c3 += word == 3 ? inc : 0ull;
+      }
+    }
+    if (!done) {
+      const unsigned long long cw[4] = {c0, c1, c2, c3};
+      int total = 0;
+      for (int j = 0; j < 16; j++) total += (int)((cw[j >> 2] >> (16 * (j & 3))) & 0xffff);
+      if (below + total <= k) { thr_d2 = hi; thr_strict = true; done = true; }      // everything in range is kept
+      else {
+        int cum = 0, B = 0, mB = 0;
+        for (int j = 0; j < 16; j++) {
+          const int c = (int)((cw[j >> 2] >> (16 * (j & 3))) & 0xffff);
+          if (below + cum + c >= k) { B = j; mB = c; break; }
+          cum += c;
+        }
+        below += cum; need = k - below;                                               // 1 <= need <= mB
+        const double nlo = bin_edge(lo, hi, w, B), nhi = bin_edge(lo, hi, w, B + 1);
+        lo = nlo; hi = nhi;
+        if (need == mB) { thr_d2 = hi; thr_strict = true; done = true; }              // the whole bin is kept
+      }
+    }
+  }
+  // ---- what is left in [lo, hi): the `need` smallest by (d2, photon index), one minimum per pass
+  if (!__all_sync(FULL, done)) {
+    double last_d2 = -1.0; uint32_t last_idx = 0; int left = done ? 0 : need;
+    while (__any_sync(FULL, left > 0)) {
+      double best_d2 = INFINITY; uint32_t best_idx = 0xffffffffu;
+      for (int i = 0; i < np; i++) {
+        const uint32_t slot = pooled ? lds_u16(a_pool + 2u * (uint32_t)i) : (uint32_t)i;
+        const P3 p = {m.px[slot], m.py[slot], m.pz[slot]};
+        const double d2 = dist2(p, qx, qy, qz);
+        if (left > 0 && d2 >= lo && d2 < hi && d2 >= last_d2 && d2 <= best_d2) {
+          const uint32_t oi = m.orig[slot];
+          const bool after_last = d2 > last_d2 || (last_d2 >= 0.0 && oi > last_idx) || last_d2 < 0.0;
+          if (after_last && (d2 < best_d2 || oi < best_idx)) { best_d2 = d2; best_idx = oi; }
+        }
+      }
+      if (left > 0) { last_d2 = best_d2; last_idx = best_idx; left--; }
+    }
+    if (!done) { thr_d2 = last_d2; thr_idx = last_idx; thr_strict = false; done = true; }
+  }
+  // ---- the query record (17 doubles per lane)
+  ThreadQuery q;
+  const double *qp = (const double *)(queries + qi);
+  if (active) {
+    q.nx = qp[3]; q.ny = qp[4]; q.nz = qp[5]; q.bx = qp[6]; q.by = qp[7]; q.bz = qp[8]; q.cos_theta = qp[9];
+    q.kd0 = qp[10]; q.kd1 = qp[11]; q.kd2 = qp[12]; q.ks0 = qp[13]; q.ks1 = qp[14]; q.ks2 = qp[15]; q.shin = qp[16];
+  } else { q.nx = q.ny = q.nz = q.bx = q.by = q.bz = q.cos_theta = q.kd0 = q.kd1 = q.kd2 = q.ks0 = q.ks1 = q.ks2 = q.shin = 0.0; }
+  const bool has_spec = q.ks0 != 0.0 || q.ks1 != 0.0 || q.ks2 != 0.0;
+  // ---- number found and the largest kept d2 (the filters other than the disk need them before the sum)
+  int found = 0; double maxkept = 0.0;
+  if (ga.filter != GI_FILTER_DISK) {
+    for (int i = 0; i < np; i++) {
+      const uint32_t slot = pooled ? lds_u16(a_pool + 2u * (uint32_t)i) : (uint32_t)i;
+      const P3 p = {m.px[slot], m.py[slot], m.pz[slot]};
+      const double d2 = dist2(p, qx, qy, qz);
+      bool in = d2 < thr_d2;
+      if (!thr_strict && d2 == thr_d2) in = m.orig[slot] <= thr_idx;
+      if (in) { found++; maxkept = fmax(maxkept, d2); }
+    }
+  }
+  double max_d2 = 1.0e-6, c1 = 1.0, c2 = 1.0;
+  if (ga.filter != GI_FILTER_DISK) {
+    max_d2 = found < k ? ga.r2 : fmax(1.0e-6, maxkept);
+    if (ga.filter == GI_FILTER_CONE) c1 = 1.0 / (ga.fk * sqrt(max_d2));
+    else { c1 = exp(-ga.fb); c2 = 1.0 / (2.0 * max_d2); }
+    found = 0; maxkept = 0.0;
+  }
+  // ---- the estimate over the kept photons
+  double e0 = 0.0, e1 = 0.0, e2 = 0.0, total_w = 0.0;
+#pragma unroll 2
+  for (int i = 0; i < np; i++) {
+    const uint32_t slot = pooled ? lds_u16(a_pool + 2u * (uint32_t)i) : (uint32_t)i;
+    const P3 p = {m.px[slot], m.py[slot], m.pz[slot]};
+    const double d2 = dist2(p, qx, qy, qz);
+    bool in = d2 < thr_d2;
+    if (!thr_strict && d2 == thr_d2) in = m.orig[slot] <= thr_idx;
+    if (in) {
+      found++; maxkept = fmax(maxkept, d2);
+      if (rgb_out) {
+        const double2 *rec = m.srec + 2 * (size_t)slot;
+        photon_term(ga, q, has_spec, rec[0], rec[1], d2, c1, c2, e0, e1, e2, total_w);
+      }
+    }
+  }
+  if (!active) return;
+  if (ga.filter == GI_FILTER_DISK) max_d2 = found < k ? ga.r2 : fmax(1.0e-6, maxkept);
+  const double PI = 3.14159265358979323846;
+  if (found > 0 && ga.filter == GI_FILTER_DISK && max_d2 > 0) { e0 /= PI * max_d2; e1 /= PI * max_d2; e2 /= PI * max_d2; }
+  else if (found > 0 && ga.filter == GI_FILTER_CONE && max_d2 > 0) { const double dn = (1.0 - 2.0 / 3.0 / ga.fk) * PI * max_d2; e0 /= dn; e1 /= dn; e2 /= dn; }
+  else if (found > 0 && ga.filter == GI_FILTER_GAUSS && total_w > 0 && max_d2 > 0) { const double f = ga.fa * (found / total_w) / (PI * max_d2); e0 *= f; e1 *= f; e2 *= f; }
+  else { e0 = e1 = e2 = 0.0; }
+  if (rgb_out) { rgb_out[3 * qi] = e0; rgb_out[3 * qi + 1] = e1; rgb_out[3 * qi + 2] = e2; }
+  if (count_out) count_out[qi] = found;
+}
+
+// Two kernels, so that the warps of an SM run one phase's code at a time (one fused kernel spent 5 cycles per issued
+// instruction waiting for instruction fetch): gather_small_kernel does the centre search and the pool of every chunk and
+// leaves them in global memory (SmallChunk + 256 u16 slots per chunk); small_rank_kernel ranks a lane per query.  Chunks
+// that cannot be pooled -- and every chunk when the index output is wanted -- are finished by the first kernel, a warp per
+// query, and marked npool = -1.
+struct SmallChunk { double cx, cy, cz, Rc; int32_t npool, centre_full; double pad; };       // 48 bytes
+
 __global__ void __launch_bounds__(GI_SMALL_WARPS * 32, 1)
 gather_small_kernel(PhotonMapDev m, const GiGatherQuery *__restrict__ queries, const uint32_t *__restrict__ order, uint64_t nq,
-                    GatherArgs ga, unsigned long long *work_counter, int32_t *idx_out, int32_t *count_out, double *rgb_out) {
+                    GatherArgs ga, unsigned long long *work_counter, SmallChunk *__restrict__ info, uint16_t *__restrict__ pools,
+                    int32_t *idx_out, int32_t *count_out, double *rgb_out) {
   extern __shared__ double smem[];
   const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
   WarpBuf b; b.cap = ga.cap; b.orig = m.orig;
   { const int room = ga.cap - 32; b.limit = room < ga.k + ga.slack ? room : ga.k + ga.slack; }
   uint32_t a_pool;
   {
-    uint32_t base = (uint32_t)__cvta_generic_to_shared(smem) + (uint32_t)warp * (uint32_t)GI_SMALL_WARP_BYTES(ga.cap);
+    uint32_t base = (uint32_t)__cvta_generic_to_shared(smem) + (uint32_t)warp * ((uint32_t)GI_WARP_BYTES(ga.cap, 0) + GI_SMALL_POOL * 2u);
     asm volatile("" : "+r"(base));
     b.a_d2 = base; b.a_slot = base + (uint32_t)ga.cap * 8u; b.a_hist = b.a_slot + (uint32_t)ga.cap * 4u; b.a_keys = 0;
-    a_pool = b.a_hist + GI_HIST_BINS * 4u;
+    a_pool = base + (uint32_t)GI_WARP_BYTES(ga.cap, 0);
   }
   const int k = ga.k;
   const uint32_t n = (uint32_t)m.n;
@@ -399,7 +611,10 @@ gather_small_kernel(PhotonMapDev m, const GiGatherQuery *__restrict__ queries, c
       const double *qp = (const double *)(queries + my_qi);
       mx = qp[0]; my = qp[1]; mz = qp[2];
     }
-    const double cx = __shfl_sync(FULL, mx, 0), cy = __shfl_sync(FULL, my, 0), cz = __shfl_sync(FULL, mz, 0);
+    // centre of the chunk: the centroid of its queries (any point would do; this one keeps the chunk radius small)
+    double cx = lane < nqc ? mx : 0.0, cy = lane < nqc ? my : 0.0, cz = lane < nqc ? mz : 0.0;
+    for (int o = 16; o > 0; o >>= 1) { cx += __shfl_xor_sync(FULL, cx, o); cy += __shfl_xor_sync(FULL, cy, o); cz += __shfl_xor_sync(FULL, cz, o); }
+    cx /= (double)nqc; cy /= (double)nqc; cz /= (double)nqc;
     double my_rho2 = 0.0;
     if (lane < nqc) { const double dx = mx - cx, dy = my - cy, dz = mz - cz; my_rho2 = (dx * dx) + (dy * dy) + (dz * dz); }
     double rho2 = my_rho2;
@@ -430,8 +645,19 @@ gather_small_kernel(PhotonMapDev m, const GiGatherQuery *__restrict__ queries, c
       npool += __popc(mask);
     }
     const bool pooled = npool <= GI_SMALL_POOL;
+    if (lane == 0) {
+      atomicAdd(&g_small_dbg[0], 1ull); if (!pooled) atomicAdd(&g_small_dbg[1], 1ull);
+      atomicAdd(&g_small_dbg[3], (unsigned long long)npool); if (!centre_full) atomicAdd(&g_small_dbg[4], 1ull);
+    }
     __syncwarp();
-    // ---- 3. every query of the chunk against the pool
+    // ---- 3. pooled chunks are ranked by small_rank_kernel (a lane per query); the others right here, a warp per query
+    if (!idx_out && pooled) {
+      if (lane == 0) { SmallChunk ci; ci.cx = cx; ci.cy = cy; ci.cz = cz; ci.Rc = Rc; ci.npool = npool; ci.centre_full = centre_full ? 1 : 0; ci.pad = 0.0; info[chunk] = ci; }
+      for (int i = lane; i < npool; i += 32) pools[chunk * GI_SMALL_POOL + i] = (uint16_t)lds_u16(a_pool + 2u * (uint32_t)i);
+      __syncwarp();
+      continue;
+    }
+    if (!idx_out && lane == 0) info[chunk].npool = -1;
     for (int qq = 0; qq < nqc; qq++) {
       const uint64_t qi = __shfl_sync(FULL, my_qi, qq);
       const double qx = __shfl_sync(FULL, mx, qq), qy = __shfl_sync(FULL, my, qq), qz = __shfl_sync(FULL, mz, qq);
@@ -468,6 +694,47 @@ gather_small_kernel(PhotonMapDev m, const GiGatherQuery *__restrict__ queries, c
       estimate_and_store(b, m, ga, mine, count, raw, bound, k, lane, qi, idx_out, count_out, rgb_out);
       __syncwarp();
     }
+  }
+}
+
+__global__ void __launch_bounds__(GI_SMALL_WARPS * 32, 1)
+small_rank_kernel(PhotonMapDev m, const GiGatherQuery *__restrict__ queries, const uint32_t *__restrict__ order, uint64_t nq, GatherArgs ga,
+                  unsigned long long *work_counter, const SmallChunk *__restrict__ info, const uint16_t *__restrict__ pools, int32_t *count_out,
+                  double *rgb_out) {
+  extern __shared__ double smem[];
+  const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+  uint32_t a_shell = (uint32_t)__cvta_generic_to_shared(smem) + (uint32_t)warp * (32u * GI_SMALL_SHELL * 10u + GI_SMALL_POOL * 2u);
+  asm volatile("" : "+r"(a_shell));
+  const uint32_t a_pool = a_shell + 32u * GI_SMALL_SHELL * 10u;
+  const uint64_t nchunks = (nq + GI_SMALL_CHUNK - 1) / GI_SMALL_CHUNK;
+  while (true) {
+    unsigned long long chunk = 0;
+    if (lane == 0) chunk = atomicAdd(work_counter, 1ull);
+    chunk = __shfl_sync(FULL, chunk, 0);
+    if (chunk >= nchunks) break;
+    const SmallChunk ci = info[chunk];
+    if (ci.npool < 0) continue;
+    for (int i = lane; i < ci.npool; i += 32) sts_u16(a_pool + 2u * (uint32_t)i, pools[chunk * GI_SMALL_POOL + i]);
+    const uint64_t q0 = chunk * GI_SMALL_CHUNK;
+    const int nqc = (int)(nq - q0 < GI_SMALL_CHUNK ? nq - q0 : GI_SMALL_CHUNK);
+    uint64_t my_qi = 0; double mx = 0.0, my = 0.0, mz = 0.0, my_rho2 = 0.0;
+    if (lane < nqc) {
+      my_qi = order ? (uint64_t)order[q0 + lane] : q0 + lane;
+      const double *qp = (const double *)(queries + my_qi);
+      mx = qp[0]; my = qp[1]; mz = qp[2];
+      const double dx = mx - ci.cx, dy = my - ci.cy, dz = mz - ci.cz;
+      my_rho2 = (dx * dx) + (dy * dy) + (dz * dz);                 // the same expression as in gather_small_kernel: the pool radius covers it
+    }
+    double bq = ga.r2, shell_lo = 0.0;
+    if (ci.centre_full) {
+      const double rq = sqrt(my_rho2);
+      const double up = (ci.Rc + rq) * (1.0 + 1.0e-12);
+      bq = fmin(ga.r2, up * up);
+      if (ci.Rc > rq) { const double dn = (ci.Rc - rq) * (1.0 - 1.0e-12); shell_lo = dn * dn; }
+    }
+    __syncwarp();
+    rank_chunk_per_thread(m, ga, a_pool, a_shell, true, ci.npool, lane < nqc, queries, my_qi, mx, my, mz, bq, shell_lo, count_out, rgb_out);
+    __syncwarp();
   }
 }
 
@@ -719,7 +986,7 @@ gather_kernel(PhotonMapDev m, const double *__restrict__ lut, const GiGatherQuer
 
 // launch-wide chunk counter, one per stream slot of the context (pipe[0], pipe[1], any other stream)
 static unsigned long long *work_counter(GiContext *ctx, cudaStream_t st) {
-  if (!ctx->gather_counters && cudaMalloc(&ctx->gather_counters, 3 * sizeof(unsigned long long)) != cudaSuccess) {
+  if (!ctx->gather_counters && cudaMalloc(&ctx->gather_counters, 8 * sizeof(unsigned long long)) != cudaSuccess) {
     ctx->gather_counters = nullptr;
     return nullptr;
   }
@@ -734,24 +1001,51 @@ cudaError_t launch_gather(GiContext *ctx, const PhotonMapDev &m, const double *d
                           cudaStream_t st) {
   GatherArgs ga = ga_in;
   // maps of a few thousand photons (the global map of a default frame): chunk-pooled brute force, no tree walk
-  static const bool small_on = getenv("GI_GATHER_SMALL") && atoi(getenv("GI_GATHER_SMALL")) != 0;       // A/B hook
-  if (m.n > 0 && m.n <= GI_SMALL_MAX_PHOTONS && small_on) {
-    const size_t per_warp_s = GI_SMALL_WARP_BYTES(ga.cap);
+  static const bool small_off = getenv("GI_GATHER_SMALL") && atoi(getenv("GI_GATHER_SMALL")) == 0;      // A/B hook
+  if (m.n > 0 && m.n <= GI_SMALL_MAX_PHOTONS && !small_off) {
+    const size_t per_warp_s = GI_WARP_BYTES(ga.cap, 0) + GI_SMALL_POOL * 2;
     int warps_s = GI_SMALL_WARPS;
-    while (warps_s > 1 && (size_t)warps_s * per_warp_s > 160 * 1024) warps_s -= 4;
+    while (warps_s > 4 && (size_t)warps_s * per_warp_s > 160 * 1024) warps_s -= 4;
     const size_t smem_s = (size_t)warps_s * per_warp_s;
+    const size_t smem_r = (size_t)GI_SMALL_WARPS * (32u * GI_SMALL_SHELL * 10u + GI_SMALL_POOL * 2u);
     if (smem_s > ctx->gather_small_smem_configured) {
       cudaError_t e = cudaFuncSetAttribute(gather_small_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem_s);
+      if (e == cudaSuccess) e = cudaFuncSetAttribute(small_rank_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem_r);
       if (e != cudaSuccess) return e;
       ctx->gather_small_smem_configured = smem_s;
     }
     unsigned long long *counter = work_counter(ctx, st);
     if (!counter) return cudaErrorMemoryAllocation;
     { cudaError_t e = cudaMemsetAsync(counter, 0, sizeof(unsigned long long), st); if (e != cudaSuccess) return e; }
+    { cudaError_t e = cudaMemsetAsync(counter + 3, 0, sizeof(unsigned long long), st); if (e != cudaSuccess) return e; }
     const uint64_t nchunks_s = (nq + GI_SMALL_CHUNK - 1) / GI_SMALL_CHUNK;
+    // pools and chunk records of this launch: grow-only scratch per stream slot (like the ordering scratch)
+    const int sslot = st == ctx->pipe[0] ? 0 : (st == ctx->pipe[1] ? 1 : 2);
+    SmallChunk *info = nullptr; uint16_t *pools = nullptr;
+    if (!d_idx) {
+      GiScratch &ws = ctx->small_ws[sslot];
+      const size_t info_bytes = ((sizeof(SmallChunk) * nchunks_s + 255) / 256) * 256;
+      if (!ws.fit(info_bytes + (size_t)nchunks_s * GI_SMALL_POOL * 2)) return cudaErrorMemoryAllocation;
+      info = (SmallChunk *)ws.p; pools = (uint16_t *)((unsigned char *)ws.p + info_bytes);
+    }
     const uint64_t want_s = (nchunks_s + warps_s - 1) / warps_s, cap_s = (uint64_t)ctx->sm_count;
-    gather_small_kernel<<<(unsigned)(want_s < cap_s ? want_s : cap_s), warps_s * 32, smem_s, st>>>(m, d_q, d_order, nq, ga, counter, d_idx, d_count, d_rgb);
+    gather_small_kernel<<<(unsigned)(want_s < cap_s ? want_s : cap_s), warps_s * 32, smem_s, st>>>(m, d_q, d_order, nq, ga, counter, info, pools, d_idx, d_count,
+                                                                                                    d_rgb);
     ctx->launches++;
+    if (!d_idx) {
+      const uint64_t want_r = (nchunks_s + GI_SMALL_WARPS - 1) / GI_SMALL_WARPS;
+      small_rank_kernel<<<(unsigned)(want_r < cap_s ? want_r : cap_s), GI_SMALL_WARPS * 32, smem_r, st>>>(m, d_q, d_order, nq, ga, counter + 3, info, pools, d_count,
+                                                                                                         d_rgb);
+      ctx->launches++;
+    }
+    static const bool dbg = getenv("GI_GATHER_DEBUG") && atoi(getenv("GI_GATHER_DEBUG")) != 0;
+    if (dbg) {
+      unsigned long long h[8] = {0}, z[8] = {0};
+      cudaStreamSynchronize(st);
+      cudaMemcpyFromSymbol(h, g_small_dbg, sizeof(h)); cudaMemcpyToSymbol(g_small_dbg, z, sizeof(z));
+      fprintf(stderr, "[gather_small] queries %llu chunks %llu pool overflow %llu slow path %llu mean pool %.1f centre<k %llu\n", (unsigned long long)nq, h[0], h[1],
+              h[2], h[0] ? (double)h[3] / h[0] : 0.0, h[4]);
+    }
     return cudaGetLastError();
   }
   ga.key_rows = m.groups > 2 ? m.groups - 2 : 0;
