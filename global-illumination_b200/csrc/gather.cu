@@ -363,9 +363,10 @@ __device__ __forceinline__ void estimate_and_store(const WarpBuf &b, const Photo
 // not fit, chunks ranked by the slow (histogram) path, pool entries, centre searches that found fewer than k
 __device__ unsigned long long g_small_dbg[8];
 #define GI_SMALL_MAX_PHOTONS 8192
-#define GI_SMALL_POOL 256            /* pool entries per chunk (u16 heap slots) */
+#define GI_SMALL_POOL 128            /* pool entries per chunk (u16 heap slots; the rank kernel also stages their positions) */
 #define GI_SMALL_CHUNK 32
 #define GI_SMALL_WARPS 24
+#define GI_SMALL_RANK_BYTES (32u * GI_SMALL_SHELL * 10u + 24u * GI_SMALL_POOL + 2u * GI_SMALL_POOL)   /* rank kernel, per warp */
 #define GI_SMALL_SHELL 16            /* shell entries per lane kept for the exact pick of the k-th (8 B d2 + 2 B slot each) */
 
 __device__ __forceinline__ uint32_t lds_u16(uint32_t a) { uint16_t v; asm volatile("ld.shared.u16 %0, [%1];" : "=h"(v) : "r"(a)); return v; }
@@ -402,9 +403,9 @@ __device__ __forceinline__ void photon_term(const GatherArgs &ga, const ThreadQu
   e0 += r0; e1 += r1; e2 += r2;
 }
 
-// np pool entries: heap slots in shared memory (pooled) or simply all slots 0 .. np-1 of the map.
+// np pool entries: positions at a_pos (x[POOL] y[POOL] z[POOL]) and heap slots at a_pool, both in shared memory.
 // active: this lane owns a query; bound: its search bound (all of its k nearest lie within, d2 <= bound).
-__device__ __forceinline__ void rank_chunk_per_thread(const PhotonMapDev &m, const GatherArgs &ga, uint32_t a_pool, uint32_t a_shell, bool pooled, int np, bool active,
+__device__ __forceinline__ void rank_chunk_per_thread(const PhotonMapDev &m, const GatherArgs &ga, uint32_t a_pool, uint32_t a_pos, uint32_t a_shell, int np, bool active,
                                                       const GiGatherQuery *__restrict__ queries, uint64_t qi, double qx, double qy, double qz,
                                                       double bound, double shell_lo, int32_t *count_out, double *rgb_out) {
   const int k = ga.k;
@@ -424,12 +425,11 @@ __device__ __forceinline__ void rank_chunk_per_thread(const PhotonMapDev &m, con
     int nb = 0, ns = 0;
 #pragma unroll 4
     for (int i = 0; i < np; i++) {
-      const uint32_t slot = pooled ? lds_u16(a_pool + 2u * (uint32_t)i) : (uint32_t)i;
-      const P3 p = {m.px[slot], m.py[slot], m.pz[slot]};
+      const P3 p = {lds_f64(a_pos + 8u * (uint32_t)i), lds_f64(a_pos + 8u * (GI_SMALL_POOL + (uint32_t)i)), lds_f64(a_pos + 8u * (2u * GI_SMALL_POOL + (uint32_t)i))};
       const double d2 = dist2(p, qx, qy, qz);
       if (d2 < shell_lo) nb++;
       else if (d2 < hi) {
-        if (ns < S) { sts_f64(a_sd2 + 256u * (uint32_t)ns, d2); sts_u16(a_ss + 64u * (uint32_t)ns, slot); }
+        if (ns < S) { sts_f64(a_sd2 + 256u * (uint32_t)ns, d2); sts_u16(a_ss + 64u * (uint32_t)ns, lds_u16(a_pool + 2u * (uint32_t)i)); }
         ns++;
       }
     }
@@ -465,8 +465,7 @@ __device__ __forceinline__ void rank_chunk_per_thread(const PhotonMapDev &m, con
     unsigned long long c0 = 0ull, c1 = 0ull, c2 = 0ull, c3 = 0ull;                 // 16 counters of 16 bits (np <= 8192)
 #pragma unroll 2
     for (int i = 0; i < np; i++) {
-      const uint32_t slot = pooled ? lds_u16(a_pool + 2u * (uint32_t)i) : (uint32_t)i;
-      const P3 p = {m.px[slot], m.py[slot], m.pz[slot]};
+      const P3 p = {lds_f64(a_pos + 8u * (uint32_t)i), lds_f64(a_pos + 8u * (GI_SMALL_POOL + (uint32_t)i)), lds_f64(a_pos + 8u * (2u * GI_SMALL_POOL + (uint32_t)i))};
       const double d2 = dist2(p, qx, qy, qz);
       if (d2 >= lo && d2 < hi) {
         int bin = (int)((d2 - lo) * scale);
@@ -503,11 +502,10 @@ __device__ __forceinline__ void rank_chunk_per_thread(const PhotonMapDev &m, con
     while (__any_sync(FULL, left > 0)) {
       double best_d2 = INFINITY; uint32_t best_idx = 0xffffffffu;
       for (int i = 0; i < np; i++) {
-        const uint32_t slot = pooled ? lds_u16(a_pool + 2u * (uint32_t)i) : (uint32_t)i;
-        const P3 p = {m.px[slot], m.py[slot], m.pz[slot]};
+        const P3 p = {lds_f64(a_pos + 8u * (uint32_t)i), lds_f64(a_pos + 8u * (GI_SMALL_POOL + (uint32_t)i)), lds_f64(a_pos + 8u * (2u * GI_SMALL_POOL + (uint32_t)i))};
         const double d2 = dist2(p, qx, qy, qz);
         if (left > 0 && d2 >= lo && d2 < hi && d2 >= last_d2 && d2 <= best_d2) {
-          const uint32_t oi = m.orig[slot];
+          const uint32_t oi = m.orig[lds_u16(a_pool + 2u * (uint32_t)i)];
           const bool after_last = d2 > last_d2 || (last_d2 >= 0.0 && oi > last_idx) || last_d2 < 0.0;
           if (after_last && (d2 < best_d2 || oi < best_idx)) { best_d2 = d2; best_idx = oi; }
         }
@@ -528,11 +526,10 @@ __device__ __forceinline__ void rank_chunk_per_thread(const PhotonMapDev &m, con
   int found = 0; double maxkept = 0.0;
   if (ga.filter != GI_FILTER_DISK) {
     for (int i = 0; i < np; i++) {
-      const uint32_t slot = pooled ? lds_u16(a_pool + 2u * (uint32_t)i) : (uint32_t)i;
-      const P3 p = {m.px[slot], m.py[slot], m.pz[slot]};
+      const P3 p = {lds_f64(a_pos + 8u * (uint32_t)i), lds_f64(a_pos + 8u * (GI_SMALL_POOL + (uint32_t)i)), lds_f64(a_pos + 8u * (2u * GI_SMALL_POOL + (uint32_t)i))};
       const double d2 = dist2(p, qx, qy, qz);
       bool in = d2 < thr_d2;
-      if (!thr_strict && d2 == thr_d2) in = m.orig[slot] <= thr_idx;
+      if (!thr_strict && d2 == thr_d2) in = m.orig[lds_u16(a_pool + 2u * (uint32_t)i)] <= thr_idx;
       if (in) { found++; maxkept = fmax(maxkept, d2); }
     }
   }
@@ -547,15 +544,14 @@ __device__ __forceinline__ void rank_chunk_per_thread(const PhotonMapDev &m, con
   double e0 = 0.0, e1 = 0.0, e2 = 0.0, total_w = 0.0;
 #pragma unroll 2
   for (int i = 0; i < np; i++) {
-    const uint32_t slot = pooled ? lds_u16(a_pool + 2u * (uint32_t)i) : (uint32_t)i;
-    const P3 p = {m.px[slot], m.py[slot], m.pz[slot]};
+    const P3 p = {lds_f64(a_pos + 8u * (uint32_t)i), lds_f64(a_pos + 8u * (GI_SMALL_POOL + (uint32_t)i)), lds_f64(a_pos + 8u * (2u * GI_SMALL_POOL + (uint32_t)i))};
     const double d2 = dist2(p, qx, qy, qz);
     bool in = d2 < thr_d2;
-    if (!thr_strict && d2 == thr_d2) in = m.orig[slot] <= thr_idx;
+    if (!thr_strict && d2 == thr_d2) in = m.orig[lds_u16(a_pool + 2u * (uint32_t)i)] <= thr_idx;
     if (in) {
       found++; maxkept = fmax(maxkept, d2);
       if (rgb_out) {
-        const double2 *rec = m.srec + 2 * (size_t)slot;
+        const double2 *rec = m.srec + 2 * (size_t)lds_u16(a_pool + 2u * (uint32_t)i);
         photon_term(ga, q, has_spec, rec[0], rec[1], d2, c1, c2, e0, e1, e2, total_w);
       }
     }
@@ -597,12 +593,20 @@ gather_small_kernel(PhotonMapDev m, const GiGatherQuery *__restrict__ queries, c
   const uint32_t n = (uint32_t)m.n;
   const uint32_t lt_mask = (1u << lane) - 1u;
   const uint64_t nchunks = (nq + GI_SMALL_CHUNK - 1) / GI_SMALL_CHUNK;
+  // a warp takes RANGES of up to 8 consecutive chunks (neighbours on the Morton curve; fewer in small launches, for balance): the k-th distance of one centre, widened,
+  // is the first search bound of the next -- the brute-force pass then keeps ~1.3 k candidates and needs one cut
+  double guess2 = ga.r2;
+  unsigned long long chunk = 0, range_end = 0;
   while (true) {
-    unsigned long long chunk = 0;
-    if (lane == 0) chunk = atomicAdd(work_counter, 1ull);
-    chunk = __shfl_sync(FULL, chunk, 0);
+    if (chunk >= range_end) {
+      if (lane == 0) chunk = atomicAdd(work_counter, (unsigned long long)ga.range);
+      chunk = __shfl_sync(FULL, chunk, 0);
+      range_end = chunk + (unsigned long long)ga.range;
+      guess2 = ga.r2;
+    }
     if (chunk >= nchunks) break;
-    const uint64_t q0 = chunk * GI_SMALL_CHUNK;
+    const unsigned long long this_chunk = chunk++;
+    const uint64_t q0 = this_chunk * GI_SMALL_CHUNK;
     const int nqc = (int)(nq - q0 < GI_SMALL_CHUNK ? nq - q0 : GI_SMALL_CHUNK);
     // lane i holds query i of the chunk
     uint64_t my_qi = 0; double mx = 0.0, my = 0.0, mz = 0.0;
@@ -621,16 +625,23 @@ gather_small_kernel(PhotonMapDev m, const GiGatherQuery *__restrict__ queries, c
     for (int o = 16; o > 0; o >>= 1) rho2 = fmax(rho2, __shfl_xor_sync(FULL, rho2, o));
     // ---- 1. the chunk centre's exact k nearest, brute force over the map (heap order; px / py / pz are L1-resident)
     int count = 0, raw = 0;
-    double bound = ga.r2;
-    for (uint32_t base = 0; base < n; base += 32) {
-      const uint32_t slot = base + (uint32_t)lane;
-      bool pred = false; double d2 = 0.0;
-      if (slot < n) { const P3 p = {m.px[slot], m.py[slot], m.pz[slot]}; d2 = dist2(p, cx, cy, cz); pred = d2 <= bound; }
-      append(b, count, bound, k, lane, lt_mask, pred, d2, slot);
+    double bound = fmin(ga.r2, guess2);
+    while (true) {
+      const double first = bound;
+      count = 0;
+      for (uint32_t base = 0; base < n; base += 32) {
+        const uint32_t slot = base + (uint32_t)lane;
+        bool pred = false; double d2 = 0.0;
+        if (slot < n) { const P3 p = {m.px[slot], m.py[slot], m.pz[slot]}; d2 = dist2(p, cx, cy, cz); pred = d2 <= bound; }
+        append(b, count, bound, k, lane, lt_mask, pred, d2, slot);
+      }
+      finish(b, count, raw, bound, k, lane, true);
+      if (count >= k || first >= ga.r2) break;
+      bound = ga.r2;                                          // the guess was too small: the full radius
     }
-    finish(b, count, raw, bound, k, lane, true);
     const bool centre_full = count >= k;
     const double Rc = sqrt(centre_full ? bound : ga.r2);
+    guess2 = centre_full ? bound * 2.0 : ga.r2;
     // ---- 2. the pool: everything within Rc + 2 rho of the centre
     const double Rp = (Rc + 2.0 * sqrt(rho2)) * (1.0 + 1.0e-9);
     const double Rp2 = Rp * Rp;
@@ -652,12 +663,12 @@ gather_small_kernel(PhotonMapDev m, const GiGatherQuery *__restrict__ queries, c
     __syncwarp();
     // ---- 3. pooled chunks are ranked by small_rank_kernel (a lane per query); the others right here, a warp per query
     if (!idx_out && pooled) {
-      if (lane == 0) { SmallChunk ci; ci.cx = cx; ci.cy = cy; ci.cz = cz; ci.Rc = Rc; ci.npool = npool; ci.centre_full = centre_full ? 1 : 0; ci.pad = 0.0; info[chunk] = ci; }
-      for (int i = lane; i < npool; i += 32) pools[chunk * GI_SMALL_POOL + i] = (uint16_t)lds_u16(a_pool + 2u * (uint32_t)i);
+      if (lane == 0) { SmallChunk ci; ci.cx = cx; ci.cy = cy; ci.cz = cz; ci.Rc = Rc; ci.npool = npool; ci.centre_full = centre_full ? 1 : 0; ci.pad = 0.0; info[this_chunk] = ci; }
+      for (int i = lane; i < npool; i += 32) pools[this_chunk * GI_SMALL_POOL + i] = (uint16_t)lds_u16(a_pool + 2u * (uint32_t)i);
       __syncwarp();
       continue;
     }
-    if (!idx_out && lane == 0) info[chunk].npool = -1;
+    if (!idx_out && lane == 0) info[this_chunk].npool = -1;
     for (int qq = 0; qq < nqc; qq++) {
       const uint64_t qi = __shfl_sync(FULL, my_qi, qq);
       const double qx = __shfl_sync(FULL, mx, qq), qy = __shfl_sync(FULL, my, qq), qz = __shfl_sync(FULL, mz, qq);
@@ -703,9 +714,10 @@ small_rank_kernel(PhotonMapDev m, const GiGatherQuery *__restrict__ queries, con
                   double *rgb_out) {
   extern __shared__ double smem[];
   const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
-  uint32_t a_shell = (uint32_t)__cvta_generic_to_shared(smem) + (uint32_t)warp * (32u * GI_SMALL_SHELL * 10u + GI_SMALL_POOL * 2u);
+  uint32_t a_shell = (uint32_t)__cvta_generic_to_shared(smem) + (uint32_t)warp * GI_SMALL_RANK_BYTES;
   asm volatile("" : "+r"(a_shell));
-  const uint32_t a_pool = a_shell + 32u * GI_SMALL_SHELL * 10u;
+  const uint32_t a_pos = a_shell + 32u * GI_SMALL_SHELL * 10u;             // x[POOL] y[POOL] z[POOL] of the pool's photons
+  const uint32_t a_pool = a_pos + 24u * GI_SMALL_POOL;                      // their heap slots
   const uint64_t nchunks = (nq + GI_SMALL_CHUNK - 1) / GI_SMALL_CHUNK;
   while (true) {
     unsigned long long chunk = 0;
@@ -714,7 +726,12 @@ small_rank_kernel(PhotonMapDev m, const GiGatherQuery *__restrict__ queries, con
     if (chunk >= nchunks) break;
     const SmallChunk ci = info[chunk];
     if (ci.npool < 0) continue;
-    for (int i = lane; i < ci.npool; i += 32) sts_u16(a_pool + 2u * (uint32_t)i, pools[chunk * GI_SMALL_POOL + i]);
+    for (int i = lane; i < ci.npool; i += 32) {
+      const uint32_t slot = pools[chunk * GI_SMALL_POOL + i];
+      sts_u16(a_pool + 2u * (uint32_t)i, slot);
+      sts_f64(a_pos + 8u * (uint32_t)i, m.px[slot]); sts_f64(a_pos + 8u * (GI_SMALL_POOL + (uint32_t)i), m.py[slot]);
+      sts_f64(a_pos + 8u * (2u * GI_SMALL_POOL + (uint32_t)i), m.pz[slot]);
+    }
     const uint64_t q0 = chunk * GI_SMALL_CHUNK;
     const int nqc = (int)(nq - q0 < GI_SMALL_CHUNK ? nq - q0 : GI_SMALL_CHUNK);
     uint64_t my_qi = 0; double mx = 0.0, my = 0.0, mz = 0.0, my_rho2 = 0.0;
@@ -733,7 +750,7 @@ small_rank_kernel(PhotonMapDev m, const GiGatherQuery *__restrict__ queries, con
       if (ci.Rc > rq) { const double dn = (ci.Rc - rq) * (1.0 - 1.0e-12); shell_lo = dn * dn; }
     }
     __syncwarp();
-    rank_chunk_per_thread(m, ga, a_pool, a_shell, true, ci.npool, lane < nqc, queries, my_qi, mx, my, mz, bq, shell_lo, count_out, rgb_out);
+    rank_chunk_per_thread(m, ga, a_pool, a_pos, a_shell, ci.npool, lane < nqc, queries, my_qi, mx, my, mz, bq, shell_lo, count_out, rgb_out);
     __syncwarp();
   }
 }
@@ -1007,7 +1024,7 @@ cudaError_t launch_gather(GiContext *ctx, const PhotonMapDev &m, const double *d
     int warps_s = GI_SMALL_WARPS;
     while (warps_s > 4 && (size_t)warps_s * per_warp_s > 160 * 1024) warps_s -= 4;
     const size_t smem_s = (size_t)warps_s * per_warp_s;
-    const size_t smem_r = (size_t)GI_SMALL_WARPS * (32u * GI_SMALL_SHELL * 10u + GI_SMALL_POOL * 2u);
+    const size_t smem_r = (size_t)GI_SMALL_WARPS * GI_SMALL_RANK_BYTES;
     if (smem_s > ctx->gather_small_smem_configured) {
       cudaError_t e = cudaFuncSetAttribute(gather_small_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem_s);
       if (e == cudaSuccess) e = cudaFuncSetAttribute(small_rank_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem_r);
@@ -1029,6 +1046,7 @@ cudaError_t launch_gather(GiContext *ctx, const PhotonMapDev &m, const double *d
       info = (SmallChunk *)ws.p; pools = (uint16_t *)((unsigned char *)ws.p + info_bytes);
     }
     const uint64_t want_s = (nchunks_s + warps_s - 1) / warps_s, cap_s = (uint64_t)ctx->sm_count;
+    { const uint64_t r = nchunks_s / ((uint64_t)ctx->sm_count * warps_s * 8); ga.range = (int)(r < 1 ? 1 : (r > 8 ? 8 : r)); }
     gather_small_kernel<<<(unsigned)(want_s < cap_s ? want_s : cap_s), warps_s * 32, smem_s, st>>>(m, d_q, d_order, nq, ga, counter, info, pools, d_idx, d_count,
                                                                                                     d_rgb);
     ctx->launches++;
