@@ -398,40 +398,45 @@ GI_DEV void closest_hit(const DevScene &sc, const RayD &world, HitRec &out) {
   best.tl = 0; best.pl = mk3(0, 0, 0); best.nl = mk3(0, 0, 0);
   float tmax = 1.0e6f * 1.00001f;
 
+  // Traversal in two alternating phases ("while-while"): a lane walks inner nodes (FP32 slab tests, near child first)
+  // until the next thing on its path is a LEAF, then decides that primitive in FP64.  The lanes of a warp reconverge
+  // between the phases, so the expensive exact tests run with every lane that has a candidate instead of with the one
+  // or two lanes that happen to reach a leaf in the same step.  Stack entries may be leaves (negative ids).
+  const int NONE = 0x7fffffff;
   int stack[GI_STACK]; int sp = 0;
   int cur = 0;
   while (true) {
-    const float4 *nd = sc.bvh + 4 * (size_t)cur;
-    const float4 A = nd[0], B = nd[1], C = nd[2], Dd = nd[3];
-    int c0 = __float_as_int(Dd.x), c1 = __float_as_int(Dd.y);
-    float tn0, tn1;
-    bool h0 = c0 != 0x7fffffff && slab(A.x, A.y, A.z, A.w, B.x, B.y, ox, oy, oz, ix, iy, iz, pad, tmax, &tn0);
-    bool h1 = c1 != 0x7fffffff && slab(B.z, B.w, C.x, C.y, C.z, C.w, ox, oy, oz, ix, iy, iz, pad, tmax, &tn1);
-    if (h0 && h1 && tn1 < tn0) { int ti = c0; c0 = c1; c1 = ti; }       // near child first
-    else if (!h0 && h1) { c0 = c1; h0 = true; h1 = false; }
-    int next = -1;
-    for (int k = 0; k < 2; k++) {
-      const int ch = k == 0 ? c0 : c1;
-      if (!(k == 0 ? h0 : h1)) continue;
-      if (ch < 0) {
-        const int prim = ~ch;
-        bool skip = false;
-        if (np > 0) { const int sh = sc.prim_meta[prim].y; for (int i = 0; i < np; i++) skip = skip || (poison[i] == sh); }
-        Cand c;
-        if (!skip && test_candidate(sc, prim, world, frame, lc, c) && c.tl >= 0.0) {
-          c.tw = frame_t_to_world(frame, c.tl);
-          if (c.tw <= GI_INFINITY && ((c.tw < best.tw && c.tw < GI_INFINITY) ||
-                                      (best.prim >= 0 && c.tw == best.tw && tie_wins(c, best)))) {
-            best = c;
-            tmax = (float)best.tw * 1.00001f + 1e-5f;
-          }
-        }
-      } else if (next < 0) next = ch;
-      else if (sp < GI_STACK) stack[sp++] = ch;
+    while (cur >= 0 && cur != NONE) {
+      const float4 *nd = sc.bvh + 4 * (size_t)cur;
+      const float4 A = nd[0], B = nd[1], C = nd[2], Dd = nd[3];
+      int c0 = __float_as_int(Dd.x), c1 = __float_as_int(Dd.y);
+      float tn0, tn1;
+      bool h0 = c0 != NONE && slab(A.x, A.y, A.z, A.w, B.x, B.y, ox, oy, oz, ix, iy, iz, pad, tmax, &tn0);
+      bool h1 = c1 != NONE && slab(B.z, B.w, C.x, C.y, C.z, C.w, ox, oy, oz, ix, iy, iz, pad, tmax, &tn1);
+      if (h0 && h1) {
+        if (tn1 < tn0) { const int ti = c0; c0 = c1; c1 = ti; }              // near child first
+        if (sp < GI_STACK) stack[sp++] = c1;
+        cur = c0;
+      } else if (h0) cur = c0;
+      else if (h1) cur = c1;
+      else cur = sp > 0 ? stack[--sp] : NONE;
     }
-    if (next >= 0) { cur = next; continue; }
-    if (sp == 0) break;
-    cur = stack[--sp];
+    if (cur == NONE) break;
+    {
+      const int prim = ~cur;
+      bool skip = false;
+      if (np > 0) { const int sh = sc.prim_meta[prim].y; for (int i = 0; i < np; i++) skip = skip || (poison[i] == sh); }
+      Cand c;
+      if (!skip && test_candidate(sc, prim, world, frame, lc, c) && c.tl >= 0.0) {
+        c.tw = frame_t_to_world(frame, c.tl);
+        if (c.tw <= GI_INFINITY && ((c.tw < best.tw && c.tw < GI_INFINITY) ||
+                                    (best.prim >= 0 && c.tw == best.tw && tie_wins(c, best)))) {
+          best = c;
+          tmax = (float)best.tw * 1.00001f + 1e-5f;
+        }
+      }
+    }
+    cur = sp > 0 ? stack[--sp] : NONE;
   }
   if (best.prim < 0) return;
 
