@@ -13,12 +13,20 @@
 // grow-only device buffer used by the host-buffer entry points to stage chunks (freed by gi_destroy)
 struct GiScratch {
   void *p = nullptr; size_t cap = 0;
+  // grows with 50 % headroom: batch sizes drift upwards during a frame, and every cudaFree / cudaMalloc synchronises the
+  // whole device (including the render's side stream)
   bool fit(size_t bytes) {
     if (bytes <= cap) return true;
     if (p) cudaFree(p);
     p = nullptr; cap = 0;
-    if (cudaMalloc(&p, bytes) != cudaSuccess) { p = nullptr; return false; }
-    cap = bytes;
+    const size_t want = bytes + bytes / 2;
+    if (cudaMalloc(&p, want) != cudaSuccess) {
+      p = nullptr;
+      if (cudaMalloc(&p, bytes) != cudaSuccess) { p = nullptr; return false; }
+      cap = bytes;
+      return true;
+    }
+    cap = want;
     return true;
   }
   void release() { if (p) cudaFree(p); p = nullptr; cap = 0; }

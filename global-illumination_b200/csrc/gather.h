@@ -27,4 +27,6 @@ cudaError_t launch_gather(GiContext *ctx, const PhotonMapDev &m, const double *d
 /* query_order.cu: Morton order of a device batch of queries through the map's bounding box */
 struct PhotonMapStore;
 const uint32_t *morton_order(GiContext *ctx, const PhotonMapStore &m, const GiGatherQuery *d_q, uint64_t n, cudaStream_t st, bool *failed);
+/* pre-sizes the per-stream scratch of gi_gather_batch_device for batches of up to n queries (query_order.cu) */
+bool gather_reserve(GiContext *ctx, uint64_t n, cudaStream_t st);
 }  // namespace gi

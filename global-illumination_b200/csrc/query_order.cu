@@ -57,4 +57,18 @@ const uint32_t *morton_order(GiContext *ctx, const PhotonMapStore &m, const GiGa
   return ord2;
 }
 
+// Sizes the ordering scratch of stream `st` and the small-map scratch for device batches of up to n queries, so that a
+// frame never reallocates (cudaFree / cudaMalloc synchronise the device) in the middle of its batches.
+bool gather_reserve(GiContext *ctx, uint64_t n, cudaStream_t st) {
+  const int slot = st == ctx->pipe[0] ? 0 : (st == ctx->pipe[1] ? 1 : 2);
+  GiScratch *sc = ctx->order_ws[slot];
+  size_t tmp_bytes = 0;
+  cub::DeviceRadixSort::SortPairs(nullptr, tmp_bytes, (uint32_t *)nullptr, (uint32_t *)nullptr, (uint32_t *)nullptr, (uint32_t *)nullptr,
+                                  (int)n, 0, 30, st);
+  for (int i = 0; i < 4; i++) if (!sc[i].fit(4 * n)) return false;
+  if (!sc[4].fit(tmp_bytes)) return false;
+  const uint64_t chunks = (n + 31) / 32;
+  return ctx->small_ws[slot].fit(((48 * chunks + 255) / 256) * 256 + chunks * 256);
+}
+
 }  // namespace gi

@@ -680,7 +680,14 @@ struct Workspace {
   size_t image_bytes = 0, strips_bytes = 0;
   QueueStore qg, qc;
   size_t scan_bytes = 0, hit_scan_bytes = 0, accum_doubles = 0, n_lights = 0;
+  cudaStream_t side = nullptr;                           // the finishing pass of a path batch runs here, beside the gather drains
+  cudaEvent_t ev_passes = nullptr, ev_tail = nullptr;
   bool ready = false;
+  ~Workspace() {
+    if (side) cudaStreamDestroy(side);
+    if (ev_passes) cudaEventDestroy(ev_passes);
+    if (ev_tail) cudaEventDestroy(ev_tail);
+  }
   bool init(cudaStream_t st) {
     if (ready) return true;
     if (!hits.alloc(sizeof(PrimHit) * chunk) || !n_items.alloc(4 * (chunk + 1)) || !offs.alloc(8 * (chunk + 1)) ||
@@ -692,6 +699,10 @@ struct Workspace {
     cub::DeviceScan::ExclusiveSum(nullptr, scan_bytes, n_items.as<uint32_t>(), offs.as<uint64_t>(), (int)(chunk + 1), st);
     cub::DeviceScan::InclusiveScan(nullptr, hit_scan_bytes, item_hit.as<uint32_t>(), item_hit.as<uint32_t>(), cub::Max(), (int)batch_max, st);
     if (!scan_tmp.alloc(scan_bytes) || !hit_scan_tmp.alloc(hit_scan_bytes)) return false;
+    if (!cuda_ok(cudaStreamCreateWithFlags(&side, cudaStreamNonBlocking), "cudaStreamCreate(side)") ||
+        !cuda_ok(cudaEventCreateWithFlags(&ev_passes, cudaEventDisableTiming), "cudaEventCreate") ||
+        !cuda_ok(cudaEventCreateWithFlags(&ev_tail, cudaEventDisableTiming), "cudaEventCreate"))
+      return false;
     ready = true;
     return true;
   }
@@ -725,7 +736,10 @@ void free_workspace(void *p) { delete (Workspace *)p; }
 Workspace *workspace(GiContext *ctx) {
   if (!ctx->render_ws) { ctx->render_ws = new Workspace(); ctx->render_ws_free = free_workspace; }
   Workspace *w = (Workspace *)ctx->render_ws;
-  return w->init(ctx->stream) ? w : nullptr;
+  const bool first = !w->ready;
+  if (!w->init(ctx->stream)) return nullptr;
+  if (first && !gather_reserve(ctx, Workspace::qcap, ctx->stream)) { set_error("gi_render: out of device memory (gather scratch)"); return nullptr; }
+  return w;
 }
 
 inline int grid_for(uint64_t n, int block, int sm_count, int per_sm) {
@@ -760,6 +774,27 @@ struct Renderer {
     ctx->clock.collect();
     ng = h[0]; nc = h[1];
     return true;
+  }
+  // The two halves of drain() for requests [off, off + n) of a queue (photon gathers only, not the -cache lookups): the
+  // estimates can be computed while the batch's finishing pass still runs; the commit waits until the batch is known good.
+  bool estimate_range(QueueStore &qs, unsigned long long off, unsigned long long n, int map) {
+    if (n == 0 || ctx->maps[map].dev.n == 0) return true;
+    const GiParams &p = env.p;
+    const int k = map == GI_MAP_GLOBAL ? p.global_estimate_size : p.caustic_estimate_size;
+    const double r = map == GI_MAP_GLOBAL ? p.global_estimate_dist : p.caustic_estimate_dist;
+    const int filter = map == GI_MAP_GLOBAL ? p.global_filter : p.caustic_filter;
+    ctx->clock.begin(map == GI_MAP_GLOBAL ? ST_GATHER_GLOBAL : ST_GATHER_CAUSTIC, st);
+    const int rc = gi_gather_batch_device(ctx, map, qs.view.q + off, n, k, r, filter, &p, nullptr, nullptr, qs.rgb.as<double>() + 3 * off, st);
+    ctx->clock.end(st);
+    return rc == 0;
+  }
+  bool commit_range(QueueStore &qs, unsigned long long n, int map) {
+    if (n == 0 || ctx->maps[map].dev.n == 0) return true;
+    ctx->clock.begin(ST_COMMIT, st);
+    commit_requests_kernel<<<(unsigned)((n + 255) / 256), 256, 0, st>>>(qs.view.w, qs.view.pix, qs.rgb.as<double>(), n, accum);
+    ctx->clock.end(st);
+    ctx->launches++;
+    return cuda_ok(cudaGetLastError(), "commit_requests_kernel");
   }
   // EstimateRadiance for every request of a queue, then accum += weight * estimate
   bool drain(QueueStore &qs, unsigned long long n, int map) {
@@ -901,6 +936,7 @@ static int render_accum(GiContext *ctx, const GiParams &params, int sw, int sh, 
                                                                       item_hit.as<uint32_t>());
       GI_CUDA(cub::DeviceScan::InclusiveScan(hit_scan_tmp.p, hit_scan_bytes, item_hit.as<uint32_t>(), item_hit.as<uint32_t>(), cub::Max(),
                                              (int)m, R.st));
+      bool overlap_tail = false;
       if (megakernel) {
         clk.begin(ST_PATH_SHADE, R.st);
         auto launch = [&](auto kernel) {
@@ -934,16 +970,29 @@ static int render_accum(GiContext *ctx, const GiParams &params, int sw, int sh, 
           wave_shade_kernel<MODE_INDIRECT, false><<<wgrid, 128, 0, R.st>>>(env, wv[cur], wv[cur ^ 1], item_rgb.as<double>(), path_qg, path_qc, d_stats + 1);
           clk.end(R.st);
         }
-        clk.begin(ST_PATH_FINISH, R.st);
-        wave_shade_kernel<MODE_PATH, true><<<wgrid, 128, 0, R.st>>>(env, wv[cur], wv[cur ^ 1], item_rgb.as<double>(), path_qg, path_qc, d_stats + 1);
-        wave_shade_kernel<MODE_INDIRECT, true><<<wgrid, 128, 0, R.st>>>(env, wv[cur], wv[cur ^ 1], item_rgb.as<double>(), path_qg, path_qc, d_stats + 1);
-        clk.end(R.st);
+        // The finishing pass -- a few walks of dozens of bounces, a thread each: ~1 ms with the GPU idle -- runs on a side
+        // stream while this stream already computes the estimates of the requests queued so far.  Nothing is committed
+        // before the final counts are known (a queue overflow repeats the batch).
+        overlap_tail = !p.irradiance_cache && !getenv("GI_NO_TAIL_OVERLAP");
+        cudaStream_t ts = overlap_tail ? ws.side : R.st;
+        if (overlap_tail) { GI_CUDA(cudaEventRecord(ws.ev_passes, R.st)); GI_CUDA(cudaStreamWaitEvent(ws.side, ws.ev_passes, 0)); }
+        clk.begin(ST_PATH_FINISH, ts);
+        wave_shade_kernel<MODE_PATH, true><<<wgrid, 128, 0, ts>>>(env, wv[cur], wv[cur ^ 1], item_rgb.as<double>(), path_qg, path_qc, d_stats + 1);
+        wave_shade_kernel<MODE_INDIRECT, true><<<wgrid, 128, 0, ts>>>(env, wv[cur], wv[cur ^ 1], item_rgb.as<double>(), path_qg, path_qc, d_stats + 1);
+        clk.end(ts);
+        if (overlap_tail) GI_CUDA(cudaEventRecord(ws.ev_tail, ws.side));
         ctx->launches += 2 + 3 * (uint64_t)wave_passes;
       }
       ctx->launches += 2;
       GI_CUDA(cudaGetLastError());
       ctx->launches++;
       RayStats bs;
+      unsigned long long ng1 = 0, nc1 = 0;
+      if (overlap_tail) {
+        if (!R.queue_counts(ng1, nc1)) return 1;              // counts before the tail's requests
+        if (ng1 <= qcap && nc1 <= qcap) { if (!R.estimate_range(R.qg, 0, ng1, GI_MAP_GLOBAL) || !R.estimate_range(R.qc, 0, nc1, GI_MAP_CAUSTIC)) return 1; }
+        GI_CUDA(cudaStreamWaitEvent(R.st, ws.ev_tail, 0));
+      }
       if (!R.queue_counts(ng, nc, &bs)) return 1;
       if (ng > qcap || nc > qcap) {                       // a queue overflowed: nothing was committed, repeat with fewer paths
         if (batch <= 1024) { set_error("gi_render: gather queue overflow"); return 1; }
@@ -956,7 +1005,10 @@ static int render_accum(GiContext *ctx, const GiParams &params, int sw, int sh, 
       clk.end(R.st);
       GI_CUDA(cudaGetLastError());
       ctx->launches++;
-      if (!R.drain(R.qg, ng, GI_MAP_GLOBAL) || !R.drain(R.qc, nc, GI_MAP_CAUSTIC)) return 1;
+      if (overlap_tail) {
+        if (!R.estimate_range(R.qg, ng1, ng - ng1, GI_MAP_GLOBAL) || !R.estimate_range(R.qc, nc1, nc - nc1, GI_MAP_CAUSTIC)) return 1;
+        if (!R.commit_range(R.qg, ng, GI_MAP_GLOBAL) || !R.commit_range(R.qc, nc, GI_MAP_CAUSTIC)) return 1;
+      } else if (!R.drain(R.qg, ng, GI_MAP_GLOBAL) || !R.drain(R.qc, nc, GI_MAP_CAUSTIC)) return 1;
       host_paths.shadow += bs.shadow; host_paths.monte += bs.monte; host_paths.transmissive += bs.transmissive;
       host_paths.specular += bs.specular; host_paths.indirect += bs.indirect; host_paths.caustic += bs.caustic;
       item0 += m;

@@ -35,18 +35,23 @@ struct StageClock {
     cudaEvent_t b = get(); cudaEventRecord(b, st);
     open.push_back(Pair{cur_stage, cur_a, b}); cur_stage = -1;
   }
-  // after a stream synchronisation: every recorded pair has completed
+  // after a stream synchronisation: the pairs that have completed are resolved (a pair recorded on another stream of the
+  // context -- the render's side stream -- may still be running: it stays open until the next call)
   void collect() {
+    std::vector<Pair> still;
     for (const Pair &p : open) {
+      if (cudaEventQuery(p.b) != cudaSuccess) { still.push_back(p); continue; }
       float t = 0; if (cudaEventElapsedTime(&t, p.a, p.b) == cudaSuccess) ms[p.stage] += t;
       pool.push_back(p.a); pool.push_back(p.b);
     }
-    open.clear();
+    open.swap(still);
   }
   void reset_photon() { for (int i = ST_EMIT_FILTER; i <= ST_KD_BUILD; i++) ms[i] = 0; }
   void reset_render() { for (int i = ST_PRIMARY; i < ST_COUNT; i++) ms[i] = 0; }
   void release() {
     collect();
+    for (const Pair &p : open) { pool.push_back(p.a); pool.push_back(p.b); }
+    open.clear();
     for (cudaEvent_t e : pool) cudaEventDestroy(e);
     pool.clear();
   }
