@@ -156,19 +156,39 @@ def hits_fields(torch, hits_u8):
     return as_i32[:, 0], as_f64
 
 
-def make_queries(torch, rays, hits_u8):
+def scene_tables(torch, scene, dev):
+    """element -> material, material -> (kd, ks, shininess) of the uploaded scene as device tensors"""
+    mats, els = scene.materials(), scene.elements()
+    e2m = torch.tensor(els["material"].astype(np.int64), dtype=torch.int64, device=dev)
+    kd = torch.tensor(mats["kd"], dtype=torch.float64, device=dev)
+    ks = torch.tensor(mats["ks"], dtype=torch.float64, device=dev)
+    sh = torch.tensor(mats["shininess"], dtype=torch.float64, device=dev)
+    return e2m, kd, ks, sh
+
+
+def make_queries(torch, rays, hits_u8, tables):
     """GiGatherQuery records at the hit points, set up as CausticIllumination is called from RayTrace
-    (raytracer.cpp:138-149, 174-190): cos_theta = n.(-view), exact_bounce = mirror direction.
-    Returns (queries [n_q, 17], index of each query's ray)."""
+    (raytracer.cpp:138-149, 174-190): cos_theta = n.(-view), exact_bounce = ReflectiveBounce(normal, view, cos_theta)
+    (graphics_utils.cpp:104-117), kd / ks / shininess of the hit element's material.
+    Returns (queries [n_q, 17], compact queries [n_q, 10] = point, normal, view, material index, index of each query's ray)."""
+    e2m, kd, ks, sh = tables
+    n_all = hits_u8.shape[0] // 72
     hit, f = hits_fields(torch, hits_u8)
+    element = hits_u8.view(torch.int32).reshape(n_all, 18)[:, 3]
     m = hit == 1
     d = rays[m, 3:6]; p = f[m, 3:6]; n = f[m, 6:9]
+    mat = e2m[element[m].long()]
     cos = -(n * d).sum(1)
+    nn = torch.where((cos < 0)[:, None], -n, n); cc = cos.abs()
+    b = d + nn * cc[:, None] * 2.0
+    b = b / torch.sqrt((b[:, 0] * b[:, 0] + b[:, 1] * b[:, 1] + b[:, 2] * b[:, 2]))[:, None]
     q = torch.zeros((int(m.sum()), 17), dtype=torch.float64, device=rays.device)
-    q[:, 0:3] = p; q[:, 3:6] = n; q[:, 6:9] = d + 2.0 * cos[:, None] * n; q[:, 9] = cos
-    q[:, 10:13] = torch.tensor([0.5, 0.5, 0.5], dtype=torch.float64, device=rays.device)
-    q[:, 13:16] = 0.0; q[:, 16] = 1.0
-    return q.contiguous(), torch.nonzero(m).reshape(-1)
+    q[:, 0:3] = p; q[:, 3:6] = n; q[:, 6:9] = b; q[:, 9] = cos
+    q[:, 10:13] = kd[mat]; q[:, 13:16] = ks[mat]; q[:, 16] = sh[mat]
+    qc = torch.zeros((q.shape[0], 10), dtype=torch.float64, device=rays.device)
+    qc[:, 0:3] = p; qc[:, 3:6] = n; qc[:, 6:9] = d
+    qc.view(torch.int32).reshape(-1, 20)[:, 18] = mat.to(torch.int32)
+    return q.contiguous(), qc.contiguous(), torch.nonzero(m).reshape(-1)
 
 
 def make_photons(torch, ctx, scene, n, seed, dev):
@@ -359,7 +379,7 @@ def run_ours(args):
     replicate_and_build()
     ctx.intersect_device(rays.data_ptr(), n_rays, hits.data_ptr(), stream)
     torch.cuda.synchronize()
-    queries, q_ray = make_queries(torch, rays, hits)
+    queries, queries_c, q_ray = make_queries(torch, rays, hits, scene_tables(torch, scene, dev))
     n_q = queries.shape[0]
     rgb = torch.empty((n_q, 3), dtype=torch.float64, device=dev)
     cnt = torch.empty(n_q, dtype=torch.int32, device=dev)
@@ -418,45 +438,65 @@ def run_ours(args):
     replicate_ms, build_ms, isect_ms, gather_ms, resolve_ms = (stage(i) for i in range(5))
     found_full = int((cnt == K).sum().item())
 
-    # ---- end to end through the host-buffer C ABI: pinned host inputs, H2D + kernels + D2H inside the timed region
+    # ---- end to end through the host-buffer C ABI: pinned host inputs, H2D + kernels + D2H inside the timed region.
+    # Two record shapes: the compact ones (16-byte hits, 80-byte queries with a material index) and the reference-shaped
+    # ones (72-byte GiHit, 136-byte GiGatherQuery); `e2e` is the compact path, the other is reported beside it.
     share_h = torch.empty((per_rank, 32), dtype=torch.uint8, pin_memory=True); share_h.copy_(share)
     share_d = torch.empty_like(share)
     rays_h = torch.empty((n_rays, 6), dtype=torch.float64, pin_memory=True); rays_h.copy_(rays)
-    q_h = torch.empty((n_q, 17), dtype=torch.float64, pin_memory=True); q_h.copy_(queries)
-    hits_h = torch.empty(n_rays * 72, dtype=torch.uint8, pin_memory=True)
     rgb_h = torch.empty((n_q, 3), dtype=torch.float64, pin_memory=True)
     cnt_h = torch.empty(n_q, dtype=torch.int32, pin_memory=True)
     L = gi_b200.lib()
 
-    def e2e_step():
+    def e2e_map():
         if world > 1:
             share_d.copy_(share_h, non_blocking=True); torch.cuda.current_stream().synchronize()
             ctx.load_photons_sharded_device(gi_b200.GI_MAP_CAUSTIC, share_d.data_ptr(), per_rank)
         else:
             gi_b200._check(L.gi_load_photons(ctx.handle, gi_b200.GI_MAP_CAUSTIC, share_h.data_ptr(), per_rank))
         ctx.build_maps(params)
+
+    def time_e2e(step_fn):
+        step_fn()
+        torch.cuda.synchronize()
+        if world > 1:
+            dist.barrier()
+        reps = max(1, min(args.steps, 3))
+        t0 = time.perf_counter()
+        for _ in range(reps):
+            step_fn()
+        torch.cuda.synchronize()
+        return (time.perf_counter() - t0) / reps
+
+    qc_h = torch.empty((n_q, 10), dtype=torch.float64, pin_memory=True); qc_h.copy_(queries_c)
+    hitc_h = torch.empty(n_rays * 16, dtype=torch.uint8, pin_memory=True)
+
+    def e2e_compact():
+        e2e_map()
+        gi_b200._check(L.gi_intersect_batch_compact(ctx.handle, rays_h.data_ptr(), n_rays, hitc_h.data_ptr()))
+        gi_b200._check(L.gi_gather_batch_compact(ctx.handle, gi_b200.GI_MAP_CAUSTIC, qc_h.data_ptr(), n_q, K, R, FILTER,
+                                                 ctypes.byref(params), cnt_h.data_ptr(), rgb_h.data_ptr()))
+    e2e_s = time_e2e(e2e_compact)
+    compact_max_rel = float(((rgb_h.to(dev) - rgb).abs().max(1).values / rgb.abs().max(1).values.clamp_min(1e-300)).max().item())
+    del qc_h, hitc_h
+    q_h = torch.empty((n_q, 17), dtype=torch.float64, pin_memory=True); q_h.copy_(queries)
+    hits_h = torch.empty(n_rays * 72, dtype=torch.uint8, pin_memory=True)
+
+    def e2e_full():
+        e2e_map()
         gi_b200._check(L.gi_intersect_batch(ctx.handle, rays_h.data_ptr(), n_rays, hits_h.data_ptr()))
         gi_b200._check(L.gi_gather_batch(ctx.handle, gi_b200.GI_MAP_CAUSTIC, q_h.data_ptr(), n_q, K, R, FILTER,
                                          ctypes.byref(params), None, cnt_h.data_ptr(), rgb_h.data_ptr()))
-    e2e_step()
-    torch.cuda.synchronize()
-    if world > 1:
-        dist.barrier()
-    e2e_steps = max(1, min(args.steps, 3))
-    t0 = time.perf_counter()
-    for _ in range(e2e_steps):
-        e2e_step()
-    torch.cuda.synchronize()
-    e2e_s = (time.perf_counter() - t0) / e2e_steps
+    e2e_full_s = time_e2e(e2e_full)
     del share_h, share_d, rays_h, q_h, hits_h, rgb_h, cnt_h
 
     # ---- max over ranks
-    t = torch.tensor([total_ms, replicate_ms, build_ms, isect_ms, gather_ms, resolve_ms, e2e_s * 1e3], dtype=torch.float64, device=dev)
+    t = torch.tensor([total_ms, replicate_ms, build_ms, isect_ms, gather_ms, resolve_ms, e2e_s * 1e3, e2e_full_s * 1e3], dtype=torch.float64, device=dev)
     units = torch.tensor([float(n_rays), float(n_q)], dtype=torch.float64, device=dev)
     if world > 1:
         dist.all_reduce(t, op=dist.ReduceOp.MAX)
         dist.all_reduce(units, op=dist.ReduceOp.SUM)
-    total_ms, replicate_ms, build_ms, isect_ms, gather_ms, resolve_ms, e2e_ms = t.tolist()
+    total_ms, replicate_ms, build_ms, isect_ms, gather_ms, resolve_ms, e2e_ms, e2e_full_ms = t.tolist()
     rays_all, q_all = units.tolist()
     ms_per_step = total_ms / args.steps
 
@@ -465,7 +505,7 @@ def run_ours(args):
         extras = extra_sections(args, torch, ctx, scene, dev, rank, queries, stream, clocks)
     frames = None
     if args.frames != "none":
-        del acc, rgb, cnt, hits, rays, queries
+        del acc, rgb, cnt, hits, rays, queries, queries_c
         torch.cuda.empty_cache()
         frames = frame_reports(args, torch, dist, ctx, dev, rank, world)
 
@@ -487,8 +527,12 @@ def run_ours(args):
                              "algorithmic_bytes_per_gather": GATHER_ALGO_BYTES,
                              "intersect_kernel_GBps": (n_rays * RAY_ALGO_BYTES) / (isect_ms * 1e-3) / 1e9},
                 "e2e": {"value": (rays_all + q_all) / (e2e_ms * 1e-3) / 1e6, "unit": "Mrays/s",
-                        "h2d_bytes_per_step": per_rank * 32 + n_rays * 48 + n_q * 136, "d2h_bytes_per_step": n_rays * 72 + n_q * 28,
-                        "ms_per_step": e2e_ms,
+                        "h2d_bytes_per_step": per_rank * 32 + n_rays * 48 + n_q * 80, "d2h_bytes_per_step": n_rays * 16 + n_q * 28,
+                        "ms_per_step": e2e_ms, "records": "compact (gi_intersect_batch_compact: 16-byte hits; gi_gather_batch_compact: 80-byte queries)",
+                        "max_rel_diff_vs_device_path": compact_max_rel,
+                        "reference_shaped_records": {"value": (rays_all + q_all) / (e2e_full_ms * 1e-3) / 1e6, "ms_per_step": e2e_full_ms,
+                                                     "h2d_bytes_per_step": per_rank * 32 + n_rays * 48 + n_q * 136,
+                                                     "d2h_bytes_per_step": n_rays * 72 + n_q * 28},
                         "note": "per rank: photon share, rays and queries from pinned host memory, hits / counts / radiance back to "
                                 "host memory; the strip gather to rank 0 is not repeated here"},
                 "gpu_launches": int(launches), "torch_glue_launches_per_step": "index_copy, clamp, sum, mul, cast (+ NCCL gather)",
@@ -594,6 +638,8 @@ FRAME_CONFIGS = {      # BASELINE.json configs as whole-program frames: (scene, 
 def frame_reports(args, torch, dist, ctx, dev, rank, world):
     names = {"small": ["cornell_512_aa1"], "default": ["cornell_512_aa1", "cornell_1024_aa2"],
              "all": list(FRAME_CONFIGS)}[args.frames]
+    if world < 8:            # BASELINE.json configs[4] is defined on 8 GPUs (4096 x 4096 aa 2, 10^8 caustic photons: minutes on fewer)
+        names = [n for n in names if not n.startswith("distributed")]
     out = {}
     for i, name in enumerate(names):
         # the first frame of the process pays one-time costs (workspace allocation, NCCL channel set-up): it is run twice

@@ -17,6 +17,7 @@
 #include "gi_math.cuh"
 #include "irradiance_cache.h"
 #include "kdtree_build.h"
+#include "shade.cuh"
 
 namespace gi {
 
@@ -70,6 +71,26 @@ static int pow2ceil(int v) { int p = 1; while (p < v) p <<= 1; return p; }
 }  // namespace gi
 
 using namespace gi;
+
+namespace gi {
+// GiGatherQueryCompact -> GiGatherQuery as RayTrace sets up its EstimateRadiance calls (raytracer.cpp:138-167, 174-190)
+__global__ void expand_queries_kernel(const GiGatherQueryCompact *__restrict__ c, uint64_t n, const DevMaterial *__restrict__ mats, int n_mats,
+                                      GiGatherQuery *__restrict__ out) {
+  const uint64_t t = (uint64_t)blockIdx.x * blockDim.x + threadIdx.x;
+  if (t >= n) return;
+  const GiGatherQueryCompact q = c[t];
+  const D3 normal = ld3(q.n), view = ld3(q.view);
+  const double cos_theta = dot(normal, -view);
+  const D3 bounce = reflective_bounce(normal, view, cos_theta);
+  GiGatherQuery o;
+  for (int a = 0; a < 3; a++) { o.p[a] = q.p[a]; o.n[a] = q.n[a]; }
+  o.bounce[0] = bounce.x; o.bounce[1] = bounce.y; o.bounce[2] = bounce.z; o.cos_theta = cos_theta;
+  const int mi = q.material >= 0 && q.material < n_mats ? q.material : 0;
+  for (int a = 0; a < 3; a++) { o.kd[a] = mats[mi].kd[a]; o.ks[a] = mats[mi].ks[a]; }
+  o.shininess = mats[mi].shininess;
+  out[t] = o;
+}
+}  // namespace gi
 
 extern "C" {
 
@@ -336,6 +357,43 @@ int gi_gather_batch(GiContext *ctx, int map, const GiGatherQuery *queries, uint6
     if (!cuda_ok(cudaMemcpyAsync(d_q, queries + o, sizeof(GiGatherQuery) * m, cudaMemcpyHostToDevice, st), "H2D queries") ||
         gi_gather_batch_device(ctx, map, d_q, m, k, r, filter, params, d_idx, d_cnt, d_rgb, st) != 0 ||
         (idx_out && !cuda_ok(cudaMemcpyAsync(idx_out + o * k, d_idx, sizeof(int32_t) * m * k, cudaMemcpyDeviceToHost, st), "D2H idx")) ||
+        (count_out && !cuda_ok(cudaMemcpyAsync(count_out + o, d_cnt, sizeof(int32_t) * m, cudaMemcpyDeviceToHost, st), "D2H count")) ||
+        (rgb_out && !cuda_ok(cudaMemcpyAsync(rgb_out + 3 * o, d_rgb, sizeof(double) * 3 * m, cudaMemcpyDeviceToHost, st), "D2H rgb")))
+      rc = 1;
+  }
+  if (!cuda_ok(cudaStreamSynchronize(ctx->pipe[0]), "gather sync") || !cuda_ok(cudaStreamSynchronize(ctx->pipe[1]), "gather sync")) rc = 1;
+  return rc;
+}
+
+int gi_gather_batch_compact(GiContext *ctx, int map, const GiGatherQueryCompact *queries, uint64_t n, int k, double r, int filter,
+                            const GiParams *params, int32_t *count_out, double *rgb_out) {
+  if (!ctx) { set_error("gi_gather_batch_compact: null context"); return 1; }
+  if (!ctx->has_scene) { set_error("gi_gather_batch_compact: no scene uploaded (the material indices refer to it)"); return 1; }
+  if (n == 0) return 0;
+  if (!queries) { set_error("gi_gather_batch_compact: null query buffer"); return 1; }
+  if (k < 1 || k > GI_MAX_K) { set_error("gi_gather_batch_compact: estimate size must be in [1, 512]"); return 1; }
+  GI_CUDA(cudaSetDevice(ctx->device));
+  const uint64_t cmax = 1ull << 21;                        // the pipeline of gi_gather_batch, 80 instead of 136 bytes per query in
+  uint64_t chunk = 1ull << 18;
+  int rc = 0;
+  for (uint64_t o = 0, c = 0; o < n && rc == 0; o += chunk, chunk = chunk * 2 < cmax ? chunk * 2 : cmax, c++) {
+    const uint64_t m = n - o < chunk ? n - o : chunk;
+    const int slot = (int)(c & 1);
+    cudaStream_t st = ctx->pipe[slot];
+    GiScratch *sc = ctx->stage[slot];
+    const uint64_t room = n < cmax ? n : cmax;
+    if (!sc[0].fit(sizeof(GiGatherQuery) * room) || (rgb_out && !sc[1].fit(sizeof(double) * 3 * room)) ||
+        (count_out && !sc[2].fit(sizeof(int32_t) * room)) || !sc[3].fit(sizeof(GiGatherQueryCompact) * room)) {
+      set_error("gi_gather_batch_compact: out of device memory"); rc = 1; break;
+    }
+    GiGatherQuery *d_q = (GiGatherQuery *)sc[0].p; GiGatherQueryCompact *d_c = (GiGatherQueryCompact *)sc[3].p;
+    double *d_rgb = rgb_out ? (double *)sc[1].p : nullptr;
+    int32_t *d_cnt = count_out ? (int32_t *)sc[2].p : nullptr;
+    if (!cuda_ok(cudaMemcpyAsync(d_c, queries + o, sizeof(GiGatherQueryCompact) * m, cudaMemcpyHostToDevice, st), "H2D queries")) { rc = 1; break; }
+    expand_queries_kernel<<<(unsigned)((m + 255) / 256), 256, 0, st>>>(d_c, m, ctx->scene.materials, ctx->scene.n_materials, d_q);
+    ctx->launches++;
+    if (!cuda_ok(cudaGetLastError(), "expand_queries_kernel") ||
+        gi_gather_batch_device(ctx, map, d_q, m, k, r, filter, params, nullptr, d_cnt, d_rgb, st) != 0 ||
         (count_out && !cuda_ok(cudaMemcpyAsync(count_out + o, d_cnt, sizeof(int32_t) * m, cudaMemcpyDeviceToHost, st), "D2H count")) ||
         (rgb_out && !cuda_ok(cudaMemcpyAsync(rgb_out + 3 * o, d_rgb, sizeof(double) * 3 * m, cudaMemcpyDeviceToHost, st), "D2H rgb")))
       rc = 1;

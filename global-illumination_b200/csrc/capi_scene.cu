@@ -65,6 +65,15 @@ __global__ void __launch_bounds__(128) intersect_kernel(DevScene sc, const GiRay
 
 using namespace gi;
 
+namespace gi {
+__global__ void compact_hits_kernel(const GiHit *__restrict__ h, uint64_t n, GiHitCompact *__restrict__ out) {
+  const uint64_t t = (uint64_t)blockIdx.x * blockDim.x + threadIdx.x;
+  if (t >= n) return;
+  GiHitCompact c; c.prim = h[t].hit ? h[t].prim : -1; c.shape = h[t].hit ? h[t].shape : -1; c.t = h[t].t;
+  out[t] = c;
+}
+}  // namespace gi
+
 extern "C" {
 
 int gi_abi_version(void) { return GI_ABI_VERSION; }
@@ -230,6 +239,35 @@ int gi_intersect_batch(GiContext *ctx, const GiRay *rays, uint64_t n, GiHit *hit
     if (!cuda_ok(cudaMemcpyAsync(d_rays, rays + o, sizeof(GiRay) * m, cudaMemcpyHostToDevice, st), "H2D rays") ||
         gi_intersect_batch_device(ctx, d_rays, m, d_hits, st) != 0 ||
         !cuda_ok(cudaMemcpyAsync(hits_out + o, d_hits, sizeof(GiHit) * m, cudaMemcpyDeviceToHost, st), "D2H hits"))
+      rc = 1;
+  }
+  if (!cuda_ok(cudaStreamSynchronize(ctx->pipe[0]), "intersect sync") || !cuda_ok(cudaStreamSynchronize(ctx->pipe[1]), "intersect sync")) rc = 1;
+  return rc;
+}
+
+int gi_intersect_batch_compact(GiContext *ctx, const GiRay *rays, uint64_t n, GiHitCompact *hits_out) {
+  if (!ctx || !ctx->has_scene) { set_error("gi_intersect_batch_compact: no scene uploaded"); return 1; }
+  if (n == 0) return 0;
+  if (!rays || !hits_out) { set_error("gi_intersect_batch_compact: null buffer"); return 1; }
+  GI_CUDA(cudaSetDevice(ctx->device));
+  const uint64_t chunk = 1ull << 21;                       // the two-slot pipeline of gi_intersect_batch; only 16 bytes per hit go back
+  int rc = 0;
+  for (uint64_t o = 0, c = 0; o < n && rc == 0; o += chunk, c++) {
+    const uint64_t m = n - o < chunk ? n - o : chunk;
+    const int slot = (int)(c & 1);
+    cudaStream_t st = ctx->pipe[slot];
+    if (!ctx->stage[slot][0].fit(sizeof(GiRay) * chunk) || !ctx->stage[slot][1].fit(sizeof(GiHit) * chunk) ||
+        !ctx->stage[slot][2].fit(sizeof(GiHitCompact) * chunk)) {
+      set_error("gi_intersect_batch_compact: out of device memory"); rc = 1; break;
+    }
+    GiRay *d_rays = (GiRay *)ctx->stage[slot][0].p; GiHit *d_hits = (GiHit *)ctx->stage[slot][1].p;
+    GiHitCompact *d_c = (GiHitCompact *)ctx->stage[slot][2].p;
+    if (!cuda_ok(cudaMemcpyAsync(d_rays, rays + o, sizeof(GiRay) * m, cudaMemcpyHostToDevice, st), "H2D rays") ||
+        gi_intersect_batch_device(ctx, d_rays, m, d_hits, st) != 0) { rc = 1; break; }
+    compact_hits_kernel<<<(unsigned)((m + 255) / 256), 256, 0, st>>>(d_hits, m, d_c);
+    ctx->launches++;
+    if (!cuda_ok(cudaGetLastError(), "compact_hits_kernel") ||
+        !cuda_ok(cudaMemcpyAsync(hits_out + o, d_c, sizeof(GiHitCompact) * m, cudaMemcpyDeviceToHost, st), "D2H hits"))
       rc = 1;
   }
   if (!cuda_ok(cudaStreamSynchronize(ctx->pipe[0]), "intersect sync") || !cuda_ok(cudaStreamSynchronize(ctx->pipe[1]), "intersect sync")) rc = 1;

@@ -759,7 +759,10 @@ small_rank_kernel(PhotonMapDev m, const GiGatherQuery *__restrict__ queries, con
 // STAGE: the position blocks of the bottom-row scan are staged in shared memory by cp.async (a two-slot ring per warp:
 // the copy of the next touched group is in flight while the current one is tested) instead of being prefetched into
 // 6-12 FP64 registers per lane.
-template <bool DEEP, bool STAGE>
+// COUNT: the instrumented instantiation behind GI_GATHER_DEBUG=1 (searches per query, groups entered, photons tested /
+// inside the bound): the figures DESIGN.md quotes come from it (profiles/r02_gather_counters.txt).
+__device__ unsigned long long g_walk_dbg[8];
+template <bool DEEP, bool STAGE, bool COUNT = false>
 __global__ void __launch_bounds__(GI_GATHER_MAX_WARPS * 32, 1)
 gather_kernel(PhotonMapDev m, const double *__restrict__ lut, const GiGatherQuery *__restrict__ queries,
               const uint32_t *__restrict__ order, uint64_t nq, GatherArgs ga, unsigned long long *work_counter, int32_t *idx_out,
@@ -831,10 +834,12 @@ gather_kernel(PhotonMapDev m, const double *__restrict__ lut, const GiGatherQuer
     const double qx = __shfl_sync(FULL, mine, 0), qy = __shfl_sync(FULL, mine, 1), qz = __shfl_sync(FULL, mine, 2);
     int count = 0, raw = 0;
     double bound = ga.r2;
+    unsigned dbg_search = 0, dbg_upper = 0, dbg_bottom = 0, dbg_tested = 0, dbg_inside = 0, dbg_cuts = 0;
     if (n > 0) {
       double init = fmin(ga.r2, guess);
       while (true) {
         count = 0; bound = init;
+        if (COUNT) dbg_search++;
         // The tree is walked as a 32-ary tree of groups (photon_dev.h), depth first.
         //   rows above gp: row g keeps the root of the group it is in (st_root, held by lane g) and, per lane, the
         //     lower bound of the squared distance from the query to child group `lane` (keys[g][lane], float bits
@@ -867,6 +872,7 @@ gather_kernel(PhotonMapDev m, const double *__restrict__ lut, const GiGatherQuer
             const double bd = box_dist2(cbox_lane, gi, qx, qy, qz);
             {
               const double d2 = dist2(ph, qx, qy, qz);
+              if (COUNT) { dbg_upper++; dbg_tested += __popc(__ballot_sync(FULL, d2 < INFINITY)); dbg_inside += __popc(__ballot_sync(FULL, d2 <= bound)); }
               append(b, count, bound, k, lane, lt_mask, d2 <= bound, d2, (s << jl) + (uint32_t)lane);
             }
             if (g == gp) {
@@ -951,6 +957,10 @@ gather_kernel(PhotonMapDev m, const double *__restrict__ lut, const GiGatherQuer
                   unsigned mb = 0u;
                   if (has6) { d2b = dist2(low, qx, qy, qz); pb = d2b <= bound; mb = __ballot_sync(FULL, pb); }
                   const unsigned ma = __ballot_sync(FULL, pa);
+                  if (COUNT) {
+                    dbg_bottom++; dbg_tested += __popc(__ballot_sync(FULL, d2a < INFINITY)) + (has6 ? __popc(__ballot_sync(FULL, d2b < INFINITY)) : 0);
+                    dbg_inside += __popc(ma) + __popc(mb);
+                  }
                   if (ma | mb) {
                     const int na = __popc(ma);
                     if (pa) { const int pos = count + __popc(ma & lt_mask); b.set_d2(pos, d2a); b.set_slot(pos, (ls << jl) + (uint32_t)lane); }
@@ -961,6 +971,7 @@ gather_kernel(PhotonMapDev m, const double *__restrict__ lut, const GiGatherQuer
                     count += na + __popc(mb);
                     __syncwarp();
                     if (count > b.limit) {
+                      if (COUNT) dbg_cuts++;
                       const Sel r = cut(b, count, bound, k, lane, true); count = r.count; bound = r.bound;
                       todo &= __ballot_sync(FULL, (double)kf <= bound);
                     }
@@ -993,6 +1004,12 @@ gather_kernel(PhotonMapDev m, const double *__restrict__ lut, const GiGatherQuer
         init = init > 0.0 ? fmin(ga.r2, init * 4.0) : ga.r2;            // the guess was too small: widen and retry
       }
       guess = count >= k ? bound * ga.guess_factor : ga.r2;
+    }
+    if (COUNT && lane == 0) {
+      atomicAdd(&g_walk_dbg[0], 1ull); atomicAdd(&g_walk_dbg[1], (unsigned long long)dbg_search); atomicAdd(&g_walk_dbg[2], (unsigned long long)dbg_upper);
+      atomicAdd(&g_walk_dbg[3], (unsigned long long)dbg_bottom); atomicAdd(&g_walk_dbg[4], (unsigned long long)dbg_tested);
+      atomicAdd(&g_walk_dbg[5], (unsigned long long)dbg_inside); atomicAdd(&g_walk_dbg[6], (unsigned long long)dbg_cuts);
+      atomicAdd(&g_walk_dbg[7], (unsigned long long)(count < k ? count : k));
     }
     estimate_and_store(b, m, ga, mine, count, raw, bound, k, lane, qi, idx_out, count_out, rgb_out);
     __syncwarp();
@@ -1107,6 +1124,23 @@ cudaError_t launch_gather(GiContext *ctx, const PhotonMapDev &m, const double *d
   { cudaError_t e = cudaMemsetAsync(counter, 0, sizeof(unsigned long long), st); if (e != cudaSuccess) return e; }
   const uint64_t want = (nchunks + warps - 1) / warps;
   const unsigned grid = (unsigned)(want < (uint64_t)ctx->sm_count ? want : (uint64_t)ctx->sm_count);
+  static const bool walk_dbg = getenv("GI_GATHER_DEBUG") && atoi(getenv("GI_GATHER_DEBUG")) != 0;
+  if (walk_dbg && !stage) {
+    // the instrumented instantiation (its shared-memory attribute is set on every launch: a debugging path)
+    if (deep) { cudaFuncSetAttribute(gather_kernel<true, false, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
+                gather_kernel<true, false, true><<<grid, warps * 32, smem, st>>>(m, d_lut, d_q, d_order, nq, ga, counter, d_idx, d_count, d_rgb); }
+    else { cudaFuncSetAttribute(gather_kernel<false, false, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
+           gather_kernel<false, false, true><<<grid, warps * 32, smem, st>>>(m, d_lut, d_q, d_order, nq, ga, counter, d_idx, d_count, d_rgb); }
+    unsigned long long h[8] = {0}, z[8] = {0};
+    cudaStreamSynchronize(st);
+    cudaMemcpyFromSymbol(h, g_walk_dbg, sizeof(h)); cudaMemcpyToSymbol(g_walk_dbg, z, sizeof(z));
+    const double q = h[0] ? (double)h[0] : 1.0;
+    fprintf(stderr, "[gather_kernel] queries %llu photons %llu k %d | per query: searches %.3f upper groups %.2f bottom groups %.2f photons tested %.1f "
+            "inside the bound when tested %.1f kept %.1f mid-scan cuts %.3f\n", h[0], (unsigned long long)m.n, ga.k, h[1] / q, h[2] / q, h[3] / q, h[4] / q, h[5] / q,
+            h[7] / q, h[6] / q);
+    ctx->launches++;
+    return cudaGetLastError();
+  }
   switch (variant) {
     case 0: gather_kernel<false, false><<<grid, warps * 32, smem, st>>>(m, d_lut, d_q, d_order, nq, ga, counter, d_idx, d_count, d_rgb); break;
     case 1: gather_kernel<true, false><<<grid, warps * 32, smem, st>>>(m, d_lut, d_q, d_order, nq, ga, counter, d_idx, d_count, d_rgb); break;

@@ -17,6 +17,10 @@ GI_VIEW_GLOBAL_PHOTONS, GI_VIEW_CAUSTIC_PHOTONS, GI_VIEW_RAYS, GI_VIEW_PATHS = 0
 NOALLOC_MAX_QUERIES = 262144      # GI_NOALLOC_MAX_QUERIES of include/gi_b200.h
 
 RAY = np.dtype([("o", "<f8", 3), ("d", "<f8", 3)])
+MATERIAL = np.dtype([("ka", "<f8", 3), ("kd", "<f8", 3), ("ks", "<f8", 3), ("kt", "<f8", 3), ("ke", "<f8", 3), ("shininess", "<f8"), ("ir", "<f8")])
+ELEMENT = np.dtype([("node", "<i4"), ("material", "<i4"), ("bbox", "<f8", 6)])
+HIT_COMPACT = np.dtype([("prim", "<i4"), ("shape", "<i4"), ("t", "<f8")])
+QUERY_COMPACT = np.dtype([("p", "<f8", 3), ("n", "<f8", 3), ("view", "<f8", 3), ("material", "<i4"), ("pad", "<i4")])
 HIT = np.dtype([("hit", "<i4"), ("shape", "<i4"), ("prim", "<i4"), ("element", "<i4"), ("t", "<f8"),
                 ("p", "<f8", 3), ("n", "<f8", 3)])
 PHOTON = np.dtype([("position", "<f8", 3), ("rgbe", "u1", 4), ("direction", "<u2"), ("pad", "<u2")])
@@ -95,7 +99,7 @@ EXPORTS = ["gi_abi_version", "gi_last_error", "gi_create", "gi_destroy", "gi_def
            "gi_upload_scene", "gi_intersect_batch", "gi_intersect_batch_device",
            "gi_load_photons", "gi_load_photons_device", "gi_load_photons_file", "gi_dump_photons_file",
            "gi_photon_count", "gi_get_photons", "gi_get_photons_device", "gi_build_maps", "gi_gather_batch", "gi_gather_batch_device",
-           "gi_gather_batch_device_noalloc", "gi_stage_timing", "gi_stage_times", "gi_load_photons_sharded_device", "gi_debug_view",
+           "gi_gather_batch_device_noalloc", "gi_stage_timing", "gi_stage_times", "gi_load_photons_sharded_device", "gi_debug_view", "gi_intersect_batch_compact", "gi_gather_batch_compact",
            "gi_trace_photons", "gi_scale_photon_power", "gi_render", "gi_render_float",
            "gi_default_cli_options", "gi_parse_args", "gi_write_image",
            "gi_comm_unique_id", "gi_comm_init_rank", "gi_comm_init_all", "gi_comm_info", "gi_comm_destroy"]
@@ -118,6 +122,8 @@ def lib():
         L.gi_default_params.argtypes = [ctypes.POINTER(GiParams)]; L.gi_default_params.restype = None
         L.gi_launch_count.argtypes = [vp, ctypes.POINTER(u64)]
         L.gi_stage_timing.argtypes = [vp, i32]
+        L.gi_intersect_batch_compact.argtypes = [vp, vp, u64, vp]
+        L.gi_gather_batch_compact.argtypes = [vp, i32, vp, u64, i32, dbl, i32, ctypes.POINTER(GiParams), vp, vp]
         L.gi_debug_view.argtypes = [vp, i32, ctypes.POINTER(GiParams), i32, i32, i32, vp]
         L.gi_stage_times.argtypes = [vp, ctypes.POINTER(GiStageTimes)]
         L.gi_queue_overflow_count.argtypes = [vp, ctypes.POINTER(u64)]
@@ -206,6 +212,16 @@ class HostScene:
         except Exception:
             pass
 
+    def materials(self):
+        """GiScene.materials as a numpy record array (MATERIAL)"""
+        n = self.view.n_materials
+        return np.frombuffer((ctypes.c_char * (n * MATERIAL.itemsize)).from_address(self.view.materials), dtype=MATERIAL).copy()
+
+    def elements(self):
+        """GiScene.elements as a numpy record array (ELEMENT): node, material index, bbox"""
+        n = self.view.n_elements
+        return np.frombuffer((ctypes.c_char * (n * ELEMENT.itemsize)).from_address(self.view.elements), dtype=ELEMENT).copy()
+
 
 class Context:
     """One GPU.  Mirrors the gi_* entry points; host numpy buffers in, host numpy buffers out."""
@@ -271,6 +287,22 @@ class Context:
         hits = np.zeros(len(rays), dtype=HIT)
         _check(lib().gi_intersect_batch(self.handle, rays.ctypes.data, len(rays), hits.ctypes.data))
         return hits
+
+    def intersect_compact(self, rays):
+        rays = np.ascontiguousarray(rays, dtype=np.float64).reshape(-1, 6)
+        hits = np.zeros(len(rays), dtype=HIT_COMPACT)
+        _check(lib().gi_intersect_batch_compact(self.handle, rays.ctypes.data, len(rays), hits.ctypes.data))
+        return hits
+
+    def gather_compact(self, which, queries, k, r, filter=GI_FILTER_DISK, params=None):
+        """queries: QUERY_COMPACT records (point, normal, view direction, material index of the uploaded scene)"""
+        queries = np.ascontiguousarray(queries, dtype=QUERY_COMPACT)
+        n = len(queries)
+        cnt = np.zeros(n, dtype=np.int32); rgb = np.zeros((n, 3), dtype=np.float64)
+        p = params or default_params()
+        _check(lib().gi_gather_batch_compact(self.handle, which, queries.ctypes.data, n, k, float(r), filter, ctypes.byref(p),
+                                             cnt.ctypes.data, rgb.ctypes.data))
+        return cnt, rgb
 
     def intersect_device(self, d_rays, n, d_hits, stream=None):
         _check(lib().gi_intersect_batch_device(self.handle, d_rays, n, d_hits, stream))

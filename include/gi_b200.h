@@ -26,7 +26,7 @@
 extern "C" {
 #endif
 
-#define GI_ABI_VERSION 6
+#define GI_ABI_VERSION 7
 
 /* ------------------------------------------------------------------------------------------------
  * Scene description (flattened R3Scene; src/R3Graphics/R3Scene.h).  Order is the order in which
@@ -296,6 +296,23 @@ int gi_gather_batch_device(GiContext *ctx, int map, const GiGatherQuery *d_queri
 int gi_gather_batch_device_noalloc(GiContext *ctx, int map, const GiGatherQuery *d_queries, uint64_t n, int k, double r,
                                    int filter, const GiParams *params, int32_t *d_idx, int32_t *d_count, double *d_rgb,
                                    void *stream);
+
+/* Compact host-buffer variants: the same results with fewer bytes over PCIe (the 72-byte GiHit and the 136-byte
+ * GiGatherQuery mirror the reference's argument lists; a host that only needs ids and distances, or whose queries are
+ * surface hits of the uploaded scene, moves 16 and 80 bytes instead).
+ *   gi_intersect_batch_compact   R3Scene::Intersects over a batch (R3Scene.cpp:471-479) returning {prim, shape, t}; prim < 0:
+ *                                miss.  Point and normal are recomputable from the ray and t / the primitive.
+ *   gi_gather_batch_compact      EstimateRadiance over a batch (photon_utils.cpp:72-162) for queries given as RayTrace has
+ *                                them at a hit (raytracer.cpp:138-167, 174-190): point, normal, the unit direction `view` of
+ *                                the ray that arrived there and the hit element's material (index into GiScene.materials of
+ *                                the uploaded scene); cos_theta = normal . (-view), exact_bounce = ReflectiveBounce(normal,
+ *                                view, cos_theta) (graphics_utils.cpp:104-117) and kd / ks / shininess are derived on the
+ *                                device.  count_out / rgb_out as gi_gather_batch (either may be NULL). */
+typedef struct GiHitCompact { int32_t prim, shape; double t; } GiHitCompact;
+typedef struct GiGatherQueryCompact { double p[3], n[3], view[3]; int32_t material, pad; } GiGatherQueryCompact;
+int gi_intersect_batch_compact(GiContext *ctx, const GiRay *rays, uint64_t n, GiHitCompact *hits_out);
+int gi_gather_batch_compact(GiContext *ctx, int map, const GiGatherQueryCompact *queries, uint64_t n, int k, double r, int filter,
+                            const GiParams *params, int32_t *count_out, double *rgb_out);
 
 /* The irradiance cache (-cache).  gi_build_maps with params->irradiance_cache (and indirect_illum or
  * direct_photon_illum) set runs the pre-pass of MapPhotons (photonmap.cpp:380-411) once per loaded global map: every

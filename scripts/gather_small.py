@@ -11,14 +11,15 @@ ctx = gi_b200.Context(0)
 scene = gi_b200.HostScene(os.path.join(ROOT, "tests", "golden", "jensen.gisc"))
 ctx.upload_scene(scene)
 st = torch.cuda.current_stream().cuda_stream
-rays = bench.camera_rays(torch, scene.view.camera, 1024, 1024, dev)
+side = int(sys.argv[1]) if len(sys.argv) > 1 else 1024          # 1024 -> 2^20 queries; 2900 -> the bench section's 2^23
+rays = bench.camera_rays(torch, scene.view.camera, side, side, dev)
 hits = torch.empty(rays.shape[0] * 72, dtype=torch.uint8, device=dev)
 ctx.intersect_device(rays.data_ptr(), rays.shape[0], hits.data_ptr(), st); torch.cuda.synchronize()
-q, _ = bench.make_queries(torch, rays, hits)
+q, _, _ = bench.make_queries(torch, rays, hits, bench.scene_tables(torch, scene, dev))
 ph = bench.make_photons(torch, ctx, scene, 2176, 7, dev)
 ctx.load_photons_device(gi_b200.GI_MAP_GLOBAL, ph.data_ptr(), 2176)
 p = gi_b200.default_params(); ctx.build_maps(p)
-nq = q.shape[0]
+nq = min(q.shape[0], 1 << 23)
 rgb = torch.empty((nq, 3), dtype=torch.float64, device=dev)
 e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
 for it in range(4):

@@ -28,7 +28,7 @@ def test_library_exports_every_declared_symbol():
     for n in names:
         assert hasattr(L, n), f"libgi_b200.so does not export {n}"
     assert sorted(gi_b200.EXPORTS) == names
-    assert L.gi_abi_version() == 6
+    assert L.gi_abi_version() == 7
 
 
 def test_default_params_match_reference_defaults():
