@@ -58,6 +58,17 @@ def main():
             assert getattr(rs, f) == getattr(r1, f), f
         solo.close()
         print("multi_check OK: world", world, "photons", st.global_stored, st.caustic_stored, "mean", img.mean())
+    # gi_load_photons_sharded_device: ragged shares (rank r holds 1000 + 317 r photons) are concatenated in rank order on every rank
+    sys.path.insert(0, os.path.join(ROOT, "tests"))
+    from gi_testlib import synthetic_photons
+    shares = [synthetic_photons(1000 + 317 * r, 40 + r) for r in range(world)]
+    mine = torch.from_numpy(shares[rank].view(np.uint8).reshape(-1, 32).copy()).to(dev)
+    ctx.load_photons_sharded_device(gi_b200.GI_MAP_CAUSTIC, mine.data_ptr(), len(shares[rank]))
+    got = ctx.get_photons(gi_b200.GI_MAP_CAUSTIC)
+    assert got.tobytes() == np.concatenate(shares).tobytes(), "sharded load: not the shares in rank order"
+    ctx.build_maps()
+    if rank == 0:
+        print("sharded load OK:", len(got), "photons")
     dist.barrier()
     ctx.close()
     dist.destroy_process_group()

@@ -25,7 +25,7 @@ def test_two_rank_job_equals_one_gpu_job():
                         "127.0.0.1", "--master-port", "29731", os.path.join(ROOT, "scripts", "multi_check.py")],
                        capture_output=True, text=True, timeout=600)
     assert r.returncode == 0, r.stdout[-2000:] + r.stderr[-4000:]
-    assert "multi_check OK" in r.stdout
+    assert "multi_check OK" in r.stdout and "sharded load OK" in r.stdout
 
 
 def test_cli_gpus_flag_renders_the_same_image(tmp_path):
