@@ -364,6 +364,7 @@ __device__ __forceinline__ void estimate_and_store(const WarpBuf &b, const Photo
 __device__ unsigned long long g_small_dbg[8];
 #define GI_SMALL_MAX_PHOTONS 8192
 #define GI_SMALL_POOL 128            /* pool entries per chunk (u16 heap slots; the rank kernel also stages their positions) */
+#define GI_SMALL_SUPER 256           /* super-pool entries collected during the centre search */
 #define GI_SMALL_CHUNK 32
 #define GI_SMALL_WARPS 24
 #define GI_SMALL_RANK_BYTES (32u * GI_SMALL_SHELL * 10u + 24u * GI_SMALL_POOL + 2u * GI_SMALL_POOL)   /* rank kernel, per warp */
@@ -582,12 +583,13 @@ gather_small_kernel(PhotonMapDev m, const GiGatherQuery *__restrict__ queries, c
   const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
   WarpBuf b; b.cap = ga.cap; b.orig = m.orig;
   { const int room = ga.cap - 32; b.limit = room < ga.k + ga.slack ? room : ga.k + ga.slack; }
-  uint32_t a_pool;
+  uint32_t a_pool, a_super;
   {
-    uint32_t base = (uint32_t)__cvta_generic_to_shared(smem) + (uint32_t)warp * ((uint32_t)GI_WARP_BYTES(ga.cap, 0) + GI_SMALL_POOL * 2u);
+    uint32_t base = (uint32_t)__cvta_generic_to_shared(smem) + (uint32_t)warp * ((uint32_t)GI_WARP_BYTES(ga.cap, 0) + GI_SMALL_POOL * 2u + GI_SMALL_SUPER * 2u);
     asm volatile("" : "+r"(base));
     b.a_d2 = base; b.a_slot = base + (uint32_t)ga.cap * 8u; b.a_hist = b.a_slot + (uint32_t)ga.cap * 4u; b.a_keys = 0;
     a_pool = base + (uint32_t)GI_WARP_BYTES(ga.cap, 0);
+    a_super = a_pool + GI_SMALL_POOL * 2u;
   }
   const int k = ga.k;
   const uint32_t n = (uint32_t)m.n;
@@ -623,37 +625,67 @@ gather_small_kernel(PhotonMapDev m, const GiGatherQuery *__restrict__ queries, c
     if (lane < nqc) { const double dx = mx - cx, dy = my - cy, dz = mz - cz; my_rho2 = (dx * dx) + (dy * dy) + (dz * dz); }
     double rho2 = my_rho2;
     for (int o = 16; o > 0; o >>= 1) rho2 = fmax(rho2, __shfl_xor_sync(FULL, rho2, o));
-    // ---- 1. the chunk centre's exact k nearest, brute force over the map (heap order; px / py / pz are L1-resident)
-    int count = 0, raw = 0;
-    double bound = fmin(ga.r2, guess2);
+    // ---- 1 + 2. ONE scan of the map (heap order; px / py / pz are L1-resident) finds the centre's exact k nearest -- first
+    //      bound = the neighbouring chunk's k-th d2, widened -- and collects a SUPER-POOL: everything within
+    //      sqrt(first bound) + 2 rho of the centre.  The pool proper (radius Rc + 2 rho, Rc the exact k-th distance) is then
+    //      filtered out of the super-pool.  Only if the guess was too small, or the super-pool does not fit, the map is
+    //      scanned again.
+    int count = 0, raw = 0, npool = 0;
+    double bound = fmin(ga.r2, guess2), Rc = 0.0, Rp2 = 0.0;
+    bool centre_full = false, have_pool = false;
+    const double rho = sqrt(rho2);
     while (true) {
       const double first = bound;
+      const double Rs = (sqrt(first) + 2.0 * rho) * (1.0 + 1.0e-9), Rs2 = Rs * Rs;
+      int nsuper = 0;
       count = 0;
       for (uint32_t base = 0; base < n; base += 32) {
         const uint32_t slot = base + (uint32_t)lane;
-        bool pred = false; double d2 = 0.0;
-        if (slot < n) { const P3 p = {m.px[slot], m.py[slot], m.pz[slot]}; d2 = dist2(p, cx, cy, cz); pred = d2 <= bound; }
+        bool pred = false, sp = false; double d2 = 0.0;
+        if (slot < n) { const P3 p = {m.px[slot], m.py[slot], m.pz[slot]}; d2 = dist2(p, cx, cy, cz); pred = d2 <= bound; sp = d2 <= Rs2; }
+        const unsigned smask = __ballot_sync(FULL, sp);
+        if (smask) {
+          const int at = nsuper + __popc(smask & lt_mask);
+          if (sp && at < GI_SMALL_SUPER) sts_u16(a_super + 2u * (uint32_t)at, slot);
+          nsuper += __popc(smask);
+        }
         append(b, count, bound, k, lane, lt_mask, pred, d2, slot);
       }
       finish(b, count, raw, bound, k, lane, true);
-      if (count >= k || first >= ga.r2) break;
+      if (count >= k || first >= ga.r2) {
+        centre_full = count >= k;
+        Rc = sqrt(centre_full ? bound : ga.r2);
+        guess2 = centre_full ? bound * 2.0 : ga.r2;
+        const double Rp = (Rc + 2.0 * rho) * (1.0 + 1.0e-9);
+        Rp2 = Rp * Rp;
+        if (nsuper <= GI_SMALL_SUPER) {                       // the pool is a subset of the super-pool (Rc^2 <= first)
+          __syncwarp();
+          for (int base = 0; base < nsuper && npool <= GI_SMALL_POOL; base += 32) {
+            const int i = base + lane;
+            bool pred = false; uint32_t slot = 0;
+            if (i < nsuper) { slot = lds_u16(a_super + 2u * (uint32_t)i); const P3 p = {m.px[slot], m.py[slot], m.pz[slot]}; pred = dist2(p, cx, cy, cz) <= Rp2; }
+            const unsigned mask = __ballot_sync(FULL, pred);
+            const int at = npool + __popc(mask & lt_mask);
+            if (pred && at < GI_SMALL_POOL) sts_u16(a_pool + 2u * (uint32_t)at, slot);
+            npool += __popc(mask);
+          }
+          have_pool = true;
+        }
+        break;
+      }
       bound = ga.r2;                                          // the guess was too small: the full radius
     }
-    const bool centre_full = count >= k;
-    const double Rc = sqrt(centre_full ? bound : ga.r2);
-    guess2 = centre_full ? bound * 2.0 : ga.r2;
-    // ---- 2. the pool: everything within Rc + 2 rho of the centre
-    const double Rp = (Rc + 2.0 * sqrt(rho2)) * (1.0 + 1.0e-9);
-    const double Rp2 = Rp * Rp;
-    int npool = 0;
-    for (uint32_t base = 0; base < n && npool <= GI_SMALL_POOL; base += 32) {
-      const uint32_t slot = base + (uint32_t)lane;
-      bool pred = false;
-      if (slot < n) { const P3 p = {m.px[slot], m.py[slot], m.pz[slot]}; pred = dist2(p, cx, cy, cz) <= Rp2; }
-      const unsigned mask = __ballot_sync(FULL, pred);
-      const int at = npool + __popc(mask & lt_mask);
-      if (pred && at < GI_SMALL_POOL) sts_u16(a_pool + 2u * (uint32_t)at, slot);
-      npool += __popc(mask);
+    if (!have_pool) {                                         // the pool by a scan of its own
+      npool = 0;
+      for (uint32_t base = 0; base < n && npool <= GI_SMALL_POOL; base += 32) {
+        const uint32_t slot = base + (uint32_t)lane;
+        bool pred = false;
+        if (slot < n) { const P3 p = {m.px[slot], m.py[slot], m.pz[slot]}; pred = dist2(p, cx, cy, cz) <= Rp2; }
+        const unsigned mask = __ballot_sync(FULL, pred);
+        const int at = npool + __popc(mask & lt_mask);
+        if (pred && at < GI_SMALL_POOL) sts_u16(a_pool + 2u * (uint32_t)at, slot);
+        npool += __popc(mask);
+      }
     }
     const bool pooled = npool <= GI_SMALL_POOL;
     if (lane == 0) {
@@ -1037,7 +1069,7 @@ cudaError_t launch_gather(GiContext *ctx, const PhotonMapDev &m, const double *d
   // maps of a few thousand photons (the global map of a default frame): chunk-pooled brute force, no tree walk
   static const bool small_off = getenv("GI_GATHER_SMALL") && atoi(getenv("GI_GATHER_SMALL")) == 0;      // A/B hook
   if (m.n > 0 && m.n <= GI_SMALL_MAX_PHOTONS && !small_off) {
-    const size_t per_warp_s = GI_WARP_BYTES(ga.cap, 0) + GI_SMALL_POOL * 2;
+    const size_t per_warp_s = GI_WARP_BYTES(ga.cap, 0) + GI_SMALL_POOL * 2 + GI_SMALL_SUPER * 2;
     int warps_s = GI_SMALL_WARPS;
     while (warps_s > 4 && (size_t)warps_s * per_warp_s > 160 * 1024) warps_s -= 4;
     const size_t smem_s = (size_t)warps_s * per_warp_s;
