@@ -541,7 +541,18 @@ __device__ __forceinline__ void rank_chunk_per_thread(const PhotonMapDev &m, con
     else { c1 = exp(-ga.fb); c2 = 1.0 / (2.0 * max_d2); }
     found = 0; maxkept = 0.0;
   }
-  // ---- the estimate over the kept photons
+  // ---- the estimate over the kept photons.  The shell lists are dead now: their region takes the pool's estimate records
+  //      (32 B each: incident direction + RGBE), so the loop below reads shared memory only.
+  __syncwarp();
+  if (rgb_out) {
+    for (int i = dbg_lane; i < np; i += 32) {
+      const double2 *rec = m.srec + 2 * (size_t)lds_u16(a_pool + 2u * (uint32_t)i);
+      const double2 ra = rec[0], rb = rec[1];
+      sts_f64(a_shell + 32u * (uint32_t)i, ra.x); sts_f64(a_shell + 32u * (uint32_t)i + 8u, ra.y);
+      sts_f64(a_shell + 32u * (uint32_t)i + 16u, rb.x); sts_f64(a_shell + 32u * (uint32_t)i + 24u, rb.y);
+    }
+  }
+  __syncwarp();
   double e0 = 0.0, e1 = 0.0, e2 = 0.0, total_w = 0.0;
 #pragma unroll 2
   for (int i = 0; i < np; i++) {
@@ -552,8 +563,9 @@ __device__ __forceinline__ void rank_chunk_per_thread(const PhotonMapDev &m, con
     if (in) {
       found++; maxkept = fmax(maxkept, d2);
       if (rgb_out) {
-        const double2 *rec = m.srec + 2 * (size_t)lds_u16(a_pool + 2u * (uint32_t)i);
-        photon_term(ga, q, has_spec, rec[0], rec[1], d2, c1, c2, e0, e1, e2, total_w);
+        const uint32_t ar = a_shell + 32u * (uint32_t)i;
+        photon_term(ga, q, has_spec, make_double2(lds_f64(ar), lds_f64(ar + 8u)), make_double2(lds_f64(ar + 16u), lds_f64(ar + 24u)), d2, c1, c2, e0, e1, e2,
+                    total_w);
       }
     }
   }
