@@ -1080,7 +1080,8 @@ cudaError_t launch_gather(GiContext *ctx, const PhotonMapDev &m, const double *d
   GatherArgs ga = ga_in;
   // maps of a few thousand photons (the global map of a default frame): chunk-pooled brute force, no tree walk
   static const bool small_off = getenv("GI_GATHER_SMALL") && atoi(getenv("GI_GATHER_SMALL")) == 0;      // A/B hook
-  if (m.n > 0 && m.n <= GI_SMALL_MAX_PHOTONS && !small_off) {
+  // (the pool of 128 must hold the k nearest of every query of a chunk with room to spare: larger estimates walk the tree)
+  if (m.n > 0 && m.n <= GI_SMALL_MAX_PHOTONS && ga.k * 5 <= GI_SMALL_POOL * 4 && !small_off) {
     const size_t per_warp_s = GI_WARP_BYTES(ga.cap, 0) + GI_SMALL_POOL * 2 + GI_SMALL_SUPER * 2;
     int warps_s = GI_SMALL_WARPS;
     while (warps_s > 4 && (size_t)warps_s * per_warp_s > 160 * 1024) warps_s -= 4;

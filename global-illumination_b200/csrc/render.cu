@@ -430,7 +430,8 @@ GI_DEV unsigned wave_slot(unsigned t, unsigned n_spec, unsigned cap) { return t 
 
 // Closest hit of every parked ray (both classes).  Nothing but BVH traversal and the FP64 primitive tests: the code all
 // warps of the SM are in fits the instruction cache.  Persistent grid.
-__global__ void __launch_bounds__(128, 6) wave_hit_kernel(DevScene sc, PathWave cur) {
+template <int MINB>
+__global__ void __launch_bounds__(128, MINB) wave_hit_kernel(DevScene sc, PathWave cur) {
   const unsigned n_spec = cur.count[CLASS_SPEC], n = n_spec + cur.count[CLASS_DIFF];
   for (unsigned t = blockIdx.x * blockDim.x + threadIdx.x; t < n; t += gridDim.x * blockDim.x) {
     const unsigned slot = wave_slot(t, n_spec, cur.cap);
@@ -903,6 +904,8 @@ static int render_accum(GiContext *ctx, const GiParams &params, int sw, int sh, 
   int path_occ = 6;                                       // resident CTAs per SM: 4 (128 registers) or 6 (80 registers)
   if (const char *e = getenv("GI_PATH_OCC")) path_occ = atoi(e);
   const bool megakernel = getenv("GI_PATH_MEGAKERNEL") && atoi(getenv("GI_PATH_MEGAKERNEL")) != 0;      // A/B hook: the round-1 thread-per-path kernel
+  int hit_occ = 6;                                        // resident CTAs per SM wave_hit_kernel is compiled for (registers: 6 -> 80, 4 -> 128, 3 -> 168)
+  if (const char *e = getenv("GI_HIT_OCC")) hit_occ = atoi(e);
   int wave_passes = 4;                                    // wavefront bounce passes per class before the finishing pass
   if (const char *e = getenv("GI_WAVE_PASSES")) wave_passes = std::min(std::max(atoi(e), 0), 64);
 
@@ -963,7 +966,10 @@ static int render_accum(GiContext *ctx, const GiParams &params, int sw, int sh, 
         for (int pass = 0; pass < wave_passes; pass++, cur ^= 1) {
           GI_CUDA(cudaMemsetAsync(wv[cur ^ 1].count, 0, 8, R.st));
           clk.begin(ST_PATH_HIT, R.st);
-          wave_hit_kernel<<<wgrid, 128, 0, R.st>>>(env.sc, wv[cur]);
+          if (hit_occ <= 3) wave_hit_kernel<3><<<wgrid, 128, 0, R.st>>>(env.sc, wv[cur]);
+          else if (hit_occ == 4) wave_hit_kernel<4><<<wgrid, 128, 0, R.st>>>(env.sc, wv[cur]);
+          else if (hit_occ == 5) wave_hit_kernel<5><<<wgrid, 128, 0, R.st>>>(env.sc, wv[cur]);
+          else wave_hit_kernel<6><<<wgrid, 128, 0, R.st>>>(env.sc, wv[cur]);
           clk.end(R.st);
           clk.begin(ST_PATH_SHADE, R.st);
           wave_shade_kernel<MODE_PATH, false><<<wgrid, 128, 0, R.st>>>(env, wv[cur], wv[cur ^ 1], item_rgb.as<double>(), path_qg, path_qc, d_stats + 1);
