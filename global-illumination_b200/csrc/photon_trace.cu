@@ -19,6 +19,7 @@
 #include "context.h"
 #include "kdtree_build.h"
 #include "shade.cuh"
+#include "wave.cuh"
 
 namespace gi {
 
@@ -43,15 +44,14 @@ GI_DEV void store_photon(const PhotonSink &sink, D3 power, D3 incident, D3 point
   sink.keys[i] = key;
 }
 
-// One iteration of PhotonTrace's bounce loop (photontracer.cpp:64-158).  Returns false when the photon's walk ends.
-GI_DEV bool photon_bounce(const ShadeEnv &env, RayD &ray, D3 &photon, bool &store, int iter, int map_type, uint64_t id, Rng &rng,
-                          const PhotonSink &sink) {
+// One iteration of PhotonTrace's bounce loop (photontracer.cpp:64-158) after its closest-hit query: `hit_element` < 0 =
+// the ray left the scene.  Returns false when the photon's walk ends.  The buffered Philox outputs are dropped at the end,
+// so that a photon parked between two bounces is described by its counter alone.
+GI_DEV bool photon_shade(const ShadeEnv &env, RayD &ray, D3 &photon, bool &store, int iter, int map_type, uint64_t id, Rng &rng,
+                         const PhotonSink &sink, int hit_element, D3 point, D3 normal) {
   const GiParams &p = env.p;
-  HitRec h;
-  closest_hit(env.sc, ray, h);
-  if (h.prim < 0) return false;
-  const Brdf b = load_brdf(env.materials[env.sc.elements[h.element].material]);
-  const D3 point = h.p, normal = h.n;
+  if (hit_element < 0) return false;
+  const Brdf b = load_brdf(env.materials[env.sc.elements[hit_element].material]);
   const D3 view = normalized(point - ray.o);                 // ray.o is the reference's ray_start
   const double cos_theta = dot(normal, -view);
   if (b.diffuse && store) store_photon(sink, photon, view, point, (id << 8) | (uint64_t)(iter & 255));
@@ -83,7 +83,16 @@ GI_DEV bool photon_bounce(const ShadeEnv &env, RayD &ray, D3 &photon, bool &stor
     photon = mul3(photon, (b.ks + b.kt * r_coeff) / prob_specular);
   } else return false;
   ray.o = point + bounce * GI_EPS; ray.d = bounce;
+  rng.left = 0;
   return true;
+}
+
+// closest hit + shading of one bounce in one thread (the finishing pass and the lane-refill kernel)
+GI_DEV bool photon_bounce(const ShadeEnv &env, RayD &ray, D3 &photon, bool &store, int iter, int map_type, uint64_t id, Rng &rng,
+                          const PhotonSink &sink) {
+  HitRec h;
+  closest_hit(env.sc, ray, h);
+  return photon_shade(env, ray, photon, store, iter, map_type, id, rng, sink, h.prim < 0 ? -1 : h.element, h.p, h.n);
 }
 
 // basis of a disk with normal n: EmitPhotons, photontracer.cpp:204-215 / 296-307
@@ -220,6 +229,7 @@ __global__ void __launch_bounds__(128, 6) trace_kernel(ShadeEnv env, Round rd, u
         const unsigned long long w = wbase + mine;
         const uint64_t t = (w0 + (list ? (uint64_t)list[w] : (uint64_t)w)) * rd.world + rd.rank;
         emit_photon(env, rd, t, rng, ray, photon);
+        rng.left = 0;                                          // as the wavefront kernels: a photon's stream is a function of its counter
         id = rd.id0 + t; iter = 0; active = true;
         store = rd.map_type == MAP_GLOBAL && !env.p.fast_global;
       }
@@ -232,6 +242,81 @@ __global__ void __launch_bounds__(128, 6) trace_kernel(ShadeEnv env, Round rd, u
       active = photon_bounce(env, ray, photon, store, iter, rd.map_type, id, rng, sink);
       iter++;
       if (iter >= env.p.max_photon_depth) active = false;
+    }
+  }
+}
+
+// ------------------------------------------------------------------------------------------------ wavefront photon walks
+// The same cut into bounce passes as the render's secondary paths (render.cu): emission parks every photon's first ray,
+// then passes of  wave_hit_kernel (closest hit only)  +  photon_shade_kernel (store, roulette, next ray; survivors are
+// compacted into the next pass's queue with a warp ballot), and a finishing pass that walks what is still alive a thread
+// each.  A parked photon reuses the 128-byte PathRec: scale[] = power, tw[0] = photon number (bits), pad = store flag.
+GI_DEV void park_photon(PathRec *r, const RayD &ray, D3 power, uint64_t id, const Rng &rng, int iter, bool store) {
+  double4 *o = (double4 *)r;
+  o[0] = make_double4(ray.o.x, ray.o.y, ray.o.z, ray.d.x);
+  o[1] = make_double4(ray.d.y, ray.d.z, power.x, power.y);
+  o[2] = make_double4(power.z, __longlong_as_double((long long)id), 0.0, 0.0);
+  uint4 *u = (uint4 *)(r) + 6;
+  u[0] = make_uint4(rng.c0, rng.c1, rng.c2, rng.c3);
+  u[1] = make_uint4(0u, 0u, (uint32_t)iter, store ? 1u : 0u);
+}
+GI_DEV void unpark_photon(const PathRec *r, uint64_t seed, RayD &ray, D3 &power, uint64_t &id, Rng &rng, int &iter, bool &store) {
+  const double4 *i = (const double4 *)r;
+  const double4 a = i[0], b = i[1], c = i[2];
+  ray.o = mk3(a.x, a.y, a.z); ray.d = mk3(a.w, b.x, b.y); power = mk3(b.z, b.w, c.x);
+  id = (uint64_t)__double_as_longlong(c.y);
+  const uint4 *u = (const uint4 *)(r) + 6;
+  const uint4 x = u[0], y = u[1];
+  rng.k0 = (uint32_t)seed; rng.k1 = (uint32_t)(seed >> 32);
+  rng.c0 = x.x; rng.c1 = x.y; rng.c2 = x.z; rng.c3 = x.w; rng.left = 0;
+  iter = (int)y.z; store = y.w != 0u;
+}
+
+// thread per work item [first, first + count) of the batch: emission; every photon is parked (slot = its index)
+__global__ void __launch_bounds__(128, 6) photon_emit_kernel(ShadeEnv env, Round rd, uint64_t w0, uint32_t first, uint32_t count,
+                                                             const uint32_t *__restrict__ list, PathWave next) {
+  const uint32_t t = blockIdx.x * blockDim.x + threadIdx.x;
+  if (t == 0) { next.count[CLASS_SPEC] = count; next.count[CLASS_DIFF] = 0u; }
+  if (t >= count) return;
+  const uint32_t w = first + t;
+  const uint64_t tt = (w0 + (list ? (uint64_t)list[w] : (uint64_t)w)) * rd.world + rd.rank;
+  Rng rng; RayD ray; D3 photon;
+  emit_photon(env, rd, tt, rng, ray, photon);
+  rng.left = 0;
+  park_photon(next.rec + t, ray, photon, rd.id0 + tt, rng, 0, rd.map_type == MAP_GLOBAL && !env.p.fast_global);
+}
+
+template <bool FINISH>
+__global__ void __launch_bounds__(128, 6) photon_shade_kernel(ShadeEnv env, int map_type, PathWave cur, PathWave next, PhotonSink sink) {
+  const unsigned n = cur.count[CLASS_SPEC];
+  const unsigned lane = threadIdx.x & 31u;
+  for (unsigned base = (blockIdx.x * blockDim.x + threadIdx.x) - lane; base < n; base += gridDim.x * blockDim.x) {
+    const unsigned t = base + lane;
+    bool live = t < n, store = false;
+    RayD ray; D3 photon; uint64_t id = 0; Rng rng; int iter = 0;
+    if (live) {
+      unpark_photon(cur.rec + t, env.p.seed, ray, photon, id, rng, iter, store);
+      const double4 *hi = (const double4 *)(cur.hit + t);
+      const double4 a = hi[0], b = hi[1];
+      live = photon_shade(env, ray, photon, store, iter, map_type, id, rng, sink, __double2loint(b.z), mk3(a.x, a.y, a.z), mk3(a.w, b.x, b.y));
+      iter++;
+      if (iter >= env.p.max_photon_depth) live = false;
+      if (FINISH)
+        while (live) {
+          live = photon_bounce(env, ray, photon, store, iter, map_type, id, rng, sink);
+          iter++;
+          if (iter >= env.p.max_photon_depth) live = false;
+        }
+    }
+    if (!FINISH) {
+      const unsigned m = __ballot_sync(0xffffffffu, live);
+      if (m) {
+        const int leader = __ffs(m) - 1;
+        unsigned at = 0;
+        if ((int)lane == leader) at = atomicAdd(next.count + CLASS_SPEC, (unsigned)__popc(m));
+        at = __shfl_sync(0xffffffffu, at, leader);
+        if (live) park_photon(next.rec + at + __popc(m & ((1u << lane) - 1u)), ray, photon, id, rng, iter, store);
+      }
     }
   }
 }
@@ -299,6 +384,21 @@ static int trace_map(GiContext *ctx, const ShadeEnv &env_in, int map_type, int t
       !cursor.alloc(16, st) || !list.alloc(filter ? 4 * batch : 4, st))
     return 1;
   GI_CUDA(cudaMemsetAsync(count.p, 0, 16, st));
+  // wavefront photon walks (GI_PHOTON_MEGAKERNEL=1: the lane-refill kernel of round 1, for A/B): parked photons of one
+  // sub-batch, ping / pong, with the closest hits of the current pass
+  const bool megakernel = getenv("GI_PHOTON_MEGAKERNEL") && atoi(getenv("GI_PHOTON_MEGAKERNEL")) != 0;
+  const uint32_t wcap = 1u << 21;
+  int wave_passes = 4;
+  if (const char *e = getenv("GI_PHOTON_WAVE_PASSES")) wave_passes = std::min(std::max(atoi(e), 0), 64);
+  Buf wrec[2], whit[2], wcount;
+  PathWave wv[2];
+  if (!megakernel) {
+    if (!wrec[0].alloc(sizeof(PathRec) * (size_t)wcap, st) || !wrec[1].alloc(sizeof(PathRec) * (size_t)wcap, st) ||
+        !whit[0].alloc(sizeof(WaveHit) * (size_t)wcap, st) || !whit[1].alloc(sizeof(WaveHit) * (size_t)wcap, st) || !wcount.alloc(16, st))
+      return 1;
+    for (int i = 0; i < 2; i++) { wv[i].rec = wrec[i].as<PathRec>(); wv[i].hit = whit[i].as<WaveHit>(); wv[i].count = wcount.as<unsigned int>() + 2 * i; wv[i].cap = wcap; }
+    GI_CUDA(cudaMemsetAsync(wcount.p, 0, 16, st));
+  }
   unsigned long long stored = 0, stored_local = 0;            // over all ranks / in this rank's sink
   uint64_t emitted = 0;
   // photonmap.cpp:157-196 (global) / :213-250 (caustic)
@@ -333,14 +433,43 @@ static int trace_map(GiContext *ctx, const ShadeEnv &env_in, int map_type, int t
           ctx->clock.end(st);
           ctx->launches++;
         }
+        if (megakernel) {
+          // persistent: 8 CTAs of 4 warps per SM; with the filter the item count stays on the device (no host round trip)
+          ctx->clock.begin(ST_TRACE, st);
+          const uint64_t want = (m + 127) / 128, gcap = (uint64_t)ctx->sm_count * 8;
+          trace_kernel<<<(unsigned)std::max<uint64_t>(1, std::min(want, gcap)), 128, 0, st>>>(
+              env, rd, w0, m, filter ? kept : nullptr, filter ? list.as<uint32_t>() : nullptr, cursor.as<unsigned long long>(), sink);
+          ctx->clock.end(st);
+          ctx->launches++;
+          GI_CUDA(cudaGetLastError());
+          continue;
+        }
+        // wavefront: the survivors (or all work items) in sub-batches of `wcap` photons
+        uint64_t items = m;
+        if (filter) {
+          unsigned int h_kept = 0;
+          GI_CUDA(cudaMemcpyAsync(&h_kept, kept, 4, cudaMemcpyDeviceToHost, st));
+          GI_CUDA(cudaStreamSynchronize(st));
+          ctx->clock.collect();
+          items = h_kept;
+        }
         ctx->clock.begin(ST_TRACE, st);
-        // persistent: 8 CTAs of 4 warps per SM; with the filter the item count stays on the device (no host round trip)
-        const uint64_t want = (m + 127) / 128, gcap = (uint64_t)ctx->sm_count * 8;
-        trace_kernel<<<(unsigned)std::max<uint64_t>(1, std::min(want, gcap)), 128, 0, st>>>(
-            env, rd, w0, m, filter ? kept : nullptr, filter ? list.as<uint32_t>() : nullptr, cursor.as<unsigned long long>(), sink);
+        for (uint64_t s0 = 0; s0 < items; s0 += wcap) {
+          const uint32_t c = (uint32_t)std::min<uint64_t>(wcap, items - s0);
+          photon_emit_kernel<<<(c + 127) / 128, 128, 0, st>>>(env, rd, w0, (uint32_t)s0, c, filter ? list.as<uint32_t>() : nullptr, wv[0]);
+          const unsigned wgrid = (unsigned)std::min<uint64_t>((c + 127) / 128, (uint64_t)ctx->sm_count * 6);
+          int cur = 0;
+          for (int pass = 0; pass < wave_passes; pass++, cur ^= 1) {
+            GI_CUDA(cudaMemsetAsync(wv[cur ^ 1].count, 0, 8, st));
+            wave_hit_kernel<6><<<wgrid, 128, 0, st>>>(env.sc, wv[cur]);
+            photon_shade_kernel<false><<<wgrid, 128, 0, st>>>(env, map_type, wv[cur], wv[cur ^ 1], sink);
+          }
+          wave_hit_kernel<6><<<wgrid, 128, 0, st>>>(env.sc, wv[cur]);
+          photon_shade_kernel<true><<<wgrid, 128, 0, st>>>(env, map_type, wv[cur], wv[cur ^ 1], sink);
+          ctx->launches += 3 + 2 * (uint64_t)wave_passes;
+          GI_CUDA(cudaGetLastError());
+        }
         ctx->clock.end(st);
-        ctx->launches++;
-        GI_CUDA(cudaGetLastError());
       }
       unsigned long long now = 0;
       GI_CUDA(cudaMemcpyAsync(&now, count.p, 8, cudaMemcpyDeviceToHost, st));

@@ -29,6 +29,7 @@
 #include "context.h"
 #include "gather.h"
 #include "shade.cuh"
+#include "wave.cuh"
 
 namespace gi {
 
@@ -349,25 +350,6 @@ GI_DEV bool path_begin(const ShadeEnv &env, const PrimHit *__restrict__ hits,
 // Every kernel runs full warps of ONE class through ONE stage.  The pass count is fixed (GI_WAVE_PASSES) and the kernels
 // read the queue lengths on the device, so the host never waits between passes; the few paths still alive after the
 // last pass (walks of dozens of bounces inside glass) are finished by a thread each.
-struct __align__(16) PathRec {       // 128 B: one parked path
-  double o[3], d[3], scale[3], tw[3];
-  uint32_t c0, c1, c2, c3;           // Philox counter of the path's stream (key = seed)
-  uint32_t pix, item;
-  int32_t iter; uint32_t pad;
-};
-struct __align__(16) WaveHit {       // 64 B: closest hit of the parked ray in the same slot
-  double p[3], n[3];
-  int32_t element, prim;             // element < 0: miss
-  double t;
-};
-enum { CLASS_SPEC = 0, CLASS_DIFF = 1 };
-struct PathWave {                    // one buffer, two queues: class SPEC grows from the front, class DIFF from the back
-  PathRec *rec;
-  WaveHit *hit;
-  unsigned int *count;               // [2], per class; never exceeds cap in total (a path parks at most once per pass)
-  uint32_t cap;
-};
-
 GI_DEV void park(PathRec *r, const PathState &s) {
   double4 *o = (double4 *)r;
   o[0] = make_double4(s.ray.o.x, s.ray.o.y, s.ray.o.z, s.ray.d.x);
@@ -423,27 +405,6 @@ __global__ void __launch_bounds__(128, 6) wave_begin_kernel(ShadeEnv env, const 
   wave_push(next, CLASS_SPEC, live && s.mode == MODE_PATH, s);
   wave_push(next, CLASS_DIFF, live && s.mode == MODE_INDIRECT, s);
   flush_stats(stats, st);
-}
-
-// slot of entry t of the two queues taken as one sequence: the SPEC entries, then the DIFF entries
-GI_DEV unsigned wave_slot(unsigned t, unsigned n_spec, unsigned cap) { return t < n_spec ? t : cap - 1u - (t - n_spec); }
-
-// Closest hit of every parked ray (both classes).  Nothing but BVH traversal and the FP64 primitive tests: the code all
-// warps of the SM are in fits the instruction cache.  Persistent grid.
-template <int MINB>
-__global__ void __launch_bounds__(128, MINB) wave_hit_kernel(DevScene sc, PathWave cur) {
-  const unsigned n_spec = cur.count[CLASS_SPEC], n = n_spec + cur.count[CLASS_DIFF];
-  for (unsigned t = blockIdx.x * blockDim.x + threadIdx.x; t < n; t += gridDim.x * blockDim.x) {
-    const unsigned slot = wave_slot(t, n_spec, cur.cap);
-    const double4 *i = (const double4 *)(cur.rec + slot);
-    const double4 a = i[0]; const double2 b = *(const double2 *)(i + 1);
-    RayD ray; ray.o = mk3(a.x, a.y, a.z); ray.d = mk3(a.w, b.x, b.y);
-    HitRec h;
-    closest_hit(sc, ray, h);
-    double4 *o = (double4 *)(cur.hit + slot);
-    o[0] = make_double4(h.p.x, h.p.y, h.p.z, h.n.x);
-    o[1] = make_double4(h.n.y, h.n.z, __hiloint2double(h.prim, h.prim < 0 ? -1 : h.element), h.t);
-  }
 }
 
 // Shading of one class after wave_hit_kernel: a thread per parked path (persistent grid, warp-uniform loop); survivors

@@ -35,12 +35,16 @@ def trace(ctx, case, seed=7):
 
 
 def close_hist(ours, ref, n_ours, n_ref, what):
-    """bins with enough photons agree within 5 sigma of counting noise + 3 %."""
+    """bins with enough photons agree within 5 sigma of counting noise + 3 %, in all but a few bins.  The allowance is 4.5 % of
+    the bins: where photons bounce between specular faces (the `stack` scene) they are stored in bursts, so a handful of
+    cells is overdispersed far beyond counting noise -- 1 to 3 of ~97 bins cross the line at every seed, in either
+    direction (cell 203 of `stack`: -11.6, -9.2, +5.3 sigma at seeds 8, 9, 10; scripts/photon_stat_diag.py), with the
+    lane-refill kernel and with the wavefront kernels alike (their maps are byte-identical)."""
     fo, fr = ours / max(n_ours, 1), ref / max(n_ref, 1)
     big = ref >= 400
     sigma = np.sqrt(fr / n_ref + fr / n_ours)
     bad = np.abs(fo - fr)[big] > 5 * sigma[big] + 0.03 * fr[big]
-    assert bad.mean() < 0.02 if big.any() else True, f"{what}: {bad.sum()} of {big.sum()} bins off"
+    assert bad.mean() < 0.045 if big.any() else True, f"{what}: {bad.sum()} of {big.sum()} bins off"
 
 
 @pytest.mark.parametrize("case", CASES)
