@@ -9,7 +9,8 @@ One "step" = one pass of the hot path over one frame's worth of synthetic input 
      NVLink (N = 1: a device copy) and gi_build_maps builds the left-balanced kd-tree on every rank;
   2. gi_intersect_batch_device over the rank's camera rays -- rank r owns the pixel columns x = r (mod N) of a
      (1024 N) x 1024 aa 2 frame, the renderer's own column split (render.cpp:90), so per-GPU work is fixed (weak scaling);
-  3. gi_gather_batch_device (k = 225, r = 0.225, the reference's caustic defaults) at every primary hit;
+  3. gi_gather_batch_device (k = 225, r = 0.225, the reference's caustic defaults) at every primary hit on a diffuse
+     material -- where RayTrace calls CausticIllumination (raytracer.cpp:138-149);
   4. the rank's radiance goes through clamp / box filter / u8 (torch glue, timed, not counted as ours) and the 8-bit
      column strips are gathered to rank 0 (NCCL), as gi_render does with its strips.
 metric = Mrays/s in the reference's own accounting (render.cpp:224-255 counts gather samples as rays); the stages are
@@ -175,7 +176,8 @@ def make_queries(torch, rays, hits_u8, tables):
     n_all = hits_u8.shape[0] // 72
     hit, f = hits_fields(torch, hits_u8)
     element = hits_u8.view(torch.int32).reshape(n_all, 18)[:, 3]
-    m = hit == 1
+    # RayTrace gathers from the caustic map only where the hit material is diffuse (raytracer.cpp:138-149, 188-190)
+    m = (hit == 1) & ((kd != 0).any(1)[e2m[element.clamp_min(0).long()]])
     d = rays[m, 3:6]; p = f[m, 3:6]; n = f[m, 6:9]
     mat = e2m[element[m].long()]
     cos = -(n * d).sum(1)
@@ -224,7 +226,7 @@ def config_dict(args, world=1):
     n = (args.width << args.aa) * (args.height << args.aa)
     return {"workload": f"input/{SCENE}.scn {args.width}x{args.height} -aa {args.aa} per GPU: photon map of {args.photons} photons "
                         f"(sharded over the ranks, all-gathered, kd-tree built per rank) + closest hit for all {n} primary rays + "
-                        f"caustic-style photon gather (k={K}, r={R}, disk filter) at every primary hit + 8-bit strips to rank 0",
+                        f"caustic-style photon gather (k={K}, r={R}, disk filter) at every DIFFUSE primary hit (where RayTrace gathers) + 8-bit strips to rank 0",
             "photons": args.photons, "k": K, "r": R, "ranks": world,
             "split": "photons/N per rank + one all-gather; pixel columns x = rank (mod N) of a (width x N) frame; strips gathered to rank 0",
             "l2": "inputs larger than L2 (0.8 GB rays, 2.3 GB queries, 0.32 GB photons per step)"}
@@ -279,11 +281,21 @@ def reference_inputs(args, tmp, scn, n_rays, n_queries, threads):
         return read_ref_hits(os.path.join(tmp, "gen.hits"))
 
     rng = np.random.default_rng(1)
+    # which reference shapes are diffuse: `material` lines (ka kd ks kt ke n ir tex) and the material index every shape line of
+    # the (flat) stock scene starts with, in file order = the reference's shape ids
+    mats, shape_mat = [], []
+    for line in open(scn):
+        t = line.split()
+        if not t or t[0].startswith("#"): continue
+        if t[0] == "material": mats.append(any(float(x) != 0.0 for x in t[4:7]))
+        elif t[0] in ("tri", "sphere", "box", "cylinder", "cone", "mesh", "line", "circle"): shape_mat.append(int(t[1]))
+    shape_diffuse = np.array([mats[i] if 0 <= i < len(mats) else True for i in shape_mat] + [True], dtype=bool)
     pick = rng.choice(len(rays), size=min(n_queries, len(rays)), replace=False)
     h = ref_isect(rays)
-    hit_fraction = float((h["hit"] == 1).mean())
+    is_diffuse_hit = (h["hit"] == 1) & shape_diffuse[np.clip(h["shape"], 0, len(shape_diffuse) - 1)]
+    hit_fraction = float(is_diffuse_hit.mean())               # gathers per primary ray of the step
     hq = h[pick]; rq = rays[pick]
-    m = hq["hit"] == 1
+    m = is_diffuse_hit[pick]
     dd = rq[m, 3:6]; n = hq["n"][m]; cos = -(n * dd).sum(1)
     q = np.zeros((int(m.sum()), 17))
     q[:, 0:3] = hq["p"][m]; q[:, 3:6] = n; q[:, 6:9] = dd + 2.0 * cos[:, None] * n; q[:, 9] = cos
