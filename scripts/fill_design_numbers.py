@@ -5,13 +5,14 @@ ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
 P = lambda *a: os.path.join(ROOT, *a)
 B = {n: json.loads(open(P("profiles", f"r02_bench_n{n}.json")).read().strip().splitlines()[-1]) for n in (1, 2, 4, 8)}
 R = json.loads(open(P("profiles", "r02_bench_reference_arm.json")).read().strip().splitlines()[-1])
-d = B[1]; f1 = d["frames"]["cornell_1024_aa2"]; f5 = d["frames"]["cornell_512_aa1"]; f8 = B[8]["frames"]
+d = B[1]; f1 = d["frames"]["cornell_1024_aa2"]; f5 = d["frames"]["cornell_512_aa1"]
+f8 = dict(json.load(open(P("profiles", "r02_frames_all_n8.json")))["frames"]); f8.update(B[8]["frames"])      # configs 3-5 on 8 GPUs: the --frames all run
 st = f1["stage_ms_max_over_ranks"]
 stages = ", ".join(f"{k[:-3].replace('_', ' ')} {v:.0f}" for k, v in sorted(st.items(), key=lambda kv: -kv[1]) if v >= 1.0) + " ms"
 table = f"""| | this repo | reference, 16 host cores |
 |---|---|---|
 | step, 1 × B200: `value` | **{d['value']:.0f} Mrays/s** ({d['ms_per_step']:.1f} ms: replicate {d['stage_ms']['photon_replicate']:.1f}, kd build {d['stage_ms']['kd_build']:.1f}, intersect {d['stage_ms']['intersect']:.2f}, gather {d['stage_ms']['gather']:.1f}, resolve + strips {d['stage_ms']['resolve_glue_and_strip_gather']:.1f}) — round-1 definition (intersect + gather only): {d['value_render_stages_only']:.0f} Mrays/s (372 in round 1) | {R['value']:.3f} Mrays/s (closest hit {R['mrays_per_s_intersect']:.1f} Mrays/s, gather {R['gathers_per_s']/1e3:.1f} k/s, build {R['kd_build_ms']/1e3:.1f} s) |
-| step, 1 × B200: `e2e` (host buffers) | **{d['e2e']['value']:.0f} Mrays/s** ({d['e2e']['ms_per_step']:.0f} ms; compact records: 2.47 GB in + 0.74 GB out per step); with the reference-shaped 72 / 136-byte records {d['e2e']['reference_shaped_records']['value']:.0f} Mrays/s (3.41 + 1.68 GB) | same (host memory is where it lives) |
+| step, 1 × B200: `e2e` (host buffers) | **{d['e2e']['value']:.0f} Mrays/s** ({d['e2e']['ms_per_step']:.0f} ms; compact records: {d['e2e']['h2d_bytes_per_step']/1e9:.2f} GB in + {d['e2e']['d2h_bytes_per_step']/1e9:.2f} GB out per step); with the reference-shaped 72 / 136-byte records {d['e2e']['reference_shaped_records']['value']:.0f} Mrays/s ({d['e2e']['reference_shaped_records']['h2d_bytes_per_step']/1e9:.2f} + {d['e2e']['reference_shaped_records']['d2h_bytes_per_step']/1e9:.2f} GB) | same (host memory is where it lives) |
 | closest hit, jensen primary rays | {d['mrays_per_s_intersect']/1e3:.1f} Grays/s | {R['mrays_per_s_intersect']:.1f} Mrays/s |
 | gather, k 225 on 10⁷ photons | {d['gathers_per_s']/1e6:.0f} M gathers/s = {d['roofline']['achieved']:.0f} GB/s algorithmic = {100*d['roofline']['frac']:.1f} % of the measured 6543 GB/s | {R['gathers_per_s']/1e3:.0f} k/s |
 | gather, k 50 on 2 176 photons (2²³ queries) | {d['gathers_small_map']['gathers_per_s']/1e6:.0f} M gathers/s (443 M with the tree walk); {d['gathers_small_map']['roofline']['warp_instructions_per_gather']:.0f} warp-instructions per gather = {100*d['gathers_small_map']['roofline']['frac']:.0f} % of the issue rate | — |
