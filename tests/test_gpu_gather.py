@@ -126,10 +126,14 @@ def check_rgb(ref, got, rtol=1e-9):
     assert (np.abs(rgb - rrgb) <= rtol * scale + 1e-300).all()
 
 
-@pytest.mark.parametrize("n,k,r,nq", [(100000, 225, 0.05, 6000), (20000, 50, 0.3, 5000), (3000, 512, 2.0, 4500)])
+@pytest.mark.parametrize("n,k,r,nq", [(100000, 225, 0.05, 6000), (20000, 50, 0.3, 5000), (3000, 512, 2.0, 4500),
+                                      # maps of <= 8192 photons with k <= 102: the small-map kernels (chunk pools, a lane per query)
+                                      (2176, 50, 2.5, 6000), (8000, 20, 0.12, 5000), (2000, 100, 0.45, 4200), (500, 50, 0.3, 4100)])
 def test_radiance_only_path_on_sorted_batches(gpu_ctx, oracle, n, k, r, nq):
     """What the renderer and the bench run: no index output (the last cut marks instead of compacting, the candidate
-    buffer is not a power of two) and batches of >= 4096 queries, which are walked along a Morton curve."""
+    buffer is not a power of two) and batches of >= 4096 queries, which are walked along a Morton curve.  The small-map
+    cases cover: every query full (r 2.5), many queries with fewer than k photons in range (r 0.12 / 0.3: the chunk
+    centre's search comes back short), sparse queries whose shells overflow the per-lane lists (histogram path)."""
     ph = synthetic_photons(n, seed=7 * n + k)
     q = surface_queries(nq, seed=k + 1)
     gpu_ctx.load_photons(gi_b200.GI_MAP_CAUSTIC, ph)
