@@ -410,7 +410,7 @@ __device__ __forceinline__ void rank_chunk_per_thread(const PhotonMapDev &m, con
                                                       const GiGatherQuery *__restrict__ queries, uint64_t qi, double qx, double qy, double qz,
                                                       double bound, double shell_lo, int32_t *count_out, double *rgb_out) {
   const int k = ga.k;
-  const int dbg_lane = threadIdx.x & 31;
+  const int lane = threadIdx.x & 31;
   // ---- selection: [lo, hi) narrows around the k-th smallest d2; `below` = candidates with d2 < lo
   double lo = 0.0, hi = __longlong_as_double(__double_as_longlong(bound) + 1);       // d2 <= bound  <=>  d2 < hi
   int below = 0, need = 0;
@@ -422,7 +422,7 @@ __device__ __forceinline__ void rank_chunk_per_thread(const PhotonMapDev &m, con
   {
     // shell lists in shared memory, entry t of lane l: d2 at a_shell + 8 (32 t + l), slot at a_shell + 8 * 32 * S + 2 (32 t + l)
     constexpr int S = GI_SMALL_SHELL;
-    const uint32_t a_sd2 = a_shell + 8u * (uint32_t)dbg_lane, a_ss = a_shell + 8u * 32u * S + 2u * (uint32_t)dbg_lane;
+    const uint32_t a_sd2 = a_shell + 8u * (uint32_t)lane, a_ss = a_shell + 8u * 32u * S + 2u * (uint32_t)lane;
     int nb = 0, ns = 0;
 #pragma unroll 4
     for (int i = 0; i < np; i++) {
@@ -456,7 +456,7 @@ __device__ __forceinline__ void rank_chunk_per_thread(const PhotonMapDev &m, con
         }
       }
       done = true;
-    } else if (dbg_lane == 0) atomicAdd(&g_small_dbg[2], 1ull);
+    } else if (lane == 0) atomicAdd(&g_small_dbg[2], 1ull);
     __syncwarp();
   }
   for (int pass = 0; pass < 3; pass++) {
@@ -545,7 +545,7 @@ __device__ __forceinline__ void rank_chunk_per_thread(const PhotonMapDev &m, con
   //      (32 B each: incident direction + RGBE), so the loop below reads shared memory only.
   __syncwarp();
   if (rgb_out) {
-    for (int i = dbg_lane; i < np; i += 32) {
+    for (int i = lane; i < np; i += 32) {
       const double2 *rec = m.srec + 2 * (size_t)lds_u16(a_pool + 2u * (uint32_t)i);
       const double2 ra = rec[0], rb = rec[1];
       sts_f64(a_shell + 32u * (uint32_t)i, ra.x); sts_f64(a_shell + 32u * (uint32_t)i + 8u, ra.y);
